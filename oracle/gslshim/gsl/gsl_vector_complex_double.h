@@ -1,0 +1,3 @@
+// GSL shim (oracle infrastructure, not product code): see gslshim.h
+#pragma once
+#include "../gslshim.h"
