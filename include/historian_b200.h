@@ -1,0 +1,332 @@
+/* historian_b200 — C ABI of the B200-native hot path of Historian.
+ *
+ * The reference (evoldoers/historian) has no FFI layer: the hot path sits behind
+ * ordinary C++ classes in one binary.  This header is the
+ * thin C boundary UNDER those classes: every entry point names the reference
+ * interface (file:line under the reference's src/) that it replaces.  Plain
+ * pointers and sizes only; no C++ or torch types.  INTEGRATION.md shows how the
+ * reference's classes bind to it.
+ *
+ * Conventions
+ *   - every function returns 0 (HIST_OK) or a negative hist_status; the message
+ *     is available from hist_last_error().  Nothing here throws, aborts or exits
+ *     (the reference's Abort/Fail, util.cpp:28-55, are mapped by the C++ wrapper).
+ *   - "zero forward likelihood" is NOT an error: lp_end = -inf is returned and the
+ *     caller widens the band (recon.cpp:954-975).
+ *   - descriptors (hist_*_desc) are borrowed for the duration of the call only.
+ *   - handles (hist_profile, hist_pair, hist_sumprod) are library-owned device
+ *     objects, released by the matching _destroy.
+ *   - a hist_ctx is bound to one device and one stream and is not thread-safe;
+ *     multi-GPU = one ctx (one process) per device.
+ *   - there is no CPU fallback: hist_ctx_create fails if no CUDA device is usable.
+ *   - PairHMM state order everywhere: IMM=0, IMD=1, IDM=2, IMI=3, IIW=4, EEE=5
+ *     (pairhmm.h:14-18).
+ */
+#ifndef HISTORIAN_B200_H
+#define HISTORIAN_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  HIST_OK = 0,
+  HIST_ERR_ARG = -1,      /* malformed descriptor / argument */
+  HIST_ERR_CUDA = -2,     /* CUDA runtime failure (message holds cudaGetErrorString) */
+  HIST_ERR_NO_DEVICE = -3,/* no usable CUDA device: there is no CPU fallback */
+  HIST_ERR_STATE = -4,    /* call order violated (e.g. trace before fill) */
+  HIST_ERR_CAPACITY = -5, /* caller buffer too small; required size is reported */
+  HIST_ERR_NUMERIC = -6   /* zero likelihood where the reference would Abort */
+} hist_status;
+
+enum { HIST_IMM = 0, HIST_IMD = 1, HIST_IDM = 2, HIST_IMI = 3, HIST_IIW = 4, HIST_EEE = 5, HIST_NSTATES = 5 };
+
+/* Order of the 23 PairHMM log transition weights (pairhmm.h:50-54). */
+enum {
+  HIST_W_IMM_IMM = 0, HIST_W_IMM_IMD, HIST_W_IMM_IDM, HIST_W_IMM_IMI, HIST_W_IMM_IIW, HIST_W_IMM_EEE,
+  HIST_W_IMD_IMM, HIST_W_IMD_IMD, HIST_W_IMD_IDM, HIST_W_IMD_EEE,
+  HIST_W_IDM_IMM, HIST_W_IDM_IMD, HIST_W_IDM_IDM, HIST_W_IDM_EEE,
+  HIST_W_IMI_IMM, HIST_W_IMI_IMD, HIST_W_IMI_IMI, HIST_W_IMI_IIW, HIST_W_IMI_EEE,
+  HIST_W_IIW_IMM, HIST_W_IIW_IDM, HIST_W_IIW_IIW, HIST_W_IIW_EEE,
+  HIST_NWEIGHTS = 23
+};
+
+/* ProfilingStrategy bits (forward.h:42-46). */
+enum {
+  HIST_COLLAPSE_CHAINS = 1, HIST_COUNT_SUBST = 2, HIST_COUNT_INDEL = 4,
+  HIST_INCLUDE_BEST_TRACE = 8, HIST_KEEP_GAPS_OPEN = 16
+};
+
+typedef struct hist_ctx hist_ctx;
+typedef struct hist_profile hist_profile;
+typedef struct hist_pair hist_pair;
+typedef struct hist_sumprod hist_sumprod;
+
+/* A DP cell coordinate: DPMatrix::CellCoords (forward.h:26-38). */
+typedef struct { int32_t xpos, ypos, state; } hist_cell;
+
+/* ------------------------------------------------------------------ T1
+ * Flattened Profile / ProfileState / ProfileTransition (profile.h:13-76).
+ * State 0 is START, state n_states-1 is END; transitions are toposorted
+ * (src < dest, profile.cpp:345,350).  A state is "null" iff is_emit == 0
+ * (profile.h:32); "ready" iff it has no null out-transition (profile.h:36);
+ * a transition is an absorbOut of its source iff its destination emits, else a
+ * nullOut (forward.cpp:828).  Per-state transition lists (state.in, nullOut,
+ * absorbOut) are the transitions in ascending index, which is the order the
+ * reference builds them in. */
+typedef struct {
+  int32_t n_states;
+  int32_t n_trans;
+  int32_t alph_size;                 /* A */
+  int32_t components;                /* C: rate-mixture components */
+  const uint8_t* is_emit;            /* [n_states] */
+  const int32_t* trans_src;          /* [n_trans] */
+  const int32_t* trans_dest;         /* [n_trans] */
+  const double* trans_lp;            /* [n_trans] ProfileTransition::lpTrans */
+  const double* lp_absorb;           /* [n_states][C][A] ProfileState::lpAbsorb; rows of null states are ignored */
+  const int32_t* closest_leaf_pos;   /* [n_states] state.seqCoords.at(closest-leaf row), 0 for START (forward.cpp:36-42); may be NULL when no envelope is used */
+} hist_profile_desc;
+
+/* ------------------------------------------------------------------ T2
+ * PairHMM (pairhmm.h:8-65, pairhmm.cpp:5-44) with the two branch ProbModels
+ * (model.cpp:374-391) and their LogProbModels (model.cpp:492). */
+typedef struct {
+  int32_t alph_size;
+  int32_t components;
+  double lp_trans[HIST_NWEIGHTS];    /* log transition weights, order HIST_W_* */
+  const double* log_root;            /* [C][A] PairHMM::logRoot (log cptWeight folded in, pairhmm.cpp:13-15) */
+  const double* l_sub;               /* [C][A][A] hmm.l.subMat, P(parent a -> child d) */
+  const double* r_sub;               /* [C][A][A] hmm.r.subMat */
+  const double* l_log_ins;           /* [C][A] hmm.logl.logInsProb */
+  const double* r_log_ins;           /* [C][A] hmm.logr.logInsProb */
+  const double* l_log_cpt_weight;    /* [C] hmm.logl.logCptWeight */
+  const double* r_log_cpt_weight;    /* [C] hmm.logr.logCptWeight */
+  double l_t, r_t;                   /* branch lengths (ProbModel::t) */
+  double l_ins_wait, l_del_wait;     /* ProbModel::insWait/delWait */
+  double r_ins_wait, r_del_wait;
+} hist_pairhmm_desc;
+
+/* ------------------------------------------------------------------ T3
+ * GuideAlignmentEnvelope (alignpath.h:43-62, alignpath.cpp:282-310).
+ * max_distance < 0 means "no envelope" (every cell in range) and the arrays may
+ * be NULL.  The band predicate itself is integer and reproduced bit-exactly:
+ * inEnvelope(i,j) = xNearStart[i] || yNearEnd[j] ||
+ *   abs(cum[row1PosToCol[xpos(i)]] - cum[row2PosToCol[ypos(j)]]) <= max_distance
+ * (forward.h:92-98). */
+typedef struct {
+  int32_t max_distance;
+  int32_t n_cols;                    /* guide alignment columns */
+  const int32_t* cumulative_matches; /* [n_cols+1] */
+  int32_t row1_len, row2_len;        /* residues in row1 / row2 */
+  const int32_t* row1_pos_to_col;    /* [row1_len+1] */
+  const int32_t* row2_pos_to_col;    /* [row2_len+1] */
+} hist_env_desc;
+
+typedef struct {
+  int32_t x_size, y_size;            /* profile sizes incl. START and END */
+  int64_t n_cells;                   /* in-envelope (i,j) pairs, i<x_size-1, j<y_size-1: exactly the
+                                        cells visited by forward.cpp:78-86 */
+  int64_t n_stored;                  /* cells allocated in HBM (>= n_cells: band rows are padded to intervals) */
+  int32_t n_diagonals;               /* wavefront steps */
+  int32_t max_diag_width;            /* widest anti-diagonal in stored cells */
+} hist_pair_info;
+
+/* ------------------------------------------------------------------ context */
+int hist_ctx_create(int device, hist_ctx** out);
+void hist_ctx_destroy(hist_ctx* ctx);
+/* Last error message of this context (or of the failed create when ctx == NULL). */
+const char* hist_last_error(const hist_ctx* ctx);
+/* CUDA stream the context launches on (a cudaStream_t), for event timing by the caller. */
+void* hist_ctx_stream(hist_ctx* ctx);
+int hist_ctx_synchronize(hist_ctx* ctx);
+/* Number of kernels this context has launched so far (bench.py's gpu_launches). */
+int64_t hist_ctx_launch_count(const hist_ctx* ctx);
+
+/* ------------------------------------------------------------------ profiles */
+/* Replaces holding a `Profile` value on the host (profile.h:41-76). */
+int hist_profile_upload(hist_ctx* ctx, const hist_profile_desc* desc, hist_profile** out);
+void hist_profile_destroy(hist_profile* p);
+
+/* ------------------------------------------------------------------ DPMatrix
+ * hist_pair_prepare = the DPMatrix constructor (forward.cpp:11-66): leftMultiply
+ * of both profiles (profile.cpp:78-91), the insx/insy/rootsubx/rootsuby tables
+ * (forward.cpp:44-56), xNearStart/yNearEnd (forward.cpp:58-65), closest-leaf band
+ * keys (forward.cpp:36-42), plus the HBM band layout.  All on device. */
+int hist_pair_prepare(hist_ctx* ctx, const hist_profile* x, const hist_profile* y,
+                      const hist_pairhmm_desc* hmm, const hist_env_desc* env, hist_pair** out);
+void hist_pair_destroy(hist_pair* pair);
+int hist_pair_get_info(const hist_pair* pair, hist_pair_info* info);
+
+/* Device results of the constructor tables, as natural-log doubles.
+ * subx/suby: [n_states][C][A] (rows of null states hold -inf); the four scalar
+ * tables: [n_states].  Any pointer may be NULL. */
+int hist_pair_fetch_tables(hist_pair* pair, double* subx, double* suby,
+                           double* insx, double* insy, double* rootsubx, double* rootsuby);
+
+/* Band bookkeeping (bit-exact integers): x_key/y_key are
+ * cum[rowPosToCol[closestLeafPos]] per state, near_start/near_end the edge flags.
+ * in_envelope, if non-NULL, is the full [x_size-1][y_size-1] predicate as bytes
+ * (only sensible for small matrices). */
+int hist_pair_fetch_envelope(hist_pair* pair, int32_t* x_key, int32_t* y_key,
+                             uint8_t* x_near_start, uint8_t* y_near_end, uint8_t* in_envelope);
+
+/* ForwardMatrix::ForwardMatrix fill (forward.cpp:68-223): anti-diagonal
+ * wavefront over the envelope; *lp_end = ForwardMatrix::lpEnd. */
+int hist_fwd_fill(hist_pair* pair, double* lp_end);
+/* BackwardMatrix::BackwardMatrix fill (forward.cpp:975-1097); *lp_start =
+ * BackwardMatrix::lpStart().  Requires hist_fwd_fill first (BackwardMatrix takes
+ * a ForwardMatrix). */
+int hist_bwd_fill(hist_pair* pair, double* lp_start);
+
+/* Batched form used for all sibling merges of one guide-tree depth
+ * (recon.cpp:938-1033 loop, independent iterations): one launch fills every
+ * pair.  do_backward != 0 also runs the Backward fills (concurrently).
+ * lp_end / lp_start: [n] outputs (lp_start may be NULL when !do_backward). */
+int hist_fill_batch(hist_ctx* ctx, hist_pair* const* pairs, int32_t n, int do_backward,
+                    double* lp_end, double* lp_start);
+
+/* DPMatrix::cell for every in-envelope cell, in the row-major order of
+ * DPMatrix::write (forward.cpp:448-464): lp[k*5+s] = natural-log value of state s
+ * of the k-th cell, (xpos[k], ypos[k]) its coordinates.  which: 0 = Forward,
+ * 1 = Backward.  capacity in cells; *n_cells receives the count. */
+int hist_cells_fetch(hist_pair* pair, int which, double* lp, int32_t* xpos, int32_t* ypos,
+                     int64_t capacity, int64_t* n_cells);
+
+/* ------------------------------------------------------------------ traceback
+ * ForwardMatrix::bestTrace(end) (forward.cpp:278-302): greedy arg-max walk from
+ * `end` back to (0,0); candidates ordered by CellCoords::operator<, first strict
+ * maximum wins (forward.cpp:245-255).  The path is returned start-to-end and
+ * includes `end`.  Pass end.state == HIST_EEE at (x_size-1, y_size-1) for the
+ * full trace. */
+int hist_trace_best(hist_pair* pair, hist_cell end, hist_cell* path, int64_t capacity, int64_t* n);
+
+/* ForwardMatrix::sampleTrace (forward.cpp:257-276) with sampleCell
+ * (forward.cpp:225-243).  mt_state is a std::mt19937 state image: 624 words
+ * followed by the position index (625 uint32); it is advanced exactly as
+ * libstdc++'s uniform_real_distribution<double>(0,ptot)(generator) would
+ * (two 32-bit draws per step), so the caller's generator stays in lock-step with
+ * the reference's stream.  n_traces traces are sampled in sequence; path_off
+ * [n_traces+1] delimits them inside `paths`. */
+int hist_trace_sample(hist_pair* pair, uint32_t* mt_state, int32_t n_traces,
+                      hist_cell* paths, int64_t capacity, int64_t* path_off);
+
+/* BackwardMatrix::bestTrace(start) (forward.cpp:1287-1300): greedy forward walk
+ * through the Backward matrix from `start` to EEE (path excludes `start`,
+ * includes EEE). */
+int hist_trace_best_forward(hist_pair* pair, hist_cell start, hist_cell* path, int64_t capacity, int64_t* n);
+
+/* BackwardMatrix::cellsAbovePostProbThreshold (forward.cpp:1302-1319): all
+ * (cell,state) with log posterior F+B-lpEnd >= log(min_post_prob), sorted by
+ * decreasing posterior (the priority_queue pop order), ties by descending
+ * (xpos, ypos, state).  Requires both fills. */
+int hist_posterior_cells(hist_pair* pair, double min_post_prob, hist_cell* cells, double* log_post,
+                         int64_t capacity, int64_t* n);
+
+/* ------------------------------------------------------------------ makeProfile
+ * Numeric core of ForwardMatrix::makeProfile (forward.cpp:686-843): given the
+ * sorted cell set (must contain SSS=(0,0,IMM) and EEE), decide retained cells
+ * (forward.cpp:703-709), run the reverse-order elimination
+ * (forward.cpp:751-807: lpPath by log-sum-exp, lpBestAlignPath by max) and
+ * gather the retained states' absorb tables (forward.cpp:714-727).
+ * Outputs (sizes queried with the *_capacity arguments; HIST_ERR_CAPACITY
+ * reports the needed sizes in n_states/n_trans):
+ *   state_cell[n_states]              retained cells in CellCoords order
+ *   state_lp_absorb[n_states][C][A]   -inf rows for non-absorbing states
+ *   state_fwd_lp[n_states]            meta "fwdLogProb"
+ *   trans_src/dest[n_trans]           indices into state_cell (before addReadyStates)
+ *   trans_lp[n_trans], trans_best_lp[n_trans]
+ *   trans_best_via_off[n_trans+1], trans_best_via[]  eliminated cells along the
+ *                                     best path of each effective transition
+ *                                     (for host-side alignPath assembly) */
+typedef struct {
+  int32_t n_states, n_trans;
+  int64_t n_via;
+  hist_cell* state_cell;
+  double* state_lp_absorb;
+  double* state_fwd_lp;
+  int32_t* trans_src;
+  int32_t* trans_dest;
+  double* trans_lp;
+  double* trans_best_lp;
+  int64_t* trans_best_via_off;
+  hist_cell* trans_best_via;
+  int32_t state_capacity, trans_capacity;
+  int64_t via_capacity;
+} hist_elim_result;
+int hist_profile_eliminate(hist_pair* pair, const hist_cell* cells, int64_t n_cells, int32_t strategy,
+                           hist_elim_result* result);
+
+/* ------------------------------------------------------------------ sum-product
+ * SumProduct / AlignColSumProduct (sumprod.h:32-104, sumprod.cpp).
+ * The model is passed in eigen-decomposed form (EigenModel, model.cpp:1135-1199):
+ * P(t) = V exp(Lambda t) V^-1 clamped to [0,1] (model.cpp:1267-1283) and
+ * eigenSubCount(t) (model.cpp:1329-1350) are built on device per branch. */
+typedef struct {
+  int32_t alph_size;
+  int32_t components;
+  const char* alphabet;              /* [A] residue characters (token order) */
+  const double* cpt_weight;          /* [C] */
+  const double* ins_prob;            /* [C][A] model.insProb */
+  const double* sub_rate;            /* [C][A][A] rate matrices (used for sub counts' R_ij) */
+  const double* eval_re;             /* [C][A] eigenvalues */
+  const double* eval_im;
+  const double* evec_re;             /* [C][A][A] right eigenvectors V[a][k] */
+  const double* evec_im;
+  const double* evec_inv_re;         /* [C][A][A] V^-1[k][b] */
+  const double* evec_inv_im;
+  const double* branch_sub;          /* optional [C][N][A][A]: branch matrices to use verbatim
+                                        (e.g. the reference's expm results); NULL = build from eigen */
+} hist_model_desc;
+
+typedef struct {
+  int32_t n_nodes;                   /* nodes indexed in postorder, children < parent, root last (tree.cpp:141) */
+  const int32_t* parent;             /* [N] parent index, -1 for the root */
+  const double* branch_length;       /* [N] length of the branch above each node */
+} hist_tree_desc;
+
+int hist_sumprod_create(hist_ctx* ctx, const hist_model_desc* model, const hist_tree_desc* tree,
+                        hist_sumprod** out);
+void hist_sumprod_destroy(hist_sumprod* sp);
+
+/* Flat layout of the count buffer: 7 indel slots (unused here, kept so the
+ * buffer is the whole EigenCounts object: ins, del, insExt, delExt, insTime,
+ * delTime, lp), then rootCount[C][A], then eigenCount[C][A][A] as (re,im) pairs. */
+size_t hist_sumprod_counts_size(const hist_sumprod* sp);
+
+enum {
+  HIST_SP_COUNTS = 1,      /* accumulateEigenCounts + accumulateRootCounts (sumprod.cpp:264-271, 294-372) */
+  HIST_SP_MAP_STATES = 2,  /* maxPostState for wildcard rows (sumprod.cpp:259, 398-412) */
+  HIST_SP_NODE_POST = 4    /* logNodePostProb for every ungapped row (sumprod.cpp:208-218) */
+};
+
+/* Processes n_cols independent alignment columns (model.cpp:900-915 loop body):
+ * initColumn, fillUp, fillDown, then whatever `flags` asks for.
+ *   columns      [n_cols][N] bytes: residue char, '-' or '.' for gap, '*' wildcard
+ *                (any char outside the alphabet is a wildcard, sumprod.cpp:67)
+ *   weights      [n_cols] or NULL (=1): weight argument of accumulateEigenCounts
+ *   col_loglike  [n_cols] columnLogLikelihood()
+ *   counts       flat count buffer, ACCUMULATED into (+=); may be a DEVICE pointer
+ *                (then it stays on device for an NCCL all-reduce by the caller)
+ *   map_state    [n_cols][N] bytes: input char with wildcards replaced by the MAP residue
+ *   node_post    [n_cols][N][A] log posteriors (-inf rows for gaps) */
+int hist_sumprod_columns(hist_sumprod* sp, const char* columns, const double* weights, int64_t n_cols,
+                         int32_t flags, double* col_loglike, double* counts, char* map_state,
+                         double* node_post);
+
+/* Fetch E/F/G messages and their log scale factors of ONE column for parity tests
+ * (SumProductStorage, sumprod.h:14-30): each [C][N][A] resp. [C][N]. */
+int hist_sumprod_debug_column(hist_sumprod* sp, const char* column, double* E, double* F, double* G,
+                              double* logE, double* logF, double* logG, double* col_loglike);
+
+/* EigenModel::getSubCounts (model.cpp:1352-1377): eigenbasis counts -> (i,j)
+ * substitution counts and wait times, sub_count[C][A][A] (diagonal = wait time). */
+int hist_sumprod_transform_counts(hist_sumprod* sp, const double* counts, double* root_count,
+                                  double* sub_count);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HISTORIAN_B200_H */

@@ -1,0 +1,182 @@
+"""ctypes binding of oracle/libhist_oracle.so — the CPU checker used by the tests.
+TEST INFRASTRUCTURE: nothing in historian_b200/ imports this."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from historian_b200 import descs as D
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+ORACLE_DIR = os.path.join(os.path.dirname(_HERE), "oracle")
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        so = os.path.join(ORACLE_DIR, "libhist_oracle.so")
+        if not os.path.exists(so):
+            subprocess.check_call(["make", "-s", "-C", ORACLE_DIR, "restatement"])
+        _lib = C.CDLL(so)
+        _lib.oracle_log_sum_exp.restype = C.c_double
+        _lib.oracle_log_sum_exp.argtypes = [C.c_double, C.c_double]
+        _lib.oracle_sum_path_absorb.restype = C.c_double
+    return _lib
+
+
+def set_exact_lse(exact):
+    lib().oracle_set_exact_lse(int(bool(exact)))
+
+
+def _p(a, t):
+    return None if a is None else a.ctypes.data_as(C.POINTER(t))
+
+
+def pair_tables(x, y, hmm, env):
+    """DPMatrix constructor tables and envelope flags (forward.cpp:11-66)."""
+    nx, ny, Cc, A = x.n_states, y.n_states, x.components, x.alph_size
+    r = dict(subx=np.empty((nx, Cc, A)), suby=np.empty((ny, Cc, A)), insx=np.empty(nx), insy=np.empty(ny),
+             rootsubx=np.empty(nx), rootsuby=np.empty(ny), x_key=np.zeros(nx, np.int32), y_key=np.zeros(ny, np.int32),
+             x_near_start=np.zeros(nx, np.uint8), y_near_end=np.zeros(ny, np.uint8),
+             in_envelope=np.zeros((nx - 1, ny - 1), np.uint8))
+    n = C.c_int64()
+    xd, yd, hd, ed = x.desc(), y.desc(), hmm.desc(), env.desc()
+    rc = lib().oracle_pair_tables(C.byref(xd), C.byref(yd), C.byref(hd), C.byref(ed),
+                                  _p(r["subx"], C.c_double), _p(r["suby"], C.c_double), _p(r["insx"], C.c_double),
+                                  _p(r["insy"], C.c_double), _p(r["rootsubx"], C.c_double), _p(r["rootsuby"], C.c_double),
+                                  _p(r["x_key"], C.c_int32), _p(r["y_key"], C.c_int32), _p(r["x_near_start"], C.c_uint8),
+                                  _p(r["y_near_end"], C.c_uint8), _p(r["in_envelope"], C.c_uint8), C.byref(n))
+    assert rc == 0
+    r["n_cells"] = n.value
+    return r
+
+
+def forward(x, y, hmm, env):
+    cells = np.empty((x.n_states - 1, y.n_states - 1, 5))
+    lp = C.c_double()
+    xd, yd, hd, ed = x.desc(), y.desc(), hmm.desc(), env.desc()
+    rc = lib().oracle_forward(C.byref(xd), C.byref(yd), C.byref(hd), C.byref(ed), _p(cells, C.c_double), C.byref(lp))
+    assert rc == 0
+    return cells, lp.value
+
+
+def backward(x, y, hmm, env):
+    cells = np.empty((x.n_states - 1, y.n_states - 1, 5))
+    lp = C.c_double()
+    xd, yd, hd, ed = x.desc(), y.desc(), hmm.desc(), env.desc()
+    rc = lib().oracle_backward(C.byref(xd), C.byref(yd), C.byref(hd), C.byref(ed), _p(cells, C.c_double), C.byref(lp))
+    assert rc == 0
+    return cells, lp.value
+
+
+def _cells_to_np(buf, n):
+    return np.array([[buf[k].xpos, buf[k].ypos, buf[k].state] for k in range(n)], np.int32).reshape(n, 3)
+
+
+def trace_best(x, y, hmm, env, fwd_cells, end):
+    cap = x.n_states + y.n_states + 8
+    buf = (D.Cell * cap)()
+    n = C.c_int64()
+    xd, yd, hd, ed = x.desc(), y.desc(), hmm.desc(), env.desc()
+    rc = lib().oracle_trace_best(C.byref(xd), C.byref(yd), C.byref(hd), C.byref(ed), _p(fwd_cells, C.c_double),
+                                 D.Cell(*end), buf, C.c_int64(cap), C.byref(n))
+    assert rc == 0, rc
+    return _cells_to_np(buf, n.value)
+
+
+def trace_best_forward(x, y, hmm, env, bwd_cells, start):
+    cap = x.n_states + y.n_states + 8
+    buf = (D.Cell * cap)()
+    n = C.c_int64()
+    xd, yd, hd, ed = x.desc(), y.desc(), hmm.desc(), env.desc()
+    rc = lib().oracle_trace_best_forward(C.byref(xd), C.byref(yd), C.byref(hd), C.byref(ed), _p(bwd_cells, C.c_double),
+                                         D.Cell(*start), buf, C.c_int64(cap), C.byref(n))
+    assert rc == 0, rc
+    return _cells_to_np(buf, n.value)
+
+
+def trace_sample(x, y, hmm, env, fwd_cells, mt_state, n_traces):
+    cap = (x.n_states + y.n_states + 8) * n_traces
+    buf = (D.Cell * cap)()
+    off = np.zeros(n_traces + 1, np.int64)
+    st = np.ascontiguousarray(mt_state, np.uint32).copy()
+    xd, yd, hd, ed = x.desc(), y.desc(), hmm.desc(), env.desc()
+    rc = lib().oracle_trace_sample(C.byref(xd), C.byref(yd), C.byref(hd), C.byref(ed), _p(fwd_cells, C.c_double),
+                                   _p(st, C.c_uint32), C.c_int32(n_traces), buf, C.c_int64(cap), _p(off, C.c_int64))
+    assert rc == 0, rc
+    allc = _cells_to_np(buf, int(off[-1]))
+    return [allc[off[k]:off[k + 1]] for k in range(n_traces)], st
+
+
+def posterior_cells(x, y, hmm, env, fwd_cells, bwd_cells, lp_end, min_post):
+    cap = fwd_cells.size
+    buf = (D.Cell * cap)()
+    lpp = np.empty(cap)
+    n = C.c_int64()
+    xd, yd, hd, ed = x.desc(), y.desc(), hmm.desc(), env.desc()
+    rc = lib().oracle_posterior_cells(C.byref(xd), C.byref(yd), C.byref(hd), C.byref(ed), _p(fwd_cells, C.c_double),
+                                      _p(bwd_cells, C.c_double), C.c_double(lp_end), C.c_double(min_post), buf,
+                                      _p(lpp, C.c_double), C.c_int64(cap), C.byref(n))
+    assert rc == 0, rc
+    return _cells_to_np(buf, n.value), lpp[:n.value].copy()
+
+
+class Elim:
+    pass
+
+
+def make_elim_buffers(Cc, A, state_cap, trans_cap, via_cap):
+    e = Elim()
+    e.state_cell = (D.Cell * state_cap)()
+    e.state_lp_absorb = np.empty((state_cap, Cc, A))
+    e.state_fwd_lp = np.empty(state_cap)
+    e.trans_src = np.empty(trans_cap, np.int32)
+    e.trans_dest = np.empty(trans_cap, np.int32)
+    e.trans_lp = np.empty(trans_cap)
+    e.trans_best_lp = np.empty(trans_cap)
+    e.via_off = np.empty(trans_cap + 1, np.int64)
+    e.via = (D.Cell * via_cap)()
+    r = D.ElimResult()
+    r.state_cell = e.state_cell
+    r.state_lp_absorb = _p(e.state_lp_absorb, C.c_double)
+    r.state_fwd_lp = _p(e.state_fwd_lp, C.c_double)
+    r.trans_src, r.trans_dest = _p(e.trans_src, C.c_int32), _p(e.trans_dest, C.c_int32)
+    r.trans_lp, r.trans_best_lp = _p(e.trans_lp, C.c_double), _p(e.trans_best_lp, C.c_double)
+    r.trans_best_via_off = _p(e.via_off, C.c_int64)
+    r.trans_best_via = e.via
+    r.state_capacity, r.trans_capacity, r.via_capacity = state_cap, trans_cap, via_cap
+    e.r = r
+    return e
+
+
+def elim_to_dict(e):
+    r = e.r
+    ns, nt = r.n_states, r.n_trans
+    return dict(state_cell=_cells_to_np(e.state_cell, ns), state_lp_absorb=e.state_lp_absorb[:ns].copy(),
+                state_fwd_lp=e.state_fwd_lp[:ns].copy(), trans_src=e.trans_src[:nt].copy(),
+                trans_dest=e.trans_dest[:nt].copy(), trans_lp=e.trans_lp[:nt].copy(),
+                trans_best_lp=e.trans_best_lp[:nt].copy(), via_off=e.via_off[:nt + 1].copy(),
+                via=_cells_to_np(e.via, int(r.n_via)))
+
+
+def profile_eliminate(x, y, hmm, env, fwd_cells, lp_end, cells, strategy):
+    cells = np.ascontiguousarray(cells, np.int32).reshape(-1, 3)
+    n = len(cells)
+    e = make_elim_buffers(x.components, x.alph_size, n + 4, 8 * n + 64, 8 * n * 8 + 64)
+    xd, yd, hd, ed = x.desc(), y.desc(), hmm.desc(), env.desc()
+    rc = lib().oracle_profile_eliminate(C.byref(xd), C.byref(yd), C.byref(hd), C.byref(ed), _p(fwd_cells, C.c_double),
+                                        C.c_double(lp_end), cells.ctypes.data_as(C.POINTER(D.Cell)), C.c_int64(n),
+                                        C.c_int32(strategy), C.byref(e.r))
+    assert rc == 0, rc
+    return elim_to_dict(e)
+
+
+def sum_path_absorb(p, log_cpt_weight, log_ins_prob):
+    cum = np.empty(p.n_states)
+    w = np.ascontiguousarray(log_cpt_weight, np.float64)
+    ins = np.ascontiguousarray(log_ins_prob, np.float64)
+    pd = p.desc()
+    tot = lib().oracle_sum_path_absorb(C.byref(pd), _p(w, C.c_double), _p(ins, C.c_double), _p(cum, C.c_double))
+    return tot, cum
