@@ -1,0 +1,211 @@
+"""ctypes binding of libhistorian_b200.so (the C ABI in include/historian_b200.h).
+
+There is no CPU fallback: loading fails loudly if the CUDA library has not been
+built, and Context() raises if no CUDA device is usable.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import descs as D
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libhistorian_b200.so")
+_lib = None
+
+
+class HistError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("historian_b200 error %d: %s" % (code, msg))
+        self.code = code
+
+
+def load():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError("%s not found: build it with `python -m historian_b200.build` (needs nvcc). "
+                          "There is no CPU fallback." % LIB_PATH)
+    lib = C.CDLL(LIB_PATH)
+    vp = C.c_void_p
+    lib.hist_ctx_create.argtypes = [C.c_int, C.POINTER(vp)]
+    lib.hist_ctx_destroy.argtypes = [vp]
+    lib.hist_ctx_destroy.restype = None
+    lib.hist_last_error.argtypes = [vp]
+    lib.hist_last_error.restype = C.c_char_p
+    lib.hist_ctx_stream.argtypes = [vp]
+    lib.hist_ctx_stream.restype = vp
+    lib.hist_ctx_synchronize.argtypes = [vp]
+    lib.hist_ctx_launch_count.argtypes = [vp]
+    lib.hist_ctx_launch_count.restype = C.c_int64
+    lib.hist_profile_upload.argtypes = [vp, C.POINTER(D.ProfileDesc), C.POINTER(vp)]
+    lib.hist_profile_destroy.argtypes = [vp]
+    lib.hist_profile_destroy.restype = None
+    lib.hist_pair_prepare.argtypes = [vp, vp, vp, C.POINTER(D.PairHmmDesc), C.POINTER(D.EnvDesc), C.POINTER(vp)]
+    lib.hist_pair_destroy.argtypes = [vp]
+    lib.hist_pair_destroy.restype = None
+    lib.hist_pair_get_info.argtypes = [vp, C.POINTER(D.PairInfo)]
+    lib.hist_pair_fetch_tables.argtypes = [vp] + [D.c_double_p] * 6
+    lib.hist_pair_fetch_envelope.argtypes = [vp, D.c_int32_p, D.c_int32_p, D.c_uint8_p, D.c_uint8_p, D.c_uint8_p]
+    lib.hist_fwd_fill.argtypes = [vp, D.c_double_p]
+    lib.hist_bwd_fill.argtypes = [vp, D.c_double_p]
+    lib.hist_fill_batch.argtypes = [vp, C.POINTER(vp), C.c_int32, C.c_int, D.c_double_p, D.c_double_p]
+    lib.hist_cells_fetch.argtypes = [vp, C.c_int, D.c_double_p, D.c_int32_p, D.c_int32_p, C.c_int64, D.c_int64_p]
+    _lib = lib
+    return lib
+
+
+def _p(a, t):
+    return None if a is None else a.ctypes.data_as(C.POINTER(t))
+
+
+class Context:
+    def __init__(self, device=0):
+        self.lib = load()
+        h = C.c_void_p()
+        rc = self.lib.hist_ctx_create(device, C.byref(h))
+        if rc != 0:
+            raise HistError(rc, self.lib.hist_last_error(None).decode())
+        self.h = h
+        self.device = device
+
+    def check(self, rc):
+        if rc != 0:
+            raise HistError(rc, self.lib.hist_last_error(self.h).decode())
+
+    def close(self):
+        if self.h:
+            self.lib.hist_ctx_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def stream(self):
+        return self.lib.hist_ctx_stream(self.h)
+
+    def synchronize(self):
+        self.check(self.lib.hist_ctx_synchronize(self.h))
+
+    @property
+    def launch_count(self):
+        return int(self.lib.hist_ctx_launch_count(self.h))
+
+    def upload(self, profile):
+        return DeviceProfile(self, profile)
+
+    def prepare(self, x, y, hmm, env=None):
+        return Pair(self, x, y, hmm, env if env is not None else D.Envelope(-1))
+
+    def fill_batch(self, pairs, backward=False):
+        n = len(pairs)
+        arr = (C.c_void_p * n)(*[p.h for p in pairs])
+        lp_end = np.empty(n)
+        lp_start = np.empty(n) if backward else None
+        self.check(self.lib.hist_fill_batch(self.h, arr, n, int(backward), _p(lp_end, C.c_double), _p(lp_start, C.c_double)))
+        return lp_end, lp_start
+
+
+class DeviceProfile:
+    """Device-resident Profile (profile.h:41-76), see hist_profile_upload."""
+
+    def __init__(self, ctx, profile):
+        self.ctx, self.host = ctx, profile
+        d = profile.desc()
+        h = C.c_void_p()
+        ctx.check(ctx.lib.hist_profile_upload(ctx.h, C.byref(d), C.byref(h)))
+        self.h = h
+
+    def close(self):
+        if self.h and self.ctx.h:
+            self.ctx.lib.hist_profile_destroy(self.h)
+        self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Pair:
+    """DPMatrix + ForwardMatrix + BackwardMatrix of one sibling merge (forward.h)."""
+
+    def __init__(self, ctx, x, y, hmm, env):
+        self.ctx, self.x, self.y = ctx, x, y
+        hd, ed = hmm.desc(), env.desc()
+        h = C.c_void_p()
+        ctx.check(ctx.lib.hist_pair_prepare(ctx.h, x.h, y.h, C.byref(hd), C.byref(ed), C.byref(h)))
+        self.h = h
+        info = D.PairInfo()
+        ctx.check(ctx.lib.hist_pair_get_info(self.h, C.byref(info)))
+        self.info = info
+        self.components, self.alph_size = x.host.components, x.host.alph_size
+
+    def close(self):
+        if self.h and self.ctx.h:
+            self.ctx.lib.hist_pair_destroy(self.h)
+        self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def n_cells(self):
+        return int(self.info.n_cells)
+
+    def tables(self):
+        nx, ny, Cc, A = self.info.x_size, self.info.y_size, self.components, self.alph_size
+        r = dict(subx=np.empty((nx, Cc, A)), suby=np.empty((ny, Cc, A)), insx=np.empty(nx), insy=np.empty(ny),
+                 rootsubx=np.empty(nx), rootsuby=np.empty(ny))
+        self.ctx.check(self.ctx.lib.hist_pair_fetch_tables(self.h, *[_p(r[k], C.c_double) for k in
+                                                                      ("subx", "suby", "insx", "insy", "rootsubx", "rootsuby")]))
+        return r
+
+    def envelope(self, full=True):
+        nx, ny = self.info.x_size, self.info.y_size
+        r = dict(x_key=np.zeros(nx, np.int32), y_key=np.zeros(ny, np.int32), x_near_start=np.zeros(nx, np.uint8),
+                 y_near_end=np.zeros(ny, np.uint8))
+        if full:
+            r["in_envelope"] = np.zeros((nx - 1, ny - 1), np.uint8)
+        self.ctx.check(self.ctx.lib.hist_pair_fetch_envelope(self.h, _p(r["x_key"], C.c_int32), _p(r["y_key"], C.c_int32),
+                                                             _p(r["x_near_start"], C.c_uint8), _p(r["y_near_end"], C.c_uint8),
+                                                             _p(r.get("in_envelope"), C.c_uint8)))
+        r["n_cells"] = self.n_cells
+        return r
+
+    def forward(self):
+        lp = C.c_double()
+        self.ctx.check(self.ctx.lib.hist_fwd_fill(self.h, C.byref(lp)))
+        return lp.value
+
+    def backward(self):
+        lp = C.c_double()
+        self.ctx.check(self.ctx.lib.hist_bwd_fill(self.h, C.byref(lp)))
+        return lp.value
+
+    def cells(self, which=0):
+        """(lp [n,5], xpos [n], ypos [n]) in the order of DPMatrix::write."""
+        n = self.n_cells
+        lp = np.empty((max(n, 1), 5))
+        xp, yp = np.empty(max(n, 1), np.int32), np.empty(max(n, 1), np.int32)
+        got = C.c_int64()
+        self.ctx.check(self.ctx.lib.hist_cells_fetch(self.h, which, _p(lp, C.c_double), _p(xp, C.c_int32), _p(yp, C.c_int32),
+                                                     n, C.byref(got)))
+        return lp[:n], xp[:n], yp[:n]
+
+    def cells_dense(self, which=0):
+        """Dense [(nx-1),(ny-1),5] array with -inf where no cell exists (the oracle's layout)."""
+        lp, xp, yp = self.cells(which)
+        out = np.full((self.info.x_size - 1, self.info.y_size - 1, 5), -np.inf)
+        out[xp, yp] = lp
+        return out

@@ -1,0 +1,197 @@
+// Internal layouts shared by the historian_b200 CUDA translation units (sm_100a).
+//
+// Numeric representation of a DP cell (the B200-first design choice):
+// the reference stores 5 natural-log doubles per cell and combines them with a
+// table-driven log-sum-exp (forward.h:14-20, logsumexp.h:42-85).  Here a cell is
+// five FP32 *linear-space* values sharing one int32 base-2 exponent E:
+//     P(state s) = v[s] * 2^E,   natural log = ln(v[s]) + E * ln 2.
+// Predecessor sums become FMAs; the per-cell exponent gives unbounded dynamic
+// range (no underflow to "-inf" that the reference would not have), and the
+// relative error per operation is 2^-24 instead of the reference table's 4.5e-5
+// absolute.  Cells are 24 B (float4 + float2) instead of 40 B.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/historian_b200.h"
+
+namespace hb {
+
+// exponent of an all-zero cell ("-inf" in the reference)
+#define HB_EXP_ZERO (-(1 << 28))
+#define HB_LN2 0.69314718055994530942
+
+// per-state flag bits
+enum { F_EMIT = 1, F_READY = 2 /* isReady() || profile empty */, F_EMIT_OR_START = 4 };
+
+// One side (x or y profile) of a pair, device pointers.
+struct SideDev {
+  int n;                 // states incl. START/END
+  int nt;                // transitions
+  const uint8_t* flags;  // [n]
+  // transitions (profile order)
+  const int* t_src;      // [nt]
+  const int* t_dst;      // [nt]
+  const double* t_lp;    // [nt] natural log (input)
+  float* t_m;            // [nt] mantissa in [1,2): exp(lp - floor(lp/ln2) ln2)
+  int* t_e;              // [nt] floor(lp/ln2) + ex[dst]  (emission exponent of the destination folded in)
+  // CSR lists of transition ids, ascending
+  const int* in_off;  const int* in_idx;    // incoming
+  const int* ao_off;  const int* ao_idx;    // absorbing out (dest emits)
+  const int* no_off;  const int* no_idx;    // null out
+  // emission tables, all relative to 2^ex[i]
+  int* ex;               // [n] floor(max_k sub[i][k] / ln2), 0 for null states
+  float* rs;             // [n] exp(rootsub - ex ln2)   (1 for null states)
+  float* ins;            // [n] exp(ins     - ex ln2)   (1 for null states)
+  float* H;              // [n][K] exp(sub - ex ln2); the y side is pre-multiplied by root[k]
+  // natural-log doubles kept for fetch / makeProfile
+  const double* lp_absorb;  // [n][K] input
+  double* sub;           // [n][K] leftMultiply result (profile.cpp:78-91), -inf rows for null states
+  double* rootsub;       // [n]
+  double* insl;          // [n]
+  // envelope
+  const int* key;        // [n] cum[rowPosToCol[closestLeafPos]]
+  const uint8_t* near_;  // [n] xNearStart / yNearEnd
+  const int* slot;       // [n] edge slot of this row/column, -1 if none
+};
+
+// per anti-diagonal d = i + j
+struct DiagInfo {
+  int ilo;     // first x index of the main interval
+  int width;   // cells in the main interval (may be 0)
+  unsigned off;  // first stored cell of this diagonal
+  int pad;
+};
+
+struct PairDev {
+  SideDev x, y;
+  int K;                  // C * A
+  int C, A;
+  int max_dist;           // <0: no envelope
+  float W[5][6];          // exp(lpTrans[src][dest]), 0 where absent
+  int n_diag;
+  int nS, nE;             // edge slots per diagonal: near-start rows, near-end columns
+  const int* start_rows;  // [nS]
+  const int* end_cols;    // [nE]
+  const DiagInfo* dinfo;  // [n_diag]
+  int max_threads;        // max over d of nS + width + nE
+  unsigned n_stored;
+  float4* fA; float2* fB; // forward cells: (IMM,IMD,IDM,IMI), (IIW, E)
+  float4* bA; float2* bB; // backward cells
+  double* lp_end;         // [1]
+  double* lp_start;       // [1]
+  unsigned long long* n_cells;  // [1] in-envelope cell count
+};
+
+__host__ __device__ inline int hb_iabs(int a) { return a < 0 ? -a : a; }
+
+// 2^sh as a float for sh <= 0 (0 when it would be subnormal)
+__device__ __forceinline__ float pow2_neg(int sh) {
+  return sh < -126 ? 0.f : __int_as_float((sh + 127) << 23);
+}
+
+struct Cell {
+  float v[5];
+  int E;
+};
+
+__device__ __forceinline__ Cell zero_cell() {
+  Cell c;
+#pragma unroll
+  for (int k = 0; k < 5; ++k) c.v[k] = 0.f;
+  c.E = HB_EXP_ZERO;
+  return c;
+}
+
+// Bring the accumulator to exponent max(acc.E, ce); returns the factor by which a
+// contribution expressed at exponent ce must be multiplied.
+__device__ __forceinline__ float acc_align(Cell& a, int ce) {
+  if (ce > a.E) {
+    const float s = pow2_neg(a.E - ce);
+#pragma unroll
+    for (int k = 0; k < 5; ++k) a.v[k] *= s;
+    a.E = ce;
+    return 1.f;
+  }
+  return pow2_neg(ce - a.E);
+}
+
+// Renormalise so that max_k v[k] is in [1,2) (E absorbs the shift).
+__device__ __forceinline__ void cell_normalise(Cell& a) {
+  float m = fmaxf(fmaxf(fmaxf(a.v[0], a.v[1]), fmaxf(a.v[2], a.v[3])), a.v[4]);
+  if (!(m > 0.f)) {
+    a = zero_cell();
+    return;
+  }
+  const int k = ((__float_as_int(m) >> 23) & 0xff) - 127;  // floor(log2 m) for normal m
+  if (k != 0) {
+    // 2^-k may not be representable for k = 127/-127: split in two
+    const int k1 = k / 2, k2 = k - k1;
+    const float s1 = __int_as_float((127 - k1) << 23), s2 = __int_as_float((127 - k2) << 23);
+#pragma unroll
+    for (int q = 0; q < 5; ++q) a.v[q] = a.v[q] * s1 * s2;
+    a.E += k;
+  }
+}
+
+__device__ __forceinline__ double cell_log(float v, int E) {
+  return v > 0.f ? log((double)v) + (double)E * HB_LN2 : -INFINITY;
+}
+
+}  // namespace hb
+
+// ------------------------------------------------------------------ host-side objects
+#include <string>
+#include <vector>
+
+struct hist_ctx {
+  int device;
+  cudaStream_t stream;
+  std::string err;
+  long long launches;
+  int sm_count;
+  size_t smem_optin;
+};
+
+struct hist_profile {
+  hist_ctx* ctx;
+  int n, nt, A, C;
+  // host copies (structure is needed on the host for CSR/layout building)
+  std::vector<uint8_t> is_emit;
+  std::vector<int> t_src, t_dst;
+  std::vector<double> t_lp;
+  std::vector<int> leaf_pos;  // empty if not given
+  bool empty;                 // Profile::isEmpty
+  // device copy of lp_absorb
+  double* d_lp_absorb;
+};
+
+struct hist_pair {
+  hist_ctx* ctx;
+  const hist_profile* x;
+  const hist_profile* y;
+  hb::PairDev dev;      // host copy of the device descriptor (pointers are device pointers)
+  hb::PairDev* d_dev;   // device copy
+  void* slab;           // one allocation holding every per-pair array
+  size_t slab_bytes;
+  hist_pair_info info;
+  bool fwd_done, bwd_done;
+  double lp_end, lp_start;
+  double w_log[6][6];   // natural-log HMM weights (host, for traceback etc.)
+  hist_pairhmm_desc hmm_scalars;  // scalar fields only (pointers nulled)
+  std::vector<int> x_key, y_key;
+  std::vector<uint8_t> x_near, y_near;
+  std::vector<hb::DiagInfo> dinfo;
+  std::vector<int> start_rows, end_cols, x_slot, y_slot;
+};
+
+namespace hb {
+int set_err(hist_ctx* ctx, int code, const char* fmt, ...);
+int check_cuda(hist_ctx* ctx, cudaError_t e, const char* what);
+}  // namespace hb
+
+#define HB_CUDA(ctx, call)                                         \
+  do {                                                             \
+    int _rc = hb::check_cuda((ctx), (call), #call);                \
+    if (_rc) return _rc;                                           \
+  } while (0)

@@ -195,6 +195,9 @@ int hist_fill_batch(hist_ctx* ctx, hist_pair* const* pairs, int32_t n, int do_ba
 int hist_cells_fetch(hist_pair* pair, int which, double* lp, int32_t* xpos, int32_t* ypos,
                      int64_t capacity, int64_t* n_cells);
 
+/* Entry points below this line are declared for the next milestones and are not yet
+ * exported by the library; they become part of the ABI as they are implemented. */
+#ifdef HIST_DECLARE_PLANNED
 /* ------------------------------------------------------------------ traceback
  * ForwardMatrix::bestTrace(end) (forward.cpp:278-302): greedy arg-max walk from
  * `end` back to (0,0); candidates ordered by CellCoords::operator<, first strict
@@ -325,6 +328,8 @@ int hist_sumprod_debug_column(hist_sumprod* sp, const char* column, double* E, d
  * substitution counts and wait times, sub_count[C][A][A] (diagonal = wait time). */
 int hist_sumprod_transform_counts(hist_sumprod* sp, const double* counts, double* root_count,
                                   double* sub_count);
+
+#endif /* HIST_DECLARE_PLANNED */
 
 #ifdef __cplusplus
 }

@@ -7,7 +7,7 @@
 // posterior cells, the parent profile).  tools/make_golden.py turns the dumps
 // into the fixtures under tests/golden/.
 //
-//   ref_dump <out.bin> <node|all> <mode> [historian recon options...]
+//   ref_dump <out.bin> <node[,node...]|all> <mode> [historian recon options...]
 //     mode: sample | best | post   (profile construction used at non-root nodes)
 #include <cstdint>
 #include <cstdio>
@@ -260,7 +260,12 @@ int main(int argc, char** argv) {
       delete forward;
     }
     const bool isRoot = node == dataset.tree.root();
-    const bool want = which == "all" || atoi(which.c_str()) == node;
+    bool want = which == "all";
+    if (!want) {  // comma-separated node list
+      stringstream ws(which);
+      string tok;
+      while (getline(ws, tok, ',')) want = want || atoi(tok.c_str()) == node;
+    }
     const string pfx = "n" + to_string(node) + ".";
     BackwardMatrix* backward = NULL;
     if (want || (mode == "post" && !isRoot)) backward = new BackwardMatrix(*forward);

@@ -1,0 +1,219 @@
+"""GPU parity tests of the DPMatrix constructor tables and the Forward/Backward fills,
+through the C ABI, against (a) the committed golden fixtures produced by the real
+reference and (b) the CPU oracle on seeded synthetic inputs.
+
+Tolerances (stated once, used everywhere below)
+  * integer band/envelope bookkeeping: bit-exact.
+  * constructor tables (leftMultiply, insx, rootsubx): the GPU computes them exactly in
+    FP64 probability space; the reference uses A table log-sum-exps per entry, each up to
+    4.54e-5 low (logsumexp.h:47 truncation) -> |diff| <= A * 4.6e-5 against the golden,
+    <= 1e-9 against the oracle run with the reference's exact (*_slow) log-sum-exp.
+  * Forward/Backward cells and log-likelihoods: north_star's bound is 1e-4 RELATIVE.
+    Against the golden (table LSE): |diff| <= 1e-4*|ref| + 5e-3 (the table error
+    accumulates along the path).  Against the exact-LSE oracle: |diff| <= 2e-6*|ref| + 2e-4
+    (FP32 linear-space mantissas, 2^-24 per operation).
+"""
+import numpy as np
+import pytest
+
+import helpers as H
+import oracle_lib as O
+import synth
+from historian_b200 import descs as D
+
+pytestmark = pytest.mark.gpu
+
+CASES = H.golden_cases()
+REL_GOLD, ABS_GOLD = 1e-4, 5e-3
+REL_EXACT, ABS_EXACT = 2e-6, 2e-4
+
+
+@pytest.fixture(scope="module")
+def goldens():
+    return {f: H.load_golden(f) for f in H.golden_files()}
+
+
+def prepare(ctx, x, y, hmm, env):
+    dx, dy = ctx.upload(x), ctx.upload(y)
+    return ctx.prepare(dx, dy, hmm, env), dx, dy
+
+
+def check_against_oracle(ctx, x, y, hmm, env, what, backward=True):
+    pair, dx, dy = prepare(ctx, x, y, hmm, env)
+    # --- bit-exact integers
+    ot = O.pair_tables(x, y, hmm, env)
+    ge = pair.envelope(full=True)
+    for k in ("x_near_start", "y_near_end", "in_envelope"):
+        assert H.same(ge[k], ot[k]), (what, k)
+    if env.max_distance >= 0:
+        assert H.same(ge["x_key"], ot["x_key"]) and H.same(ge["y_key"], ot["y_key"])
+    assert pair.n_cells == ot["n_cells"], what
+    # --- exact-LSE oracle
+    O.set_exact_lse(True)
+    try:
+        et = O.pair_tables(x, y, hmm, env)
+        efwd, elp_end = O.forward(x, y, hmm, env)
+        ebwd, elp_start = O.backward(x, y, hmm, env) if backward else (None, None)
+    finally:
+        O.set_exact_lse(False)
+    gt = pair.tables()
+    for k in ("subx", "suby", "insx", "insy", "rootsubx", "rootsuby"):
+        H.assert_log_close(gt[k][..., None], et[k][..., None], 1e-12, 1e-9, what=what + ":" + k)
+    lp_end = pair.forward()
+    gfwd = pair.cells_dense(0)
+    H.assert_log_close(gfwd, efwd, REL_EXACT, ABS_EXACT, what=what + ":fwd")
+    if np.isfinite(elp_end):
+        assert abs(lp_end - elp_end) <= REL_EXACT * abs(elp_end) + ABS_EXACT, (what, lp_end, elp_end)
+    else:
+        assert lp_end == elp_end
+    if backward:
+        lp_start = pair.backward()
+        gbwd = pair.cells_dense(1)
+        H.assert_log_close(gbwd, ebwd, REL_EXACT, ABS_EXACT, what=what + ":bwd")
+        if np.isfinite(elp_start):
+            assert abs(lp_start - elp_start) <= REL_EXACT * abs(elp_start) + ABS_EXACT
+            # Forward == Backward (the reference checks this at 1e-2 relative, forward.cpp:1091)
+            assert abs(lp_start - lp_end) <= 1e-5 * abs(lp_end) + 1e-3
+    # --- and the reference's own table arithmetic
+    tfwd, tlp_end = O.forward(x, y, hmm, env)
+    H.assert_log_close(gfwd, tfwd, REL_GOLD, ABS_GOLD, what=what + ":fwd-vs-table")
+    return pair
+
+
+@pytest.mark.parametrize("cid,path,node", CASES, ids=[c[0] for c in CASES])
+def test_golden_fixture(ctx, goldens, cid, path, node):
+    """GPU vs the REAL reference's outputs (golden fixtures)."""
+    d = goldens[path]
+    pfx = "n%d." % node
+    x, y, hmm, env = H.node_inputs(d, node)
+    pair, dx, dy = prepare(ctx, x, y, hmm, env)
+    ge = pair.envelope(full=True)
+    assert H.same(ge["x_near_start"], d[pfx + "x_near_start"])
+    assert H.same(ge["y_near_end"], d[pfx + "y_near_end"])
+    assert H.same(ge["in_envelope"], d[pfx + "in_envelope"])
+    assert pair.n_cells == int(d[pfx + "in_envelope"].sum())
+    A = x.alph_size
+    gt = pair.tables()
+    for k in ("subx", "suby", "insx", "insy", "rootsubx", "rootsuby"):
+        H.assert_log_close(gt[k][..., None], d[pfx + k][..., None], 0.0, (A * x.components + 1) * 4.6e-5, what=cid + ":" + k)
+    lp_end = pair.forward()
+    ref_end = float(d[pfx + "lp_end"][0])
+    assert abs(lp_end - ref_end) <= REL_GOLD * abs(ref_end) + ABS_GOLD, (lp_end, ref_end)
+    H.assert_log_close(pair.cells_dense(0), d[pfx + "fwd"], REL_GOLD, ABS_GOLD, what=cid + ":fwd")
+    lp_start = pair.backward()
+    ref_start = float(d[pfx + "lp_start"][0])
+    assert abs(lp_start - ref_start) <= REL_GOLD * abs(ref_start) + ABS_GOLD
+    H.assert_log_close(pair.cells_dense(1), d[pfx + "bwd"], REL_GOLD, ABS_GOLD, what=cid + ":bwd")
+    # cell order of hist_cells_fetch == DPMatrix::write order (row-major over the envelope)
+    lp, xp, yp = pair.cells(0)
+    ii, jj = np.nonzero(d[pfx + "in_envelope"])
+    assert H.same(xp, ii.astype(np.int32)) and H.same(yp, jj.astype(np.int32))
+
+
+@pytest.mark.parametrize("cid,path,node", CASES[:6], ids=[c[0] for c in CASES[:6]])
+def test_golden_inputs_vs_exact_oracle(ctx, goldens, cid, path, node):
+    x, y, hmm, env = H.node_inputs(goldens[path], node)
+    check_against_oracle(ctx, x, y, hmm, env, cid)
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_synthetic_dag_profiles(ctx, seed):
+    """Random state DAGs with null/wait/ready states, skip transitions, mixtures, with and
+    without band, monotone and non-monotone closest-leaf coordinates."""
+    rng = np.random.default_rng(1000 + seed)
+    A = [4, 20, 4, 20, 7, 20, 4, 61][seed]
+    C = [1, 1, 2, 1, 3, 4, 1, 1][seed]
+    nx, ny = int(rng.integers(5, 70)), int(rng.integers(5, 70))
+    x = synth.random_profile(rng, nx, A, C, one_hot=seed % 2 == 0, jitter_leaf=seed >= 4)
+    y = synth.random_profile(rng, ny, A, C, one_hot=seed % 2 == 0, jitter_leaf=seed >= 4)
+    hmm = synth.random_hmm(rng, A, C)
+    env = D.Envelope(-1) if seed % 3 == 0 else synth.random_envelope(rng, x, y, int(rng.integers(0, 8)))
+    check_against_oracle(ctx, x, y, hmm, env, "synth%d" % seed)
+
+
+def test_leaf_pair_banded_1000(ctx):
+    """Leaf x leaf merge of ~1000-residue amino sequences inside the default band (20): the
+    BASELINE config-3 cherry shape, at full size (the oracle needs a few seconds)."""
+    rng = np.random.default_rng(7)
+    alphabet = "arndcqeghilkmfpstwyv"
+    x, y, (r1, r2) = synth.leaf_pair(rng, alphabet, 1000, 990)
+    hmm = synth.random_hmm(rng, 20, 1, tl=0.05, tr=0.05)
+    env = D.Envelope.from_guide_rows(r1, r2, 20)
+    pair = check_against_oracle(ctx, x, y, hmm, env, "leaf1000")
+    assert pair.info.max_diag_width <= 48
+
+
+def test_leaf_pair_unbanded_300(ctx):
+    rng = np.random.default_rng(8)
+    alphabet = "acgt"
+    x, y, _ = synth.leaf_pair(rng, alphabet, 300, 280)
+    hmm = synth.random_hmm(rng, 4, 2)
+    x = D.Profile(x.is_emit, x.trans_src, x.trans_dest, x.trans_lp, np.repeat(x.lp_absorb, 2, axis=1), x.closest_leaf_pos)
+    y = D.Profile(y.is_emit, y.trans_src, y.trans_dest, y.trans_lp, np.repeat(y.lp_absorb, 2, axis=1), y.closest_leaf_pos)
+    check_against_oracle(ctx, x, y, hmm, D.Envelope(-1), "leaf300-noband")
+
+
+def test_edge_cases_empty_and_tiny(ctx):
+    """Zero-length sequences (xEmpty / yEmpty, forward.cpp:16-17,97; the reference's testzerolen)
+    and single-residue sequences."""
+    rng = np.random.default_rng(3)
+    alphabet = "acgt"
+    hmm = synth.random_hmm(rng, 4, 1)
+    for sx, sy in (("", ""), ("", "acg"), ("a", ""), ("a", "c"), ("ac", "a")):
+        x, y = D.Profile.from_sequence(sx, alphabet), D.Profile.from_sequence(sy, alphabet)
+        check_against_oracle(ctx, x, y, hmm, D.Envelope(-1), "tiny-%s-%s" % (sx, sy))
+
+
+def test_zero_likelihood_band_is_not_an_error(ctx):
+    """lpEnd = -inf must come back as a value (the caller widens the band, recon.cpp:956-975)."""
+    rng = np.random.default_rng(5)
+    alphabet = "acgt"
+    x, y = D.Profile.from_sequence("a" * 30, alphabet), D.Profile.from_sequence("c" * 3, alphabet)
+    hmm = synth.random_hmm(rng, 4, 1)
+    # guide: all of x first, then y: band 0 leaves no path from start to end
+    r1 = np.array([1] * 30 + [0] * 3, bool)
+    r2 = np.array([0] * 30 + [1] * 3, bool)
+    env = D.Envelope.from_guide_rows(r1, r2, 0)
+    ofwd, olp = O.forward(x, y, hmm, env)
+    pair, dx, dy = prepare(ctx, x, y, hmm, env)
+    lp = pair.forward()
+    assert lp == olp or abs(lp - olp) < 1e-3 + 1e-4 * abs(olp)
+
+
+def test_batch_fill_matches_single(ctx):
+    """hist_fill_batch (one launch for all sibling merges of a level) == per-pair fills."""
+    rng = np.random.default_rng(11)
+    alphabet = "arndcqeghilkmfpstwyv"
+    hmm = synth.random_hmm(rng, 20, 1, tl=0.1, tr=0.2)
+    pairs, keep, singles = [], [], []
+    for k in range(9):
+        x, y, (r1, r2) = synth.leaf_pair(rng, alphabet, 60 + 7 * k, 50 + 11 * k)
+        env = D.Envelope.from_guide_rows(r1, r2, 5 + k)
+        p, dx, dy = prepare(ctx, x, y, hmm, env)
+        q, ex, ey = prepare(ctx, x, y, hmm, env)
+        pairs.append(p); keep += [dx, dy, ex, ey]; singles.append(q)
+    lp_end, lp_start = ctx.fill_batch(pairs, backward=True)
+    for k, q in enumerate(singles):
+        assert q.forward() == lp_end[k]
+        assert q.backward() == lp_start[k]
+        assert H.same(q.cells_dense(0), pairs[k].cells_dense(0))
+        assert H.same(q.cells_dense(1), pairs[k].cells_dense(1))
+
+
+def test_errors_are_reported_not_thrown(ctx):
+    from historian_b200 import capi
+    alphabet = "acgt"
+    x = D.Profile.from_sequence("acgt", alphabet)
+    bad = D.Profile(x.is_emit, x.trans_dest, x.trans_src, x.trans_lp, x.lp_absorb)  # src > dest
+    with pytest.raises(capi.HistError) as e:
+        ctx.upload(bad)
+    assert e.value.code == -1 and "toposorted" in str(e.value)
+    hmm20 = synth.random_hmm(np.random.default_rng(1), 20, 1)
+    dx = ctx.upload(x)
+    with pytest.raises(capi.HistError):
+        ctx.prepare(dx, dx, hmm20)  # alphabet mismatch
+    hmm = synth.random_hmm(np.random.default_rng(1), 4, 1)
+    pair = ctx.prepare(dx, dx, hmm)
+    with pytest.raises(capi.HistError) as e:
+        pair.backward()  # BackwardMatrix needs a ForwardMatrix
+    assert e.value.code == -4
