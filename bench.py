@@ -1,0 +1,326 @@
+#!/usr/bin/env python3
+"""Benchmark of the hot path: banded profile Forward/Backward fills (metric: cells/s, GCUPS).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+Workload (BASELINE.json configs[2], the configuration the metric's target is quoted on): a
+synthetic LG protein family, 1024 sequences x ~1000 residues on a balanced tree (branch length
+0.05), simulated with a fixed seed (historian_b200/simulator.py: the reference simulator's
+algorithm; the reference binary itself needs >10 h for 1024 leaves, see that file).  One STEP =
+the Forward AND Backward fill (forward.cpp:68-223, 975-1097) of all 512 sibling merges of the
+deepest guide-tree level (leaf x leaf, guide band 20: recon.cpp:954-984), one batched launch.
+A cell = one in-envelope (i,j) of one matrix with all five states (forward.cpp:78-86); a step
+updates 2 * sum(n_cells) cells.  N GPUs: weak scaling, every rank fills the 512 merges of its own
+family (seed 1 + rank), no data-path collective (the reference loops over datasets the same way,
+recon.cpp:1368-1372).
+
+Prints ONE JSON line (rank 0).  `value`: inputs resident in HBM.  `e2e`: the same step through
+the C ABI from HOST buffers (profile upload + DPMatrix preparation + fills + likelihood read-back
+inside the timed region).  `roofline`: the fill kernel alone, CUDA events on its own stream.
+`cpu_baseline`: the unmodified reference (oracle/_ref/bin/ref_time) on a bounded sample.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+BAND = 20
+BRANCH = 0.05
+N_LEAVES = 1024
+ROOT_LEN = 1000
+ALG_BYTES_PER_CELL = 80.0   # 40 B written once + 40 B read once per DP cell (reference layout)
+METRIC = "profile Forward/Backward cells/s (GCUPS)"
+UNIT = "Gcells/s"
+
+
+def make_family(seed):
+    from historian_b200 import model as M, simulator as S
+    tree = S.Tree.balanced(N_LEAVES, BRANCH)
+    lg = M.RateModel.preset("lg")
+    gapped, _ = S.simulate_family(lg, tree, ROOT_LEN, seed)
+    _, guide = S.leaf_guide(tree, gapped)
+    return lg, guide
+
+
+def cherry_inputs(lg, guide, n_pairs):
+    """Flattened inputs of the leaf x leaf merges (rows 2k, 2k+1 of the guide)."""
+    from historian_b200 import descs as D, model as M
+    hmm = M.pair_hmm(lg, BRANCH, BRANCH)
+    out = []
+    gap = ord("-")
+    for k in range(n_pairs):
+        r1, r2 = guide[2 * k], guide[2 * k + 1]
+        x = D.Profile.from_sequence(bytes(r1[r1 != gap]).decode(), lg.alphabet, lg.components)
+        y = D.Profile.from_sequence(bytes(r2[r2 != gap]).decode(), lg.alphabet, lg.components)
+        env = D.Envelope.from_guide_rows(r1 != gap, r2 != gap, BAND)
+        out.append((x, y, env))
+    return hmm, out
+
+
+def write_fasta(path, guide):
+    with open(path, "w") as f:
+        for k, row in enumerate(guide):
+            f.write(">s%04d\n%s\n" % (k, bytes(row).decode()))
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.stop_flag, self.rows = index, threading.Event(), []
+
+    def run(self):
+        while not self.stop_flag.is_set():
+            try:
+                o = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits"],
+                                   capture_output=True, text=True, timeout=5).stdout.strip()
+                if o:
+                    self.rows.append([c.strip() for c in o.split(",")])
+            except Exception:
+                pass
+            self.stop_flag.wait(0.2)
+
+    def summary(self):
+        self.stop_flag.set()
+        self.join(timeout=6)
+        sm, mx, reasons = [], 0.0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx = max(mx, float(r[1]))
+            except Exception:
+                continue
+            for n, v in zip(names, r[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ------------------------------------------------------------------ CPU side (reference arm and cpu_baseline)
+REF_TIME = os.path.join(ROOT, "oracle", "_ref", "bin", "ref_time")
+
+
+def run_ref_time(fasta, first, count, procs):
+    """The unmodified reference's ForwardMatrix+BackwardMatrix on `count` cherries starting at
+    `first`, spread over `procs` single-threaded processes (the reference has no threads).
+    Returns (cells updated [both matrices], wall seconds of the slowest-finishing set)."""
+    per = [count // procs + (1 if p < count % procs else 0) for p in range(procs)]
+    jobs, start = [], first
+    t0 = time.perf_counter()
+    for p in range(procs):
+        if per[p] == 0:
+            continue
+        jobs.append(subprocess.Popen([REF_TIME, "lg", fasta, str(BAND), str(BRANCH), str(BRANCH), str(start), str(per[p])],
+                                     stdout=subprocess.PIPE, text=True))
+        start += per[p]
+    outs = [json.loads(j.communicate()[0]) for j in jobs]
+    wall = time.perf_counter() - t0
+    for j in jobs:
+        if j.returncode != 0:
+            raise RuntimeError("ref_time failed")
+    return 2 * sum(o["cells"] for o in outs), wall, outs
+
+
+def cpu_baseline(guide, sample_pairs, procs):
+    if not os.path.exists(REF_TIME):
+        return {"value": None, "unit": UNIT, "cores": procs, "kind": "reference",
+                "sample": "oracle/_ref/bin/ref_time missing (build with __graft_entry__.build() where /root/reference exists)"}
+    with tempfile.TemporaryDirectory() as tmp:
+        fa = os.path.join(tmp, "leaves.fa")
+        write_fasta(fa, guide[:2 * sample_pairs])
+        cells, wall, _ = run_ref_time(fa, 0, sample_pairs, procs)
+    return {"value": cells / wall / 1e9, "unit": UNIT, "cores": procs, "kind": "reference",
+            "sample": "%d of the 512 leaf x leaf merges (Forward+Backward, band %d), unmodified reference ForwardMatrix/BackwardMatrix "
+                      "via oracle/_ref/bin/ref_time, %d single-threaded process(es), %.1f s wall" % (sample_pairs, BAND, procs, wall)}
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    if not os.path.exists(REF_TIME):
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/bin/ref_time not built (needs /root/reference at build time)"}))
+        return
+    lg, guide = make_family(1)
+    # one step = a bounded sample: 4 cherries per core (about 0.15 s of CPU work each)
+    per_step = min(512, 4 * cores)
+    with tempfile.TemporaryDirectory() as tmp:
+        fa = os.path.join(tmp, "leaves.fa")
+        write_fasta(fa, guide)
+        for w in range(args.warmup):
+            run_ref_time(fa, (w * per_step) % (512 - per_step + 1), per_step, cores)
+        cells, wall = 0, 0.0
+        for s in range(args.steps):
+            c, t, _ = run_ref_time(fa, (s * per_step) % (512 - per_step + 1), per_step, cores)
+            cells += c
+            wall += t
+    v = cells / wall / 1e9
+    sample = "%d leaf x leaf merges per step (Forward+Backward, band %d) on %d single-threaded processes" % (per_step, BAND, cores)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * wall / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic", "config": workload_config(512),
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}))
+
+
+def workload_config(pairs):
+    return {"workload": "lg_1024x1000_seed1 level-0 sibling merges (leaf x leaf), Forward+Backward fill, guide band %d" % BAND,
+            "family": "LG, %d leaves x %d root residues, balanced tree, branch %.2f, insrate=delrate=0.01" % (N_LEAVES, ROOT_LEN, BRANCH),
+            "merges_per_step_per_gpu": pairs, "band": BAND, "alphabet": 20, "components": 1,
+            "l2_policy": "cell planes written per step (>1 GB) exceed the 126 MB L2; no reuse between steps"}
+
+
+# ------------------------------------------------------------------ GPU arm
+def gpu_arm(args):
+    import torch
+    import torch.distributed as dist
+    from historian_b200 import capi
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; historian_b200 has no CPU fallback (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    n_pairs = args.pairs
+    lg, guide = make_family(1 + rank)
+    hmm, inputs = cherry_inputs(lg, guide, n_pairs)
+    ctx = capi.Context(local)
+    stream = torch.cuda.ExternalStream(ctx.stream, device=local)
+
+    # ---- resident inputs: profiles uploaded, DPMatrix tables prepared once
+    profs = [(ctx.upload(x), ctx.upload(y)) for x, y, _ in inputs]
+    pairs = [ctx.prepare(dx, dy, hmm, env) for (dx, dy), (_, _, env) in zip(profs, inputs)]
+    cells_per_step = 2 * sum(p.n_cells for p in pairs)
+
+    def step_resident():
+        return ctx.fill_batch(pairs, backward=True)
+
+    for _ in range(args.warmup):
+        lp_end, lp_start = step_resident()
+    assert np.all(np.isfinite(lp_end)) and np.allclose(lp_end, lp_start, rtol=1e-5, atol=1e-3), "Forward != Backward likelihood"
+    ctx.set_timing(True)
+    ctx.fill_time_ms()
+    launches0 = ctx.launch_count
+    clocks = ClockSampler(local)
+    clocks.start()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        step_resident()
+    e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    clk = clocks.summary()
+    launches = ctx.launch_count - launches0
+    kernel_ms, kernel_launches = ctx.fill_time_ms()
+    ctx.set_timing(False)
+
+    # ---- end to end from host buffers through the public C-ABI calls
+    def step_e2e():
+        pp = [(ctx.upload(x), ctx.upload(y)) for x, y, _ in inputs]
+        pr = [ctx.prepare(dx, dy, hmm, env) for (dx, dy), (_, _, env) in zip(pp, inputs)]
+        r = ctx.fill_batch(pr, backward=True)
+        h2d = sum(x.lp_absorb.nbytes + y.lp_absorb.nbytes for x, y, _ in inputs) + sum(int(p.info.h2d_bytes) for p in pr)
+        for p in pr:
+            p.close()
+        for a, b in pp:
+            a.close(); b.close()
+        return r, h2d
+
+    for _ in range(min(args.warmup, 2)):
+        step_e2e()
+    barrier()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record(stream)
+    e2e_steps = max(1, min(args.steps, 5))
+    for _ in range(e2e_steps):
+        (lp_e, lp_s), h2d_bytes = step_e2e()
+    f1.record(stream)
+    barrier()
+    e2e_ms = f0.elapsed_time(f1)
+
+    t = torch.tensor([ms, e2e_ms, kernel_ms], dtype=torch.float64, device="cuda")
+    c = torch.tensor([float(cells_per_step)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(c, op=dist.ReduceOp.SUM)
+    ms, e2e_ms, kernel_ms = t.tolist()
+    total_cells_per_step = c.item()
+
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        per_launch_s = kernel_ms / 1e3 / max(1, kernel_launches)
+        achieved = cells_per_step * ALG_BYTES_PER_CELL / per_launch_s / 1e9
+        cores = os.cpu_count() or 1
+        base = cpu_baseline(guide, args.cpu_pairs, 1) if world == 1 else None
+        line = {
+            "metric": METRIC, "value": total_cells_per_step * args.steps / (ms / 1e3) / 1e9, "unit": UNIT, "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32 mantissas + int32 exponent per cell (f64 tables and likelihoods)", "data": "synthetic",
+            "config": workload_config(n_pairs),
+            "e2e": {"value": total_cells_per_step * e2e_steps / (e2e_ms / 1e3) / 1e9, "unit": UNIT,
+                    "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": int(n_pairs * 24), "steps": e2e_steps,
+                    "host_memory": "pageable numpy buffers borrowed by the C ABI"},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "kernel": "hb::fill_kernel", "launches_timed": int(kernel_launches),
+                         "avg_launch_ms": 1e3 * per_launch_s, "algorithmic_bytes_per_cell": ALG_BYTES_PER_CELL,
+                         "cells_per_launch": int(cells_per_step),
+                         "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"},
+            "cpu_baseline": base, "clocks": clk, "cpu_cores": cores,
+        }
+        print(json.dumps(line))
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--pairs", type=int, default=512, help="sibling merges per step per GPU")
+    ap.add_argument("--cpu-pairs", type=int, default=96, help="merges in the cpu_baseline sample (about 15 s on one core)")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        reference_arm(args)
+    else:
+        gpu_arm(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -40,6 +40,8 @@ def load():
     lib.hist_ctx_synchronize.argtypes = [vp]
     lib.hist_ctx_launch_count.argtypes = [vp]
     lib.hist_ctx_launch_count.restype = C.c_int64
+    lib.hist_ctx_set_timing.argtypes = [vp, C.c_int]
+    lib.hist_ctx_fill_time_ms.argtypes = [vp, D.c_double_p, D.c_int64_p]
     lib.hist_profile_upload.argtypes = [vp, C.POINTER(D.ProfileDesc), C.POINTER(vp)]
     lib.hist_profile_destroy.argtypes = [vp]
     lib.hist_profile_destroy.restype = None
@@ -96,6 +98,15 @@ class Context:
     @property
     def launch_count(self):
         return int(self.lib.hist_ctx_launch_count(self.h))
+
+    def set_timing(self, enabled=True):
+        self.check(self.lib.hist_ctx_set_timing(self.h, int(enabled)))
+
+    def fill_time_ms(self):
+        """(summed fill-kernel milliseconds, launches) since the last call; CUDA events on the ctx stream."""
+        ms, n = C.c_double(), C.c_int64()
+        self.check(self.lib.hist_ctx_fill_time_ms(self.h, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
 
     def upload(self, profile):
         return DeviceProfile(self, profile)

@@ -203,6 +203,7 @@ extern "C" int hist_ctx_create(int device, hist_ctx** out) {
   hist_ctx* ctx = new hist_ctx();
   ctx->device = device;
   ctx->launches = 0;
+  ctx->timing = false;
   e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
   if (e != cudaSuccess) {
     set_err(nullptr, HIST_ERR_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(e));
@@ -221,6 +222,7 @@ extern "C" void hist_ctx_destroy(hist_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
+  for (auto& e : ctx->fill_events) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
   cudaStreamDestroy(ctx->stream);
   delete ctx;
 }
@@ -230,6 +232,28 @@ extern "C" void* hist_ctx_stream(hist_ctx* ctx) { return ctx ? (void*)ctx->strea
 extern "C" int hist_ctx_synchronize(hist_ctx* ctx) {
   if (!ctx) return HIST_ERR_ARG;
   HB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return HIST_OK;
+}
+extern "C" int hist_ctx_set_timing(hist_ctx* ctx, int enabled) {
+  if (!ctx) return HIST_ERR_ARG;
+  ctx->timing = enabled != 0;
+  return HIST_OK;
+}
+extern "C" int hist_ctx_fill_time_ms(hist_ctx* ctx, double* total_ms, int64_t* n_launches) {
+  if (!ctx || !total_ms) return HIST_ERR_ARG;
+  cudaSetDevice(ctx->device);
+  double tot = 0;
+  for (auto& e : ctx->fill_events) {
+    HB_CUDA(ctx, cudaEventSynchronize(e.second));
+    float ms = 0;
+    HB_CUDA(ctx, cudaEventElapsedTime(&ms, e.first, e.second));
+    tot += ms;
+    cudaEventDestroy(e.first);
+    cudaEventDestroy(e.second);
+  }
+  *total_ms = tot;
+  if (n_launches) *n_launches = (int64_t)ctx->fill_events.size();
+  ctx->fill_events.clear();
   return HIST_OK;
 }
 extern "C" int64_t hist_ctx_launch_count(const hist_ctx* ctx) { return ctx ? ctx->launches : 0; }
@@ -610,6 +634,7 @@ extern "C" int hist_pair_prepare(hist_ctx* ctx, const hist_profile* x, const his
   pr->info.n_stored = nStored;
   pr->info.n_diagonals = nDiag;
   pr->info.max_diag_width = maxWidth;
+  pr->info.h2d_bytes = (int64_t)(o_host_end + sizeof(PairDev));
   *out = pr;
   return HIST_OK;
 }

@@ -442,8 +442,18 @@ int launch_fill(hist_ctx* ctx, hist_pair* const* pairs, int n, int n_dir, int on
   PairDev** dptrs = nullptr;
   HB_CUDA(ctx, cudaMallocAsync((void**)&dptrs, n * sizeof(PairDev*), ctx->stream));
   HB_CUDA(ctx, cudaMemcpyAsync(dptrs, h.data(), n * sizeof(PairDev*), cudaMemcpyHostToDevice, ctx->stream));
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (ctx->timing) {
+    HB_CUDA(ctx, cudaEventCreate(&e0));
+    HB_CUDA(ctx, cudaEventCreate(&e1));
+    HB_CUDA(ctx, cudaEventRecord(e0, ctx->stream));
+  }
   fill_kernel<<<n * n_dir, block, smem, ctx->stream>>>(dptrs, n_dir, only_dir, ring_cap);
   ctx->launches += 1;
+  if (ctx->timing) {
+    HB_CUDA(ctx, cudaEventRecord(e1, ctx->stream));
+    ctx->fill_events.push_back({e0, e1});
+  }
   HB_CUDA(ctx, cudaGetLastError());
   HB_CUDA(ctx, cudaFreeAsync(dptrs, ctx->stream));
   // h[] is pageable host memory: the copy above must finish before it goes out of scope

@@ -151,6 +151,9 @@ struct hist_ctx {
   long long launches;
   int sm_count;
   size_t smem_optin;
+  // optional per-kernel timing of the fill launches (bench.py's roofline leg)
+  bool timing;
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> fill_events;
 };
 
 struct hist_profile {

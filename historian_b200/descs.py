@@ -56,7 +56,7 @@ class EnvDesc(C.Structure):
 class PairInfo(C.Structure):
     _fields_ = [
         ("x_size", C.c_int32), ("y_size", C.c_int32), ("n_cells", C.c_int64), ("n_stored", C.c_int64),
-        ("n_diagonals", C.c_int32), ("max_diag_width", C.c_int32),
+        ("n_diagonals", C.c_int32), ("max_diag_width", C.c_int32), ("h2d_bytes", C.c_int64),
     ]
 
 

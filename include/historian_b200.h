@@ -132,6 +132,7 @@ typedef struct {
   int64_t n_stored;                  /* cells allocated in HBM (>= n_cells: band rows are padded to intervals) */
   int32_t n_diagonals;               /* wavefront steps */
   int32_t max_diag_width;            /* widest anti-diagonal in stored cells */
+  int64_t h2d_bytes;                 /* bytes hist_pair_prepare copied host->device for this pair */
 } hist_pair_info;
 
 /* ------------------------------------------------------------------ context */
@@ -144,6 +145,11 @@ void* hist_ctx_stream(hist_ctx* ctx);
 int hist_ctx_synchronize(hist_ctx* ctx);
 /* Number of kernels this context has launched so far (bench.py's gpu_launches). */
 int64_t hist_ctx_launch_count(const hist_ctx* ctx);
+/* Device-side timing of the Forward/Backward fill kernels: when enabled, every fill launch is
+ * bracketed by CUDA events on the context's stream.  hist_ctx_fill_time_ms waits for them,
+ * returns the summed kernel time and launch count since the last query, and resets. */
+int hist_ctx_set_timing(hist_ctx* ctx, int enabled);
+int hist_ctx_fill_time_ms(hist_ctx* ctx, double* total_ms, int64_t* n_launches);
 
 /* ------------------------------------------------------------------ profiles */
 /* Replaces holding a `Profile` value on the host (profile.h:41-76). */
