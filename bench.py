@@ -215,7 +215,7 @@ def gpu_arm(args):
 
     # ---- resident inputs: profiles uploaded, DPMatrix tables prepared once
     profs = [(ctx.upload(x), ctx.upload(y)) for x, y, _ in inputs]
-    pairs = [ctx.prepare(dx, dy, hmm, env) for (dx, dy), (_, _, env) in zip(profs, inputs)]
+    pairs = ctx.prepare_batch([a for a, _ in profs], [b for _, b in profs], hmm, [e for _, _, e in inputs], backward=True)
     cells_per_step = 2 * sum(p.n_cells for p in pairs)
 
     def step_resident():
@@ -245,7 +245,7 @@ def gpu_arm(args):
     # ---- end to end from host buffers through the public C-ABI calls
     def step_e2e():
         pp = [(ctx.upload(x), ctx.upload(y)) for x, y, _ in inputs]
-        pr = [ctx.prepare(dx, dy, hmm, env) for (dx, dy), (_, _, env) in zip(pp, inputs)]
+        pr = ctx.prepare_batch([a for a, _ in pp], [b for _, b in pp], hmm, [e for _, _, e in inputs], backward=True)
         r = ctx.fill_batch(pr, backward=True)
         h2d = sum(x.lp_absorb.nbytes + y.lp_absorb.nbytes for x, y, _ in inputs) + sum(int(p.info.h2d_bytes) for p in pr)
         for p in pr:

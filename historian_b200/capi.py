@@ -46,6 +46,8 @@ def load():
     lib.hist_profile_destroy.argtypes = [vp]
     lib.hist_profile_destroy.restype = None
     lib.hist_pair_prepare.argtypes = [vp, vp, vp, C.POINTER(D.PairHmmDesc), C.POINTER(D.EnvDesc), C.POINTER(vp)]
+    lib.hist_pair_prepare_batch.argtypes = [vp, C.c_int32, C.POINTER(vp), C.POINTER(vp), C.POINTER(C.POINTER(D.PairHmmDesc)),
+                                            C.POINTER(C.POINTER(D.EnvDesc)), C.c_int32, C.POINTER(vp)]
     lib.hist_pair_destroy.argtypes = [vp]
     lib.hist_pair_destroy.restype = None
     lib.hist_pair_get_info.argtypes = [vp, C.POINTER(D.PairInfo)]
@@ -114,6 +116,12 @@ class Context:
     def prepare(self, x, y, hmm, env=None):
         return Pair(self, x, y, hmm, env if env is not None else D.Envelope(-1))
 
+    def prepare_batch(self, xs, ys, hmms, envs=None, backward=False):
+        """hist_pair_prepare_batch: the DPMatrix constructors of a whole level of sibling merges.
+        hmms: one PairHmm (shared) or a list; envs: list of Envelope (None = no envelope)."""
+        plan = PrepareBatch(self, xs, ys, hmms, envs, backward)
+        return plan.run()
+
     def fill_batch(self, pairs, backward=False):
         n = len(pairs)
         arr = (C.c_void_p * n)(*[p.h for p in pairs])
@@ -145,15 +153,42 @@ class DeviceProfile:
             pass
 
 
+class PrepareBatch:
+    """Argument arrays of hist_pair_prepare_batch, built once (they only point at host buffers) and
+    runnable many times: run() performs the host->device transfer and the table kernels."""
+
+    def __init__(self, ctx, xs, ys, hmms, envs=None, backward=False):
+        n = len(xs)
+        self.ctx, self.xs, self.ys, self.n = ctx, list(xs), list(ys), n
+        hmms = list(hmms) if isinstance(hmms, (list, tuple)) else [hmms] * n
+        envs = list(envs) if envs is not None else [None] * n
+        self.keep = (hmms, envs)
+        uniq = {}
+        self.hd = [uniq.setdefault(id(h), h.desc()) for h in hmms]
+        self.ed = [None if e is None else e.desc() for e in envs]
+        self.hp = (C.POINTER(D.PairHmmDesc) * n)(*[C.pointer(d) for d in self.hd])
+        self.ep = (C.POINTER(D.EnvDesc) * n)(*[C.POINTER(D.EnvDesc)() if d is None else C.pointer(d) for d in self.ed])
+        self.flags = 1 if backward else 0
+
+    def run(self):
+        n, ctx = self.n, self.ctx
+        xp = (C.c_void_p * n)(*[x.h for x in self.xs])
+        yp = (C.c_void_p * n)(*[y.h for y in self.ys])
+        out = (C.c_void_p * n)()
+        ctx.check(ctx.lib.hist_pair_prepare_batch(ctx.h, n, xp, yp, self.hp, self.ep, self.flags, out))
+        return [Pair(ctx, self.xs[k], self.ys[k], handle=C.c_void_p(out[k])) for k in range(n)]
+
+
 class Pair:
     """DPMatrix + ForwardMatrix + BackwardMatrix of one sibling merge (forward.h)."""
 
-    def __init__(self, ctx, x, y, hmm, env):
+    def __init__(self, ctx, x, y, hmm=None, env=None, handle=None):
         self.ctx, self.x, self.y = ctx, x, y
-        hd, ed = hmm.desc(), env.desc()
-        h = C.c_void_p()
-        ctx.check(ctx.lib.hist_pair_prepare(ctx.h, x.h, y.h, C.byref(hd), C.byref(ed), C.byref(h)))
-        self.h = h
+        if handle is None:
+            hd, ed = hmm.desc(), env.desc()
+            handle = C.c_void_p()
+            ctx.check(ctx.lib.hist_pair_prepare(ctx.h, x.h, y.h, C.byref(hd), C.byref(ed), C.byref(handle)))
+        self.h = handle
         info = D.PairInfo()
         ctx.check(ctx.lib.hist_pair_get_info(self.h, C.byref(info)))
         self.info = info

@@ -37,29 +37,54 @@ int check_cuda(hist_ctx* ctx, cudaError_t e, const char* what) {
 }
 
 // ------------------------------------------------------------------ F0 / F1 kernels
-// One CTA per profile state.  Thread k < K computes sub[i][c][a] for k = c*A + a:
+// grid = (states, pairs, 2 sides).  One CTA per profile state.  Thread k < K computes sub[i][c][a] for k = c*A + a:
 //   sub = m_c + log( sum_d P_c(a->d) * exp(lpAbsorb[i][c][d] - m_c) )        (profile.cpp:78-91)
 // in FP64 probability space (the reference does A log-sum-exps in log space; the
 // results agree to the reference table's own error).  Then the CTA
 // reduces rootsub = log sum_k exp(logRoot[k] + sub[k]) and
 // ins = LSE_c(logCptWeight[c] + log sum_a exp(logIns[c][a] + lpAbsorb[i][c][a]))   (forward.cpp:44-56)
 // and writes the FP32 tables the fill kernels use, scaled by 2^-ex[i].
-__global__ void prepare_side_kernel(SideDev s, int C, int A, const double* __restrict__ subMat,
-                                    const double* __restrict__ logRoot, const double* __restrict__ logIns,
-                                    const double* __restrict__ logCptWeight, int foldRoot) {
+__device__ __forceinline__ double warp_max(double v) {
+  for (int o = 16; o; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ double warp_sum(double v) {
+  for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+// block-wide reduction through shared scratch `red` (blockDim.x/32 doubles); every thread gets the result
+template <bool MAX>
+__device__ __forceinline__ double block_reduce(double v, double* red) {
+  v = MAX ? warp_max(v) : warp_sum(v);
+  const int w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) red[w] = v;
+  __syncthreads();
+  double r = red[0];
+  for (int q = 1; q < nw; ++q) r = MAX ? fmax(r, red[q]) : r + red[q];
+  return r;
+}
+
+__global__ void prepare_side_kernel(PairDev* const* __restrict__ pairs) {
   extern __shared__ double sm[];
-  const int K = C * A;
-  double* e_abs = sm;          // [K] exp(lpAbsorb - m_c)
-  double* red = sm + K;        // [K] scratch
-  double* mc = sm + 2 * K;     // [C] per-component max
+  const PairDev& P = *pairs[blockIdx.y];
+  const bool isY = blockIdx.z == 1;
+  const SideDev& s = isY ? P.y : P.x;
   const int i = blockIdx.x;
+  if (i >= s.n) return;
+  const int C = P.C, A = P.A, K = P.K, Kp = P.Kp;
+  const double* __restrict__ subMat = isY ? P.r_sub : P.l_sub;
+  const double* __restrict__ logRoot = P.log_root;
+  const double* __restrict__ logIns = isY ? P.r_ins : P.l_ins;
+  const double* __restrict__ logCptWeight = isY ? P.r_cw : P.l_cw;
+  double* e_abs = sm;          // [K] exp(lpAbsorb - m_c)
+  double* mc = sm + K;         // [C] per-component max
+  double* red = sm + K + C;    // [32] reduction scratch
   const int k = threadIdx.x;
   const bool emit = (s.flags[i] & F_EMIT) != 0;
   if (!emit || i == 0 || i == s.n - 1) {
-    if (k < K) {
-      s.sub[(size_t)i * K + k] = -INFINITY;
-      s.H[(size_t)i * K + k] = 0.f;
-    }
+    if (k < K) s.sub[(size_t)i * K + k] = -INFINITY;
+    if (k < Kp) s.H[(size_t)i * Kp + k] = 0.f;
     if (k == 0) {
       s.ex[i] = 0;
       s.rs[i] = 1.f;
@@ -76,52 +101,33 @@ __global__ void prepare_side_kernel(SideDev s, int C, int A, const double* __res
     mc[k] = m;
   }
   __syncthreads();
-  if (k < K) {
-    const int c = k / A;
-    e_abs[k] = mc[c] == -INFINITY ? 0.0 : exp(la[k] - mc[c]);
-  }
+  const int c = k < K ? k / A : 0, a = k - c * A;
+  const double lak = k < K ? la[k] : -INFINITY;
+  if (k < K) e_abs[k] = mc[c] == -INFINITY ? 0.0 : exp(lak - mc[c]);
   __syncthreads();
   double subv = -INFINITY;
   if (k < K) {
-    const int c = k / A, a = k - c * A;
-    const double* P = subMat + ((size_t)c * A + a) * A;
+    const double* Pm = subMat + ((size_t)c * A + a) * A;
     double acc = 0;
-    for (int d = 0; d < A; ++d) acc = fma(P[d], e_abs[c * A + d], acc);
+    for (int d = 0; d < A; ++d) acc = fma(Pm[d], e_abs[c * A + d], acc);
     subv = acc > 0 ? mc[c] + log(acc) : -INFINITY;
     s.sub[(size_t)i * K + k] = subv;
-    red[k] = subv;
   }
-  __syncthreads();
-  // block max of sub -> ex
-  __shared__ double s_max, s_root, s_ins;
-  if (k == 0) {
-    double m = -INFINITY;
-    for (int q = 0; q < K; ++q) m = fmax(m, red[q]);
-    s_max = m;
-    // rootsub
-    double lr = -INFINITY;
-    for (int q = 0; q < K; ++q) lr = fmax(lr, logRoot[q] + red[q]);
-    double acc = 0;
-    if (lr > -INFINITY)
-      for (int q = 0; q < K; ++q) acc += exp(logRoot[q] + red[q] - lr);
-    s_root = lr > -INFINITY ? lr + log(acc) : -INFINITY;
-    // ins
-    double li = -INFINITY;
-    for (int c = 0; c < C; ++c)
-      for (int a = 0; a < A; ++a) li = fmax(li, logCptWeight[c] + logIns[c * A + a] + la[c * A + a]);
-    double acc2 = 0;
-    if (li > -INFINITY)
-      for (int c = 0; c < C; ++c)
-        for (int a = 0; a < A; ++a) acc2 += exp(logCptWeight[c] + logIns[c * A + a] + la[c * A + a] - li);
-    s_ins = li > -INFINITY ? li + log(acc2) : -INFINITY;
-  }
-  __syncthreads();
-  const double mx = s_max;
+  // block reductions: max of sub -> ex; rootsub; ins
+  const double mx = block_reduce<true>(subv, red);
+  const double rterm = k < K ? logRoot[k] + subv : -INFINITY;
+  const double lr = block_reduce<true>(rterm, red);
+  const double racc = block_reduce<false>(lr > -INFINITY && k < K ? exp(rterm - lr) : 0.0, red);
+  const double s_root = lr > -INFINITY ? lr + log(racc) : -INFINITY;
+  const double iterm = k < K ? logCptWeight[c] + logIns[k] + lak : -INFINITY;
+  const double li = block_reduce<true>(iterm, red);
+  const double iacc = block_reduce<false>(li > -INFINITY && k < K ? exp(iterm - li) : 0.0, red);
+  const double s_ins = li > -INFINITY ? li + log(iacc) : -INFINITY;
   const int ex = mx > -INFINITY ? (int)floor(mx / HB_LN2) : 0;
-  if (k < K) {
+  if (k < Kp) {
     double h = subv > -INFINITY ? exp(subv - ex * HB_LN2) : 0.0;
-    if (foldRoot) h *= exp(logRoot[k]);
-    s.H[(size_t)i * K + k] = (float)h;
+    if (isY && k < K) h *= exp(logRoot[k]);
+    s.H[(size_t)i * Kp + k] = (float)h;
   }
   if (k == 0) {
     s.ex[i] = ex;
@@ -133,7 +139,10 @@ __global__ void prepare_side_kernel(SideDev s, int C, int A, const double* __res
 }
 
 // Per transition: lp -> (mantissa, exponent) with the destination's emission exponent folded in.
-__global__ void prepare_trans_kernel(SideDev s) {
+// grid = (chunks, pairs, 2 sides).
+__global__ void prepare_trans_kernel(PairDev* const* __restrict__ pairs) {
+  const PairDev& P = *pairs[blockIdx.y];
+  const SideDev& s = blockIdx.z == 1 ? P.y : P.x;
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= s.nt) return;
   const double lp = s.t_lp[t];
@@ -148,9 +157,71 @@ __global__ void prepare_trans_kernel(SideDev s) {
   s.t_e[t] = (int)fe + s.ex[s.t_dst[t]];
 }
 
+// Packed per-state and per-edge records of the fill kernels (layout: hist_internal.cuh).
+// grid = (chunks, pairs, 2 sides), one thread per state.
+__global__ void pack_meta_kernel(PairDev* const* __restrict__ pairs) {
+  const PairDev& P = *pairs[blockIdx.y];
+  const SideDev& s = blockIdx.z == 1 ? P.y : P.x;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= s.n) return;
+  int flags = s.flags[i];
+  if (s.near_[i]) flags |= F_NEAR;
+  // in-edges
+  const int ib = s.in_off[i], ic = s.in_off[i + 1] - ib;
+  int4 first = make_int4(0, 0, 0, -1);
+  for (int q = 0; q < ic; ++q) {
+    const int t = s.in_idx[ib + q];
+    const int src = s.t_src[t];
+    const int4 e = make_int4(src, s.t_e[t], __float_as_int(s.t_m[t]), s.slot[src]);
+    s.in_edges[ib + q] = e;
+    if (q == 0) first = e;
+  }
+  // out-edges
+  const int ab = s.ao_off[i], ac = s.ao_off[i + 1] - ab;
+  int4 f0 = make_int4(0, 0, -1, 0), f1 = make_int4(0, 0, 0, 0);
+  for (int q = 0; q < ac; ++q) {
+    const int t = s.ao_idx[ab + q];
+    const int dst = s.t_dst[t];
+    const float m = s.t_m[t];
+    const int4 e0 = make_int4(dst, s.t_e[t], s.slot[dst], 0);
+    const int4 e1 = make_int4(__float_as_int(m), __float_as_int(m * s.rs[dst]), __float_as_int(m * s.ins[dst]), 0);
+    s.ao_edges[2 * (ab + q)] = e0;
+    s.ao_edges[2 * (ab + q) + 1] = e1;
+    if (q == 0) { f0 = e0; f1 = e1; }
+  }
+  const int nb = s.no_off[i], nc = s.no_off[i + 1] - nb;
+  // null transitions into END (summed if there are several): (mantissa, exponent) of their total weight
+  double end_sum = 0;
+  int end_e = 0;
+  bool has_end = false;
+  for (int q = 0; q < nc; ++q) {
+    const int t = s.no_idx[nb + q];
+    const int dst = s.t_dst[t];
+    const bool toEnd = dst == s.n - 1;
+    const float m = s.t_m[t];
+    s.no_edges[2 * (nb + q)] = make_int4(dst, s.t_e[t], toEnd ? -1 : s.slot[dst], toEnd ? 1 : 0);
+    s.no_edges[2 * (nb + q) + 1] = make_int4(__float_as_int(m), 0, 0, 0);
+    if (toEnd && m > 0.f) {
+      const int e = s.t_e[t];
+      if (!has_end) { end_sum = m; end_e = e; has_end = true; }
+      else if (e > end_e) { end_sum = ldexp(end_sum, end_e - e) + m; end_e = e; }
+      else end_sum += ldexp((double)m, e - end_e);
+    }
+  }
+  if (has_end) flags |= F_TO_END;
+  s.fm_a[i] = make_int4(flags | (ic << 8), ib, s.key[i], s.slot[i]);
+  s.fm_b[i] = first;
+  s.emis[i] = make_float2(s.rs[i], s.ins[i]);
+  s.bm[4 * i] = make_int4(flags | (ac << 8), ab, s.key[i], s.slot[i]);
+  s.bm[4 * i + 1] = make_int4(nb, nc, end_e, __float_as_int((float)end_sum));
+  s.bm[4 * i + 2] = f0;
+  s.bm[4 * i + 3] = f1;
+}
+
 // Exact in-envelope cell count (the GCUPS unit, forward.cpp:78-86), one thread per stored slot.
-__global__ void count_cells_kernel(const PairDev* __restrict__ Pp) {
-  const PairDev& P = *Pp;
+// grid = (chunks, pairs).
+__global__ void count_cells_kernel(PairDev* const* __restrict__ pairs) {
+  const PairDev& P = *pairs[blockIdx.y];
   __shared__ unsigned long long s_cnt;
   if (threadIdx.x == 0) s_cnt = 0;
   __syncthreads();
@@ -204,6 +275,9 @@ extern "C" int hist_ctx_create(int device, hist_ctx** out) {
   ctx->device = device;
   ctx->launches = 0;
   ctx->timing = false;
+  ctx->fill_smem_configured = 0;
+  ctx->staging = nullptr;
+  ctx->staging_bytes = 0;
   e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
   if (e != cudaSuccess) {
     set_err(nullptr, HIST_ERR_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(e));
@@ -223,6 +297,7 @@ extern "C" void hist_ctx_destroy(hist_ctx* ctx) {
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
   for (auto& e : ctx->fill_events) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
+  if (ctx->staging) cudaFreeHost(ctx->staging);
   cudaStreamDestroy(ctx->stream);
   delete ctx;
 }
@@ -288,6 +363,7 @@ extern "C" int hist_profile_upload(hist_ctx* ctx, const hist_profile_desc* d, hi
     if (p->is_emit[i]) p->empty = false;
   const size_t bytes = (size_t)p->n * p->C * p->A * sizeof(double);
   p->d_lp_absorb = nullptr;
+  p->arena = nullptr;
   int rc = check_cuda(ctx, cudaMallocAsync((void**)&p->d_lp_absorb, bytes, ctx->stream), "cudaMallocAsync(lp_absorb)");
   if (!rc) rc = check_cuda(ctx, cudaMemcpyAsync(p->d_lp_absorb, d->lp_absorb, bytes, cudaMemcpyHostToDevice, ctx->stream), "H2D lp_absorb");
   // the descriptor is only borrowed for the duration of the call
@@ -311,7 +387,9 @@ extern "C" void hist_profile_destroy(hist_profile* p) {
 // ------------------------------------------------------------------ pair preparation
 namespace {
 
-struct SlabBuilder {
+// Byte layout of one pair inside the batch arena: a host-initialised part (copied in ONE H2D
+// transfer for the whole batch) and a device-only part.
+struct Layout {
   size_t bytes = 0;
   std::vector<std::pair<size_t, std::pair<const void*, size_t>>> copies;  // (offset, (src, nbytes))
   size_t reserve(size_t n, size_t align = 16) {
@@ -322,7 +400,7 @@ struct SlabBuilder {
   }
   size_t put(const void* src, size_t n, size_t align = 16) {
     const size_t off = reserve(n, align);
-    copies.push_back({off, {src, n}});
+    if (n) copies.push_back({off, {src, n}});
     return off;
   }
 };
@@ -330,6 +408,22 @@ struct SlabBuilder {
 struct SideHost {
   std::vector<uint8_t> flags, near_;
   std::vector<int> in_off, in_idx, ao_off, ao_idx, no_off, no_idx, key, slot;
+};
+
+struct SideOff {  // h_*: offsets in the host-initialised part, d_*: in the device-only part
+  size_t h_flags, h_t_src, h_t_dst, h_t_lp, h_in_off, h_in_idx, h_ao_off, h_ao_idx, h_no_off, h_no_idx, h_key, h_near, h_slot;
+  size_t d_t_m, d_t_e, d_ex, d_rs, d_ins, d_H, d_sub, d_rootsub, d_insl, d_fm_a, d_fm_b, d_emis, d_in_edges, d_bm, d_ao_edges, d_no_edges;
+};
+
+struct PairBuild {
+  hist_pair* pr = nullptr;
+  SideHost sx, sy;
+  Layout host, dev;
+  SideOff ox, oy;
+  size_t h_start, h_end, h_dinfo, h_lsub, h_rsub, h_root, h_lins, h_rins, h_lcw, h_rcw, h_pairdev;
+  size_t d_scal, d_fA, d_fB, d_bA, d_bB, d_absorb;
+  size_t host_base = 0, dev_base = 0;  // position of this pair's two parts in the arena
+  std::vector<int> one0 = std::vector<int>(1, 0);
 };
 
 void build_side_lists(const hist_profile* p, SideHost& s) {
@@ -363,16 +457,16 @@ void build_side_lists(const hist_profile* p, SideHost& s) {
   }
 }
 
-}  // namespace
-
-extern "C" int hist_pair_prepare(hist_ctx* ctx, const hist_profile* x, const hist_profile* y, const hist_pairhmm_desc* hmm,
-                                 const hist_env_desc* env, hist_pair** out) {
-  if (!ctx || !x || !y || !hmm || !out) return set_err(ctx, HIST_ERR_ARG, "hist_pair_prepare: NULL argument");
-  *out = nullptr;
+// Host part of the DPMatrix constructor for one pair: transition lists, band keys, edge flags and
+// the anti-diagonal layout, all O(states + diagonals).  Fills b.host / b.dev layouts.
+int build_pair_host(hist_ctx* ctx, const hist_profile* x, const hist_profile* y, const hist_pairhmm_desc* hmm,
+                    const hist_env_desc* env, bool want_bwd, PairBuild& b) {
+  if (!x || !y || !hmm) return set_err(ctx, HIST_ERR_ARG, "hist_pair_prepare: NULL argument");
+  if (x->ctx != ctx || y->ctx != ctx) return set_err(ctx, HIST_ERR_ARG, "hist_pair_prepare: profile belongs to another context");
   if (x->A != hmm->alph_size || y->A != hmm->alph_size || x->C != hmm->components || y->C != hmm->components)
     return set_err(ctx, HIST_ERR_ARG, "hist_pair_prepare: alphabet/component mismatch between profiles and PairHMM");
-  const int nx = x->n, ny = y->n, A = x->A, C = x->C, K = A * C;
-  if (K > 1024) return set_err(ctx, HIST_ERR_ARG, "hist_pair_prepare: C*A = %d exceeds 1024", K);
+  const int nx = x->n, ny = y->n, A = x->A, C = x->C, K = A * C, Kp = (K + 3) & ~3;
+  if (Kp > 1024) return set_err(ctx, HIST_ERR_ARG, "hist_pair_prepare: C*A = %d exceeds 1024", K);
   const int maxDist = env ? env->max_distance : -1;
   if (maxDist >= 0) {
     if (x->leaf_pos.empty() || y->leaf_pos.empty())
@@ -380,11 +474,16 @@ extern "C" int hist_pair_prepare(hist_ctx* ctx, const hist_profile* x, const his
     if (!env->cumulative_matches || !env->row1_pos_to_col || !env->row2_pos_to_col)
       return set_err(ctx, HIST_ERR_ARG, "hist_pair_prepare: envelope arrays are NULL");
   }
-  cudaSetDevice(ctx->device);
-
-  SideHost sx, sy;
+  SideHost& sx = b.sx;
+  SideHost& sy = b.sy;
   build_side_lists(x, sx);
   build_side_lists(y, sy);
+  for (int i = 0; i < nx; ++i)
+    if (sx.in_off[i + 1] - sx.in_off[i] > HB_MAX_DEGREE || sx.ao_off[i + 1] - sx.ao_off[i] > HB_MAX_DEGREE)
+      return set_err(ctx, HIST_ERR_ARG, "hist_pair_prepare: x state %d has more than %d transitions", i, HB_MAX_DEGREE);
+  for (int j = 0; j < ny; ++j)
+    if (sy.in_off[j + 1] - sy.in_off[j] > HB_MAX_DEGREE || sy.ao_off[j + 1] - sy.ao_off[j] > HB_MAX_DEGREE)
+      return set_err(ctx, HIST_ERR_ARG, "hist_pair_prepare: y state %d has more than %d transitions", j, HB_MAX_DEGREE);
 
   // ---- envelope keys (forward.cpp:36-42, alignpath.h:56-61) and edge flags (forward.cpp:58-65)
   sx.key.assign(nx, 0);
@@ -420,45 +519,43 @@ extern "C" int hist_pair_prepare(hist_ctx* ctx, const hist_profile* x, const his
     for (int j = 0; j < NJ; ++j) pmax[j] = j ? std::max(pmax[j - 1], sy.key[j]) : sy.key[0];
     for (int j = NJ - 1; j >= 0; --j) smin[j] = j < NJ - 1 ? std::min(smin[j + 1], sy.key[j]) : sy.key[NJ - 1];
     for (int i = 0; i < NI; ++i) {
-      const int a = sx.key[i] - maxDist, b = sx.key[i] + maxDist;
-      const int lo = (int)(std::lower_bound(pmax.begin(), pmax.end(), a) - pmax.begin());        // first j: key[j] >= a
-      const int hi = (int)(std::upper_bound(smin.begin(), smin.end(), b) - smin.begin()) - 1;    // last j: key[j] <= b
-      jlo[i] = lo;
-      jhi[i] = hi;
+      const int a = sx.key[i] - maxDist, bb = sx.key[i] + maxDist;
+      jlo[i] = (int)(std::lower_bound(pmax.begin(), pmax.end(), a) - pmax.begin());        // first j: key[j] >= a
+      jhi[i] = (int)(std::upper_bound(smin.begin(), smin.end(), bb) - smin.begin()) - 1;   // last j: key[j] <= b
     }
   }
   // monotone hull so that every anti-diagonal meets the band in ONE interval of i
+  std::vector<int> rows;  // non-empty rows, ascending
+  rows.reserve(NI);
   {
     int run = -1;
-    for (int i = 0; i < NI; ++i) {  // jhi non-decreasing
-      if (jlo[i] <= jhi[i]) run = std::max(run, jhi[i]);
-      if (run >= 0 && jlo[i] <= jhi[i]) jhi[i] = run;
-    }
+    for (int i = 0; i < NI; ++i)  // jhi non-decreasing
+      if (jlo[i] <= jhi[i]) { run = std::max(run, jhi[i]); jhi[i] = run; rows.push_back(i); }
     run = NJ;
-    for (int i = NI - 1; i >= 0; --i) {  // jlo non-decreasing
-      if (jlo[i] <= jhi[i]) run = std::min(run, jlo[i]);
-      if (jlo[i] <= jhi[i]) jlo[i] = run;
-    }
+    for (int i = NI - 1; i >= 0; --i)  // jlo non-decreasing
+      if (jlo[i] <= jhi[i]) { run = std::min(run, jlo[i]); jlo[i] = run; }
   }
+  // Over the non-empty rows i + jlo[i] and i + jhi[i] are strictly increasing, so the rows meeting
+  // diagonal d form a contiguous run of `rows`: two pointers, O(rows + diagonals).
   const int nDiag = NI + NJ - 1;
-  std::vector<int> dlo(nDiag, std::numeric_limits<int>::max()), dhi(nDiag, -1);
-  for (int i = 0; i < NI; ++i) {
-    if (jlo[i] > jhi[i]) continue;
-    // row i covers diagonals i+jlo .. i+jhi; with monotone jlo/jhi the per-diagonal set is an interval,
-    // so only its end points need updating: sweep the two boundary chains
-    const int d0 = i + jlo[i], d1 = i + jhi[i];
-    // dlo[d] = min i with d in [d0,d1]; dhi[d] = max i.  (rows are visited in ascending i)
-    for (int d = d0; d <= d1; ++d) {
-      if (dlo[d] == std::numeric_limits<int>::max()) dlo[d] = i;
-      dhi[d] = i;
+  std::vector<int> dlo(nDiag, 0), dhi(nDiag, -1);
+  {
+    size_t lo = 0, hi = 0;  // lo: first row with i + jhi[i] >= d;  hi: one past the last row with i + jlo[i] <= d
+    for (int d = 0; d < nDiag; ++d) {
+      while (lo < rows.size() && rows[lo] + jhi[rows[lo]] < d) ++lo;
+      while (hi < rows.size() && rows[hi] + jlo[rows[hi]] <= d) ++hi;
+      if (lo < hi) { dlo[d] = rows[lo]; dhi[d] = rows[hi - 1]; }
     }
   }
-  // (the loop above is O(stored cells); good enough on the host for banded merges)
 
   hist_pair* pr = new hist_pair();
+  b.pr = pr;
   pr->ctx = ctx;
   pr->x = x;
   pr->y = y;
+  pr->arena = nullptr;
+  pr->bwd_planes = nullptr;
+  pr->d_dev = nullptr;
   pr->fwd_done = pr->bwd_done = false;
   pr->lp_end = pr->lp_start = -INFINITY;
   // edge slots
@@ -482,94 +579,76 @@ extern "C" int hist_pair_prepare(hist_ctx* ctx, const hist_profile* x, const his
     maxThreads = std::max(maxThreads, nS + di.width + nE);
     maxWidth = std::max(maxWidth, di.width);
   }
-  if (off >= (1ull << 31)) {
-    delete pr;
+  if (off >= (1ull << 31))
     return set_err(ctx, HIST_ERR_ARG, "hist_pair_prepare: %llu stored cells exceed the 2^31 limit of one pair", off);
-  }
   const unsigned nStored = (unsigned)off;
 
-  // ---- slab: every per-pair array in one allocation, host-built parts in one staging buffer
-  SlabBuilder sb;
-  auto putv = [&](const auto& v) { return sb.put(v.data(), v.size() * sizeof(v[0])); };
-  struct SideOff { size_t flags, t_src, t_dst, t_lp, t_m, t_e, in_off, in_idx, ao_off, ao_idx, no_off, no_idx, ex, rs, ins, H, sub, rootsub, insl, key, near_, slot; };
+  // ---- layouts
+  Layout& H = b.host;
+  Layout& Dv = b.dev;
+  auto putv = [&](const auto& v) { return H.put(v.data(), v.size() * sizeof(v[0])); };
   auto layout_side = [&](const hist_profile* p, const SideHost& s) {
     SideOff o;
-    o.flags = putv(s.flags);
-    o.t_src = sb.put(p->t_src.data(), std::max<size_t>(1, p->nt) * sizeof(int));
-    o.t_dst = sb.put(p->t_dst.data(), std::max<size_t>(1, p->nt) * sizeof(int));
-    o.t_lp = sb.put(p->t_lp.data(), std::max<size_t>(1, p->nt) * sizeof(double));
-    o.t_m = sb.reserve(std::max<size_t>(1, p->nt) * sizeof(float));
-    o.t_e = sb.reserve(std::max<size_t>(1, p->nt) * sizeof(int));
-    o.in_off = putv(s.in_off); o.in_idx = putv(s.in_idx);
-    o.ao_off = putv(s.ao_off); o.ao_idx = putv(s.ao_idx);
-    o.no_off = putv(s.no_off); o.no_idx = putv(s.no_idx);
-    o.ex = sb.reserve((size_t)p->n * sizeof(int));
-    o.rs = sb.reserve((size_t)p->n * sizeof(float));
-    o.ins = sb.reserve((size_t)p->n * sizeof(float));
-    o.H = sb.reserve((size_t)p->n * K * sizeof(float));
-    o.sub = sb.reserve((size_t)p->n * K * sizeof(double));
-    o.rootsub = sb.reserve((size_t)p->n * sizeof(double));
-    o.insl = sb.reserve((size_t)p->n * sizeof(double));
-    o.key = putv(s.key); o.near_ = putv(s.near_); o.slot = putv(s.slot);
+    const size_t nt1 = std::max<size_t>(1, p->nt);
+    o.h_flags = putv(s.flags);
+    o.h_t_src = H.put(p->t_src.data(), p->nt * sizeof(int)); H.reserve(p->nt ? 0 : sizeof(int));
+    o.h_t_dst = H.put(p->t_dst.data(), p->nt * sizeof(int)); H.reserve(p->nt ? 0 : sizeof(int));
+    o.h_t_lp = H.put(p->t_lp.data(), p->nt * sizeof(double)); H.reserve(p->nt ? 0 : sizeof(double));
+    o.h_in_off = putv(s.in_off); o.h_in_idx = putv(s.in_idx);
+    o.h_ao_off = putv(s.ao_off); o.h_ao_idx = putv(s.ao_idx);
+    o.h_no_off = putv(s.no_off); o.h_no_idx = putv(s.no_idx);
+    o.h_key = putv(s.key); o.h_near = putv(s.near_); o.h_slot = putv(s.slot);
+    o.d_t_m = Dv.reserve(nt1 * sizeof(float));
+    o.d_t_e = Dv.reserve(nt1 * sizeof(int));
+    o.d_ex = Dv.reserve((size_t)p->n * sizeof(int));
+    o.d_rs = Dv.reserve((size_t)p->n * sizeof(float));
+    o.d_ins = Dv.reserve((size_t)p->n * sizeof(float));
+    o.d_H = Dv.reserve((size_t)p->n * Kp * sizeof(float));
+    o.d_sub = Dv.reserve((size_t)p->n * K * sizeof(double));
+    o.d_rootsub = Dv.reserve((size_t)p->n * sizeof(double));
+    o.d_insl = Dv.reserve((size_t)p->n * sizeof(double));
+    o.d_fm_a = Dv.reserve((size_t)p->n * sizeof(int4));
+    o.d_fm_b = Dv.reserve((size_t)p->n * sizeof(int4));
+    o.d_emis = Dv.reserve((size_t)p->n * sizeof(float2));
+    o.d_in_edges = Dv.reserve(nt1 * sizeof(int4));
+    o.d_bm = Dv.reserve((size_t)p->n * 4 * sizeof(int4));
+    o.d_ao_edges = Dv.reserve(nt1 * 2 * sizeof(int4));
+    o.d_no_edges = Dv.reserve(nt1 * 2 * sizeof(int4));
     return o;
   };
-  // guard against zero-length vectors handed to put(): t_src etc. of a profile always has >= 1 entry
-  // (START -> ... -> END needs at least one transition), so .data() is valid.
-  const SideOff ox = layout_side(x, sx), oy = layout_side(y, sy);
-  std::vector<int> one0(1, 0);
-  const size_t o_start = sb.put(nS ? (const void*)pr->start_rows.data() : (const void*)one0.data(), std::max(1, nS) * sizeof(int));
-  const size_t o_end = sb.put(nE ? (const void*)pr->end_cols.data() : (const void*)one0.data(), std::max(1, nE) * sizeof(int));
-  const size_t o_dinfo = sb.put(pr->dinfo.data(), pr->dinfo.size() * sizeof(DiagInfo));
-  // model tables
-  const size_t o_lsub = sb.put(hmm->l_sub, (size_t)K * A * sizeof(double));
-  const size_t o_rsub = sb.put(hmm->r_sub, (size_t)K * A * sizeof(double));
-  const size_t o_root = sb.put(hmm->log_root, (size_t)K * sizeof(double));
-  const size_t o_lins = sb.put(hmm->l_log_ins, (size_t)K * sizeof(double));
-  const size_t o_rins = sb.put(hmm->r_log_ins, (size_t)K * sizeof(double));
-  const size_t o_lcw = sb.put(hmm->l_log_cpt_weight, (size_t)C * sizeof(double));
-  const size_t o_rcw = sb.put(hmm->r_log_cpt_weight, (size_t)C * sizeof(double));
-  const size_t o_host_end = sb.bytes;  // everything before this offset is (partly) host-initialised
-  const size_t o_scal = sb.reserve(4 * sizeof(double));  // lp_end, lp_start, n_cells, spare
-  const size_t o_dev = sb.reserve(sizeof(PairDev), 64);
-  const size_t o_fA = sb.reserve((size_t)nStored * sizeof(float4), 256);
-  const size_t o_fB = sb.reserve((size_t)nStored * sizeof(float2), 256);
-  // backward planes are allocated lazily by hist_bwd_fill (most merges never need them)
+  b.ox = layout_side(x, sx);
+  b.oy = layout_side(y, sy);
+  b.h_start = H.put(nS ? (const void*)pr->start_rows.data() : (const void*)b.one0.data(), std::max(1, nS) * sizeof(int));
+  b.h_end = H.put(nE ? (const void*)pr->end_cols.data() : (const void*)b.one0.data(), std::max(1, nE) * sizeof(int));
+  b.h_dinfo = H.put(pr->dinfo.data(), pr->dinfo.size() * sizeof(DiagInfo));
+  b.h_lsub = H.put(hmm->l_sub, (size_t)K * A * sizeof(double));
+  b.h_rsub = H.put(hmm->r_sub, (size_t)K * A * sizeof(double));
+  b.h_root = H.put(hmm->log_root, (size_t)K * sizeof(double));
+  b.h_lins = H.put(hmm->l_log_ins, (size_t)K * sizeof(double));
+  b.h_rins = H.put(hmm->r_log_ins, (size_t)K * sizeof(double));
+  b.h_lcw = H.put(hmm->l_log_cpt_weight, (size_t)C * sizeof(double));
+  b.h_rcw = H.put(hmm->r_log_cpt_weight, (size_t)C * sizeof(double));
+  b.h_pairdev = H.reserve(sizeof(PairDev), 64);
+  H.reserve(0, 256);
+  b.d_scal = 0;  // assigned by the batch (scalars of all pairs are contiguous)
+  b.d_fA = Dv.reserve((size_t)nStored * sizeof(float4), 256);
+  b.d_fB = Dv.reserve((size_t)nStored * sizeof(float2), 256);
+  b.d_absorb = Dv.reserve((size_t)nStored * sizeof(float), 256);
+  if (want_bwd) {
+    b.d_bA = Dv.reserve((size_t)nStored * sizeof(float4), 256);
+    b.d_bB = Dv.reserve((size_t)nStored * sizeof(float2), 256);
+  }
+  Dv.reserve(0, 256);
 
-  char* slab = nullptr;
-  int rc = check_cuda(ctx, cudaMallocAsync((void**)&slab, sb.bytes, ctx->stream), "cudaMallocAsync(pair slab)");
-  if (rc) { delete pr; return rc; }
-  pr->slab = slab;
-  pr->slab_bytes = sb.bytes;
-  std::vector<char> staging(o_host_end, 0);
-  for (auto& c : sb.copies) memcpy(staging.data() + c.first, c.second.first, c.second.second);
-  rc = check_cuda(ctx, cudaMemcpyAsync(slab, staging.data(), o_host_end, cudaMemcpyHostToDevice, ctx->stream), "H2D pair slab");
-  if (!rc) rc = check_cuda(ctx, cudaMemsetAsync(slab + o_scal, 0, 4 * sizeof(double), ctx->stream), "memset scalars");
-
-  auto side_dev = [&](const hist_profile* p, const SideOff& o) {
-    SideDev s;
-    s.n = p->n; s.nt = p->nt;
-    s.flags = (const uint8_t*)(slab + o.flags);
-    s.t_src = (const int*)(slab + o.t_src); s.t_dst = (const int*)(slab + o.t_dst);
-    s.t_lp = (const double*)(slab + o.t_lp);
-    s.t_m = (float*)(slab + o.t_m); s.t_e = (int*)(slab + o.t_e);
-    s.in_off = (const int*)(slab + o.in_off); s.in_idx = (const int*)(slab + o.in_idx);
-    s.ao_off = (const int*)(slab + o.ao_off); s.ao_idx = (const int*)(slab + o.ao_idx);
-    s.no_off = (const int*)(slab + o.no_off); s.no_idx = (const int*)(slab + o.no_idx);
-    s.ex = (int*)(slab + o.ex); s.rs = (float*)(slab + o.rs); s.ins = (float*)(slab + o.ins);
-    s.H = (float*)(slab + o.H);
-    s.lp_absorb = p->d_lp_absorb;
-    s.sub = (double*)(slab + o.sub); s.rootsub = (double*)(slab + o.rootsub); s.insl = (double*)(slab + o.insl);
-    s.key = (const int*)(slab + o.key); s.near_ = (const uint8_t*)(slab + o.near_); s.slot = (const int*)(slab + o.slot);
-    return s;
-  };
   PairDev& D = pr->dev;
-  D.x = side_dev(x, ox);
-  D.y = side_dev(y, oy);
-  D.K = K; D.C = C; D.A = A;
+  memset(&D, 0, sizeof(D));
+  D.K = K; D.Kp = Kp; D.C = C; D.A = A;
   D.max_dist = maxDist;
+  D.x.n = nx; D.x.nt = x->nt;
+  D.y.n = ny; D.y.nt = y->nt;
   // HMM weights, w[src][dest] (pairhmm.cpp:46-115); absent pairs are -inf / 0
   for (int a = 0; a < 6; ++a)
-    for (int b = 0; b < 6; ++b) pr->w_log[a][b] = -INFINITY;
+    for (int c = 0; c < 6; ++c) pr->w_log[a][c] = -INFINITY;
   {
     const double* l = hmm->lp_trans;
     double (*w)[6] = pr->w_log;
@@ -581,7 +660,7 @@ extern "C" int hist_pair_prepare(hist_ctx* ctx, const hist_profile* x, const his
     w[3][4] = l[HIST_W_IMI_IIW]; w[3][5] = l[HIST_W_IMI_EEE];
     w[4][0] = l[HIST_W_IIW_IMM]; w[4][2] = l[HIST_W_IIW_IDM]; w[4][4] = l[HIST_W_IIW_IIW]; w[4][5] = l[HIST_W_IIW_EEE];
     for (int a = 0; a < 5; ++a)
-      for (int b = 0; b < 6; ++b) D.W[a][b] = w[a][b] > -INFINITY ? (float)exp(w[a][b]) : 0.f;
+      for (int c = 0; c < 6; ++c) D.W[a][c] = w[a][c] > -INFINITY ? (float)exp(w[a][c]) : 0.f;
   }
   pr->hmm_scalars = *hmm;
   pr->hmm_scalars.log_root = pr->hmm_scalars.l_sub = pr->hmm_scalars.r_sub = nullptr;
@@ -589,61 +668,189 @@ extern "C" int hist_pair_prepare(hist_ctx* ctx, const hist_profile* x, const his
   pr->hmm_scalars.l_log_cpt_weight = pr->hmm_scalars.r_log_cpt_weight = nullptr;
   D.n_diag = nDiag;
   D.nS = nS; D.nE = nE;
-  D.start_rows = (const int*)(slab + o_start);
-  D.end_cols = (const int*)(slab + o_end);
-  D.dinfo = (const DiagInfo*)(slab + o_dinfo);
   D.max_threads = maxThreads;
   D.n_stored = nStored;
-  D.fA = (float4*)(slab + o_fA); D.fB = (float2*)(slab + o_fB);
-  D.bA = nullptr; D.bB = nullptr;
-  D.lp_end = (double*)(slab + o_scal);
-  D.lp_start = (double*)(slab + o_scal) + 1;
-  D.n_cells = (unsigned long long*)((double*)(slab + o_scal) + 2);
-  pr->d_dev = (PairDev*)(slab + o_dev);
-  if (!rc) rc = check_cuda(ctx, cudaMemcpyAsync(pr->d_dev, &D, sizeof(PairDev), cudaMemcpyHostToDevice, ctx->stream), "H2D PairDev");
-
-  // ---- F0/F1 on device
-  if (!rc) {
-    const int threads = std::max(32, (K + 31) / 32 * 32);
-    const size_t smem = (size_t)(2 * K + C) * sizeof(double);
-    prepare_side_kernel<<<nx, threads, smem, ctx->stream>>>(D.x, C, A, (const double*)(slab + o_lsub), (const double*)(slab + o_root),
-                                                           (const double*)(slab + o_lins), (const double*)(slab + o_lcw), 0);
-    prepare_side_kernel<<<ny, threads, smem, ctx->stream>>>(D.y, C, A, (const double*)(slab + o_rsub), (const double*)(slab + o_root),
-                                                           (const double*)(slab + o_rins), (const double*)(slab + o_rcw), 1);
-    prepare_trans_kernel<<<(x->nt + 127) / 128, 128, 0, ctx->stream>>>(D.x);
-    prepare_trans_kernel<<<(y->nt + 127) / 128, 128, 0, ctx->stream>>>(D.y);
-    count_cells_kernel<<<std::min(nDiag, 4 * ctx->sm_count), 128, 0, ctx->stream>>>(pr->d_dev);
-    ctx->launches += 5;
-    rc = check_cuda(ctx, cudaGetLastError(), "prepare kernels");
-  }
-  unsigned long long ncells = 0;
-  if (!rc) rc = check_cuda(ctx, cudaMemcpyAsync(&ncells, D.n_cells, sizeof(ncells), cudaMemcpyDeviceToHost, ctx->stream), "D2H n_cells");
-  // staging buffers are host-owned: wait before they go out of scope
-  if (!rc) rc = check_cuda(ctx, cudaStreamSynchronize(ctx->stream), "sync after pair prepare");
-  if (rc) {
-    cudaFreeAsync(slab, ctx->stream);
-    delete pr;
-    return rc;
-  }
   pr->x_key = sx.key; pr->y_key = sy.key;
   pr->x_near = sx.near_; pr->y_near = sy.near_;
   pr->x_slot = sx.slot; pr->y_slot = sy.slot;
   pr->info.x_size = nx;
   pr->info.y_size = ny;
-  pr->info.n_cells = (int64_t)ncells;
+  pr->info.n_cells = 0;
   pr->info.n_stored = nStored;
   pr->info.n_diagonals = nDiag;
   pr->info.max_diag_width = maxWidth;
-  pr->info.h2d_bytes = (int64_t)(o_host_end + sizeof(PairDev));
-  *out = pr;
+  pr->info.h2d_bytes = (int64_t)H.bytes;
   return HIST_OK;
+}
+
+// Resolve the device pointers of one pair once its two arena parts are placed.
+void place_pair(PairBuild& b, char* arena, size_t scal_off, bool want_bwd) {
+  hist_pair* pr = b.pr;
+  char* hb_ = arena + b.host_base;
+  char* db = arena + b.dev_base;
+  auto side = [&](SideDev& s, const hist_profile* p, const SideOff& o) {
+    s.flags = (const uint8_t*)(hb_ + o.h_flags);
+    s.t_src = (const int*)(hb_ + o.h_t_src); s.t_dst = (const int*)(hb_ + o.h_t_dst);
+    s.t_lp = (const double*)(hb_ + o.h_t_lp);
+    s.in_off = (const int*)(hb_ + o.h_in_off); s.in_idx = (const int*)(hb_ + o.h_in_idx);
+    s.ao_off = (const int*)(hb_ + o.h_ao_off); s.ao_idx = (const int*)(hb_ + o.h_ao_idx);
+    s.no_off = (const int*)(hb_ + o.h_no_off); s.no_idx = (const int*)(hb_ + o.h_no_idx);
+    s.key = (const int*)(hb_ + o.h_key); s.near_ = (const uint8_t*)(hb_ + o.h_near); s.slot = (const int*)(hb_ + o.h_slot);
+    s.t_m = (float*)(db + o.d_t_m); s.t_e = (int*)(db + o.d_t_e);
+    s.ex = (int*)(db + o.d_ex); s.rs = (float*)(db + o.d_rs); s.ins = (float*)(db + o.d_ins);
+    s.H = (float*)(db + o.d_H);
+    s.lp_absorb = p->d_lp_absorb;
+    s.sub = (double*)(db + o.d_sub); s.rootsub = (double*)(db + o.d_rootsub); s.insl = (double*)(db + o.d_insl);
+    s.fm_a = (int4*)(db + o.d_fm_a); s.fm_b = (int4*)(db + o.d_fm_b); s.emis = (float2*)(db + o.d_emis);
+    s.in_edges = (int4*)(db + o.d_in_edges); s.bm = (int4*)(db + o.d_bm);
+    s.ao_edges = (int4*)(db + o.d_ao_edges); s.no_edges = (int4*)(db + o.d_no_edges);
+  };
+  PairDev& D = pr->dev;
+  side(D.x, pr->x, b.ox);
+  side(D.y, pr->y, b.oy);
+  D.start_rows = (const int*)(hb_ + b.h_start);
+  D.end_cols = (const int*)(hb_ + b.h_end);
+  D.dinfo = (const DiagInfo*)(hb_ + b.h_dinfo);
+  D.l_sub = (const double*)(hb_ + b.h_lsub); D.r_sub = (const double*)(hb_ + b.h_rsub);
+  D.log_root = (const double*)(hb_ + b.h_root);
+  D.l_ins = (const double*)(hb_ + b.h_lins); D.r_ins = (const double*)(hb_ + b.h_rins);
+  D.l_cw = (const double*)(hb_ + b.h_lcw); D.r_cw = (const double*)(hb_ + b.h_rcw);
+  D.fA = (float4*)(db + b.d_fA); D.fB = (float2*)(db + b.d_fB);
+  D.absorb = (float*)(db + b.d_absorb);
+  if (want_bwd) { D.bA = (float4*)(db + b.d_bA); D.bB = (float2*)(db + b.d_bB); } else { D.bA = nullptr; D.bB = nullptr; }
+  double* scal = (double*)(arena + scal_off);
+  D.lp_end = scal;
+  D.lp_start = scal + 1;
+  D.n_cells = (unsigned long long*)(scal + 2);
+  pr->d_dev = (PairDev*)(hb_ + b.h_pairdev);
+}
+
+int ensure_staging(hist_ctx* ctx, size_t bytes) {
+  if (ctx->staging_bytes >= bytes) return HIST_OK;
+  if (ctx->staging) {
+    HB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    cudaFreeHost(ctx->staging);
+    ctx->staging = nullptr;
+    ctx->staging_bytes = 0;
+  }
+  const size_t want = std::max(bytes + bytes / 4, (size_t)1 << 20);
+  HB_CUDA(ctx, cudaMallocHost((void**)&ctx->staging, want));
+  ctx->staging_bytes = want;
+  return HIST_OK;
+}
+
+void arena_release(hist_ctx* ctx, hb_arena* a) {
+  if (!a) return;
+  if (--a->refs == 0) {
+    if (a->dev) cudaFreeAsync(a->dev, ctx->stream);
+    delete a;
+  }
+}
+
+}  // namespace
+
+extern "C" int hist_pair_prepare_batch(hist_ctx* ctx, int32_t n, const hist_profile* const* xs, const hist_profile* const* ys,
+                                       const hist_pairhmm_desc* const* hmms, const hist_env_desc* const* envs, int32_t flags,
+                                       hist_pair** out) {
+  if (!ctx || n <= 0 || !xs || !ys || !hmms || !out) return set_err(ctx, HIST_ERR_ARG, "hist_pair_prepare_batch: bad arguments");
+  for (int k = 0; k < n; ++k) out[k] = nullptr;
+  cudaSetDevice(ctx->device);
+  const bool want_bwd = (flags & HIST_PREP_BACKWARD) != 0;
+  std::vector<PairBuild> builds(n);
+  auto fail = [&](int rc) {
+    for (auto& b : builds) delete b.pr;
+    return rc;
+  };
+  size_t host_total = 0, dev_total = 0;
+  for (int k = 0; k < n; ++k) {
+    int rc = build_pair_host(ctx, xs[k], ys[k], hmms[k], envs ? envs[k] : nullptr, want_bwd, builds[k]);
+    if (rc) return fail(rc);
+    builds[k].host_base = host_total;
+    host_total += builds[k].host.bytes;
+  }
+  // arena = [host-initialised parts][pointer table][scalars of all pairs][device-only parts]
+  const size_t ptr_off = host_total;
+  host_total += ((size_t)n * sizeof(PairDev*) + 255) / 256 * 256;
+  const size_t scal_off = host_total;
+  size_t total = scal_off + ((size_t)n * 4 * sizeof(double) + 255) / 256 * 256;
+  for (int k = 0; k < n; ++k) {
+    builds[k].dev_base = total;
+    total += builds[k].dev.bytes;
+    dev_total += builds[k].dev.bytes;
+  }
+  (void)dev_total;
+  hb_arena* arena = new hb_arena{nullptr, total, 0};
+  int rc = check_cuda(ctx, cudaMallocAsync((void**)&arena->dev, total, ctx->stream), "cudaMallocAsync(pair arena)");
+  if (!rc) rc = ensure_staging(ctx, scal_off);
+  if (rc) {
+    if (arena->dev) cudaFreeAsync(arena->dev, ctx->stream);
+    delete arena;
+    return fail(rc);
+  }
+  // fill the pinned staging image and ship it in one transfer
+  char* st = ctx->staging;
+  int maxN = 1, maxNt = 1, maxDiag = 1, maxKp = 4, maxKC = 1;
+  for (int k = 0; k < n; ++k) {
+    PairBuild& b = builds[k];
+    place_pair(b, arena->dev, scal_off + (size_t)k * 4 * sizeof(double), want_bwd);
+    char* base = st + b.host_base;
+    for (auto& c : b.host.copies) memcpy(base + c.first, c.second.first, c.second.second);
+    memcpy(base + b.h_pairdev, &b.pr->dev, sizeof(PairDev));
+    ((PairDev**)(st + ptr_off))[k] = b.pr->d_dev;
+    const PairDev& D = b.pr->dev;
+    maxN = std::max(maxN, std::max(D.x.n, D.y.n));
+    maxNt = std::max(maxNt, std::max(D.x.nt, D.y.nt));
+    maxDiag = std::max(maxDiag, D.n_diag);
+    maxKp = std::max(maxKp, D.Kp);
+    maxKC = std::max(maxKC, D.K + D.C);
+  }
+  rc = check_cuda(ctx, cudaMemcpyAsync(arena->dev, st, scal_off, cudaMemcpyHostToDevice, ctx->stream), "H2D pair arena");
+  if (!rc) rc = check_cuda(ctx, cudaMemsetAsync(arena->dev + scal_off, 0, (size_t)n * 4 * sizeof(double), ctx->stream), "memset scalars");
+  // ---- F0/F1 and the packed records on device, one launch each for the whole batch
+  PairDev* const* dptrs = (PairDev* const*)(arena->dev + ptr_off);
+  if (!rc) {
+    const int threads = std::max(32, (maxKp + 31) / 32 * 32);
+    const size_t smem = (size_t)(maxKC + 32) * sizeof(double);
+    prepare_side_kernel<<<dim3(maxN, n, 2), threads, smem, ctx->stream>>>(dptrs);
+    prepare_trans_kernel<<<dim3((maxNt + 127) / 128, n, 2), 128, 0, ctx->stream>>>(dptrs);
+    pack_meta_kernel<<<dim3((maxN + 127) / 128, n, 2), 128, 0, ctx->stream>>>(dptrs);
+    const int chunks = std::max(1, std::min(maxDiag, (4 * ctx->sm_count + n - 1) / n));
+    count_cells_kernel<<<dim3(chunks, n), 128, 0, ctx->stream>>>(dptrs);
+    ctx->launches += 4;
+    rc = check_cuda(ctx, cudaGetLastError(), "prepare kernels");
+  }
+  std::vector<double> scal((size_t)n * 4);
+  if (!rc) rc = check_cuda(ctx, cudaMemcpyAsync(scal.data(), arena->dev + scal_off, scal.size() * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream), "D2H n_cells");
+  // descriptors were only borrowed, and the staging buffer is reused by the next call
+  if (!rc) rc = check_cuda(ctx, cudaStreamSynchronize(ctx->stream), "sync after pair prepare");
+  if (rc) {
+    cudaFreeAsync(arena->dev, ctx->stream);
+    delete arena;
+    return fail(rc);
+  }
+  for (int k = 0; k < n; ++k) {
+    hist_pair* pr = builds[k].pr;
+    unsigned long long nc;
+    memcpy(&nc, &scal[(size_t)k * 4 + 2], sizeof(nc));
+    pr->info.n_cells = (int64_t)nc;
+    pr->arena = arena;
+    ++arena->refs;
+    out[k] = pr;
+  }
+  return HIST_OK;
+}
+
+extern "C" int hist_pair_prepare(hist_ctx* ctx, const hist_profile* x, const hist_profile* y, const hist_pairhmm_desc* hmm,
+                                 const hist_env_desc* env, hist_pair** out) {
+  if (!ctx || !x || !y || !hmm || !out) return set_err(ctx, HIST_ERR_ARG, "hist_pair_prepare: NULL argument");
+  return hist_pair_prepare_batch(ctx, 1, &x, &y, &hmm, &env, 0, out);
 }
 
 extern "C" void hist_pair_destroy(hist_pair* pr) {
   if (!pr) return;
   cudaSetDevice(pr->ctx->device);
-  if (pr->dev.bA) cudaFreeAsync(pr->dev.bA, pr->ctx->stream);
-  if (pr->slab) cudaFreeAsync(pr->slab, pr->ctx->stream);
+  if (pr->bwd_planes) cudaFreeAsync(pr->bwd_planes, pr->ctx->stream);
+  arena_release(pr->ctx, pr->arena);
   delete pr;
 }
 

@@ -23,12 +23,15 @@
 
 namespace hb {
 
-#define HB_RING 4  // diagonals kept in shared memory (power of two)
+#define HB_RING_MAX 16  // most diagonals kept in shared memory (power of two)
 
+// Shared-memory view of one strip: the last R diagonals of cells ("ring") plus their layout records.
 struct Ring {
-  float4* A;
-  float2* B;
-  int cap;   // slots per ring row; 0 = ring disabled
+  float4* A;     // [R][cap] (IMM, IMD, IDM, IMI)
+  float4* B;     // [R][cap] (IIW, exponent bits, Backward only: IMM * absorb, 0)
+  int4* info;    // [R] {ilo, width, off, 0} of the diagonal held in each ring row
+  int cap;       // slots per ring row
+  int R;         // ring rows (0 = ring disabled), power of two
 };
 
 __device__ __forceinline__ int cell_slot(const PairDev& P, const DiagInfo& di, int i, int j) {
@@ -41,69 +44,116 @@ __device__ __forceinline__ int cell_slot(const PairDev& P, const DiagInfo& di, i
   return -1;
 }
 
-// Fetch cell (i,j) written `dist` = |d - dcur| diagonals ago.  Returns false for cells that do
-// not exist (outside the matrix / storage) or are all-zero ("-inf" in the reference).
-__device__ __forceinline__ bool fetch_cell(const PairDev& P, const float4* __restrict__ gA, const float2* __restrict__ gB,
-                                           const Ring& ring, int dcur, int i, int j, float4& a, float2& b) {
-  if (i < 0 || j < 0 || i > P.x.n - 2 || j > P.y.n - 2) return false;
-  const int d = i + j;
-  const DiagInfo di = P.dinfo[d];
-  const int s = cell_slot(P, di, i, j);
-  if (s < 0) return false;
-  const int dist = d > dcur ? d - dcur : dcur - d;
-  if (ring.cap > 0 && dist < HB_RING) {
-    const int r = (d & (HB_RING - 1)) * ring.cap + s;
-    a = ring.A[r];
-    b = ring.B[r];
+// Layout of the two most recently finished diagonals (d -/+ 1, d -/+ 2 in sweep direction), kept in
+// registers: they hold nearly every predecessor, so the common fetch needs no layout lookup.
+struct Recent {
+  int ilo1, w1, ilo2, w2;
+};
+
+// Fetch cell (i2,j2), whose edge slots (xs for row i2, ys for column j2) the caller already holds.
+// Returns false when !en, for cells that are not stored, or all-zero cells ("-inf" in the reference).
+template <bool BWD>
+__device__ __forceinline__ bool fetch_cell(const PairDev& P, const Ring& ring, const Recent& rc, int dcur, bool en, int i2, int j2,
+                                           int xs, int ys, float4& a, float4& b) {
+  if (!en) return false;
+  const int d2 = i2 + j2;
+  const int dist = BWD ? d2 - dcur : dcur - d2;
+  const bool near = dist < ring.R;
+  int ilo, width;
+  unsigned off = 0;
+  if (near) {
+    if (dist <= 2) {
+      ilo = dist == 1 ? rc.ilo1 : rc.ilo2;
+      width = dist == 1 ? rc.w1 : rc.w2;
+    } else {
+      const int4 ri = ring.info[d2 & (ring.R - 1)];
+      ilo = ri.x; width = ri.y;
+    }
   } else {
-    a = gA[di.off + s];
-    b = gB[di.off + s];
+    const DiagInfo di = P.dinfo[d2];
+    ilo = di.ilo; width = di.width; off = di.off;
+  }
+  const int r = i2 - ilo;
+  int s;
+  if ((unsigned)r < (unsigned)width) s = P.nS + r;
+  else if (xs >= 0) s = xs;
+  else if (ys >= 0) s = P.nS + width + ys;
+  else return false;
+  if (near) {
+    const int q = (d2 & (ring.R - 1)) * ring.cap + s;
+    a = ring.A[q];
+    b = ring.B[q];
+  } else {
+    const float4* gA = BWD ? P.bA : P.fA;
+    const float2* gB = BWD ? P.bB : P.fB;
+    a = gA[off + s];
+    const float2 t = gB[off + s];
+    b = make_float4(t.x, t.y, BWD ? a.x * P.absorb[off + s] : 0.f, 0.f);
   }
   return __float_as_int(b.y) > HB_EXP_ZERO / 2;
 }
 
-__device__ __forceinline__ float absorb_hat(const PairDev& P, int i, int j) {
-  // sum_k Xhat[i][k] * (root[k] * Yhat[j][k])  ==  exp(computeLogProbAbsorb(i,j)) * 2^-(ex[i]+ey[j])   (forward.h:112-124)
-  const float* __restrict__ hx = P.x.H + (size_t)i * P.K;
-  const float* __restrict__ hy = P.y.H + (size_t)j * P.K;
-  float acc = 0.f;
-  if ((P.K & 3) == 0) {
-    const float4* x4 = reinterpret_cast<const float4*>(hx);
-    const float4* y4 = reinterpret_cast<const float4*>(hy);
-    for (int k = 0; k < P.K / 4; ++k) {
-      const float4 u = __ldg(x4 + k), v = __ldg(y4 + k);
-      acc = fmaf(u.x, v.x, acc);
-      acc = fmaf(u.y, v.y, acc);
-      acc = fmaf(u.z, v.z, acc);
-      acc = fmaf(u.w, v.w, acc);
-    }
-  } else {
-    for (int k = 0; k < P.K; ++k) acc = fmaf(__ldg(hx + k), __ldg(hy + k), acc);
-  }
-  return acc;
-}
-
 // ------------------------------------------------------------------ Forward cell (forward.cpp:86-200)
-__device__ Cell forward_cell(const PairDev& P, const Ring& ring, int d, int i, int j) {
-  const unsigned fx = P.x.flags[i], fy = P.y.flags[j];
+// xa/xb/xe, ya/yb/ye: packed records of x state i and y state j; ab = absorb plane value of this cell.
+// The contributions through the FIRST in-edge of each state (the only one for almost every state) are
+// fetched together and combined under one common exponent, so the three cell reads and the FMA groups
+// are independent instructions; further in-edges go through the generic aligned accumulation.
+__device__ __forceinline__ Cell forward_cell(const PairDev& P, const Ring& ring, const Recent& rc, int d, int i, int j,
+                                             const int4 xa, const int4 xb, const float2 xe, const int4 ya, const int4 yb,
+                                             const float2 ye, const float ab) {
+  const unsigned fx = xa.x & 0xff, fy = ya.x & 0xff;
+  const int xc = (int)((unsigned)xa.x >> 8), yc = (int)((unsigned)ya.x >> 8);
   const bool xEmit = fx & F_EMIT, yEmit = fy & F_EMIT;
   const bool xReady = fx & F_READY, yReady = fy & F_READY;
   const bool xEmitOrStart = fx & F_EMIT_OR_START;
-  Cell a = zero_cell();
-  if (i == 0 && j == 0) {  // lpStart() = 0 (forward.cpp:73)
-    a.v[0] = 1.f;
-    a.E = 0;
-  }
+  const bool immByX = !xEmit && !(!yEmit && xEmitOrStart);  // third IMM branch (forward.cpp:193-199)
+  const bool doX = yReady && xc > 0;                         // x-moves: sources (src_x, j)   (forward.cpp:95-129)
+  const bool doY = (yEmit ? xReady : true) && yc > 0;        // y-moves: sources (i, src_y)   (forward.cpp:131-163)
+  const bool doD = xEmit && yEmit && xc > 0 && yc > 0;       // xy-moves into IMM              (forward.cpp:165-184)
   const float (*W)[6] = P.W;
-  float4 sa;
-  float2 sb;
-  // x-moves: sources (src_x, j)   (forward.cpp:95-129, 193-199)
-  if (yReady) {
-    const bool immByX = !xEmit && !(!yEmit && xEmitOrStart);  // third IMM branch
-    for (int q = P.x.in_off[i]; q < P.x.in_off[i + 1]; ++q) {
-      const int t = P.x.in_idx[q];
-      if (!fetch_cell(P, P.fA, P.fB, ring, d, P.x.t_src[t], j, sa, sb)) continue;
-      const float s = acc_align(a, __float_as_int(sb.y) + P.x.t_e[t]) * P.x.t_m[t];
+  float4 xA, xB, yA, yB, dA, dB;
+  const bool vX = fetch_cell<false>(P, ring, rc, d, doX, xb.x, j, xb.w, ya.w, xA, xB);
+  const bool vY = fetch_cell<false>(P, ring, rc, d, doY, i, yb.x, xa.w, yb.w, yA, yB);
+  const bool vD = fetch_cell<false>(P, ring, rc, d, doD, xb.x, yb.x, xb.w, yb.w, dA, dB);
+  const bool origin = i == 0 && j == 0;  // lpStart() = 0 (forward.cpp:73)
+  const int eX = vX ? __float_as_int(xB.y) + xb.y : HB_EXP_ZERO;
+  const int eY = vY ? __float_as_int(yB.y) + yb.y : HB_EXP_ZERO;
+  const int eD = vD ? __float_as_int(dB.y) + xb.y + yb.y : HB_EXP_ZERO;
+  Cell a;
+  a.E = max(max(eX, eY), max(eD, origin ? 0 : HB_EXP_ZERO));
+  const float sX = vX ? pow2_neg(eX - a.E) * __int_as_float(xb.z) : 0.f;
+  const float sY = vY ? pow2_neg(eY - a.E) * __int_as_float(yb.z) : 0.f;
+  const float sD = vD ? pow2_neg(eD - a.E) * __int_as_float(xb.z) * __int_as_float(yb.z) : 0.f;
+  a.v[0] = origin ? pow2_neg(-a.E) : 0.f;
+  a.v[1] = a.v[2] = a.v[3] = a.v[4] = 0.f;
+  if (vX) {
+    if (xEmit) {
+      a.v[1] = sX * (xA.x * W[0][1] + xA.y * W[1][1] + xA.z * W[2][1] + xA.w * W[3][1]);
+      a.v[4] = sX * (xA.x * W[0][4] + xA.w * W[3][4] + xB.x * W[4][4]);
+    } else {
+      a.v[1] = sX * xA.y;
+      a.v[4] = sX * xB.x;
+      if (immByX) a.v[0] = fmaf(sX, xA.x, a.v[0]);
+    }
+  }
+  if (vY) {
+    if (yEmit) {
+      a.v[2] = sY * (yA.x * W[0][2] + yA.y * W[1][2] + yA.z * W[2][2] + yB.x * W[4][2]);
+      a.v[3] = sY * (yA.x * W[0][3] + yA.w * W[3][3]);
+    } else {
+      a.v[2] = sY * yA.z;
+      a.v[3] = sY * yA.w;
+      if (xEmitOrStart) a.v[0] = fmaf(sY, yA.x, a.v[0]);
+    }
+  }
+  if (vD) a.v[0] = fmaf(sD, dA.x * W[0][0] + dA.y * W[1][0] + dA.z * W[2][0] + dA.w * W[3][0] + dB.x * W[4][0], a.v[0]);
+  // ---- further in-edges (state DAGs)
+  float4 sa, sb;
+  if (doX)
+    for (int q = 1; q < xc; ++q) {
+      const int4 e = P.x.in_edges[xa.y + q];
+      if (!fetch_cell<false>(P, ring, rc, d, true, e.x, j, e.w, ya.w, sa, sb)) continue;
+      const float s = acc_align(a, __float_as_int(sb.y) + e.y) * __int_as_float(e.z);
       if (xEmit) {
         a.v[1] = fmaf(s, sa.x * W[0][1] + sa.y * W[1][1] + sa.z * W[2][1] + sa.w * W[3][1], a.v[1]);
         a.v[4] = fmaf(s, sa.x * W[0][4] + sa.w * W[3][4] + sb.x * W[4][4], a.v[4]);
@@ -113,13 +163,11 @@ __device__ Cell forward_cell(const PairDev& P, const Ring& ring, int d, int i, i
         if (immByX) a.v[0] = fmaf(s, sa.x, a.v[0]);
       }
     }
-  }
-  // y-moves: sources (i, src_y)   (forward.cpp:131-163, 186-191)
-  if (yEmit ? xReady : true) {
-    for (int q = P.y.in_off[j]; q < P.y.in_off[j + 1]; ++q) {
-      const int t = P.y.in_idx[q];
-      if (!fetch_cell(P, P.fA, P.fB, ring, d, i, P.y.t_src[t], sa, sb)) continue;
-      const float s = acc_align(a, __float_as_int(sb.y) + P.y.t_e[t]) * P.y.t_m[t];
+  if (doY)
+    for (int q = 1; q < yc; ++q) {
+      const int4 e = P.y.in_edges[ya.y + q];
+      if (!fetch_cell<false>(P, ring, rc, d, true, i, e.x, xa.w, e.w, sa, sb)) continue;
+      const float s = acc_align(a, __float_as_int(sb.y) + e.y) * __int_as_float(e.z);
       if (yEmit) {
         a.v[2] = fmaf(s, sa.x * W[0][2] + sa.y * W[1][2] + sa.z * W[2][2] + sb.x * W[4][2], a.v[2]);
         a.v[3] = fmaf(s, sa.x * W[0][3] + sa.w * W[3][3], a.v[3]);
@@ -129,119 +177,132 @@ __device__ Cell forward_cell(const PairDev& P, const Ring& ring, int d, int i, i
         if (xEmitOrStart) a.v[0] = fmaf(s, sa.x, a.v[0]);
       }
     }
-  }
-  // xy-moves into IMM   (forward.cpp:165-184)
-  if (xEmit && yEmit) {
-    for (int qx = P.x.in_off[i]; qx < P.x.in_off[i + 1]; ++qx) {
-      const int tx = P.x.in_idx[qx];
-      const int sx = P.x.t_src[tx];
-      const float mx = P.x.t_m[tx];
-      const int ex = P.x.t_e[tx];
-      for (int qy = P.y.in_off[j]; qy < P.y.in_off[j + 1]; ++qy) {
-        const int ty = P.y.in_idx[qy];
-        if (!fetch_cell(P, P.fA, P.fB, ring, d, sx, P.y.t_src[ty], sa, sb)) continue;
-        const float s = acc_align(a, __float_as_int(sb.y) + ex + P.y.t_e[ty]) * mx * P.y.t_m[ty];
-        a.v[0] = fmaf(s, sa.x * W[0][0] + sa.y * W[1][0] + sa.z * W[2][0] + sa.w * W[3][0] + sb.x * W[4][0], a.v[0]);
+  if (doD && xc + yc > 2) {
+    int4 ex = xb;
+    for (int qx = 0; qx < xc;) {
+      int4 ey = yb;
+      for (int qy = 0; qy < yc;) {
+        if ((qx | qy) && fetch_cell<false>(P, ring, rc, d, true, ex.x, ey.x, ex.w, ey.w, sa, sb)) {
+          const float s = acc_align(a, __float_as_int(sb.y) + ex.y + ey.y) * __int_as_float(ex.z) * __int_as_float(ey.z);
+          a.v[0] = fmaf(s, sa.x * W[0][0] + sa.y * W[1][0] + sa.z * W[2][0] + sa.w * W[3][0] + sb.x * W[4][0], a.v[0]);
+        }
+        if (++qy < yc) ey = P.y.in_edges[ya.y + qy];
       }
+      if (++qx < xc) ex = P.x.in_edges[xa.y + qx];
     }
-    a.v[0] *= absorb_hat(P, i, j);
   }
+  if (xEmit && yEmit) a.v[0] *= ab;
   // emissions are applied after the predecessor sums (forward.cpp:116-117, 151-152)
   if (xEmit && yReady) {
-    a.v[1] *= P.x.rs[i];
-    a.v[4] *= P.x.ins[i];
+    a.v[1] *= xe.x;
+    a.v[4] *= xe.y;
   }
   if (yEmit && xReady) {
-    a.v[2] *= P.y.rs[j];
-    a.v[3] *= P.y.ins[j];
+    a.v[2] *= ye.x;
+    a.v[3] *= ye.y;
   }
   cell_normalise(a);
   return a;
 }
 
 // ------------------------------------------------------------------ Backward cell (forward.cpp:1008-1086)
-__device__ Cell backward_cell(const PairDev& P, const Ring& ring, int d, int i, int j) {
-  const unsigned fx = P.x.flags[i], fy = P.y.flags[j];
+// xa,xn,x0,x1 / ya,yn,y0,y1: the four backward records of x state i / y state j.
+__device__ __forceinline__ Cell backward_cell(const PairDev& P, const Ring& ring, const Recent& rc, int d, int i, int j, const int4 xa,
+                                              const int4 xn, const int4 x0, const int4 x1, const int4 ya, const int4 yn,
+                                              const int4 y0, const int4 y1) {
+  const unsigned fx = xa.x & 0xff, fy = ya.x & 0xff;
+  const int xac = (int)((unsigned)xa.x >> 8), yac = (int)((unsigned)ya.x >> 8);
   const bool xReady = fx & F_READY, yReady = fy & F_READY;
   const bool xEmitOrStart = fx & F_EMIT_OR_START;
-  const int xEnd = P.x.n - 1, yEnd = P.y.n - 1;
-  Cell a = zero_cell();
   const float (*W)[6] = P.W;
-  float4 sa;
-  float2 sb;
-  // xy-absorbing transitions into IMM (forward.cpp:1017-1030)
-  for (int qx = P.x.ao_off[i]; qx < P.x.ao_off[i + 1]; ++qx) {
-    const int tx = P.x.ao_idx[qx];
-    const int dx = P.x.t_dst[tx];
-    for (int qy = P.y.ao_off[j]; qy < P.y.ao_off[j + 1]; ++qy) {
-      const int ty = P.y.ao_idx[qy];
-      const int dy = P.y.t_dst[ty];
-      if (!fetch_cell(P, P.bA, P.bB, ring, d, dx, dy, sa, sb)) continue;
-      const float s = acc_align(a, __float_as_int(sb.y) + P.x.t_e[tx] + P.y.t_e[ty]) * P.x.t_m[tx] * P.y.t_m[ty];
-      const float dest = s * absorb_hat(P, dx, dy) * sa.x;
+  const bool doD = xac > 0 && yac > 0;   // xy-absorbing transitions into IMM (forward.cpp:1017-1030)
+  const bool doX = yReady && xac > 0;    // x-absorbing transitions into IMD, IIW (forward.cpp:1032-1048)
+  const bool doY = xReady && yac > 0;    // y-absorbing transitions into IDM, IMI (forward.cpp:1050-1065)
+  // transitions into EEE: the initial assignment of forward.cpp:981-995, which the sweep then accumulates onto
+  const bool toEnd = (fx & F_TO_END) && (fy & F_TO_END);
+  float4 dA, dB, xA, xB, yA, yB;
+  const bool vD = fetch_cell<true>(P, ring, rc, d, doD, x0.x, y0.x, x0.z, y0.z, dA, dB);
+  const bool vX = fetch_cell<true>(P, ring, rc, d, doX, x0.x, j, x0.z, ya.w, xA, xB);
+  const bool vY = fetch_cell<true>(P, ring, rc, d, doY, i, y0.x, xa.w, y0.z, yA, yB);
+  const int eD = vD ? __float_as_int(dB.y) + x0.y + y0.y : HB_EXP_ZERO;
+  const int eX = vX ? __float_as_int(xB.y) + x0.y : HB_EXP_ZERO;
+  const int eY = vY ? __float_as_int(yB.y) + y0.y : HB_EXP_ZERO;
+  const int eE = toEnd ? xn.z + yn.z : HB_EXP_ZERO;
+  Cell a;
+  a.E = max(max(eD, eX), max(eY, eE));
+  const float dest = vD ? pow2_neg(eD - a.E) * __int_as_float(x1.x) * __int_as_float(y1.x) * dB.z : 0.f;  // absorb(dx,dy) * B(dx,dy,IMM)
+  const float sX = vX ? pow2_neg(eX - a.E) : 0.f;
+  const float sY = vY ? pow2_neg(eY - a.E) : 0.f;
+  const float sE = toEnd ? pow2_neg(eE - a.E) * __int_as_float(xn.w) * __int_as_float(yn.w) : 0.f;
+  const float dmd = vX ? sX * __int_as_float(x1.y) * xA.y : 0.f, diw = vX ? sX * __int_as_float(x1.z) * xB.x : 0.f;
+  const float ddm = vY ? sY * __int_as_float(y1.y) * yA.z : 0.f, dmi = vY ? sY * __int_as_float(y1.z) * yA.w : 0.f;
+  a.v[0] = W[0][0] * dest + W[0][1] * dmd + W[0][4] * diw + W[0][2] * ddm + W[0][3] * dmi + sE * W[0][5];
+  a.v[1] = W[1][0] * dest + W[1][1] * dmd + W[1][2] * ddm + sE * W[1][5];
+  a.v[2] = W[2][0] * dest + W[2][1] * dmd + W[2][2] * ddm + sE * W[2][5];
+  a.v[3] = W[3][0] * dest + W[3][1] * dmd + W[3][4] * diw + W[3][3] * dmi + sE * W[3][5];
+  a.v[4] = W[4][0] * dest + W[4][4] * diw + W[4][2] * ddm + sE * W[4][5];
+  // ---- further absorbing out-edges (state DAGs)
+  float4 sa, sb;
+  if (doD && xac + yac > 2) {
+    int4 ex0 = x0, ex1 = x1;
+    for (int qx = 0; qx < xac;) {
+      int4 ey0 = y0, ey1 = y1;
+      for (int qy = 0; qy < yac;) {
+        if ((qx | qy) && fetch_cell<true>(P, ring, rc, d, true, ex0.x, ey0.x, ex0.z, ey0.z, sa, sb)) {
+          const float s = acc_align(a, __float_as_int(sb.y) + ex0.y + ey0.y) * __int_as_float(ex1.x) * __int_as_float(ey1.x);
+          const float dst = s * sb.z;
 #pragma unroll
-      for (int k = 0; k < 5; ++k) a.v[k] = fmaf(W[k][0], dest, a.v[k]);
+          for (int k = 0; k < 5; ++k) a.v[k] = fmaf(W[k][0], dst, a.v[k]);
+        }
+        if (++qy < yac) { ey0 = P.y.ao_edges[2 * (ya.y + qy)]; ey1 = P.y.ao_edges[2 * (ya.y + qy) + 1]; }
+      }
+      if (++qx < xac) { ex0 = P.x.ao_edges[2 * (xa.y + qx)]; ex1 = P.x.ao_edges[2 * (xa.y + qx) + 1]; }
     }
   }
-  // x-absorbing transitions into IMD, IIW (forward.cpp:1032-1048)
-  if (yReady)
-    for (int qx = P.x.ao_off[i]; qx < P.x.ao_off[i + 1]; ++qx) {
-      const int tx = P.x.ao_idx[qx];
-      const int dx = P.x.t_dst[tx];
-      if (!fetch_cell(P, P.bA, P.bB, ring, d, dx, j, sa, sb)) continue;
-      const float s = acc_align(a, __float_as_int(sb.y) + P.x.t_e[tx]) * P.x.t_m[tx];
-      const float dmd = s * P.x.rs[dx] * sa.y, diw = s * P.x.ins[dx] * sb.x;
-      a.v[0] = fmaf(W[0][1], dmd, fmaf(W[0][4], diw, a.v[0]));
-      a.v[1] = fmaf(W[1][1], dmd, a.v[1]);
-      a.v[2] = fmaf(W[2][1], dmd, a.v[2]);
-      a.v[3] = fmaf(W[3][1], dmd, fmaf(W[3][4], diw, a.v[3]));
-      a.v[4] = fmaf(W[4][4], diw, a.v[4]);
+  if (doX)
+    for (int q = 1; q < xac; ++q) {
+      const int4 e0 = P.x.ao_edges[2 * (xa.y + q)], e1 = P.x.ao_edges[2 * (xa.y + q) + 1];
+      if (!fetch_cell<true>(P, ring, rc, d, true, e0.x, j, e0.z, ya.w, sa, sb)) continue;
+      const float s = acc_align(a, __float_as_int(sb.y) + e0.y);
+      const float md = s * __int_as_float(e1.y) * sa.y, iw = s * __int_as_float(e1.z) * sb.x;
+      a.v[0] = fmaf(W[0][1], md, fmaf(W[0][4], iw, a.v[0]));
+      a.v[1] = fmaf(W[1][1], md, a.v[1]);
+      a.v[2] = fmaf(W[2][1], md, a.v[2]);
+      a.v[3] = fmaf(W[3][1], md, fmaf(W[3][4], iw, a.v[3]));
+      a.v[4] = fmaf(W[4][4], iw, a.v[4]);
     }
-  // y-absorbing transitions into IDM, IMI (forward.cpp:1050-1065)
-  if (xReady)
-    for (int qy = P.y.ao_off[j]; qy < P.y.ao_off[j + 1]; ++qy) {
-      const int ty = P.y.ao_idx[qy];
-      const int dy = P.y.t_dst[ty];
-      if (!fetch_cell(P, P.bA, P.bB, ring, d, i, dy, sa, sb)) continue;
-      const float s = acc_align(a, __float_as_int(sb.y) + P.y.t_e[ty]) * P.y.t_m[ty];
-      const float ddm = s * P.y.rs[dy] * sa.z, dmi = s * P.y.ins[dy] * sa.w;
-      a.v[0] = fmaf(W[0][2], ddm, fmaf(W[0][3], dmi, a.v[0]));
-      a.v[1] = fmaf(W[1][2], ddm, a.v[1]);
-      a.v[2] = fmaf(W[2][2], ddm, a.v[2]);
-      a.v[4] = fmaf(W[4][2], ddm, a.v[4]);
-      a.v[3] = fmaf(W[3][3], dmi, a.v[3]);
+  if (doY)
+    for (int q = 1; q < yac; ++q) {
+      const int4 e0 = P.y.ao_edges[2 * (ya.y + q)], e1 = P.y.ao_edges[2 * (ya.y + q) + 1];
+      if (!fetch_cell<true>(P, ring, rc, d, true, i, e0.x, xa.w, e0.z, sa, sb)) continue;
+      const float s = acc_align(a, __float_as_int(sb.y) + e0.y);
+      const float dm = s * __int_as_float(e1.y) * sa.z, mi = s * __int_as_float(e1.z) * sa.w;
+      a.v[0] = fmaf(W[0][2], dm, fmaf(W[0][3], mi, a.v[0]));
+      a.v[1] = fmaf(W[1][2], dm, a.v[1]);
+      a.v[2] = fmaf(W[2][2], dm, a.v[2]);
+      a.v[4] = fmaf(W[4][2], dm, a.v[4]);
+      a.v[3] = fmaf(W[3][3], mi, a.v[3]);
     }
-  // x-nonabsorbing transitions in IMD, IIW, IMM (forward.cpp:1067-1075)
+  // x-nonabsorbing transitions in IMD, IIW, IMM (forward.cpp:1067-1075); transitions into END carry no cell
   if (yReady)
-    for (int qx = P.x.no_off[i]; qx < P.x.no_off[i + 1]; ++qx) {
-      const int tx = P.x.no_idx[qx];
-      if (!fetch_cell(P, P.bA, P.bB, ring, d, P.x.t_dst[tx], j, sa, sb)) continue;
-      const float s = acc_align(a, __float_as_int(sb.y) + P.x.t_e[tx]) * P.x.t_m[tx];
+    for (int q = 0; q < xn.y; ++q) {
+      const int4 e0 = P.x.no_edges[2 * (xn.x + q)], e1 = P.x.no_edges[2 * (xn.x + q) + 1];
+      if (e0.w) continue;  // -> END
+      if (!fetch_cell<true>(P, ring, rc, d, true, e0.x, j, e0.z, ya.w, sa, sb)) continue;
+      const float s = acc_align(a, __float_as_int(sb.y) + e0.y) * __int_as_float(e1.x);
       a.v[1] = fmaf(s, sa.y, a.v[1]);
       a.v[4] = fmaf(s, sb.x, a.v[4]);
       a.v[0] = fmaf(s, sa.x, a.v[0]);
     }
   // y-nonabsorbing transitions in IDM, IMI, IMM (forward.cpp:1077-1085)
-  for (int qy = P.y.no_off[j]; qy < P.y.no_off[j + 1]; ++qy) {
-    const int ty = P.y.no_idx[qy];
-    if (!fetch_cell(P, P.bA, P.bB, ring, d, i, P.y.t_dst[ty], sa, sb)) continue;
-    const float s = acc_align(a, __float_as_int(sb.y) + P.y.t_e[ty]) * P.y.t_m[ty];
+  for (int q = 0; q < yn.y; ++q) {
+    const int4 e0 = P.y.no_edges[2 * (yn.x + q)], e1 = P.y.no_edges[2 * (yn.x + q) + 1];
+    if (e0.w) continue;
+    if (!fetch_cell<true>(P, ring, rc, d, true, i, e0.x, xa.w, e0.z, sa, sb)) continue;
+    const float s = acc_align(a, __float_as_int(sb.y) + e0.y) * __int_as_float(e1.x);
     a.v[2] = fmaf(s, sa.z, a.v[2]);
     a.v[3] = fmaf(s, sa.w, a.v[3]);
     if (xEmitOrStart) a.v[0] = fmaf(s, sa.x, a.v[0]);
-  }
-  // transitions into EEE: the initial assignment of forward.cpp:981-995, which the sweep
-  // then accumulates onto
-  for (int qx = P.x.no_off[i]; qx < P.x.no_off[i + 1]; ++qx) {
-    const int tx = P.x.no_idx[qx];
-    if (P.x.t_dst[tx] != xEnd) continue;
-    for (int qy = P.y.no_off[j]; qy < P.y.no_off[j + 1]; ++qy) {
-      const int ty = P.y.no_idx[qy];
-      if (P.y.t_dst[ty] != yEnd) continue;
-      const float s = acc_align(a, P.x.t_e[tx] + P.y.t_e[ty]) * P.x.t_m[tx] * P.y.t_m[ty];
-#pragma unroll
-      for (int k = 0; k < 5; ++k) a.v[k] = fmaf(s, W[k][5], a.v[k]);
-    }
   }
   cell_normalise(a);
   return a;
@@ -254,12 +315,432 @@ __device__ __forceinline__ double lse_exact(double a, double b) {
   return m + log1p(exp(-fabs(a - b)));
 }
 
+// Map thread slot t of diagonal d to its cell; false if the slot owns no in-envelope cell.
+// xk / yk receive the first packed record of the two states (flags, band key, edge slot).
+template <bool BWD>
+__device__ __forceinline__ bool slot_cell(const PairDev& P, const DiagInfo& di, int d, int t, int& i, int& j, int4& xk, int4& yk) {
+  bool ok = true;
+  if (t < P.nS) {
+    i = P.start_rows[t];
+    j = d - i;
+    if (i >= di.ilo && i < di.ilo + di.width) ok = false;  // the main interval owns this cell
+  } else if (t < P.nS + di.width) {
+    i = di.ilo + (t - P.nS);
+    j = d - i;
+  } else {
+    j = P.end_cols[t - P.nS - di.width];
+    i = d - j;
+    if (i >= di.ilo && i < di.ilo + di.width) ok = false;
+  }
+  if (!ok || i < 0 || j < 0 || i > P.x.n - 2 || j > P.y.n - 2) return false;
+  xk = BWD ? P.x.bm[4 * i] : P.x.fm_a[i];
+  yk = BWD ? P.y.bm[4 * j] : P.y.fm_a[j];
+  if (t >= P.nS + di.width && xk.w >= 0) return false;  // a near-start slot owns it
+  // DPMatrix::inEnvelope (forward.h:92-98)
+  return ((xk.x | yk.x) & F_NEAR) || P.max_dist < 0 || hb_iabs(xk.z - yk.z) <= P.max_dist;
+}
+
+// ------------------------------------------------------------------ absorb plane
+// exp(computeLogProbAbsorb(i,j)) (forward.h:112-124) for every stored both-emit cell, as
+// sum_k Xhat[i][k] * (root[k] Yhat[j][k]) relative to 2^(ex[i]+ey[j]).  One warp per diagonal: the lanes
+// read consecutive rows of the two emission tables (coalesced 16-B loads) and write consecutive floats.
+// grid = (chunks, pairs).
+__global__ void __launch_bounds__(256) absorb_kernel(PairDev* const* __restrict__ pairs) {
+  __shared__ PairDev P;
+  {
+    const int* s = reinterpret_cast<const int*>(pairs[blockIdx.y]);
+    int* dptr = reinterpret_cast<int*>(&P);
+    for (int k = threadIdx.x; k < (int)(sizeof(PairDev) / sizeof(int)); k += blockDim.x) dptr[k] = s[k];
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const int warps = (blockDim.x >> 5) * gridDim.x;
+  const int K4 = P.Kp >> 2;
+  for (int d = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); d < P.n_diag; d += warps) {
+    const DiagInfo di = P.dinfo[d];
+    const int nthr = P.nS + di.width + P.nE;
+    for (int t = lane; t < nthr; t += 32) {
+      int i, j;
+      int4 xk, yk;
+      float acc = 0.f;
+      if (slot_cell<false>(P, di, d, t, i, j, xk, yk) && (xk.x & yk.x & F_EMIT)) {
+        const float4* __restrict__ x4 = reinterpret_cast<const float4*>(P.x.H + (size_t)i * P.Kp);
+        const float4* __restrict__ y4 = reinterpret_cast<const float4*>(P.y.H + (size_t)j * P.Kp);
+        float a0 = 0.f, a1 = 0.f;
+        for (int k = 0; k < K4; ++k) {
+          const float4 u = __ldg(x4 + k), v = __ldg(y4 + k);
+          a0 = fmaf(u.x, v.x, a0);
+          a1 = fmaf(u.y, v.y, a1);
+          a0 = fmaf(u.z, v.z, a0);
+          a1 = fmaf(u.w, v.w, a1);
+        }
+        acc = a0 + a1;
+      }
+      P.absorb[di.off + t] = acc;
+    }
+  }
+}
+
 // ------------------------------------------------------------------ the wavefront kernel
+// Everything a lane needs for one cell that does NOT depend on earlier cells: coordinates, packed
+// state records, absorb value.  Loaded one step ahead of its use in the narrow sweep.
+template <bool BWD>
+struct LaneMeta {
+  int i, j;
+  bool ok;       // slot owns an in-range cell (the envelope test still follows, it needs the records)
+  bool tail;     // slot is a near-end column slot
+  int4 xa, xb, ya, yb;   // Forward: fm_a, fm_b;  Backward: bm[0], bm[1]
+  int4 x0, x1, y0, y1;   // Backward only: first absorbing out-edge
+  float2 xe, ye;         // Forward only
+  float ab;
+};
+
+template <bool BWD>
+__device__ __forceinline__ LaneMeta<BWD> load_meta(const PairDev& P, const DiagInfo& di, int d, int t, bool with_ab = true) {
+  LaneMeta<BWD> m;
+  bool ok = t < P.nS + di.width + P.nE;
+  int i = 0, j = 0;
+  m.tail = false;
+  if (t < P.nS) {
+    i = P.start_rows[t];
+    j = d - i;
+    if (i >= di.ilo && i < di.ilo + di.width) ok = false;  // the main interval owns this cell
+  } else if (t < P.nS + di.width) {
+    i = di.ilo + (t - P.nS);
+    j = d - i;
+  } else if (ok) {
+    j = P.end_cols[t - P.nS - di.width];
+    i = d - j;
+    m.tail = true;
+    if (i >= di.ilo && i < di.ilo + di.width) ok = false;
+  }
+  ok = ok && i >= 0 && j >= 0 && i <= P.x.n - 2 && j <= P.y.n - 2;
+  if (!ok) i = j = 0;
+  m.i = i; m.j = j; m.ok = ok;
+  if (BWD) {
+    const int4* xm = P.x.bm + 4 * i;
+    const int4* ym = P.y.bm + 4 * j;
+    m.xa = xm[0]; m.xb = xm[1]; m.x0 = xm[2]; m.x1 = xm[3];
+    m.ya = ym[0]; m.yb = ym[1]; m.y0 = ym[2]; m.y1 = ym[3];
+  } else {
+    m.xa = P.x.fm_a[i]; m.xb = P.x.fm_b[i]; m.xe = P.x.emis[i];
+    m.ya = P.y.fm_a[j]; m.yb = P.y.fm_b[j]; m.ye = P.y.emis[j];
+  }
+  m.ab = ok && with_ab ? P.absorb[di.off + t] : 0.f;
+  return m;
+}
+
+template <bool BWD>
+__device__ __forceinline__ void compute_store(const PairDev& P, const Ring& ring, const Recent& rc, const DiagInfo& di, int d, int t,
+                                              const LaneMeta<BWD>& m, float4* gA, float2* gB) {
+  Cell c = zero_cell();
+  float aux = 0.f;
+  // a near-start slot owns cells of near-end columns; then DPMatrix::inEnvelope (forward.h:92-98)
+  const bool ok = m.ok && !(m.tail && m.xa.w >= 0) &&
+                  (((m.xa.x | m.ya.x) & F_NEAR) || P.max_dist < 0 || hb_iabs(m.xa.z - m.ya.z) <= P.max_dist);
+  if (ok) {
+    if (BWD) {
+      c = backward_cell(P, ring, rc, d, m.i, m.j, m.xa, m.xb, m.x0, m.x1, m.ya, m.yb, m.y0, m.y1);
+      aux = c.v[0] * m.ab;  // absorb is 0 unless both states emit
+    } else {
+      c = forward_cell(P, ring, rc, d, m.i, m.j, m.xa, m.xb, m.xe, m.ya, m.yb, m.ye, m.ab);
+    }
+  }
+  const float4 va = make_float4(c.v[0], c.v[1], c.v[2], c.v[3]);
+  gA[di.off + t] = va;
+  gB[di.off + t] = make_float2(c.v[4], __int_as_float(c.E));
+  if (ring.R > 0) {
+    const int r = (d & (ring.R - 1)) * ring.cap + t;
+    ring.A[r] = va;
+    ring.B[r] = make_float4(c.v[4], __int_as_float(c.E), aux, 0.f);
+  }
+}
+
+// ------------------------------------------------------------------ narrow strips: warp-specialised sweep
+// Banded merges are thin strips: ~20-40 cells per anti-diagonal, thousands of dependent steps.  The
+// time of a step is the latency of ONE warp's instruction stream, so the stream of the warp that
+// carries the dependency is cut to the arithmetic: a CONSUMER warp (one cell per lane per step) reads
+// its predecessors from the shared-memory ring, does the FMAs, normalises and stores.  Everything
+// that does not depend on earlier cells -- slot -> (i,j), packed state records, envelope test, ring
+// addresses of the predecessors, transition mantissas/exponents, emission factors and the absorb
+// dot product (forward.h:112-124) -- is prepared by HB_NPROD PRODUCER warps, each working
+// HB_NPROD steps ahead, and handed over as a 64-B per-lane record through a shared-memory queue
+// guarded by named barriers (bar.arrive / bar.sync full/empty pairs).  Cells with more than one
+// in-/out-edge, null out-edges or predecessors older than the ring fall back to the generic cell
+// routine on the consumer ("slow" flag).
+#define HB_NPROD 2
+#define HB_DEPTH 4
+#define HB_BAR_FULL 1
+#define HB_BAR_EMPTY (1 + HB_DEPTH)
+enum { R_OK = 1, R_XEMIT = 2, R_YEMIT = 4, R_IMM_BY_X = 8, R_IMM_BY_Y = 16, R_ORIGIN = 32, R_SLOW = 64, R_BOTH = 128, R_TO_END = 256 };
+
+__device__ __forceinline__ void bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+__device__ __forceinline__ void bar_arrive(int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+
+// Ring entry index of cell (i2,j2); -1: not stored; -2: older than the ring (generic path).
+template <bool BWD>
+__device__ __forceinline__ int pred_index(const PairDev& P, const Ring& ring, int dcur, bool en, int i2, int j2, int xs, int ys) {
+  if (!en) return -1;
+  const int d2 = i2 + j2;
+  const int dist = BWD ? d2 - dcur : dcur - d2;
+  if (dist >= ring.R) return -2;
+  const DiagInfo di = P.dinfo[d2];
+  const int r = i2 - di.ilo;
+  int s;
+  if ((unsigned)r < (unsigned)di.width) s = P.nS + r;
+  else if (xs >= 0) s = xs;
+  else if (ys >= 0) s = P.nS + di.width + ys;
+  else return -1;
+  return (d2 & (ring.R - 1)) * ring.cap + s;
+}
+
+__device__ __forceinline__ float absorb_dot(const PairDev& P, int i, int j) {
+  const float4* __restrict__ x4 = reinterpret_cast<const float4*>(P.x.H + (size_t)i * P.Kp);
+  const float4* __restrict__ y4 = reinterpret_cast<const float4*>(P.y.H + (size_t)j * P.Kp);
+  float a0 = 0.f, a1 = 0.f;
+  for (int k = 0; k < (P.Kp >> 2); ++k) {
+    const float4 u = __ldg(x4 + k), v = __ldg(y4 + k);
+    a0 = fmaf(u.x, v.x, a0);
+    a1 = fmaf(u.y, v.y, a1);
+    a0 = fmaf(u.z, v.z, a0);
+    a1 = fmaf(u.w, v.w, a1);
+  }
+  return a0 + a1;
+}
+
+template <bool BWD>
+__device__ __forceinline__ void producer(const PairDev& P, const Ring& ring, int4* rec, int p) {
+  const int t = threadIdx.x & 31;
+  const int nD = P.n_diag;
+  for (int q = p; q < nD; q += HB_NPROD) {
+    const int slot = q % HB_DEPTH;
+    const int d = BWD ? nD - 1 - q : q;
+    const DiagInfo di = P.dinfo[d];
+    const LaneMeta<BWD> m = load_meta<BWD>(P, di, d, t, false);
+    // a near-start slot owns cells of near-end columns; then DPMatrix::inEnvelope (forward.h:92-98)
+    const bool ok = m.ok && !(m.tail && m.xa.w >= 0) &&
+                    (((m.xa.x | m.ya.x) & F_NEAR) || P.max_dist < 0 || hb_iabs(m.xa.z - m.ya.z) <= P.max_dist);
+    const int i = m.i, j = m.j;
+    const unsigned fx = m.xa.x & 0xff, fy = m.ya.x & 0xff;
+    const bool xEmit = fx & F_EMIT, yEmit = fy & F_EMIT;
+    const bool xReady = fx & F_READY, yReady = fy & F_READY;
+    const bool xEmitOrStart = fx & F_EMIT_OR_START;
+    const bool both = xEmit && yEmit;
+    float ab = 0.f;
+    if (ok && both) ab = absorb_dot(P, i, j);
+    int4 r0, r1, r2, r3;
+    int flags = ok ? R_OK : 0;
+    if (!BWD) {
+      const int xc = (int)((unsigned)m.xa.x >> 8), yc = (int)((unsigned)m.ya.x >> 8);
+      const bool doX = ok && yReady && xc > 0;
+      const bool doY = ok && (yEmit ? xReady : true) && yc > 0;
+      const bool doD = ok && both && xc > 0 && yc > 0;
+      const int aX = pred_index<false>(P, ring, d, doX, m.xb.x, j, m.xb.w, m.ya.w);
+      const int aY = pred_index<false>(P, ring, d, doY, i, m.yb.x, m.xa.w, m.yb.w);
+      const int aD = pred_index<false>(P, ring, d, doD, m.xb.x, m.yb.x, m.xb.w, m.yb.w);
+      if (xEmit) flags |= R_XEMIT;
+      if (yEmit) flags |= R_YEMIT;
+      if (!xEmit && !(!yEmit && xEmitOrStart)) flags |= R_IMM_BY_X;
+      if (!yEmit && xEmitOrStart) flags |= R_IMM_BY_Y;
+      if (i == 0 && j == 0) flags |= R_ORIGIN;
+      if (both) flags |= R_BOTH;
+      if (xc > 1 || yc > 1 || aX == -2 || aY == -2 || aD == -2) flags |= R_SLOW;
+      r0 = make_int4(aX, aY, aD, flags);
+      r1 = make_int4(m.xb.y, m.yb.y, m.xb.y + m.yb.y, i);
+      r2 = make_int4(m.xb.z, m.yb.z, __float_as_int(__int_as_float(m.xb.z) * __int_as_float(m.yb.z)), __float_as_int(ab));
+      const bool ex = xEmit && yReady, ey = yEmit && xReady;
+      r3 = make_int4(__float_as_int(ex ? m.xe.x : 1.f), __float_as_int(ex ? m.xe.y : 1.f), __float_as_int(ey ? m.ye.x : 1.f),
+                     __float_as_int(ey ? m.ye.y : 1.f));
+      if (ok) P.absorb[di.off + t] = ab;  // kept for the generic path and for a later Backward fill
+    } else {
+      const int xac = (int)((unsigned)m.xa.x >> 8), yac = (int)((unsigned)m.ya.x >> 8);
+      const bool doD = ok && xac > 0 && yac > 0;
+      const bool doX = ok && yReady && xac > 0;
+      const bool doY = ok && xReady && yac > 0;
+      const int aD = pred_index<true>(P, ring, d, doD, m.x0.x, m.y0.x, m.x0.z, m.y0.z);
+      const int aX = pred_index<true>(P, ring, d, doX, m.x0.x, j, m.x0.z, m.ya.w);
+      const int aY = pred_index<true>(P, ring, d, doY, i, m.y0.x, m.xa.w, m.y0.z);
+      const bool toEnd = (fx & F_TO_END) && (fy & F_TO_END);
+      if (toEnd) flags |= R_TO_END;
+      const bool xNull = yReady && m.xb.y > ((fx & F_TO_END) ? 1 : 0);
+      const bool yNull = m.yb.y > ((fy & F_TO_END) ? 1 : 0);
+      if (xac > 1 || yac > 1 || xNull || yNull || aX == -2 || aY == -2 || aD == -2) flags |= R_SLOW;
+      r0 = make_int4(aD, aX, aY, flags);
+      r1 = make_int4(m.x0.y + m.y0.y, m.x0.y, m.y0.y, i);
+      r2 = make_int4(__float_as_int(__int_as_float(m.x1.x) * __int_as_float(m.y1.x)), m.x1.y, m.x1.z, __float_as_int(ab));
+      r3 = make_int4(m.y1.y, m.y1.z, m.xb.z + m.yb.z, __float_as_int(__int_as_float(m.xb.w) * __int_as_float(m.yb.w)));
+    }
+    if (q >= HB_DEPTH) bar_sync(HB_BAR_EMPTY + slot, 64);
+    int4* R = rec + slot * 128;
+    R[t] = r0; R[32 + t] = r1; R[64 + t] = r2; R[96 + t] = r3;
+    bar_arrive(HB_BAR_FULL + slot, 64);
+  }
+}
+
+__device__ __forceinline__ bool ring_read(const Ring& ring, int idx, float4& a, float4& b) {
+  if (idx < 0) return false;
+  a = ring.A[idx];
+  b = ring.B[idx];
+  return __float_as_int(b.y) > HB_EXP_ZERO / 2;
+}
+
+// Forward cell from a producer record (same arithmetic as the first-edge part of forward_cell)
+__device__ __forceinline__ Cell forward_fast(const PairDev& P, const Ring& ring, const int4 r0, const int4 r1, const int4 r2, const int4 r3) {
+  const float (*W)[6] = P.W;
+  const int flags = r0.w;
+  float4 xA, xB, yA, yB, dA, dB;
+  const bool vX = ring_read(ring, r0.x, xA, xB);
+  const bool vY = ring_read(ring, r0.y, yA, yB);
+  const bool vD = ring_read(ring, r0.z, dA, dB);
+  const bool origin = flags & R_ORIGIN;
+  const int eX = vX ? __float_as_int(xB.y) + r1.x : HB_EXP_ZERO;
+  const int eY = vY ? __float_as_int(yB.y) + r1.y : HB_EXP_ZERO;
+  const int eD = vD ? __float_as_int(dB.y) + r1.z : HB_EXP_ZERO;
+  Cell a;
+  a.E = max(max(eX, eY), max(eD, origin ? 0 : HB_EXP_ZERO));
+  const float sX = vX ? pow2_neg(eX - a.E) * __int_as_float(r2.x) : 0.f;
+  const float sY = vY ? pow2_neg(eY - a.E) * __int_as_float(r2.y) : 0.f;
+  const float sD = vD ? pow2_neg(eD - a.E) * __int_as_float(r2.z) : 0.f;
+  a.v[0] = origin ? pow2_neg(-a.E) : 0.f;
+  a.v[1] = a.v[2] = a.v[3] = a.v[4] = 0.f;
+  if (vX) {
+    if (flags & R_XEMIT) {
+      a.v[1] = sX * (xA.x * W[0][1] + xA.y * W[1][1] + xA.z * W[2][1] + xA.w * W[3][1]);
+      a.v[4] = sX * (xA.x * W[0][4] + xA.w * W[3][4] + xB.x * W[4][4]);
+    } else {
+      a.v[1] = sX * xA.y;
+      a.v[4] = sX * xB.x;
+      if (flags & R_IMM_BY_X) a.v[0] = fmaf(sX, xA.x, a.v[0]);
+    }
+  }
+  if (vY) {
+    if (flags & R_YEMIT) {
+      a.v[2] = sY * (yA.x * W[0][2] + yA.y * W[1][2] + yA.z * W[2][2] + yB.x * W[4][2]);
+      a.v[3] = sY * (yA.x * W[0][3] + yA.w * W[3][3]);
+    } else {
+      a.v[2] = sY * yA.z;
+      a.v[3] = sY * yA.w;
+      if (flags & R_IMM_BY_Y) a.v[0] = fmaf(sY, yA.x, a.v[0]);
+    }
+  }
+  if (vD) a.v[0] = fmaf(sD, dA.x * W[0][0] + dA.y * W[1][0] + dA.z * W[2][0] + dA.w * W[3][0] + dB.x * W[4][0], a.v[0]);
+  if (flags & R_BOTH) a.v[0] *= __int_as_float(r2.w);
+  a.v[1] *= __int_as_float(r3.x);
+  a.v[4] *= __int_as_float(r3.y);
+  a.v[2] *= __int_as_float(r3.z);
+  a.v[3] *= __int_as_float(r3.w);
+  cell_normalise(a);
+  return a;
+}
+
+__device__ __forceinline__ Cell backward_fast(const PairDev& P, const Ring& ring, const int4 r0, const int4 r1, const int4 r2, const int4 r3) {
+  const float (*W)[6] = P.W;
+  const int flags = r0.w;
+  float4 dA, dB, xA, xB, yA, yB;
+  const bool vD = ring_read(ring, r0.x, dA, dB);
+  const bool vX = ring_read(ring, r0.y, xA, xB);
+  const bool vY = ring_read(ring, r0.z, yA, yB);
+  const bool toEnd = flags & R_TO_END;
+  const int eD = vD ? __float_as_int(dB.y) + r1.x : HB_EXP_ZERO;
+  const int eX = vX ? __float_as_int(xB.y) + r1.y : HB_EXP_ZERO;
+  const int eY = vY ? __float_as_int(yB.y) + r1.z : HB_EXP_ZERO;
+  const int eE = toEnd ? r3.z : HB_EXP_ZERO;
+  Cell a;
+  a.E = max(max(eD, eX), max(eY, eE));
+  const float dest = vD ? pow2_neg(eD - a.E) * __int_as_float(r2.x) * dB.z : 0.f;  // absorb(dx,dy) * B(dx,dy,IMM)
+  const float sX = vX ? pow2_neg(eX - a.E) : 0.f;
+  const float sY = vY ? pow2_neg(eY - a.E) : 0.f;
+  const float sE = toEnd ? pow2_neg(eE - a.E) * __int_as_float(r3.w) : 0.f;
+  const float dmd = vX ? sX * __int_as_float(r2.y) * xA.y : 0.f, diw = vX ? sX * __int_as_float(r2.z) * xB.x : 0.f;
+  const float ddm = vY ? sY * __int_as_float(r3.x) * yA.z : 0.f, dmi = vY ? sY * __int_as_float(r3.y) * yA.w : 0.f;
+  a.v[0] = W[0][0] * dest + W[0][1] * dmd + W[0][4] * diw + W[0][2] * ddm + W[0][3] * dmi + sE * W[0][5];
+  a.v[1] = W[1][0] * dest + W[1][1] * dmd + W[1][2] * ddm + sE * W[1][5];
+  a.v[2] = W[2][0] * dest + W[2][1] * dmd + W[2][2] * ddm + sE * W[2][5];
+  a.v[3] = W[3][0] * dest + W[3][1] * dmd + W[3][4] * diw + W[3][3] * dmi + sE * W[3][5];
+  a.v[4] = W[4][0] * dest + W[4][4] * diw + W[4][2] * ddm + sE * W[4][5];
+  cell_normalise(a);
+  return a;
+}
+
+template <bool BWD>
+__device__ __noinline__ Cell generic_cell(const PairDev& P, const Ring& ring, const Recent& rc, const DiagInfo& di, int d, int t, float ab) {
+  const LaneMeta<BWD> m = load_meta<BWD>(P, di, d, t, false);
+  if (BWD) return backward_cell(P, ring, rc, d, m.i, m.j, m.xa, m.xb, m.x0, m.x1, m.ya, m.yb, m.y0, m.y1);
+  return forward_cell(P, ring, rc, d, m.i, m.j, m.xa, m.xb, m.xe, m.ya, m.yb, m.ye, ab);
+}
+
+template <bool BWD>
+__device__ __forceinline__ void consumer(const PairDev& P, const Ring& ring, const int4* rec) {
+  float4* gA = BWD ? P.bA : P.fA;
+  float2* gB = BWD ? P.bB : P.fB;
+  const int nD = P.n_diag;
+  const int t = threadIdx.x;
+  Recent rc = {0, 0, 0, 0};
+  for (int q = 0; q < nD; ++q) {
+    const int slot = q % HB_DEPTH;
+    const int d = BWD ? nD - 1 - q : q;
+    const DiagInfo di = P.dinfo[d];
+    bar_sync(HB_BAR_FULL + slot, 64);
+    const int4* R = rec + slot * 128;
+    const int4 r0 = R[t], r1 = R[32 + t], r2 = R[64 + t], r3 = R[96 + t];
+    if (q + HB_DEPTH < nD) bar_arrive(HB_BAR_EMPTY + slot, 64);
+    if (t == 0) ring.info[d & (ring.R - 1)] = make_int4(di.ilo, di.width, (int)di.off, 0);
+    if (t < P.nS + di.width + P.nE) {
+      Cell c = zero_cell();
+      float aux = 0.f;
+      if (r0.w & R_OK) {
+        const float ab = __int_as_float(r2.w);
+        if (r0.w & R_SLOW) c = generic_cell<BWD>(P, ring, rc, di, d, t, ab);
+        else c = BWD ? backward_fast(P, ring, r0, r1, r2, r3) : forward_fast(P, ring, r0, r1, r2, r3);
+        if (BWD) aux = c.v[0] * ab;  // absorb is 0 unless both states emit
+      }
+      const float4 va = make_float4(c.v[0], c.v[1], c.v[2], c.v[3]);
+      gA[di.off + t] = va;
+      gB[di.off + t] = make_float2(c.v[4], __int_as_float(c.E));
+      const int r = (d & (ring.R - 1)) * ring.cap + t;
+      ring.A[r] = va;
+      ring.B[r] = make_float4(c.v[4], __int_as_float(c.E), aux, 0.f);
+    }
+    __syncwarp();
+    rc.ilo2 = rc.ilo1; rc.w2 = rc.w1;
+    rc.ilo1 = di.ilo; rc.w1 = di.width;
+  }
+}
+
+template <bool BWD>
+__device__ __forceinline__ void sweep_narrow(const PairDev& P, const Ring& ring, int4* rec) {
+  if (threadIdx.x < 32) consumer<BWD>(P, ring, rec);
+  else producer<BWD>(P, ring, rec, (threadIdx.x >> 5) - 1);
+}
+
+// General strips: a CTA of several warps, each thread looping over the slots of the diagonal.
+template <bool BWD>
+__device__ __forceinline__ void sweep_wide(const PairDev& P, const Ring& ring) {
+  float4* gA = BWD ? P.bA : P.fA;
+  float2* gB = BWD ? P.bB : P.fB;
+  Recent rc = {0, 0, 0, 0};
+  for (int step = 0; step < P.n_diag; ++step) {
+    const int d = BWD ? P.n_diag - 1 - step : step;
+    const DiagInfo di = P.dinfo[d];
+    if (ring.R > 0 && threadIdx.x == 0) ring.info[d & (ring.R - 1)] = make_int4(di.ilo, di.width, (int)di.off, 0);
+    const int nthr = P.nS + di.width + P.nE;
+    for (int t = threadIdx.x; t < nthr; t += blockDim.x) {
+      const LaneMeta<BWD> m = load_meta<BWD>(P, di, d, t);
+      compute_store<BWD>(P, ring, rc, di, d, t, m, gA, gB);
+    }
+    __syncthreads();
+    rc.ilo2 = rc.ilo1; rc.w2 = rc.w1;
+    rc.ilo1 = di.ilo; rc.w1 = di.width;
+  }
+}
+
 // grid.x = n_pairs * n_dir; block b handles pair b / n_dir, direction (b % n_dir) (0 = Forward, 1 = Backward;
 // with n_dir == 1 the direction is `only_dir`).
-__global__ void __launch_bounds__(512) fill_kernel(PairDev* const* __restrict__ pairs, int n_dir, int only_dir, int ring_cap) {
+template <bool NARROW>
+__device__ __forceinline__ void fill_body(PairDev* const* __restrict__ pairs, int n_dir, int only_dir, int ring_cap, int ring_rows) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ PairDev P;
+  __shared__ int4 ring_info[HB_RING_MAX];
   {
     const PairDev* src = pairs[blockIdx.x / n_dir];
     const int* s = reinterpret_cast<const int*>(src);
@@ -270,66 +751,33 @@ __global__ void __launch_bounds__(512) fill_kernel(PairDev* const* __restrict__ 
   const bool bwd = n_dir == 2 ? (blockIdx.x % n_dir) == 1 : only_dir == 1;
   Ring ring;
   ring.cap = ring_cap;
+  ring.R = ring_rows;
   ring.A = reinterpret_cast<float4*>(smem_raw);
-  ring.B = reinterpret_cast<float2*>(smem_raw + (size_t)HB_RING * ring_cap * sizeof(float4));
-  float4* gA = bwd ? P.bA : P.fA;
-  float2* gB = bwd ? P.bB : P.fB;
-  const int nx2 = P.x.n - 2, ny2 = P.y.n - 2;
-  const bool one_warp = blockDim.x == 32;
-
-  for (int step = 0; step < P.n_diag; ++step) {
-    const int d = bwd ? P.n_diag - 1 - step : step;
-    const DiagInfo di = P.dinfo[d];
-    const int nthr = P.nS + di.width + P.nE;
-    for (int t = threadIdx.x; t < nthr; t += blockDim.x) {
-      int i, j;
-      bool ok = true;
-      if (t < P.nS) {
-        i = P.start_rows[t];
-        j = d - i;
-        if (i >= di.ilo && i < di.ilo + di.width) ok = false;  // the main interval owns this cell
-      } else if (t < P.nS + di.width) {
-        i = di.ilo + (t - P.nS);
-        j = d - i;
-      } else {
-        j = P.end_cols[t - P.nS - di.width];
-        i = d - j;
-        if (i >= di.ilo && i < di.ilo + di.width) ok = false;
-        if (ok && i >= 0 && i <= nx2 && P.x.slot[i] >= 0) ok = false;  // a near-start slot owns it
-      }
-      ok = ok && i >= 0 && j >= 0 && i <= nx2 && j <= ny2;
-      if (ok)  // DPMatrix::inEnvelope (forward.h:92-98)
-        ok = P.x.near_[i] || P.y.near_[j] || P.max_dist < 0 || hb_iabs(P.x.key[i] - P.y.key[j]) <= P.max_dist;
-      Cell c = ok ? (bwd ? backward_cell(P, ring, d, i, j) : forward_cell(P, ring, d, i, j)) : zero_cell();
-      const float4 va = make_float4(c.v[0], c.v[1], c.v[2], c.v[3]);
-      const float2 vb = make_float2(c.v[4], __int_as_float(c.E));
-      gA[di.off + t] = va;
-      gB[di.off + t] = vb;
-      if (ring_cap > 0) {
-        const int r = (d & (HB_RING - 1)) * ring_cap + t;
-        ring.A[r] = va;
-        ring.B[r] = vb;
-      }
-    }
-    if (one_warp) __syncwarp(); else __syncthreads();
+  ring.B = ring.A + (size_t)ring_rows * ring_cap;
+  ring.info = ring_info;
+  if (NARROW) {
+    int4* rec = reinterpret_cast<int4*>(ring.B + (size_t)ring_rows * ring_cap);
+    if (bwd) sweep_narrow<true>(P, ring, rec); else sweep_narrow<false>(P, ring, rec);
+  } else {
+    if (bwd) sweep_wide<true>(P, ring); else sweep_wide<false>(P, ring);
   }
 
   if (threadIdx.x == 0) {
-    Ring none;
-    none.cap = 0;
-    none.A = nullptr;
-    none.B = nullptr;
-    float4 sa;
-    float2 sb;
+    Ring none = ring;
+    none.R = 0;
+    const Recent rc = {0, 0, 0, 0};
+    float4 sa, sb;
     if (!bwd) {
       // transitions into EEE (forward.cpp:205-220)
       double lp = -INFINITY;
       const int xe = P.x.n - 1, ye = P.y.n - 1;
       for (int qx = P.x.in_off[xe]; qx < P.x.in_off[xe + 1]; ++qx) {
         const int tx = P.x.in_idx[qx];
+        const int sx = P.x.t_src[tx];
         for (int qy = P.y.in_off[ye]; qy < P.y.in_off[ye + 1]; ++qy) {
           const int ty = P.y.in_idx[qy];
-          if (!fetch_cell(P, gA, gB, none, 1 << 30, P.x.t_src[tx], P.y.t_src[ty], sa, sb)) continue;
+          const int sy = P.y.t_src[ty];
+          if (!fetch_cell<false>(P, none, rc, 1 << 30, true, sx, sy, P.x.slot[sx], P.y.slot[sy], sa, sb)) continue;
           const double s = (double)sa.x * P.W[0][5] + (double)sa.y * P.W[1][5] + (double)sa.z * P.W[2][5] +
                            (double)sa.w * P.W[3][5] + (double)sb.x * P.W[4][5];
           if (!(s > 0)) continue;
@@ -341,10 +789,19 @@ __global__ void __launch_bounds__(512) fill_kernel(PairDev* const* __restrict__ 
       *P.lp_end = lp;
     } else {
       double lp = -INFINITY;
-      if (fetch_cell(P, gA, gB, none, 1 << 30, 0, 0, sa, sb)) lp = cell_log(sa.x, __float_as_int(sb.y));
+      if (fetch_cell<true>(P, none, rc, -(1 << 30), true, 0, 0, P.x.slot[0], P.y.slot[0], sa, sb)) lp = cell_log(sa.x, __float_as_int(sb.y));
       *P.lp_start = lp;  // BackwardMatrix::lpStart() = cell(0,0,IMM)
     }
   }
+}
+
+// one consumer + HB_NPROD producer warps per strip; requires blockDim.x == 32 * (1 + HB_NPROD),
+// ring_rows >= 4 and max_threads <= 32 for every pair; dynamic smem = ring + HB_DEPTH * 2 KB of records
+__global__ void __launch_bounds__(32 * (1 + HB_NPROD)) fill_narrow_kernel(PairDev* const* __restrict__ pairs, int n_dir, int only_dir, int ring_cap, int ring_rows) {
+  fill_body<true>(pairs, n_dir, only_dir, ring_cap, ring_rows);
+}
+__global__ void __launch_bounds__(512) fill_kernel(PairDev* const* __restrict__ pairs, int n_dir, int only_dir, int ring_cap, int ring_rows) {
+  fill_body<false>(pairs, n_dir, only_dir, ring_cap, ring_rows);
 }
 
 // Convert stored cells to the reference's representation: natural-log doubles in the row-major
@@ -414,6 +871,7 @@ int ensure_backward_planes(hist_pair* pr) {
   const size_t bytesA = (n * sizeof(float4) + 255) / 256 * 256;
   char* p = nullptr;
   HB_CUDA(ctx, cudaMallocAsync((void**)&p, bytesA + n * sizeof(float2), ctx->stream));
+  pr->bwd_planes = p;
   pr->dev.bA = (float4*)p;
   pr->dev.bB = (float2*)(p + bytesA);
   HB_CUDA(ctx, cudaMemcpyAsync(pr->d_dev, &pr->dev, sizeof(PairDev), cudaMemcpyHostToDevice, ctx->stream));
@@ -421,21 +879,25 @@ int ensure_backward_planes(hist_pair* pr) {
 }
 
 int launch_fill(hist_ctx* ctx, hist_pair* const* pairs, int n, int n_dir, int only_dir) {
-  int maxThreads = 1;
-  for (int k = 0; k < n; ++k) maxThreads = std::max(maxThreads, pairs[k]->dev.max_threads);
-  int block = std::min(512, (maxThreads + 31) / 32 * 32);
-  // shared-memory ring of the last HB_RING diagonals, if it fits
-  int ring_cap = maxThreads;
-  size_t smem = (size_t)HB_RING * ring_cap * (sizeof(float4) + sizeof(float2));
-  const size_t limit = ctx->smem_optin > 4096 ? ctx->smem_optin - 2048 : 0;
-  if (smem > limit) {
-    ring_cap = 0;
-    smem = 0;
+  int maxThreads = 1, maxDiag = 1;
+  for (int k = 0; k < n; ++k) {
+    maxThreads = std::max(maxThreads, pairs[k]->dev.max_threads);
+    maxDiag = std::max(maxDiag, pairs[k]->dev.n_diag);
   }
-  static size_t configured = 0;
-  if (smem > 48 * 1024 && smem > configured) {
+  const int block = std::min(512, (maxThreads + 31) / 32 * 32);
+  // shared-memory ring of the last R diagonals: as many rows as fit a modest budget (narrow strips
+  // keep several CTAs per SM), at least 4 rows if the opt-in limit allows, none otherwise
+  const int ring_cap = maxThreads;
+  const size_t row = (size_t)ring_cap * 2 * sizeof(float4);
+  const size_t limit = ctx->smem_optin > 4096 ? ctx->smem_optin - 4096 : 0;
+  int rows = HB_RING_MAX;
+  while (rows > 4 && rows * row > 32 * 1024) rows >>= 1;
+  while (rows > 0 && rows * row > limit) rows >>= 1;
+  if (rows < 4) rows = 0;
+  const size_t smem = rows * row;
+  if (smem > 48 * 1024 && smem > ctx->fill_smem_configured) {
     HB_CUDA(ctx, cudaFuncSetAttribute(fill_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)limit));
-    configured = limit;
+    ctx->fill_smem_configured = limit;
   }
   std::vector<PairDev*> h(n);
   for (int k = 0; k < n; ++k) h[k] = pairs[k]->d_dev;
@@ -448,7 +910,19 @@ int launch_fill(hist_ctx* ctx, hist_pair* const* pairs, int n, int n_dir, int on
     HB_CUDA(ctx, cudaEventCreate(&e1));
     HB_CUDA(ctx, cudaEventRecord(e0, ctx->stream));
   }
-  fill_kernel<<<n * n_dir, block, smem, ctx->stream>>>(dptrs, n_dir, only_dir, ring_cap);
+  const bool narrow = block == 32 && rows >= 4;
+  if (!narrow && (n_dir == 2 || only_dir == 0)) {
+    // the absorb plane is part of the Forward fill (computeLogProbAbsorb, forward.cpp:183); the
+    // Backward fill reuses it (BackwardMatrix is built from a ForwardMatrix, forward.cpp:975).  The narrow
+    // kernel computes the same values in its producer warps instead.
+    const int chunks = std::max(1, std::min((maxDiag + 7) / 8, (8 * ctx->sm_count + n - 1) / n));
+    absorb_kernel<<<dim3(chunks, n), 256, 0, ctx->stream>>>(dptrs);
+    ctx->launches += 1;
+  }
+  if (narrow)
+    fill_narrow_kernel<<<n * n_dir, 32 * (1 + HB_NPROD), smem + HB_DEPTH * 128 * sizeof(int4), ctx->stream>>>(dptrs, n_dir, only_dir, ring_cap, rows);
+  else
+    fill_kernel<<<n * n_dir, block, smem, ctx->stream>>>(dptrs, n_dir, only_dir, ring_cap, rows);
   ctx->launches += 1;
   if (ctx->timing) {
     HB_CUDA(ctx, cudaEventRecord(e1, ctx->stream));
@@ -456,7 +930,7 @@ int launch_fill(hist_ctx* ctx, hist_pair* const* pairs, int n, int n_dir, int on
   }
   HB_CUDA(ctx, cudaGetLastError());
   HB_CUDA(ctx, cudaFreeAsync(dptrs, ctx->stream));
-  // h[] is pageable host memory: the copy above must finish before it goes out of scope
+  // h[] is pageable host memory: the copy above has been staged by the time cudaMemcpyAsync returns
   return HIST_OK;
 }
 
@@ -474,18 +948,23 @@ extern "C" int hist_fill_batch(hist_ctx* ctx, hist_pair* const* pairs, int32_t n
   }
   int rc = launch_fill(ctx, pairs, n, do_backward ? 2 : 1, 0);
   if (rc) return rc;
-  std::vector<double> tmp(2 * (size_t)n);
-  for (int k = 0; k < n; ++k) {
-    HB_CUDA(ctx, cudaMemcpyAsync(&tmp[2 * k], pairs[k]->dev.lp_end, (do_backward ? 2 : 1) * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+  // likelihoods: the scalar blocks (4 doubles) of pairs prepared in one batch are contiguous, so
+  // consecutive pairs come back in one transfer
+  std::vector<double> tmp(4 * (size_t)n);
+  for (int k = 0; k < n;) {
+    int e = k + 1;
+    while (e < n && pairs[e]->dev.lp_end == pairs[e - 1]->dev.lp_end + 4) ++e;
+    HB_CUDA(ctx, cudaMemcpyAsync(&tmp[4 * (size_t)k], pairs[k]->dev.lp_end, (size_t)(e - k) * 4 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    k = e;
   }
   HB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   for (int k = 0; k < n; ++k) {
     pairs[k]->fwd_done = true;
-    pairs[k]->lp_end = lp_end[k] = tmp[2 * k];
+    pairs[k]->lp_end = lp_end[k] = tmp[4 * (size_t)k];
     if (do_backward) {
       pairs[k]->bwd_done = true;
-      pairs[k]->lp_start = tmp[2 * k + 1];
-      if (lp_start) lp_start[k] = tmp[2 * k + 1];
+      pairs[k]->lp_start = tmp[4 * (size_t)k + 1];
+      if (lp_start) lp_start[k] = tmp[4 * (size_t)k + 1];
     }
   }
   return HIST_OK;

@@ -22,7 +22,22 @@ namespace hb {
 #define HB_LN2 0.69314718055994530942
 
 // per-state flag bits
-enum { F_EMIT = 1, F_READY = 2 /* isReady() || profile empty */, F_EMIT_OR_START = 4 };
+enum {
+  F_EMIT = 1, F_READY = 2 /* isReady() || profile empty */, F_EMIT_OR_START = 4,
+  F_NEAR = 8,    // xNearStart / yNearEnd (forward.cpp:58-65): the whole row / column is in the envelope
+  F_TO_END = 16  // has a null transition into END
+};
+
+// Packed per-state / per-edge records read by the fill kernels (built on device by
+// pack_meta_kernel).  One 16-B load per record, coalesced across the lanes of a diagonal.
+//   forward  state: fm_a = {flags | in_cnt << 8, in_begin, band key, edge slot}
+//                   fm_b = first in-edge (in-degree is 1 for almost every state)
+//   in-edge       : {src, exponent (dest emission folded in), mantissa bits, edge slot of src}
+//   backward state: bm[4] = {flags | ao_cnt << 8, ao_begin, band key, edge slot},
+//                           {no_begin, no_cnt, END-edge exponent, END-edge mantissa bits},
+//                           first absorbing out-edge (2 x int4)
+//   out-edge      : {dst, exponent, edge slot of dst, 0}, {m, m*rs[dst], m*ins[dst], 0} as float bits
+#define HB_MAX_DEGREE ((1 << 23) - 1)
 
 // One side (x or y profile) of a pair, device pointers.
 struct SideDev {
@@ -43,7 +58,12 @@ struct SideDev {
   int* ex;               // [n] floor(max_k sub[i][k] / ln2), 0 for null states
   float* rs;             // [n] exp(rootsub - ex ln2)   (1 for null states)
   float* ins;            // [n] exp(ins     - ex ln2)   (1 for null states)
-  float* H;              // [n][K] exp(sub - ex ln2); the y side is pre-multiplied by root[k]
+  float* H;              // [n][Kp] exp(sub - ex ln2), rows zero-padded to Kp = 4*ceil(K/4); the y side is pre-multiplied by root[k]
+  // packed records for the fill kernels
+  int4* fm_a; int4* fm_b; float2* emis;   // [n] forward meta, (rs, ins)
+  int4* in_edges;                         // [max(1,nt)]
+  int4* bm;                               // [n][4] backward meta
+  int4* ao_edges; int4* no_edges;         // [max(1,n_ao)][2], [max(1,n_no)][2]
   // natural-log doubles kept for fetch / makeProfile
   const double* lp_absorb;  // [n][K] input
   double* sub;           // [n][K] leftMultiply result (profile.cpp:78-91), -inf rows for null states
@@ -66,6 +86,7 @@ struct DiagInfo {
 struct PairDev {
   SideDev x, y;
   int K;                  // C * A
+  int Kp;                 // K rounded up to a multiple of 4 (row stride of H)
   int C, A;
   int max_dist;           // <0: no envelope
   float W[5][6];          // exp(lpTrans[src][dest]), 0 where absent
@@ -78,9 +99,15 @@ struct PairDev {
   unsigned n_stored;
   float4* fA; float2* fB; // forward cells: (IMM,IMD,IDM,IMI), (IIW, E)
   float4* bA; float2* bB; // backward cells
+  float* absorb;          // [n_stored] exp(computeLogProbAbsorb(i,j)) * 2^-(ex[i]+ey[j]) (forward.h:112-124); 0 unless both states emit
   double* lp_end;         // [1]
   double* lp_start;       // [1]
   unsigned long long* n_cells;  // [1] in-envelope cell count
+  // model tables of this merge (inputs of the DPMatrix-constructor kernels)
+  const double* l_sub; const double* r_sub;      // [C][A][A]
+  const double* log_root;                        // [C][A]
+  const double* l_ins; const double* r_ins;      // [C][A]
+  const double* l_cw; const double* r_cw;        // [C]
 };
 
 __host__ __device__ inline int hb_iabs(int a) { return a < 0 ? -a : a; }
@@ -106,14 +133,13 @@ __device__ __forceinline__ Cell zero_cell() {
 // Bring the accumulator to exponent max(acc.E, ce); returns the factor by which a
 // contribution expressed at exponent ce must be multiplied.
 __device__ __forceinline__ float acc_align(Cell& a, int ce) {
-  if (ce > a.E) {
-    const float s = pow2_neg(a.E - ce);
+  // branch-free: lanes of a diagonal take different sides, so a branch would only serialise
+  const int ne = max(a.E, ce);
+  const float s = pow2_neg(a.E - ne);
 #pragma unroll
-    for (int k = 0; k < 5; ++k) a.v[k] *= s;
-    a.E = ce;
-    return 1.f;
-  }
-  return pow2_neg(ce - a.E);
+  for (int k = 0; k < 5; ++k) a.v[k] *= s;
+  a.E = ne;
+  return pow2_neg(ce - ne);
 }
 
 // Renormalise so that max_k v[k] is in [1,2) (E absorbs the shift).
@@ -144,6 +170,13 @@ __device__ __forceinline__ double cell_log(float v, int E) {
 #include <string>
 #include <vector>
 
+// One device allocation shared by the pairs (or profiles) of a batch; freed with the last of them.
+struct hb_arena {
+  char* dev;
+  size_t bytes;
+  int refs;
+};
+
 struct hist_ctx {
   int device;
   cudaStream_t stream;
@@ -151,9 +184,13 @@ struct hist_ctx {
   long long launches;
   int sm_count;
   size_t smem_optin;
+  size_t fill_smem_configured;
   // optional per-kernel timing of the fill launches (bench.py's roofline leg)
   bool timing;
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> fill_events;
+  // pinned staging buffer for host-built layouts (grown on demand)
+  char* staging;
+  size_t staging_bytes;
 };
 
 struct hist_profile {
@@ -167,6 +204,7 @@ struct hist_profile {
   bool empty;                 // Profile::isEmpty
   // device copy of lp_absorb
   double* d_lp_absorb;
+  hb_arena* arena;            // owner of d_lp_absorb
 };
 
 struct hist_pair {
@@ -175,8 +213,8 @@ struct hist_pair {
   const hist_profile* y;
   hb::PairDev dev;      // host copy of the device descriptor (pointers are device pointers)
   hb::PairDev* d_dev;   // device copy
-  void* slab;           // one allocation holding every per-pair array
-  size_t slab_bytes;
+  hb_arena* arena;      // the batch allocation holding every per-pair array
+  void* bwd_planes;     // separately allocated Backward planes (when not part of the arena)
   hist_pair_info info;
   bool fwd_done, bwd_done;
   double lp_end, lp_start;

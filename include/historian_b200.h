@@ -163,6 +163,15 @@ void hist_profile_destroy(hist_profile* p);
  * keys (forward.cpp:36-42), plus the HBM band layout.  All on device. */
 int hist_pair_prepare(hist_ctx* ctx, const hist_profile* x, const hist_profile* y,
                       const hist_pairhmm_desc* hmm, const hist_env_desc* env, hist_pair** out);
+/* Batched form: the DPMatrix constructors of all sibling merges of one guide-tree depth
+ * (independent iterations of the recon.cpp:938-1033 loop) in one host->device transfer and one
+ * launch per table kernel.  xs/ys/hmms: [n]; envs: [n] or NULL (entries may be NULL = no envelope).
+ * flags: HIST_PREP_BACKWARD reserves the Backward planes up front (otherwise hist_bwd_fill
+ * allocates them on first use).  out: [n] handles, each released by hist_pair_destroy. */
+enum { HIST_PREP_BACKWARD = 1 };
+int hist_pair_prepare_batch(hist_ctx* ctx, int32_t n, const hist_profile* const* xs, const hist_profile* const* ys,
+                            const hist_pairhmm_desc* const* hmms, const hist_env_desc* const* envs, int32_t flags,
+                            hist_pair** out);
 void hist_pair_destroy(hist_pair* pair);
 int hist_pair_get_info(const hist_pair* pair, hist_pair_info* info);
 

@@ -185,13 +185,20 @@ def test_batch_fill_matches_single(ctx):
     rng = np.random.default_rng(11)
     alphabet = "arndcqeghilkmfpstwyv"
     hmm = synth.random_hmm(rng, 20, 1, tl=0.1, tr=0.2)
-    pairs, keep, singles = [], [], []
+    keep, singles, xs, ys, envs = [], [], [], [], []
     for k in range(9):
         x, y, (r1, r2) = synth.leaf_pair(rng, alphabet, 60 + 7 * k, 50 + 11 * k)
-        env = D.Envelope.from_guide_rows(r1, r2, 5 + k)
-        p, dx, dy = prepare(ctx, x, y, hmm, env)
-        q, ex, ey = prepare(ctx, x, y, hmm, env)
-        pairs.append(p); keep += [dx, dy, ex, ey]; singles.append(q)
+        env = D.Envelope.from_guide_rows(r1, r2, 5 + k) if k != 4 else None
+        q, ex, ey = prepare(ctx, x, y, hmm, env if env is not None else D.Envelope(-1))
+        xs.append(ctx.upload(x)); ys.append(ctx.upload(y)); envs.append(env)
+        keep += [ex, ey]; singles.append(q)
+    # hist_pair_prepare_batch: one transfer + one launch per table kernel for the whole level
+    pairs = ctx.prepare_batch(xs, ys, hmm, envs, backward=True)
+    for p, q in zip(pairs, singles):
+        assert p.n_cells == q.n_cells
+        tp, tq = p.tables(), q.tables()
+        for key in tp:
+            assert H.same(tp[key], tq[key]), key
     lp_end, lp_start = ctx.fill_batch(pairs, backward=True)
     for k, q in enumerate(singles):
         assert q.forward() == lp_end[k]
