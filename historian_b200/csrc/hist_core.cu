@@ -276,6 +276,7 @@ extern "C" int hist_ctx_create(int device, hist_ctx** out) {
   ctx->launches = 0;
   ctx->timing = false;
   ctx->fill_smem_configured = 0;
+  ctx->absorb_smem_configured = 0;
   ctx->staging = nullptr;
   ctx->staging_bytes = 0;
   e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);

@@ -32,6 +32,8 @@ struct Ring {
   int4* info;    // [R] {ilo, width, off, 0} of the diagonal held in each ring row
   int cap;       // slots per ring row
   int R;         // ring rows (0 = ring disabled), power of two
+  const int* srows;  // near-start rows / near-end columns of the edge slots (shared-memory copies in the
+  const int* ecols;  // narrow kernel, the global arrays otherwise)
 };
 
 __device__ __forceinline__ int cell_slot(const PairDev& P, const DiagInfo& di, int i, int j) {
@@ -342,21 +344,75 @@ __device__ __forceinline__ bool slot_cell(const PairDev& P, const DiagInfo& di, 
 
 // ------------------------------------------------------------------ absorb plane
 // exp(computeLogProbAbsorb(i,j)) (forward.h:112-124) for every stored both-emit cell, as
-// sum_k Xhat[i][k] * (root[k] Yhat[j][k]) relative to 2^(ex[i]+ey[j]).  One warp per diagonal: the lanes
-// read consecutive rows of the two emission tables (coalesced 16-B loads) and write consecutive floats.
-// grid = (chunks, pairs).
-__global__ void __launch_bounds__(256) absorb_kernel(PairDev* const* __restrict__ pairs) {
+// sum_k Xhat[i][k] * (root[k] Yhat[j][k]) relative to 2^(ex[i]+ey[j]).  A banded GEMM on CUDA cores:
+// a CTA takes HB_ABS_DIAGS consecutive anti-diagonals, stages the rows of the two emission tables
+// they touch in shared memory once (coalesced), then one warp per diagonal computes the dot products
+// from shared memory (the row of a state is reused by every cell of its band row: ~40x) and writes
+// consecutive floats.  Slots whose rows fall outside the staged tiles (the near-start / near-end
+// edge slots, or diagonals wider than a tile) read their rows from global memory.
+// grid = (diagonal blocks, pairs); dynamic smem = 2 * tile_rows * Kp floats.
+#define HB_ABS_DIAGS 32
+
+__device__ __forceinline__ float dot_rows(const float4* __restrict__ x4, const float4* __restrict__ y4, int K4) {
+  float a0 = 0.f, a1 = 0.f;
+#pragma unroll 5
+  for (int k = 0; k < K4; ++k) {
+    const float4 u = x4[k], v = y4[k];
+    a0 = fmaf(u.x, v.x, a0);
+    a1 = fmaf(u.y, v.y, a1);
+    a0 = fmaf(u.z, v.z, a0);
+    a1 = fmaf(u.w, v.w, a1);
+  }
+  return a0 + a1;
+}
+
+__global__ void __launch_bounds__(256) absorb_kernel(PairDev* const* __restrict__ pairs, int tile_rows) {
+  extern __shared__ __align__(16) float tile[];
   __shared__ PairDev P;
+  __shared__ int s_rng[4];  // rlo, rhi, clo, chi of the staged block
   {
     const int* s = reinterpret_cast<const int*>(pairs[blockIdx.y]);
     int* dptr = reinterpret_cast<int*>(&P);
     for (int k = threadIdx.x; k < (int)(sizeof(PairDev) / sizeof(int)); k += blockDim.x) dptr[k] = s[k];
   }
   __syncthreads();
-  const int lane = threadIdx.x & 31;
-  const int warps = (blockDim.x >> 5) * gridDim.x;
-  const int K4 = P.Kp >> 2;
-  for (int d = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); d < P.n_diag; d += warps) {
+  const int d0 = blockIdx.x * HB_ABS_DIAGS;
+  if (d0 >= P.n_diag) return;
+  const int d1 = min(d0 + HB_ABS_DIAGS, P.n_diag);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (warp == 0) {
+    int rlo = 1 << 30, rhi = -1, clo = 1 << 30, chi = -1;
+    if (d0 + lane < d1) {
+      const DiagInfo di = P.dinfo[d0 + lane];
+      if (di.width > 0) {
+        rlo = di.ilo; rhi = di.ilo + di.width - 1;
+        clo = d0 + lane - rhi; chi = d0 + lane - rlo;
+      }
+    }
+    for (int o = 16; o; o >>= 1) {
+      rlo = min(rlo, __shfl_xor_sync(0xffffffffu, rlo, o)); rhi = max(rhi, __shfl_xor_sync(0xffffffffu, rhi, o));
+      clo = min(clo, __shfl_xor_sync(0xffffffffu, clo, o)); chi = max(chi, __shfl_xor_sync(0xffffffffu, chi, o));
+    }
+    if (lane == 0) {
+      // keep what fits: rows beyond the tile are served from global memory
+      s_rng[0] = rlo; s_rng[1] = min(rhi, rlo + tile_rows - 1);
+      s_rng[2] = clo; s_rng[3] = min(chi, clo + tile_rows - 1);
+    }
+  }
+  __syncthreads();
+  const int rlo = s_rng[0], rhi = s_rng[1], clo = s_rng[2], chi = s_rng[3];
+  const int Kp = P.Kp, K4 = Kp >> 2;
+  float4* tx = reinterpret_cast<float4*>(tile);
+  float4* ty = tx + (size_t)tile_rows * K4;
+  if (rhi >= rlo) {
+    const float4* gx = reinterpret_cast<const float4*>(P.x.H + (size_t)rlo * Kp);
+    const float4* gy = reinterpret_cast<const float4*>(P.y.H + (size_t)clo * Kp);
+    const int nx4 = (rhi - rlo + 1) * K4, ny4 = (chi - clo + 1) * K4;
+    for (int k = threadIdx.x; k < nx4; k += blockDim.x) tx[k] = __ldg(gx + k);
+    for (int k = threadIdx.x; k < ny4; k += blockDim.x) ty[k] = __ldg(gy + k);
+  }
+  __syncthreads();
+  for (int d = d0 + warp; d < d1; d += (blockDim.x >> 5)) {
     const DiagInfo di = P.dinfo[d];
     const int nthr = P.nS + di.width + P.nE;
     for (int t = lane; t < nthr; t += 32) {
@@ -364,17 +420,9 @@ __global__ void __launch_bounds__(256) absorb_kernel(PairDev* const* __restrict_
       int4 xk, yk;
       float acc = 0.f;
       if (slot_cell<false>(P, di, d, t, i, j, xk, yk) && (xk.x & yk.x & F_EMIT)) {
-        const float4* __restrict__ x4 = reinterpret_cast<const float4*>(P.x.H + (size_t)i * P.Kp);
-        const float4* __restrict__ y4 = reinterpret_cast<const float4*>(P.y.H + (size_t)j * P.Kp);
-        float a0 = 0.f, a1 = 0.f;
-        for (int k = 0; k < K4; ++k) {
-          const float4 u = __ldg(x4 + k), v = __ldg(y4 + k);
-          a0 = fmaf(u.x, v.x, a0);
-          a1 = fmaf(u.y, v.y, a1);
-          a0 = fmaf(u.z, v.z, a0);
-          a1 = fmaf(u.w, v.w, a1);
-        }
-        acc = a0 + a1;
+        const float4* x4 = (i >= rlo && i <= rhi) ? tx + (size_t)(i - rlo) * K4 : reinterpret_cast<const float4*>(P.x.H + (size_t)i * Kp);
+        const float4* y4 = (j >= clo && j <= chi) ? ty + (size_t)(j - clo) * K4 : reinterpret_cast<const float4*>(P.y.H + (size_t)j * Kp);
+        acc = dot_rows(x4, y4, K4);
       }
       P.absorb[di.off + t] = acc;
     }
@@ -396,20 +444,20 @@ struct LaneMeta {
 };
 
 template <bool BWD>
-__device__ __forceinline__ LaneMeta<BWD> load_meta(const PairDev& P, const DiagInfo& di, int d, int t, bool with_ab = true) {
+__device__ __forceinline__ LaneMeta<BWD> load_meta(const PairDev& P, const Ring& ring, const DiagInfo& di, int d, int t, bool with_ab = true) {
   LaneMeta<BWD> m;
   bool ok = t < P.nS + di.width + P.nE;
   int i = 0, j = 0;
   m.tail = false;
   if (t < P.nS) {
-    i = P.start_rows[t];
+    i = ring.srows[t];
     j = d - i;
     if (i >= di.ilo && i < di.ilo + di.width) ok = false;  // the main interval owns this cell
   } else if (t < P.nS + di.width) {
     i = di.ilo + (t - P.nS);
     j = d - i;
   } else if (ok) {
-    j = P.end_cols[t - P.nS - di.width];
+    j = ring.ecols[t - P.nS - di.width];
     i = d - j;
     m.tail = true;
     if (i >= di.ilo && i < di.ilo + di.width) ok = false;
@@ -426,7 +474,7 @@ __device__ __forceinline__ LaneMeta<BWD> load_meta(const PairDev& P, const DiagI
     m.xa = P.x.fm_a[i]; m.xb = P.x.fm_b[i]; m.xe = P.x.emis[i];
     m.ya = P.y.fm_a[j]; m.yb = P.y.fm_b[j]; m.ye = P.y.emis[j];
   }
-  m.ab = ok && with_ab ? P.absorb[di.off + t] : 0.f;
+  m.ab = ok && with_ab ? __ldcs(P.absorb + di.off + t) : 0.f;
   return m;
 }
 
@@ -447,8 +495,8 @@ __device__ __forceinline__ void compute_store(const PairDev& P, const Ring& ring
     }
   }
   const float4 va = make_float4(c.v[0], c.v[1], c.v[2], c.v[3]);
-  gA[di.off + t] = va;
-  gB[di.off + t] = make_float2(c.v[4], __int_as_float(c.E));
+  __stcs(gA + di.off + t, va);
+  __stcs(gB + di.off + t, make_float2(c.v[4], __int_as_float(c.E)));
   if (ring.R > 0) {
     const int r = (d & (ring.R - 1)) * ring.cap + t;
     ring.A[r] = va;
@@ -470,53 +518,71 @@ __device__ __forceinline__ void compute_store(const PairDev& P, const Ring& ring
 // routine on the consumer ("slow" flag).
 #define HB_NPROD 2
 #define HB_DEPTH 4
-#define HB_BAR_FULL 1
-#define HB_BAR_EMPTY (1 + HB_DEPTH)
 enum { R_OK = 1, R_XEMIT = 2, R_YEMIT = 4, R_IMM_BY_X = 8, R_IMM_BY_Y = 16, R_ORIGIN = 32, R_SLOW = 64, R_BOTH = 128, R_TO_END = 256 };
 
-__device__ __forceinline__ void bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
-__device__ __forceinline__ void bar_arrive(int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+// shared-memory mbarriers (no per-SM limit, unlike named barriers): full[slot] counts the 32 lanes of
+// the producing warp, empty[slot] the 32 lanes of the consumer
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("{\n .reg .b64 st;\n mbarrier.arrive.shared::cta.b64 st, [%0];\n}" ::"r"((unsigned)__cvta_generic_to_shared(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {
+  asm volatile(
+      "{\n .reg .pred p;\n WAIT_LOOP:\n mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n @p bra WAIT_DONE;\n bra WAIT_LOOP;\n WAIT_DONE:\n}" ::
+          "r"((unsigned)__cvta_generic_to_shared(bar)), "r"(parity)
+      : "memory");
+}
 
 // Ring entry index of cell (i2,j2); -1: not stored; -2: older than the ring (generic path).
 template <bool BWD>
-__device__ __forceinline__ int pred_index(const PairDev& P, const Ring& ring, int dcur, bool en, int i2, int j2, int xs, int ys) {
+__device__ __forceinline__ int pred_index(const PairDev& P, const Ring& ring, const Recent& rc, int dcur, bool en, int i2, int j2, int xs,
+                                          int ys) {
   if (!en) return -1;
   const int d2 = i2 + j2;
   const int dist = BWD ? d2 - dcur : dcur - d2;
   if (dist >= ring.R) return -2;
-  const DiagInfo di = P.dinfo[d2];
-  const int r = i2 - di.ilo;
+  int ilo, width;
+  if (dist <= 2) {
+    ilo = dist == 1 ? rc.ilo1 : rc.ilo2;
+    width = dist == 1 ? rc.w1 : rc.w2;
+  } else {
+    const DiagInfo di = P.dinfo[d2];
+    ilo = di.ilo; width = di.width;
+  }
+  const int r = i2 - ilo;
   int s;
-  if ((unsigned)r < (unsigned)di.width) s = P.nS + r;
+  if ((unsigned)r < (unsigned)width) s = P.nS + r;
   else if (xs >= 0) s = xs;
-  else if (ys >= 0) s = P.nS + di.width + ys;
+  else if (ys >= 0) s = P.nS + width + ys;
   else return -1;
   return (d2 & (ring.R - 1)) * ring.cap + s;
 }
 
-__device__ __forceinline__ float absorb_dot(const PairDev& P, int i, int j) {
-  const float4* __restrict__ x4 = reinterpret_cast<const float4*>(P.x.H + (size_t)i * P.Kp);
-  const float4* __restrict__ y4 = reinterpret_cast<const float4*>(P.y.H + (size_t)j * P.Kp);
-  float a0 = 0.f, a1 = 0.f;
-  for (int k = 0; k < (P.Kp >> 2); ++k) {
-    const float4 u = __ldg(x4 + k), v = __ldg(y4 + k);
-    a0 = fmaf(u.x, v.x, a0);
-    a1 = fmaf(u.y, v.y, a1);
-    a0 = fmaf(u.z, v.z, a0);
-    a1 = fmaf(u.w, v.w, a1);
-  }
-  return a0 + a1;
+__device__ __forceinline__ DiagInfo load_dinfo_early(const DiagInfo* p) {
+  // volatile: keeps the load where it is written (ahead of its use in the NEXT iteration)
+  DiagInfo d;
+  asm volatile("ld.global.nc.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(d.ilo), "=r"(d.width), "=r"(d.off), "=r"(d.pad) : "l"(p));
+  return d;
 }
 
 template <bool BWD>
-__device__ __forceinline__ void producer(const PairDev& P, const Ring& ring, int4* rec, int p) {
+__device__ __forceinline__ void producer(const PairDev& P, const Ring& ring, int4* rec, uint64_t* full, uint64_t* empty, int p) {
   const int t = threadIdx.x & 31;
   const int nD = P.n_diag;
+  // layout records of diagonal d and of the two diagonals before it in sweep order, loaded one iteration ahead
+  auto diag_of = [&](int q) { return min(max(BWD ? nD - 1 - q : q, 0), nD - 1); };
+  DiagInfo n0 = P.dinfo[diag_of(p)], n1 = P.dinfo[diag_of(p - 1)], n2 = P.dinfo[diag_of(p - 2)];
   for (int q = p; q < nD; q += HB_NPROD) {
     const int slot = q % HB_DEPTH;
     const int d = BWD ? nD - 1 - q : q;
-    const DiagInfo di = P.dinfo[d];
-    const LaneMeta<BWD> m = load_meta<BWD>(P, di, d, t, false);
+    const DiagInfo di = n0;
+    const Recent rc = {n1.ilo, n1.width, n2.ilo, n2.width};
+    n0 = load_dinfo_early(P.dinfo + diag_of(q + HB_NPROD));
+    n1 = load_dinfo_early(P.dinfo + diag_of(q + HB_NPROD - 1));
+    n2 = load_dinfo_early(P.dinfo + diag_of(q + HB_NPROD - 2));
+    const LaneMeta<BWD> m = load_meta<BWD>(P, ring, di, d, t, true);
     // a near-start slot owns cells of near-end columns; then DPMatrix::inEnvelope (forward.h:92-98)
     const bool ok = m.ok && !(m.tail && m.xa.w >= 0) &&
                     (((m.xa.x | m.ya.x) & F_NEAR) || P.max_dist < 0 || hb_iabs(m.xa.z - m.ya.z) <= P.max_dist);
@@ -526,8 +592,7 @@ __device__ __forceinline__ void producer(const PairDev& P, const Ring& ring, int
     const bool xReady = fx & F_READY, yReady = fy & F_READY;
     const bool xEmitOrStart = fx & F_EMIT_OR_START;
     const bool both = xEmit && yEmit;
-    float ab = 0.f;
-    if (ok && both) ab = absorb_dot(P, i, j);
+    const float ab = ok && both ? m.ab : 0.f;
     int4 r0, r1, r2, r3;
     int flags = ok ? R_OK : 0;
     if (!BWD) {
@@ -535,9 +600,9 @@ __device__ __forceinline__ void producer(const PairDev& P, const Ring& ring, int
       const bool doX = ok && yReady && xc > 0;
       const bool doY = ok && (yEmit ? xReady : true) && yc > 0;
       const bool doD = ok && both && xc > 0 && yc > 0;
-      const int aX = pred_index<false>(P, ring, d, doX, m.xb.x, j, m.xb.w, m.ya.w);
-      const int aY = pred_index<false>(P, ring, d, doY, i, m.yb.x, m.xa.w, m.yb.w);
-      const int aD = pred_index<false>(P, ring, d, doD, m.xb.x, m.yb.x, m.xb.w, m.yb.w);
+      const int aX = pred_index<false>(P, ring, rc, d, doX, m.xb.x, j, m.xb.w, m.ya.w);
+      const int aY = pred_index<false>(P, ring, rc, d, doY, i, m.yb.x, m.xa.w, m.yb.w);
+      const int aD = pred_index<false>(P, ring, rc, d, doD, m.xb.x, m.yb.x, m.xb.w, m.yb.w);
       if (xEmit) flags |= R_XEMIT;
       if (yEmit) flags |= R_YEMIT;
       if (!xEmit && !(!yEmit && xEmitOrStart)) flags |= R_IMM_BY_X;
@@ -551,15 +616,14 @@ __device__ __forceinline__ void producer(const PairDev& P, const Ring& ring, int
       const bool ex = xEmit && yReady, ey = yEmit && xReady;
       r3 = make_int4(__float_as_int(ex ? m.xe.x : 1.f), __float_as_int(ex ? m.xe.y : 1.f), __float_as_int(ey ? m.ye.x : 1.f),
                      __float_as_int(ey ? m.ye.y : 1.f));
-      if (ok) P.absorb[di.off + t] = ab;  // kept for the generic path and for a later Backward fill
     } else {
       const int xac = (int)((unsigned)m.xa.x >> 8), yac = (int)((unsigned)m.ya.x >> 8);
       const bool doD = ok && xac > 0 && yac > 0;
       const bool doX = ok && yReady && xac > 0;
       const bool doY = ok && xReady && yac > 0;
-      const int aD = pred_index<true>(P, ring, d, doD, m.x0.x, m.y0.x, m.x0.z, m.y0.z);
-      const int aX = pred_index<true>(P, ring, d, doX, m.x0.x, j, m.x0.z, m.ya.w);
-      const int aY = pred_index<true>(P, ring, d, doY, i, m.y0.x, m.xa.w, m.y0.z);
+      const int aD = pred_index<true>(P, ring, rc, d, doD, m.x0.x, m.y0.x, m.x0.z, m.y0.z);
+      const int aX = pred_index<true>(P, ring, rc, d, doX, m.x0.x, j, m.x0.z, m.ya.w);
+      const int aY = pred_index<true>(P, ring, rc, d, doY, i, m.y0.x, m.xa.w, m.y0.z);
       const bool toEnd = (fx & F_TO_END) && (fy & F_TO_END);
       if (toEnd) flags |= R_TO_END;
       const bool xNull = yReady && m.xb.y > ((fx & F_TO_END) ? 1 : 0);
@@ -570,10 +634,10 @@ __device__ __forceinline__ void producer(const PairDev& P, const Ring& ring, int
       r2 = make_int4(__float_as_int(__int_as_float(m.x1.x) * __int_as_float(m.y1.x)), m.x1.y, m.x1.z, __float_as_int(ab));
       r3 = make_int4(m.y1.y, m.y1.z, m.xb.z + m.yb.z, __float_as_int(__int_as_float(m.xb.w) * __int_as_float(m.yb.w)));
     }
-    if (q >= HB_DEPTH) bar_sync(HB_BAR_EMPTY + slot, 64);
+    if (q >= HB_DEPTH) mbar_wait(empty + slot, ((q / HB_DEPTH) - 1) & 1);
     int4* R = rec + slot * 128;
     R[t] = r0; R[32 + t] = r1; R[64 + t] = r2; R[96 + t] = r3;
-    bar_arrive(HB_BAR_FULL + slot, 64);
+    mbar_arrive(full + slot);
   }
 }
 
@@ -664,13 +728,13 @@ __device__ __forceinline__ Cell backward_fast(const PairDev& P, const Ring& ring
 
 template <bool BWD>
 __device__ __noinline__ Cell generic_cell(const PairDev& P, const Ring& ring, const Recent& rc, const DiagInfo& di, int d, int t, float ab) {
-  const LaneMeta<BWD> m = load_meta<BWD>(P, di, d, t, false);
+  const LaneMeta<BWD> m = load_meta<BWD>(P, ring, di, d, t, false);
   if (BWD) return backward_cell(P, ring, rc, d, m.i, m.j, m.xa, m.xb, m.x0, m.x1, m.ya, m.yb, m.y0, m.y1);
   return forward_cell(P, ring, rc, d, m.i, m.j, m.xa, m.xb, m.xe, m.ya, m.yb, m.ye, ab);
 }
 
 template <bool BWD>
-__device__ __forceinline__ void consumer(const PairDev& P, const Ring& ring, const int4* rec) {
+__device__ __forceinline__ void consumer(const PairDev& P, const Ring& ring, const int4* rec, uint64_t* full, uint64_t* empty) {
   float4* gA = BWD ? P.bA : P.fA;
   float2* gB = BWD ? P.bB : P.fB;
   const int nD = P.n_diag;
@@ -680,10 +744,10 @@ __device__ __forceinline__ void consumer(const PairDev& P, const Ring& ring, con
     const int slot = q % HB_DEPTH;
     const int d = BWD ? nD - 1 - q : q;
     const DiagInfo di = P.dinfo[d];
-    bar_sync(HB_BAR_FULL + slot, 64);
+    mbar_wait(full + slot, (q / HB_DEPTH) & 1);
     const int4* R = rec + slot * 128;
     const int4 r0 = R[t], r1 = R[32 + t], r2 = R[64 + t], r3 = R[96 + t];
-    if (q + HB_DEPTH < nD) bar_arrive(HB_BAR_EMPTY + slot, 64);
+    mbar_arrive(empty + slot);
     if (t == 0) ring.info[d & (ring.R - 1)] = make_int4(di.ilo, di.width, (int)di.off, 0);
     if (t < P.nS + di.width + P.nE) {
       Cell c = zero_cell();
@@ -695,8 +759,8 @@ __device__ __forceinline__ void consumer(const PairDev& P, const Ring& ring, con
         if (BWD) aux = c.v[0] * ab;  // absorb is 0 unless both states emit
       }
       const float4 va = make_float4(c.v[0], c.v[1], c.v[2], c.v[3]);
-      gA[di.off + t] = va;
-      gB[di.off + t] = make_float2(c.v[4], __int_as_float(c.E));
+      __stcs(gA + di.off + t, va);
+      __stcs(gB + di.off + t, make_float2(c.v[4], __int_as_float(c.E)));
       const int r = (d & (ring.R - 1)) * ring.cap + t;
       ring.A[r] = va;
       ring.B[r] = make_float4(c.v[4], __int_as_float(c.E), aux, 0.f);
@@ -708,9 +772,9 @@ __device__ __forceinline__ void consumer(const PairDev& P, const Ring& ring, con
 }
 
 template <bool BWD>
-__device__ __forceinline__ void sweep_narrow(const PairDev& P, const Ring& ring, int4* rec) {
-  if (threadIdx.x < 32) consumer<BWD>(P, ring, rec);
-  else producer<BWD>(P, ring, rec, (threadIdx.x >> 5) - 1);
+__device__ __forceinline__ void sweep_narrow(const PairDev& P, const Ring& ring, int4* rec, uint64_t* full, uint64_t* empty) {
+  if (threadIdx.x < 32) consumer<BWD>(P, ring, rec, full, empty);
+  else producer<BWD>(P, ring, rec, full, empty, (threadIdx.x >> 5) - 1);
 }
 
 // General strips: a CTA of several warps, each thread looping over the slots of the diagonal.
@@ -725,7 +789,7 @@ __device__ __forceinline__ void sweep_wide(const PairDev& P, const Ring& ring) {
     if (ring.R > 0 && threadIdx.x == 0) ring.info[d & (ring.R - 1)] = make_int4(di.ilo, di.width, (int)di.off, 0);
     const int nthr = P.nS + di.width + P.nE;
     for (int t = threadIdx.x; t < nthr; t += blockDim.x) {
-      const LaneMeta<BWD> m = load_meta<BWD>(P, di, d, t);
+      const LaneMeta<BWD> m = load_meta<BWD>(P, ring, di, d, t);
       compute_store<BWD>(P, ring, rc, di, d, t, m, gA, gB);
     }
     __syncthreads();
@@ -741,6 +805,8 @@ __device__ __forceinline__ void fill_body(PairDev* const* __restrict__ pairs, in
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ PairDev P;
   __shared__ int4 ring_info[HB_RING_MAX];
+  __shared__ uint64_t mbar[2 * HB_DEPTH];
+  if (NARROW && threadIdx.x < 2 * HB_DEPTH) mbar_init(mbar + threadIdx.x, 32);
   {
     const PairDev* src = pairs[blockIdx.x / n_dir];
     const int* s = reinterpret_cast<const int*>(src);
@@ -755,9 +821,19 @@ __device__ __forceinline__ void fill_body(PairDev* const* __restrict__ pairs, in
   ring.A = reinterpret_cast<float4*>(smem_raw);
   ring.B = ring.A + (size_t)ring_rows * ring_cap;
   ring.info = ring_info;
+  ring.srows = P.start_rows;
+  ring.ecols = P.end_cols;
+  __shared__ int edge_rows[32], edge_cols[32];
+  if (NARROW) {
+    if (threadIdx.x < P.nS) edge_rows[threadIdx.x] = P.start_rows[threadIdx.x];
+    if (threadIdx.x < P.nE) edge_cols[threadIdx.x] = P.end_cols[threadIdx.x];
+    ring.srows = edge_rows;
+    ring.ecols = edge_cols;
+    __syncthreads();
+  }
   if (NARROW) {
     int4* rec = reinterpret_cast<int4*>(ring.B + (size_t)ring_rows * ring_cap);
-    if (bwd) sweep_narrow<true>(P, ring, rec); else sweep_narrow<false>(P, ring, rec);
+    if (bwd) sweep_narrow<true>(P, ring, rec, mbar, mbar + HB_DEPTH); else sweep_narrow<false>(P, ring, rec, mbar, mbar + HB_DEPTH);
   } else {
     if (bwd) sweep_wide<true>(P, ring); else sweep_wide<false>(P, ring);
   }
@@ -797,7 +873,7 @@ __device__ __forceinline__ void fill_body(PairDev* const* __restrict__ pairs, in
 
 // one consumer + HB_NPROD producer warps per strip; requires blockDim.x == 32 * (1 + HB_NPROD),
 // ring_rows >= 4 and max_threads <= 32 for every pair; dynamic smem = ring + HB_DEPTH * 2 KB of records
-__global__ void __launch_bounds__(32 * (1 + HB_NPROD)) fill_narrow_kernel(PairDev* const* __restrict__ pairs, int n_dir, int only_dir, int ring_cap, int ring_rows) {
+__global__ void __maxnreg__(HB_NPROD == 1 ? 144 : 96) fill_narrow_kernel(PairDev* const* __restrict__ pairs, int n_dir, int only_dir, int ring_cap, int ring_rows) {
   fill_body<true>(pairs, n_dir, only_dir, ring_cap, ring_rows);
 }
 __global__ void __launch_bounds__(512) fill_kernel(PairDev* const* __restrict__ pairs, int n_dir, int only_dir, int ring_cap, int ring_rows) {
@@ -911,12 +987,19 @@ int launch_fill(hist_ctx* ctx, hist_pair* const* pairs, int n, int n_dir, int on
     HB_CUDA(ctx, cudaEventRecord(e0, ctx->stream));
   }
   const bool narrow = block == 32 && rows >= 4;
-  if (!narrow && (n_dir == 2 || only_dir == 0)) {
+  if (n_dir == 2 || only_dir == 0) {
     // the absorb plane is part of the Forward fill (computeLogProbAbsorb, forward.cpp:183); the
-    // Backward fill reuses it (BackwardMatrix is built from a ForwardMatrix, forward.cpp:975).  The narrow
-    // kernel computes the same values in its producer warps instead.
-    const int chunks = std::max(1, std::min((maxDiag + 7) / 8, (8 * ctx->sm_count + n - 1) / n));
-    absorb_kernel<<<dim3(chunks, n), 256, 0, ctx->stream>>>(dptrs);
+    // Backward fill reuses it (BackwardMatrix is built from a ForwardMatrix, forward.cpp:975)
+    int maxKp = 4;
+    for (int k = 0; k < n; ++k) maxKp = std::max(maxKp, pairs[k]->dev.Kp);
+    int tile_rows = 96;
+    while (tile_rows > 8 && (size_t)2 * tile_rows * maxKp * sizeof(float) > 96 * 1024) tile_rows >>= 1;
+    const size_t abs_smem = (size_t)2 * tile_rows * maxKp * sizeof(float);
+    if (abs_smem > 48 * 1024 && abs_smem > ctx->absorb_smem_configured) {
+      HB_CUDA(ctx, cudaFuncSetAttribute(absorb_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+      ctx->absorb_smem_configured = 96 * 1024;
+    }
+    absorb_kernel<<<dim3((maxDiag + HB_ABS_DIAGS - 1) / HB_ABS_DIAGS, n), 256, abs_smem, ctx->stream>>>(dptrs, tile_rows);
     ctx->launches += 1;
   }
   if (narrow)

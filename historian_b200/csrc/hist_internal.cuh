@@ -185,6 +185,7 @@ struct hist_ctx {
   int sm_count;
   size_t smem_optin;
   size_t fill_smem_configured;
+  size_t absorb_smem_configured;
   // optional per-kernel timing of the fill launches (bench.py's roofline leg)
   bool timing;
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> fill_events;
