@@ -57,6 +57,10 @@ def load():
     lib.hist_bwd_fill.argtypes = [vp, D.c_double_p]
     lib.hist_fill_batch.argtypes = [vp, C.POINTER(vp), C.c_int32, C.c_int, D.c_double_p, D.c_double_p]
     lib.hist_cells_fetch.argtypes = [vp, C.c_int, D.c_double_p, D.c_int32_p, D.c_int32_p, C.c_int64, D.c_int64_p]
+    lib.hist_trace_best.argtypes = [vp, D.Cell, C.POINTER(D.Cell), C.c_int64, D.c_int64_p]
+    lib.hist_trace_best_forward.argtypes = [vp, D.Cell, C.POINTER(D.Cell), C.c_int64, D.c_int64_p]
+    lib.hist_trace_sample.argtypes = [vp, D.c_uint32_p, C.c_int32, C.POINTER(D.Cell), C.c_int64, D.c_int64_p]
+    lib.hist_posterior_cells.argtypes = [vp, C.c_double, C.POINTER(D.Cell), D.c_double_p, C.c_int64, D.c_int64_p]
     _lib = lib
     return lib
 
@@ -255,3 +259,48 @@ class Pair:
         out = np.full((self.info.x_size - 1, self.info.y_size - 1, 5), -np.inf)
         out[xp, yp] = lp
         return out
+
+    # ---- traceback (forward.cpp:257-302, 1287-1300)
+    def _cells_np(self, buf, n):
+        return np.frombuffer(buf, dtype=np.int32, count=3 * n).reshape(n, 3).copy()
+
+    def trace_best(self, end=None):
+        """ForwardMatrix::bestTrace(end); default end = EEE.  Returns [n,3] (xpos, ypos, state), start -> end."""
+        if end is None:
+            end = (self.info.x_size - 1, self.info.y_size - 1, D.EEE)
+        cap = self.info.x_size + self.info.y_size + 8
+        buf = (D.Cell * cap)()
+        n = C.c_int64()
+        self.ctx.check(self.ctx.lib.hist_trace_best(self.h, D.Cell(*[int(v) for v in end]), buf, cap, C.byref(n)))
+        return self._cells_np(buf, n.value)
+
+    def trace_best_forward(self, start):
+        """BackwardMatrix::bestTrace(start): greedy walk through the Backward matrix to EEE."""
+        cap = self.info.x_size + self.info.y_size + 8
+        buf = (D.Cell * cap)()
+        n = C.c_int64()
+        self.ctx.check(self.ctx.lib.hist_trace_best_forward(self.h, D.Cell(*[int(v) for v in start]), buf, cap, C.byref(n)))
+        return self._cells_np(buf, n.value)
+
+    def trace_sample(self, mt_state, n_traces=1):
+        """ForwardMatrix::sampleTrace x n_traces.  mt_state: uint32[625] (std::mt19937 image), updated in place."""
+        cap = (self.info.x_size + self.info.y_size + 8) * n_traces
+        buf = (D.Cell * cap)()
+        off = np.zeros(n_traces + 1, np.int64)
+        assert mt_state.dtype == np.uint32 and mt_state.size == 625 and mt_state.flags.c_contiguous
+        self.ctx.check(self.ctx.lib.hist_trace_sample(self.h, _p(mt_state, C.c_uint32), n_traces, buf, cap, _p(off, C.c_int64)))
+        allc = self._cells_np(buf, int(off[-1]))
+        return [allc[off[k]:off[k + 1]] for k in range(n_traces)]
+
+    def posterior_cells(self, min_post_prob):
+        """BackwardMatrix::cellsAbovePostProbThreshold (forward.cpp:1302-1319): ([n,3] cells, [n] log posteriors)
+        in priority-queue pop order."""
+        n = C.c_int64()
+        rc = self.ctx.lib.hist_posterior_cells(self.h, float(min_post_prob), None, None, 0, C.byref(n))
+        if rc not in (0, -5):
+            self.ctx.check(rc)
+        cap = max(1, n.value)
+        buf = (D.Cell * cap)()
+        lpp = np.empty(cap)
+        self.ctx.check(self.ctx.lib.hist_posterior_cells(self.h, float(min_post_prob), buf, _p(lpp, C.c_double), cap, C.byref(n)))
+        return self._cells_np(buf, n.value), lpp[:n.value].copy()

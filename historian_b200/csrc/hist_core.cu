@@ -359,6 +359,14 @@ extern "C" int hist_profile_upload(hist_ctx* ctx, const hist_profile_desc* d, hi
   p->t_dst.assign(d->trans_dest, d->trans_dest + p->nt);
   p->t_lp.assign(d->trans_lp, d->trans_lp + p->nt);
   if (d->closest_leaf_pos) p->leaf_pos.assign(d->closest_leaf_pos, d->closest_leaf_pos + p->n);
+  p->sorted_in = true;
+  {
+    std::vector<int> last(p->n, -1);
+    for (int t = 0; t < p->nt; ++t) {
+      if (p->t_src[t] <= last[p->t_dst[t]]) p->sorted_in = false;
+      last[p->t_dst[t]] = p->t_src[t];
+    }
+  }
   p->empty = true;
   for (int i = 0; i < p->n; ++i)
     if (p->is_emit[i]) p->empty = false;
@@ -662,6 +670,8 @@ int build_pair_host(hist_ctx* ctx, const hist_profile* x, const hist_profile* y,
     w[4][0] = l[HIST_W_IIW_IMM]; w[4][2] = l[HIST_W_IIW_IDM]; w[4][4] = l[HIST_W_IIW_IIW]; w[4][5] = l[HIST_W_IIW_EEE];
     for (int a = 0; a < 5; ++a)
       for (int c = 0; c < 6; ++c) D.W[a][c] = w[a][c] > -INFINITY ? (float)exp(w[a][c]) : 0.f;
+    for (int a = 0; a < 6; ++a)
+      for (int c = 0; c < 6; ++c) D.Wlog[a][c] = w[a][c];
   }
   pr->hmm_scalars = *hmm;
   pr->hmm_scalars.log_root = pr->hmm_scalars.l_sub = pr->hmm_scalars.r_sub = nullptr;

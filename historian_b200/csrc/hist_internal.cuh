@@ -90,6 +90,7 @@ struct PairDev {
   int C, A;
   int max_dist;           // <0: no envelope
   float W[5][6];          // exp(lpTrans[src][dest]), 0 where absent
+  double Wlog[6][6];      // lpTrans[src][dest] (natural log), -inf where absent
   int n_diag;
   int nS, nE;             // edge slots per diagonal: near-start rows, near-end columns
   const int* start_rows;  // [nS]
@@ -203,6 +204,7 @@ struct hist_profile {
   std::vector<double> t_lp;
   std::vector<int> leaf_pos;  // empty if not given
   bool empty;                 // Profile::isEmpty
+  bool sorted_in;             // every in-list ascending in source state, no repeated (src,dest)
   // device copy of lp_absorb
   double* d_lp_absorb;
   hb_arena* arena;            // owner of d_lp_absorb

@@ -210,9 +210,6 @@ int hist_fill_batch(hist_ctx* ctx, hist_pair* const* pairs, int32_t n, int do_ba
 int hist_cells_fetch(hist_pair* pair, int which, double* lp, int32_t* xpos, int32_t* ypos,
                      int64_t capacity, int64_t* n_cells);
 
-/* Entry points below this line are declared for the next milestones and are not yet
- * exported by the library; they become part of the ABI as they are implemented. */
-#ifdef HIST_DECLARE_PLANNED
 /* ------------------------------------------------------------------ traceback
  * ForwardMatrix::bestTrace(end) (forward.cpp:278-302): greedy arg-max walk from
  * `end` back to (0,0); candidates ordered by CellCoords::operator<, first strict
@@ -232,17 +229,20 @@ int hist_trace_sample(hist_pair* pair, uint32_t* mt_state, int32_t n_traces,
                       hist_cell* paths, int64_t capacity, int64_t* path_off);
 
 /* BackwardMatrix::bestTrace(start) (forward.cpp:1287-1300): greedy forward walk
- * through the Backward matrix from `start` to EEE (path excludes `start`,
- * includes EEE). */
+ * through the Backward matrix from `start` to EEE (path excludes `start`; the
+ * reference appends endCell after the walk, so EEE appears twice at the end). */
 int hist_trace_best_forward(hist_pair* pair, hist_cell start, hist_cell* path, int64_t capacity, int64_t* n);
 
 /* BackwardMatrix::cellsAbovePostProbThreshold (forward.cpp:1302-1319): all
  * (cell,state) with log posterior F+B-lpEnd >= log(min_post_prob), sorted by
  * decreasing posterior (the priority_queue pop order), ties by descending
- * (xpos, ypos, state).  Requires both fills. */
+ * (xpos, ypos, state).  Requires both fills and min_post_prob > 0. */
 int hist_posterior_cells(hist_pair* pair, double min_post_prob, hist_cell* cells, double* log_post,
                          int64_t capacity, int64_t* n);
 
+/* Entry points below this line are declared for the next milestones and are not yet
+ * exported by the library; they become part of the ABI as they are implemented. */
+#ifdef HIST_DECLARE_PLANNED
 /* ------------------------------------------------------------------ makeProfile
  * Numeric core of ForwardMatrix::makeProfile (forward.cpp:686-843): given the
  * sorted cell set (must contain SSS=(0,0,IMM) and EEE), decide retained cells
