@@ -61,6 +61,7 @@ def load():
     lib.hist_trace_best_forward.argtypes = [vp, D.Cell, C.POINTER(D.Cell), C.c_int64, D.c_int64_p]
     lib.hist_trace_sample.argtypes = [vp, D.c_uint32_p, C.c_int32, C.POINTER(D.Cell), C.c_int64, D.c_int64_p]
     lib.hist_posterior_cells.argtypes = [vp, C.c_double, C.POINTER(D.Cell), D.c_double_p, C.c_int64, D.c_int64_p]
+    lib.hist_profile_eliminate.argtypes = [vp, C.POINTER(D.Cell), C.c_int64, C.c_int32, C.POINTER(D.ElimResult)]
     _lib = lib
     return lib
 
@@ -304,3 +305,35 @@ class Pair:
         lpp = np.empty(cap)
         self.ctx.check(self.ctx.lib.hist_posterior_cells(self.h, float(min_post_prob), buf, _p(lpp, C.c_double), cap, C.byref(n)))
         return self._cells_np(buf, n.value), lpp[:n.value].copy()
+
+    def eliminate(self, cells, strategy=D.COLLAPSE_CHAINS):
+        """Numeric core of ForwardMatrix::makeProfile (forward.cpp:686-843) on a sorted cell set [n,3].
+        Returns a dict: state_cell [S,3], state_lp_absorb [S,C,A], state_fwd_lp [S], trans_src/dest/lp/best_lp [T],
+        via_off [T+1], via [V,3]."""
+        cells = np.ascontiguousarray(cells, np.int32).reshape(-1, 3)
+        n = len(cells)
+        Cc, A = self.components, self.alph_size
+        cap_s, cap_t, cap_v = n + 4, 8 * n + 64, 16 * n + 64
+        while True:
+            r = D.ElimResult()
+            st_cell = (D.Cell * cap_s)()
+            st_abs, st_fwd = np.empty((cap_s, Cc, A)), np.empty(cap_s)
+            t_src, t_dst = np.empty(cap_t, np.int32), np.empty(cap_t, np.int32)
+            t_lp, t_best = np.empty(cap_t), np.empty(cap_t)
+            via_off = np.empty(cap_t + 1, np.int64)
+            via = (D.Cell * cap_v)()
+            r.state_cell, r.state_lp_absorb, r.state_fwd_lp = st_cell, _p(st_abs, C.c_double), _p(st_fwd, C.c_double)
+            r.trans_src, r.trans_dest = _p(t_src, C.c_int32), _p(t_dst, C.c_int32)
+            r.trans_lp, r.trans_best_lp = _p(t_lp, C.c_double), _p(t_best, C.c_double)
+            r.trans_best_via_off, r.trans_best_via = _p(via_off, C.c_int64), via
+            r.state_capacity, r.trans_capacity, r.via_capacity = cap_s, cap_t, cap_v
+            rc = self.ctx.lib.hist_profile_eliminate(self.h, cells.ctypes.data_as(C.POINTER(D.Cell)), n, int(strategy), C.byref(r))
+            if rc == -5 and (r.n_states > cap_s or r.n_trans > cap_t or r.n_via > cap_v):
+                cap_s, cap_t, cap_v = max(cap_s, r.n_states), max(cap_t, r.n_trans), max(cap_v, int(r.n_via))
+                continue
+            self.ctx.check(rc)
+            break
+        ns, nt, nv = r.n_states, r.n_trans, int(r.n_via)
+        return dict(state_cell=self._cells_np(st_cell, ns), state_lp_absorb=st_abs[:ns].copy(), state_fwd_lp=st_fwd[:ns].copy(),
+                    trans_src=t_src[:nt].copy(), trans_dest=t_dst[:nt].copy(), trans_lp=t_lp[:nt].copy(),
+                    trans_best_lp=t_best[:nt].copy(), via_off=via_off[:nt + 1].copy(), via=self._cells_np(via, nv))

@@ -240,9 +240,6 @@ int hist_trace_best_forward(hist_pair* pair, hist_cell start, hist_cell* path, i
 int hist_posterior_cells(hist_pair* pair, double min_post_prob, hist_cell* cells, double* log_post,
                          int64_t capacity, int64_t* n);
 
-/* Entry points below this line are declared for the next milestones and are not yet
- * exported by the library; they become part of the ABI as they are implemented. */
-#ifdef HIST_DECLARE_PLANNED
 /* ------------------------------------------------------------------ makeProfile
  * Numeric core of ForwardMatrix::makeProfile (forward.cpp:686-843): given the
  * sorted cell set (must contain SSS=(0,0,IMM) and EEE), decide retained cells
@@ -277,6 +274,9 @@ typedef struct {
 int hist_profile_eliminate(hist_pair* pair, const hist_cell* cells, int64_t n_cells, int32_t strategy,
                            hist_elim_result* result);
 
+/* Entry points below this line are declared for the next milestones and are not yet
+ * exported by the library; they become part of the ABI as they are implemented. */
+#ifdef HIST_DECLARE_PLANNED
 /* ------------------------------------------------------------------ sum-product
  * SumProduct / AlignColSumProduct (sumprod.h:32-104, sumprod.cpp).
  * The model is passed in eigen-decomposed form (EigenModel, model.cpp:1135-1199):
