@@ -1,0 +1,403 @@
+"""Host-side driver of the progressive reconstruction: the caller of the hot path.
+
+Mirrors, on top of the C ABI, the parts of the reference that are bookkeeping around the DP:
+  * ForwardMatrix::bestProfile / sampleProfile (forward.cpp:845-895) and
+    BackwardMatrix::postProbProfile / addTrace / addCells (forward.cpp:1321-1379): which cells go
+    into the parent profile (the traces themselves come from the device);
+  * ForwardMatrix::makeProfile's assembly (forward.cpp:686-843): states/transitions from the device
+    elimination (hist_profile_eliminate), seqCoords (forward.cpp:533-538), alignPaths
+    (forward.cpp:540-578), then Profile::addReadyStates (profile.cpp:268-319);
+  * Dataset::prepareRecon's closest-leaf table (recon.cpp:864-915) and the node loop of
+    Reconstructor::reconstruct with its band-widening retry (recon.cpp:917-1052);
+  * traceAlignPath (forward.cpp:654-684) for the final alignment.
+AlignPaths are kept as lazy expressions (only the cells of the final root path are ever expanded).
+There is no CPU implementation of the DP here: every matrix is filled, traced and eliminated on the
+device.
+"""
+import numpy as np
+
+from . import descs as D
+from .profile_ops import add_ready_states
+
+IMM, IMD, IDM, IMI, IIW, EEE = D.IMM, D.IMD, D.IDM, D.IMI, D.IIW, D.EEE
+
+
+# ------------------------------------------------------------------ lazy AlignPath (alignpath.cpp:56-83)
+class Path:
+    """AlignPath expression: ('empty',) | ('col', row) | ('union', a, b) | ('concat', [..]) | ('addrow', a, row)."""
+    __slots__ = ("op", "args", "_cache")
+
+    def __init__(self, op, *args):
+        self.op, self.args, self._cache = op, args, None
+
+    def expand(self):
+        """dict row -> list of bool (the reference's AlignPath)."""
+        if self._cache is None:
+            op = self.op
+            if op == "empty":
+                r = {}
+            elif op == "col":
+                r = {self.args[0]: [True]}
+            elif op == "union":  # alignPathUnion: rows of the second are added to the first
+                r = dict(self.args[0].expand())
+                for k, v in self.args[1].expand().items():
+                    r.setdefault(k, v)
+            elif op == "addrow":  # alignPath[parentRow].push_back(true)
+                r = {k: list(v) for k, v in self.args[0].expand().items()}
+                r.setdefault(self.args[1], []).append(True)
+            else:
+                r = {}
+                for p in self.args[0]:
+                    r = concat_paths(r, p.expand())
+            self._cache = r
+        return self._cache
+
+
+EMPTY = Path("empty")
+
+
+def path_columns(a):
+    return max((len(v) for v in a.values()), default=0)
+
+
+def concat_paths(a1, a2):
+    """alignPathConcat (alignpath.cpp:62-78)."""
+    c1, c2 = path_columns(a1), path_columns(a2)
+    a = {k: list(v) for k, v in a1.items()}
+    for k in a:
+        if k not in a2:
+            a[k].extend([False] * c2)
+    for row, rp in a2.items():
+        lp = a.setdefault(row, [])
+        if not lp:
+            lp.extend([False] * c1)
+        lp.extend(rp)
+    return a
+
+
+# ------------------------------------------------------------------ host profile
+class HostProfile:
+    """A Profile (profile.h:41-76) on the host: the flattened arrays the C ABI takes plus the
+    bookkeeping that never goes to the device."""
+
+    def __init__(self, flat, state_path, trans_path, leaf_rows, root_row, name=""):
+        self.flat = flat                  # descs.Profile (closest_leaf_pos set by select_leaf)
+        self.state_path = state_path      # [n_states] Path
+        self.trans_path = trans_path      # [n_trans] Path
+        self.leaf_rows = leaf_rows        # {row: int32[n_states]} ProfileState::seqCoords of the rows still needed
+        self.root_row = root_row
+        self.name = name
+        self._trans_index = None
+        has_in = np.zeros(flat.n_states, bool)
+        has_in[flat.trans_dest] = True
+        self.emit_or_start = flat.is_emit.astype(bool) | ~has_in  # profile.h:34-35
+
+    @staticmethod
+    def leaf(seq, alphabet, components, row, name=""):
+        """Profile(components, alphabet, FastSeq, row) (profile.cpp:23-76)."""
+        flat = D.Profile.from_sequence(seq, alphabet, components)
+        n = flat.n_states
+        sp = [EMPTY] + [Path("col", row) for _ in range(n - 2)] + [EMPTY]
+        coords = np.arange(n, dtype=np.int32).clip(0, len(seq))
+        return HostProfile(flat, sp, [EMPTY] * flat.n_trans, {row: coords}, row, name)
+
+    def with_leaf(self, row):
+        """The flattened profile carrying seqCoords.at(row) as closest_leaf_pos (forward.cpp:36-42)."""
+        f = self.flat
+        return D.Profile(f.is_emit, f.trans_src, f.trans_dest, f.trans_lp, f.lp_absorb, self.leaf_rows[row], name=self.name)
+
+    def trans_between(self, s, d):
+        if self._trans_index is None:
+            self._trans_index = {(int(a), int(b)): t for t, (a, b) in enumerate(zip(self.flat.trans_src, self.flat.trans_dest))}
+        return self._trans_index[(int(s), int(d))]
+
+    def is_null(self, i):
+        return not self.flat.is_emit[i]
+
+    def is_emit_or_start(self, i):
+        return bool(self.emit_or_start[i])
+
+
+class PairView:
+    """What the assembly needs from one sibling merge: the two child profiles and the parent row."""
+
+    def __init__(self, x, y, parent_row):
+        self.x, self.y, self.parent_row = x, y, parent_row
+
+    def is_absorbing(self, c):  # forward.cpp:470-474
+        i, j, s = c
+        return ((s == IMM and not self.x.is_null(i) and not self.y.is_null(j)) or (s == IMD and not self.x.is_null(i))
+                or (s == IDM and not self.y.is_null(j)))
+
+    def cell_path(self, c):  # cellAlignPath, forward.cpp:540-568
+        i, j, s = c
+        if s == IMM:
+            if not self.x.is_null(i) and not self.y.is_null(j):
+                p = Path("union", self.x.state_path[i], self.y.state_path[j])
+            elif self.x.is_emit_or_start(i):
+                p = self.y.state_path[j]
+            else:
+                p = self.x.state_path[i]
+        elif s in (IMD, IIW):
+            p = self.x.state_path[i]
+        elif s in (IDM, IMI):
+            p = self.y.state_path[j]
+        else:
+            p = EMPTY
+        if self.is_absorbing(c):
+            p = Path("addrow", p, self.parent_row)
+        return p
+
+    def trans_path(self, src, dest):  # transitionAlignPath, forward.cpp:570-577
+        parts = []
+        if src[0] != dest[0]:
+            parts.append(self.x.trans_path[self.x.trans_between(src[0], dest[0])])
+        if src[1] != dest[1]:
+            parts.append(self.y.trans_path[self.y.trans_between(src[1], dest[1])])
+        if not parts:
+            return EMPTY
+        return parts[0] if len(parts) == 1 else Path("concat", parts)
+
+    def trace_path(self, trace):  # traceAlignPath, forward.cpp:654-684
+        parts = []
+        tr = [tuple(int(v) for v in c) for c in trace]
+        for n in range(len(tr) - 1):
+            parts += [self.cell_path(tr[n]), self.trans_path(tr[n], tr[n + 1])]
+        parts.append(self.cell_path(tr[-1]))
+        p = Path("concat", parts).expand()
+        for row in (self.parent_row, self.x.root_row, self.y.root_row):  # ensureAlignPathHasRow
+            p.setdefault(row, [])
+        return p
+
+
+# ------------------------------------------------------------------ which cells make the parent profile
+def _cellset(cells):
+    return np.array(sorted(cells), np.int32).reshape(-1, 3)
+
+
+def best_cells(pair):
+    """ForwardMatrix::bestProfile's cell set (forward.cpp:891-895)."""
+    return _cellset({tuple(int(v) for v in c) for c in pair.trace_best()})
+
+
+def sampled_cells(pair, mt_state, profile_samples, max_cells, strategy, min_len=0, max_len=None):
+    """ForwardMatrix::sampleProfile's cell set (forward.cpp:845-889).  mt_state is advanced in place."""
+    count = {}
+    n_traces = 0
+    if strategy & D.INCLUDE_BEST_TRACE:
+        for c in pair.trace_best():
+            count[tuple(int(v) for v in c)] = 2  # avoid dropping these cells
+        n_traces += 1
+    elif profile_samples <= 0:
+        raise ValueError("Must allow at least one sample path in the profile")
+    accepted = 0
+    while accepted < profile_samples and (max_cells == 0 or len(count) < max_cells):
+        tr = pair.trace_sample(mt_state, 1)[0]
+        anc_len = int(np.sum((tr[:, 2] == IMM) | (tr[:, 2] == IDM) | (tr[:, 2] == IMD)))
+        if anc_len < min_len or (max_len is not None and anc_len > max_len):
+            break
+        for c in tr:
+            k = tuple(int(v) for v in c)
+            count[k] = count.get(k, 0) + 1
+        n_traces += 1
+        accepted += 1
+    threshold = 2 if (n_traces > 1 and max_cells > 0 and len(count) >= max_cells) else 1
+    return _cellset({c for c, n in count.items() if n >= threshold})
+
+
+def posterior_cells(pair, min_post_prob, max_cells, strategy):
+    """BackwardMatrix::postProbProfile's cell set (forward.cpp:1327-1379), KeepGapsOpen excluded."""
+    if strategy & D.KEEP_GAPS_OPEN:
+        raise NotImplementedError("KeepGapsOpen posterior profiles (forward.cpp:1368-1375)")
+    queue, _ = pair.posterior_cells(min_post_prob)
+    cells = set()
+
+    def add_cells(fwd_trace, back_trace):  # addCells, forward.cpp:1344-1377
+        new = []
+        for c in fwd_trace[::-1]:
+            k = tuple(int(v) for v in c)
+            if k in cells:
+                break
+            new.append(k)
+        for c in back_trace:
+            k = tuple(int(v) for v in c)
+            if k in cells:
+                break
+            new.append(k)
+        if max_cells > 0 and len(cells) > 0 and len(cells) + len(new) > max_cells:
+            return False
+        cells.update(new)
+        return True
+
+    if len(queue) == 0 or (strategy & D.INCLUDE_BEST_TRACE):
+        add_cells(pair.trace_best(), [])
+    k = 0
+    while (max_cells == 0 or len(cells) < max_cells) and k < len(queue):
+        best = tuple(int(v) for v in queue[k])
+        if best in cells:
+            k += 1
+        elif not add_cells(pair.trace_best(best), pair.trace_best_forward(best)):  # addTrace, forward.cpp:1379-1384
+            break
+    return _cellset(cells)
+
+
+# ------------------------------------------------------------------ makeProfile assembly
+def make_profile(pair, view, cells, strategy, name=""):
+    """ForwardMatrix::makeProfile (forward.cpp:686-843) from the device elimination, then
+    Profile::addReadyStates (profile.cpp:268-319).  Returns (HostProfile, elimination dict)."""
+    e = pair.eliminate(cells, strategy)
+    st = [tuple(int(v) for v in c) for c in e["state_cell"]]
+    ns = len(st)
+    is_emit = np.array([view.is_absorbing(c) for c in st], np.uint8)
+    state_path = [view.cell_path(c) for c in st]
+    trans_path = []
+    via, off = e["via"], e["via_off"]
+    for t in range(len(e["trans_src"])):
+        chain = [st[e["trans_src"][t]]] + [tuple(int(v) for v in c) for c in via[off[t]:off[t + 1]]] + [st[e["trans_dest"][t]]]
+        parts = []
+        for k in range(len(chain) - 1):  # tap(src,c1), cap(c1), tap(c1,c2), ... , tap(c_last,dest)   (forward.cpp:764, 797)
+            parts.append(view.trans_path(chain[k], chain[k + 1]))
+            if k + 1 < len(chain) - 1:
+                parts.append(view.cell_path(chain[k + 1]))
+        trans_path.append(parts[0] if len(parts) == 1 else Path("concat", parts))
+    xi = np.array([c[0] for c in st]), np.array([c[1] for c in st])
+    leaf_rows = {}
+    for row, arr in view.x.leaf_rows.items():  # cellSeqCoords, forward.cpp:533-538 (y entries override x)
+        leaf_rows[row] = arr[xi[0]]
+    for row, arr in view.y.leaf_rows.items():
+        leaf_rows[row] = arr[xi[1]]
+    flat = D.Profile(is_emit, e["trans_src"], e["trans_dest"], e["trans_lp"], e["state_lp_absorb"], None, name=name)
+    q, old2new, extra = add_ready_states(flat, dict(leaf_rows))
+    n_new = q.n_states
+    sp = [EMPTY] * n_new
+    for s in range(ns):
+        sp[old2new[s]] = state_path[s]
+    tp = trans_path + [EMPTY] * (q.n_trans - len(trans_path))
+    prof = HostProfile(q, sp, tp, {r: np.ascontiguousarray(a, np.int32) for r, a in extra.items()}, view.parent_row, name)
+    prof.state_cell = [None] * n_new
+    prof.fwd_lp = np.full(n_new, np.nan)
+    for s in range(ns):
+        prof.state_cell[old2new[s]] = st[s]
+        prof.fwd_lp[old2new[s]] = e["state_fwd_lp"][s]
+    return prof, e
+
+
+# ------------------------------------------------------------------ Reconstructor::reconstruct (recon.cpp:917-1052)
+def closest_leaves(tree):
+    """Dataset::prepareRecon's closestLeaf / closestLeafDistance (recon.cpp:890-911)."""
+    n = tree.n_nodes
+    cl, dcl = np.zeros(n, np.int64), np.zeros(n)
+    for node in range(n):
+        if tree.is_leaf(node):
+            cl[node], dcl[node] = node, 0.0
+        else:
+            best, dbest = -1, 0.0
+            for nc, c in enumerate(tree.children[node]):
+                dc = dcl[c] + tree.branch_length[c]
+                if nc == 0 or dc < dbest:
+                    best, dbest = cl[c], dc
+            cl[node], dcl[node] = best, dbest
+    return cl, dcl
+
+
+def mt19937_seed(seed):
+    """std::mt19937(seed) as the 625-word image the C ABI passes in and out."""
+    mt = np.zeros(625, np.uint32)
+    x = seed & 0xffffffff
+    mt[0] = x
+    for k in range(1, 624):
+        x = (1812433253 * (x ^ (x >> 30)) + k) & 0xffffffff
+        mt[k] = x
+    mt[624] = 624
+    return mt
+
+
+class Reconstructor:
+    """The node loop of Reconstructor::reconstruct on the device context `ctx`.
+
+    Defaults follow recon.cpp:32-75 / recon.h:13-27: band 20, 10 profile samples, seed 5489 (mt19937's
+    default), CollapseChains | IncludeBestTrace.  `max_profile_states` must be given explicitly (the reference
+    derives it from host RAM, recon.cpp:77-79)."""
+
+    def __init__(self, ctx, model, band=20, profile_samples=10, max_profile_states=0, min_post_prob=None, seed=5489,
+                 include_best_trace=True, keep_gaps_open=False):
+        self.ctx, self.model = ctx, model
+        self.band, self.profile_samples, self.max_profile_states = band, profile_samples, max_profile_states
+        self.min_post_prob = min_post_prob       # not None: usePosteriorsForProfile (-profminpost)
+        self.seed = seed
+        self.strategy = (D.COLLAPSE_CHAINS | (D.INCLUDE_BEST_TRACE if include_best_trace else 0)
+                         | (D.KEEP_GAPS_OPEN if keep_gaps_open else 0))
+        self.log = []
+
+    def merge(self, node, lprof, rprof, tl, tr, guide_rows, cl_l, cl_r, is_root, mt_state):
+        """One internal node: DPMatrix + Forward (+ Backward), cell selection, makeProfile."""
+        from . import model as M
+        hmm = M.pair_hmm(self.model, tl, tr)
+        have_guide = guide_rows is not None
+        xf = lprof.with_leaf(cl_l) if have_guide else lprof.flat
+        yf = rprof.with_leaf(cl_r) if have_guide else rprof.flat
+        dx, dy = self.ctx.upload(xf), self.ctx.upload(yf)
+        max_dist = self.band if have_guide else -1
+        while True:  # band-widening retry (recon.cpp:954-975)
+            env = D.Envelope.from_guide_rows(guide_rows[cl_l], guide_rows[cl_r], max_dist) if max_dist >= 0 else D.Envelope(-1)
+            pair = self.ctx.prepare(dx, dy, hmm, env)
+            lp_end = pair.forward()
+            if lp_end > -np.inf:
+                break
+            if max_dist < 0:
+                raise RuntimeError("Zero forward likelihood even in the absence of guide alignment constraints")
+            n_cols = len(next(iter(guide_rows.values())))
+            max_dist = -1 if max_dist * 2 > n_cols else (1 if max_dist == 0 else max_dist * 2)
+            pair.close()
+        view = PairView(lprof, rprof, node)
+        use_post = self.min_post_prob is not None
+        path = None
+        if is_root:
+            best = pair.trace_best()
+            path = view.trace_path(best)                      # forward->bestAlignPath()
+            cells = _cellset({tuple(int(v) for v in c) for c in best})
+            prof, _ = make_profile(pair, view, cells, D.COLLAPSE_CHAINS)  # forward->bestProfile() (default strategy, forward.h:163)
+        elif use_post:
+            pair.backward()
+            cells = posterior_cells(pair, self.min_post_prob, self.max_profile_states, self.strategy)
+            prof, _ = make_profile(pair, view, cells, self.strategy)
+        else:
+            cells = sampled_cells(pair, mt_state, self.profile_samples, self.max_profile_states, self.strategy)
+            prof, _ = make_profile(pair, view, cells, self.strategy)
+        self.log.append(dict(node=node, lp_end=lp_end, cells=int(pair.n_cells), states=prof.flat.n_states, band=max_dist))
+        pair.close(); dx.close(); dy.close()
+        return prof, lp_end, path
+
+    def reconstruct(self, tree, seqs, guide=None):
+        """tree: simulator.Tree (postorder, root last); seqs: {leaf node: str}; guide: {leaf node: bool[cols]} or None.
+        Returns (alignment path {row: [bool]}, final Forward log-likelihood, {node: HostProfile})."""
+        cl, _ = closest_leaves(tree)
+        mt_state = mt19937_seed(self.seed)
+        prof, path, lp_final = {}, None, -np.inf
+        for node in range(tree.n_nodes):
+            if tree.is_leaf(node):
+                prof[node] = HostProfile.leaf(seqs[node], self.model.alphabet, self.model.components, node, tree.names[node])
+                continue
+            l, r = tree.children[node]
+            keep = int(cl[node])
+            p, lp_end, pth = self.merge(node, prof[l], prof[r], float(tree.branch_length[l]), float(tree.branch_length[r]), guide,
+                                        int(cl[l]), int(cl[r]), node == tree.root, mt_state)
+            # only the closest-leaf coordinates of this node are needed further up (forward.cpp:36-42)
+            p.leaf_rows = {keep: p.leaf_rows[keep]} if keep in p.leaf_rows else p.leaf_rows
+            prof[node] = p
+            if node == tree.root:
+                path, lp_final = pth, lp_end
+            else:
+                # children are not needed again except for their alignPath expressions, which the parent references
+                prof[l].leaf_rows, prof[r].leaf_rows = {}, {}
+        return path, lp_final, prof
+
+
+def gapped_rows(path, tree, seqs, wildcard="*"):
+    """Alignment(ungapped, path).gapped() (alignpath.cpp:232-280) with wildcard ancestors (recon.cpp:1410-1421)."""
+    out = {}
+    for row, rp in path.items():
+        s = seqs[row] if tree.is_leaf(row) else wildcard * int(np.sum(rp))
+        it = iter(s)
+        out[row] = "".join(next(it) if b else "-" for b in rp)
+    return out

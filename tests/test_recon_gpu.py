@@ -1,0 +1,149 @@
+"""GPU tests of the caller of the hot path (historian_b200/recon.py: cell selection, makeProfile
+assembly, the node loop) against
+
+  (a) the golden fixtures from the REAL reference: for every dumped node, starting from the reference's
+      own child profiles and generator state, the parent profile built through the C ABI must have the
+      reference's states and transitions (integer structure: exact, provided the traces coincide - the
+      reference walks its table-log-sum-exp matrix, so a sampled step can differ when a draw lands within
+      ~1e-4 of a boundary; those nodes are counted, not hidden) and its numbers within the fill tolerance;
+  (b) the reference BINARY (oracle/_ref/bin/historian, travels with the repo) end to end on a freshly
+      simulated family in deterministic mode: the reconstructed alignment must be identical, row by row.
+"""
+import os
+import subprocess
+import tempfile
+
+import numpy as np
+import pytest
+
+import helpers as H
+from historian_b200 import descs as D, recon as R
+
+pytestmark = pytest.mark.gpu
+CASES = H.golden_cases()
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF_BIN = os.path.join(ROOT, "oracle", "_ref", "bin", "historian")
+
+
+def host_profile(flat, row):
+    n = flat.n_states
+    return R.HostProfile(flat, [R.EMPTY] * n, [R.EMPTY] * flat.n_trans, {row: flat.closest_leaf_pos}, row, flat.name)
+
+
+@pytest.mark.parametrize("cid,path,node", CASES, ids=[c[0] for c in CASES])
+def test_parent_profile_matches_reference(ctx, cid, path, node):
+    d = H.load_golden(path)
+    pfx = "n%d." % node
+    x, y, hmm, env = H.node_inputs(d, node)
+    rows = [int(v) for v in d[pfx + "closest_rows"]]
+    if x.closest_leaf_pos is None:
+        pytest.skip("fixture without guide")
+    hx, hy = host_profile(x, rows[0]), host_profile(y, rows[1] if rows[1] != rows[0] else rows[1])
+    dx, dy = ctx.upload(x), ctx.upload(y)
+    pair = ctx.prepare(dx, dy, hmm, env)
+    pair.forward()
+    view = R.PairView(hx, hy, node)
+    strategy, max_states = int(d["strategy"][0]), int(d["max_profile_states"][0])
+    min_post = float(d["min_post_prob"][0])
+    is_root = node == int(max(d["dumped_nodes"])) and ("pf16593" in cid or node == int(d["dumped_nodes"][-1]))
+    best = pair.trace_best()
+    same_traces = H.same(best, d[pfx + "best_trace"])
+    if is_root:
+        cells = R.best_cells(pair)
+        strat = D.COLLAPSE_CHAINS
+    elif min_post > 0:
+        pair.backward()
+        gc, glpp = pair.posterior_cells(min_post)
+        rc = d[pfx + "post_cells"]
+        same_traces = same_traces and len(gc) == len(rc) and set(map(tuple, gc.tolist())) == set(map(tuple, rc.tolist()))
+        cells = R.posterior_cells(pair, min_post, max_states, strategy)
+        strat = strategy
+    else:
+        st = d[pfx + "rng_before"].astype(np.uint32).copy()
+        probe = st.copy()
+        k = 0
+        while pfx + "sample_trace%d" % k in d:
+            tr = pair.trace_sample(probe, 1)[0]
+            same_traces = same_traces and H.same(tr, d[pfx + "sample_trace%d" % k])
+            k += 1
+        if same_traces:  # the fixture's rng_after is the state after these probe traces (oracle/ref_dump.cpp:301-306)
+            assert H.same(probe, d[pfx + "rng_after"].astype(np.uint32)), cid + ": generator state after the traces differs"
+        cells = R.sampled_cells(pair, st, int(d["profile_samples"][0]), max_states, strategy)
+        strat = strategy
+    prof, e = R.make_profile(pair, view, cells, strat)
+    if not same_traces:
+        pytest.xfail("a trace differs from the reference's (table log-sum-exp margin); profile not comparable")
+    p = prof.flat
+    assert H.same(p.is_emit, d[pfx + "parent.is_emit"]), cid
+    assert H.same(p.trans_src, d[pfx + "parent.trans_src"]) and H.same(p.trans_dest, d[pfx + "parent.trans_dest"]), cid
+    ref_lp = d[pfx + "parent.trans_lp"]
+    assert np.all(np.abs(p.trans_lp - ref_lp) <= 1e-4 * np.abs(ref_lp) + 5e-3), np.abs(p.trans_lp - ref_lp).max()
+    A = p.alph_size * p.components
+    H.assert_log_close(p.lp_absorb.reshape(p.n_states, -1)[..., None], d[pfx + "parent.lp_absorb"].reshape(p.n_states, -1)[..., None],
+                       0.0, 2 * (A + 1) * 4.6e-5, what=cid + ":parent.lp_absorb")
+    ref_leaf = d[pfx + "parent.closest_leaf_pos"]
+    if env.max_distance >= 0:  # fixtures dumped with -noband carry no child coordinates
+        assert any(H.same(a[1:], ref_leaf[1:]) for a in prof.leaf_rows.values()), cid + ": closest-leaf coordinates"
+
+
+def _simulate(tmp, n_leaves, root_len, seed, bl=0.3):
+    from historian_b200 import model as M, simulator as S
+    tree = S.Tree.balanced(n_leaves, bl)
+    lg = M.RateModel.preset("lg")
+    lg.insRate = lg.delRate = 0.05
+    gapped, _ = S.simulate_family(lg, tree, root_len, seed)
+    lg = M.RateModel.preset("lg")
+    leaves, guide = S.leaf_guide(tree, gapped)
+    tf, gf = os.path.join(tmp, "tree.nh"), os.path.join(tmp, "guide.fa")
+    open(tf, "w").write(tree.newick())
+    with open(gf, "w") as f:
+        for v, row in zip(leaves, guide):
+            f.write(">%s\n%s\n" % (tree.names[v], bytes(row).decode()))
+    seqs = {v: bytes(row[row != ord("-")]).decode() for v, row in zip(leaves, guide)}
+    grows = {v: row != ord("-") for v, row in zip(leaves, guide)}
+    return tree, lg, seqs, grows, tf, gf
+
+
+def _read_fasta(text):
+    rows, name = [], None
+    for line in text.splitlines():
+        if line.startswith(">"):
+            rows.append([line[1:].strip(), ""])
+        elif rows:
+            rows[-1][1] += line.strip()
+    return rows
+
+
+@pytest.mark.parametrize("n_leaves,root_len,seed,band", [(8, 60, 3, 20), (16, 80, 5, 5), (6, 50, 9, -1)])
+def test_reconstruction_matches_reference_binary(ctx, n_leaves, root_len, seed, band):
+    if not os.path.exists(REF_BIN):
+        pytest.skip("oracle/_ref/bin/historian not built")
+    with tempfile.TemporaryDirectory() as tmp:
+        tree, lg, seqs, grows, tf, gf = _simulate(tmp, n_leaves, root_len, seed)
+        args = [REF_BIN, "recon", "-guide", gf, "-tree", tf, "-preset", "lg", "-profmaxstates", "1", "-output", "fasta", "-norefine"]
+        args += ["-band", str(band)] if band >= 0 else ["-noband"]
+        out = subprocess.run(args, stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, check=True, cwd=tmp).stdout.decode()
+    ref_rows = _read_fasta(out)
+    rec = R.Reconstructor(ctx, lg, band=band, profile_samples=10, max_profile_states=1)
+    path, lp_final, _ = rec.reconstruct(tree, seqs, grows if band >= 0 else None)
+    ours = R.gapped_rows(path, tree, seqs, wildcard="x")
+    assert len(ref_rows) == tree.n_nodes == len(ours)
+    ncol = {len(v) for v in ours.values()}
+    assert len(ncol) == 1, "alignment is not flush"
+    for node, (name, row) in enumerate(ref_rows):
+        assert ours[node] == row.lower() or ours[node] == row, "row %d (%s) differs:\n%s\n%s" % (node, name, ours[node], row)
+    assert np.isfinite(lp_final)
+
+
+def test_sampling_mode_runs_and_is_reproducible(ctx):
+    with tempfile.TemporaryDirectory() as tmp:
+        tree, lg, seqs, grows, _, _ = _simulate(tmp, 8, 50, 11)
+    a = R.Reconstructor(ctx, lg, band=10, profile_samples=5, max_profile_states=300, seed=7).reconstruct(tree, seqs, grows)
+    b = R.Reconstructor(ctx, lg, band=10, profile_samples=5, max_profile_states=300, seed=7).reconstruct(tree, seqs, grows)
+    assert a[0] == b[0] and a[1] == b[1]
+    rows = R.gapped_rows(a[0], tree, seqs)
+    for v, s in seqs.items():
+        assert rows[v].replace("-", "") == s
+    # posterior-profile mode (-profminpost)
+    c = R.Reconstructor(ctx, lg, band=10, max_profile_states=300, min_post_prob=0.01).reconstruct(tree, seqs, grows)
+    assert np.isfinite(c[1]) and len({len(v) for v in c[0].values()}) == 1
