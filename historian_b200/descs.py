@@ -296,3 +296,71 @@ def env_from_dump(d, pfx):
     if md < 0:
         return Envelope(-1)
     return Envelope(md, d[pfx + "cumulative_matches"], d[pfx + "row1_pos_to_col"], d[pfx + "row2_pos_to_col"])
+
+
+class SumProdModel:
+    """hist_model_desc: a RateModel in eigen-decomposed form (EigenModel, model.cpp:1135-1199)."""
+
+    def __init__(self, alphabet, cpt_weight, ins_prob, sub_rate, evals, evec, evec_inv, branch_sub=None):
+        self.alphabet = alphabet if isinstance(alphabet, bytes) else alphabet.encode()
+        self.cpt_weight = _arr(cpt_weight, np.float64)
+        self.ins_prob = _arr(ins_prob, np.float64)
+        self.sub_rate = _arr(sub_rate, np.float64)
+        ev, v, vi = np.asarray(evals, complex), np.asarray(evec, complex), np.asarray(evec_inv, complex)
+        self.parts = [_arr(a, np.float64) for a in (ev.real, ev.imag, v.real, v.imag, vi.real, vi.imag)]
+        self.branch_sub = None if branch_sub is None else _arr(branch_sub, np.float64)
+
+    @property
+    def components(self):
+        return self.ins_prob.shape[0]
+
+    @property
+    def alph_size(self):
+        return self.ins_prob.shape[1]
+
+    def desc(self):
+        d = ModelDesc()
+        d.alph_size, d.components = self.alph_size, self.components
+        d.alphabet = self.alphabet
+        d.cpt_weight, d.ins_prob, d.sub_rate = (_ptr(a, C.c_double) for a in (self.cpt_weight, self.ins_prob, self.sub_rate))
+        (d.eval_re, d.eval_im, d.evec_re, d.evec_im, d.evec_inv_re, d.evec_inv_im) = (_ptr(a, C.c_double) for a in self.parts)
+        if self.branch_sub is not None:
+            d.branch_sub = _ptr(self.branch_sub, C.c_double)
+        return d
+
+    @staticmethod
+    def from_golden(d, use_branch_sub=True):
+        return SumProdModel(bytes(d["alphabet"]), d["cpt_weight"], d["ins_prob"], d["sub_rate"], d["eval_re"] + 1j * d["eval_im"],
+                            d["evec_re"] + 1j * d["evec_im"], d["evec_inv_re"] + 1j * d["evec_inv_im"],
+                            d["branch_sub"] if use_branch_sub else None)
+
+    @staticmethod
+    def from_rate_model(model):
+        """Eigen-decompose a model.RateModel with numpy (host-side model preparation, O(C A^3) once)."""
+        from .model import EigenModel
+        e = EigenModel(model)
+        return SumProdModel(model.alphabet, model.cptWeight, model.insProb, model.subRate, np.array(e.eval), np.array(e.evec),
+                            np.array(e.evecInv))
+
+
+class TreeTopology:
+    """hist_tree_desc: nodes in postorder, children < parent, root last (tree.cpp:141)."""
+
+    def __init__(self, parent, branch_length):
+        self.parent = _arr(parent, np.int32)
+        self.branch_length = _arr(branch_length, np.float64)
+
+    @property
+    def n_nodes(self):
+        return len(self.parent)
+
+    def desc(self):
+        d = TreeDesc()
+        d.n_nodes = self.n_nodes
+        d.parent, d.branch_length = _ptr(self.parent, C.c_int32), _ptr(self.branch_length, C.c_double)
+        return d
+
+
+def counts_size(components, alph_size):
+    """Doubles in the flat EigenCounts buffer: 7 indel slots + rootCount[C][A] + eigenCount[C][A][A] (re, im)."""
+    return 7 + components * alph_size + 2 * components * alph_size * alph_size

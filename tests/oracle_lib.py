@@ -180,3 +180,57 @@ def sum_path_absorb(p, log_cpt_weight, log_ins_prob):
     pd = p.desc()
     tot = lib().oracle_sum_path_absorb(C.byref(pd), _p(w, C.c_double), _p(ins, C.c_double), _p(cum, C.c_double))
     return tot, cum
+
+
+# ------------------------------------------------------------------ sum-product (oracle/oracle_sumprod.cpp)
+SP_COUNTS, SP_MAP_STATES, SP_NODE_POST = 1, 2, 4
+
+
+def sumprod_branch_tables(model, tree):
+    Cc, A, N = model.components, model.alph_size, tree.n_nodes
+    sub = np.zeros((Cc, N, A, A))
+    esc = np.zeros((Cc, N, A, A, 2))
+    md, td = model.desc(), tree.desc()
+    rc = lib().oracle_sumprod_branch_tables(C.byref(md), C.byref(td), _p(sub, C.c_double), _p(esc, C.c_double))
+    assert rc == 0
+    return sub, esc[..., 0] + 1j * esc[..., 1]
+
+
+def sumprod_columns(model, tree, columns, weights=None, flags=SP_COUNTS | SP_MAP_STATES | SP_NODE_POST, debug=False):
+    """columns: uint8 [n_cols, N].  Returns dict(col_loglike, counts, map_state, node_post[, E, F, G, logE, logF, logG])."""
+    columns = np.ascontiguousarray(columns, np.uint8)
+    L, N = columns.shape
+    Cc, A = model.components, model.alph_size
+    r = dict(col_loglike=np.zeros(L), counts=np.zeros(D.counts_size(Cc, A)), map_state=np.zeros((L, N), np.uint8),
+             node_post=np.zeros((L, N, A)))
+    dbg = [None] * 6
+    if debug:
+        r.update(E=np.zeros((L, Cc, N, A)), F=np.zeros((L, Cc, N, A)), G=np.zeros((L, Cc, N, A)), logE=np.zeros((L, Cc, N)),
+                 logF=np.zeros((L, Cc, N)), logG=np.zeros((L, Cc, N)))
+        dbg = [r[k] for k in ("E", "F", "G", "logE", "logF", "logG")]
+    w = None if weights is None else np.ascontiguousarray(weights, np.float64)
+    md, td = model.desc(), tree.desc()
+    rc = lib().oracle_sumprod_columns(C.byref(md), C.byref(td), columns.ctypes.data_as(C.c_char_p), _p(w, C.c_double), C.c_int64(L),
+                                      C.c_int32(flags), _p(r["col_loglike"], C.c_double), _p(r["counts"], C.c_double),
+                                      r["map_state"].ctypes.data_as(C.c_char_p), _p(r["node_post"], C.c_double),
+                                      *[_p(a, C.c_double) for a in dbg])
+    assert rc == 0, rc
+    return r
+
+
+def sumprod_transform_counts(model, counts):
+    Cc, A = model.components, model.alph_size
+    root, sub = np.zeros((Cc, A)), np.zeros((Cc, A, A))
+    md = model.desc()
+    counts = np.ascontiguousarray(counts, np.float64)
+    rc = lib().oracle_sumprod_transform_counts(C.byref(md), _p(counts, C.c_double), _p(root, C.c_double), _p(sub, C.c_double))
+    assert rc == 0
+    return root, sub
+
+
+def split_counts(counts, Cc, A):
+    """flat EigenCounts -> (indel[7], rootCount[C][A], eigenCount[C][A][A] complex)."""
+    counts = np.asarray(counts)
+    root = counts[7:7 + Cc * A].reshape(Cc, A)
+    ec = counts[7 + Cc * A:].reshape(Cc, A, A, 2)
+    return counts[:7], root, ec[..., 0] + 1j * ec[..., 1]
