@@ -62,6 +62,15 @@ def load():
     lib.hist_trace_sample.argtypes = [vp, D.c_uint32_p, C.c_int32, C.POINTER(D.Cell), C.c_int64, D.c_int64_p]
     lib.hist_posterior_cells.argtypes = [vp, C.c_double, C.POINTER(D.Cell), D.c_double_p, C.c_int64, D.c_int64_p]
     lib.hist_profile_eliminate.argtypes = [vp, C.POINTER(D.Cell), C.c_int64, C.c_int32, C.POINTER(D.ElimResult)]
+    lib.hist_sumprod_create.argtypes = [vp, C.POINTER(D.ModelDesc), C.POINTER(D.TreeDesc), C.POINTER(vp)]
+    lib.hist_sumprod_destroy.argtypes = [vp]
+    lib.hist_sumprod_destroy.restype = None
+    lib.hist_sumprod_counts_size.argtypes = [vp]
+    lib.hist_sumprod_counts_size.restype = C.c_size_t
+    lib.hist_sumprod_columns.argtypes = [vp, vp, vp, C.c_int64, C.c_int32, vp, vp, vp, vp]
+    lib.hist_sumprod_debug_column.argtypes = [vp, C.c_char_p] + [D.c_double_p] * 7
+    lib.hist_sumprod_transform_counts.argtypes = [vp, vp, D.c_double_p, D.c_double_p]
+    lib.hist_sumprod_branch_tables.argtypes = [vp, D.c_double_p, D.c_double_p]
     _lib = lib
     return lib
 
@@ -117,6 +126,9 @@ class Context:
 
     def upload(self, profile):
         return DeviceProfile(self, profile)
+
+    def sumprod(self, model, tree):
+        return SumProd(self, model, tree)
 
     def prepare(self, x, y, hmm, env=None):
         return Pair(self, x, y, hmm, env if env is not None else D.Envelope(-1))
@@ -337,3 +349,94 @@ class Pair:
         return dict(state_cell=self._cells_np(st_cell, ns), state_lp_absorb=st_abs[:ns].copy(), state_fwd_lp=st_fwd[:ns].copy(),
                     trans_src=t_src[:nt].copy(), trans_dest=t_dst[:nt].copy(), trans_lp=t_lp[:nt].copy(),
                     trans_best_lp=t_best[:nt].copy(), via_off=via_off[:nt + 1].copy(), via=self._cells_np(via, nv))
+
+
+SP_COUNTS, SP_MAP_STATES, SP_NODE_POST = 1, 2, 4
+
+
+def _addr(a):
+    """Raw address of a numpy array, a torch tensor (host or CUDA) or None."""
+    if a is None:
+        return None
+    if hasattr(a, "data_ptr"):
+        return C.c_void_p(a.data_ptr())
+    return C.c_void_p(a.ctypes.data)
+
+
+class SumProd:
+    """SumProduct / AlignColSumProduct (sumprod.h:32-104) for one model and tree, on the device.
+
+    `columns` is a uint8 array [n_cols, N] (rows in the tree's postorder node order): residue
+    characters, '-' or '.' for gaps, '*' (or anything outside the alphabet) for wildcards."""
+
+    def __init__(self, ctx, model, tree):
+        self.ctx = ctx
+        self.C, self.A, self.N = model.components, model.alph_size, tree.n_nodes
+        md, td = model.desc(), tree.desc()
+        h = C.c_void_p()
+        ctx.check(ctx.lib.hist_sumprod_create(ctx.h, C.byref(md), C.byref(td), C.byref(h)))
+        self.h = h
+        self.counts_size = int(ctx.lib.hist_sumprod_counts_size(h))
+
+    def close(self):
+        if self.h and self.ctx.h:
+            self.ctx.lib.hist_sumprod_destroy(self.h)
+        self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def columns(self, columns, weights=None, flags=SP_COUNTS, counts=None, col_loglike=True):
+        """The column loop of EigenCounts::accumulateSubstitutionCounts (model.cpp:900-915) over all columns.
+        `counts`: flat EigenCounts buffer accumulated into (numpy array, or a CUDA torch tensor that then stays
+        on the device for an all-reduce); allocated if None.  Returns a dict."""
+        columns = np.ascontiguousarray(columns, np.uint8)
+        L, N = columns.shape
+        assert N == self.N, "columns must be [n_cols, %d]" % self.N
+        r = {}
+        if flags & SP_COUNTS:
+            r["counts"] = np.zeros(self.counts_size) if counts is None else counts
+        if col_loglike:
+            r["col_loglike"] = np.zeros(L)
+        if flags & SP_MAP_STATES:
+            r["map_state"] = np.zeros((L, N), np.uint8)
+        if flags & SP_NODE_POST:
+            r["node_post"] = np.zeros((L, N, self.A))
+        w = None if weights is None else np.ascontiguousarray(weights, np.float64)
+        self.ctx.check(self.ctx.lib.hist_sumprod_columns(self.h, _addr(columns), _addr(w), L, int(flags), _addr(r.get("col_loglike")),
+                                                         _addr(r.get("counts")), _addr(r.get("map_state")), _addr(r.get("node_post"))))
+        return r
+
+    def columns_device(self, d_columns, n_cols, d_counts, d_col_loglike=None, d_weights=None, flags=SP_COUNTS):
+        """Same call with every buffer already resident on the device (torch CUDA tensors)."""
+        self.ctx.check(self.ctx.lib.hist_sumprod_columns(self.h, _addr(d_columns), _addr(d_weights), int(n_cols), int(flags),
+                                                         _addr(d_col_loglike), _addr(d_counts), None, None))
+
+    def debug_column(self, column):
+        column = np.ascontiguousarray(column, np.uint8)
+        Cc, A, N = self.C, self.A, self.N
+        r = dict(E=np.zeros((Cc, N, A)), F=np.zeros((Cc, N, A)), G=np.zeros((Cc, N, A)), logE=np.zeros((Cc, N)), logF=np.zeros((Cc, N)),
+                 logG=np.zeros((Cc, N)))
+        ll = C.c_double()
+        self.ctx.check(self.ctx.lib.hist_sumprod_debug_column(self.h, column.ctypes.data_as(C.c_char_p),
+                                                              *[_p(r[k], C.c_double) for k in ("E", "F", "G", "logE", "logF", "logG")],
+                                                              C.byref(ll)))
+        r["col_loglike"] = ll.value
+        return r
+
+    def branch_tables(self):
+        Cc, A, N = self.C, self.A, self.N
+        sub, esc = np.zeros((Cc, N, A, A)), np.zeros((Cc, N, A, A, 2))
+        self.ctx.check(self.ctx.lib.hist_sumprod_branch_tables(self.h, _p(sub, C.c_double), _p(esc, C.c_double)))
+        return sub, esc[..., 0] + 1j * esc[..., 1]
+
+    def transform_counts(self, counts):
+        """EigenModel::getSubCounts (model.cpp:1352-1377): (rootCount[C][A], subCount[C][A][A])."""
+        root, sub = np.zeros((self.C, self.A)), np.zeros((self.C, self.A, self.A))
+        if not hasattr(counts, "data_ptr"):
+            counts = np.ascontiguousarray(counts, np.float64)
+        self.ctx.check(self.ctx.lib.hist_sumprod_transform_counts(self.h, _addr(counts), _p(root, C.c_double), _p(sub, C.c_double)))
+        return root, sub

@@ -276,7 +276,6 @@ int hist_profile_eliminate(hist_pair* pair, const hist_cell* cells, int64_t n_ce
 
 /* Entry points below this line are declared for the next milestones and are not yet
  * exported by the library; they become part of the ABI as they are implemented. */
-#ifdef HIST_DECLARE_PLANNED
 /* ------------------------------------------------------------------ sum-product
  * SumProduct / AlignColSumProduct (sumprod.h:32-104, sumprod.cpp).
  * The model is passed in eigen-decomposed form (EigenModel, model.cpp:1135-1199):
@@ -344,7 +343,11 @@ int hist_sumprod_debug_column(hist_sumprod* sp, const char* column, double* E, d
 int hist_sumprod_transform_counts(hist_sumprod* sp, const double* counts, double* root_count,
                                   double* sub_count);
 
-#endif /* HIST_DECLARE_PLANNED */
+/* The per-branch tables built on device by hist_sumprod_create (SumProduct ctor,
+ * sumprod.cpp:21-50): branch_sub [C][N][A][A] = branchSubProb, branch_esc
+ * [C][N][A][A] (re,im) = branchEigenSubCount (model.cpp:1329-1350).  Either may
+ * be NULL.  For parity tests. */
+int hist_sumprod_branch_tables(hist_sumprod* sp, double* branch_sub, double* branch_esc);
 
 #ifdef __cplusplus
 }
