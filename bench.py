@@ -185,6 +185,131 @@ def workload_config(pairs):
             "l2_policy": "cell planes written per step (>1 GB) exceed the 126 MB L2; no reuse between steps"}
 
 
+# ------------------------------------------------------------------ EM count leg (BASELINE.json metric 3, configs[3])
+EM_LEAVES, EM_ROOT_LEN = 4096, 1000
+
+
+def em_family():
+    """configs[3]: DNA, Jukes-Cantor with a 2-component discretised gamma, balanced 4096-leaf tree, full history
+    (ancestral rows included) as `historian fit -stockrecon` reads it."""
+    from historian_b200 import descs as D, model as M, simulator as S
+    tree = S.Tree.balanced(EM_LEAVES, BRANCH)
+    jc = M.RateModel.preset("jc").gamma(2, 1.0)
+    gapped, _ = S.simulate_family(jc, tree, EM_ROOT_LEN, 1)
+    cols = np.ascontiguousarray(gapped.T)                      # [n_cols, N]
+    return D.SumProdModel.from_rate_model(jc), D.TreeTopology(tree.parent, tree.branch_length), cols
+
+
+def em_leg(ctx, args, rank, world, local, barrier):
+    """EM count columns/s: one step = the E-step substitution counts (sum-product up/down + eigen-counts,
+    model.cpp:900-915) of the whole alignment, columns sharded over the ranks, one NCCL all-reduce of the
+    count buffer per step (strong scaling: the alignment is fixed)."""
+    import torch
+    import torch.distributed as dist
+    from historian_b200 import em
+    model, tree, cols = em_family()
+    n_cols, N = cols.shape
+    lo, hi = em.column_shard(n_cols, rank, world)
+    sp = ctx.sumprod(model, tree)
+    dev = torch.device("cuda", local)
+    stream = torch.cuda.ExternalStream(ctx.stream, device=local)
+    d_cols = torch.from_numpy(cols[lo:hi]).to(dev)
+    d_counts = torch.zeros(sp.counts_size, dtype=torch.float64, device=dev)
+    d_ll = torch.zeros(max(1, hi - lo), dtype=torch.float64, device=dev)
+
+    def step_resident():
+        d_counts.zero_()
+        torch.cuda.synchronize()
+        sp.columns_device(d_cols, hi - lo, d_counts, d_ll)
+        if world > 1:
+            ctx.synchronize()
+            dist.all_reduce(d_counts)
+
+    for _ in range(args.warmup):
+        step_resident()
+    ctx.set_timing(True)
+    ctx.fill_time_ms()
+    barrier()
+    steps = max(1, min(args.steps, 5))
+    t0 = time.perf_counter()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(steps):
+        step_resident()
+    e1.record(stream)
+    barrier()
+    wall_ms = 1e3 * (time.perf_counter() - t0)
+    ms = max(e0.elapsed_time(e1), 0.0)
+    if world > 1:
+        ms = wall_ms          # the all-reduce runs on torch's stream: bracket the whole step on the host clock between barriers
+    kernel_ms, kernel_launches = ctx.fill_time_ms()
+    ctx.set_timing(False)
+    resident_counts = d_counts.cpu().numpy()
+
+    pinned = torch.from_numpy(cols[lo:hi]).pin_memory()
+    host_cols = pinned.numpy()
+
+    def step_e2e():
+        buf = torch.zeros(sp.counts_size, dtype=torch.float64, device=dev)
+        torch.cuda.synchronize()
+        sp.columns(host_cols, counts=buf, col_loglike=False)
+        if world > 1:
+            dist.all_reduce(buf)
+        return buf.cpu().numpy()
+
+    step_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        e2e_counts = step_e2e()
+    barrier()
+    e2e_ms = 1e3 * (time.perf_counter() - t0)
+    assert np.allclose(e2e_counts, resident_counts, rtol=1e-9, atol=1e-9)
+
+    t = torch.tensor([ms, e2e_ms, kernel_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, e2e_ms, kernel_ms = t.tolist()
+    out = None
+    if rank == 0:
+        A, Cc = model.alph_size, model.components
+        alg_bytes = 3.0 * Cc * N * A * 8 + N        # SURVEY.md 8(d): E/F/G messages of one column + its characters
+        per_launch_s = kernel_ms / 1e3 / max(1, kernel_launches)
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        achieved = (hi - lo) * alg_bytes / per_launch_s / 1e9
+        base = None
+        if world == 1:
+            sys.path.insert(0, os.path.join(ROOT, "tests"))
+            import oracle_lib as O
+            sample = cols[:: max(1, n_cols // args.cpu_cols)][: args.cpu_cols]
+            c0 = time.perf_counter()
+            oc = O.sumprod_columns(model, tree, sample, flags=O.SP_COUNTS)["counts"]
+            cpu_s = time.perf_counter() - c0
+            dc = sp.columns(sample)["counts"]
+            assert np.allclose(dc, oc, rtol=1e-8, atol=1e-8), "device counts differ from the CPU oracle on the sample"
+            base = {"value": len(sample) / cpu_s, "unit": "columns/s", "cores": 1, "kind": "port",
+                    "sample": "%d evenly spaced columns of the same alignment through oracle/oracle_sumprod.cpp (FP64, 1 thread), %.1f s; "
+                              "device counts checked against it" % (len(sample), cpu_s)}
+        out = {"metric": "EM count columns/s", "value": n_cols * steps / (ms / 1e3), "unit": "columns/s", "steps": steps,
+               "ms_per_step": ms / steps, "scaling": "strong", "dtype": "f64",
+               "config": {"workload": "dna_jc_gamma2_4096x1000_seed1 full-history alignment, substitution E-step (sum-product + eigen-counts)",
+                          "columns": int(n_cols), "nodes": int(N), "alphabet": int(A), "components": int(Cc),
+                          "parallelism": "columns sharded over %d GPU(s), one all-reduce of %d doubles per step" % (world, sp.counts_size)},
+               "e2e": {"value": n_cols * steps / (e2e_ms / 1e3), "unit": "columns/s", "h2d_bytes_per_step": int((hi - lo) * N),
+                       "d2h_bytes_per_step": int(8 * sp.counts_size)},
+               "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                            "kernel": "hb::sumprod_columns_kernel", "avg_launch_ms": 1e3 * per_launch_s,
+                            "algorithmic_bytes_per_column": alg_bytes, "columns_per_launch": int(hi - lo)},
+               "cpu_baseline": base, "gpu_launches": int(2 * steps)}
+    sp.close()
+    return out
+
+
 # ------------------------------------------------------------------ GPU arm
 def gpu_arm(args):
     import torch
@@ -301,6 +426,12 @@ def gpu_arm(args):
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"},
             "cpu_baseline": base, "clocks": clk, "cpu_cores": cores,
         }
+    em_line = None
+    if not args.no_em:
+        em_line = em_leg(ctx, args, rank, world, local, barrier)
+    if rank == 0:
+        if em_line is not None:
+            line["em_counts"] = em_line
         print(json.dumps(line))
     ctx.close()
     if world > 1:
@@ -315,6 +446,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--pairs", type=int, default=512, help="sibling merges per step per GPU")
     ap.add_argument("--cpu-pairs", type=int, default=96, help="merges in the cpu_baseline sample (about 15 s on one core)")
+    ap.add_argument("--cpu-cols", type=int, default=64, help="columns in the EM leg's cpu_baseline sample")
+    ap.add_argument("--no-em", action="store_true", help="skip the EM count leg (profiling runs)")
     args = ap.parse_args()
     if args.impl == "reference":
         reference_arm(args)
