@@ -43,6 +43,7 @@ def load():
     lib.hist_ctx_set_timing.argtypes = [vp, C.c_int]
     lib.hist_ctx_fill_time_ms.argtypes = [vp, D.c_double_p, D.c_int64_p]
     lib.hist_profile_upload.argtypes = [vp, C.POINTER(D.ProfileDesc), C.POINTER(vp)]
+    lib.hist_profile_from_sequences.argtypes = [vp, C.c_int32, C.POINTER(vp), D.c_int32_p, C.c_int32, C.c_int32, C.POINTER(vp)]
     lib.hist_profile_destroy.argtypes = [vp]
     lib.hist_profile_destroy.restype = None
     lib.hist_pair_prepare.argtypes = [vp, vp, vp, C.POINTER(D.PairHmmDesc), C.POINTER(D.EnvDesc), C.POINTER(vp)]
@@ -127,6 +128,25 @@ class Context:
     def upload(self, profile):
         return DeviceProfile(self, profile)
 
+    def upload_sequences(self, seqs, alphabet, components=1, wildcard="*"):
+        """Leaf profiles Profile(components, alphabet, FastSeq, row) (profile.cpp:23-76) of a batch of residue
+        strings, built on the device (hist_profile_from_sequences): only the residues cross the bus."""
+        lut = np.full(256, -1, np.int8)                      # tokenize(), fastseq.cpp:10-16: exact char, then swapped case
+        for k, ch in enumerate(alphabet):
+            for c in (ch.swapcase(), ch):
+                lut[ord(c)] = k
+        for k, ch in enumerate(alphabet):
+            lut[ord(ch)] = k
+        lut[ord(wildcard)] = -1
+        toks = [lut[np.frombuffer(s.encode() if isinstance(s, str) else bytes(s), np.uint8)] for s in seqs]
+        n = len(toks)
+        ptrs = (C.c_void_p * n)(*[t.ctypes.data for t in toks])
+        lens = np.array([len(t) for t in toks], np.int32)
+        out = (C.c_void_p * n)()
+        self.check(self.lib.hist_profile_from_sequences(self.h, n, ptrs, _p(lens, C.c_int32), len(alphabet), components, out))
+        return [DeviceProfile(self, None, handle=C.c_void_p(out[k]), seq=seqs[k], alphabet=alphabet, components=components,
+                              wildcard=wildcard) for k in range(n)]
+
     def sumprod(self, model, tree):
         return SumProd(self, model, tree)
 
@@ -151,12 +171,27 @@ class Context:
 class DeviceProfile:
     """Device-resident Profile (profile.h:41-76), see hist_profile_upload."""
 
-    def __init__(self, ctx, profile):
-        self.ctx, self.host = ctx, profile
-        d = profile.desc()
-        h = C.c_void_p()
-        ctx.check(ctx.lib.hist_profile_upload(ctx.h, C.byref(d), C.byref(h)))
-        self.h = h
+    def __init__(self, ctx, profile, handle=None, seq=None, alphabet=None, components=1, wildcard="*"):
+        self.ctx, self._host = ctx, profile
+        self._leaf = (seq, alphabet, components, wildcard)
+        if handle is None:
+            d = profile.desc()
+            handle = C.c_void_p()
+            ctx.check(ctx.lib.hist_profile_upload(ctx.h, C.byref(d), C.byref(handle)))
+        self.h = handle
+        if profile is not None:
+            self.components, self.alph_size = profile.components, profile.alph_size
+        else:
+            self.components, self.alph_size = components, len(alphabet)
+
+    @property
+    def host(self):
+        """Host-side flattened Profile (built lazily for profiles constructed on the device)."""
+        if self._host is None:
+            seq, alphabet, components, wildcard = self._leaf
+            seq = seq if isinstance(seq, str) else bytes(seq).decode()
+            self._host = D.Profile.from_sequence(seq, alphabet, components, wildcard)
+        return self._host
 
     def close(self):
         if self.h and self.ctx.h:
@@ -209,7 +244,7 @@ class Pair:
         info = D.PairInfo()
         ctx.check(ctx.lib.hist_pair_get_info(self.h, C.byref(info)))
         self.info = info
-        self.components, self.alph_size = x.host.components, x.host.alph_size
+        self.components, self.alph_size = x.components, x.alph_size
 
     def close(self):
         if self.h and self.ctx.h:

@@ -15,6 +15,8 @@
 #include <cstring>
 #include <limits>
 
+#include <mutex>
+#include <thread>
 #include "hist_internal.cuh"
 
 namespace hb {
@@ -27,7 +29,11 @@ int set_err(hist_ctx* ctx, int code, const char* fmt, ...) {
   va_start(ap, fmt);
   vsnprintf(buf, sizeof(buf), fmt, ap);
   va_end(ap);
-  if (ctx) ctx->err = buf; else g_create_err = buf;
+  {
+    static std::mutex mu;  // build_pair_host runs on several host threads
+    std::lock_guard<std::mutex> lock(mu);
+    if (ctx) ctx->err = buf; else g_create_err = buf;
+  }
   return code;
 }
 
@@ -285,6 +291,15 @@ extern "C" int hist_ctx_create(int device, hist_ctx** out) {
     delete ctx;
     return HIST_ERR_CUDA;
   }
+  {
+    // keep freed arenas in the stream-ordered pool: every level of a reconstruction allocates a multi-GB
+    // arena, and the default threshold (0) would hand it back to the OS at each synchronisation
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+      unsigned long long keep = ~0ull;
+      cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    }
+  }
   cudaDeviceProp prop;
   cudaGetDeviceProperties(&prop, device);
   ctx->sm_count = prop.multiProcessorCount;
@@ -386,15 +401,141 @@ extern "C" int hist_profile_upload(hist_ctx* ctx, const hist_profile_desc* d, hi
   return HIST_OK;
 }
 
+namespace {
+int ensure_staging(hist_ctx* ctx, size_t bytes);
+void arena_release(hist_ctx* ctx, hb_arena* a);
+}  // namespace
+
+namespace hb {
+// lpAbsorb of leaf profiles (profile.cpp:52-66): state 0 and END are null (rows unused, kept -inf), state pos+1
+// is 0 at the residue's token and -inf elsewhere, or all 0 for a wildcard / invalid character.
+// One thread per (state, component, residue) of the concatenated batch.
+__global__ void leaf_absorb_kernel(const int8_t* tokens, const long long* state_off, int n_seq, int C, int A, double* lp) {
+  const long long total = state_off[n_seq] * C * A;
+  for (long long q = blockIdx.x * (long long)blockDim.x + threadIdx.x; q < total; q += (long long)gridDim.x * blockDim.x) {
+    const int a = q % A;
+    const long long st = q / ((long long)C * A);  // global state index
+    // sequence of this state: binary search in state_off
+    int lo = 0, hi = n_seq;
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (state_off[mid] <= st) lo = mid; else hi = mid;
+    }
+    const long long local = st - state_off[lo], n_states = state_off[lo + 1] - state_off[lo];
+    double v = -INFINITY;
+    if (local > 0 && local < n_states - 1) {
+      const int tok = tokens[st - 2 * lo - 1];  // token index = global state index minus the START/END rows before it
+      v = (tok < 0 || tok == a) ? 0.0 : -INFINITY;
+    }
+    lp[q] = v;
+  }
+}
+}  // namespace hb
+
+extern "C" int hist_profile_from_sequences(hist_ctx* ctx, int32_t n, const int8_t* const* tokens, const int32_t* lengths,
+                                           int32_t alph_size, int32_t components, hist_profile** out) {
+  if (!ctx || n <= 0 || !tokens || !lengths || !out) return set_err(ctx, HIST_ERR_ARG, "hist_profile_from_sequences: bad arguments");
+  if (alph_size < 1 || alph_size > 127 || components < 1) return set_err(ctx, HIST_ERR_ARG, "hist_profile_from_sequences: bad A/C");
+  for (int k = 0; k < n; ++k) out[k] = nullptr;
+  cudaSetDevice(ctx->device);
+  std::vector<long long> state_off(n + 1, 0);
+  long long n_tok = 0;
+  for (int k = 0; k < n; ++k) {
+    if (lengths[k] < 0 || (lengths[k] > 0 && !tokens[k])) return set_err(ctx, HIST_ERR_ARG, "hist_profile_from_sequences: sequence %d", k);
+    state_off[k + 1] = state_off[k] + lengths[k] + 2;
+    n_tok += lengths[k];
+  }
+  const size_t K = (size_t)alph_size * components;
+  const size_t lp_bytes = (size_t)state_off[n] * K * sizeof(double), off_bytes = (n + 1) * sizeof(long long);
+  const size_t tok_off = (lp_bytes + 255) & ~(size_t)255, so_off = (tok_off + n_tok + 255) & ~(size_t)255, total = so_off + off_bytes;
+  hb_arena* arena = new hb_arena{nullptr, total, 0};
+  int rc = check_cuda(ctx, cudaMallocAsync((void**)&arena->dev, total, ctx->stream), "cudaMallocAsync(leaf profiles)");
+  const size_t so_st = (n_tok + 255) & ~(size_t)255;
+  if (!rc) rc = ensure_staging(ctx, so_st + off_bytes);
+  if (rc) {
+    if (arena->dev) cudaFreeAsync(arena->dev, ctx->stream);
+    delete arena;
+    return rc;
+  }
+  {
+    char* st = ctx->staging;
+    long long at = 0;
+    for (int k = 0; k < n; ++k) {
+      for (int q = 0; q < lengths[k]; ++q) st[at + q] = tokens[k][q] >= alph_size ? -1 : tokens[k][q];
+      at += lengths[k];
+    }
+    memcpy(ctx->staging + so_st, state_off.data(), off_bytes);
+    rc = check_cuda(ctx, cudaMemcpyAsync(arena->dev + tok_off, ctx->staging, n_tok, cudaMemcpyHostToDevice, ctx->stream), "H2D tokens");
+    if (!rc) rc = check_cuda(ctx, cudaMemcpyAsync(arena->dev + so_off, ctx->staging + so_st, off_bytes, cudaMemcpyHostToDevice, ctx->stream), "H2D offsets");
+  }
+  if (!rc) {
+    const long long work = state_off[n] * (long long)K;
+    const int blocks = (int)std::max<long long>(1, std::min<long long>((work + 255) / 256, (long long)ctx->sm_count * 16));
+    hb::leaf_absorb_kernel<<<blocks, 256, 0, ctx->stream>>>((const int8_t*)(arena->dev + tok_off), (const long long*)(arena->dev + so_off), n,
+                                                           components, alph_size, (double*)arena->dev);
+    ctx->launches += 1;
+    rc = check_cuda(ctx, cudaGetLastError(), "leaf_absorb_kernel");
+  }
+  // the token strings are only borrowed, and the staging buffer is reused by the next call
+  if (!rc) rc = check_cuda(ctx, cudaStreamSynchronize(ctx->stream), "sync after leaf profiles");
+  if (rc) {
+    cudaFreeAsync(arena->dev, ctx->stream);
+    delete arena;
+    return rc;
+  }
+  for (int k = 0; k < n; ++k) {
+    hist_profile* p = new hist_profile();
+    const int L = lengths[k];
+    p->ctx = ctx;
+    p->n = L + 2;
+    p->nt = L + 1;
+    p->A = alph_size;
+    p->C = components;
+    p->is_emit.assign(p->n, 1);
+    p->is_emit.front() = p->is_emit.back() = 0;
+    p->t_src.resize(p->nt);
+    p->t_dst.resize(p->nt);
+    p->t_lp.assign(p->nt, 0.0);
+    p->leaf_pos.resize(p->n);
+    for (int t = 0; t < p->nt; ++t) { p->t_src[t] = t; p->t_dst[t] = t + 1; }
+    for (int i = 0; i < p->n; ++i) p->leaf_pos[i] = std::min(i, L);   // seqCoords of the leaf row (profile.cpp:33-36, 49)
+    p->sorted_in = true;
+    p->empty = L == 0;
+    p->d_lp_absorb = (double*)arena->dev + (size_t)state_off[k] * K;
+    p->arena = arena;
+    ++arena->refs;
+    out[k] = p;
+  }
+  return HIST_OK;
+}
+
 extern "C" void hist_profile_destroy(hist_profile* p) {
   if (!p) return;
   cudaSetDevice(p->ctx->device);
-  if (p->d_lp_absorb) cudaFreeAsync(p->d_lp_absorb, p->ctx->stream);
+  if (p->arena) arena_release(p->ctx, p->arena);
+  else if (p->d_lp_absorb) cudaFreeAsync(p->d_lp_absorb, p->ctx->stream);
   delete p;
 }
 
 // ------------------------------------------------------------------ pair preparation
 namespace {
+
+// Runs fn(0..n-1) on up to hardware_concurrency host threads (at least `grain` items per thread).
+template <class F>
+void parallel_for(int n, int grain, F fn) {
+  int nthreads = (int)std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 16u);
+  nthreads = std::max(1, std::min(nthreads, n / std::max(1, grain)));
+  if (nthreads <= 1) {
+    for (int k = 0; k < n; ++k) fn(k);
+    return;
+  }
+  std::vector<std::thread> pool;
+  for (int t = 0; t < nthreads; ++t)
+    pool.emplace_back([=, &fn]() {
+      for (int k = t; k < n; k += nthreads) fn(k);
+    });
+  for (auto& th : pool) th.join();
+}
 
 // Byte layout of one pair inside the batch arena: a host-initialised part (copied in ONE H2D
 // transfer for the whole batch) and a device-only part.
@@ -773,9 +914,14 @@ extern "C" int hist_pair_prepare_batch(hist_ctx* ctx, int32_t n, const hist_prof
     return rc;
   };
   size_t host_total = 0, dev_total = 0;
+  {
+    // the host part of the DPMatrix constructors is independent per pair: spread it over host threads
+    std::vector<int> rcs(n, 0);
+    parallel_for(n, 8, [&](int k) { rcs[k] = build_pair_host(ctx, xs[k], ys[k], hmms[k], envs ? envs[k] : nullptr, want_bwd, builds[k]); });
+    for (int k = 0; k < n; ++k)
+      if (rcs[k]) return fail(rcs[k]);
+  }
   for (int k = 0; k < n; ++k) {
-    int rc = build_pair_host(ctx, xs[k], ys[k], hmms[k], envs ? envs[k] : nullptr, want_bwd, builds[k]);
-    if (rc) return fail(rc);
     builds[k].host_base = host_total;
     host_total += builds[k].host.bytes;
   }
@@ -801,13 +947,16 @@ extern "C" int hist_pair_prepare_batch(hist_ctx* ctx, int32_t n, const hist_prof
   // fill the pinned staging image and ship it in one transfer
   char* st = ctx->staging;
   int maxN = 1, maxNt = 1, maxDiag = 1, maxKp = 4, maxKC = 1;
-  for (int k = 0; k < n; ++k) {
+  parallel_for(n, 8, [&](int k) {
     PairBuild& b = builds[k];
     place_pair(b, arena->dev, scal_off + (size_t)k * 4 * sizeof(double), want_bwd);
     char* base = st + b.host_base;
     for (auto& c : b.host.copies) memcpy(base + c.first, c.second.first, c.second.second);
     memcpy(base + b.h_pairdev, &b.pr->dev, sizeof(PairDev));
     ((PairDev**)(st + ptr_off))[k] = b.pr->d_dev;
+  });
+  for (int k = 0; k < n; ++k) {
+    PairBuild& b = builds[k];
     const PairDev& D = b.pr->dev;
     maxN = std::max(maxN, std::max(D.x.n, D.y.n));
     maxNt = std::max(maxNt, std::max(D.x.nt, D.y.nt));

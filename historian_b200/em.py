@@ -3,7 +3,9 @@ EigenCounts::accumulateSubstitutionCounts (model.cpp:900-915) sharded over GPUs,
 IndelCounts::accumulateIndelCounts (model.cpp:847-898) and EigenCounts::transform (model.cpp:924-931).
 
 Partitioning: alignment columns are independent given the model, so rank r of W takes the
-contiguous block column_shard(n_cols, r, W); the model, eigen-system and tree are replicated.  The only
+columns r, r+W, r+2W, ... (column_shard): interleaving balances the load, because the cost of a column grows
+with its number of ungapped rows and dense (root-derived) and sparse (insertion) columns come in runs.  The
+model, eigen-system and tree are replicated.  The only
 exchange is ONE all-reduce (sum) of the flat EigenCounts buffer (7 + C*A + 2*C*A^2 doubles), issued on the
 device-resident buffer the count kernel accumulated into (torch.distributed, NCCL over NVLink); the M-step
 is replicated.  The per-branch indel counts are sharded by branch (each branch is a sequential scan over
@@ -15,17 +17,14 @@ import numpy as np
 
 
 def column_shard(n_cols, rank, world):
-    """Contiguous block [lo, hi) of rank `rank`: sizes differ by at most one, blocks in rank order."""
-    base, extra = divmod(int(n_cols), int(world))
-    lo = rank * base + min(rank, extra)
-    return lo, lo + base + (1 if rank < extra else 0)
+    """The columns of rank `rank` as a slice: rank, rank + world, ...  (a partition of range(n_cols))."""
+    return slice(int(rank), int(n_cols), int(world))
 
 
 def count_sharded(compute, n_cols, rank=0, world=1, all_reduce=None):
-    """Runs `compute(lo, hi)` (-> flat counts of this rank's column block, any array type the reducer
-    understands) on this rank's shard and sums over ranks with `all_reduce(buf)` (in place)."""
-    lo, hi = column_shard(n_cols, rank, world)
-    buf = compute(lo, hi)
+    """Runs `compute(shard)` (-> flat counts of this rank's columns, any array type the reducer understands)
+    on this rank's shard (a slice of the column index) and sums over ranks with `all_reduce(buf)` (in place)."""
+    buf = compute(column_shard(n_cols, rank, world))
     if world > 1:
         if all_reduce is None:
             raise ValueError("world > 1 needs an all_reduce")
@@ -107,12 +106,13 @@ class ColumnCounter:
         columns = np.ascontiguousarray(columns, np.uint8)
         dev = torch.device("cuda", self.ctx.device)
 
-        def compute(lo, hi):
+        def compute(shard):
             buf = torch.zeros(self.sp.counts_size, dtype=torch.float64, device=dev)
-            if hi > lo:
+            mine = np.ascontiguousarray(columns[shard])
+            if len(mine):
                 torch.cuda.synchronize(dev)
-                w = None if weights is None else np.ascontiguousarray(weights[lo:hi], np.float64)
-                self.sp.columns(columns[lo:hi], w, counts=buf, col_loglike=False)
+                w = None if weights is None else np.ascontiguousarray(np.asarray(weights, np.float64)[shard])
+                self.sp.columns(mine, w, counts=buf, col_loglike=False)
             return buf
 
         def all_reduce(buf):

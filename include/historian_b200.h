@@ -154,6 +154,14 @@ int hist_ctx_fill_time_ms(hist_ctx* ctx, double* total_ms, int64_t* n_launches);
 /* ------------------------------------------------------------------ profiles */
 /* Replaces holding a `Profile` value on the host (profile.h:41-76). */
 int hist_profile_upload(hist_ctx* ctx, const hist_profile_desc* desc, hist_profile** out);
+/* Leaf profiles, Profile(components, alphabet, FastSeq, rowIndex) (profile.cpp:23-76), for a batch of n
+ * sequences, built on device: START -> residue 1 -> ... -> residue L -> END with log-weight 0 transitions;
+ * lpAbsorb of residue state pos+1 is 0 at its token and -inf elsewhere, or all 0 for a wildcard / invalid
+ * character (token < 0).  closest_leaf_pos of state i is min(i, L) (the seqCoords of the leaf row).
+ * tokens[k] points at lengths[k] tokens (Alphabet tokenize, fastseq.cpp:10-16).  Only the residues cross
+ * the bus, not the [L+2][C][A] table. */
+int hist_profile_from_sequences(hist_ctx* ctx, int32_t n, const int8_t* const* tokens, const int32_t* lengths,
+                                int32_t alph_size, int32_t components, hist_profile** out);
 void hist_profile_destroy(hist_profile* p);
 
 /* ------------------------------------------------------------------ DPMatrix

@@ -224,3 +224,24 @@ def test_errors_are_reported_not_thrown(ctx):
     with pytest.raises(capi.HistError) as e:
         pair.backward()  # BackwardMatrix needs a ForwardMatrix
     assert e.value.code == -4
+
+
+def test_leaf_profiles_built_on_device_match_uploaded_ones(ctx):
+    """hist_profile_from_sequences (Profile leaf constructor, profile.cpp:23-76) vs uploading the host-built
+    flattened profile: identical DPMatrix tables, cells and likelihoods; wildcards, invalid characters,
+    lower case, an empty sequence and ragged lengths."""
+    rng = np.random.default_rng(5)
+    alphabet = "arndcqeghilkmfpstwyv"
+    seqs = ["".join(rng.choice(list(alphabet), size=L)) for L in (37, 5, 64, 1, 20)] + ["ar*dXc", "ARND", ""]
+    dev = ctx.upload_sequences(seqs, alphabet, components=1)
+    hmm = synth.random_hmm(rng, 20, 1, tl=0.2, tr=0.3)
+    for a in range(0, len(seqs) - 1):
+        b = a + 1
+        hx, hy = D.Profile.from_sequence(seqs[a], alphabet, 1), D.Profile.from_sequence(seqs[b], alphabet, 1)
+        ux, uy = ctx.upload(hx), ctx.upload(hy)
+        p1, p2 = ctx.prepare(dev[a], dev[b], hmm), ctx.prepare(ux, uy, hmm)
+        l1, l2 = p1.forward(), p2.forward()
+        assert l1 == l2 or (np.isneginf(l1) and np.isneginf(l2))
+        assert H.same(p1.cells_dense(0), p2.cells_dense(0))
+        for t1, t2 in zip(p1.tables(), p2.tables()):
+            assert H.same(t1, t2)

@@ -1,0 +1,32 @@
+"""Where the end-to-end step of bench.py spends its time (host clock around each C-ABI stage)."""
+import sys, os, time
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+import bench
+from historian_b200 import capi
+
+lg, guide = bench.make_family(1)
+hmm, inputs = bench.cherry_inputs(lg, guide, 512)
+ctx = capi.Context(0)
+for it in range(3):
+    t0 = time.perf_counter()
+    pp = [(ctx.upload(x), ctx.upload(y)) for x, y, _ in inputs]
+    t1 = time.perf_counter()
+    pr = ctx.prepare_batch([a for a, _ in pp], [b for _, b in pp], hmm, [e for _, _, e in inputs], backward=True)
+    ctx.synchronize()
+    t2 = time.perf_counter()
+    r = ctx.fill_batch(pr, backward=True)
+    t3 = time.perf_counter()
+    for p in pr:
+        p.close()
+    for a, b in pp:
+        a.close(); b.close()
+    t4 = time.perf_counter()
+    print("upload %.1f ms  prepare %.1f ms  fill %.1f ms  close %.1f ms" % (1e3 * (t1 - t0), 1e3 * (t2 - t1), 1e3 * (t3 - t2), 1e3 * (t4 - t3)))
+import cProfile, pstats
+pr_ = cProfile.Profile()
+pr_.enable()
+pp = [(ctx.upload(x), ctx.upload(y)) for x, y, _ in inputs]
+pr = ctx.prepare_batch([a for a, _ in pp], [b for _, b in pp], hmm, [e for _, _, e in inputs], backward=True)
+pr_.disable()
+pstats.Stats(pr_).sort_stats("cumulative").print_stats(18)
