@@ -282,8 +282,6 @@ typedef struct {
 int hist_profile_eliminate(hist_pair* pair, const hist_cell* cells, int64_t n_cells, int32_t strategy,
                            hist_elim_result* result);
 
-/* Entry points below this line are declared for the next milestones and are not yet
- * exported by the library; they become part of the ABI as they are implemented. */
 /* ------------------------------------------------------------------ sum-product
  * SumProduct / AlignColSumProduct (sumprod.h:32-104, sumprod.cpp).
  * The model is passed in eigen-decomposed form (EigenModel, model.cpp:1135-1199):
