@@ -11,7 +11,7 @@ import numpy as np
 from . import descs as D
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libhistorian_b200.so")
+LIB_PATH = os.environ.get("HIST_B200_LIB") or os.path.join(_HERE, "libhistorian_b200.so")   # override: kernel tuning variants
 _lib = None
 
 

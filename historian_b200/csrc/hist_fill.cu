@@ -516,8 +516,17 @@ __device__ __forceinline__ void compute_store(const PairDev& P, const Ring& ring
 // guarded by named barriers (bar.arrive / bar.sync full/empty pairs).  Cells with more than one
 // in-/out-edge, null out-edges or predecessors older than the ring fall back to the generic cell
 // routine on the consumer ("slow" flag).
-#define HB_NPROD 2
+// measured on B200 (tools/ab_variants.sh): 1 producer + 128 registers (8 CTAs/SM: 1024 strips in ONE wave,
+// no spills) 3.27 ms; 2 producers + 96 registers (6 CTAs/SM, two waves, spills) 3.6 ms
+#ifndef HB_NPROD
+#define HB_NPROD 1
+#endif
+#ifndef HB_DEPTH
 #define HB_DEPTH 4
+#endif
+#ifndef HB_NARROW_REGS
+#define HB_NARROW_REGS (HB_NPROD == 1 ? 128 : 96)
+#endif
 enum { R_OK = 1, R_XEMIT = 2, R_YEMIT = 4, R_IMM_BY_X = 8, R_IMM_BY_Y = 16, R_ORIGIN = 32, R_SLOW = 64, R_BOTH = 128, R_TO_END = 256 };
 
 // shared-memory mbarriers (no per-SM limit, unlike named barriers): full[slot] counts the 32 lanes of
@@ -573,16 +582,24 @@ __device__ __forceinline__ void producer(const PairDev& P, const Ring& ring, int
   const int nD = P.n_diag;
   // layout records of diagonal d and of the two diagonals before it in sweep order, loaded one iteration ahead
   auto diag_of = [&](int q) { return min(max(BWD ? nD - 1 - q : q, 0), nD - 1); };
-  DiagInfo n0 = P.dinfo[diag_of(p)], n1 = P.dinfo[diag_of(p - 1)], n2 = P.dinfo[diag_of(p - 2)];
+  // Software pipeline, two iterations deep: the layout records (dinfo) of iteration q + 2*HB_NPROD and the
+  // per-lane state records / absorb value of iteration q + HB_NPROD are requested BEFORE iteration q is
+  // processed, so their L2/HBM latency overlaps the record construction and the wait for a free queue slot.
+  auto dq = [&](int q) { return BWD ? nD - 1 - q : q; };
+  DiagInfo c0 = P.dinfo[diag_of(p)], c1 = P.dinfo[diag_of(p - 1)], c2 = P.dinfo[diag_of(p - 2)];
+  DiagInfo n0 = P.dinfo[diag_of(p + HB_NPROD)], n1 = P.dinfo[diag_of(p + HB_NPROD - 1)], n2 = P.dinfo[diag_of(p + HB_NPROD - 2)];
+  LaneMeta<BWD> m = load_meta<BWD>(P, ring, c0, dq(p), t, true);
   for (int q = p; q < nD; q += HB_NPROD) {
     const int slot = q % HB_DEPTH;
-    const int d = BWD ? nD - 1 - q : q;
-    const DiagInfo di = n0;
-    const Recent rc = {n1.ilo, n1.width, n2.ilo, n2.width};
-    n0 = load_dinfo_early(P.dinfo + diag_of(q + HB_NPROD));
-    n1 = load_dinfo_early(P.dinfo + diag_of(q + HB_NPROD - 1));
-    n2 = load_dinfo_early(P.dinfo + diag_of(q + HB_NPROD - 2));
-    const LaneMeta<BWD> m = load_meta<BWD>(P, ring, di, d, t, true);
+    const int d = dq(q);
+    const DiagInfo di = c0;
+    const Recent rc = {c1.ilo, c1.width, c2.ilo, c2.width};
+    // requests for the next iteration (clamped to a valid diagonal past the end; then unused)
+    const LaneMeta<BWD> m_next = load_meta<BWD>(P, ring, n0, diag_of(q + HB_NPROD), t, true);
+    c0 = n0; c1 = n1; c2 = n2;
+    n0 = load_dinfo_early(P.dinfo + diag_of(q + 2 * HB_NPROD));
+    n1 = load_dinfo_early(P.dinfo + diag_of(q + 2 * HB_NPROD - 1));
+    n2 = load_dinfo_early(P.dinfo + diag_of(q + 2 * HB_NPROD - 2));
     // a near-start slot owns cells of near-end columns; then DPMatrix::inEnvelope (forward.h:92-98)
     const bool ok = m.ok && !(m.tail && m.xa.w >= 0) &&
                     (((m.xa.x | m.ya.x) & F_NEAR) || P.max_dist < 0 || hb_iabs(m.xa.z - m.ya.z) <= P.max_dist);
@@ -638,6 +655,7 @@ __device__ __forceinline__ void producer(const PairDev& P, const Ring& ring, int
     int4* R = rec + slot * 128;
     R[t] = r0; R[32 + t] = r1; R[64 + t] = r2; R[96 + t] = r3;
     mbar_arrive(full + slot);
+    m = m_next;
   }
 }
 
@@ -740,10 +758,13 @@ __device__ __forceinline__ void consumer(const PairDev& P, const Ring& ring, con
   const int nD = P.n_diag;
   const int t = threadIdx.x;
   Recent rc = {0, 0, 0, 0};
+  DiagInfo di_next = P.dinfo[BWD ? nD - 1 : 0];
   for (int q = 0; q < nD; ++q) {
     const int slot = q % HB_DEPTH;
     const int d = BWD ? nD - 1 - q : q;
-    const DiagInfo di = P.dinfo[d];
+    const DiagInfo di = di_next;
+    // layout record of the next diagonal, requested a whole step ahead of its use
+    di_next = load_dinfo_early(P.dinfo + (BWD ? max(d - 1, 0) : min(d + 1, nD - 1)));
     mbar_wait(full + slot, (q / HB_DEPTH) & 1);
     const int4* R = rec + slot * 128;
     const int4 r0 = R[t], r1 = R[32 + t], r2 = R[64 + t], r3 = R[96 + t];
@@ -873,7 +894,7 @@ __device__ __forceinline__ void fill_body(PairDev* const* __restrict__ pairs, in
 
 // one consumer + HB_NPROD producer warps per strip; requires blockDim.x == 32 * (1 + HB_NPROD),
 // ring_rows >= 4 and max_threads <= 32 for every pair; dynamic smem = ring + HB_DEPTH * 2 KB of records
-__global__ void __maxnreg__(HB_NPROD == 1 ? 144 : 96) fill_narrow_kernel(PairDev* const* __restrict__ pairs, int n_dir, int only_dir, int ring_cap, int ring_rows) {
+__global__ void __maxnreg__(HB_NARROW_REGS) fill_narrow_kernel(PairDev* const* __restrict__ pairs, int n_dir, int only_dir, int ring_cap, int ring_rows) {
   fill_body<true>(pairs, n_dir, only_dir, ring_cap, ring_rows);
 }
 __global__ void __launch_bounds__(512) fill_kernel(PairDev* const* __restrict__ pairs, int n_dir, int only_dir, int ring_cap, int ring_rows) {
