@@ -393,6 +393,81 @@ class Reconstructor:
         return path, lp_final, prof
 
 
+def merge_levels(tree):
+    """Internal nodes grouped by height above the leaves (level 0 = cherries).  The merges of one level
+    depend only on lower levels (recon.cpp:938-1033 is a postorder loop whose only dependencies are
+    child -> parent), so they are independent and can run side by side / on different GPUs."""
+    h = np.zeros(tree.n_nodes, int)
+    for v in range(tree.n_nodes):
+        if tree.children[v]:
+            h[v] = 1 + max(h[c] for c in tree.children[v])
+    levels = [[] for _ in range(int(h.max()))]
+    for v in range(tree.n_nodes):
+        if tree.children[v]:
+            levels[h[v] - 1].append(v)
+    return levels
+
+
+def level_owner(level_nodes, world):
+    """Round-robin placement of the merges of one level: {node: rank}."""
+    return {node: k % world for k, node in enumerate(level_nodes)}
+
+
+def run_levels(tree, leaf_value, merge_fn, rank=0, world=1, all_gather=None):
+    """Level-synchronous driver of the progressive reconstruction over `world` ranks (one process per GPU).
+
+    leaf_value(node) -> value of a leaf; merge_fn(node, left_value, right_value) -> value of an internal node.
+    Every rank computes the merges level_owner() assigns to it, then the level's results are exchanged with
+    all_gather(dict) -> list of dicts (torch.distributed.all_gather_object: the flattened profiles are host
+    objects of <= ~1 MB), so that every rank holds every profile of the finished level.
+    There is no collective on the data path of a merge.  Returns {node: value} (complete on every rank)."""
+    val = {v: leaf_value(v) for v in range(tree.n_nodes) if tree.is_leaf(v)}
+    for nodes in merge_levels(tree):
+        owner = level_owner(nodes, world)
+        mine = {}
+        for node in nodes:
+            if owner[node] == rank:
+                l, r = tree.children[node]
+                mine[node] = merge_fn(node, val[l], val[r])
+        if world > 1:
+            if all_gather is None:
+                raise ValueError("world > 1 needs an all_gather")
+            for part in all_gather(mine):
+                val.update(part)
+        else:
+            val.update(mine)
+    return val
+
+
+def reconstruct_distributed(rec, tree, seqs, guide=None, rank=0, world=1, all_gather=None):
+    """Reconstructor.reconstruct with the sibling merges of each guide-tree level spread over the ranks.
+
+    Sampled profiles draw from ONE mt19937 stream in node order in the reference (recon.cpp:38, forward.cpp:
+    257-276), which serialises the tree; here a multi-rank run is only allowed for the stream-free modes
+    (best-trace profiles: profile_samples == 0 or -profmaxstates 1; or posterior profiles, -profminpost), where the result is
+    identical to the single-stream run.  Returns (path, final log-likelihood, {node: HostProfile})."""
+    draws = rec.min_post_prob is None and rec.profile_samples > 0 and rec.max_profile_states != 1
+    if world > 1 and draws:  # max_profile_states == 1: the best trace alone fills the cell budget, no draw is made
+        raise ValueError("sampled profiles share one RNG stream in node order; use profile_samples=0 or min_post_prob for multi-GPU runs")
+    cl, _ = closest_leaves(tree)
+    mt_state = mt19937_seed(rec.seed)
+
+    def leaf_value(node):
+        return (HostProfile.leaf(seqs[node], rec.model.alphabet, rec.model.components, node, tree.names[node]), -np.inf, None)
+
+    def merge_fn(node, lv, rv):
+        l, r = tree.children[node]
+        keep = int(cl[node])
+        p, lp_end, pth = rec.merge(node, lv[0], rv[0], float(tree.branch_length[l]), float(tree.branch_length[r]), guide,
+                                   int(cl[l]), int(cl[r]), node == tree.root, mt_state)
+        p.leaf_rows = {keep: p.leaf_rows[keep]} if keep in p.leaf_rows else p.leaf_rows
+        return (p, lp_end, pth)
+
+    val = run_levels(tree, leaf_value, merge_fn, rank, world, all_gather)
+    p, lp_final, path = val[tree.root]
+    return path, lp_final, {node: v[0] for node, v in val.items()}
+
+
 def gapped_rows(path, tree, seqs, wildcard="*"):
     """Alignment(ungapped, path).gapped() (alignpath.cpp:232-280) with wildcard ancestors (recon.cpp:1410-1421)."""
     out = {}
