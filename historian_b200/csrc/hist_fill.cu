@@ -576,86 +576,102 @@ __device__ __forceinline__ DiagInfo load_dinfo_early(const DiagInfo* p) {
   return d;
 }
 
+// One diagonal's worth of producer work: turn the per-lane state records `m` of diagonal d (sweep step q) into
+// the 64-B consumer record and publish it in queue slot q % HB_DEPTH.
+template <bool BWD>
+__device__ __forceinline__ void produce_one(const PairDev& P, const Ring& ring, int4* rec, uint64_t* full, uint64_t* empty, int t, int q,
+                                            int d, const Recent rc, const LaneMeta<BWD>& m) {
+  const int slot = q % HB_DEPTH;
+  // a near-start slot owns cells of near-end columns; then DPMatrix::inEnvelope (forward.h:92-98)
+  const bool ok = m.ok && !(m.tail && m.xa.w >= 0) &&
+                  (((m.xa.x | m.ya.x) & F_NEAR) || P.max_dist < 0 || hb_iabs(m.xa.z - m.ya.z) <= P.max_dist);
+  const int i = m.i, j = m.j;
+  const unsigned fx = m.xa.x & 0xff, fy = m.ya.x & 0xff;
+  const bool xEmit = fx & F_EMIT, yEmit = fy & F_EMIT;
+  const bool xReady = fx & F_READY, yReady = fy & F_READY;
+  const bool xEmitOrStart = fx & F_EMIT_OR_START;
+  const bool both = xEmit && yEmit;
+  const float ab = ok && both ? m.ab : 0.f;
+  int4 r0, r1, r2, r3;
+  int flags = ok ? R_OK : 0;
+  if (!BWD) {
+    const int xc = (int)((unsigned)m.xa.x >> 8), yc = (int)((unsigned)m.ya.x >> 8);
+    const bool doX = ok && yReady && xc > 0;
+    const bool doY = ok && (yEmit ? xReady : true) && yc > 0;
+    const bool doD = ok && both && xc > 0 && yc > 0;
+    const int aX = pred_index<false>(P, ring, rc, d, doX, m.xb.x, j, m.xb.w, m.ya.w);
+    const int aY = pred_index<false>(P, ring, rc, d, doY, i, m.yb.x, m.xa.w, m.yb.w);
+    const int aD = pred_index<false>(P, ring, rc, d, doD, m.xb.x, m.yb.x, m.xb.w, m.yb.w);
+    if (xEmit) flags |= R_XEMIT;
+    if (yEmit) flags |= R_YEMIT;
+    if (!xEmit && !(!yEmit && xEmitOrStart)) flags |= R_IMM_BY_X;
+    if (!yEmit && xEmitOrStart) flags |= R_IMM_BY_Y;
+    if (i == 0 && j == 0) flags |= R_ORIGIN;
+    if (both) flags |= R_BOTH;
+    if (xc > 1 || yc > 1 || aX == -2 || aY == -2 || aD == -2) flags |= R_SLOW;
+    r0 = make_int4(aX, aY, aD, flags);
+    r1 = make_int4(m.xb.y, m.yb.y, m.xb.y + m.yb.y, i);
+    r2 = make_int4(m.xb.z, m.yb.z, __float_as_int(__int_as_float(m.xb.z) * __int_as_float(m.yb.z)), __float_as_int(ab));
+    const bool ex = xEmit && yReady, ey = yEmit && xReady;
+    r3 = make_int4(__float_as_int(ex ? m.xe.x : 1.f), __float_as_int(ex ? m.xe.y : 1.f), __float_as_int(ey ? m.ye.x : 1.f),
+                   __float_as_int(ey ? m.ye.y : 1.f));
+  } else {
+    const int xac = (int)((unsigned)m.xa.x >> 8), yac = (int)((unsigned)m.ya.x >> 8);
+    const bool doD = ok && xac > 0 && yac > 0;
+    const bool doX = ok && yReady && xac > 0;
+    const bool doY = ok && xReady && yac > 0;
+    const int aD = pred_index<true>(P, ring, rc, d, doD, m.x0.x, m.y0.x, m.x0.z, m.y0.z);
+    const int aX = pred_index<true>(P, ring, rc, d, doX, m.x0.x, j, m.x0.z, m.ya.w);
+    const int aY = pred_index<true>(P, ring, rc, d, doY, i, m.y0.x, m.xa.w, m.y0.z);
+    const bool toEnd = (fx & F_TO_END) && (fy & F_TO_END);
+    if (toEnd) flags |= R_TO_END;
+    const bool xNull = yReady && m.xb.y > ((fx & F_TO_END) ? 1 : 0);
+    const bool yNull = m.yb.y > ((fy & F_TO_END) ? 1 : 0);
+    if (xac > 1 || yac > 1 || xNull || yNull || aX == -2 || aY == -2 || aD == -2) flags |= R_SLOW;
+    r0 = make_int4(aD, aX, aY, flags);
+    r1 = make_int4(m.x0.y + m.y0.y, m.x0.y, m.y0.y, i);
+    r2 = make_int4(__float_as_int(__int_as_float(m.x1.x) * __int_as_float(m.y1.x)), m.x1.y, m.x1.z, __float_as_int(ab));
+    r3 = make_int4(m.y1.y, m.y1.z, m.xb.z + m.yb.z, __float_as_int(__int_as_float(m.xb.w) * __int_as_float(m.yb.w)));
+  }
+  if (q >= HB_DEPTH) mbar_wait(empty + slot, ((q / HB_DEPTH) - 1) & 1);
+  int4* R = rec + slot * 128;
+  R[t] = r0; R[32 + t] = r1; R[64 + t] = r2; R[96 + t] = r3;
+  mbar_arrive(full + slot);
+}
+
 template <bool BWD>
 __device__ __forceinline__ void producer(const PairDev& P, const Ring& ring, int4* rec, uint64_t* full, uint64_t* empty, int p) {
   const int t = threadIdx.x & 31;
   const int nD = P.n_diag;
-  // layout records of diagonal d and of the two diagonals before it in sweep order, loaded one iteration ahead
   auto diag_of = [&](int q) { return min(max(BWD ? nD - 1 - q : q, 0), nD - 1); };
-  // Software pipeline, two iterations deep: the layout records (dinfo) of iteration q + 2*HB_NPROD and the
-  // per-lane state records / absorb value of iteration q + HB_NPROD are requested BEFORE iteration q is
-  // processed, so their L2/HBM latency overlaps the record construction and the wait for a free queue slot.
   auto dq = [&](int q) { return BWD ? nD - 1 - q : q; };
+  // Software pipeline: the layout records (dinfo) are requested two iterations ahead and the per-lane state
+  // records / absorb value one iteration ahead of their use, so their L2/HBM latency overlaps the record
+  // construction and the wait for a free queue slot.  The loop is unrolled by two over two named buffers
+  // (mA, mB): rotating one buffer through a register copy would make the copy wait for the loads.
   DiagInfo c0 = P.dinfo[diag_of(p)], c1 = P.dinfo[diag_of(p - 1)], c2 = P.dinfo[diag_of(p - 2)];
   DiagInfo n0 = P.dinfo[diag_of(p + HB_NPROD)], n1 = P.dinfo[diag_of(p + HB_NPROD - 1)], n2 = P.dinfo[diag_of(p + HB_NPROD - 2)];
-  LaneMeta<BWD> m = load_meta<BWD>(P, ring, c0, dq(p), t, true);
-  for (int q = p; q < nD; q += HB_NPROD) {
-    const int slot = q % HB_DEPTH;
-    const int d = dq(q);
-    const DiagInfo di = c0;
-    const Recent rc = {c1.ilo, c1.width, c2.ilo, c2.width};
-    // requests for the next iteration (clamped to a valid diagonal past the end; then unused)
-    const LaneMeta<BWD> m_next = load_meta<BWD>(P, ring, n0, diag_of(q + HB_NPROD), t, true);
-    c0 = n0; c1 = n1; c2 = n2;
-    n0 = load_dinfo_early(P.dinfo + diag_of(q + 2 * HB_NPROD));
-    n1 = load_dinfo_early(P.dinfo + diag_of(q + 2 * HB_NPROD - 1));
-    n2 = load_dinfo_early(P.dinfo + diag_of(q + 2 * HB_NPROD - 2));
-    // a near-start slot owns cells of near-end columns; then DPMatrix::inEnvelope (forward.h:92-98)
-    const bool ok = m.ok && !(m.tail && m.xa.w >= 0) &&
-                    (((m.xa.x | m.ya.x) & F_NEAR) || P.max_dist < 0 || hb_iabs(m.xa.z - m.ya.z) <= P.max_dist);
-    const int i = m.i, j = m.j;
-    const unsigned fx = m.xa.x & 0xff, fy = m.ya.x & 0xff;
-    const bool xEmit = fx & F_EMIT, yEmit = fy & F_EMIT;
-    const bool xReady = fx & F_READY, yReady = fy & F_READY;
-    const bool xEmitOrStart = fx & F_EMIT_OR_START;
-    const bool both = xEmit && yEmit;
-    const float ab = ok && both ? m.ab : 0.f;
-    int4 r0, r1, r2, r3;
-    int flags = ok ? R_OK : 0;
-    if (!BWD) {
-      const int xc = (int)((unsigned)m.xa.x >> 8), yc = (int)((unsigned)m.ya.x >> 8);
-      const bool doX = ok && yReady && xc > 0;
-      const bool doY = ok && (yEmit ? xReady : true) && yc > 0;
-      const bool doD = ok && both && xc > 0 && yc > 0;
-      const int aX = pred_index<false>(P, ring, rc, d, doX, m.xb.x, j, m.xb.w, m.ya.w);
-      const int aY = pred_index<false>(P, ring, rc, d, doY, i, m.yb.x, m.xa.w, m.yb.w);
-      const int aD = pred_index<false>(P, ring, rc, d, doD, m.xb.x, m.yb.x, m.xb.w, m.yb.w);
-      if (xEmit) flags |= R_XEMIT;
-      if (yEmit) flags |= R_YEMIT;
-      if (!xEmit && !(!yEmit && xEmitOrStart)) flags |= R_IMM_BY_X;
-      if (!yEmit && xEmitOrStart) flags |= R_IMM_BY_Y;
-      if (i == 0 && j == 0) flags |= R_ORIGIN;
-      if (both) flags |= R_BOTH;
-      if (xc > 1 || yc > 1 || aX == -2 || aY == -2 || aD == -2) flags |= R_SLOW;
-      r0 = make_int4(aX, aY, aD, flags);
-      r1 = make_int4(m.xb.y, m.yb.y, m.xb.y + m.yb.y, i);
-      r2 = make_int4(m.xb.z, m.yb.z, __float_as_int(__int_as_float(m.xb.z) * __int_as_float(m.yb.z)), __float_as_int(ab));
-      const bool ex = xEmit && yReady, ey = yEmit && xReady;
-      r3 = make_int4(__float_as_int(ex ? m.xe.x : 1.f), __float_as_int(ex ? m.xe.y : 1.f), __float_as_int(ey ? m.ye.x : 1.f),
-                     __float_as_int(ey ? m.ye.y : 1.f));
-    } else {
-      const int xac = (int)((unsigned)m.xa.x >> 8), yac = (int)((unsigned)m.ya.x >> 8);
-      const bool doD = ok && xac > 0 && yac > 0;
-      const bool doX = ok && yReady && xac > 0;
-      const bool doY = ok && xReady && yac > 0;
-      const int aD = pred_index<true>(P, ring, rc, d, doD, m.x0.x, m.y0.x, m.x0.z, m.y0.z);
-      const int aX = pred_index<true>(P, ring, rc, d, doX, m.x0.x, j, m.x0.z, m.ya.w);
-      const int aY = pred_index<true>(P, ring, rc, d, doY, i, m.y0.x, m.xa.w, m.y0.z);
-      const bool toEnd = (fx & F_TO_END) && (fy & F_TO_END);
-      if (toEnd) flags |= R_TO_END;
-      const bool xNull = yReady && m.xb.y > ((fx & F_TO_END) ? 1 : 0);
-      const bool yNull = m.yb.y > ((fy & F_TO_END) ? 1 : 0);
-      if (xac > 1 || yac > 1 || xNull || yNull || aX == -2 || aY == -2 || aD == -2) flags |= R_SLOW;
-      r0 = make_int4(aD, aX, aY, flags);
-      r1 = make_int4(m.x0.y + m.y0.y, m.x0.y, m.y0.y, i);
-      r2 = make_int4(__float_as_int(__int_as_float(m.x1.x) * __int_as_float(m.y1.x)), m.x1.y, m.x1.z, __float_as_int(ab));
-      r3 = make_int4(m.y1.y, m.y1.z, m.xb.z + m.yb.z, __float_as_int(__int_as_float(m.xb.w) * __int_as_float(m.yb.w)));
+  LaneMeta<BWD> mA = load_meta<BWD>(P, ring, c0, dq(p), t, true), mB;
+  for (int q = p; q < nD; q += 2 * HB_NPROD) {
+    {
+      const Recent rc = {c1.ilo, c1.width, c2.ilo, c2.width};
+      mB = load_meta<BWD>(P, ring, n0, diag_of(q + HB_NPROD), t, true);   // clamped past the end; then unused
+      c0 = n0; c1 = n1; c2 = n2;
+      n0 = load_dinfo_early(P.dinfo + diag_of(q + 2 * HB_NPROD));
+      n1 = load_dinfo_early(P.dinfo + diag_of(q + 2 * HB_NPROD - 1));
+      n2 = load_dinfo_early(P.dinfo + diag_of(q + 2 * HB_NPROD - 2));
+      produce_one<BWD>(P, ring, rec, full, empty, t, q, dq(q), rc, mA);
     }
-    if (q >= HB_DEPTH) mbar_wait(empty + slot, ((q / HB_DEPTH) - 1) & 1);
-    int4* R = rec + slot * 128;
-    R[t] = r0; R[32 + t] = r1; R[64 + t] = r2; R[96 + t] = r3;
-    mbar_arrive(full + slot);
-    m = m_next;
+    if (q + HB_NPROD >= nD) break;
+    {
+      const Recent rc = {c1.ilo, c1.width, c2.ilo, c2.width};
+      mA = load_meta<BWD>(P, ring, n0, diag_of(q + 2 * HB_NPROD), t, true);
+      c0 = n0; c1 = n1; c2 = n2;
+      n0 = load_dinfo_early(P.dinfo + diag_of(q + 3 * HB_NPROD));
+      n1 = load_dinfo_early(P.dinfo + diag_of(q + 3 * HB_NPROD - 1));
+      n2 = load_dinfo_early(P.dinfo + diag_of(q + 3 * HB_NPROD - 2));
+      produce_one<BWD>(P, ring, rec, full, empty, t, q + HB_NPROD, dq(q + HB_NPROD), rc, mB);
+    }
   }
 }
 
