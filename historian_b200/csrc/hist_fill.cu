@@ -17,6 +17,8 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
+#include <cstring>
 #include <vector>
 
 #include "hist_internal.cuh"
@@ -465,14 +467,16 @@ __device__ __forceinline__ LaneMeta<BWD> load_meta(const PairDev& P, const Ring&
   ok = ok && i >= 0 && j >= 0 && i <= P.x.n - 2 && j <= P.y.n - 2;
   if (!ok) i = j = 0;
   m.i = i; m.j = j; m.ok = ok;
+  // whole 16-B records through the read-only path: one LDG.128 each (plain struct copies get split into
+  // 4/8-byte loads of the fields in use, several times the L1 wavefronts)
   if (BWD) {
     const int4* xm = P.x.bm + 4 * i;
     const int4* ym = P.y.bm + 4 * j;
-    m.xa = xm[0]; m.xb = xm[1]; m.x0 = xm[2]; m.x1 = xm[3];
-    m.ya = ym[0]; m.yb = ym[1]; m.y0 = ym[2]; m.y1 = ym[3];
+    m.xa = __ldg(xm); m.xb = __ldg(xm + 1); m.x0 = __ldg(xm + 2); m.x1 = __ldg(xm + 3);
+    m.ya = __ldg(ym); m.yb = __ldg(ym + 1); m.y0 = __ldg(ym + 2); m.y1 = __ldg(ym + 3);
   } else {
-    m.xa = P.x.fm_a[i]; m.xb = P.x.fm_b[i]; m.xe = P.x.emis[i];
-    m.ya = P.y.fm_a[j]; m.yb = P.y.fm_b[j]; m.ye = P.y.emis[j];
+    m.xa = __ldg(P.x.fm_a + i); m.xb = __ldg(P.x.fm_b + i); m.xe = __ldg(P.x.emis + i);
+    m.ya = __ldg(P.y.fm_a + j); m.yb = __ldg(P.y.fm_b + j); m.ye = __ldg(P.y.emis + j);
   }
   m.ab = ok && with_ab ? __ldcs(P.absorb + di.off + t) : 0.f;
   return m;
@@ -576,12 +580,12 @@ __device__ __forceinline__ DiagInfo load_dinfo_early(const DiagInfo* p) {
   return d;
 }
 
-// One diagonal's worth of producer work: turn the per-lane state records `m` of diagonal d (sweep step q) into
-// the 64-B consumer record and publish it in queue slot q % HB_DEPTH.
+// Everything about one cell that does not depend on earlier cells, as the 64-B record (r0..r3) the consumer
+// works from: ring addresses of its predecessors, flags, transition exponents / mantissas, emission factors,
+// absorb value.  `m`: the per-lane state records of diagonal d.
 template <bool BWD>
-__device__ __forceinline__ void produce_one(const PairDev& P, const Ring& ring, int4* rec, uint64_t* full, uint64_t* empty, int t, int q,
-                                            int d, const Recent rc, const LaneMeta<BWD>& m) {
-  const int slot = q % HB_DEPTH;
+__device__ __forceinline__ void make_record(const PairDev& P, const Ring& ring, int d, const Recent rc, const LaneMeta<BWD>& m, int4& r0,
+                                            int4& r1, int4& r2, int4& r3) {
   // a near-start slot owns cells of near-end columns; then DPMatrix::inEnvelope (forward.h:92-98)
   const bool ok = m.ok && !(m.tail && m.xa.w >= 0) &&
                   (((m.xa.x | m.ya.x) & F_NEAR) || P.max_dist < 0 || hb_iabs(m.xa.z - m.ya.z) <= P.max_dist);
@@ -592,7 +596,6 @@ __device__ __forceinline__ void produce_one(const PairDev& P, const Ring& ring, 
   const bool xEmitOrStart = fx & F_EMIT_OR_START;
   const bool both = xEmit && yEmit;
   const float ab = ok && both ? m.ab : 0.f;
-  int4 r0, r1, r2, r3;
   int flags = ok ? R_OK : 0;
   if (!BWD) {
     const int xc = (int)((unsigned)m.xa.x >> 8), yc = (int)((unsigned)m.ya.x >> 8);
@@ -633,6 +636,14 @@ __device__ __forceinline__ void produce_one(const PairDev& P, const Ring& ring, 
     r2 = make_int4(__float_as_int(__int_as_float(m.x1.x) * __int_as_float(m.y1.x)), m.x1.y, m.x1.z, __float_as_int(ab));
     r3 = make_int4(m.y1.y, m.y1.z, m.xb.z + m.yb.z, __float_as_int(__int_as_float(m.xb.w) * __int_as_float(m.yb.w)));
   }
+}
+
+template <bool BWD>
+__device__ __forceinline__ void produce_one(const PairDev& P, const Ring& ring, int4* rec, uint64_t* full, uint64_t* empty, int t, int q,
+                                            int d, const Recent rc, const LaneMeta<BWD>& m) {
+  const int slot = q % HB_DEPTH;
+  int4 r0, r1, r2, r3;
+  make_record<BWD>(P, ring, d, rc, m, r0, r1, r2, r3);
   if (q >= HB_DEPTH) mbar_wait(empty + slot, ((q / HB_DEPTH) - 1) & 1);
   int4* R = rec + slot * 128;
   R[t] = r0; R[32 + t] = r1; R[64 + t] = r2; R[96 + t] = r3;
@@ -683,8 +694,20 @@ __device__ __forceinline__ bool ring_read(const Ring& ring, int idx, float4& a, 
 }
 
 // Forward cell from a producer record (same arithmetic as the first-edge part of forward_cell)
-__device__ __forceinline__ Cell forward_fast(const PairDev& P, const Ring& ring, const int4 r0, const int4 r1, const int4 r2, const int4 r3) {
-  const float (*W)[6] = P.W;
+// The 5x6 transition weights held in registers for the whole sweep (the shared-memory copy in PairDev would be
+// re-read every step: the barrier waits are compiler memory barriers).
+struct WReg { float w[5][6]; };
+__device__ __forceinline__ WReg load_weights(const PairDev& P) {
+  WReg r;
+#pragma unroll
+  for (int a = 0; a < 5; ++a)
+#pragma unroll
+    for (int b = 0; b < 6; ++b) r.w[a][b] = P.W[a][b];
+  return r;
+}
+
+__device__ __forceinline__ Cell forward_fast(const WReg& WR, const Ring& ring, const int4 r0, const int4 r1, const int4 r2, const int4 r3) {
+  const float (*W)[6] = WR.w;
   const int flags = r0.w;
   float4 xA, xB, yA, yB, dA, dB;
   const bool vX = ring_read(ring, r0.x, xA, xB);
@@ -731,8 +754,8 @@ __device__ __forceinline__ Cell forward_fast(const PairDev& P, const Ring& ring,
   return a;
 }
 
-__device__ __forceinline__ Cell backward_fast(const PairDev& P, const Ring& ring, const int4 r0, const int4 r1, const int4 r2, const int4 r3) {
-  const float (*W)[6] = P.W;
+__device__ __forceinline__ Cell backward_fast(const WReg& WR, const Ring& ring, const int4 r0, const int4 r1, const int4 r2, const int4 r3) {
+  const float (*W)[6] = WR.w;
   const int flags = r0.w;
   float4 dA, dB, xA, xB, yA, yB;
   const bool vD = ring_read(ring, r0.x, dA, dB);
@@ -767,6 +790,26 @@ __device__ __noinline__ Cell generic_cell(const PairDev& P, const Ring& ring, co
   return forward_cell(P, ring, rc, d, m.i, m.j, m.xa, m.xb, m.xe, m.ya, m.yb, m.ye, ab);
 }
 
+// One cell of the consumer: arithmetic from the record, store to HBM (streaming) and to the ring.
+template <bool BWD>
+__device__ __forceinline__ void consume_store(const PairDev& P, const WReg& WR, const Ring& ring, const Recent& rc, const DiagInfo& di, int d, int t,
+                                              const int4 r0, const int4 r1, const int4 r2, const int4 r3, float4* gA, float2* gB) {
+  Cell c = zero_cell();
+  float aux = 0.f;
+  if (r0.w & R_OK) {
+    const float ab = __int_as_float(r2.w);
+    if (r0.w & R_SLOW) c = generic_cell<BWD>(P, ring, rc, di, d, t, ab);
+    else c = BWD ? backward_fast(WR, ring, r0, r1, r2, r3) : forward_fast(WR, ring, r0, r1, r2, r3);
+    if (BWD) aux = c.v[0] * ab;  // absorb is 0 unless both states emit
+  }
+  const float4 va = make_float4(c.v[0], c.v[1], c.v[2], c.v[3]);
+  __stcs(gA + di.off + t, va);
+  __stcs(gB + di.off + t, make_float2(c.v[4], __int_as_float(c.E)));
+  const int r = (d & (ring.R - 1)) * ring.cap + t;
+  ring.A[r] = va;
+  ring.B[r] = make_float4(c.v[4], __int_as_float(c.E), aux, 0.f);
+}
+
 template <bool BWD>
 __device__ __forceinline__ void consumer(const PairDev& P, const Ring& ring, const int4* rec, uint64_t* full, uint64_t* empty) {
   float4* gA = BWD ? P.bA : P.fA;
@@ -774,6 +817,7 @@ __device__ __forceinline__ void consumer(const PairDev& P, const Ring& ring, con
   const int nD = P.n_diag;
   const int t = threadIdx.x;
   Recent rc = {0, 0, 0, 0};
+  const WReg WR = load_weights(P);
   DiagInfo di_next = P.dinfo[BWD ? nD - 1 : 0];
   for (int q = 0; q < nD; ++q) {
     const int slot = q % HB_DEPTH;
@@ -786,22 +830,7 @@ __device__ __forceinline__ void consumer(const PairDev& P, const Ring& ring, con
     const int4 r0 = R[t], r1 = R[32 + t], r2 = R[64 + t], r3 = R[96 + t];
     mbar_arrive(empty + slot);
     if (t == 0) ring.info[d & (ring.R - 1)] = make_int4(di.ilo, di.width, (int)di.off, 0);
-    if (t < P.nS + di.width + P.nE) {
-      Cell c = zero_cell();
-      float aux = 0.f;
-      if (r0.w & R_OK) {
-        const float ab = __int_as_float(r2.w);
-        if (r0.w & R_SLOW) c = generic_cell<BWD>(P, ring, rc, di, d, t, ab);
-        else c = BWD ? backward_fast(P, ring, r0, r1, r2, r3) : forward_fast(P, ring, r0, r1, r2, r3);
-        if (BWD) aux = c.v[0] * ab;  // absorb is 0 unless both states emit
-      }
-      const float4 va = make_float4(c.v[0], c.v[1], c.v[2], c.v[3]);
-      __stcs(gA + di.off + t, va);
-      __stcs(gB + di.off + t, make_float2(c.v[4], __int_as_float(c.E)));
-      const int r = (d & (ring.R - 1)) * ring.cap + t;
-      ring.A[r] = va;
-      ring.B[r] = make_float4(c.v[4], __int_as_float(c.E), aux, 0.f);
-    }
+    if (t < P.nS + di.width + P.nE) consume_store<BWD>(P, WR, ring, rc, di, d, t, r0, r1, r2, r3, gA, gB);
     __syncwarp();
     rc.ilo2 = rc.ilo1; rc.w2 = rc.w1;
     rc.ilo1 = di.ilo; rc.w1 = di.width;
@@ -812,6 +841,137 @@ template <bool BWD>
 __device__ __forceinline__ void sweep_narrow(const PairDev& P, const Ring& ring, int4* rec, uint64_t* full, uint64_t* empty) {
   if (threadIdx.x < 32) consumer<BWD>(P, ring, rec, full, empty);
   else producer<BWD>(P, ring, rec, full, empty, (threadIdx.x >> 5) - 1);
+}
+
+// ------------------------------------------------------------------ narrow strips, streamed records
+// The producer's work depends on no DP value, so it does not have to ride along the wavefront at all:
+// build_records_kernel computes the 64-B record of EVERY stored cell of a batch in one massively parallel,
+// bandwidth-bound pass (one warp per anti-diagonal), laid out per diagonal as four planes of cnt = nS +
+// width + nE int4's (one contiguous block of 64 * cnt bytes at 64 * off[d]).  fill_stream_kernel is then
+// the consumer alone -- ONE warp per strip -- whose lane 0 streams the diagonals' blocks into a
+// shared-memory queue with bulk async copies (cp.async.bulk + mbarrier complete_tx) HB_SDEPTH diagonals
+// ahead of their use.  The dependent instruction stream of a step is the arithmetic and nothing else, and a
+// strip costs 32 threads instead of 64-96, so a whole level of sibling merges is resident at once.
+#define HB_SDEPTH 8
+#define HB_BUILD_WARPS 8
+#define HB_BUILD_DIAGS 8   // diagonals per warp
+
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, unsigned bytes) {
+  asm volatile("{\n .reg .b64 st;\n mbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n}" ::"r"((unsigned)__cvta_generic_to_shared(bar)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   (unsigned)__cvta_generic_to_shared(dst)),
+               "l"(src), "r"(bytes), "r"((unsigned)__cvta_generic_to_shared(bar))
+               : "memory");
+}
+
+// Copies the PairDev descriptor and the edge-slot lists of this CTA's pair into shared memory.
+__device__ __forceinline__ void stage_pair(const PairDev* src, PairDev& P, int* edge_rows, int* edge_cols) {
+  const int* s = reinterpret_cast<const int*>(src);
+  int* dptr = reinterpret_cast<int*>(&P);
+  for (int k = threadIdx.x; k < (int)(sizeof(PairDev) / sizeof(int)); k += blockDim.x) dptr[k] = s[k];
+  __syncthreads();
+  for (int k = threadIdx.x; k < P.nS && k < 32; k += blockDim.x) edge_rows[k] = P.start_rows[k];
+  for (int k = threadIdx.x; k < P.nE && k < 32; k += blockDim.x) edge_cols[k] = P.end_cols[k];
+  __syncthreads();
+}
+
+template <bool BWD>
+__device__ __forceinline__ void build_records(const PairDev& P, const Ring& ring, int4* __restrict__ out, int q0, int q1) {
+  const int t = threadIdx.x & 31;
+  const int nD = P.n_diag;
+  auto diag_of = [&](int q) { return min(max(BWD ? nD - 1 - q : q, 0), nD - 1); };
+  for (int q = q0; q < q1; ++q) {
+    const int d = BWD ? nD - 1 - q : q;
+    const DiagInfo di = P.dinfo[d], c1 = P.dinfo[diag_of(q - 1)], c2 = P.dinfo[diag_of(q - 2)];
+    const Recent rc = {c1.ilo, c1.width, c2.ilo, c2.width};
+    const int cnt = P.nS + di.width + P.nE;
+    const LaneMeta<BWD> m = load_meta<BWD>(P, ring, di, d, t, true);
+    int4 r0, r1, r2, r3;
+    make_record<BWD>(P, ring, d, rc, m, r0, r1, r2, r3);
+    if (t < cnt) {
+      int4* o = out + (size_t)di.off * 4 + t;
+      __stcs(o, r0);
+      __stcs(o + cnt, r1);
+      __stcs(o + 2 * cnt, r2);
+      __stcs(o + 3 * cnt, r3);
+    }
+  }
+}
+
+// grid = (diagonal chunks, pairs * n_dir); recs[b] = record buffer of (pair, direction) b
+__global__ void __launch_bounds__(32 * HB_BUILD_WARPS) build_records_kernel(PairDev* const* __restrict__ pairs, int4* const* __restrict__ recs,
+                                                                           int n_dir, int only_dir, int ring_cap, int ring_rows) {
+  __shared__ PairDev P;
+  __shared__ int edge_rows[32], edge_cols[32];
+  stage_pair(pairs[blockIdx.y / n_dir], P, edge_rows, edge_cols);
+  const bool bwd = n_dir == 2 ? (blockIdx.y % n_dir) == 1 : only_dir == 1;
+  Ring ring;
+  ring.cap = ring_cap; ring.R = ring_rows;
+  ring.A = nullptr; ring.B = nullptr; ring.info = nullptr;
+  ring.srows = edge_rows; ring.ecols = edge_cols;
+  const int q0 = (blockIdx.x * HB_BUILD_WARPS + (threadIdx.x >> 5)) * HB_BUILD_DIAGS;
+  const int q1 = min(q0 + HB_BUILD_DIAGS, P.n_diag);
+  if (q0 >= q1) return;
+  if (bwd) build_records<true>(P, ring, recs[blockIdx.y], q0, q1); else build_records<false>(P, ring, recs[blockIdx.y], q0, q1);
+}
+
+template <bool BWD>
+__device__ __forceinline__ void consumer_stream(const PairDev& P, const Ring& ring, const int4* __restrict__ recs, int4* queue, uint64_t* full) {
+  float4* gA = BWD ? P.bA : P.fA;
+  float2* gB = BWD ? P.bB : P.fB;
+  const int nD = P.n_diag;
+  const int t = threadIdx.x;
+  const int nEdge = P.nS + P.nE;
+  auto diag_at = [&](int q) { return min(max(BWD ? nD - 1 - q : q, 0), nD - 1); };
+  // lane 0: request the record block of sweep step q into queue slot q % HB_SDEPTH
+  auto issue = [&](int q, const DiagInfo& dj) {
+    const int slot = q % HB_SDEPTH;
+    const unsigned bytes = 64u * (unsigned)(nEdge + dj.width);
+    if (bytes) {
+      mbar_expect_tx(full + slot, bytes);
+      bulk_g2s(queue + slot * 128, recs + (size_t)dj.off * 4, bytes, full + slot);
+    } else {
+      mbar_arrive(full + slot);
+    }
+  };
+  if (t == 0)
+    for (int q = 0; q < HB_SDEPTH && q < nD; ++q) issue(q, P.dinfo[diag_at(q)]);
+  Recent rc = {0, 0, 0, 0};
+  const WReg WR = load_weights(P);
+  // layout records: of this step's diagonal (di) and of the diagonal requested at the end of this step (dj),
+  // both loaded two steps ahead of their use
+  DiagInfo di_n1 = P.dinfo[diag_at(0)], di_n2 = P.dinfo[diag_at(1)];
+  DiagInfo dj_n1 = P.dinfo[diag_at(HB_SDEPTH)], dj_n2 = P.dinfo[diag_at(HB_SDEPTH + 1)];
+  for (int q = 0; q < nD; ++q) {
+    const int slot = q % HB_SDEPTH;
+    const int d = BWD ? nD - 1 - q : q;
+    const DiagInfo di = di_n1, dj = dj_n1;
+    di_n1 = di_n2; dj_n1 = dj_n2;
+    di_n2 = load_dinfo_early(P.dinfo + diag_at(q + 2));
+    dj_n2 = load_dinfo_early(P.dinfo + diag_at(q + 2 + HB_SDEPTH));
+    const int cnt = nEdge + di.width;
+    mbar_wait(full + slot, (q / HB_SDEPTH) & 1);
+    const int4* R = queue + slot * 128;
+    int4 r0 = make_int4(0, 0, 0, 0), r1 = r0, r2 = r0, r3 = r0;
+    if (t < cnt) { r0 = R[t]; r1 = R[cnt + t]; r2 = R[2 * cnt + t]; r3 = R[3 * cnt + t]; }
+    __syncwarp();
+    if (t == 0) {
+      ring.info[d & (ring.R - 1)] = make_int4(di.ilo, di.width, (int)di.off, 0);
+      if (q + HB_SDEPTH < nD) {
+        // the slot has been read by every lane; order those generic-proxy reads before the async-proxy write
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        issue(q + HB_SDEPTH, dj);
+      }
+    }
+    if (t < cnt) consume_store<BWD>(P, WR, ring, rc, di, d, t, r0, r1, r2, r3, gA, gB);
+    __syncwarp();
+    rc.ilo2 = rc.ilo1; rc.w2 = rc.w1;
+    rc.ilo1 = di.ilo; rc.w1 = di.width;
+  }
 }
 
 // General strips: a CTA of several warps, each thread looping over the slots of the diagonal.
@@ -837,13 +997,18 @@ __device__ __forceinline__ void sweep_wide(const PairDev& P, const Ring& ring) {
 
 // grid.x = n_pairs * n_dir; block b handles pair b / n_dir, direction (b % n_dir) (0 = Forward, 1 = Backward;
 // with n_dir == 1 the direction is `only_dir`).
-template <bool NARROW>
-__device__ __forceinline__ void fill_body(PairDev* const* __restrict__ pairs, int n_dir, int only_dir, int ring_cap, int ring_rows) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
+// MODE 0: general strips (CTA-wide sweep); 1: narrow strips, producer/consumer warps; 2: narrow strips, streamed records
+template <int MODE>
+__device__ __forceinline__ void fill_body(PairDev* const* __restrict__ pairs, int n_dir, int only_dir, int ring_cap, int ring_rows,
+                                          int4* const* __restrict__ recs = nullptr) {
+  constexpr bool NARROW = MODE != 0;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ PairDev P;
   __shared__ int4 ring_info[HB_RING_MAX];
-  __shared__ uint64_t mbar[2 * HB_DEPTH];
-  if (NARROW && threadIdx.x < 2 * HB_DEPTH) mbar_init(mbar + threadIdx.x, 32);
+  __shared__ uint64_t mbar[2 * HB_DEPTH > HB_SDEPTH ? 2 * HB_DEPTH : HB_SDEPTH];
+  if (MODE == 1 && threadIdx.x < 2 * HB_DEPTH) mbar_init(mbar + threadIdx.x, 32);
+  if (MODE == 2 && threadIdx.x < HB_SDEPTH) mbar_init(mbar + threadIdx.x, 1);
+  if (MODE == 2) asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   {
     const PairDev* src = pairs[blockIdx.x / n_dir];
     const int* s = reinterpret_cast<const int*>(src);
@@ -868,7 +1033,10 @@ __device__ __forceinline__ void fill_body(PairDev* const* __restrict__ pairs, in
     ring.ecols = edge_cols;
     __syncthreads();
   }
-  if (NARROW) {
+  if (MODE == 2) {
+    int4* queue = reinterpret_cast<int4*>(ring.B + (size_t)ring_rows * ring_cap);
+    if (bwd) consumer_stream<true>(P, ring, recs[blockIdx.x], queue, mbar); else consumer_stream<false>(P, ring, recs[blockIdx.x], queue, mbar);
+  } else if (MODE == 1) {
     int4* rec = reinterpret_cast<int4*>(ring.B + (size_t)ring_rows * ring_cap);
     if (bwd) sweep_narrow<true>(P, ring, rec, mbar, mbar + HB_DEPTH); else sweep_narrow<false>(P, ring, rec, mbar, mbar + HB_DEPTH);
   } else {
@@ -911,10 +1079,15 @@ __device__ __forceinline__ void fill_body(PairDev* const* __restrict__ pairs, in
 // one consumer + HB_NPROD producer warps per strip; requires blockDim.x == 32 * (1 + HB_NPROD),
 // ring_rows >= 4 and max_threads <= 32 for every pair; dynamic smem = ring + HB_DEPTH * 2 KB of records
 __global__ void __maxnreg__(HB_NARROW_REGS) fill_narrow_kernel(PairDev* const* __restrict__ pairs, int n_dir, int only_dir, int ring_cap, int ring_rows) {
-  fill_body<true>(pairs, n_dir, only_dir, ring_cap, ring_rows);
+  fill_body<1>(pairs, n_dir, only_dir, ring_cap, ring_rows);
+}
+// one warp per strip; dynamic smem = ring + HB_SDEPTH * 2 KB of record blocks; recs[blockIdx.x] built by build_records_kernel
+__global__ void __launch_bounds__(32) fill_stream_kernel(PairDev* const* __restrict__ pairs, int4* const* __restrict__ recs, int n_dir, int only_dir,
+                                                         int ring_cap, int ring_rows) {
+  fill_body<2>(pairs, n_dir, only_dir, ring_cap, ring_rows, recs);
 }
 __global__ void __launch_bounds__(512) fill_kernel(PairDev* const* __restrict__ pairs, int n_dir, int only_dir, int ring_cap, int ring_rows) {
-  fill_body<false>(pairs, n_dir, only_dir, ring_cap, ring_rows);
+  fill_body<0>(pairs, n_dir, only_dir, ring_cap, ring_rows);
 }
 
 // Convert stored cells to the reference's representation: natural-log doubles in the row-major
@@ -1039,7 +1212,30 @@ int launch_fill(hist_ctx* ctx, hist_pair* const* pairs, int n, int n_dir, int on
     absorb_kernel<<<dim3((maxDiag + HB_ABS_DIAGS - 1) / HB_ABS_DIAGS, n), 256, abs_smem, ctx->stream>>>(dptrs, tile_rows);
     ctx->launches += 1;
   }
-  if (narrow)
+  static const bool use_queue = getenv("HIST_B200_FILL") && !strcmp(getenv("HIST_B200_FILL"), "queue");
+  char* rec_buf = nullptr;
+  if (narrow && !use_queue) {
+    // streamed records: 64 B per stored cell and direction, built by one parallel pass, then the consumer-only sweep
+    const int n_cta = n * n_dir;
+    std::vector<size_t> off(n_cta + 1, 0);
+    for (int b = 0; b < n_cta; ++b) off[b + 1] = off[b] + (((size_t)pairs[b / n_dir]->dev.n_stored * 64 + 255) & ~(size_t)255);
+    const size_t tab = ((size_t)n_cta * sizeof(int4*) + 255) & ~(size_t)255;
+    int rc = check_cuda(ctx, cudaMallocAsync((void**)&rec_buf, tab + off[n_cta] + 256, ctx->stream), "cudaMallocAsync(fill records)");
+    if (rc) { cudaFreeAsync(dptrs, ctx->stream); return rc; }
+    std::vector<int4*> hrec(n_cta);
+    for (int b = 0; b < n_cta; ++b) hrec[b] = (int4*)(rec_buf + tab + off[b]);
+    HB_CUDA(ctx, cudaMemcpyAsync(rec_buf, hrec.data(), n_cta * sizeof(int4*), cudaMemcpyHostToDevice, ctx->stream));
+    // ring rows: as many as still let the whole batch be resident at once (one wave)
+    const int per_sm = (n_cta + ctx->sm_count - 1) / ctx->sm_count;
+    int srows = HB_RING_MAX;
+    while (srows > 4 && (size_t)per_sm * (srows * row + HB_SDEPTH * 2048 + 2048) > 200 * 1024) srows >>= 1;
+    const size_t ssmem = srows * row + HB_SDEPTH * 2048;
+    const int chunk = HB_BUILD_WARPS * HB_BUILD_DIAGS;
+    build_records_kernel<<<dim3((maxDiag + chunk - 1) / chunk, n_cta), 32 * HB_BUILD_WARPS, 0, ctx->stream>>>(dptrs, (int4* const*)rec_buf, n_dir,
+                                                                                                            only_dir, ring_cap, srows);
+    fill_stream_kernel<<<n_cta, 32, ssmem, ctx->stream>>>(dptrs, (int4* const*)rec_buf, n_dir, only_dir, ring_cap, srows);
+    ctx->launches += 1;
+  } else if (narrow)
     fill_narrow_kernel<<<n * n_dir, 32 * (1 + HB_NPROD), smem + HB_DEPTH * 128 * sizeof(int4), ctx->stream>>>(dptrs, n_dir, only_dir, ring_cap, rows);
   else
     fill_kernel<<<n * n_dir, block, smem, ctx->stream>>>(dptrs, n_dir, only_dir, ring_cap, rows);
@@ -1049,6 +1245,7 @@ int launch_fill(hist_ctx* ctx, hist_pair* const* pairs, int n, int n_dir, int on
     ctx->fill_events.push_back({e0, e1});
   }
   HB_CUDA(ctx, cudaGetLastError());
+  if (rec_buf) HB_CUDA(ctx, cudaFreeAsync(rec_buf, ctx->stream));
   HB_CUDA(ctx, cudaFreeAsync(dptrs, ctx->stream));
   // h[] is pageable host memory: the copy above has been staged by the time cudaMemcpyAsync returns
   return HIST_OK;
