@@ -37,6 +37,8 @@ BAND = 20
 BRANCH = 0.05
 N_LEAVES = 1024
 ROOT_LEN = 1000
+# dram__bytes_read.sum + dram__bytes_write.sum of the three fill kernels per launch, from the ncu --set full capture under profiles/ (None = not captured)
+FILL_TRAFFIC_BYTES = 7.33e9   # profiles/r01_fill_stream_ncu_details.txt: absorb 0.17 + build_records 3.13 + fill_stream 4.03 GB
 ALG_BYTES_PER_CELL = 80.0   # 40 B written once + 40 B read once per DP cell (reference layout)
 METRIC = "profile Forward/Backward cells/s (GCUPS)"
 UNIT = "Gcells/s"
@@ -433,7 +435,7 @@ def gpu_arm(args):
                     "host_memory": "residue strings and band descriptors in pageable host memory, staged through the context's pinned buffer"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "kernel": "hb::fill_kernel", "launches_timed": int(kernel_launches),
+                         "traffic": FILL_TRAFFIC_BYTES, "kernel": "hb::absorb_kernel + hb::build_records_kernel + hb::fill_stream_kernel (one batched Forward+Backward fill call; events bracket all three)", "launches_timed": int(kernel_launches),
                          "avg_launch_ms": 1e3 * per_launch_s, "algorithmic_bytes_per_cell": ALG_BYTES_PER_CELL,
                          "cells_per_launch": int(cells_per_step),
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"},

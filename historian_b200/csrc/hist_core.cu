@@ -218,10 +218,10 @@ __global__ void pack_meta_kernel(PairDev* const* __restrict__ pairs) {
   s.fm_a[i] = make_int4(flags | (ic << 8), ib, s.key[i], s.slot[i]);
   s.fm_b[i] = first;
   s.emis[i] = make_float2(s.rs[i], s.ins[i]);
-  s.bm[4 * i] = make_int4(flags | (ac << 8), ab, s.key[i], s.slot[i]);
-  s.bm[4 * i + 1] = make_int4(nb, nc, end_e, __float_as_int((float)end_sum));
-  s.bm[4 * i + 2] = f0;
-  s.bm[4 * i + 3] = f1;
+  s.bm[i] = make_int4(flags | (ac << 8), ab, s.key[i], s.slot[i]);
+  s.bm[s.n + i] = make_int4(nb, nc, end_e, __float_as_int((float)end_sum));
+  s.bm[2 * s.n + i] = f0;
+  s.bm[3 * s.n + i] = f1;
 }
 
 // Exact in-envelope cell count (the GCUPS unit, forward.cpp:78-86), one thread per stored slot.

@@ -337,8 +337,8 @@ __device__ __forceinline__ bool slot_cell(const PairDev& P, const DiagInfo& di, 
     if (i >= di.ilo && i < di.ilo + di.width) ok = false;
   }
   if (!ok || i < 0 || j < 0 || i > P.x.n - 2 || j > P.y.n - 2) return false;
-  xk = BWD ? P.x.bm[4 * i] : P.x.fm_a[i];
-  yk = BWD ? P.y.bm[4 * j] : P.y.fm_a[j];
+  xk = BWD ? P.x.bm[i] : P.x.fm_a[i];
+  yk = BWD ? P.y.bm[j] : P.y.fm_a[j];
   if (t >= P.nS + di.width && xk.w >= 0) return false;  // a near-start slot owns it
   // DPMatrix::inEnvelope (forward.h:92-98)
   return ((xk.x | yk.x) & F_NEAR) || P.max_dist < 0 || hb_iabs(xk.z - yk.z) <= P.max_dist;
@@ -470,10 +470,11 @@ __device__ __forceinline__ LaneMeta<BWD> load_meta(const PairDev& P, const Ring&
   // whole 16-B records through the read-only path: one LDG.128 each (plain struct copies get split into
   // 4/8-byte loads of the fields in use, several times the L1 wavefronts)
   if (BWD) {
-    const int4* xm = P.x.bm + 4 * i;
-    const int4* ym = P.y.bm + 4 * j;
-    m.xa = __ldg(xm); m.xb = __ldg(xm + 1); m.x0 = __ldg(xm + 2); m.x1 = __ldg(xm + 3);
-    m.ya = __ldg(ym); m.yb = __ldg(ym + 1); m.y0 = __ldg(ym + 2); m.y1 = __ldg(ym + 3);
+    const int4* xm = P.x.bm + i;   // four planes of n records: consecutive lanes read consecutive 16-B records
+    const int4* ym = P.y.bm + j;
+    const int nx = P.x.n, ny = P.y.n;
+    m.xa = __ldg(xm); m.xb = __ldg(xm + nx); m.x0 = __ldg(xm + 2 * nx); m.x1 = __ldg(xm + 3 * nx);
+    m.ya = __ldg(ym); m.yb = __ldg(ym + ny); m.y0 = __ldg(ym + 2 * ny); m.y1 = __ldg(ym + 3 * ny);
   } else {
     m.xa = __ldg(P.x.fm_a + i); m.xb = __ldg(P.x.fm_b + i); m.xe = __ldg(P.x.emis + i);
     m.ya = __ldg(P.y.fm_a + j); m.yb = __ldg(P.y.fm_b + j); m.ye = __ldg(P.y.emis + j);

@@ -62,7 +62,7 @@ struct SideDev {
   // packed records for the fill kernels
   int4* fm_a; int4* fm_b; float2* emis;   // [n] forward meta, (rs, ins)
   int4* in_edges;                         // [max(1,nt)]
-  int4* bm;                               // [n][4] backward meta
+  int4* bm;                               // [4][n] backward meta (plane-major)
   int4* ao_edges; int4* no_edges;         // [max(1,n_ao)][2], [max(1,n_no)][2]
   // natural-log doubles kept for fetch / makeProfile
   const double* lp_absorb;  // [n][K] input
