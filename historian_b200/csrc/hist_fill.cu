@@ -885,21 +885,34 @@ __device__ __forceinline__ void build_records(const PairDev& P, const Ring& ring
   const int t = threadIdx.x & 31;
   const int nD = P.n_diag;
   auto diag_of = [&](int q) { return min(max(BWD ? nD - 1 - q : q, 0), nD - 1); };
+  // layout records: the sweep-order neighbours are carried over from the previous iteration, the next diagonal's
+  // and the "request ahead" diagonal's are loaded one iteration early
+  DiagInfo di_n = P.dinfo[diag_of(q0)], c1 = P.dinfo[diag_of(q0 - 1)], c2 = P.dinfo[diag_of(q0 - 2)];
+  DiagInfo dj_n = P.dinfo[diag_of(q0 + HB_SDEPTH)];
   for (int q = q0; q < q1; ++q) {
     const int d = BWD ? nD - 1 - q : q;
-    const DiagInfo di = P.dinfo[d], c1 = P.dinfo[diag_of(q - 1)], c2 = P.dinfo[diag_of(q - 2)];
+    const DiagInfo di = di_n, dj = dj_n;
+    di_n = P.dinfo[diag_of(q + 1)];
+    dj_n = P.dinfo[diag_of(q + 1 + HB_SDEPTH)];
     const Recent rc = {c1.ilo, c1.width, c2.ilo, c2.width};
     const int cnt = P.nS + di.width + P.nE;
     const LaneMeta<BWD> m = load_meta<BWD>(P, ring, di, d, t, true);
     int4 r0, r1, r2, r3;
     make_record<BWD>(P, ring, d, rc, m, r0, r1, r2, r3);
+    int4* blk = out + (size_t)di.off * 4 + 2 * (size_t)d;   // block of diagonal d: 2 header int4's + 4 planes of cnt
+    if (t == 0) {
+      // header: this diagonal's layout, and the layout of the diagonal the consumer requests at the end of this step
+      __stcs(blk, make_int4(di.ilo, di.width, (int)di.off, 0));
+      __stcs(blk + 1, make_int4((int)dj.off, dj.width, diag_of(q + HB_SDEPTH), 0));
+    }
     if (t < cnt) {
-      int4* o = out + (size_t)di.off * 4 + t;
+      int4* o = blk + 2 + t;
       __stcs(o, r0);
       __stcs(o + cnt, r1);
       __stcs(o + 2 * cnt, r2);
       __stcs(o + 3 * cnt, r3);
     }
+    c2 = c1; c1 = di;
   }
 }
 
@@ -920,6 +933,8 @@ __global__ void __launch_bounds__(32 * HB_BUILD_WARPS) build_records_kernel(Pair
   if (bwd) build_records<true>(P, ring, recs[blockIdx.y], q0, q1); else build_records<false>(P, ring, recs[blockIdx.y], q0, q1);
 }
 
+#define HB_SSLOT 130   // int4's per queue slot: 2 header + 4 planes of up to 32 records
+
 template <bool BWD>
 __device__ __forceinline__ void consumer_stream(const PairDev& P, const Ring& ring, const int4* __restrict__ recs, int4* queue, uint64_t* full) {
   float4* gA = BWD ? P.bA : P.fA;
@@ -927,45 +942,40 @@ __device__ __forceinline__ void consumer_stream(const PairDev& P, const Ring& ri
   const int nD = P.n_diag;
   const int t = threadIdx.x;
   const int nEdge = P.nS + P.nE;
-  auto diag_at = [&](int q) { return min(max(BWD ? nD - 1 - q : q, 0), nD - 1); };
-  // lane 0: request the record block of sweep step q into queue slot q % HB_SDEPTH
-  auto issue = [&](int q, const DiagInfo& dj) {
+  // lane 0: request the block of diagonal dd (stored cells start at off, main interval `width` wide) into queue slot q % HB_SDEPTH
+  auto issue = [&](int q, int dd, unsigned off, int width) {
     const int slot = q % HB_SDEPTH;
-    const unsigned bytes = 64u * (unsigned)(nEdge + dj.width);
-    if (bytes) {
-      mbar_expect_tx(full + slot, bytes);
-      bulk_g2s(queue + slot * 128, recs + (size_t)dj.off * 4, bytes, full + slot);
-    } else {
-      mbar_arrive(full + slot);
-    }
+    const unsigned bytes = 32u + 64u * (unsigned)(nEdge + width);
+    mbar_expect_tx(full + slot, bytes);
+    bulk_g2s(queue + slot * HB_SSLOT, recs + (size_t)off * 4 + 2 * (size_t)dd, bytes, full + slot);
   };
   if (t == 0)
-    for (int q = 0; q < HB_SDEPTH && q < nD; ++q) issue(q, P.dinfo[diag_at(q)]);
+    for (int q = 0; q < HB_SDEPTH && q < nD; ++q) {
+      const int dd = BWD ? nD - 1 - q : q;
+      const DiagInfo dj = P.dinfo[dd];
+      issue(q, dd, dj.off, dj.width);
+    }
   Recent rc = {0, 0, 0, 0};
   const WReg WR = load_weights(P);
-  // layout records: of this step's diagonal (di) and of the diagonal requested at the end of this step (dj),
-  // both loaded two steps ahead of their use
-  DiagInfo di_n1 = P.dinfo[diag_at(0)], di_n2 = P.dinfo[diag_at(1)];
-  DiagInfo dj_n1 = P.dinfo[diag_at(HB_SDEPTH)], dj_n2 = P.dinfo[diag_at(HB_SDEPTH + 1)];
   for (int q = 0; q < nD; ++q) {
     const int slot = q % HB_SDEPTH;
     const int d = BWD ? nD - 1 - q : q;
-    const DiagInfo di = di_n1, dj = dj_n1;
-    di_n1 = di_n2; dj_n1 = dj_n2;
-    di_n2 = load_dinfo_early(P.dinfo + diag_at(q + 2));
-    dj_n2 = load_dinfo_early(P.dinfo + diag_at(q + 2 + HB_SDEPTH));
-    const int cnt = nEdge + di.width;
     mbar_wait(full + slot, (q / HB_SDEPTH) & 1);
-    const int4* R = queue + slot * 128;
+    const int4* Q = queue + slot * HB_SSLOT;
+    const int4 h0 = Q[0], h1 = Q[1];   // the diagonal's layout travels with its records: no global load in this loop
+    DiagInfo di;
+    di.ilo = h0.x; di.width = h0.y; di.off = (unsigned)h0.z; di.pad = 0;
+    const int cnt = nEdge + di.width;
+    const int4* R = Q + 2;
     int4 r0 = make_int4(0, 0, 0, 0), r1 = r0, r2 = r0, r3 = r0;
     if (t < cnt) { r0 = R[t]; r1 = R[cnt + t]; r2 = R[2 * cnt + t]; r3 = R[3 * cnt + t]; }
     __syncwarp();
     if (t == 0) {
-      ring.info[d & (ring.R - 1)] = make_int4(di.ilo, di.width, (int)di.off, 0);
+      ring.info[d & (ring.R - 1)] = h0;
       if (q + HB_SDEPTH < nD) {
         // the slot has been read by every lane; order those generic-proxy reads before the async-proxy write
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        issue(q + HB_SDEPTH, dj);
+        issue(q + HB_SDEPTH, h1.z, (unsigned)h1.x, h1.y);
       }
     }
     if (t < cnt) consume_store<BWD>(P, WR, ring, rc, di, d, t, r0, r1, r2, r3, gA, gB);
@@ -1083,7 +1093,7 @@ __global__ void __maxnreg__(HB_NARROW_REGS) fill_narrow_kernel(PairDev* const* _
   fill_body<1>(pairs, n_dir, only_dir, ring_cap, ring_rows);
 }
 // one warp per strip; dynamic smem = ring + HB_SDEPTH * 2 KB of record blocks; recs[blockIdx.x] built by build_records_kernel
-__global__ void __launch_bounds__(32) fill_stream_kernel(PairDev* const* __restrict__ pairs, int4* const* __restrict__ recs, int n_dir, int only_dir,
+__global__ void __maxnreg__(200) fill_stream_kernel(PairDev* const* __restrict__ pairs, int4* const* __restrict__ recs, int n_dir, int only_dir,
                                                          int ring_cap, int ring_rows) {
   fill_body<2>(pairs, n_dir, only_dir, ring_cap, ring_rows, recs);
 }
@@ -1219,7 +1229,7 @@ int launch_fill(hist_ctx* ctx, hist_pair* const* pairs, int n, int n_dir, int on
     // streamed records: 64 B per stored cell and direction, built by one parallel pass, then the consumer-only sweep
     const int n_cta = n * n_dir;
     std::vector<size_t> off(n_cta + 1, 0);
-    for (int b = 0; b < n_cta; ++b) off[b + 1] = off[b] + (((size_t)pairs[b / n_dir]->dev.n_stored * 64 + 255) & ~(size_t)255);
+    for (int b = 0; b < n_cta; ++b) off[b + 1] = off[b] + (((size_t)pairs[b / n_dir]->dev.n_stored * 64 + (size_t)pairs[b / n_dir]->dev.n_diag * 32 + 255) & ~(size_t)255);
     const size_t tab = ((size_t)n_cta * sizeof(int4*) + 255) & ~(size_t)255;
     int rc = check_cuda(ctx, cudaMallocAsync((void**)&rec_buf, tab + off[n_cta] + 256, ctx->stream), "cudaMallocAsync(fill records)");
     if (rc) { cudaFreeAsync(dptrs, ctx->stream); return rc; }
@@ -1229,8 +1239,8 @@ int launch_fill(hist_ctx* ctx, hist_pair* const* pairs, int n, int n_dir, int on
     // ring rows: as many as still let the whole batch be resident at once (one wave)
     const int per_sm = (n_cta + ctx->sm_count - 1) / ctx->sm_count;
     int srows = HB_RING_MAX;
-    while (srows > 4 && (size_t)per_sm * (srows * row + HB_SDEPTH * 2048 + 2048) > 200 * 1024) srows >>= 1;
-    const size_t ssmem = srows * row + HB_SDEPTH * 2048;
+    while (srows > 4 && (size_t)per_sm * (srows * row + HB_SDEPTH * HB_SSLOT * 16 + 2048) > 200 * 1024) srows >>= 1;
+    const size_t ssmem = srows * row + HB_SDEPTH * HB_SSLOT * 16;
     const int chunk = HB_BUILD_WARPS * HB_BUILD_DIAGS;
     build_records_kernel<<<dim3((maxDiag + chunk - 1) / chunk, n_cta), 32 * HB_BUILD_WARPS, 0, ctx->stream>>>(dptrs, (int4* const*)rec_buf, n_dir,
                                                                                                             only_dir, ring_cap, srows);
