@@ -37,6 +37,7 @@ struct SpDev {
   const int* kid_off;    // [N+1]
   const int* kid_idx;    // children in the reference's order (ascending original index)
   const int* orig;       // [N] internal -> original (postorder) index
+  const int* lvl_of;     // [N] depth level of each internal index
   const double* P;       // [N][C][A][A] branch matrices P(i->j)
   const double* PT;      // [N][C][A][A] transposed (j major)
   const double2* eet;    // [N][C][A] exp(lambda_k t)
@@ -113,6 +114,61 @@ __global__ void exp_eval_kernel(int N, int C, int A, const double* t, const doub
   }
 }
 
+// ------------------------------------------------------------------ load balance
+// The cost of a column grows with its number of ungapped rows, and full-tree columns sit next to insertions
+// that touch a handful of rows.  Columns are therefore processed in order of decreasing occupancy class
+// (floor(log2(ungapped rows))), round-robin over the resident blocks: every block gets its share of the dense
+// columns first and fills up with cheap ones.  The order is computed on device and is deterministic (stable
+// within a class), so the summation order of the counts is reproducible.
+__global__ void column_occupancy_kernel(const char* __restrict__ cols, long long n_cols, int N, int* __restrict__ occ) {
+  const long long col = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
+  if (col >= n_cols) return;
+  const int lane = threadIdx.x & 31;
+  const char* c = cols + (size_t)col * N;
+  int n = 0;
+  for (int r = lane; r < N; r += 32) n += c[r] != '-' && c[r] != '.';
+  for (int o = 16; o; o >>= 1) n += __shfl_down_sync(0xffffffffu, n, o);
+  if (lane == 0) occ[col] = n;
+}
+
+#define SP_BINS 32
+// one block of 1024 threads: stable multi-split of the columns by class, densest class first
+__global__ void __launch_bounds__(1024) column_order_kernel(const int* __restrict__ occ, int n_cols, int* __restrict__ order) {
+  __shared__ int s_cnt[32][SP_BINS];   // per warp, per class: members in this chunk
+  __shared__ int s_base[SP_BINS];      // next output position of each class
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  auto cls = [](int o) { return o <= 0 ? SP_BINS - 1 : min(SP_BINS - 2, __clz(o)); };  // fewer leading zeros = denser = earlier
+  // class totals
+  if (tid < SP_BINS) s_base[tid] = 0;
+  __syncthreads();
+  for (int c = tid; c < n_cols; c += 1024) atomicAdd(&s_base[cls(occ[c])], 1);
+  __syncthreads();
+  if (tid == 0) {
+    int run = 0;
+    for (int b = 0; b < SP_BINS; ++b) { const int n = s_base[b]; s_base[b] = run; run += n; }
+  }
+  __syncthreads();
+  for (int c0 = 0; c0 < n_cols; c0 += 1024) {
+    const int c = c0 + tid;
+    const int b = c < n_cols ? cls(occ[c]) : -1;
+    if (lane < SP_BINS) s_cnt[warp][lane] = 0;
+    __syncwarp();
+    const unsigned peers = __match_any_sync(0xffffffffu, b);
+    const int rank = __popc(peers & ((1u << lane) - 1));
+    if (b >= 0 && rank == 0) s_cnt[warp][b] = __popc(peers);
+    __syncthreads();
+    // exclusive prefix over the warps, per class (thread = class)
+    if (tid < SP_BINS) {
+      int run = s_base[tid];
+      for (int w = 0; w < 32; ++w) { const int n = s_cnt[w][tid]; s_cnt[w][tid] = run; run += n; }
+      s_base[tid] = run;
+    }
+    __syncthreads();
+    if (b >= 0) order[s_cnt[warp][b] + rank] = c;
+    __syncthreads();
+  }
+}
+
 // ------------------------------------------------------------------ S1-S4: the column kernel
 struct SpArgs {
   const char* columns;     // [n_cols][N] original row order
@@ -129,6 +185,9 @@ struct SpArgs {
   int chunk;               // nodes per staging chunk of the count phase
   int n_slices;            // node slices per (c,k,l) in the count phase
   int* err;                // device error flag
+  const int* order;        // [n_cols] processing order (densest columns first: static load balance) or NULL
+  int full;                // process every node of every level (debug fetch of all messages); else only the
+                           // per-level index ranges that hold ungapped nodes
 };
 
 __global__ void __launch_bounds__(SP_THREADS) sumprod_columns_kernel(SpDev S, SpArgs a) {
@@ -149,6 +208,8 @@ __global__ void __launch_bounds__(SP_THREADS) sumprod_columns_kernel(SpDev S, Sp
   int* s_int = (int*)(s_misc + 4);                           // [4]: n_ungapped, n_roots, root (internal), -
   signed char* s_tok = (signed char*)(s_int + 4);            // [N]
   unsigned char* s_valid = (unsigned char*)(s_tok + ((N + 15) & ~15));  // [chunk][C]
+  int* s_lo = (int*)(s_valid + (((size_t)a.chunk * C + 15) & ~(size_t)15));  // [n_levels] first / last internal index of
+  int* s_hi = s_lo + S.n_levels;                                             // the ungapped nodes of each level
 
   // ---- per-block workspace (stays in L2)
   double* W = a.work + (size_t)blockIdx.x * a.work_stride;
@@ -165,10 +226,15 @@ __global__ void __launch_bounds__(SP_THREADS) sumprod_columns_kernel(SpDev S, Sp
   if (tid == 0) s_misc[1] = 0;
   __syncthreads();
 
-  for (long long col = blockIdx.x; col < a.n_cols; col += gridDim.x) {
+  for (long long slot = blockIdx.x; slot < a.n_cols; slot += gridDim.x) {
+    const long long col = a.order ? a.order[slot] : slot;
     const char* cs = a.columns + (size_t)col * N;
     // ---- initColumn (sumprod.cpp:58-87)
     if (tid < 4) s_int[tid] = tid == 2 ? 0x7fffffff : 0;
+    for (int lev = tid; lev < S.n_levels; lev += nt) {
+      s_lo[lev] = a.full ? S.lvl_off[lev] : 0x7fffffff;
+      s_hi[lev] = a.full ? S.lvl_off[lev + 1] - 1 : -1;
+    }
     __syncthreads();
     for (int node = tid; node < N; node += nt) {
       const unsigned char ch = (unsigned char)cs[S.orig[node]];
@@ -183,41 +249,50 @@ __global__ void __launch_bounds__(SP_THREADS) sumprod_columns_kernel(SpDev S, Sp
       bool is_root = false;
       if (!gap) {
         atomicAdd(&s_int[0], 1);
+        if (!a.full) {
+          // the ungapped nodes of a column form (a few) subtrees, which are contiguous index ranges per level
+          const int lev = S.lvl_of[node];
+          atomicMin(&s_lo[lev], node);
+          atomicMax(&s_hi[lev], node);
+        }
         const int p = S.parent[node];
         is_root = p < 0 || s_tok[p] == SP_TOK_GAP;
         if (is_root) {
+          s_int[3] = node;  // internal index of the column root (unique whenever it is used)
           atomicAdd(&s_int[1], 1);
           atomicMin(&s_int[2], S.orig[node]);  // roots.front(): the first root in postorder
         }
       }
-      for (int c = 0; c < C; ++c) {
-        rootterm[(size_t)node * C + c] = 0;
-        if (gap) {
+      if (gap && a.full)  // E = 1, logE = 0 of gapped rows (sumprod.cpp:76-80); the passes below skip gapped children instead
+        for (int c = 0; c < C; ++c) {
           logE[(size_t)node * C + c] = 0;
           for (int i = 0; i < A; ++i) E[((size_t)node * C + c) * A + i] = 1;
         }
-      }
     }
     __syncthreads();
     const int n_ungapped = s_int[0], n_roots = s_int[1];
 
     // ---- fillUp (sumprod.cpp:99-161), deepest level first
     for (int lev = S.n_levels - 1; lev >= 0; --lev) {
-      const int l0 = S.lvl_off[lev], ln = S.lvl_off[lev + 1] - l0;
+      const int l0 = s_lo[lev], ln = s_hi[lev] - l0 + 1;
+      if (ln <= 0) continue;  // uniform over the block
       // F, logF, root terms: one thread per (node, component)
       for (int q = tid; q < ln * C; q += nt) {
         const int node = l0 + q / C, c = q % C;
         const int k0 = S.kid_off[node], k1 = S.kid_off[node + 1];
         double lF = 0;
-        for (int k = k0; k < k1; ++k) lF += logE[(size_t)S.kid_idx[k] * C + c];
+        for (int k = k0; k < k1; ++k)
+          if (s_tok[S.kid_idx[k]] != SP_TOK_GAP) lF += logE[(size_t)S.kid_idx[k] * C + c];  // gapped children: logE = 0, E = 1
         const int tk = s_tok[node];
+        double rterm = 0;
         if (tk != SP_TOK_GAP) {
           double* Fn = F + ((size_t)node * C + c) * A;
           if (tk == SP_TOK_WILD) {
             double Fmax = 0;
             for (int i = 0; i < A; ++i) {
               double Fi = 1;
-              for (int k = k0; k < k1; ++k) Fi *= E[((size_t)S.kid_idx[k] * C + c) * A + i];
+              for (int k = k0; k < k1; ++k)
+                if (s_tok[S.kid_idx[k]] != SP_TOK_GAP) Fi *= E[((size_t)S.kid_idx[k] * C + c) * A + i];
               Fn[i] = Fi;
               if (Fi > Fmax) Fmax = Fi;
             }
@@ -227,7 +302,8 @@ __global__ void __launch_bounds__(SP_THREADS) sumprod_columns_kernel(SpDev S, Sp
             }
           } else {
             double Ftok = 1;
-            for (int k = k0; k < k1; ++k) Ftok *= E[((size_t)S.kid_idx[k] * C + c) * A + tk];
+            for (int k = k0; k < k1; ++k)
+              if (s_tok[S.kid_idx[k]] != SP_TOK_GAP) Ftok *= E[((size_t)S.kid_idx[k] * C + c) * A + tk];
             if (Ftok < SP_RESCALE) {
               lF += log(Ftok);
               Ftok = 1;
@@ -239,11 +315,13 @@ __global__ void __launch_bounds__(SP_THREADS) sumprod_columns_kernel(SpDev S, Sp
           if (p < 0 || s_tok[p] == SP_TOK_GAP) {
             double ip = 0;
             for (int i = 0; i < A; ++i) ip += Fn[i] * S.ins[c * A + i];
-            rootterm[(size_t)node * C + c] = lF + log(ip);
+            rterm = lF + log(ip);
+            logE[(size_t)node * C + c] = 0;  // never read as a message (the parent is a gap); defined for the debug fetch
           } else {
             logE[(size_t)node * C + c] = lF;
           }
         }
+        rootterm[(size_t)node * C + c] = rterm;
         logF[(size_t)node * C + c] = lF;
       }
       __syncthreads();
@@ -271,7 +349,9 @@ __global__ void __launch_bounds__(SP_THREADS) sumprod_columns_kernel(SpDev S, Sp
       const int warp = tid >> 5, lane = tid & 31;
       for (int c = 0; c < C; ++c) {
         double v = 0;
-        for (int node = tid; node < N; node += nt) v += rootterm[(size_t)node * C + c];
+        for (int lev = 0; lev < S.n_levels; ++lev)
+          if (s_hi[lev] >= 0)  // an empty level has lo = INT_MAX
+            for (int node = s_lo[lev] + tid; node <= s_hi[lev]; node += nt) v += rootterm[(size_t)node * C + c];
         for (int o = 16; o; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
         if (lane == 0) s_red[warp * C + c] = v;
       }
@@ -294,7 +374,8 @@ __global__ void __launch_bounds__(SP_THREADS) sumprod_columns_kernel(SpDev S, Sp
 
     // ---- fillDown (sumprod.cpp:163-198), root first
     for (int lev = 0; lev < S.n_levels; ++lev) {
-      const int l0 = S.lvl_off[lev], ln = S.lvl_off[lev + 1] - l0;
+      const int l0 = s_lo[lev], ln = s_hi[lev] - l0 + 1;
+      if (ln <= 0) continue;
       for (int q = tid; q < ln * CA; q += nt) {
         const int node = l0 + q / CA, c = (q / A) % C, j = q % A;
         if (s_tok[node] == SP_TOK_GAP) continue;
@@ -307,7 +388,7 @@ __global__ void __launch_bounds__(SP_THREADS) sumprod_columns_kernel(SpDev S, Sp
           if (j == 0) {
             double lG = logG[(size_t)p * C + c];
             for (int k = k0; k < k1; ++k)
-              if (S.kid_idx[k] != node) lG += logE[(size_t)S.kid_idx[k] * C + c];
+              if (S.kid_idx[k] != node && s_tok[S.kid_idx[k]] != SP_TOK_GAP) lG += logE[(size_t)S.kid_idx[k] * C + c];
             logG[(size_t)node * C + c] = lG;
           }
           const double* Gp = G + ((size_t)p * C + c) * A;
@@ -339,14 +420,7 @@ __global__ void __launch_bounds__(SP_THREADS) sumprod_columns_kernel(SpDev S, Sp
       // internal index of the column root
       int root = -1;
       {
-        // orig -> internal is not stored; the root is the unique ungapped node whose parent is a gap / absent
-        for (int node = tid; node < N; node += nt)
-          if (s_tok[node] != SP_TOK_GAP) {
-            const int p = S.parent[node];
-            if (p < 0 || s_tok[p] == SP_TOK_GAP) s_int[3] = node;
-          }
-        __syncthreads();
-        root = s_int[3];
+        root = s_int[3];  // recorded by initColumn above
       }
       for (int q = tid; q < CA; q += nt) {
         const int c = q / A;
@@ -354,8 +428,9 @@ __global__ void __launch_bounds__(SP_THREADS) sumprod_columns_kernel(SpDev S, Sp
         s_root_acc[q] += weight * S.ins[q] * F[(size_t)root * CA + q] * norm;
       }
       if (tid == 0) s_misc[1] += colLL;  // indelCounts.lp += columnLogLikelihood (model.cpp:909)
-      for (int n0 = 0; n0 < N; n0 += a.chunk) {
-        const int nn = min(a.chunk, N - n0);
+      for (int lev = 0; lev < S.n_levels; ++lev)
+      for (int n0 = s_lo[lev]; n0 <= s_hi[lev]; n0 += a.chunk) {
+        const int nn = min(a.chunk, s_hi[lev] + 1 - n0);
         // U, D, scale: one thread per (node, component)
         for (int q = tid; q < nn * C; q += nt) {
           const int node = n0 + q / C, c = q % C;
@@ -369,11 +444,11 @@ __global__ void __launch_bounds__(SP_THREADS) sumprod_columns_kernel(SpDev S, Sp
           double* D = s_D + (size_t)q * A;
           double maxU = -INFINITY, maxD = -INFINITY, lsib = 0;
           for (int k = k0; k < k1; ++k)
-            if (S.kid_idx[k] != node) lsib += logE[(size_t)S.kid_idx[k] * C + c];
+            if (S.kid_idx[k] != node && s_tok[S.kid_idx[k]] != SP_TOK_GAP) lsib += logE[(size_t)S.kid_idx[k] * C + c];
           for (int i = 0; i < A; ++i) {
             double d = G[((size_t)p * C + c) * A + i];
             for (int k = k0; k < k1; ++k)
-              if (S.kid_idx[k] != node) d *= E[((size_t)S.kid_idx[k] * C + c) * A + i];
+              if (S.kid_idx[k] != node && s_tok[S.kid_idx[k]] != SP_TOK_GAP) d *= E[((size_t)S.kid_idx[k] * C + c) * A + i];
             D[i] = d;
             maxD = fmax(maxD, d);
             maxU = fmax(maxU, U0[i]);
@@ -520,6 +595,8 @@ struct hist_sumprod {
   double* partials;
   double* d_counts;           // staging of a host counts buffer
   int* d_err;
+  int* d_order;               // [order_cap] occupancy + processing order scratch (2 * order_cap ints)
+  int64_t order_cap;
   int chunk, n_slices;
   size_t smem;
   int max_blocks;
@@ -544,7 +621,7 @@ struct ArenaPlan {
   }
 };
 
-size_t sp_smem_bytes(int A, int C, int N, int chunk, int n_slices) {
+size_t sp_smem_bytes(int A, int C, int N, int chunk, int n_slices, int n_levels) {
   const size_t CA = (size_t)C * A, CAA = CA * A;
   size_t b = 16 * n_slices * CAA;           // s_acc
   b += 2 * 16 * chunk * CA;                 // s_Ub, s_Db
@@ -552,7 +629,8 @@ size_t sp_smem_bytes(int A, int C, int N, int chunk, int n_slices) {
   b += 8 * (size_t)chunk * C;               // s_scale
   b += 8 * CA + 8 * C + 8 * (SP_THREADS / 32) * C + 8 * 4 + 4 * 4;
   b += (N + 15) & ~15;                      // s_tok
-  b += (size_t)chunk * C;                   // s_valid
+  b += ((size_t)chunk * C + 15) & ~(size_t)15;  // s_valid
+  b += 8 * (size_t)n_levels;                // s_lo, s_hi
   return (b + 15) & ~(size_t)15;
 }
 
@@ -601,6 +679,9 @@ extern "C" int hist_sumprod_create(hist_ctx* ctx, const hist_model_desc* m, cons
     kid_off[q + 1] = (int)kid_idx.size();
   }
   if (kid_idx.empty()) kid_idx.push_back(0);
+  std::vector<int> lvl_of(N);
+  for (int lev = 0; lev < n_levels; ++lev)
+    for (int q = lvl_off[lev]; q < lvl_off[lev + 1]; ++q) lvl_of[q] = lev;
   // ---- model tables
   const size_t CA = (size_t)C * A, CAA = CA * A;
   bool is_real = true;  // EigenModel ctor, model.cpp:1175-1181
@@ -647,13 +728,13 @@ extern "C" int hist_sumprod_create(hist_ctx* ctx, const hist_model_desc* m, cons
   sp->A = A; sp->C = C; sp->N = N;
   sp->orig = orig;
   sp->internal = internal;
-  sp->arena = nullptr; sp->work = nullptr; sp->partials = nullptr; sp->d_counts = nullptr; sp->d_err = nullptr;
+  sp->arena = nullptr; sp->work = nullptr; sp->partials = nullptr; sp->d_counts = nullptr; sp->d_err = nullptr; sp->d_order = nullptr; sp->order_cap = 0;
   sp->work_blocks = 0;
   cudaSetDevice(ctx->device);
 
   ArenaPlan plan;
   const size_t o_lvl = plan.add(sizeof(int) * (n_levels + 1)), o_par = plan.add(sizeof(int) * N), o_koff = plan.add(sizeof(int) * (N + 1)),
-               o_kidx = plan.add(sizeof(int) * kid_idx.size()), o_orig = plan.add(sizeof(int) * N), o_P = plan.add(8 * (size_t)N * CAA),
+               o_kidx = plan.add(sizeof(int) * kid_idx.size()), o_orig = plan.add(sizeof(int) * N), o_lvlof = plan.add(sizeof(int) * N), o_P = plan.add(8 * (size_t)N * CAA),
                o_PT = plan.add(8 * (size_t)N * CAA), o_eet = plan.add(16 * (size_t)N * CA), o_t = plan.add(8 * (size_t)N),
                o_V = plan.add(16 * CAA), o_Vinv = plan.add(16 * CAA), o_invdl = plan.add(16 * CAA), o_eveq = plan.add(CAA),
                o_ins = plan.add(8 * CA), o_logcw = plan.add(8 * C), o_rate = plan.add(8 * CAA), o_tok = plan.add(256),
@@ -673,7 +754,7 @@ extern "C" int hist_sumprod_create(hist_ctx* ctx, const hist_model_desc* m, cons
   }
   cudaError_t es[] = {up(o_lvl, lvl_off.data(), sizeof(int) * (n_levels + 1)), up(o_par, parent.data(), sizeof(int) * N),
                       up(o_koff, kid_off.data(), sizeof(int) * (N + 1)), up(o_kidx, kid_idx.data(), sizeof(int) * kid_idx.size()),
-                      up(o_orig, orig.data(), sizeof(int) * N), up(o_t, t.data(), 8 * (size_t)N), up(o_V, V.data(), 16 * CAA),
+                      up(o_orig, orig.data(), sizeof(int) * N), up(o_lvlof, lvl_of.data(), sizeof(int) * N), up(o_t, t.data(), 8 * (size_t)N), up(o_V, V.data(), 16 * CAA),
                       up(o_Vinv, Vinv.data(), 16 * CAA), up(o_invdl, invdl.data(), 16 * CAA), up(o_eveq, eveq.data(), CAA),
                       up(o_ins, m->ins_prob, 8 * CA), up(o_logcw, logcw.data(), 8 * C), up(o_rate, rate, 8 * CAA),
                       up(o_tok, tokmap.data(), 256), up(o_alpha, m->alphabet, A), up(o_eval, eval.data(), 16 * CA),
@@ -687,7 +768,7 @@ extern "C" int hist_sumprod_create(hist_ctx* ctx, const hist_model_desc* m, cons
   SpDev& S = sp->dev;
   S.A = A; S.C = C; S.N = N; S.n_levels = n_levels; S.is_real = is_real;
   S.lvl_off = (const int*)(base + o_lvl); S.parent = (const int*)(base + o_par); S.kid_off = (const int*)(base + o_koff);
-  S.kid_idx = (const int*)(base + o_kidx); S.orig = (const int*)(base + o_orig); S.P = (const double*)(base + o_P);
+  S.kid_idx = (const int*)(base + o_kidx); S.orig = (const int*)(base + o_orig); S.lvl_of = (const int*)(base + o_lvlof); S.P = (const double*)(base + o_P);
   S.PT = (const double*)(base + o_PT); S.eet = (const double2*)(base + o_eet); S.t = (const double*)(base + o_t);
   S.V = (const double2*)(base + o_V); S.Vinv = (const double2*)(base + o_Vinv); S.invdl = (const double2*)(base + o_invdl);
   S.eveq = (const uint8_t*)(base + o_eveq); S.ins = (const double*)(base + o_ins); S.logcw = (const double*)(base + o_logcw);
@@ -712,16 +793,16 @@ extern "C" int hist_sumprod_create(hist_ctx* ctx, const hist_model_desc* m, cons
   // aim for several resident blocks per SM (56 KB each); larger alphabets take what they need
   int n_slices = std::max(1, SP_THREADS / (int)CAA);
   int chunk = 256;
-  while (chunk > 32 && sp_smem_bytes(A, C, N, chunk, n_slices) > 56 * 1024) chunk /= 2;
-  while (chunk > 8 && sp_smem_bytes(A, C, N, chunk, n_slices) > std::min<size_t>(ctx->smem_optin, 160 * 1024)) chunk /= 2;
-  if (sp_smem_bytes(A, C, N, chunk, n_slices) > ctx->smem_optin) {
+  while (chunk > 32 && sp_smem_bytes(A, C, N, chunk, n_slices, n_levels) > 56 * 1024) chunk /= 2;
+  while (chunk > 8 && sp_smem_bytes(A, C, N, chunk, n_slices, n_levels) > std::min<size_t>(ctx->smem_optin, 160 * 1024)) chunk /= 2;
+  if (sp_smem_bytes(A, C, N, chunk, n_slices, n_levels) > ctx->smem_optin) {
     cudaFree(sp->arena);
     delete sp;
     return set_err(ctx, HIST_ERR_CAPACITY, "hist_sumprod_create: tree/alphabet too large for shared memory (N=%d A=%d C=%d)", N, A, C);
   }
   sp->chunk = chunk;
   sp->n_slices = n_slices;
-  sp->smem = sp_smem_bytes(A, C, N, chunk, n_slices);
+  sp->smem = sp_smem_bytes(A, C, N, chunk, n_slices, n_levels);
   e = cudaFuncSetAttribute(sumprod_columns_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sp->smem);
   int per_sm = 1;
   if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sumprod_columns_kernel, SP_THREADS, sp->smem);
@@ -752,6 +833,7 @@ extern "C" void hist_sumprod_destroy(hist_sumprod* sp) {
   cudaFree(sp->partials);
   cudaFree(sp->d_counts);
   cudaFree(sp->d_err);
+  cudaFree(sp->d_order);
   delete sp;
 }
 
@@ -797,10 +879,26 @@ int run_columns(hist_sumprod* sp, const char* d_cols, const double* d_w, int64_t
   a.partials = ((flags & HIST_SP_COUNTS) && counts_dev) ? sp->partials : nullptr;
   a.counts_size = (int)hist_sumprod_counts_size(sp);
   a.chunk = sp->chunk; a.n_slices = sp->n_slices; a.err = sp->d_err;
+  a.full = force_blocks > 0;  // the debug fetch reads every node's messages
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (ctx->timing) {
     cudaEventCreate(&e0); cudaEventCreate(&e1);
     cudaEventRecord(e0, ctx->stream);
+  }
+  a.order = nullptr;
+  if (n_cols > blocks && n_cols < (1ll << 30)) {
+    if (sp->order_cap < n_cols) {
+      cudaStreamSynchronize(ctx->stream);
+      cudaFree(sp->d_order);
+      sp->d_order = nullptr; sp->order_cap = 0;
+      HB_CUDA(ctx, cudaMalloc(&sp->d_order, 2 * sizeof(int) * (size_t)n_cols));
+      sp->order_cap = n_cols;
+    }
+    int* occ = sp->d_order + sp->order_cap;
+    column_occupancy_kernel<<<(int)((n_cols * 32 + 255) / 256), 256, 0, ctx->stream>>>(d_cols, n_cols, sp->N, occ);
+    column_order_kernel<<<1, 1024, 0, ctx->stream>>>(occ, (int)n_cols, sp->d_order);
+    ctx->launches += 2;
+    a.order = sp->d_order;
   }
   sumprod_columns_kernel<<<blocks, SP_THREADS, sp->smem, ctx->stream>>>(sp->dev, a);
   if (ctx->timing) {
