@@ -383,6 +383,7 @@ def gpu_arm(args):
     # the ctypes argument arrays of hist_pair_prepare_batch (pointers to the host descriptors) are built once;
     # every step passes them, with that step's fresh profile handles, to the C ABI
     plan = capi.PrepareBatch(ctx, [a for a, _ in profs], [b for _, b in profs], hmm, envs, backward=True)
+    prep_h2d = sum(int(p.info.h2d_bytes) for p in pairs)   # bytes hist_pair_prepare_batch ships per step (same inputs as the resident pairs)
 
     def step_e2e():
         # the calls a reference user makes per level: leaf Profile constructors (profile.cpp:23-76) from the residue
@@ -390,7 +391,7 @@ def gpu_arm(args):
         leaves = ctx.upload_sequences(seqs, lg.alphabet, lg.components)
         pr = plan.run(leaves[0::2], leaves[1::2])
         r = ctx.fill_batch(pr, backward=True)
-        h2d = sum(len(q) for q in seqs) + sum(int(p.info.h2d_bytes) for p in pr)
+        h2d = sum(len(q) for q in seqs) + prep_h2d
         for p in pr:
             p.close()
         for a in leaves:

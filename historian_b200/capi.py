@@ -246,10 +246,17 @@ class Pair:
             handle = C.c_void_p()
             ctx.check(ctx.lib.hist_pair_prepare(ctx.h, x.h, y.h, C.byref(hd), C.byref(ed), C.byref(handle)))
         self.h = handle
-        info = D.PairInfo()
-        ctx.check(ctx.lib.hist_pair_get_info(self.h, C.byref(info)))
-        self.info = info
+        self._info = None
         self.components, self.alph_size = x.components, x.alph_size
+
+    @property
+    def info(self):
+        """hist_pair_info, fetched on first use (a level of merges creates hundreds of pairs at once)."""
+        if self._info is None:
+            info = D.PairInfo()
+            self.ctx.check(self.ctx.lib.hist_pair_get_info(self.h, C.byref(info)))
+            self._info = info
+        return self._info
 
     def close(self):
         if self.h and self.ctx.h:

@@ -15,6 +15,7 @@
 #include <cstring>
 #include <limits>
 
+#include <chrono>
 #include <mutex>
 #include <thread>
 #include "hist_internal.cuh"
@@ -265,6 +266,39 @@ __global__ void count_cells_kernel(PairDev* const* __restrict__ pairs) {
 
 using namespace hb;
 
+namespace {
+// Runs fn(0..n-1) on up to hardware_concurrency host threads (at least `grain` items per thread).
+template <class F>
+void parallel_for(int n, int grain, F fn) {
+  int nthreads = (int)std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 16u);
+  nthreads = std::max(1, std::min(nthreads, n / std::max(1, grain)));
+  if (nthreads <= 1) {
+    for (int k = 0; k < n; ++k) fn(k);
+    return;
+  }
+  std::vector<std::thread> pool;
+  for (int t = 0; t < nthreads; ++t)
+    pool.emplace_back([=, &fn]() {
+      for (int k = t; k < n; k += nthreads) fn(k);
+    });
+  for (auto& th : pool) th.join();
+}
+
+// HIST_B200_HOST_TIMING=1: wall-clock split of the host side of the batched constructors on stderr
+struct HostTimer {
+  bool on;
+  const char* what;
+  std::chrono::steady_clock::time_point t0;
+  explicit HostTimer(const char* w) : on(getenv("HIST_B200_HOST_TIMING") != nullptr), what(w), t0(std::chrono::steady_clock::now()) {}
+  void lap(const char* stage) {
+    if (!on) return;
+    const auto t1 = std::chrono::steady_clock::now();
+    fprintf(stderr, "[%s] %-18s %.2f ms\n", what, stage, std::chrono::duration<double, std::milli>(t1 - t0).count());
+    t0 = t1;
+  }
+};
+}  // namespace
+
 // ------------------------------------------------------------------ context
 extern "C" int hist_ctx_create(int device, hist_ctx** out) {
   if (!out) return set_err(nullptr, HIST_ERR_ARG, "hist_ctx_create: out is NULL");
@@ -483,7 +517,8 @@ extern "C" int hist_profile_from_sequences(hist_ctx* ctx, int32_t n, const int8_
     delete arena;
     return rc;
   }
-  for (int k = 0; k < n; ++k) {
+  HostTimer tm("from_sequences");
+  parallel_for(n, 16, [&](int k) {
     hist_profile* p = new hist_profile();
     const int L = lengths[k];
     p->ctx = ctx;
@@ -503,9 +538,10 @@ extern "C" int hist_profile_from_sequences(hist_ctx* ctx, int32_t n, const int8_
     p->empty = L == 0;
     p->d_lp_absorb = (double*)arena->dev + (size_t)state_off[k] * K;
     p->arena = arena;
-    ++arena->refs;
     out[k] = p;
-  }
+  });
+  arena->refs += n;
+  tm.lap("host objects");
   return HIST_OK;
 }
 
@@ -519,23 +555,6 @@ extern "C" void hist_profile_destroy(hist_profile* p) {
 
 // ------------------------------------------------------------------ pair preparation
 namespace {
-
-// Runs fn(0..n-1) on up to hardware_concurrency host threads (at least `grain` items per thread).
-template <class F>
-void parallel_for(int n, int grain, F fn) {
-  int nthreads = (int)std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 16u);
-  nthreads = std::max(1, std::min(nthreads, n / std::max(1, grain)));
-  if (nthreads <= 1) {
-    for (int k = 0; k < n; ++k) fn(k);
-    return;
-  }
-  std::vector<std::thread> pool;
-  for (int t = 0; t < nthreads; ++t)
-    pool.emplace_back([=, &fn]() {
-      for (int k = t; k < n; k += nthreads) fn(k);
-    });
-  for (auto& th : pool) th.join();
-}
 
 // Byte layout of one pair inside the batch arena: a host-initialised part (copied in ONE H2D
 // transfer for the whole batch) and a device-only part.
@@ -908,6 +927,7 @@ extern "C" int hist_pair_prepare_batch(hist_ctx* ctx, int32_t n, const hist_prof
   for (int k = 0; k < n; ++k) out[k] = nullptr;
   cudaSetDevice(ctx->device);
   const bool want_bwd = (flags & HIST_PREP_BACKWARD) != 0;
+  HostTimer tm("prepare_batch");
   std::vector<PairBuild> builds(n);
   auto fail = [&](int rc) {
     for (auto& b : builds) delete b.pr;
@@ -921,6 +941,7 @@ extern "C" int hist_pair_prepare_batch(hist_ctx* ctx, int32_t n, const hist_prof
     for (int k = 0; k < n; ++k)
       if (rcs[k]) return fail(rcs[k]);
   }
+  tm.lap("host build");
   for (int k = 0; k < n; ++k) {
     builds[k].host_base = host_total;
     host_total += builds[k].host.bytes;
@@ -944,6 +965,7 @@ extern "C" int hist_pair_prepare_batch(hist_ctx* ctx, int32_t n, const hist_prof
     delete arena;
     return fail(rc);
   }
+  tm.lap("alloc");
   // fill the pinned staging image and ship it in one transfer
   char* st = ctx->staging;
   int maxN = 1, maxNt = 1, maxDiag = 1, maxKp = 4, maxKC = 1;
@@ -964,6 +986,7 @@ extern "C" int hist_pair_prepare_batch(hist_ctx* ctx, int32_t n, const hist_prof
     maxKp = std::max(maxKp, D.Kp);
     maxKC = std::max(maxKC, D.K + D.C);
   }
+  tm.lap("staging fill");
   rc = check_cuda(ctx, cudaMemcpyAsync(arena->dev, st, scal_off, cudaMemcpyHostToDevice, ctx->stream), "H2D pair arena");
   if (!rc) rc = check_cuda(ctx, cudaMemsetAsync(arena->dev + scal_off, 0, (size_t)n * 4 * sizeof(double), ctx->stream), "memset scalars");
   // ---- F0/F1 and the packed records on device, one launch each for the whole batch
@@ -982,7 +1005,9 @@ extern "C" int hist_pair_prepare_batch(hist_ctx* ctx, int32_t n, const hist_prof
   std::vector<double> scal((size_t)n * 4);
   if (!rc) rc = check_cuda(ctx, cudaMemcpyAsync(scal.data(), arena->dev + scal_off, scal.size() * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream), "D2H n_cells");
   // descriptors were only borrowed, and the staging buffer is reused by the next call
+  tm.lap("enqueue");
   if (!rc) rc = check_cuda(ctx, cudaStreamSynchronize(ctx->stream), "sync after pair prepare");
+  tm.lap("device wait");
   if (rc) {
     cudaFreeAsync(arena->dev, ctx->stream);
     delete arena;
