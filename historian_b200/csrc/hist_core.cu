@@ -997,7 +997,7 @@ extern "C" int hist_pair_prepare_batch(hist_ctx* ctx, int32_t n, const hist_prof
     prepare_side_kernel<<<dim3(maxN, n, 2), threads, smem, ctx->stream>>>(dptrs);
     prepare_trans_kernel<<<dim3((maxNt + 127) / 128, n, 2), 128, 0, ctx->stream>>>(dptrs);
     pack_meta_kernel<<<dim3((maxN + 127) / 128, n, 2), 128, 0, ctx->stream>>>(dptrs);
-    const int chunks = std::max(1, std::min(maxDiag, (4 * ctx->sm_count + n - 1) / n));
+    const int chunks = std::max(1, std::min(maxDiag / 64 + 1, std::max(8, (4 * ctx->sm_count + n - 1) / n)));  // >= 8 chunks of diagonals per pair
     count_cells_kernel<<<dim3(chunks, n), 128, 0, ctx->stream>>>(dptrs);
     ctx->launches += 4;
     rc = check_cuda(ctx, cudaGetLastError(), "prepare kernels");

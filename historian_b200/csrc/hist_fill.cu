@@ -353,7 +353,9 @@ __device__ __forceinline__ bool slot_cell(const PairDev& P, const DiagInfo& di, 
 // consecutive floats.  Slots whose rows fall outside the staged tiles (the near-start / near-end
 // edge slots, or diagonals wider than a tile) read their rows from global memory.
 // grid = (diagonal blocks, pairs); dynamic smem = 2 * tile_rows * Kp floats.
+#ifndef HB_ABS_DIAGS
 #define HB_ABS_DIAGS 32
+#endif
 
 __device__ __forceinline__ float dot_rows(const float4* __restrict__ x4, const float4* __restrict__ y4, int K4) {
   float a0 = 0.f, a1 = 0.f;
@@ -854,8 +856,12 @@ __device__ __forceinline__ void sweep_narrow(const PairDev& P, const Ring& ring,
 // ahead of their use.  The dependent instruction stream of a step is the arithmetic and nothing else, and a
 // strip costs 32 threads instead of 64-96, so a whole level of sibling merges is resident at once.
 #define HB_SDEPTH 8
-#define HB_BUILD_WARPS 8
-#define HB_BUILD_DIAGS 8   // diagonals per warp
+#ifndef HB_BUILD_WARPS
+#define HB_BUILD_WARPS 4   // measured: 4 warps x 8 diagonals 1.04 ms, 8 x 8 1.14 ms, 8 x 16 1.09 ms, 16 x 4 1.79 ms
+#endif
+#ifndef HB_BUILD_DIAGS
+#define HB_BUILD_DIAGS 16  // diagonals per warp (4 x 16: 1.00 ms)
+#endif
 
 __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, unsigned bytes) {
   asm volatile("{\n .reg .b64 st;\n mbarrier.arrive.expect_tx.shared::cta.b64 st, [%0], %1;\n}" ::"r"((unsigned)__cvta_generic_to_shared(bar)),
@@ -1225,14 +1231,18 @@ int launch_fill(hist_ctx* ctx, hist_pair* const* pairs, int n, int n_dir, int on
   }
   static const bool use_queue = getenv("HIST_B200_FILL") && !strcmp(getenv("HIST_B200_FILL"), "queue");
   char* rec_buf = nullptr;
+  const int n_cta = n * n_dir;
+  std::vector<size_t> off(n_cta + 1, 0);
+  const size_t tab = ((size_t)n_cta * sizeof(int4*) + 255) & ~(size_t)255;
   if (narrow && !use_queue) {
-    // streamed records: 64 B per stored cell and direction, built by one parallel pass, then the consumer-only sweep
-    const int n_cta = n * n_dir;
-    std::vector<size_t> off(n_cta + 1, 0);
+    // streamed records: 64 B per stored cell and direction (+ 32 B per diagonal), built by one parallel pass
     for (int b = 0; b < n_cta; ++b) off[b + 1] = off[b] + (((size_t)pairs[b / n_dir]->dev.n_stored * 64 + (size_t)pairs[b / n_dir]->dev.n_diag * 32 + 255) & ~(size_t)255);
-    const size_t tab = ((size_t)n_cta * sizeof(int4*) + 255) & ~(size_t)255;
-    int rc = check_cuda(ctx, cudaMallocAsync((void**)&rec_buf, tab + off[n_cta] + 256, ctx->stream), "cudaMallocAsync(fill records)");
-    if (rc) { cudaFreeAsync(dptrs, ctx->stream); return rc; }
+    if (cudaMallocAsync((void**)&rec_buf, tab + off[n_cta] + 256, ctx->stream) != cudaSuccess) {
+      cudaGetLastError();   // no room for the record buffer: the in-CTA producer/consumer kernel needs none
+      rec_buf = nullptr;
+    }
+  }
+  if (rec_buf) {
     std::vector<int4*> hrec(n_cta);
     for (int b = 0; b < n_cta; ++b) hrec[b] = (int4*)(rec_buf + tab + off[b]);
     HB_CUDA(ctx, cudaMemcpyAsync(rec_buf, hrec.data(), n_cta * sizeof(int4*), cudaMemcpyHostToDevice, ctx->stream));

@@ -13,6 +13,8 @@ Tolerances (stated once, used everywhere below)
     accumulates along the path).  Against the exact-LSE oracle: |diff| <= 2e-6*|ref| + 2e-4
     (FP32 linear-space mantissas, 2^-24 per operation).
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -245,3 +247,15 @@ def test_leaf_profiles_built_on_device_match_uploaded_ones(ctx):
         assert H.same(p1.cells_dense(0), p2.cells_dense(0))
         for t1, t2 in zip(p1.tables(), p2.tables()):
             assert H.same(t1, t2)
+
+
+def test_queue_kernel_variant_still_matches():
+    """HIST_B200_FILL=queue selects the in-CTA producer/consumer kernel (the fallback when the record buffer of
+    the streamed path cannot be allocated); it must pass the same parity tests."""
+    import subprocess
+    import sys
+    env = dict(os.environ, HIST_B200_FILL="queue")
+    here = os.path.abspath(__file__)
+    r = subprocess.run([sys.executable, "-m", "pytest", here, "-m", "gpu", "-q", "-x", "-k", "leaf_pair_banded or synthetic_dag or batch_fill"],
+                       env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, cwd=os.path.dirname(os.path.dirname(here)))
+    assert r.returncode == 0, r.stdout[-2000:]
