@@ -46,9 +46,7 @@ class Path:
                 r = {k: list(v) for k, v in self.args[0].expand().items()}
                 r.setdefault(self.args[1], []).append(True)
             else:
-                r = {}
-                for p in self.args[0]:
-                    r = concat_paths(r, p.expand())
+                r = concat_many([p.expand() for p in self.args[0]])
             self._cache = r
         return self._cache
 
@@ -73,6 +71,28 @@ def concat_paths(a1, a2):
             lp.extend([False] * c1)
         lp.extend(rp)
     return a
+
+
+def concat_many(paths):
+    """Left fold of alignPathConcat over a list of expanded paths in linear time (the fold itself copies the
+    accumulated path at every step).  Rows of one path all have that path's column count."""
+    out, offset = {}, 0
+    for a in paths:
+        if not a:
+            continue
+        c = path_columns(a)
+        for row, rp in a.items():
+            lst = out.get(row)
+            if lst is None:
+                lst = out[row] = []
+            if len(lst) < offset:
+                lst.extend([False] * (offset - len(lst)))
+            lst.extend(rp)
+        offset += c
+    for lst in out.values():
+        if len(lst) < offset:
+            lst.extend([False] * (offset - len(lst)))
+    return out
 
 
 # ------------------------------------------------------------------ host profile
