@@ -44,6 +44,7 @@ def load():
     lib.hist_ctx_fill_time_ms.argtypes = [vp, D.c_double_p, D.c_int64_p]
     lib.hist_profile_upload.argtypes = [vp, C.POINTER(D.ProfileDesc), C.POINTER(vp)]
     lib.hist_profile_from_sequences.argtypes = [vp, C.c_int32, C.POINTER(vp), D.c_int32_p, C.c_int32, C.c_int32, C.POINTER(vp)]
+    lib.hist_profile_sum_path_absorb.argtypes = [vp, D.c_double_p, D.c_double_p, D.c_double_p, D.c_double_p]
     lib.hist_profile_destroy.argtypes = [vp]
     lib.hist_profile_destroy.restype = None
     lib.hist_pair_prepare.argtypes = [vp, vp, vp, C.POINTER(D.PairHmmDesc), C.POINTER(D.EnvDesc), C.POINTER(vp)]
@@ -194,6 +195,17 @@ class DeviceProfile:
             seq = seq if isinstance(seq, str) else bytes(seq).decode()
             self._host = D.Profile.from_sequence(seq, alphabet, components, wildcard)
         return self._host
+
+    def sum_path_absorb(self, log_cpt_weight, log_ins_prob):
+        """Profile::calcSumPathAbsorbProbs (profile.cpp:112-131): (lpCumAbs of END, per-state lpCumAbs)."""
+        n = self.host.n_states if self._host is not None else len(self._leaf[0]) + 2
+        cum = np.empty(n)
+        w = np.ascontiguousarray(log_cpt_weight, np.float64)
+        ins = np.ascontiguousarray(log_ins_prob, np.float64)
+        res = C.c_double()
+        self.ctx.check(self.ctx.lib.hist_profile_sum_path_absorb(self.h, _p(w, C.c_double), _p(ins, C.c_double), _p(cum, C.c_double),
+                                                                 C.byref(res)))
+        return res.value, cum
 
     def close(self):
         if self.h and self.ctx.h:

@@ -118,3 +118,101 @@ extern "C" int hist_posterior_cells(hist_pair* pair, double min_post_prob, hist_
   cudaFreeAsync(buf, ctx->stream);
   return rc;
 }
+
+// ------------------------------------------------------------------ P3: Profile::calcSumPathAbsorbProbs
+// (profile.cpp:112-131): a 1-D Forward over the profile, lpCum[pos] = LSE over in-transitions of
+// lpCum[src] + lpTrans + lpAbs[pos], lpAbs[pos] = LSE_c(logCptWeight[c] + logInnerProduct(logInsProb[c],
+// lpAbsorb[pos][c])) for emitting states and 0 for null states.  One block: all threads compute lpAbs in
+// parallel, then warp 0 walks the states in order (lanes over the in-transitions, exact log-sum-exp).
+namespace hb {
+__device__ __forceinline__ double sp_lse2(double a, double b) {
+  if (a == -INFINITY) return b;
+  if (b == -INFINITY) return a;
+  const double m = fmax(a, b);
+  return m + log1p(exp(-fabs(a - b)));
+}
+
+__global__ void __launch_bounds__(256) sum_path_absorb_kernel(int n, int C, int A, const uint8_t* __restrict__ is_emit,
+                                                              const double* __restrict__ lp_absorb, const int* __restrict__ in_off,
+                                                              const int* __restrict__ in_src, const double* __restrict__ in_lp,
+                                                              const double* __restrict__ log_cw, const double* __restrict__ log_ins,
+                                                              double* __restrict__ lp_abs, double* __restrict__ cum) {
+  for (int pos = threadIdx.x; pos < n; pos += blockDim.x) {
+    double v = 0;
+    if (is_emit[pos]) {
+      v = -INFINITY;
+      for (int c = 0; c < C; ++c) {
+        double inner = -INFINITY;  // logInnerProduct (logsumexp.h:126-151)
+        for (int a = 0; a < A; ++a) inner = sp_lse2(inner, log_ins[c * A + a] + lp_absorb[((size_t)pos * C + c) * A + a]);
+        v = sp_lse2(v, log_cw[c] + inner);
+      }
+    }
+    lp_abs[pos] = v;
+    cum[pos] = pos == 0 ? 0.0 : -INFINITY;
+  }
+  __syncthreads();
+  if (threadIdx.x >= 32) return;
+  const int lane = threadIdx.x;
+  for (int pos = 1; pos < n; ++pos) {
+    const int e0 = in_off[pos], e1 = in_off[pos + 1];
+    const double la = lp_abs[pos];
+    double v = -INFINITY;
+    for (int e = e0 + lane; e < e1; e += 32) v = sp_lse2(v, cum[in_src[e]] + in_lp[e] + la);
+    if (e1 - e0 > 1)
+      for (int o = 16; o; o >>= 1) v = sp_lse2(v, __shfl_xor_sync(0xffffffffu, v, o));
+    else
+      v = __shfl_sync(0xffffffffu, v, 0);
+    if (lane == 0) cum[pos] = v;
+    __syncwarp();
+  }
+}
+}  // namespace hb
+
+extern "C" int hist_profile_sum_path_absorb(hist_profile* p, const double* log_cpt_weight, const double* log_ins_prob, double* cum,
+                                            double* result) {
+  if (!p || !log_cpt_weight || !log_ins_prob || !result) return HIST_ERR_ARG;
+  hist_ctx* ctx = p->ctx;
+  cudaSetDevice(ctx->device);
+  const int n = p->n, nt = p->nt, C = p->C, A = p->A;
+  // incoming transitions per state, ascending transition index (the order of ProfileState::in)
+  std::vector<int> in_off(n + 1, 0), in_src(std::max(1, nt));
+  std::vector<double> in_lp(std::max(1, nt));
+  for (int t = 0; t < nt; ++t) ++in_off[p->t_dst[t] + 1];
+  for (int i = 0; i < n; ++i) in_off[i + 1] += in_off[i];
+  {
+    std::vector<int> at(in_off.begin(), in_off.end() - 1);
+    for (int t = 0; t < nt; ++t) {
+      const int q = at[p->t_dst[t]]++;
+      in_src[q] = p->t_src[t];
+      in_lp[q] = p->t_lp[t];
+    }
+  }
+  const size_t o_emit = 0, o_off = (n + 255) & ~(size_t)255, o_src = o_off + ((sizeof(int) * (n + 1) + 255) & ~(size_t)255),
+               o_lp = o_src + ((sizeof(int) * in_src.size() + 255) & ~(size_t)255), o_cw = o_lp + ((8 * in_lp.size() + 255) & ~(size_t)255),
+               o_ins = o_cw + ((8 * (size_t)C + 255) & ~(size_t)255), o_abs = o_ins + ((8 * (size_t)C * A + 255) & ~(size_t)255),
+               o_cum = o_abs + ((8 * (size_t)n + 255) & ~(size_t)255), total = o_cum + 8 * (size_t)n;
+  char* d = nullptr;
+  HB_CUDA(ctx, cudaMallocAsync((void**)&d, total, ctx->stream));
+  int rc = 0;
+  auto up = [&](size_t off, const void* src, size_t bytes) {
+    if (!rc) rc = hb::check_cuda(ctx, cudaMemcpyAsync(d + off, src, bytes, cudaMemcpyHostToDevice, ctx->stream), "H2D sum_path_absorb");
+  };
+  up(o_emit, p->is_emit.data(), n);
+  up(o_off, in_off.data(), sizeof(int) * (n + 1));
+  up(o_src, in_src.data(), sizeof(int) * in_src.size());
+  up(o_lp, in_lp.data(), 8 * in_lp.size());
+  up(o_cw, log_cpt_weight, 8 * (size_t)C);
+  up(o_ins, log_ins_prob, 8 * (size_t)C * A);
+  if (!rc) {
+    hb::sum_path_absorb_kernel<<<1, 256, 0, ctx->stream>>>(n, C, A, (const uint8_t*)(d + o_emit), p->d_lp_absorb, (const int*)(d + o_off),
+                                                          (const int*)(d + o_src), (const double*)(d + o_lp), (const double*)(d + o_cw),
+                                                          (const double*)(d + o_ins), (double*)(d + o_abs), (double*)(d + o_cum));
+    ctx->launches += 1;
+    rc = hb::check_cuda(ctx, cudaGetLastError(), "sum_path_absorb_kernel");
+  }
+  if (!rc && cum) rc = hb::check_cuda(ctx, cudaMemcpyAsync(cum, d + o_cum, 8 * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream), "D2H cum");
+  if (!rc) rc = hb::check_cuda(ctx, cudaMemcpyAsync(result, d + o_cum + 8 * (size_t)(n - 1), 8, cudaMemcpyDeviceToHost, ctx->stream), "D2H result");
+  if (!rc) rc = hb::check_cuda(ctx, cudaStreamSynchronize(ctx->stream), "sync");
+  cudaFreeAsync(d, ctx->stream);
+  return rc;
+}

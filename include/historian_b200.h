@@ -282,6 +282,14 @@ typedef struct {
 int hist_profile_eliminate(hist_pair* pair, const hist_cell* cells, int64_t n_cells, int32_t strategy,
                            hist_elim_result* result);
 
+/* ------------------------------------------------------------------ P3
+ * Profile::calcSumPathAbsorbProbs (profile.cpp:112-131): 1-D Forward over the profile with the insertion
+ * distribution as emission (the "cumLogProb" tag of t/testforward and the log line of recon.cpp:1022).
+ * log_cpt_weight [C], log_ins_prob [C][A]; cum (optional) receives lpCumAbs per state [n_states];
+ * *result = lpCumAbs of the END state. */
+int hist_profile_sum_path_absorb(hist_profile* profile, const double* log_cpt_weight, const double* log_ins_prob,
+                                 double* cum, double* result);
+
 /* ------------------------------------------------------------------ sum-product
  * SumProduct / AlignColSumProduct (sumprod.h:32-104, sumprod.cpp).
  * The model is passed in eigen-decomposed form (EigenModel, model.cpp:1135-1199):

@@ -94,3 +94,36 @@ def test_eliminate_argument_checks(ctx):
     assert e.value.code == -1
     with pytest.raises(capi.HistError):
         pair.eliminate(best[:-1])  # end cell missing
+
+
+def test_sum_path_absorb_on_device(ctx):
+    """P3, Profile::calcSumPathAbsorbProbs (profile.cpp:112-131) through hist_profile_sum_path_absorb vs the oracle
+    with exact log-sum-exp (1e-9 relative; the device and the oracle fold the same terms, the device in a
+    lane-strided order), on leaf chains and on random DAG profiles with several components."""
+    import oracle_lib as O
+    import synth
+    rng = np.random.default_rng(12)
+    O.set_exact_lse(True)
+    try:
+        for A, Cc, n in ((20, 1, 60), (4, 2, 35), (20, 3, 150), (61, 1, 40)):
+            p = synth.random_profile(rng, n, A, Cc)
+            logw = np.log(rng.dirichlet(np.ones(Cc)))
+            logins = np.log(rng.dirichlet(np.ones(A), size=Cc))
+            want, want_cum = O.sum_path_absorb(p, logw, logins)
+            dp = ctx.upload(p)
+            got, cum = dp.sum_path_absorb(logw, logins)
+            assert abs(got - want) <= 1e-9 * abs(want) + 1e-9
+            fin = np.isfinite(want_cum)
+            assert np.array_equal(np.isfinite(cum), fin)
+            assert np.all(np.abs(cum[fin] - want_cum[fin]) <= 1e-9 * np.abs(want_cum[fin]) + 1e-9)
+            dp.close()
+        x, _, _ = synth.leaf_pair(rng, "acgt", 50, 40)
+        logw, logins = np.zeros(1), np.log(np.full((1, 4), 0.25))
+        want, _ = O.sum_path_absorb(x, logw, logins)
+        dx = ctx.upload(x)
+        got, _ = dx.sum_path_absorb(logw, logins)
+        assert abs(got - want) <= 1e-9 * abs(want)
+        assert abs(got - 50 * np.log(0.25)) <= 1e-9 * abs(want)   # every residue contributes log(1/4)
+        dx.close()
+    finally:
+        O.set_exact_lse(False)
