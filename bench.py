@@ -459,6 +459,11 @@ def gpu_arm(args):
 
 
 def main():
+    # ONE JSON line on stdout: anything libraries print to fd 1 (e.g. NCCL's version banner) goes to stderr instead
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real_stdout, "w", buffering=1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)

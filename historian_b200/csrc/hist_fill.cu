@@ -1181,7 +1181,7 @@ int ensure_backward_planes(hist_pair* pr) {
   return HIST_OK;
 }
 
-int launch_fill(hist_ctx* ctx, hist_pair* const* pairs, int n, int n_dir, int only_dir) {
+int launch_fill_uniform(hist_ctx* ctx, hist_pair* const* pairs, int n, int n_dir, int only_dir) {
   int maxThreads = 1, maxDiag = 1;
   for (int k = 0; k < n; ++k) {
     maxThreads = std::max(maxThreads, pairs[k]->dev.max_threads);
@@ -1270,6 +1270,17 @@ int launch_fill(hist_ctx* ctx, hist_pair* const* pairs, int n, int n_dir, int on
   HB_CUDA(ctx, cudaFreeAsync(dptrs, ctx->stream));
   // h[] is pageable host memory: the copy above has been staged by the time cudaMemcpyAsync returns
   return HIST_OK;
+}
+
+// Narrow strips (every anti-diagonal fits one warp) and general strips use different kernels; one wide merge
+// must not push a whole level of narrow ones onto the general kernel, so a mixed batch is launched in two parts.
+int launch_fill(hist_ctx* ctx, hist_pair* const* pairs, int n, int n_dir, int only_dir) {
+  std::vector<hist_pair*> narrow, wide;
+  for (int k = 0; k < n; ++k) (pairs[k]->dev.max_threads <= 32 ? narrow : wide).push_back(pairs[k]);
+  if (narrow.empty() || wide.empty()) return launch_fill_uniform(ctx, pairs, n, n_dir, only_dir);
+  int rc = launch_fill_uniform(ctx, narrow.data(), (int)narrow.size(), n_dir, only_dir);
+  if (!rc) rc = launch_fill_uniform(ctx, wide.data(), (int)wide.size(), n_dir, only_dir);
+  return rc;
 }
 
 }  // namespace
