@@ -342,7 +342,7 @@ def gpu_arm(args):
         torch.cuda.synchronize()
 
     n_pairs = args.pairs
-    lg, guide = make_family(1 + rank)
+    lg, guide = make_family(args.family_seed + rank)
     hmm, inputs = cherry_inputs(lg, guide, n_pairs)
     ctx = capi.Context(local)
     stream = torch.cuda.ExternalStream(ctx.stream, device=local)
@@ -472,6 +472,7 @@ def main():
     ap.add_argument("--pairs", type=int, default=512, help="sibling merges per step per GPU")
     ap.add_argument("--cpu-pairs", type=int, default=96, help="merges in the cpu_baseline sample (about 15 s on one core)")
     ap.add_argument("--cpu-cols", type=int, default=64, help="columns in the EM leg's cpu_baseline sample")
+    ap.add_argument("--family-seed", type=int, default=1, help="simulation seed of rank 0's family (rank r uses seed + r)")
     ap.add_argument("--no-em", action="store_true", help="skip the EM count leg (profiling runs)")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -319,6 +319,8 @@ extern "C" int hist_ctx_create(int device, hist_ctx** out) {
   ctx->absorb_smem_configured = 0;
   ctx->staging = nullptr;
   ctx->staging_bytes = 0;
+  ctx->stream2 = nullptr;
+  ctx->ev_fork = ctx->ev_join = nullptr;
   e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
   if (e != cudaSuccess) {
     set_err(nullptr, HIST_ERR_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(e));
@@ -348,6 +350,9 @@ extern "C" void hist_ctx_destroy(hist_ctx* ctx) {
   cudaStreamSynchronize(ctx->stream);
   for (auto& e : ctx->fill_events) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
   if (ctx->staging) cudaFreeHost(ctx->staging);
+  if (ctx->stream2) { cudaStreamSynchronize(ctx->stream2); cudaStreamDestroy(ctx->stream2); }
+  if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
+  if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
   cudaStreamDestroy(ctx->stream);
   delete ctx;
 }

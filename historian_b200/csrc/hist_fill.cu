@@ -902,21 +902,23 @@ __device__ __forceinline__ void build_records(const PairDev& P, const Ring& ring
     dj_n = P.dinfo[diag_of(q + 1 + HB_SDEPTH)];
     const Recent rc = {c1.ilo, c1.width, c2.ilo, c2.width};
     const int cnt = P.nS + di.width + P.nE;
-    const LaneMeta<BWD> m = load_meta<BWD>(P, ring, di, d, t, true);
-    int4 r0, r1, r2, r3;
-    make_record<BWD>(P, ring, d, rc, m, r0, r1, r2, r3);
     int4* blk = out + (size_t)di.off * 4 + 2 * (size_t)d;   // block of diagonal d: 2 header int4's + 4 planes of cnt
     if (t == 0) {
       // header: this diagonal's layout, and the layout of the diagonal the consumer requests at the end of this step
       __stcs(blk, make_int4(di.ilo, di.width, (int)di.off, 0));
       __stcs(blk + 1, make_int4((int)dj.off, dj.width, diag_of(q + HB_SDEPTH), 0));
     }
-    if (t < cnt) {
-      int4* o = blk + 2 + t;
-      __stcs(o, r0);
-      __stcs(o + cnt, r1);
-      __stcs(o + 2 * cnt, r2);
-      __stcs(o + 3 * cnt, r3);
+    for (int tt = t; tt < max(cnt, 1); tt += 32) {   // one pass for strips of up to 32 slots, more for wider ones
+      const LaneMeta<BWD> m = load_meta<BWD>(P, ring, di, d, tt, true);
+      int4 r0, r1, r2, r3;
+      make_record<BWD>(P, ring, d, rc, m, r0, r1, r2, r3);
+      if (tt < cnt) {
+        int4* o = blk + 2 + tt;
+        __stcs(o, r0);
+        __stcs(o + cnt, r1);
+        __stcs(o + 2 * cnt, r2);
+        __stcs(o + 3 * cnt, r3);
+      }
     }
     c2 = c1; c1 = di;
   }
@@ -939,10 +941,13 @@ __global__ void __launch_bounds__(32 * HB_BUILD_WARPS) build_records_kernel(Pair
   if (bwd) build_records<true>(P, ring, recs[blockIdx.y], q0, q1); else build_records<false>(P, ring, recs[blockIdx.y], q0, q1);
 }
 
-#define HB_SSLOT 130   // int4's per queue slot: 2 header + 4 planes of up to 32 records
+#define HB_SMAX 96      // widest anti-diagonal (in slots) the streamed kernels take; wider strips use fill_kernel
+// int4's per queue slot: 2 header + 4 planes of up to `cap` records
+__host__ __device__ inline int hb_sslot(int cap) { return 2 + 4 * cap; }
 
 template <bool BWD>
 __device__ __forceinline__ void consumer_stream(const PairDev& P, const Ring& ring, const int4* __restrict__ recs, int4* queue, uint64_t* full) {
+  const int sslot = hb_sslot(ring.cap);
   float4* gA = BWD ? P.bA : P.fA;
   float2* gB = BWD ? P.bB : P.fB;
   const int nD = P.n_diag;
@@ -953,7 +958,7 @@ __device__ __forceinline__ void consumer_stream(const PairDev& P, const Ring& ri
     const int slot = q % HB_SDEPTH;
     const unsigned bytes = 32u + 64u * (unsigned)(nEdge + width);
     mbar_expect_tx(full + slot, bytes);
-    bulk_g2s(queue + slot * HB_SSLOT, recs + (size_t)off * 4 + 2 * (size_t)dd, bytes, full + slot);
+    bulk_g2s(queue + slot * sslot, recs + (size_t)off * 4 + 2 * (size_t)dd, bytes, full + slot);
   };
   if (t == 0)
     for (int q = 0; q < HB_SDEPTH && q < nD; ++q) {
@@ -967,25 +972,21 @@ __device__ __forceinline__ void consumer_stream(const PairDev& P, const Ring& ri
     const int slot = q % HB_SDEPTH;
     const int d = BWD ? nD - 1 - q : q;
     mbar_wait(full + slot, (q / HB_SDEPTH) & 1);
-    const int4* Q = queue + slot * HB_SSLOT;
+    const int4* Q = queue + slot * sslot;
     const int4 h0 = Q[0], h1 = Q[1];   // the diagonal's layout travels with its records: no global load in this loop
     DiagInfo di;
     di.ilo = h0.x; di.width = h0.y; di.off = (unsigned)h0.z; di.pad = 0;
     const int cnt = nEdge + di.width;
     const int4* R = Q + 2;
-    int4 r0 = make_int4(0, 0, 0, 0), r1 = r0, r2 = r0, r3 = r0;
-    if (t < cnt) { r0 = R[t]; r1 = R[cnt + t]; r2 = R[2 * cnt + t]; r3 = R[3 * cnt + t]; }
+    if (t == 0) ring.info[d & (ring.R - 1)] = h0;
+    for (int tt = t; tt < cnt; tt += 32)   // one cell per lane; a second pass only where a diagonal exceeds 32 slots
+      consume_store<BWD>(P, WR, ring, rc, di, d, tt, R[tt], R[cnt + tt], R[2 * cnt + tt], R[3 * cnt + tt], gA, gB);
     __syncwarp();
-    if (t == 0) {
-      ring.info[d & (ring.R - 1)] = h0;
-      if (q + HB_SDEPTH < nD) {
-        // the slot has been read by every lane; order those generic-proxy reads before the async-proxy write
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        issue(q + HB_SDEPTH, h1.z, (unsigned)h1.x, h1.y);
-      }
+    if (t == 0 && q + HB_SDEPTH < nD) {
+      // the slot has been read by every lane; order those generic-proxy reads before the async-proxy write
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      issue(q + HB_SDEPTH, h1.z, (unsigned)h1.x, h1.y);
     }
-    if (t < cnt) consume_store<BWD>(P, WR, ring, rc, di, d, t, r0, r1, r2, r3, gA, gB);
-    __syncwarp();
     rc.ilo2 = rc.ilo1; rc.w2 = rc.w1;
     rc.ilo1 = di.ilo; rc.w1 = di.width;
   }
@@ -1207,13 +1208,8 @@ int launch_fill_uniform(hist_ctx* ctx, hist_pair* const* pairs, int n, int n_dir
   PairDev** dptrs = nullptr;
   HB_CUDA(ctx, cudaMallocAsync((void**)&dptrs, n * sizeof(PairDev*), ctx->stream));
   HB_CUDA(ctx, cudaMemcpyAsync(dptrs, h.data(), n * sizeof(PairDev*), cudaMemcpyHostToDevice, ctx->stream));
-  cudaEvent_t e0 = nullptr, e1 = nullptr;
-  if (ctx->timing) {
-    HB_CUDA(ctx, cudaEventCreate(&e0));
-    HB_CUDA(ctx, cudaEventCreate(&e1));
-    HB_CUDA(ctx, cudaEventRecord(e0, ctx->stream));
-  }
-  const bool narrow = block == 32 && rows >= 4;
+  bool narrow = maxThreads <= HB_SMAX && rows >= 4;
+  for (int k = 0; k < n && narrow; ++k) narrow = pairs[k]->dev.nS <= 32 && pairs[k]->dev.nE <= 32;   // edge-slot lists are staged in 32-entry arrays
   if (n_dir == 2 || only_dir == 0) {
     // the absorb plane is part of the Forward fill (computeLogProbAbsorb, forward.cpp:183); the
     // Backward fill reuses it (BackwardMatrix is built from a ForwardMatrix, forward.cpp:975)
@@ -1249,22 +1245,20 @@ int launch_fill_uniform(hist_ctx* ctx, hist_pair* const* pairs, int n, int n_dir
     // ring rows: as many as still let the whole batch be resident at once (one wave)
     const int per_sm = (n_cta + ctx->sm_count - 1) / ctx->sm_count;
     int srows = HB_RING_MAX;
-    while (srows > 4 && (size_t)per_sm * (srows * row + HB_SDEPTH * HB_SSLOT * 16 + 2048) > 200 * 1024) srows >>= 1;
-    const size_t ssmem = srows * row + HB_SDEPTH * HB_SSLOT * 16;
+    const size_t qbytes = (size_t)HB_SDEPTH * hb_sslot(ring_cap) * 16;
+    while (srows > 4 && (size_t)per_sm * (srows * row + qbytes + 2048) > 200 * 1024) srows >>= 1;
+    const size_t ssmem = srows * row + qbytes;
+    if (ssmem > 48 * 1024) HB_CUDA(ctx, cudaFuncSetAttribute(fill_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
     const int chunk = HB_BUILD_WARPS * HB_BUILD_DIAGS;
     build_records_kernel<<<dim3((maxDiag + chunk - 1) / chunk, n_cta), 32 * HB_BUILD_WARPS, 0, ctx->stream>>>(dptrs, (int4* const*)rec_buf, n_dir,
                                                                                                             only_dir, ring_cap, srows);
     fill_stream_kernel<<<n_cta, 32, ssmem, ctx->stream>>>(dptrs, (int4* const*)rec_buf, n_dir, only_dir, ring_cap, srows);
     ctx->launches += 1;
-  } else if (narrow)
+  } else if (narrow && maxThreads <= 32)
     fill_narrow_kernel<<<n * n_dir, 32 * (1 + HB_NPROD), smem + HB_DEPTH * 128 * sizeof(int4), ctx->stream>>>(dptrs, n_dir, only_dir, ring_cap, rows);
   else
     fill_kernel<<<n * n_dir, block, smem, ctx->stream>>>(dptrs, n_dir, only_dir, ring_cap, rows);
   ctx->launches += 1;
-  if (ctx->timing) {
-    HB_CUDA(ctx, cudaEventRecord(e1, ctx->stream));
-    ctx->fill_events.push_back({e0, e1});
-  }
   HB_CUDA(ctx, cudaGetLastError());
   if (rec_buf) HB_CUDA(ctx, cudaFreeAsync(rec_buf, ctx->stream));
   HB_CUDA(ctx, cudaFreeAsync(dptrs, ctx->stream));
@@ -1276,10 +1270,37 @@ int launch_fill_uniform(hist_ctx* ctx, hist_pair* const* pairs, int n, int n_dir
 // must not push a whole level of narrow ones onto the general kernel, so a mixed batch is launched in two parts.
 int launch_fill(hist_ctx* ctx, hist_pair* const* pairs, int n, int n_dir, int only_dir) {
   std::vector<hist_pair*> narrow, wide;
-  for (int k = 0; k < n; ++k) (pairs[k]->dev.max_threads <= 32 ? narrow : wide).push_back(pairs[k]);
-  if (narrow.empty() || wide.empty()) return launch_fill_uniform(ctx, pairs, n, n_dir, only_dir);
-  int rc = launch_fill_uniform(ctx, narrow.data(), (int)narrow.size(), n_dir, only_dir);
-  if (!rc) rc = launch_fill_uniform(ctx, wide.data(), (int)wide.size(), n_dir, only_dir);
+  for (int k = 0; k < n; ++k) (pairs[k]->dev.max_threads <= 32 ? narrow : wide).push_back(pairs[k]);   // wide: streamed up to HB_SMAX slots, else general
+  cudaEvent_t e0 = nullptr, e1 = nullptr;   // one event pair per fill call (bench.py's roofline leg)
+  if (ctx->timing) {
+    HB_CUDA(ctx, cudaEventCreate(&e0));
+    HB_CUDA(ctx, cudaEventCreate(&e1));
+    HB_CUDA(ctx, cudaEventRecord(e0, ctx->stream));
+  }
+  int rc = HIST_OK;
+  if (narrow.empty() || wide.empty()) {
+    rc = launch_fill_uniform(ctx, pairs, n, n_dir, only_dir);
+  } else {
+    // the few general strips are latency-bound on their own (one CTA each): run them beside the narrow part
+    if (!ctx->stream2) {
+      HB_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking));
+      HB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
+      HB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
+    }
+    HB_CUDA(ctx, cudaEventRecord(ctx->ev_fork, ctx->stream));
+    HB_CUDA(ctx, cudaStreamWaitEvent(ctx->stream2, ctx->ev_fork, 0));
+    cudaStream_t main_stream = ctx->stream;
+    ctx->stream = ctx->stream2;
+    rc = launch_fill_uniform(ctx, wide.data(), (int)wide.size(), n_dir, only_dir);
+    ctx->stream = main_stream;
+    if (!rc) rc = launch_fill_uniform(ctx, narrow.data(), (int)narrow.size(), n_dir, only_dir);
+    HB_CUDA(ctx, cudaEventRecord(ctx->ev_join, ctx->stream2));
+    HB_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_join, 0));
+  }
+  if (ctx->timing) {
+    HB_CUDA(ctx, cudaEventRecord(e1, ctx->stream));
+    ctx->fill_events.push_back({e0, e1});
+  }
   return rc;
 }
 

@@ -190,6 +190,9 @@ struct hist_ctx {
   // optional per-kernel timing of the fill launches (bench.py's roofline leg)
   bool timing;
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> fill_events;
+  // second stream + fork/join events: the general-strip part of a mixed fill batch runs beside the narrow part
+  cudaStream_t stream2;
+  cudaEvent_t ev_fork, ev_join;
   // pinned staging buffer for host-built layouts (grown on demand)
   char* staging;
   size_t staging_bytes;
