@@ -12,6 +12,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 
@@ -271,6 +272,9 @@ namespace {
 template <class F>
 void parallel_for(int n, int grain, F fn) {
   int nthreads = (int)std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 16u);
+  if (const char* lw = getenv("LOCAL_WORLD_SIZE"))  // one process per GPU: share the host cores between the ranks of the box
+    nthreads = std::max(2, (int)std::thread::hardware_concurrency() / std::max(1, atoi(lw)));
+  nthreads = std::min(nthreads, 16);
   nthreads = std::max(1, std::min(nthreads, n / std::max(1, grain)));
   if (nthreads <= 1) {
     for (int k = 0; k < n; ++k) fn(k);
