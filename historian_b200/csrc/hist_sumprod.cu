@@ -191,6 +191,7 @@ struct SpArgs {
                            // per-level index ranges that hold ungapped nodes
 };
 
+// (forcing more resident blocks through a register cap was measured: 48 / 40 / 32 registers all spill and lose)
 __global__ void __launch_bounds__(SP_THREADS) sumprod_columns_kernel(SpDev S, SpArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int A = S.A, C = S.C, N = S.N, CA = C * A, CAA = C * A * A;
