@@ -38,7 +38,7 @@ BRANCH = 0.05
 N_LEAVES = 1024
 ROOT_LEN = 1000
 # dram__bytes_read.sum + dram__bytes_write.sum of the three fill kernels per launch, from the ncu --set full capture under profiles/ (None = not captured)
-FILL_TRAFFIC_BYTES = 7.42e9   # profiles/r01_fill_and_sumprod_ncu_details_final.txt: absorb 0.17 + build_records 3.19 + fill_stream 4.06 GB
+FILL_TRAFFIC_BYTES = 7.44e9   # profiles/r01_fill_ncu_details_final.txt: absorb 0.17 + build_records 3.21 + fill_stream 4.06 GB
 ALG_BYTES_PER_CELL = 80.0   # 40 B written once + 40 B read once per DP cell (reference layout)
 METRIC = "profile Forward/Backward cells/s (GCUPS)"
 UNIT = "Gcells/s"

@@ -73,13 +73,20 @@ __device__ __forceinline__ double block_reduce(double v, double* red) {
   return r;
 }
 
-__global__ void prepare_side_kernel(PairDev* const* __restrict__ pairs) {
-  extern __shared__ double sm[];
+// WARP: C*A <= 32, one warp per state and blockDim.y states per CTA (a CTA per state would be a million
+// 32-thread CTAs for a level of merges); otherwise one CTA per state.  Same arithmetic either way.
+template <bool WARP>
+__global__ void prepare_side_kernel(PairDev* const* __restrict__ pairs, int sm_stride) {
+  extern __shared__ double sm_all[];
+  double* sm = WARP ? sm_all + (size_t)threadIdx.y * sm_stride : sm_all;
   const PairDev& P = *pairs[blockIdx.y];
   const bool isY = blockIdx.z == 1;
   const SideDev& s = isY ? P.y : P.x;
-  const int i = blockIdx.x;
+  const int i = WARP ? blockIdx.x * blockDim.y + threadIdx.y : blockIdx.x;
   if (i >= s.n) return;
+  auto sync = [&]() { if (WARP) __syncwarp(); else __syncthreads(); };
+  auto red_max = [&](double v, double* r) { return WARP ? warp_max(v) : block_reduce<true>(v, r); };
+  auto red_sum = [&](double v, double* r) { return WARP ? warp_sum(v) : block_reduce<false>(v, r); };
   const int C = P.C, A = P.A, K = P.K, Kp = P.Kp;
   const double* __restrict__ subMat = isY ? P.r_sub : P.l_sub;
   const double* __restrict__ logRoot = P.log_root;
@@ -108,11 +115,11 @@ __global__ void prepare_side_kernel(PairDev* const* __restrict__ pairs) {
     for (int d = 0; d < A; ++d) m = fmax(m, la[k * A + d]);
     mc[k] = m;
   }
-  __syncthreads();
+  sync();
   const int c = k < K ? k / A : 0, a = k - c * A;
   const double lak = k < K ? la[k] : -INFINITY;
   if (k < K) e_abs[k] = mc[c] == -INFINITY ? 0.0 : exp(lak - mc[c]);
-  __syncthreads();
+  sync();
   double subv = -INFINITY;
   if (k < K) {
     const double* Pm = subMat + ((size_t)c * A + a) * A;
@@ -122,14 +129,14 @@ __global__ void prepare_side_kernel(PairDev* const* __restrict__ pairs) {
     s.sub[(size_t)i * K + k] = subv;
   }
   // block reductions: max of sub -> ex; rootsub; ins
-  const double mx = block_reduce<true>(subv, red);
+  const double mx = red_max(subv, red);
   const double rterm = k < K ? logRoot[k] + subv : -INFINITY;
-  const double lr = block_reduce<true>(rterm, red);
-  const double racc = block_reduce<false>(lr > -INFINITY && k < K ? exp(rterm - lr) : 0.0, red);
+  const double lr = red_max(rterm, red);
+  const double racc = red_sum(lr > -INFINITY && k < K ? exp(rterm - lr) : 0.0, red);
   const double s_root = lr > -INFINITY ? lr + log(racc) : -INFINITY;
   const double iterm = k < K ? logCptWeight[c] + logIns[k] + lak : -INFINITY;
-  const double li = block_reduce<true>(iterm, red);
-  const double iacc = block_reduce<false>(li > -INFINITY && k < K ? exp(iterm - li) : 0.0, red);
+  const double li = red_max(iterm, red);
+  const double iacc = red_sum(li > -INFINITY && k < K ? exp(iterm - li) : 0.0, red);
   const double s_ins = li > -INFINITY ? li + log(iacc) : -INFINITY;
   const int ex = mx > -INFINITY ? (int)floor(mx / HB_LN2) : 0;
   if (k < Kp) {
@@ -1002,8 +1009,13 @@ extern "C" int hist_pair_prepare_batch(hist_ctx* ctx, int32_t n, const hist_prof
   PairDev* const* dptrs = (PairDev* const*)(arena->dev + ptr_off);
   if (!rc) {
     const int threads = std::max(32, (maxKp + 31) / 32 * 32);
-    const size_t smem = (size_t)(maxKC + 32) * sizeof(double);
-    prepare_side_kernel<<<dim3(maxN, n, 2), threads, smem, ctx->stream>>>(dptrs);
+    const int stride = maxKC + 32;
+    if (threads == 32) {
+      const int per_cta = 8;
+      prepare_side_kernel<true><<<dim3((maxN + per_cta - 1) / per_cta, n, 2), dim3(32, per_cta), (size_t)per_cta * stride * sizeof(double), ctx->stream>>>(dptrs, stride);
+    } else {
+      prepare_side_kernel<false><<<dim3(maxN, n, 2), threads, (size_t)stride * sizeof(double), ctx->stream>>>(dptrs, stride);
+    }
     prepare_trans_kernel<<<dim3((maxNt + 127) / 128, n, 2), 128, 0, ctx->stream>>>(dptrs);
     pack_meta_kernel<<<dim3((maxN + 127) / 128, n, 2), 128, 0, ctx->stream>>>(dptrs);
     const int chunks = std::max(1, std::min(maxDiag / 64 + 1, std::max(8, (4 * ctx->sm_count + n - 1) / n)));  // >= 8 chunks of diagonals per pair
