@@ -63,6 +63,8 @@ def load():
     lib.hist_trace_best_forward.argtypes = [vp, D.Cell, C.POINTER(D.Cell), C.c_int64, D.c_int64_p]
     lib.hist_trace_sample.argtypes = [vp, D.c_uint32_p, C.c_int32, C.POINTER(D.Cell), C.c_int64, D.c_int64_p]
     lib.hist_posterior_cells.argtypes = [vp, C.c_double, C.POINTER(D.Cell), D.c_double_p, C.c_int64, D.c_int64_p]
+    lib.hist_fb_counts.argtypes = [vp, D.c_double_p, D.c_double_p, D.c_double_p, D.c_double_p, C.POINTER(D.Cell), D.c_double_p,
+                                   C.c_int64, D.c_int64_p]
     lib.hist_profile_eliminate.argtypes = [vp, C.POINTER(D.Cell), C.c_int64, C.c_int32, C.POINTER(D.ElimResult)]
     lib.hist_sumprod_create.argtypes = [vp, C.POINTER(D.ModelDesc), C.POINTER(D.TreeDesc), C.POINTER(vp)]
     lib.hist_sumprod_destroy.argtypes = [vp]
@@ -376,6 +378,21 @@ class Pair:
         lpp = np.empty(cap)
         self.ctx.check(self.ctx.lib.hist_posterior_cells(self.h, float(min_post_prob), buf, _p(lpp, C.c_double), cap, C.byref(n)))
         return self._cells_np(buf, n.value), lpp[:n.value].copy()
+
+    def fb_counts(self, waits):
+        """Numeric part of BackwardMatrix::getCounts (forward.cpp:1183-1214): (indel[6], w_x[2,xn], w_y[2,yn],
+        match cells [n,3], match weights [n]); see hist_fb_counts in include/historian_b200.h."""
+        waits = np.ascontiguousarray(waits, np.float64)
+        assert waits.shape == (6,)
+        xn, yn = int(self.info.x_size), int(self.info.y_size)
+        indel, wx, wy = np.zeros(6), np.zeros((2, xn)), np.zeros((2, yn))
+        cap = max(1, int(self.info.n_cells))
+        buf = (D.Cell * cap)()
+        cw = np.empty(cap)
+        n = C.c_int64()
+        self.ctx.check(self.ctx.lib.hist_fb_counts(self.h, _p(waits, C.c_double), _p(indel, C.c_double), _p(wx, C.c_double),
+                                                   _p(wy, C.c_double), buf, _p(cw, C.c_double), cap, C.byref(n)))
+        return indel, wx, wy, self._cells_np(buf, n.value), cw[:n.value].copy()
 
     def eliminate(self, cells, strategy=D.COLLAPSE_CHAINS):
         """Numeric core of ForwardMatrix::makeProfile (forward.cpp:686-843) on a sorted cell set [n,3].

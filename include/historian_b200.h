@@ -248,6 +248,27 @@ int hist_trace_best_forward(hist_pair* pair, hist_cell start, hist_cell* path, i
 int hist_posterior_cells(hist_pair* pair, double min_post_prob, hist_cell* cells, double* log_post,
                          int64_t capacity, int64_t* n);
 
+/* BackwardMatrix::getCounts (forward.cpp:1183-1214), numeric part.  Requires both fills.
+ *   waits[6]  = { l.t, r.t, l.insWait, l.delWait, r.insWait, r.delWait } of the PairHMM's two
+ *               ProbModels (model.cpp:374-391), the constants transitionEigenCounts adds
+ *               (forward.cpp:579-652);
+ *   indel[6]  = posterior-weighted ins, del, insExt, delExt, insTime, delTime summed over every
+ *               (cell, state, incoming transition); profile transitions are taken to carry no
+ *               counts of their own;
+ *   w_x[2][x.n_states] = posterior weight of the alignment column of each x state, [0] without
+ *               and [1] with a wildcard parent row (getAlignmentColumn, forward.cpp:940-973: IIW and
+ *               null-state cells / IMD cells); w_y[2][y.n_states] likewise (IMI / IDM);
+ *   cells, cell_w = the IMM cells whose two states both emit, in (xpos, ypos) order, with
+ *               their posterior weights: one column (x column + y column + wildcard parent) each.
+ * The caller appends those columns, weighted, to a hist_sumprod_columns batch; that is what
+ * accumulateCachedEigenCounts does one column at a time (forward.cpp:903-938).  The
+ * reference's per-row insert-column cache keeps an EMPTY column for a row whose first
+ * envelope cell is on ypos == 0 (forward.cpp:905-918 with :942); w_x[0] / w_y[0] are zero for
+ * such rows / columns so the counts stay identical to the reference's.
+ * Returns HIST_ERR_CAPACITY (with *n_cells set) when `capacity` is too small. */
+int hist_fb_counts(hist_pair* pair, const double* waits, double* indel, double* w_x, double* w_y,
+                   hist_cell* cells, double* cell_w, int64_t capacity, int64_t* n_cells);
+
 /* ------------------------------------------------------------------ makeProfile
  * Numeric core of ForwardMatrix::makeProfile (forward.cpp:686-843): given the
  * sorted cell set (must contain SSS=(0,0,IMM) and EEE), decide retained cells

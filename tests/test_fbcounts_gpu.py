@@ -1,0 +1,99 @@
+"""BackwardMatrix::getCounts (forward.cpp:1183-1214) on the device (hist_fb_counts + a weighted
+hist_sumprod_columns batch, driven by historian_b200/fbcounts.py) against the REAL reference's getCounts() on
+two-leaf families: tests/golden/fbcounts_*.npz, made by tools/make_golden_fbcounts.py from
+oracle/ref_dump_fbcounts.cpp.  The fixtures hold only sequences, branch lengths, the band and the reference's
+outputs; model, PairHMM, leaf profiles, envelope and eigen-system are rebuilt here through the product path.
+
+Tolerance.  The reference adds log-probabilities with a lookup-table log-sum-exp (<= 4.6e-5 per binary op,
+logsumexp.h:47) in both fills; the device fills are exact-sum FP32-mantissa + exponent.
+Posterior weights therefore differ by a few 1e-4 relative; counts are compared at 2e-3 of the largest count of
+their block, the Forward likelihood at 2e-3 absolute (the same bound test_fill_gpu.py uses against goldens)."""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+import helpers as H
+from historian_b200 import capi, descs as D, fbcounts, model as M
+
+pytestmark = pytest.mark.gpu
+FIX = sorted(glob.glob(os.path.join(H.GOLDEN_DIR, "fbcounts_*.npz")))
+IDS = [os.path.basename(f)[9:-4] for f in FIX]
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = capi.Context(0)
+    yield c
+    c.close()
+
+
+def rate_model(spec):
+    f = spec.split(":")
+    m = M.RateModel.preset(f[0])
+    return m.gamma(int(f[1]), float(f[2])) if len(f) == 3 else m
+
+
+def run_case(ctx, d):
+    model = rate_model(bytes(d["preset"]).decode())
+    x, y = bytes(d["x_seq"]).decode(), bytes(d["y_seq"]).decode()
+    tl, tr = (float(v) for v in d["branch"])
+    band = int(d["band"][0])
+    env = None
+    if band >= 0:
+        env = D.Envelope.from_guide_rows(d["x_row"] != ord("-"), d["y_row"] != ord("-"), band)
+    dev = ctx.upload_sequences([x, y], model.alphabet, components=model.components)
+    lp, rp = M.ProbModel(model, tl), M.ProbModel(model, tr)
+    hmm = M.pair_hmm(model, tl, tr)
+    pair = ctx.prepare(dev[0], dev[1], hmm, env)
+    lp_end = pair.forward()
+    pair.backward()
+    sp = ctx.sumprod(D.SumProdModel.from_rate_model(model), D.TreeTopology([2, 2, -1], [tl, tr, 0.0]))
+    waits = fbcounts.prob_model_waits(lp, rp)
+    counts = fbcounts.fb_counts(pair, sp, waits, fbcounts.leaf_columns(x, 0, 3), fbcounts.leaf_columns(y, 1, 3), 2, lp_end)
+    root, sub = sp.transform_counts(counts)
+    raw = pair.fb_counts(waits)
+    sp.close()
+    return lp_end, waits, counts, root, sub, raw
+
+
+def near(a, b, rel):
+    a, b = np.asarray(a, float), np.asarray(b, float)
+    return bool(np.all(np.abs(a - b) <= rel * max(1e-12, np.abs(b).max())))
+
+
+@pytest.mark.parametrize("path", FIX, ids=IDS)
+def test_counts_match_reference_getcounts(ctx, path):
+    d = H.load_golden(path)
+    lp_end, waits, counts, root, sub, _ = run_case(ctx, d)
+    assert np.allclose(waits, d["waits"], rtol=1e-12, atol=0)
+    assert abs(lp_end - d["lp_end"][0]) <= 2e-3
+    assert counts[6] == lp_end
+    ref = d["indel"]
+    assert near(counts[0:4], ref[0:4], 2e-3), (counts[:6], ref[:6])      # ins, del, insExt, delExt
+    assert near(counts[4:6], ref[4:6], 2e-3), (counts[:6], ref[:6])      # insTime, delTime
+    assert near(root, d["root_count"], 2e-3)
+    assert near(sub, d["sub_count"], 2e-3)
+
+
+@pytest.mark.parametrize("path", FIX, ids=IDS)
+def test_posterior_weights_are_consistent(ctx, path):
+    """Size-independent properties: every x residue is absorbed exactly once along any path, so its posterior
+    weights over match, deletion and insertion columns sum to one (up to the insert-cache quirk, which only
+    zeroes weights); the run is bit-reproducible."""
+    d = H.load_golden(path)
+    _, waits, counts, _, _, (indel, w_x, w_y, cells, cell_w) = run_case(ctx, d)
+    _, _, counts2, _, _, raw2 = run_case(ctx, d)
+    assert H.same(counts, counts2) and all(H.same(a, b) for a, b in zip((indel, w_x, w_y, cells, cell_w), raw2))
+    xn, yn = w_x.shape[1], w_y.shape[1]
+    mx, my = np.zeros(xn), np.zeros(yn)
+    np.add.at(mx, cells[:, 0], cell_w)
+    np.add.at(my, cells[:, 1], cell_w)
+    banded = int(d["band"][0]) >= 0
+    for w, m, n in ((w_x, mx, xn), (w_y, my, yn)):
+        tot = (w[0] + w[1] + m)[1:n - 1]
+        assert np.all(tot <= 1 + 1e-4)
+        if banded:   # rows away from the matrix edge keep their insert weight
+            assert np.all(np.abs(tot[8:-8] - 1) <= 1e-4), tot
+    assert np.all(cells[:, 2] == D.IMM) and np.all(np.diff(cells[:, 0] * 100000 + cells[:, 1]) > 0)

@@ -1,0 +1,59 @@
+#!/usr/bin/env python3
+"""Generates tests/golden/fbcounts_*.npz from the REAL reference: BackwardMatrix::getCounts
+(forward.cpp:1183-1214) on two-leaf families, through oracle/_ref/bin/ref_dump_fbcounts
+(oracle/ref_dump_fbcounts.cpp, linked against the unmodified reference objects).
+
+Run in the build container (needs /root/reference and `make -C oracle ref`)."""
+import os
+import subprocess
+import sys
+import tempfile
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from historian_b200 import descs as D
+
+BIN = os.path.join(ROOT, "oracle", "_ref", "bin")
+OUT = os.path.join(ROOT, "tests", "golden")
+
+CASES = [
+    # name, preset spec, generate args, branch lengths, band
+    ("fbcounts_lg_band4", "lg", ["-preset", "lg", "-rootlen", "30", "-seed", "5", "-insrate", "0.06", "-delrate", "0.06"], (0.3, 0.5), 4),
+    ("fbcounts_lg_noband", "lg", ["-preset", "lg", "-rootlen", "18", "-seed", "9", "-insrate", "0.08", "-delrate", "0.08"], (0.4, 0.2), -1),
+    ("fbcounts_jc_gamma2_band3", "jc:2:1", ["-preset", "jc", "-gamma", "2", "-rootlen", "40", "-seed", "2", "-insrate", "0.05", "-delrate", "0.05"], (0.25, 0.25), 3),
+]
+
+
+def main():
+    for name, spec, gen, (tl, tr), band in CASES:
+        with tempfile.TemporaryDirectory() as tmp:
+            tf = os.path.join(tmp, "tree.nh")
+            open(tf, "w").write("(x:%g,y:%g);\n" % (tl, tr))
+            out = subprocess.run([os.path.join(BIN, "historian"), "generate"] + gen + [tf, "-output", "fasta"],
+                                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, check=True).stdout.decode()
+            seqs, cur = {}, None
+            for line in out.splitlines():
+                if line.startswith(">"):
+                    cur = line[1:].strip()
+                    seqs[cur] = ""
+                elif cur:
+                    seqs[cur] += line.strip()
+            rows = {k: seqs[k] for k in ("x", "y")}
+            keep = [i for i in range(len(rows["x"])) if any(v[i] not in "-." for v in rows.values())]
+            gf = os.path.join(tmp, "pair.fa")
+            with open(gf, "w") as f:
+                for k, v in rows.items():
+                    f.write(">%s\n%s\n" % (k, "".join(v[i] for i in keep)))
+            binf = os.path.join(tmp, "d.bin")
+            subprocess.run([os.path.join(BIN, "ref_dump_fbcounts"), binf, "preset:" + spec, gf, tf, str(band)], check=True,
+                           stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+            d = D.read_dump(binf)
+        d = {k: (np.frombuffer(v.encode(), np.uint8) if isinstance(v, str) else v) for k, v in d.items()}
+        np.savez_compressed(os.path.join(OUT, name + ".npz"), **d)
+        print(name, "x", len(d["x_seq"]), "y", len(d["y_seq"]), "lp_end %.4f" % d["lp_end"][0], "indel", np.round(d["indel"], 4))
+
+
+if __name__ == "__main__":
+    main()
