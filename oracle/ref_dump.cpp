@@ -133,8 +133,8 @@ static void dumpEnv(const string& pfx, const GuideAlignmentEnvelope& e) {
 }
 
 struct FwdPeek : ForwardMatrix {
-  FwdPeek(const Profile& x, const Profile& y, const PairHMM& hmm, AlignRowIndex row, const GuideAlignmentEnvelope& env)
-      : ForwardMatrix(x, y, hmm, row, env) {}
+  FwdPeek(const Profile& x, const Profile& y, const PairHMM& hmm, AlignRowIndex row, const GuideAlignmentEnvelope& env, SumProduct* sp = NULL)
+      : ForwardMatrix(x, y, hmm, row, env, sp) {}
   void dumpTables(const string& pfx) {
     const int C = components(), A = (int)alphSize;
     vector<double> sx((size_t)xSize * C * A, -numeric_limits<double>::infinity()), sy((size_t)ySize * C * A, -numeric_limits<double>::infinity());
@@ -231,6 +231,22 @@ int main(int argc, char** argv) {
   putI("max_profile_states", {(int32_t)recon.maxProfileStates()});
   putD("min_post_prob", {recon.minPostProb});
 
+  // REF_DUMP_COUNTS=1: also run BackwardMatrix::getCounts (forward.cpp:1183-1214) at the dumped nodes, with the
+  // SumProduct attached as recon.cpp:932-934 does.  The profiling strategy above carries no Count* flags, so
+  // profile transitions hold no counts of their own.
+  const bool wantCounts = getenv("REF_DUMP_COUNTS") != NULL;
+  SumProduct* sumProd = wantCounts ? new SumProduct(model, dataset.tree) : NULL;
+  if (wantCounts) {
+    vector<int32_t> parent;
+    vector<double> blen;
+    for (TreeNodeIndex n = 0; n < dataset.tree.nodes(); ++n) {
+      parent.push_back((int32_t)dataset.tree.parentNode(n));
+      blen.push_back(n == dataset.tree.root() ? 0. : dataset.tree.branchLength(n));
+    }
+    putI("tree.parent", parent);
+    putD("tree.branch_length", blen);
+  }
+
   vector<int32_t> dumped;
   map<int, Profile> prof;
   for (TreeNodeIndex node = 0; node < dataset.tree.nodes(); ++node) {
@@ -251,7 +267,7 @@ int main(int argc, char** argv) {
     while (true) {  // recon.cpp:954-975
       env = haveGuide ? GuideAlignmentEnvelope(dataset.guide, dataset.closestLeaf[l], dataset.closestLeaf[r], maxDist)
                       : GuideAlignmentEnvelope();
-      forward = new FwdPeek(lProf, rProf, hmm, node, env);
+      forward = new FwdPeek(lProf, rProf, hmm, node, env, sumProd);
       if (forward->lpEnd > -numeric_limits<double>::infinity()) break;
       if (maxDist < 0) { cerr << "zero likelihood" << endl; return 1; }
       if (maxDist * 2 > (int)alignPathColumns(dataset.guide)) maxDist = -1;
@@ -297,6 +313,30 @@ int main(int argc, char** argv) {
         putI(pfx + "post_cells", pc, {(uint64_t)pl.size(), 3});
         putD(pfx + "post_lp", pl);
         putD(pfx + "post_threshold", {recon.minPostProb > 0 ? recon.minPostProb : .01});
+      }
+      if (wantCounts) {
+        const int N = (int)dataset.tree.nodes();
+        for (int side = 0; side < 2; ++side) {
+          const Profile& p = side ? rProf : lProf;
+          vector<uint8_t> cols(p.size() * (size_t)N, (uint8_t)'-');
+          for (size_t s = 0; s < p.size(); ++s)
+            for (const auto& rc : p.alignColumn(s)) cols[s * N + rc.first] = (uint8_t)rc.second;
+          putB(pfx + (side ? "y." : "x.") + "align_col", cols, {(uint64_t)p.size(), (uint64_t)N});
+        }
+        const EigenCounts ec = backward->getCounts();
+        const EventCounts ev = ec.transform(model);
+        const IndelCounts& ic = ev.indelCounts;
+        putD(pfx + "fbc.indel", {ic.ins, ic.del, ic.insExt, ic.delExt, ic.insTime, ic.delTime, ic.lp});
+        const int C = model.components(), A = model.alphabetSize();
+        vector<double> rootCount, subCount;
+        for (int c = 0; c < C; ++c)
+          for (int i = 0; i < A; ++i) {
+            rootCount.push_back(ev.rootCount[c][i]);
+            for (int j = 0; j < A; ++j) subCount.push_back(ev.subCount[c][i][j]);
+          }
+        putD(pfx + "fbc.root_count", rootCount, {(uint64_t)C, (uint64_t)A});
+        putD(pfx + "fbc.sub_count", subCount, {(uint64_t)C, (uint64_t)A, (uint64_t)A});
+        putD(pfx + "fbc.waits", {lProbs.t, rProbs.t, lProbs.insWait, lProbs.delWait, rProbs.insWait, rProbs.delWait});
       }
       // three sampled traces from a COPY of the generator (does not disturb the run)
       {

@@ -7,7 +7,7 @@ outputs; model, PairHMM, leaf profiles, envelope and eigen-system are rebuilt he
 Tolerance.  The reference adds log-probabilities with a lookup-table log-sum-exp (<= 4.6e-5 per binary op,
 logsumexp.h:47) in both fills; the device fills are exact-sum FP32-mantissa + exponent.
 Posterior weights therefore differ by a few 1e-4 relative; counts are compared at 2e-3 of the largest count of
-their block, the Forward likelihood at 2e-3 absolute (the same bound test_fill_gpu.py uses against goldens)."""
+their block, the Forward likelihood at 5e-3 + 1e-4 relative (the bound test_fill_gpu.py uses against goldens)."""
 import glob
 import os
 
@@ -18,8 +18,11 @@ import helpers as H
 from historian_b200 import capi, descs as D, fbcounts, model as M
 
 pytestmark = pytest.mark.gpu
-FIX = sorted(glob.glob(os.path.join(H.GOLDEN_DIR, "fbcounts_*.npz")))
+ALL = sorted(glob.glob(os.path.join(H.GOLDEN_DIR, "fbcounts_*.npz")))
+FIX = [f for f in ALL if "_tree" not in os.path.basename(f)]         # two leaf profiles
 IDS = [os.path.basename(f)[9:-4] for f in FIX]
+TREES = [f for f in ALL if "_tree" in os.path.basename(f)]           # root merge of a progressive reconstruction
+TREE_IDS = [os.path.basename(f)[9:-4] for f in TREES]
 
 
 @pytest.fixture(scope="module")
@@ -68,7 +71,7 @@ def test_counts_match_reference_getcounts(ctx, path):
     d = H.load_golden(path)
     lp_end, waits, counts, root, sub, _ = run_case(ctx, d)
     assert np.allclose(waits, d["waits"], rtol=1e-12, atol=0)
-    assert abs(lp_end - d["lp_end"][0]) <= 2e-3
+    assert abs(lp_end - d["lp_end"][0]) <= 5e-3 + 1e-4 * abs(lp_end)
     assert counts[6] == lp_end
     ref = d["indel"]
     assert near(counts[0:4], ref[0:4], 2e-3), (counts[:6], ref[:6])      # ins, del, insExt, delExt
@@ -91,10 +94,38 @@ def test_posterior_weights_are_consistent(ctx, path):
     np.add.at(mx, cells[:, 0], cell_w)
     np.add.at(my, cells[:, 1], cell_w)
     banded = int(d["band"][0]) >= 0
-    for w, m, n in ((w_x, mx, xn), (w_y, my, yn)):
+    for w, m, n, side in ((w_x, mx, xn, "x"), (w_y, my, yn, "y")):
         tot = (w[0] + w[1] + m)[1:n - 1]
         kept = w[0][1:n - 1] > 0          # rows whose insert-column cache the reference did not leave empty
         assert np.all(tot <= 1 + 1e-3)
         assert np.all(np.abs(tot[kept] - 1) <= 1e-3), tot
-        assert kept.sum() >= (n - 2) // 2 if banded else not kept.any()
+        if side == "y" or not banded:     # xNearStart[0] puts all of row 0 inside the envelope (forward.cpp:58): the
+            assert not kept.any()         # y cache is always filled from xpos == 0; without a band so is the x cache
+        else:
+            assert kept.sum() >= (n - 2) // 2
     assert np.all(cells[:, 2] == D.IMM) and np.all(np.diff(cells[:, 0] * 100000 + cells[:, 1]) > 0)
+
+
+@pytest.mark.parametrize("path", TREES, ids=TREE_IDS)
+def test_root_merge_of_a_progressive_reconstruction(ctx, path):
+    """getCounts at the root of a 4- and a 6-leaf reconstruction: DAG profiles with null states, alignment
+    columns spanning several tree rows (Profile::alignColumn, profile.cpp:100-110, dumped by the reference), a
+    gamma mixture.  Profiles, PairHMM and envelope come from the reference's dump, as in test_fill_gpu.py."""
+    d = H.load_golden(path)
+    root = int(d["root"][0])
+    pfx = "n%d." % root
+    x, y, hmm, env = H.node_inputs(d, root)
+    model = rate_model(bytes(d["preset"]).decode())
+    pair = ctx.prepare(ctx.upload(x), ctx.upload(y), hmm, env)
+    lp_end = pair.forward()
+    pair.backward()
+    assert abs(lp_end - d[pfx + "lp_end"][0]) <= 5e-3 + 1e-4 * abs(lp_end)
+    sp = ctx.sumprod(D.SumProdModel.from_rate_model(model), D.TreeTopology(d["tree.parent"], d["tree.branch_length"]))
+    counts = fbcounts.fb_counts(pair, sp, d[pfx + "fbc.waits"], d[pfx + "x.align_col"], d[pfx + "y.align_col"], root, lp_end)
+    rc, sub = sp.transform_counts(counts)
+    sp.close()
+    ref = d[pfx + "fbc.indel"]
+    assert near(counts[0:4], ref[0:4], 2e-3), (counts[:6], ref[:6])
+    assert near(counts[4:6], ref[4:6], 2e-3), (counts[:6], ref[:6])
+    assert near(rc, d[pfx + "fbc.root_count"], 2e-3)
+    assert near(sub, d[pfx + "fbc.sub_count"], 2e-3)

@@ -26,7 +26,40 @@ CASES = [
 ]
 
 
+TREE_CASES = [
+    # name, leaves, branch length, preset, generate args, recon args: getCounts at the ROOT of a progressive reconstruction
+    # (internal profiles with null states and multi-row alignment columns; transitions carry no counts)
+    ("fbcounts_tree4_lg", 4, 0.25, "lg", ["-preset", "lg", "-rootlen", "24", "-seed", "4", "-insrate", "0.06", "-delrate", "0.06"],
+     ["-preset", "lg", "-band", "5", "-profmaxstates", "300", "-seed", "3", "-profsamples", "8"]),
+    ("fbcounts_tree6_jc_gamma2", 6, 0.2, "jc:2:1", ["-preset", "jc", "-gamma", "2", "-rootlen", "30", "-seed", "8"],
+     ["-preset", "jc", "-gamma", "2", "-band", "4", "-profmaxstates", "300", "-seed", "5", "-profsamples", "6"]),
+]
+KEEP = ("x.", "y.", "hmm.", "env.", "fbc.")
+
+
+def tree_cases():
+    import make_golden as G
+    for name, n, bl, spec, gen, rec in TREE_CASES:
+        with tempfile.TemporaryDirectory() as tmp:
+            tf, gf = G.simulate(tmp, G.balanced(n, bl), gen, n)
+            binf = os.path.join(tmp, "d.bin")
+            root = 2 * n - 2
+            subprocess.run([os.path.join(BIN, "ref_dump"), binf, str(root), "sample", "-guide", gf, "-tree", tf] + rec, check=True,
+                           cwd=G.REF, env=dict(os.environ, REF_DUMP_COUNTS="1"), stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+            d = D.read_dump(binf)
+        pfx = "n%d." % root
+        out = {"preset": spec, "root": np.array([root], np.int32)}
+        for k, v in d.items():
+            if k.startswith("tree.") or k in (pfx + "lp_end", pfx + "children") or (k.startswith(pfx) and k[len(pfx):].startswith(KEEP)):
+                out[k] = v
+        out = {k: (np.frombuffer(v.encode(), np.uint8) if isinstance(v, str) else v) for k, v in out.items()}
+        np.savez_compressed(os.path.join(OUT, name + ".npz"), **out)
+        print(name, "root", root, "x", out[pfx + "x.dims"], "y", out[pfx + "y.dims"], "indel", np.round(out[pfx + "fbc.indel"], 4),
+              "%.1f kB" % (os.path.getsize(os.path.join(OUT, name + ".npz")) / 1e3))
+
+
 def main():
+    tree_cases()
     for name, spec, gen, (tl, tr), band in CASES:
         with tempfile.TemporaryDirectory() as tmp:
             tf = os.path.join(tmp, "tree.nh")
