@@ -69,9 +69,10 @@ def cherry_inputs(lg, guide, n_pairs):
 
 
 def cherry_sequences(guide, n_pairs):
-    """The ungapped residue strings of the leaf x leaf merges, as a reference user holds them (FASTA)."""
+    """The ungapped residue strings of the leaf x leaf merges, as a reference user holds them after reading a
+    FASTA file (one byte string per sequence, like FastSeq::seq)."""
     gap = ord("-")
-    return [bytes(guide[r][guide[r] != gap]).decode() for r in range(2 * n_pairs)]
+    return [bytes(guide[r][guide[r] != gap]) for r in range(2 * n_pairs)]
 
 
 def write_fasta(path, guide):
@@ -392,10 +393,8 @@ def gpu_arm(args):
         pr = plan.run(leaves[0::2], leaves[1::2])
         r = ctx.fill_batch(pr, backward=True)
         h2d = sum(len(q) for q in seqs) + prep_h2d
-        for p in pr:
-            p.close()
-        for a in leaves:
-            a.close()
+        ctx.close_all(pr)
+        ctx.close_all(leaves)
         return r, h2d
 
     for _ in range(min(args.warmup, 2)):

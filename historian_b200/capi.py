@@ -43,6 +43,11 @@ def load():
     lib.hist_ctx_set_timing.argtypes = [vp, C.c_int]
     lib.hist_ctx_fill_time_ms.argtypes = [vp, D.c_double_p, D.c_int64_p]
     lib.hist_profile_upload.argtypes = [vp, C.POINTER(D.ProfileDesc), C.POINTER(vp)]
+    lib.hist_pairs_destroy.argtypes = [C.POINTER(vp), C.c_int32]
+    lib.hist_pairs_destroy.restype = None
+    lib.hist_profiles_destroy.argtypes = [C.POINTER(vp), C.c_int32]
+    lib.hist_profiles_destroy.restype = None
+    lib.hist_profile_from_residues.argtypes = [vp, C.c_int32, C.POINTER(C.c_char_p), D.c_int32_p, C.c_char_p, C.c_int32, C.POINTER(vp)]
     lib.hist_profile_from_sequences.argtypes = [vp, C.c_int32, C.POINTER(vp), D.c_int32_p, C.c_int32, C.c_int32, C.POINTER(vp)]
     lib.hist_profile_sum_path_absorb.argtypes = [vp, D.c_double_p, D.c_double_p, D.c_double_p, D.c_double_p]
     lib.hist_profile_destroy.argtypes = [vp]
@@ -133,27 +138,42 @@ class Context:
 
     def upload_sequences(self, seqs, alphabet, components=1, wildcard="*"):
         """Leaf profiles Profile(components, alphabet, FastSeq, row) (profile.cpp:23-76) of a batch of residue
-        strings, built on the device (hist_profile_from_sequences): only the residues cross the bus."""
-        lut = np.full(256, -1, np.int8)                      # tokenize(), fastseq.cpp:10-16: exact char, then swapped case
-        for k, ch in enumerate(alphabet):
-            for c in (ch.swapcase(), ch):
-                lut[ord(c)] = k
-        for k, ch in enumerate(alphabet):
-            lut[ord(ch)] = k
-        lut[ord(wildcard)] = -1
-        raw = [s.encode() if isinstance(s, str) else bytes(s) for s in seqs]
-        n = len(raw)
-        lens = np.array([len(r) for r in raw], np.int32)
-        toks = lut[np.frombuffer(b"".join(raw), np.uint8)] if lens.sum() else np.zeros(1, np.int8)   # one pass over all residues
-        starts = np.concatenate(([0], np.cumsum(lens[:-1], dtype=np.int64))) if n else np.zeros(0, np.int64)
-        ptrs = (C.c_void_p * n)(*(toks.ctypes.data + starts).tolist())
+        strings (str or bytes), built on the device: only the residues cross the bus.  Tokenisation
+        (fastseq.cpp:10-16) happens inside the library (hist_profile_from_residues)."""
+        n = len(seqs)
+        raw = [s if isinstance(s, bytes) else s.encode("latin-1", "replace") if isinstance(s, str) else bytes(s) for s in seqs]
+        lens = np.fromiter(map(len, raw), np.int32, n)
         out = (C.c_void_p * n)()
-        self.check(self.lib.hist_profile_from_sequences(self.h, n, ptrs, _p(lens, C.c_int32), len(alphabet), components, out))
-        return [DeviceProfile(self, None, handle=C.c_void_p(out[k]), seq=seqs[k], alphabet=alphabet, components=components,
-                              wildcard=wildcard) for k in range(n)]
+        if wildcard.lower() in alphabet.lower():
+            raise ValueError("the wildcard character must not be part of the alphabet")
+        self.check(self.lib.hist_profile_from_residues(self.h, n, (C.c_char_p * n)(*raw), _p(lens, C.c_int32), alphabet.encode(),
+                                                       components, out))
+        leaf = DeviceProfile.leaf
+        A = len(alphabet)
+        return [leaf(self, h, s, alphabet, components, wildcard, A) for h, s in zip(out, seqs)]
+
+    def upload_tokens(self, tokens, alph_size, components=1):
+        """Same from token strings (int8 arrays, negative = wildcard): hist_profile_from_sequences."""
+        toks = [np.ascontiguousarray(t, np.int8) for t in tokens]
+        n = len(toks)
+        lens = np.fromiter(map(len, toks), np.int32, n)
+        ptrs = (C.c_void_p * n)(*[t.ctypes.data for t in toks])
+        out = (C.c_void_p * n)()
+        self.check(self.lib.hist_profile_from_sequences(self.h, n, ptrs, _p(lens, C.c_int32), alph_size, components, out))
+        return [DeviceProfile(self, None, handle=C.c_void_p(h), seq=None, alphabet="x" * alph_size, components=components) for h in out]
 
     def sumprod(self, model, tree):
         return SumProd(self, model, tree)
+
+    def close_all(self, objs):
+        """Destroy a level's pairs or profiles with one call (hist_pairs_destroy / hist_profiles_destroy)."""
+        objs = [o for o in objs if o.h]
+        if not objs or not self.h:
+            return
+        fn = self.lib.hist_pairs_destroy if isinstance(objs[0], Pair) else self.lib.hist_profiles_destroy
+        fn((C.c_void_p * len(objs))(*[o.h for o in objs]), len(objs))
+        for o in objs:
+            o.h = None
 
     def prepare(self, x, y, hmm, env=None):
         return Pair(self, x, y, hmm, env if env is not None else D.Envelope(-1))
@@ -188,6 +208,13 @@ class DeviceProfile:
             self.components, self.alph_size = profile.components, profile.alph_size
         else:
             self.components, self.alph_size = components, len(alphabet)
+
+    @classmethod
+    def leaf(cls, ctx, handle, seq, alphabet, components, wildcard, alph_size):
+        """A leaf profile the library has just built (a level holds thousands: no ctypes objects, no checks)."""
+        p = object.__new__(cls)
+        p.ctx, p._host, p._leaf, p.h, p.components, p.alph_size = ctx, None, (seq, alphabet, components, wildcard), handle, components, alph_size
+        return p
 
     @property
     def host(self):
@@ -247,7 +274,8 @@ class PrepareBatch:
         yp = (C.c_void_p * n)(*[y.h for y in self.ys])
         out = (C.c_void_p * n)()
         ctx.check(ctx.lib.hist_pair_prepare_batch(ctx.h, n, xp, yp, self.hp, self.ep, self.flags, out))
-        return [Pair(ctx, self.xs[k], self.ys[k], handle=C.c_void_p(out[k])) for k in range(n)]
+        made = Pair.made
+        return [made(ctx, x, y, h) for x, y, h in zip(self.xs, self.ys, out)]
 
 
 class Pair:
@@ -262,6 +290,13 @@ class Pair:
         self.h = handle
         self._info = None
         self.components, self.alph_size = x.components, x.alph_size
+
+    @classmethod
+    def made(cls, ctx, x, y, handle):
+        """A pair the library has just prepared as part of a batch."""
+        p = object.__new__(cls)
+        p.ctx, p.x, p.y, p.h, p._info, p.components, p.alph_size = ctx, x, y, handle, None, x.components, x.alph_size
+        return p
 
     @property
     def info(self):

@@ -9,6 +9,7 @@
 // the reference) and the anti-diagonal HBM layout are built on the host in
 // O(states) and uploaded in one copy.
 #include <algorithm>
+#include <cctype>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -482,8 +483,9 @@ __global__ void leaf_absorb_kernel(const int8_t* tokens, const long long* state_
 }
 }  // namespace hb
 
-extern "C" int hist_profile_from_sequences(hist_ctx* ctx, int32_t n, const int8_t* const* tokens, const int32_t* lengths,
-                                           int32_t alph_size, int32_t components, hist_profile** out) {
+// lut == nullptr: `tokens` are token strings; else they are residue characters mapped through lut[256]
+static int leaf_profiles(hist_ctx* ctx, int32_t n, const int8_t* const* tokens, const int32_t* lengths, int32_t alph_size,
+                         int32_t components, const int8_t* lut, hist_profile** out) {
   if (!ctx || n <= 0 || !tokens || !lengths || !out) return set_err(ctx, HIST_ERR_ARG, "hist_profile_from_sequences: bad arguments");
   if (alph_size < 1 || alph_size > 127 || components < 1) return set_err(ctx, HIST_ERR_ARG, "hist_profile_from_sequences: bad A/C");
   for (int k = 0; k < n; ++k) out[k] = nullptr;
@@ -509,11 +511,14 @@ extern "C" int hist_profile_from_sequences(hist_ctx* ctx, int32_t n, const int8_
   }
   {
     char* st = ctx->staging;
-    long long at = 0;
-    for (int k = 0; k < n; ++k) {
-      for (int q = 0; q < lengths[k]; ++q) st[at + q] = tokens[k][q] >= alph_size ? -1 : tokens[k][q];
-      at += lengths[k];
-    }
+    parallel_for(n, 64, [&](int k) {
+      char* dst = st + (state_off[k] - 2 * (long long)k);
+      const int8_t* src = tokens[k];
+      if (lut)
+        for (int q = 0; q < lengths[k]; ++q) dst[q] = lut[(uint8_t)src[q]];
+      else
+        for (int q = 0; q < lengths[k]; ++q) dst[q] = src[q] >= alph_size ? -1 : src[q];
+    });
     memcpy(ctx->staging + so_st, state_off.data(), off_bytes);
     rc = check_cuda(ctx, cudaMemcpyAsync(arena->dev + tok_off, ctx->staging, n_tok, cudaMemcpyHostToDevice, ctx->stream), "H2D tokens");
     if (!rc) rc = check_cuda(ctx, cudaMemcpyAsync(arena->dev + so_off, ctx->staging + so_st, off_bytes, cudaMemcpyHostToDevice, ctx->stream), "H2D offsets");
@@ -561,12 +566,38 @@ extern "C" int hist_profile_from_sequences(hist_ctx* ctx, int32_t n, const int8_
   return HIST_OK;
 }
 
+extern "C" int hist_profile_from_sequences(hist_ctx* ctx, int32_t n, const int8_t* const* tokens, const int32_t* lengths,
+                                           int32_t alph_size, int32_t components, hist_profile** out) {
+  return leaf_profiles(ctx, n, tokens, lengths, alph_size, components, nullptr, out);
+}
+
+extern "C" int hist_profile_from_residues(hist_ctx* ctx, int32_t n, const char* const* residues, const int32_t* lengths,
+                                          const char* alphabet, int32_t components, hist_profile** out) {
+  if (!alphabet) return set_err(ctx, HIST_ERR_ARG, "hist_profile_from_residues: no alphabet");
+  const size_t A = strlen(alphabet);
+  if (A < 1 || A > 127) return set_err(ctx, HIST_ERR_ARG, "hist_profile_from_residues: bad alphabet size");
+  // tokenize() (fastseq.cpp:10-16): the exact character first, then the other case; anything else is a wildcard
+  int8_t lut[256];
+  for (int c = 0; c < 256; ++c) lut[c] = -1;
+  for (size_t k = 0; k < A; ++k) {
+    const unsigned char ch = (unsigned char)alphabet[k];
+    const int other = isupper(ch) ? tolower(ch) : toupper(ch);
+    if (lut[other] < 0) lut[other] = (int8_t)k;
+  }
+  for (size_t k = A; k-- > 0;) lut[(unsigned char)alphabet[k]] = (int8_t)k;   // first exact occurrence wins
+  return leaf_profiles(ctx, n, (const int8_t* const*)residues, lengths, (int32_t)A, components, lut, out);
+}
+
 extern "C" void hist_profile_destroy(hist_profile* p) {
   if (!p) return;
   cudaSetDevice(p->ctx->device);
   if (p->arena) arena_release(p->ctx, p->arena);
   else if (p->d_lp_absorb) cudaFreeAsync(p->d_lp_absorb, p->ctx->stream);
   delete p;
+}
+
+extern "C" void hist_profiles_destroy(hist_profile* const* profiles, int32_t n) {
+  for (int k = 0; profiles && k < n; ++k) hist_profile_destroy(profiles[k]);
 }
 
 // ------------------------------------------------------------------ pair preparation
@@ -1058,6 +1089,10 @@ extern "C" void hist_pair_destroy(hist_pair* pr) {
   if (pr->bwd_planes) cudaFreeAsync(pr->bwd_planes, pr->ctx->stream);
   arena_release(pr->ctx, pr->arena);
   delete pr;
+}
+
+extern "C" void hist_pairs_destroy(hist_pair* const* pairs, int32_t n) {
+  for (int k = 0; pairs && k < n; ++k) hist_pair_destroy(pairs[k]);
 }
 
 extern "C" int hist_pair_get_info(const hist_pair* pr, hist_pair_info* info) {

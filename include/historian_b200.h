@@ -162,6 +162,13 @@ int hist_profile_upload(hist_ctx* ctx, const hist_profile_desc* desc, hist_profi
  * the bus, not the [L+2][C][A] table. */
 int hist_profile_from_sequences(hist_ctx* ctx, int32_t n, const int8_t* const* tokens, const int32_t* lengths,
                                 int32_t alph_size, int32_t components, hist_profile** out);
+
+/* The same constructor from residue characters: tokenisation as tokenize() does it
+ * (fastseq.cpp:10-16: the exact character's first occurrence in `alphabet`, else the other
+ * case's; anything else, the wildcard included, is an invalid token = wildcard row of zeros,
+ * profile.cpp:56-60).  residues[k] need not be NUL-terminated. */
+int hist_profile_from_residues(hist_ctx* ctx, int32_t n, const char* const* residues, const int32_t* lengths,
+                               const char* alphabet, int32_t components, hist_profile** out);
 void hist_profile_destroy(hist_profile* p);
 
 /* ------------------------------------------------------------------ DPMatrix
@@ -181,6 +188,9 @@ int hist_pair_prepare_batch(hist_ctx* ctx, int32_t n, const hist_profile* const*
                             const hist_pairhmm_desc* const* hmms, const hist_env_desc* const* envs, int32_t flags,
                             hist_pair** out);
 void hist_pair_destroy(hist_pair* pair);
+/* Destructors of a whole level at once (one call instead of n). */
+void hist_pairs_destroy(hist_pair* const* pairs, int32_t n);
+void hist_profiles_destroy(hist_profile* const* profiles, int32_t n);
 int hist_pair_get_info(const hist_pair* pair, hist_pair_info* info);
 
 /* Device results of the constructor tables, as natural-log doubles.

@@ -22,9 +22,7 @@ for it in range(3):
     t2 = time.perf_counter()
     r = ctx.fill_batch(pr, backward=True)
     t3 = time.perf_counter()
-    for p in pr:
-        p.close()
-    for a, b in pp:
-        a.close(); b.close()
+    ctx.close_all(pr)
+    ctx.close_all(lv)
     t4 = time.perf_counter()
     print("upload %.1f ms  prepare %.1f ms  fill %.1f ms  close %.1f ms" % (1e3 * (t1 - t0), 1e3 * (t2 - t1), 1e3 * (t3 - t2), 1e3 * (t4 - t3)))
