@@ -74,6 +74,10 @@ __device__ __forceinline__ double block_reduce(double v, double* red) {
   return r;
 }
 
+// exp / log with the exact trivial cases taken out (one-hot leaf rows are all trivial cases): same results
+__device__ __forceinline__ double exp_t(double x) { return x == 0.0 ? 1.0 : x == -INFINITY ? 0.0 : exp(x); }
+__device__ __forceinline__ double log_t(double x) { return x == 1.0 ? 0.0 : log(x); }
+
 // WARP: C*A <= 32, one warp per state and blockDim.y states per CTA (a CTA per state would be a million
 // 32-thread CTAs for a level of merges); otherwise one CTA per state.  Same arithmetic either way.
 template <bool WARP>
@@ -119,7 +123,7 @@ __global__ void prepare_side_kernel(PairDev* const* __restrict__ pairs, int sm_s
   sync();
   const int c = k < K ? k / A : 0, a = k - c * A;
   const double lak = k < K ? la[k] : -INFINITY;
-  if (k < K) e_abs[k] = mc[c] == -INFINITY ? 0.0 : exp(lak - mc[c]);
+  if (k < K) e_abs[k] = mc[c] == -INFINITY ? 0.0 : exp_t(lak - mc[c]);
   sync();
   double subv = -INFINITY;
   if (k < K) {
@@ -137,8 +141,8 @@ __global__ void prepare_side_kernel(PairDev* const* __restrict__ pairs, int sm_s
   const double s_root = lr > -INFINITY ? lr + log(racc) : -INFINITY;
   const double iterm = k < K ? logCptWeight[c] + logIns[k] + lak : -INFINITY;
   const double li = red_max(iterm, red);
-  const double iacc = red_sum(li > -INFINITY && k < K ? exp(iterm - li) : 0.0, red);
-  const double s_ins = li > -INFINITY ? li + log(iacc) : -INFINITY;
+  const double iacc = red_sum(li > -INFINITY && k < K ? exp_t(iterm - li) : 0.0, red);
+  const double s_ins = li > -INFINITY ? li + log_t(iacc) : -INFINITY;
   const int ex = mx > -INFINITY ? (int)floor(mx / HB_LN2) : 0;
   if (k < Kp) {
     double h = subv > -INFINITY ? exp(subv - ex * HB_LN2) : 0.0;
@@ -242,10 +246,12 @@ __global__ void count_cells_kernel(PairDev* const* __restrict__ pairs) {
   if (threadIdx.x == 0) s_cnt = 0;
   __syncthreads();
   unsigned long long local = 0;
-  for (int d = blockIdx.x; d < P.n_diag; d += gridDim.x) {
+  // one warp per anti-diagonal (banded strips hold a few dozen slots)
+  const int warps = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int d = blockIdx.x * warps + warp; d < P.n_diag; d += gridDim.x * warps) {
     const DiagInfo di = P.dinfo[d];
     const int nthr = P.nS + di.width + P.nE;
-    for (int t = threadIdx.x; t < nthr; t += blockDim.x) {
+    for (int t = lane; t < nthr; t += 32) {
       int i, j;
       bool ok = true;
       if (t < P.nS) {
@@ -331,6 +337,10 @@ extern "C" int hist_ctx_create(int device, hist_ctx** out) {
   ctx->absorb_smem_configured = 0;
   ctx->staging = nullptr;
   ctx->staging_bytes = 0;
+  ctx->staging2 = nullptr;
+  ctx->staging2_bytes = 0;
+  cudaEventCreateWithFlags(&ctx->ev_stage[0], cudaEventDisableTiming);
+  cudaEventCreateWithFlags(&ctx->ev_stage[1], cudaEventDisableTiming);
   ctx->stream2 = nullptr;
   ctx->ev_fork = ctx->ev_join = nullptr;
   e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
@@ -362,6 +372,9 @@ extern "C" void hist_ctx_destroy(hist_ctx* ctx) {
   cudaStreamSynchronize(ctx->stream);
   for (auto& e : ctx->fill_events) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
   if (ctx->staging) cudaFreeHost(ctx->staging);
+  if (ctx->staging2) cudaFreeHost(ctx->staging2);
+  cudaEventDestroy(ctx->ev_stage[0]);
+  cudaEventDestroy(ctx->ev_stage[1]);
   if (ctx->stream2) { cudaStreamSynchronize(ctx->stream2); cudaStreamDestroy(ctx->stream2); }
   if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
   if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
@@ -453,7 +466,7 @@ extern "C" int hist_profile_upload(hist_ctx* ctx, const hist_profile_desc* d, hi
 }
 
 namespace {
-int ensure_staging(hist_ctx* ctx, size_t bytes);
+int ensure_staging(hist_ctx* ctx, size_t bytes, int slot = 0);
 void arena_release(hist_ctx* ctx, hb_arena* a);
 }  // namespace
 
@@ -597,7 +610,15 @@ extern "C" void hist_profile_destroy(hist_profile* p) {
 }
 
 extern "C" void hist_profiles_destroy(hist_profile* const* profiles, int32_t n) {
-  for (int k = 0; profiles && k < n; ++k) hist_profile_destroy(profiles[k]);
+  if (!profiles || n <= 0) return;
+  for (int k = 0; k < n; ++k) {
+    hist_profile* p = profiles[k];
+    if (!p) continue;
+    cudaSetDevice(p->ctx->device);
+    if (p->arena) arena_release(p->ctx, p->arena);
+    else if (p->d_lp_absorb) cudaFreeAsync(p->d_lp_absorb, p->ctx->stream);
+  }
+  parallel_for(n, 64, [&](int k) { delete profiles[k]; });
 }
 
 // ------------------------------------------------------------------ pair preparation
@@ -943,17 +964,57 @@ void place_pair(PairBuild& b, char* arena, size_t scal_off, bool want_bwd) {
   pr->d_dev = (PairDev*)(hb_ + b.h_pairdev);
 }
 
-int ensure_staging(hist_ctx* ctx, size_t bytes) {
-  if (ctx->staging_bytes >= bytes) return HIST_OK;
-  if (ctx->staging) {
+int ensure_staging(hist_ctx* ctx, size_t bytes, int slot) {
+  char*& buf = slot ? ctx->staging2 : ctx->staging;
+  size_t& have = slot ? ctx->staging2_bytes : ctx->staging_bytes;
+  if (have >= bytes) return HIST_OK;
+  if (buf) {
     HB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    cudaFreeHost(ctx->staging);
-    ctx->staging = nullptr;
-    ctx->staging_bytes = 0;
+    cudaFreeHost(buf);
+    buf = nullptr;
+    have = 0;
   }
   const size_t want = std::max(bytes + bytes / 4, (size_t)1 << 20);
-  HB_CUDA(ctx, cudaMallocHost((void**)&ctx->staging, want));
-  ctx->staging_bytes = want;
+  HB_CUDA(ctx, cudaMallocHost((void**)&buf, want));
+  have = want;
+  return HIST_OK;
+}
+
+// A sub-batch whose transfer and table kernels are enqueued but not yet waited for.
+struct PrepPending {
+  std::vector<PairBuild> builds;
+  hb_arena* arena = nullptr;
+  size_t scal_off = 0;
+  hist_pair** out = nullptr;
+};
+
+void drop_pending(hist_ctx* ctx, PrepPending& pd) {
+  for (auto& b : pd.builds) delete b.pr;
+  pd.builds.clear();
+  if (pd.arena) {
+    if (pd.arena->dev) cudaFreeAsync(pd.arena->dev, ctx->stream);
+    delete pd.arena;
+    pd.arena = nullptr;
+  }
+}
+
+// After the stream has been waited for: cell counts back, pairs handed to the caller.
+int finish_pending(hist_ctx* ctx, PrepPending& pd) {
+  const int n = (int)pd.builds.size();
+  std::vector<double> scal((size_t)n * 4);
+  HB_CUDA(ctx, cudaMemcpyAsync(scal.data(), pd.arena->dev + pd.scal_off, scal.size() * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+  HB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  for (int k = 0; k < n; ++k) {
+    hist_pair* pr = pd.builds[k].pr;
+    unsigned long long nc;
+    memcpy(&nc, &scal[(size_t)k * 4 + 2], sizeof(nc));
+    pr->info.n_cells = (int64_t)nc;
+    pr->arena = pd.arena;
+    ++pd.arena->refs;
+    pd.out[k] = pr;
+  }
+  pd.builds.clear();
+  pd.arena = nullptr;
   return HIST_OK;
 }
 
@@ -967,17 +1028,21 @@ void arena_release(hist_ctx* ctx, hb_arena* a) {
 
 }  // namespace
 
-extern "C" int hist_pair_prepare_batch(hist_ctx* ctx, int32_t n, const hist_profile* const* xs, const hist_profile* const* ys,
-                                       const hist_pairhmm_desc* const* hmms, const hist_env_desc* const* envs, int32_t flags,
-                                       hist_pair** out) {
-  if (!ctx || n <= 0 || !xs || !ys || !hmms || !out) return set_err(ctx, HIST_ERR_ARG, "hist_pair_prepare_batch: bad arguments");
-  for (int k = 0; k < n; ++k) out[k] = nullptr;
-  cudaSetDevice(ctx->device);
+namespace {
+// Host build, one H2D transfer and the table kernels of a sub-batch, enqueued on the context's stream through staging
+// buffer `slot`; does not wait for the device.
+int prepare_enqueue(hist_ctx* ctx, int32_t n, const hist_profile* const* xs, const hist_profile* const* ys,
+                    const hist_pairhmm_desc* const* hmms, const hist_env_desc* const* envs, int32_t flags, int slot,
+                    PrepPending& pd) {
   const bool want_bwd = (flags & HIST_PREP_BACKWARD) != 0;
   HostTimer tm("prepare_batch");
-  std::vector<PairBuild> builds(n);
+  pd.builds.assign(n, PairBuild());
+  std::vector<PairBuild>& builds = pd.builds;
   auto fail = [&](int rc) {
-    for (auto& b : builds) delete b.pr;
+    for (auto& b : builds) {
+      delete b.pr;
+      b.pr = nullptr;
+    }
     return rc;
   };
   size_t host_total = 0, dev_total = 0;
@@ -1006,7 +1071,8 @@ extern "C" int hist_pair_prepare_batch(hist_ctx* ctx, int32_t n, const hist_prof
   (void)dev_total;
   hb_arena* arena = new hb_arena{nullptr, total, 0};
   int rc = check_cuda(ctx, cudaMallocAsync((void**)&arena->dev, total, ctx->stream), "cudaMallocAsync(pair arena)");
-  if (!rc) rc = ensure_staging(ctx, scal_off);
+  if (!rc) rc = ensure_staging(ctx, scal_off, slot);
+  if (!rc) rc = check_cuda(ctx, cudaEventSynchronize(ctx->ev_stage[slot]), "wait for the staging buffer");  // its previous transfer
   if (rc) {
     if (arena->dev) cudaFreeAsync(arena->dev, ctx->stream);
     delete arena;
@@ -1014,7 +1080,7 @@ extern "C" int hist_pair_prepare_batch(hist_ctx* ctx, int32_t n, const hist_prof
   }
   tm.lap("alloc");
   // fill the pinned staging image and ship it in one transfer
-  char* st = ctx->staging;
+  char* st = slot ? ctx->staging2 : ctx->staging;
   int maxN = 1, maxNt = 1, maxDiag = 1, maxKp = 4, maxKC = 1;
   parallel_for(n, 8, [&](int k) {
     PairBuild& b = builds[k];
@@ -1035,6 +1101,7 @@ extern "C" int hist_pair_prepare_batch(hist_ctx* ctx, int32_t n, const hist_prof
   }
   tm.lap("staging fill");
   rc = check_cuda(ctx, cudaMemcpyAsync(arena->dev, st, scal_off, cudaMemcpyHostToDevice, ctx->stream), "H2D pair arena");
+  if (!rc) rc = check_cuda(ctx, cudaEventRecord(ctx->ev_stage[slot], ctx->stream), "record staging event");
   if (!rc) rc = check_cuda(ctx, cudaMemsetAsync(arena->dev + scal_off, 0, (size_t)n * 4 * sizeof(double), ctx->stream), "memset scalars");
   // ---- F0/F1 and the packed records on device, one launch each for the whole batch
   PairDev* const* dptrs = (PairDev* const*)(arena->dev + ptr_off);
@@ -1049,32 +1116,54 @@ extern "C" int hist_pair_prepare_batch(hist_ctx* ctx, int32_t n, const hist_prof
     }
     prepare_trans_kernel<<<dim3((maxNt + 127) / 128, n, 2), 128, 0, ctx->stream>>>(dptrs);
     pack_meta_kernel<<<dim3((maxN + 127) / 128, n, 2), 128, 0, ctx->stream>>>(dptrs);
-    const int chunks = std::max(1, std::min(maxDiag / 64 + 1, std::max(8, (4 * ctx->sm_count + n - 1) / n)));  // >= 8 chunks of diagonals per pair
+    const int chunks = std::max(1, std::min(maxDiag / 16 + 1, std::max(32, (4 * ctx->sm_count + n - 1) / n)));  // 4 diagonals in flight per CTA
     count_cells_kernel<<<dim3(chunks, n), 128, 0, ctx->stream>>>(dptrs);
     ctx->launches += 4;
     rc = check_cuda(ctx, cudaGetLastError(), "prepare kernels");
   }
-  std::vector<double> scal((size_t)n * 4);
-  if (!rc) rc = check_cuda(ctx, cudaMemcpyAsync(scal.data(), arena->dev + scal_off, scal.size() * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream), "D2H n_cells");
-  // descriptors were only borrowed, and the staging buffer is reused by the next call
   tm.lap("enqueue");
-  if (!rc) rc = check_cuda(ctx, cudaStreamSynchronize(ctx->stream), "sync after pair prepare");
-  tm.lap("device wait");
   if (rc) {
+    cudaStreamSynchronize(ctx->stream);
     cudaFreeAsync(arena->dev, ctx->stream);
     delete arena;
     return fail(rc);
   }
-  for (int k = 0; k < n; ++k) {
-    hist_pair* pr = builds[k].pr;
-    unsigned long long nc;
-    memcpy(&nc, &scal[(size_t)k * 4 + 2], sizeof(nc));
-    pr->info.n_cells = (int64_t)nc;
-    pr->arena = arena;
-    ++arena->refs;
-    out[k] = pr;
-  }
+  pd.arena = arena;
+  pd.scal_off = scal_off;
   return HIST_OK;
+}
+}  // namespace
+
+extern "C" int hist_pair_prepare_batch(hist_ctx* ctx, int32_t n, const hist_profile* const* xs, const hist_profile* const* ys,
+                                       const hist_pairhmm_desc* const* hmms, const hist_env_desc* const* envs, int32_t flags,
+                                       hist_pair** out) {
+  if (!ctx || n <= 0 || !xs || !ys || !hmms || !out) return set_err(ctx, HIST_ERR_ARG, "hist_pair_prepare_batch: bad arguments");
+  for (int k = 0; k < n; ++k) out[k] = nullptr;
+  cudaSetDevice(ctx->device);
+  // a level is shipped in sub-batches: while the device receives and tabulates one, the host threads build the next
+  int parts = n >= 128 ? 2 : 1;   // measured on the 512-merge level: 1 -> 11.9 ms, 2 -> 11.0, 4 -> 12.5 (host-build bound)
+  if (const char* e = getenv("HIST_B200_PREP_PARTS")) parts = std::max(1, std::min(n, atoi(e)));
+  const int per = (n + parts - 1) / parts;
+  std::vector<PrepPending> pend((n + per - 1) / per);
+  int rc = HIST_OK;
+  for (size_t c = 0; c < pend.size() && !rc; ++c) {
+    const int first = (int)c * per, cnt = std::min(per, n - first);
+    pend[c].out = out + first;
+    rc = prepare_enqueue(ctx, cnt, xs + first, ys + first, hmms + first, envs ? envs + first : nullptr, flags, (int)(c & 1), pend[c]);
+  }
+  // descriptors were only borrowed, and the staging buffers are reused by the next call
+  if (!rc) rc = check_cuda(ctx, cudaStreamSynchronize(ctx->stream), "sync after pair prepare");
+  for (size_t c = 0; c < pend.size() && !rc; ++c) rc = finish_pending(ctx, pend[c]);
+  if (rc) {
+    cudaStreamSynchronize(ctx->stream);
+    for (auto& pd : pend) drop_pending(ctx, pd);
+    for (int k = 0; k < n; ++k)
+      if (out[k]) {
+        hist_pair_destroy(out[k]);
+        out[k] = nullptr;
+      }
+  }
+  return rc;
 }
 
 extern "C" int hist_pair_prepare(hist_ctx* ctx, const hist_profile* x, const hist_profile* y, const hist_pairhmm_desc* hmm,
@@ -1092,7 +1181,15 @@ extern "C" void hist_pair_destroy(hist_pair* pr) {
 }
 
 extern "C" void hist_pairs_destroy(hist_pair* const* pairs, int32_t n) {
-  for (int k = 0; pairs && k < n; ++k) hist_pair_destroy(pairs[k]);
+  if (!pairs || n <= 0) return;
+  for (int k = 0; k < n; ++k) {   // device memory and reference counts on the calling thread, in order
+    hist_pair* pr = pairs[k];
+    if (!pr) continue;
+    cudaSetDevice(pr->ctx->device);
+    if (pr->bwd_planes) cudaFreeAsync(pr->bwd_planes, pr->ctx->stream);
+    arena_release(pr->ctx, pr->arena);
+  }
+  parallel_for(n, 32, [&](int k) { delete pairs[k]; });   // the host-side vectors of a level: spread the frees
 }
 
 extern "C" int hist_pair_get_info(const hist_pair* pr, hist_pair_info* info) {

@@ -196,6 +196,11 @@ struct hist_ctx {
   // pinned staging buffer for host-built layouts (grown on demand)
   char* staging;
   size_t staging_bytes;
+  // second staging buffer + one event per buffer: hist_pair_prepare_batch ships a level in sub-batches so that the
+  // host build of one overlaps the transfer and table kernels of the previous one
+  char* staging2;
+  size_t staging2_bytes;
+  cudaEvent_t ev_stage[2];
 };
 
 struct hist_profile {
