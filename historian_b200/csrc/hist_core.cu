@@ -17,6 +17,9 @@
 #include <cstring>
 #include <limits>
 
+#include <atomic>
+#include <condition_variable>
+#include <functional>
 #include <chrono>
 #include <mutex>
 #include <thread>
@@ -282,6 +285,83 @@ __global__ void count_cells_kernel(PairDev* const* __restrict__ pairs) {
 using namespace hb;
 
 namespace {
+// Persistent host worker threads: a level of merges goes through half a dozen parallel loops per call, and spawning
+// sixteen threads for each costs more than some of the loops themselves.
+class HostPool {
+ public:
+  static HostPool& get() {
+    static HostPool pool;
+    return pool;
+  }
+  // fn(k) for k in [0, n) on `nthreads` threads (the caller is one of them); items are handed out dynamically
+  void run(int n, int nthreads, const std::function<void(int)>& fn) {
+    std::lock_guard<std::mutex> serial(run_mu_);
+    grow(nthreads - 1);
+    {
+      std::lock_guard<std::mutex> lk(mu_);
+      job_ = &fn;
+      n_ = n;
+      next_.store(0);
+      want_ = nthreads - 1;
+      active_ = want_;
+      ++gen_;
+    }
+    cv_.notify_all();
+    work(fn, n);
+    std::unique_lock<std::mutex> lk(mu_);
+    done_.wait(lk, [&] { return active_ == 0; });
+    job_ = nullptr;
+  }
+
+ private:
+  HostPool() {}
+  ~HostPool() {
+    {
+      std::lock_guard<std::mutex> lk(mu_);
+      stop_ = true;
+    }
+    cv_.notify_all();
+    for (auto& t : threads_) t.join();
+  }
+  void work(const std::function<void(int)>& fn, int n) {
+    for (int k = next_.fetch_add(1); k < n; k = next_.fetch_add(1)) fn(k);
+  }
+  void grow(int workers) {
+    while ((int)threads_.size() < workers) {
+      const int id = (int)threads_.size();
+      threads_.emplace_back([this, id] {
+        unsigned long long seen = 0;
+        for (;;) {
+          const std::function<void(int)>* job = nullptr;
+          int n = 0;
+          {
+            std::unique_lock<std::mutex> lk(mu_);
+            cv_.wait(lk, [&] { return stop_ || (gen_ != seen && id < want_); });
+            if (stop_) return;
+            seen = gen_;
+            job = job_;
+            n = n_;
+          }
+          work(*job, n);
+          {
+            std::lock_guard<std::mutex> lk(mu_);
+            --active_;
+          }
+          done_.notify_one();
+        }
+      });
+    }
+  }
+  std::vector<std::thread> threads_;
+  std::mutex mu_, run_mu_;
+  std::condition_variable cv_, done_;
+  const std::function<void(int)>* job_ = nullptr;
+  std::atomic<int> next_{0};
+  int n_ = 0, want_ = 0, active_ = 0;
+  unsigned long long gen_ = 0;
+  bool stop_ = false;
+};
+
 // Runs fn(0..n-1) on up to hardware_concurrency host threads (at least `grain` items per thread).
 template <class F>
 void parallel_for(int n, int grain, F fn) {
@@ -294,12 +374,7 @@ void parallel_for(int n, int grain, F fn) {
     for (int k = 0; k < n; ++k) fn(k);
     return;
   }
-  std::vector<std::thread> pool;
-  for (int t = 0; t < nthreads; ++t)
-    pool.emplace_back([=, &fn]() {
-      for (int k = t; k < n; k += nthreads) fn(k);
-    });
-  for (auto& th : pool) th.join();
+  HostPool::get().run(n, nthreads, std::function<void(int)>(fn));
 }
 
 // HIST_B200_HOST_TIMING=1: wall-clock split of the host side of the batched constructors on stderr
@@ -1013,6 +1088,11 @@ int finish_pending(hist_ctx* ctx, PrepPending& pd) {
     ++pd.arena->refs;
     pd.out[k] = pr;
   }
+  // every build record owns a few dozen host vectors: free them on the worker threads
+  parallel_for(n, 32, [&](int k) {
+    PairBuild done;
+    std::swap(pd.builds[k], done);
+  });
   pd.builds.clear();
   pd.arena = nullptr;
   return HIST_OK;
@@ -1141,7 +1221,7 @@ extern "C" int hist_pair_prepare_batch(hist_ctx* ctx, int32_t n, const hist_prof
   for (int k = 0; k < n; ++k) out[k] = nullptr;
   cudaSetDevice(ctx->device);
   // a level is shipped in sub-batches: while the device receives and tabulates one, the host threads build the next
-  int parts = n >= 128 ? 2 : 1;   // measured on the 512-merge level: 1 -> 11.9 ms, 2 -> 11.0, 4 -> 12.5 (host-build bound)
+  int parts = n >= 128 ? 4 : 1;   // measured on the 512-merge level: 1 -> 12.3 ms, 2 -> 10.9, 4 -> 10.0 (host-build bound)
   if (const char* e = getenv("HIST_B200_PREP_PARTS")) parts = std::max(1, std::min(n, atoi(e)));
   const int per = (n + parts - 1) / parts;
   std::vector<PrepPending> pend((n + per - 1) / per);
