@@ -1,0 +1,46 @@
+"""Host side of getCounts (historian_b200/fbcounts.py): the alignment columns ForwardMatrix::getAlignmentColumn
+(forward.cpp:940-973) builds one cell at a time, assembled as one weighted batch.  No GPU needed."""
+import numpy as np
+
+from historian_b200 import fbcounts as F
+
+GAP, WILD = ord("-"), ord("*")
+
+
+def test_leaf_columns_follow_profile_align_column():
+    cols = F.leaf_columns("acg", 1, 3)
+    assert cols.shape == (5, 3)                       # START, three residues, END
+    assert bytes(cols[:, 1]) == b"-acg-"
+    assert np.all(cols[:, [0, 2]] == GAP)
+    assert F.leaf_columns(b"", 0, 3).shape == (2, 3)  # empty sequence: START and END only
+
+
+def test_column_batch_classes_order_and_weights():
+    x, y = F.leaf_columns("ac", 0, 3), F.leaf_columns("gt", 1, 3)
+    w_x = np.array([[0, 0.25, 0, 0], [0, 0.5, 0.125, 0]])     # insert / delete weights per x state
+    w_y = np.array([[0, 0, 0, 0], [0, 0, 0.75, 0]])
+    cells = np.array([[1, 1, 0], [2, 2, 0]], np.int32)
+    cols, w = F.column_batch(x, y, 2, w_x, w_y, cells, np.array([0.3, 0.6]))
+    got = [(bytes(c).decode(), float(v)) for c, v in zip(cols, w)]
+    assert got == [("a--", 0.25),                 # x insert: the child's own column, no parent
+                   ("a-*", 0.5), ("c-*", 0.125),  # x deleted: wildcard parent
+                   ("-t*", 0.75),                 # y deleted
+                   ("ag*", 0.3), ("ct*", 0.6)]    # matches: both children and the parent
+
+
+def test_column_batch_skips_empty_columns_and_merges_tree_rows():
+    # internal profiles: columns span several tree rows; a null state's column is empty and never emitted
+    x = np.array([list(b"-----"), list(b"a-c--"), list(b"-----"), list(b"-----")], np.uint8)
+    y = np.array([list(b"-----"), list(b"---g-"), list(b"-----")], np.uint8)
+    w_x = np.array([[0, 0.5, 0.5, 0], [0, 0.25, 0.25, 0]])
+    w_y = np.zeros((2, 3))
+    cols, w = F.column_batch(x, y, 4, w_x, w_y, np.array([[1, 1, 0]], np.int32), np.array([1.0]))
+    got = [(bytes(c).decode(), float(v)) for c, v in zip(cols, w)]
+    assert got == [("a-c--", 0.5), ("a-c-*", 0.25), ("a-cg*", 1.0)]
+
+
+def test_prob_model_waits_order():
+    class P:
+        def __init__(self, t, i, d):
+            self.t, self.insWait, self.delWait = t, i, d
+    assert list(F.prob_model_waits(P(1, 2, 3), P(4, 5, 6))) == [1, 4, 2, 3, 5, 6]
