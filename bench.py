@@ -38,6 +38,7 @@ BRANCH = 0.05
 N_LEAVES = 1024
 ROOT_LEN = 1000
 # dram__bytes_read.sum + dram__bytes_write.sum of the three fill kernels per launch, from the ncu --set full capture under profiles/ (None = not captured)
+EM_TRAFFIC_BYTES = 5.78e9     # profiles/r01_sumprod_ncu_details_final.txt: sumprod_columns_kernel 3.68 GB read + 2.10 GB written per launch (default EM family)
 FILL_TRAFFIC_BYTES = 7.44e9   # profiles/r01_fill_ncu_details_final.txt: absorb 0.17 + build_records 3.21 + fill_stream 4.06 GB
 ALG_BYTES_PER_CELL = 80.0   # 40 B written once + 40 B read once per DP cell (reference layout)
 METRIC = "profile Forward/Backward cells/s (GCUPS)"
@@ -312,7 +313,7 @@ def em_leg(ctx, args, rank, world, local, barrier):
                           "parallelism": "columns sharded over %d GPU(s), one all-reduce of %d doubles per step" % (world, sp.counts_size)},
                "e2e": {"value": n_cols * steps / (e2e_ms / 1e3), "unit": "columns/s", "h2d_bytes_per_step": int((hi - lo) * N),
                        "d2h_bytes_per_step": int(8 * sp.counts_size)},
-               "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+               "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": EM_TRAFFIC_BYTES if (world == 1 and int(n_cols) == 12997 and int(N) == 8191) else None,
                             "kernel": "hb::sumprod_columns_kernel", "avg_launch_ms": 1e3 * per_launch_s,
                             "algorithmic_bytes_per_column": alg_bytes, "columns_per_launch": int(hi - lo)},
                "cpu_baseline": base, "gpu_launches": int(2 * steps)}
