@@ -129,3 +129,54 @@ def test_root_merge_of_a_progressive_reconstruction(ctx, path):
     assert near(counts[4:6], ref[4:6], 2e-3), (counts[:6], ref[:6])
     assert near(rc, d[pfx + "fbc.root_count"], 2e-3)
     assert near(sub, d[pfx + "fbc.sub_count"], 2e-3)
+
+
+def test_full_size_pair_properties(ctx):
+    """BASELINE-sized merge (two 1000-residue LG leaves, guide band 20, visible indel rates): properties that do
+    not need the reference - posterior mass per residue, the expected number of root residues, the closed-form
+    link between indel events and waiting times, and bit-reproducibility."""
+    from historian_b200 import simulator as S
+    lg = M.RateModel.preset("lg")
+    lg.insRate = lg.delRate = 0.05
+    t = 0.2
+    tree = S.Tree.balanced(2, t)
+    gapped, _ = S.simulate_family(lg, tree, 1000, 11)
+    _, guide = S.leaf_guide(tree, gapped)
+    gap = ord("-")
+    seqs = [bytes(r[r != gap]) for r in guide[:2]]
+    env = D.Envelope.from_guide_rows(guide[0] != gap, guide[1] != gap, 20)
+    x, y = ctx.upload_sequences(seqs, lg.alphabet, lg.components)
+    pair = ctx.prepare(x, y, M.pair_hmm(lg, t, t), env)
+    lp_end = pair.forward()
+    pair.backward()
+    lp, rp = M.ProbModel(lg, t), M.ProbModel(lg, t)
+    waits = fbcounts.prob_model_waits(lp, rp)
+    indel, w_x, w_y, cells, cell_w = pair.fb_counts(waits)
+    again = pair.fb_counts(waits)
+    assert all(H.same(a, b) for a, b in zip((indel, w_x, w_y, cells, cell_w), again))
+    xn, yn = w_x.shape[1], w_y.shape[1]
+    assert (xn, yn) == (len(seqs[0]) + 2, len(seqs[1]) + 2)
+    mx, my = np.zeros(xn), np.zeros(yn)
+    np.add.at(mx, cells[:, 0], cell_w)
+    np.add.at(my, cells[:, 1], cell_w)
+    kept = w_x[0] > 0
+    # (the last residues of x and y can only be matched to each other: neither profile is 'ready' in its last state,
+    # forward.cpp:97, so row L has no insert or delete weight at all)
+    assert mx[xn - 2] == 1.0 and kept[80:xn - 2].all() and not (w_y[0] > 0).any()      # the insert-cache quirk: x rows next to the start, all of y
+    assert np.all(np.abs((w_x[0] + w_x[1] + mx)[kept] - 1) <= 2e-3)
+    assert np.all((w_y[1] + my)[1:-1] <= 1 + 2e-3)
+    # every event count is a posterior expectation of a non-negative quantity
+    assert np.all(indel >= 0) and indel[0] + indel[1] > 0.5
+    # waiting times (forward.cpp:590-640): a match adds at most both branch lengths (exactly both when it follows a
+    # match), a deletion at most one branch, an opening event one decay wait
+    matches, dels_x, dels_y = cell_w.sum(), w_x[1].sum(), w_y[1].sum()
+    lo = 0.9 * matches * 2 * t
+    hi = (matches + dels_x + dels_y + 50) * 2 * t + (indel[0] + indel[1]) * max(waits[2:])
+    assert lo <= indel[4] <= hi and lo <= indel[5] <= hi
+    sp = ctx.sumprod(D.SumProdModel.from_rate_model(lg), D.TreeTopology([2, 2, -1], [t, t, 0.0]))
+    counts = fbcounts.fb_counts(pair, sp, waits, fbcounts.leaf_columns(seqs[0], 0, 3), fbcounts.leaf_columns(seqs[1], 1, 3), 2, lp_end)
+    root, sub = sp.transform_counts(counts)
+    sp.close()
+    # one root residue per weighted column: matches, deletions, and the x inserts whose cache is not empty
+    assert abs(root.sum() - (matches + dels_x + dels_y + w_x[0].sum())) <= 1e-6 * root.sum()
+    assert np.all(root >= -1e-9) and np.all(np.diagonal(sub, axis1=1, axis2=2) >= -1e-9)
