@@ -373,7 +373,6 @@ def gpu_arm(args):
     e1.record(stream)
     barrier()
     ms = e0.elapsed_time(e1)
-    clk = clocks.summary()
     launches = ctx.launch_count - launches0
     kernel_ms, kernel_launches = ctx.fill_time_ms()
     ctx.set_timing(False)
@@ -410,6 +409,12 @@ def gpu_arm(args):
     assert np.array_equal(lp_e, lp_end) and np.array_equal(lp_s, lp_start), "end-to-end likelihoods differ from the resident run"
     barrier()
     e2e_ms = f0.elapsed_time(f1)
+    # the sampler has been running since the resident region started; a short run (tens of milliseconds) may have
+    # seen a single nvidia-smi reading, so keep the same load on until it has three (untimed, at most 2 s)
+    t_load = time.perf_counter()
+    while len(clocks.rows) < 3 and time.perf_counter() - t_load < 2.0:
+        step_resident()
+    clk = clocks.summary()
 
     t = torch.tensor([ms, e2e_ms, kernel_ms], dtype=torch.float64, device="cuda")
     c = torch.tensor([float(cells_per_step)], dtype=torch.float64, device="cuda")
