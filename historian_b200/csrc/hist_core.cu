@@ -644,6 +644,7 @@ static int leaf_profiles(hist_ctx* ctx, int32_t n, const int8_t* const* tokens, 
     for (int t = 0; t < p->nt; ++t) { p->t_src[t] = t; p->t_dst[t] = t + 1; }
     for (int i = 0; i < p->n; ++i) p->leaf_pos[i] = std::min(i, L);   // seqCoords of the leaf row (profile.cpp:33-36, 49)
     p->sorted_in = true;
+    p->chain = true;
     p->empty = L == 0;
     p->d_lp_absorb = (double*)arena->dev + (size_t)state_off[k] * K;
     p->arena = arena;
@@ -740,6 +741,31 @@ struct PairBuild {
 
 void build_side_lists(const hist_profile* p, SideHost& s) {
   const int n = p->n, nt = p->nt;
+  if (p->chain) {
+    // a leaf: START -> residue 1 -> ... -> residue L -> END.  Transition t enters state t+1; it is an absorbing
+    // out-edge of state t unless it enters END (t == n-2), which makes it the one null out-edge.
+    s.in_off.resize(n + 1); s.ao_off.resize(n + 1); s.no_off.resize(n + 1);
+    for (int k = 0; k <= n; ++k) {
+      s.in_off[k] = std::max(0, k - 1);
+      s.ao_off[k] = std::min(k, n - 2);
+      s.no_off[k] = k > n - 2 ? 1 : 0;
+    }
+    s.in_idx.resize(std::max(1, nt));
+    for (int q = 0; q < nt; ++q) s.in_idx[q] = q;
+    s.ao_idx.resize(std::max(1, n - 2));
+    for (int q = 0; q < n - 2; ++q) s.ao_idx[q] = q;
+    if (n == 2) s.ao_idx[0] = 0;
+    s.no_idx.assign(1, n - 2);
+    s.flags.resize(n);
+    for (int i = 0; i < n; ++i) {
+      uint8_t f = 0;
+      if (p->is_emit[i]) f |= F_EMIT;
+      if (i != n - 2 || p->empty) f |= F_READY;
+      if (p->is_emit[i] || i == 0) f |= F_EMIT_OR_START;
+      s.flags[i] = f;
+    }
+    return;
+  }
   std::vector<int> in_cnt(n + 1, 0), ao_cnt(n + 1, 0), no_cnt(n + 1, 0);
   for (int t = 0; t < nt; ++t) {
     ++in_cnt[p->t_dst[t] + 1];

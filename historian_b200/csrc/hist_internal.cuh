@@ -213,6 +213,7 @@ struct hist_profile {
   std::vector<int> leaf_pos;  // empty if not given
   bool empty;                 // Profile::isEmpty
   bool sorted_in;             // every in-list ascending in source state, no repeated (src,dest)
+  bool chain = false;         // leaf profile built by the library: transition t is t -> t+1, states 1..n-2 emit
   // device copy of lp_absorb
   double* d_lp_absorb;
   hb_arena* arena;            // owner of d_lp_absorb
