@@ -259,3 +259,25 @@ def test_queue_kernel_variant_still_matches():
     r = subprocess.run([sys.executable, "-m", "pytest", here, "-m", "gpu", "-q", "-x", "-k", "leaf_pair_banded or synthetic_dag or batch_fill"],
                        env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, cwd=os.path.dirname(os.path.dirname(here)))
     assert r.returncode == 0, r.stdout[-2000:]
+
+
+def test_leaf_profiles_from_tokens_match_those_from_residues(ctx):
+    """hist_profile_from_sequences (token strings) and hist_profile_from_residues (characters, tokenised inside the
+    library as fastseq.cpp:10-16 does) build the same leaf profiles; hist_profiles_destroy / hist_pairs_destroy
+    release a whole level."""
+    rng = np.random.default_rng(9)
+    alphabet = "arndcqeghilkmfpstwyv"
+    seqs = ["".join(rng.choice(list(alphabet), size=L)) for L in (30, 7, 41)] + ["aRn*dZ"]
+    toks = [np.array([alphabet.find(c.lower()) if c.lower() in alphabet else -1 for c in s], np.int8) for s in seqs]
+    by_res = ctx.upload_sequences(seqs, alphabet, components=1)
+    by_tok = ctx.upload_tokens(toks, len(alphabet), components=1)
+    hmm = synth.random_hmm(rng, 20, 1, tl=0.3, tr=0.2)
+    pairs = []
+    for a, b in ((0, 1), (2, 3), (3, 0)):
+        p1, p2 = ctx.prepare(by_res[a], by_res[b], hmm), ctx.prepare(by_tok[a], by_tok[b], hmm)
+        assert p1.forward() == p2.forward()
+        assert H.same(p1.cells_dense(0), p2.cells_dense(0))
+        pairs += [p1, p2]
+    ctx.close_all(pairs)
+    ctx.close_all(by_res + by_tok)
+    assert all(p.h is None for p in pairs + by_res + by_tok)
