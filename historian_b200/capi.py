@@ -71,6 +71,18 @@ def load():
     lib.hist_fb_counts.argtypes = [vp, D.c_double_p, D.c_double_p, D.c_double_p, D.c_double_p, C.POINTER(D.Cell), D.c_double_p,
                                    C.c_int64, D.c_int64_p]
     lib.hist_profile_eliminate.argtypes = [vp, C.POINTER(D.Cell), C.c_int64, C.c_int32, C.POINTER(D.ElimResult)]
+    lib.hist_recon_create.argtypes = [vp, C.c_int32, C.c_char_p, C.c_int32, C.POINTER(vp)]
+    lib.hist_recon_destroy.argtypes = [vp]
+    lib.hist_recon_destroy.restype = None
+    lib.hist_recon_set_guide.argtypes = [vp, C.c_int32, C.c_int32, D.c_int32_p, D.c_uint8_p]
+    lib.hist_recon_add_leaves.argtypes = [vp, C.c_int32, D.c_int32_p, C.POINTER(C.c_char_p), D.c_int32_p]
+    lib.hist_recon_level.argtypes = [vp, C.c_int32, C.POINTER(D.MergeDesc), C.POINTER(D.ReconParams), D.c_double_p]
+    lib.hist_recon_alignment.argtypes = [vp, D.c_int32_p, D.c_uint8_p, C.c_int64]
+    lib.hist_recon_stage_ms.argtypes = [vp, D.c_double_p, C.c_int]
+    lib.hist_recon_profile.argtypes = [vp, C.c_int32]
+    lib.hist_recon_profile.restype = vp
+    lib.hist_profile_get_sizes.argtypes = [vp, D.c_int32_p, D.c_int32_p, D.c_int32_p, D.c_int32_p]
+    lib.hist_profile_fetch.argtypes = [vp, D.c_uint8_p, D.c_int32_p, D.c_int32_p, D.c_double_p, D.c_double_p, D.c_int32_p]
     lib.hist_sumprod_create.argtypes = [vp, C.POINTER(D.ModelDesc), C.POINTER(D.TreeDesc), C.POINTER(vp)]
     lib.hist_sumprod_destroy.argtypes = [vp]
     lib.hist_sumprod_destroy.restype = None
@@ -463,6 +475,95 @@ class Pair:
 
 
 SP_COUNTS, SP_MAP_STATES, SP_NODE_POST = 1, 2, 4
+
+
+def fetch_profile(ctx, handle, with_absorb=True):
+    """hist_profile_fetch: a device profile read back as a descs.Profile."""
+    lib = ctx.lib
+    n, nt, A, Cc = C.c_int32(), C.c_int32(), C.c_int32(), C.c_int32()
+    ctx.check(lib.hist_profile_get_sizes(handle, C.byref(n), C.byref(nt), C.byref(A), C.byref(Cc)))
+    is_emit = np.empty(n.value, np.uint8)
+    src, dst, lp = np.empty(nt.value, np.int32), np.empty(nt.value, np.int32), np.empty(nt.value)
+    leaf = np.empty(n.value, np.int32)
+    ab = np.full((n.value, Cc.value, A.value), -np.inf)
+    ctx.check(lib.hist_profile_fetch(handle, _p(is_emit, C.c_uint8), _p(src, C.c_int32), _p(dst, C.c_int32), _p(lp, C.c_double),
+                                     _p(ab, C.c_double) if with_absorb else None, _p(leaf, C.c_int32)))
+    return D.Profile(is_emit, src, dst, lp, ab, leaf)
+
+
+class Recon:
+    """hist_recon: the level-batched, device-resident progressive reconstruction (recon.cpp:917-1052)."""
+
+    def __init__(self, ctx, n_nodes, alphabet, components=1):
+        self.ctx, self.n_nodes = ctx, n_nodes
+        h = C.c_void_p()
+        ctx.check(ctx.lib.hist_recon_create(ctx.h, n_nodes, alphabet.encode(), components, C.byref(h)))
+        self.h = h
+
+    def close(self):
+        if self.h and self.ctx.h:
+            self.ctx.lib.hist_recon_destroy(self.h)
+        self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_guide(self, row_nodes, bits):
+        """bits: [n_rows][n_cols] bool/uint8 (True = residue); row_nodes[r] = tree node of row r."""
+        bits = np.ascontiguousarray(bits, np.uint8)
+        rn = np.ascontiguousarray(row_nodes, np.int32)
+        self.ctx.check(self.ctx.lib.hist_recon_set_guide(self.h, bits.shape[0], bits.shape[1], _p(rn, C.c_int32), _p(bits, C.c_uint8)))
+
+    def add_leaves(self, nodes, seqs):
+        n = len(nodes)
+        raw = [s if isinstance(s, bytes) else s.encode("latin-1", "replace") for s in seqs]
+        lens = np.fromiter(map(len, raw), np.int32, n)
+        nd = np.ascontiguousarray(nodes, np.int32)
+        self.ctx.check(self.ctx.lib.hist_recon_add_leaves(self.h, n, _p(nd, C.c_int32), (C.c_char_p * n)(*raw), _p(lens, C.c_int32)))
+
+    def level(self, merges, hmm_descs, band, strategy, profile_samples, max_profile_states, root_node=-1, mt_state=None):
+        """merges: list of (node, left, right, closest_left, closest_right, closest); hmm_descs: one PairHmmDesc per merge
+        (kept alive by the caller).  Returns lp_end per merge."""
+        n = len(merges)
+        arr = (D.MergeDesc * n)()
+        for k, (m, hd) in enumerate(zip(merges, hmm_descs)):
+            a = arr[k]
+            a.node, a.left, a.right, a.closest_left, a.closest_right, a.closest = (int(v) for v in m)
+            a.hmm = C.pointer(hd)
+        prm = D.ReconParams()
+        prm.band, prm.strategy, prm.profile_samples, prm.max_profile_states = int(band), int(strategy), int(profile_samples), int(max_profile_states)
+        prm.min_post_prob = 0.0
+        prm.root_node = int(root_node)
+        if mt_state is not None:
+            prm.mt_state = _p(mt_state, C.c_uint32)
+        lp = np.empty(n)
+        self.ctx.check(self.ctx.lib.hist_recon_level(self.h, n, arr, C.byref(prm), _p(lp, C.c_double)))
+        return lp
+
+    def alignment(self):
+        """Dense bool [n_nodes][n_cols] of the root's best alignment path."""
+        nc = C.c_int32()
+        rc = self.ctx.lib.hist_recon_alignment(self.h, C.byref(nc), None, 0)
+        if rc not in (0, -5):
+            self.ctx.check(rc)
+        bits = np.zeros((self.n_nodes, max(nc.value, 0)), np.uint8)
+        if bits.size:
+            self.ctx.check(self.ctx.lib.hist_recon_alignment(self.h, C.byref(nc), _p(bits, C.c_uint8), bits.size))
+        return bits.astype(bool)
+
+    def stage_ms(self, reset=False):
+        ms = np.zeros(len(D.RECON_STAGES))
+        self.ctx.check(self.ctx.lib.hist_recon_stage_ms(self.h, _p(ms, C.c_double), int(reset)))
+        return dict(zip(D.RECON_STAGES, ms.tolist()))
+
+    def profile(self, node, with_absorb=True):
+        h = self.ctx.lib.hist_recon_profile(self.h, node)
+        if not h:
+            raise KeyError("node %d has no live device profile" % node)
+        return fetch_profile(self.ctx, C.c_void_p(h), with_absorb)
 
 
 def _addr(a):

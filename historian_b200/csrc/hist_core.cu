@@ -679,6 +679,10 @@ extern "C" int hist_profile_from_residues(hist_ctx* ctx, int32_t n, const char* 
 
 extern "C" void hist_profile_destroy(hist_profile* p) {
   if (!p) return;
+  if (p->refs > 0) {   // pairs built on this profile still read its host lists and device table: released with the last of them
+    p->doomed = true;
+    return;
+  }
   cudaSetDevice(p->ctx->device);
   if (p->arena) arena_release(p->ctx, p->arena);
   else if (p->d_lp_absorb) cudaFreeAsync(p->d_lp_absorb, p->ctx->stream);
@@ -687,14 +691,21 @@ extern "C" void hist_profile_destroy(hist_profile* p) {
 
 extern "C" void hist_profiles_destroy(hist_profile* const* profiles, int32_t n) {
   if (!profiles || n <= 0) return;
+  std::vector<hist_profile*> gone;
+  gone.reserve(n);
   for (int k = 0; k < n; ++k) {
     hist_profile* p = profiles[k];
     if (!p) continue;
+    if (p->refs > 0) {
+      p->doomed = true;
+      continue;
+    }
     cudaSetDevice(p->ctx->device);
     if (p->arena) arena_release(p->ctx, p->arena);
     else if (p->d_lp_absorb) cudaFreeAsync(p->d_lp_absorb, p->ctx->stream);
+    gone.push_back(p);
   }
-  parallel_for(n, 64, [&](int k) { delete profiles[k]; });
+  parallel_for((int)gone.size(), 64, [&](int k) { delete gone[k]; });
 }
 
 // ------------------------------------------------------------------ pair preparation
@@ -1112,6 +1123,8 @@ int finish_pending(hist_ctx* ctx, PrepPending& pd) {
     pr->info.n_cells = (int64_t)nc;
     pr->arena = pd.arena;
     ++pd.arena->refs;
+    ++const_cast<hist_profile*>(pr->x)->refs;
+    ++const_cast<hist_profile*>(pr->y)->refs;
     pd.out[k] = pr;
   }
   // every build record owns a few dozen host vectors: free them on the worker threads
@@ -1133,6 +1146,12 @@ void arena_release(hist_ctx* ctx, hb_arena* a) {
 }
 
 }  // namespace
+
+namespace hb {
+void host_parallel_for(int n, int grain, const std::function<void(int)>& fn) { parallel_for(n, grain, fn); }
+int ensure_staging_buf(hist_ctx* ctx, size_t bytes, int slot) { return ensure_staging(ctx, bytes, slot); }
+void arena_drop(hist_ctx* ctx, hb_arena* a) { arena_release(ctx, a); }
+}  // namespace hb
 
 namespace {
 // Host build, one H2D transfer and the table kernels of a sub-batch, enqueued on the context's stream through staging
@@ -1278,11 +1297,21 @@ extern "C" int hist_pair_prepare(hist_ctx* ctx, const hist_profile* x, const his
   return hist_pair_prepare_batch(ctx, 1, &x, &y, &hmm, &env, 0, out);
 }
 
+namespace {
+// a pair holds its two profiles (their host transition lists and the device lpAbsorb table are read after prepare)
+void profile_unref(const hist_profile* cp) {
+  hist_profile* p = const_cast<hist_profile*>(cp);
+  if (p && --p->refs == 0 && p->doomed) hist_profile_destroy(p);
+}
+}  // namespace
+
 extern "C" void hist_pair_destroy(hist_pair* pr) {
   if (!pr) return;
   cudaSetDevice(pr->ctx->device);
   if (pr->bwd_planes) cudaFreeAsync(pr->bwd_planes, pr->ctx->stream);
   arena_release(pr->ctx, pr->arena);
+  profile_unref(pr->x);
+  profile_unref(pr->y);
   delete pr;
 }
 
@@ -1294,6 +1323,8 @@ extern "C" void hist_pairs_destroy(hist_pair* const* pairs, int32_t n) {
     cudaSetDevice(pr->ctx->device);
     if (pr->bwd_planes) cudaFreeAsync(pr->bwd_planes, pr->ctx->stream);
     arena_release(pr->ctx, pr->arena);
+    profile_unref(pr->x);
+    profile_unref(pr->y);
   }
   parallel_for(n, 32, [&](int k) { delete pairs[k]; });   // the host-side vectors of a level: spread the frees
 }

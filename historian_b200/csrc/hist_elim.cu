@@ -5,19 +5,20 @@
 // become states of the parent profile, sum out the others in reverse order (lpPath by log-sum-exp,
 // lpBestAlignPath by max, remembering the eliminated cells along the best path) and gather the
 // states' absorb tables.  The alignPath / seqCoords / name assembly and addReadyStates
-// (profile.cpp:268-319) are host bookkeeping on top of this result.
+// (profile.cpp:268-319) are host bookkeeping on top of this result (hist_recon.cu).
 //
-// Kernels: (1) one thread per selected cell lists its in-set predecessors (binary search in the
-// sorted cell list) -> CSR of the selected sub-DAG + out-degree counts; (2) retained flags and
-// state numbering (CellCoords order, forward.cpp:703-732); (3) the reverse-order elimination, a
-// dependent chain over the sub-DAG, run by one thread over pooled sorted lists (the sub-DAG of a
-// merge is a few thousand cells; batching across merges is the parallel axis); (4) per-state
-// table gather and per-transition via-path expansion, fully parallel.
-#include <thrust/execution_policy.h>
-#include <thrust/scan.h>
-
+// Every kernel takes a BATCH of jobs (one per sibling merge of a guide-tree level; blockIdx.y = job):
+// (1) one thread per selected cell lists its in-set predecessors (binary search in the sorted cell
+// list) -> CSR of the selected sub-DAG + out-degree counts; (2) retained flags and state numbering
+// (CellCoords order, forward.cpp:703-732); (3) the reverse-order elimination, a dependent chain over
+// the sub-DAG of one merge, run by one thread per job over pooled sorted lists (the sub-DAG of a
+// merge is a few thousand cells; the jobs of a level are the parallel axis); (4) a packing pass that
+// lays the results of every job out compactly for ONE device->host copy; (5) the states' absorb rows
+// are gathered straight into the parent profiles' device tables (gather_absorb_rows), they never
+// visit the host.
 #include <algorithm>
 #include <cmath>
+#include <cstring>
 #include <vector>
 
 #include "hist_dpgraph.cuh"
@@ -42,11 +43,13 @@ struct ElimDev {
   int* p_k; int* p_next; int* p_via_cell; int* p_via_next;
   double* p_path; double* p_best;
   // results
-  int* counts;          // [4]: n_states, n_trans, n_via (low/high words unused), pool overflow flag
+  int* counts;          // [4]: n_states, n_trans, unused, pool overflow flag
   long long* n_via;     // [1]
   int* t_src; int* t_dst; int* t_entry;   // [pool_cap]
   double* t_lp; double* t_best;
   long long* t_via_off; // [pool_cap + 1]
+  // packed output of this job (set once the counts are known): state cells, transitions, via lists
+  hist_cell* o_state; int* o_src; int* o_dst; double* o_lp; double* o_best; long long* o_via_off; hist_cell* o_via;
 };
 
 __device__ __forceinline__ int find_cell(const DCell* cells, int n, const DCell& c) {
@@ -59,29 +62,70 @@ __device__ __forceinline__ int find_cell(const DCell* cells, int n, const DCell&
 }
 
 // pass 0: count in-set sources of every cell and out-degrees; pass 1: fill the CSR
-__global__ void elim_edges_kernel(ElimDev E, int pass) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= E.n) return;
+__global__ void elim_edges_kernel(const ElimDev* __restrict__ jobs, int pass) {
+  const ElimDev E = jobs[blockIdx.y];
   const PairDev& P = *E.P;
-  const DCell d = E.cells[c];
-  const SrcEnum e = source_enum(P, d, nullptr);
-  int cnt = 0;
-  const int base = pass ? E.in_cnt[c] : 0;
-  for (int q = 0; q < e.n; ++q) {
-    DCell s;
-    double lp;
-    source_get(P, P.Wlog, d, e, q, s, lp);
-    const int si = find_cell(E.cells, E.n, s);
-    if (si < 0) continue;
-    if (pass) {
-      E.e_src[base + cnt] = si;
-      E.e_lp[base + cnt] = lp;
-    } else {
-      atomicAdd(E.out_cnt + si, 1);
+  for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < E.n; c += gridDim.x * blockDim.x) {
+    const DCell d = E.cells[c];
+    const SrcEnum e = source_enum(P, d, nullptr);
+    int cnt = 0;
+    const int base = pass ? E.in_cnt[c] : 0;
+    for (int q = 0; q < e.n; ++q) {
+      DCell s;
+      double lp;
+      source_get(P, P.Wlog, d, e, q, s, lp);
+      const int si = find_cell(E.cells, E.n, s);
+      if (si < 0) continue;
+      if (pass) {
+        E.e_src[base + cnt] = si;
+        E.e_lp[base + cnt] = lp;
+      } else {
+        atomicAdd(E.out_cnt + si, 1);
+      }
+      ++cnt;
     }
-    ++cnt;
+    if (!pass) E.in_cnt[c] = cnt;
   }
-  if (!pass) E.in_cnt[c] = cnt;
+}
+
+// Exclusive scan of in_cnt (which == 0) or retained (which == 1) over n+1 entries, one CTA per job;
+// totals[job] receives the sum.
+__global__ void __launch_bounds__(1024) elim_scan_kernel(const ElimDev* __restrict__ jobs, int which, int* __restrict__ totals) {
+  const ElimDev E = jobs[blockIdx.x];
+  int* a = which ? E.retained : E.in_cnt;
+  const int n = E.n + 1;
+  __shared__ int wsum[32];
+  __shared__ int carry;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  for (int base = 0; base < n; base += blockDim.x) {
+    const int i = base + threadIdx.x;
+    const int v = i < n ? a[i] : 0;
+    int x = v;
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= o) x += y;
+    }
+    if (lane == 31) wsum[w] = x;
+    __syncthreads();
+    if (w == 0) {
+      int s = lane < nw ? wsum[lane] : 0;
+      for (int o = 1; o < 32; o <<= 1) {
+        const int y = __shfl_up_sync(0xffffffffu, s, o);
+        if (lane >= o) s += y;
+      }
+      wsum[lane] = s;
+    }
+    __syncthreads();
+    const int c0 = carry;
+    const int incl = c0 + (w ? wsum[w - 1] : 0) + x;
+    if (i < n) a[i] = incl - v;
+    __syncthreads();
+    if (threadIdx.x == blockDim.x - 1) carry = incl;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0 && totals) totals[blockIdx.x] = carry;
 }
 
 // isAbsorbing (forward.cpp:470-474)
@@ -90,21 +134,22 @@ __device__ __forceinline__ bool is_absorbing(const PairDev& P, const DCell& c) {
   return (c.s == HIST_IMM && xe && ye) || (c.s == HIST_IMD && xe) || (c.s == HIST_IDM && ye);
 }
 
-__global__ void elim_retain_kernel(ElimDev E) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= E.n) return;
+__global__ void elim_retain_kernel(const ElimDev* __restrict__ jobs) {
+  const ElimDev E = jobs[blockIdx.y];
   const PairDev& P = *E.P;
-  const DCell d = E.cells[c];
-  const bool isStart = d.x == 0 && d.y == 0 && d.s == HIST_IMM;
-  const bool isEnd = d.x == P.x.n - 1 && d.y == P.y.n - 1 && d.s == HIST_EEE;
-  // forward.cpp:703-709
-  E.retained[c] = (is_absorbing(P, d) || isStart || isEnd || E.out_cnt[c] > 1 || (E.strategy & HIST_KEEP_GAPS_OPEN) ||
-                   !(E.strategy & HIST_COLLAPSE_CHAINS)) ? 1 : 0;
-  E.head[c] = -1;
+  for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < E.n; c += gridDim.x * blockDim.x) {
+    const DCell d = E.cells[c];
+    const bool isStart = d.x == 0 && d.y == 0 && d.s == HIST_IMM;
+    const bool isEnd = d.x == P.x.n - 1 && d.y == P.y.n - 1 && d.s == HIST_EEE;
+    // forward.cpp:703-709
+    E.retained[c] = (is_absorbing(P, d) || isStart || isEnd || E.out_cnt[c] > 1 || (E.strategy & HIST_KEEP_GAPS_OPEN) ||
+                     !(E.strategy & HIST_COLLAPSE_CHAINS)) ? 1 : 0;
+    E.head[c] = -1;
+  }
 }
 
 // find-or-insert the entry of destination state k in the sorted list of cell s; -1 on pool overflow
-__device__ int pool_entry(ElimDev& E, int& pool_n, int s, int k) {
+__device__ int pool_entry(const ElimDev& E, int& pool_n, int s, int k) {
   int prev = -1, cur = E.head[s];
   while (cur >= 0 && E.p_k[cur] < k) { prev = cur; cur = E.p_next[cur]; }
   if (cur >= 0 && E.p_k[cur] == k) return cur;
@@ -122,8 +167,10 @@ __device__ int pool_entry(ElimDev& E, int& pool_n, int s, int k) {
 
 // forward.cpp:751-807, then the transition list of forward.cpp:810-831.  `retained` holds state indices
 // (exclusive scan) with retained[n] = number of states; is_ret = retained[c+1] != retained[c].
-__global__ void elim_reduce_kernel(ElimDev E) {
-  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+// One thread per job.
+__global__ void elim_reduce_kernel(const ElimDev* __restrict__ jobs) {
+  if (threadIdx.x != 0) return;
+  const ElimDev E = jobs[blockIdx.x];
   const PairDev& P = *E.P;
   int pool_n = 0;
   bool overflow = false;
@@ -179,41 +226,281 @@ __global__ void elim_reduce_kernel(ElimDev E) {
   E.t_via_off[nt] = nv;
   E.counts[0] = E.retained[E.n];
   E.counts[1] = nt;
+  E.counts[2] = 0;
   E.counts[3] = overflow ? 1 : 0;
   *E.n_via = nv;
 }
 
-// state cells, absorb tables (forward.cpp:713-727) and fwdLogProb (forward.cpp:731)
-__global__ void elim_states_kernel(ElimDev E, double lp_end, hist_cell* st_cell, double* st_abs, double* st_fwd) {
-  const int c = blockIdx.x;
-  if (E.retained[c + 1] == E.retained[c]) return;
-  const PairDev& P = *E.P;
-  const int k = E.retained[c];
-  const DCell d = E.cells[c];
-  const bool ab = is_absorbing(P, d);
-  for (int q = threadIdx.x; q < P.K; q += blockDim.x) {
-    double v = -INFINITY;
-    if (ab) {
-      if (d.s == HIST_IMM) v = P.x.sub[(size_t)d.x * P.K + q] + P.y.sub[(size_t)d.y * P.K + q];
-      else if (d.s == HIST_IMD) v = P.x.sub[(size_t)d.x * P.K + q];
-      else v = P.y.sub[(size_t)d.y * P.K + q];
+// compact results of every job: state cells in state order, transitions, via lists
+__global__ void elim_pack_kernel(const ElimDev* __restrict__ jobs) {
+  const ElimDev E = jobs[blockIdx.y];
+  if (!E.o_state) return;
+  const int nt = E.counts[1];
+  const int stride = gridDim.x * blockDim.x, t0 = blockIdx.x * blockDim.x + threadIdx.x;
+  for (int c = t0; c < E.n; c += stride)
+    if (E.retained[c + 1] != E.retained[c]) {
+      const DCell d = E.cells[c];
+      E.o_state[E.retained[c]] = {d.x, d.y, d.s};
     }
-    st_abs[(size_t)k * P.K + q] = v;
-  }
-  if (threadIdx.x == 0) {
-    st_cell[k] = {d.x, d.y, d.s};
-    st_fwd[k] = d.s == HIST_EEE ? lp_end : dp_cell(P, false, d.x, d.y, d.s);
+  for (int t = t0; t <= nt; t += stride) {
+    E.o_via_off[t] = E.t_via_off[t];
+    if (t == nt) break;
+    E.o_src[t] = E.t_src[t];
+    E.o_dst[t] = E.t_dst[t];
+    E.o_lp[t] = E.t_lp[t];
+    E.o_best[t] = E.t_best[t];
+    long long o = E.t_via_off[t];
+    for (int v = E.t_entry[t]; v >= 0 && E.p_via_cell[v] >= 0; v = E.p_via_next[v]) {
+      const DCell c = E.cells[E.p_via_cell[v]];
+      E.o_via[o++] = {c.x, c.y, c.s};
+    }
   }
 }
 
-__global__ void elim_via_kernel(ElimDev E, int n_trans, hist_cell* via) {
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= n_trans) return;
-  long long o = E.t_via_off[t];
-  for (int v = E.t_entry[t]; v >= 0 && E.p_via_cell[v] >= 0; v = E.p_via_next[v]) {
-    const DCell c = E.cells[E.p_via_cell[v]];
-    via[o++] = {c.x, c.y, c.s};
+// absorb tables of profile states (forward.cpp:713-727): IMM both-emit -> subx[i] + suby[j], IMD -> subx[i], IDM -> suby[j];
+// anything else (and s < 0) is a null state: a row of -inf.  One warp per row.
+__global__ void gather_rows_kernel(const GatherRow* __restrict__ rows, long long n_rows, int K, double* __restrict__ out) {
+  const long long r = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (r >= n_rows) return;
+  const GatherRow g = rows[r];
+  const int lane = threadIdx.x & 31;
+  int mode = 0;   // 0 null, 1 x + y, 2 x, 3 y
+  if (g.s >= 0) {
+    const PairDev& P = *g.P;
+    const bool xe = P.x.flags[g.x] & F_EMIT, ye = P.y.flags[g.y] & F_EMIT;
+    if (g.s == HIST_IMM && xe && ye) mode = 1;
+    else if (g.s == HIST_IMD && xe) mode = 2;
+    else if (g.s == HIST_IDM && ye) mode = 3;
   }
+  double* o = out + r * K;
+  if (mode == 0) {
+    for (int q = lane; q < K; q += 32) o[q] = -INFINITY;
+    return;
+  }
+  const PairDev& P = *g.P;
+  const double* sx = P.x.sub + (size_t)g.x * K;
+  const double* sy = P.y.sub + (size_t)g.y * K;
+  for (int q = lane; q < K; q += 32) o[q] = mode == 1 ? sx[q] + sy[q] : mode == 2 ? sx[q] : sy[q];
+}
+
+// fwdLogProb tag of each state (forward.cpp:731)
+__global__ void elim_fwd_kernel(const PairDev* __restrict__ Pp, const hist_cell* __restrict__ st, int ns, double lp_end, double* __restrict__ out) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= ns) return;
+  const hist_cell d = st[k];
+  out[k] = d.state == HIST_EEE ? lp_end : dp_cell(*Pp, false, d.xpos, d.ypos, d.state);
+}
+
+int gather_absorb_rows(hist_ctx* ctx, const GatherRow* d_rows, long long n_rows, int K, double* d_out) {
+  if (n_rows <= 0) return HIST_OK;
+  const int warps = 8;
+  gather_rows_kernel<<<(unsigned)((n_rows + warps - 1) / warps), 32 * warps, 0, ctx->stream>>>(d_rows, n_rows, K, d_out);
+  ctx->launches += 1;
+  return check_cuda(ctx, cudaGetLastError(), "gather_rows_kernel");
+}
+
+namespace {
+struct JobLayout {
+  size_t cells, in, out, ret, head, pk, pn, pvc, pvn, pp, pb, cnt, nv, ts, td, te, tl, tb, tv, end;
+  long long pool_cap;
+};
+
+JobLayout layout_job(size_t base, int n, long long pool_cap, bool own_cells) {
+  JobLayout L;
+  size_t off = base;
+  auto take = [&](size_t bytes) { off = (off + 15) / 16 * 16; const size_t o = off; off += bytes; return o; };
+  L.pool_cap = pool_cap;
+  L.cells = take(own_cells ? (size_t)n * sizeof(DCell) : 0);
+  L.in = take((size_t)(n + 1) * 4); L.out = take((size_t)n * 4); L.ret = take((size_t)(n + 1) * 4); L.head = take((size_t)n * 4);
+  L.pk = take((size_t)pool_cap * 4); L.pn = take((size_t)pool_cap * 4); L.pvc = take((size_t)pool_cap * 4); L.pvn = take((size_t)pool_cap * 4);
+  L.pp = take((size_t)pool_cap * 8); L.pb = take((size_t)pool_cap * 8); L.cnt = take(16); L.nv = take(8);
+  L.ts = take((size_t)pool_cap * 4); L.td = take((size_t)pool_cap * 4); L.te = take((size_t)pool_cap * 4);
+  L.tl = take((size_t)pool_cap * 8); L.tb = take((size_t)pool_cap * 8); L.tv = take((size_t)(pool_cap + 1) * 8);
+  L.end = (off + 255) & ~(size_t)255;
+  return L;
+}
+
+// One attempt over a set of jobs with the given pool capacities; overflowed[k] is set for jobs whose pool ran out.
+int eliminate_attempt(hist_ctx* ctx, const std::vector<ElimJob>& jobs, const std::vector<int>& which, const std::vector<long long>& pool_cap,
+                      std::vector<ElimOut>& out, std::vector<char>& overflowed) {
+  static_assert(sizeof(DCell) == sizeof(hist_cell), "cell layouts must agree");
+  const int nj = (int)which.size();
+  std::vector<JobLayout> L(nj);
+  size_t total = ((size_t)nj * sizeof(ElimDev) + 255) & ~(size_t)255;
+  const size_t tot_off = total;
+  total += ((size_t)nj * sizeof(int) + 255) & ~(size_t)255;
+  int max_n = 1;
+  for (int q = 0; q < nj; ++q) {
+    const ElimJob& J = jobs[which[q]];
+    L[q] = layout_job(total, J.n, pool_cap[q], J.d_cells == nullptr);
+    total = L[q].end;
+    max_n = std::max(max_n, J.n);
+  }
+  char* buf = nullptr;
+  HB_CUDA(ctx, cudaMallocAsync((void**)&buf, total, ctx->stream));
+  char* ebuf = nullptr;
+  char* obuf = nullptr;
+  auto cleanup = [&]() {
+    if (obuf) cudaFreeAsync(obuf, ctx->stream);
+    if (ebuf) cudaFreeAsync(ebuf, ctx->stream);
+    cudaFreeAsync(buf, ctx->stream);
+  };
+  std::vector<ElimDev> E(nj);
+  int rc = HIST_OK;
+  for (int q = 0; q < nj && !rc; ++q) {
+    const ElimJob& J = jobs[which[q]];
+    const JobLayout& l = L[q];
+    ElimDev& e = E[q];
+    memset(&e, 0, sizeof(e));
+    e.P = J.pair->d_dev;
+    e.n = J.n;
+    e.strategy = J.strategy;
+    if (J.d_cells) e.cells = (const DCell*)J.d_cells;
+    else {
+      e.cells = (const DCell*)(buf + l.cells);
+      rc = check_cuda(ctx, cudaMemcpyAsync(buf + l.cells, J.h_cells, (size_t)J.n * sizeof(DCell), cudaMemcpyHostToDevice, ctx->stream), "H2D cells");
+    }
+    e.in_cnt = (int*)(buf + l.in); e.out_cnt = (int*)(buf + l.out); e.retained = (int*)(buf + l.ret); e.head = (int*)(buf + l.head);
+    e.pool_cap = (int)l.pool_cap;
+    e.p_k = (int*)(buf + l.pk); e.p_next = (int*)(buf + l.pn); e.p_via_cell = (int*)(buf + l.pvc); e.p_via_next = (int*)(buf + l.pvn);
+    e.p_path = (double*)(buf + l.pp); e.p_best = (double*)(buf + l.pb);
+    e.counts = (int*)(buf + l.cnt); e.n_via = (long long*)(buf + l.nv);
+    e.t_src = (int*)(buf + l.ts); e.t_dst = (int*)(buf + l.td); e.t_entry = (int*)(buf + l.te);
+    e.t_lp = (double*)(buf + l.tl); e.t_best = (double*)(buf + l.tb); e.t_via_off = (long long*)(buf + l.tv);
+    if (!rc) rc = check_cuda(ctx, cudaMemsetAsync(buf + l.in, 0, l.head - l.in, ctx->stream), "memset counts");
+  }
+  if (rc) { cleanup(); return rc; }
+  ElimDev* d_jobs = (ElimDev*)buf;
+  int* d_tot = (int*)(buf + tot_off);
+  auto upload_jobs = [&]() { return check_cuda(ctx, cudaMemcpyAsync(d_jobs, E.data(), (size_t)nj * sizeof(ElimDev), cudaMemcpyHostToDevice, ctx->stream), "H2D jobs"); };
+  rc = upload_jobs();
+  if (rc) { cleanup(); return rc; }
+  const int tb = 128;
+  const dim3 grid((unsigned)std::min(64, (max_n + tb - 1) / tb), (unsigned)nj);
+  elim_edges_kernel<<<grid, tb, 0, ctx->stream>>>(d_jobs, 0);
+  elim_scan_kernel<<<nj, 1024, 0, ctx->stream>>>(d_jobs, 0, d_tot);
+  ctx->launches += 2;
+  std::vector<int> n_edges(nj);
+  rc = check_cuda(ctx, cudaGetLastError(), "elimination kernels (edges)");
+  if (!rc) rc = check_cuda(ctx, cudaMemcpyAsync(n_edges.data(), d_tot, (size_t)nj * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream), "D2H edge counts");
+  if (!rc) rc = check_cuda(ctx, cudaStreamSynchronize(ctx->stream), "sync");
+  if (rc) { cleanup(); return rc; }
+  size_t etot = 0;
+  std::vector<size_t> eoff(nj);
+  for (int q = 0; q < nj; ++q) {
+    eoff[q] = etot;
+    etot += ((size_t)std::max(n_edges[q], 1) * 12 + 255) & ~(size_t)255;
+  }
+  rc = check_cuda(ctx, cudaMallocAsync((void**)&ebuf, etot, ctx->stream), "cudaMallocAsync(edges)");
+  if (rc) { ebuf = nullptr; cleanup(); return rc; }
+  for (int q = 0; q < nj; ++q) {
+    E[q].e_lp = (double*)(ebuf + eoff[q]);
+    E[q].e_src = (int*)(ebuf + eoff[q] + (size_t)std::max(n_edges[q], 1) * 8);
+  }
+  rc = upload_jobs();
+  if (rc) { cleanup(); return rc; }
+  elim_edges_kernel<<<grid, tb, 0, ctx->stream>>>(d_jobs, 1);
+  elim_retain_kernel<<<grid, tb, 0, ctx->stream>>>(d_jobs);
+  elim_scan_kernel<<<nj, 1024, 0, ctx->stream>>>(d_jobs, 1, nullptr);
+  elim_reduce_kernel<<<nj, 32, 0, ctx->stream>>>(d_jobs);
+  ctx->launches += 4;
+  rc = check_cuda(ctx, cudaGetLastError(), "elimination kernels");
+  std::vector<int> counts((size_t)nj * 4);
+  std::vector<long long> nvia(nj);
+  for (int q = 0; q < nj && !rc; ++q) {
+    rc = check_cuda(ctx, cudaMemcpyAsync(&counts[(size_t)q * 4], E[q].counts, 16, cudaMemcpyDeviceToHost, ctx->stream), "D2H counts");
+    if (!rc) rc = check_cuda(ctx, cudaMemcpyAsync(&nvia[q], E[q].n_via, 8, cudaMemcpyDeviceToHost, ctx->stream), "D2H via count");
+  }
+  if (!rc) rc = check_cuda(ctx, cudaStreamSynchronize(ctx->stream), "sync");
+  if (rc) { cleanup(); return rc; }
+  // ---- packed results, one device->host copy
+  size_t otot = 0;
+  std::vector<size_t> o_base(nj);
+  struct OOff { size_t st, src, dst, lp, best, voff, via, end; };
+  std::vector<OOff> oo(nj);
+  int max_work = 1;
+  for (int q = 0; q < nj; ++q) {
+    overflowed[q] = counts[(size_t)q * 4 + 3] != 0;
+    if (overflowed[q]) continue;
+    const size_t ns = counts[(size_t)q * 4], nt = counts[(size_t)q * 4 + 1], nv = (size_t)nvia[q];
+    size_t off = otot;
+    auto take = [&](size_t bytes) { off = (off + 15) / 16 * 16; const size_t o = off; off += bytes; return o; };
+    oo[q].voff = take((nt + 1) * 8); oo[q].lp = take(nt * 8); oo[q].best = take(nt * 8);
+    oo[q].st = take(ns * sizeof(hist_cell)); oo[q].via = take(nv * sizeof(hist_cell));
+    oo[q].src = take(nt * 4); oo[q].dst = take(nt * 4);
+    oo[q].end = (off + 15) / 16 * 16;
+    otot = oo[q].end;
+    max_work = std::max(max_work, std::max(jobs[which[q]].n, (int)nt + 1));
+  }
+  if (otot) {
+    rc = check_cuda(ctx, cudaMallocAsync((void**)&obuf, otot, ctx->stream), "cudaMallocAsync(results)");
+    if (rc) { obuf = nullptr; cleanup(); return rc; }
+    for (int q = 0; q < nj; ++q) {
+      if (overflowed[q]) continue;
+      E[q].o_state = (hist_cell*)(obuf + oo[q].st); E[q].o_src = (int*)(obuf + oo[q].src); E[q].o_dst = (int*)(obuf + oo[q].dst);
+      E[q].o_lp = (double*)(obuf + oo[q].lp); E[q].o_best = (double*)(obuf + oo[q].best);
+      E[q].o_via_off = (long long*)(obuf + oo[q].voff); E[q].o_via = (hist_cell*)(obuf + oo[q].via);
+    }
+    rc = upload_jobs();
+    if (!rc) {
+      elim_pack_kernel<<<dim3((unsigned)std::min(64, (max_work + tb - 1) / tb), (unsigned)nj), tb, 0, ctx->stream>>>(d_jobs);
+      ctx->launches += 1;
+      rc = check_cuda(ctx, cudaGetLastError(), "elim_pack_kernel");
+    }
+    std::vector<char> host;
+    if (!rc) {
+      host.resize(otot);
+      rc = check_cuda(ctx, cudaMemcpyAsync(host.data(), obuf, otot, cudaMemcpyDeviceToHost, ctx->stream), "D2H elimination results");
+    }
+    if (!rc) rc = check_cuda(ctx, cudaStreamSynchronize(ctx->stream), "sync");
+    if (rc) { cleanup(); return rc; }
+    host_parallel_for(nj, 16, [&](int q) {
+      if (overflowed[q]) return;
+      ElimOut& o = out[which[q]];
+      const size_t ns = counts[(size_t)q * 4], nt = counts[(size_t)q * 4 + 1], nv = (size_t)nvia[q];
+      o.n_states = (int)ns; o.n_trans = (int)nt; o.n_via = (long long)nv;
+      const char* h = host.data();
+      o.state_cell.assign((const hist_cell*)(h + oo[q].st), (const hist_cell*)(h + oo[q].st) + ns);
+      o.t_src.assign((const int*)(h + oo[q].src), (const int*)(h + oo[q].src) + nt);
+      o.t_dst.assign((const int*)(h + oo[q].dst), (const int*)(h + oo[q].dst) + nt);
+      o.t_lp.assign((const double*)(h + oo[q].lp), (const double*)(h + oo[q].lp) + nt);
+      o.t_best.assign((const double*)(h + oo[q].best), (const double*)(h + oo[q].best) + nt);
+      o.via_off.assign((const long long*)(h + oo[q].voff), (const long long*)(h + oo[q].voff) + nt + 1);
+      o.via.assign((const hist_cell*)(h + oo[q].via), (const hist_cell*)(h + oo[q].via) + nv);
+    });
+  }
+  cleanup();
+  return HIST_OK;
+}
+}  // namespace
+
+int eliminate_batch(hist_ctx* ctx, const std::vector<ElimJob>& jobs, std::vector<ElimOut>& out) {
+  const int nj = (int)jobs.size();
+  out.assign(nj, ElimOut());
+  if (!nj) return HIST_OK;
+  cudaSetDevice(ctx->device);
+  std::vector<int> which(nj);
+  std::vector<long long> cap(nj);
+  for (int k = 0; k < nj; ++k) {
+    which[k] = k;
+    cap[k] = 8ll * jobs[k].n + 1024;
+  }
+  while (!which.empty()) {
+    std::vector<char> over(which.size(), 0);
+    const int rc = eliminate_attempt(ctx, jobs, which, cap, out, over);
+    if (rc) return rc;
+    std::vector<int> again;
+    std::vector<long long> cap2;
+    for (size_t q = 0; q < which.size(); ++q)
+      if (over[q]) {   // pool too small: retry this job with a larger one
+        if (cap[q] > (1ll << 28)) return set_err(ctx, HIST_ERR_CAPACITY, "hist_profile_eliminate: effective-transition pool exhausted");
+        again.push_back(which[q]);
+        cap2.push_back(cap[q] * 4);
+      }
+    which.swap(again);
+    cap.swap(cap2);
+  }
+  return HIST_OK;
 }
 
 }  // namespace hb
@@ -226,7 +513,7 @@ extern "C" int hist_profile_eliminate(hist_pair* pair, const hist_cell* cells, i
   if (!pair->fwd_done) return set_err(ctx, HIST_ERR_STATE, "hist_profile_eliminate: the Forward matrix has not been filled");
   if (!pair->x->sorted_in || !pair->y->sorted_in)
     return set_err(ctx, HIST_ERR_ARG, "hist_profile_eliminate: profile transitions must be sorted by (source, destination) without repeats");
-  if (n_cells > (1ll << 28)) return set_err(ctx, HIST_ERR_ARG, "hist_profile_eliminate: too many cells");
+  if (n_cells > (1ll << 24)) return set_err(ctx, HIST_ERR_ARG, "hist_profile_eliminate: too many cells");
   const int n = (int)n_cells, nx = pair->info.x_size, ny = pair->info.y_size, K = pair->dev.K;
   for (int k = 0; k < n; ++k) {
     const hist_cell& c = cells[k];
@@ -244,105 +531,46 @@ extern "C" int hist_profile_eliminate(hist_pair* pair, const hist_cell* cells, i
     return set_err(ctx, HIST_ERR_ARG, "hist_profile_eliminate: the cell set must contain the start cell (0,0,IMM) and the end cell");
   cudaSetDevice(ctx->device);
 
-  int rc = HIST_OK;
-  for (int pool_cap = 8 * n + 1024;; pool_cap *= 4) {
-    // ---- scratch
-    size_t off = 0;
-    auto take = [&](size_t bytes) { off = (off + 15) / 16 * 16; const size_t o = off; off += bytes; return o; };
-    const size_t o_cells = take((size_t)n * sizeof(DCell)), o_in = take((size_t)(n + 1) * 4), o_out = take((size_t)n * 4),
-                 o_ret = take((size_t)(n + 1) * 4), o_head = take((size_t)n * 4), o_pk = take((size_t)pool_cap * 4),
-                 o_pn = take((size_t)pool_cap * 4), o_pvc = take((size_t)pool_cap * 4), o_pvn = take((size_t)pool_cap * 4),
-                 o_pp = take((size_t)pool_cap * 8), o_pb = take((size_t)pool_cap * 8), o_cnt = take(16), o_nv = take(8),
-                 o_ts = take((size_t)pool_cap * 4), o_td = take((size_t)pool_cap * 4), o_te = take((size_t)pool_cap * 4),
-                 o_tl = take((size_t)pool_cap * 8), o_tb = take((size_t)pool_cap * 8), o_tv = take((size_t)(pool_cap + 1) * 8);
-    char* buf = nullptr;
-    HB_CUDA(ctx, cudaMallocAsync((void**)&buf, off, ctx->stream));
-    ElimDev E;
-    E.P = pair->d_dev;
-    E.cells = (const DCell*)(buf + o_cells);
-    E.n = n;
-    E.strategy = strategy;
-    E.in_cnt = (int*)(buf + o_in); E.out_cnt = (int*)(buf + o_out);
-    E.retained = (int*)(buf + o_ret); E.head = (int*)(buf + o_head);
-    E.pool_cap = pool_cap;
-    E.p_k = (int*)(buf + o_pk); E.p_next = (int*)(buf + o_pn); E.p_via_cell = (int*)(buf + o_pvc); E.p_via_next = (int*)(buf + o_pvn);
-    E.p_path = (double*)(buf + o_pp); E.p_best = (double*)(buf + o_pb);
-    E.counts = (int*)(buf + o_cnt); E.n_via = (long long*)(buf + o_nv);
-    E.t_src = (int*)(buf + o_ts); E.t_dst = (int*)(buf + o_td); E.t_entry = (int*)(buf + o_te);
-    E.t_lp = (double*)(buf + o_tl); E.t_best = (double*)(buf + o_tb); E.t_via_off = (long long*)(buf + o_tv);
-    E.e_src = nullptr; E.e_lp = nullptr;
-    auto cleanup = [&](char* extra) { if (extra) cudaFreeAsync(extra, ctx->stream); cudaFreeAsync(buf, ctx->stream); };
-    static_assert(sizeof(DCell) == sizeof(hist_cell), "cell layouts must agree");
-    rc = check_cuda(ctx, cudaMemcpyAsync(buf + o_cells, cells, (size_t)n * sizeof(DCell), cudaMemcpyHostToDevice, ctx->stream), "H2D cells");
-    if (!rc) rc = check_cuda(ctx, cudaMemsetAsync(buf + o_in, 0, o_head - o_in, ctx->stream), "memset counts");
-    if (rc) { cleanup(nullptr); return rc; }
-    const int tb = 128, gb = (n + tb - 1) / tb;
-    elim_edges_kernel<<<gb, tb, 0, ctx->stream>>>(E, 0);
-    thrust::exclusive_scan(thrust::cuda::par.on(ctx->stream), E.in_cnt, E.in_cnt + n + 1, E.in_cnt);
-    int n_edges = 0;
-    rc = check_cuda(ctx, cudaMemcpyAsync(&n_edges, E.in_cnt + n, 4, cudaMemcpyDeviceToHost, ctx->stream), "D2H edge count");
-    if (!rc) rc = check_cuda(ctx, cudaStreamSynchronize(ctx->stream), "sync");
-    if (rc) { cleanup(nullptr); return rc; }
-    char* ebuf = nullptr;
-    const size_t eb = (size_t)std::max(n_edges, 1);
-    rc = check_cuda(ctx, cudaMallocAsync((void**)&ebuf, eb * 16, ctx->stream), "cudaMallocAsync(edges)");
-    if (rc) { cleanup(nullptr); return rc; }
-    E.e_lp = (double*)ebuf;
-    E.e_src = (int*)(ebuf + eb * 8);
-    elim_edges_kernel<<<gb, tb, 0, ctx->stream>>>(E, 1);
-    elim_retain_kernel<<<gb, tb, 0, ctx->stream>>>(E);
-    thrust::exclusive_scan(thrust::cuda::par.on(ctx->stream), E.retained, E.retained + n + 1, E.retained);
-    elim_reduce_kernel<<<1, 32, 0, ctx->stream>>>(E);
-    ctx->launches += 6;
-    int counts[4] = {0, 0, 0, 0};
-    long long nvia = 0;
-    rc = check_cuda(ctx, cudaGetLastError(), "elimination kernels");
-    if (!rc) rc = check_cuda(ctx, cudaMemcpyAsync(counts, E.counts, 16, cudaMemcpyDeviceToHost, ctx->stream), "D2H counts");
-    if (!rc) rc = check_cuda(ctx, cudaMemcpyAsync(&nvia, E.n_via, 8, cudaMemcpyDeviceToHost, ctx->stream), "D2H via count");
-    if (!rc) rc = check_cuda(ctx, cudaStreamSynchronize(ctx->stream), "sync");
-    if (rc) { cleanup(ebuf); return rc; }
-    if (counts[3]) {  // pool too small: retry with a larger one
-      cleanup(ebuf);
-      if (pool_cap > (1 << 28)) return set_err(ctx, HIST_ERR_CAPACITY, "hist_profile_eliminate: effective-transition pool exhausted");
-      continue;
-    }
-    const int ns = counts[0], nt = counts[1];
-    r->n_states = ns;
-    r->n_trans = nt;
-    r->n_via = nvia;
-    if (ns > r->state_capacity || nt > r->trans_capacity || nvia > r->via_capacity) {
-      cleanup(ebuf);
-      return set_err(ctx, HIST_ERR_CAPACITY, "hist_profile_eliminate: need %d states, %d transitions, %lld via cells", ns, nt, nvia);
-    }
-    // ---- results
-    char* obuf = nullptr;
-    const size_t b_cell = ((size_t)ns * sizeof(hist_cell) + 15) / 16 * 16, b_abs = (size_t)ns * K * 8, b_fwd = (size_t)ns * 8,
-                 b_via = (size_t)std::max<long long>(nvia, 1) * sizeof(hist_cell);
-    rc = check_cuda(ctx, cudaMallocAsync((void**)&obuf, b_cell + b_abs + b_fwd + b_via, ctx->stream), "cudaMallocAsync(results)");
-    if (rc) { cleanup(ebuf); return rc; }
-    hist_cell* d_cell = (hist_cell*)obuf;
-    double* d_abs = (double*)(obuf + b_cell);
-    double* d_fwd = (double*)(obuf + b_cell + b_abs);
-    hist_cell* d_via = (hist_cell*)(obuf + b_cell + b_abs + b_fwd);
-    elim_states_kernel<<<n, 64, 0, ctx->stream>>>(E, pair->lp_end, d_cell, d_abs, d_fwd);
-    if (nt) elim_via_kernel<<<(nt + 127) / 128, 128, 0, ctx->stream>>>(E, nt, d_via);
-    ctx->launches += 2;
-    rc = check_cuda(ctx, cudaGetLastError(), "result kernels");
-    auto d2h = [&](void* dst, const void* src, size_t bytes) {
-      if (!rc && bytes) rc = check_cuda(ctx, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->stream), "D2H results");
-    };
-    d2h(r->state_cell, d_cell, (size_t)ns * sizeof(hist_cell));
-    d2h(r->state_lp_absorb, d_abs, b_abs);
-    d2h(r->state_fwd_lp, d_fwd, b_fwd);
-    d2h(r->trans_src, E.t_src, (size_t)nt * 4);
-    d2h(r->trans_dest, E.t_dst, (size_t)nt * 4);
-    d2h(r->trans_lp, E.t_lp, (size_t)nt * 8);
-    d2h(r->trans_best_lp, E.t_best, (size_t)nt * 8);
-    d2h(r->trans_best_via_off, E.t_via_off, (size_t)(nt + 1) * 8);
-    d2h(r->trans_best_via, d_via, (size_t)nvia * sizeof(hist_cell));
-    if (!rc) rc = check_cuda(ctx, cudaStreamSynchronize(ctx->stream), "sync");
-    cudaFreeAsync(obuf, ctx->stream);
-    cleanup(ebuf);
-    return rc;
+  std::vector<ElimJob> jobs(1);
+  jobs[0] = {pair, nullptr, cells, n, strategy};
+  std::vector<ElimOut> outs;
+  int rc = eliminate_batch(ctx, jobs, outs);
+  if (rc) return rc;
+  const ElimOut& o = outs[0];
+  const int ns = o.n_states, nt = o.n_trans;
+  r->n_states = ns;
+  r->n_trans = nt;
+  r->n_via = o.n_via;
+  if (ns > r->state_capacity || nt > r->trans_capacity || o.n_via > r->via_capacity)
+    return set_err(ctx, HIST_ERR_CAPACITY, "hist_profile_eliminate: need %d states, %d transitions, %lld via cells", ns, nt, o.n_via);
+  memcpy(r->state_cell, o.state_cell.data(), (size_t)ns * sizeof(hist_cell));
+  memcpy(r->trans_src, o.t_src.data(), (size_t)nt * 4);
+  memcpy(r->trans_dest, o.t_dst.data(), (size_t)nt * 4);
+  memcpy(r->trans_lp, o.t_lp.data(), (size_t)nt * 8);
+  memcpy(r->trans_best_lp, o.t_best.data(), (size_t)nt * 8);
+  memcpy(r->trans_best_via_off, o.via_off.data(), (size_t)(nt + 1) * 8);
+  if (o.n_via) memcpy(r->trans_best_via, o.via.data(), (size_t)o.n_via * sizeof(hist_cell));
+  // ---- absorb tables and fwdLogProb of the states
+  const size_t b_rows = ((size_t)ns * sizeof(GatherRow) + 255) & ~(size_t)255, b_abs = ((size_t)ns * K * 8 + 255) & ~(size_t)255,
+               b_cell = ((size_t)ns * sizeof(hist_cell) + 255) & ~(size_t)255;
+  char* obuf = nullptr;
+  HB_CUDA(ctx, cudaMallocAsync((void**)&obuf, b_rows + b_abs + b_cell + (size_t)ns * 8, ctx->stream));
+  std::vector<GatherRow> rows(ns);
+  for (int k = 0; k < ns; ++k) rows[k] = {pair->d_dev, o.state_cell[k].xpos, o.state_cell[k].ypos, o.state_cell[k].state == HIST_EEE ? -1 : o.state_cell[k].state};
+  double* d_abs = (double*)(obuf + b_rows);
+  hist_cell* d_cell = (hist_cell*)(obuf + b_rows + b_abs);
+  double* d_fwd = (double*)(obuf + b_rows + b_abs + b_cell);
+  rc = check_cuda(ctx, cudaMemcpyAsync(obuf, rows.data(), (size_t)ns * sizeof(GatherRow), cudaMemcpyHostToDevice, ctx->stream), "H2D rows");
+  if (!rc) rc = check_cuda(ctx, cudaMemcpyAsync(d_cell, o.state_cell.data(), (size_t)ns * sizeof(hist_cell), cudaMemcpyHostToDevice, ctx->stream), "H2D state cells");
+  if (!rc) rc = gather_absorb_rows(ctx, (const GatherRow*)obuf, ns, K, d_abs);
+  if (!rc) {
+    elim_fwd_kernel<<<(ns + 127) / 128, 128, 0, ctx->stream>>>(pair->d_dev, d_cell, ns, pair->lp_end, d_fwd);
+    ctx->launches += 1;
+    rc = check_cuda(ctx, cudaGetLastError(), "elim_fwd_kernel");
   }
+  if (!rc) rc = check_cuda(ctx, cudaMemcpyAsync(r->state_lp_absorb, d_abs, (size_t)ns * K * 8, cudaMemcpyDeviceToHost, ctx->stream), "D2H absorb tables");
+  if (!rc) rc = check_cuda(ctx, cudaMemcpyAsync(r->state_fwd_lp, d_fwd, (size_t)ns * 8, cudaMemcpyDeviceToHost, ctx->stream), "D2H fwd lp");
+  if (!rc) rc = check_cuda(ctx, cudaStreamSynchronize(ctx->stream), "sync");
+  cudaFreeAsync(obuf, ctx->stream);
+  return rc;
 }

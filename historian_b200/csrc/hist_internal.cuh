@@ -214,6 +214,8 @@ struct hist_profile {
   bool empty;                 // Profile::isEmpty
   bool sorted_in;             // every in-list ascending in source state, no repeated (src,dest)
   bool chain = false;         // leaf profile built by the library: transition t is t -> t+1, states 1..n-2 emit
+  int refs = 0;               // pairs currently built on this profile (hist_profile_destroy defers while > 0)
+  bool doomed = false;        // destroy requested while pairs still referred to it
   // device copy of lp_absorb
   double* d_lp_absorb;
   hb_arena* arena;            // owner of d_lp_absorb
@@ -238,9 +240,54 @@ struct hist_pair {
   std::vector<int> start_rows, end_cols, x_slot, y_slot;
 };
 
+#include <functional>
+
 namespace hb {
 int set_err(hist_ctx* ctx, int code, const char* fmt, ...);
 int check_cuda(hist_ctx* ctx, cudaError_t e, const char* what);
+
+// fn(0..n-1) on the library's persistent host worker pool (hist_core.cu); at least `grain` items per thread
+void host_parallel_for(int n, int grain, const std::function<void(int)>& fn);
+// pinned staging buffer `slot` (0/1) of the context, grown on demand (hist_core.cu)
+int ensure_staging_buf(hist_ctx* ctx, size_t bytes, int slot);
+void arena_drop(hist_ctx* ctx, hb_arena* a);
+
+// ---- batched traceback (hist_trace.cu)
+// Best traces from EEE of n filled pairs in ONE launch (one warp per pair).  The paths stay on the device:
+// *d_paths is one allocation (release with cudaFreeAsync on the context's stream) in which pair k's path
+// (start -> end) occupies [path_off[k], path_off[k] + len[k]).
+int trace_best_batch(hist_ctx* ctx, hist_pair* const* pairs, int n, hist_cell** d_paths, std::vector<long long>& path_off,
+                     std::vector<long long>& len);
+// n_traces sampled traces of one pair in one launch; mt_snap (host, [n_traces][625]) receives the generator state
+// after each trace, so the caller can rewind to the state after the traces it actually consumes.
+int trace_sample_snap(hist_pair* pair, const uint32_t* mt_state, int n_traces, std::vector<hist_cell>& paths,
+                      std::vector<long long>& path_off, std::vector<uint32_t>& mt_snap);
+
+// ---- batched makeProfile elimination (hist_elim.cu)
+struct ElimJob {
+  hist_pair* pair;
+  const hist_cell* d_cells;   // sorted cell set on the device, or nullptr ...
+  const hist_cell* h_cells;   // ... then on the host (uploaded by the batch)
+  int n;
+  int strategy;
+};
+struct ElimOut {
+  int n_states = 0, n_trans = 0;
+  long long n_via = 0;
+  std::vector<hist_cell> state_cell;
+  std::vector<int> t_src, t_dst;
+  std::vector<double> t_lp, t_best;
+  std::vector<long long> via_off;
+  std::vector<hist_cell> via;
+};
+int eliminate_batch(hist_ctx* ctx, const std::vector<ElimJob>& jobs, std::vector<ElimOut>& out);
+// One row of a parent profile's lpAbsorb table (forward.cpp:713-727): the absorb vector of cell (x, y, s) of pair P,
+// or a row of -inf when s < 0.
+struct GatherRow {
+  const PairDev* P;
+  int x, y, s;
+};
+int gather_absorb_rows(hist_ctx* ctx, const GatherRow* d_rows, long long n_rows, int K, double* d_out);
 }  // namespace hb
 
 #define HB_CUDA(ctx, call)                                         \

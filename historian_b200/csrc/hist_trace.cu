@@ -28,6 +28,7 @@ struct TraceArgs {
   long long* offs;     // [n_traces + 1]
   int* status;         // 0 ok, 1 capacity, 2 numeric (no finite candidate while sampling), 3 candidate buffer too small
   int cand_cap;
+  uint32_t* mt_snap;   // optional [n_traces][625]: generator state after each sampled trace
 };
 
 struct Mt {
@@ -109,8 +110,10 @@ __device__ int list_dests(const PairDev& P, const DCell& sc, DCell* cand, double
   return n;
 }
 
-__global__ void __launch_bounds__(32) trace_kernel(TraceArgs a) {
+// grid = traces batch: block b walks the trace(s) described by args[b]
+__global__ void __launch_bounds__(32) trace_kernel(const TraceArgs* __restrict__ args) {
   extern __shared__ __align__(16) unsigned char sm_raw[];
+  const TraceArgs a = args[blockIdx.x];
   const PairDev& P = *a.P;
   const int lane = threadIdx.x;
   double* clp = reinterpret_cast<double*>(sm_raw);                 // [cand_cap]
@@ -225,6 +228,8 @@ __global__ void __launch_bounds__(32) trace_kernel(TraceArgs a) {
     off += len;
     if (lane == 0) a.offs[tr + 1] = off;
     __syncwarp();
+    if (a.mode == 1 && a.mt_snap)
+      for (int k = lane; k < 625; k += 32) a.mt_snap[(size_t)tr * 625 + k] = s_mt[k];
   }
   __syncwarp();
   if (a.mode == 1)
@@ -270,7 +275,8 @@ int run_trace(hist_pair* pair, int mode, hist_cell origin, uint32_t* mt_state, i
   char* buf = nullptr;
   const size_t b_paths = (size_t)cap * sizeof(hist_cell), b_offs = (size_t)(n_traces + 1) * sizeof(long long);
   const size_t o_offs = (b_paths + 15) / 16 * 16, o_mt = o_offs + (b_offs + 15) / 16 * 16, o_status = o_mt + 625 * 4 + 12;
-  HB_CUDA(ctx, cudaMallocAsync((void**)&buf, o_status + 16, ctx->stream));
+  const size_t o_args = o_status + 16;
+  HB_CUDA(ctx, cudaMallocAsync((void**)&buf, o_args + sizeof(TraceArgs), ctx->stream));
   TraceArgs a;
   a.P = pair->d_dev;
   a.mode = mode;
@@ -282,8 +288,10 @@ int run_trace(hist_pair* pair, int mode, hist_cell origin, uint32_t* mt_state, i
   a.offs = (long long*)(buf + o_offs);
   a.status = (int*)(buf + o_status);
   a.cand_cap = (int)cand;
+  a.mt_snap = nullptr;
   if (mode == 1) HB_CUDA(ctx, cudaMemcpyAsync(a.mt, mt_state, 625 * 4, cudaMemcpyHostToDevice, ctx->stream));
-  trace_kernel<<<1, 32, smem, ctx->stream>>>(a);
+  HB_CUDA(ctx, cudaMemcpyAsync(buf + o_args, &a, sizeof(TraceArgs), cudaMemcpyHostToDevice, ctx->stream));   // pageable: staged before return
+  trace_kernel<<<1, 32, smem, ctx->stream>>>((const TraceArgs*)(buf + o_args));
   ctx->launches += 1;
   HB_CUDA(ctx, cudaGetLastError());
   std::vector<long long> offs(n_traces + 1);
@@ -307,6 +315,142 @@ int run_trace(hist_pair* pair, int mode, hist_cell origin, uint32_t* mt_state, i
 }
 
 }  // namespace
+
+namespace {
+long long cand_bound(const hist_pair* pair) {
+  const int nx = pair->info.x_size, ny = pair->info.y_size;
+  const int dx = std::max(max_degree(pair->x->t_dst, nx), max_degree(pair->x->t_src, nx));
+  const int dy = std::max(max_degree(pair->y->t_dst, ny), max_degree(pair->y->t_src, ny));
+  return 5ll * dx * dy + 4ll * (dx + dy) + 8;
+}
+}  // namespace
+
+namespace hb {
+
+int trace_best_batch(hist_ctx* ctx, hist_pair* const* pairs, int n, hist_cell** d_paths, std::vector<long long>& path_off,
+                     std::vector<long long>& len) {
+  const char* what = "trace_best_batch";
+  *d_paths = nullptr;
+  if (n <= 0) return HIST_OK;
+  cudaSetDevice(ctx->device);
+  std::vector<long long> cands(n);
+  host_parallel_for(n, 16, [&](int k) { cands[k] = pairs[k]->x->chain && pairs[k]->y->chain ? 21 : cand_bound(pairs[k]); });
+  long long cand = 8;
+  path_off.assign(n + 1, 0);
+  for (int k = 0; k < n; ++k) {
+    hist_pair* pr = pairs[k];
+    if (!pr->fwd_done) return set_err(ctx, HIST_ERR_STATE, "%s: the matrix has not been filled", what);
+    if (!pr->x->sorted_in || !pr->y->sorted_in)
+      return set_err(ctx, HIST_ERR_ARG, "%s: profile transitions must be sorted by (source, destination) without repeats", what);
+    cand = std::max(cand, cands[k]);
+    path_off[k + 1] = path_off[k] + pr->info.x_size + pr->info.y_size + 4;
+  }
+  if (cand * 24 > 200 * 1024) return set_err(ctx, HIST_ERR_CAPACITY, "%s: %lld candidate cells per step exceed the device buffer", what, cand);
+  const size_t smem = (size_t)cand * (sizeof(double) + sizeof(DCell));
+  if (smem > 48 * 1024) HB_CUDA(ctx, cudaFuncSetAttribute(trace_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const size_t b_paths = ((size_t)path_off[n] * sizeof(hist_cell) + 255) & ~(size_t)255;
+  const size_t b_offs = ((size_t)n * 2 * sizeof(long long) + 255) & ~(size_t)255, b_stat = ((size_t)n * sizeof(int) + 255) & ~(size_t)255;
+  char* buf = nullptr;
+  HB_CUDA(ctx, cudaMallocAsync((void**)&buf, b_paths + b_offs + b_stat + (size_t)n * sizeof(TraceArgs), ctx->stream));
+  std::vector<TraceArgs> args(n);
+  for (int k = 0; k < n; ++k) {
+    TraceArgs& a = args[k];
+    a.P = pairs[k]->d_dev;
+    a.mode = 0;
+    a.origin = {pairs[k]->info.x_size - 1, pairs[k]->info.y_size - 1, HIST_EEE};
+    a.n_traces = 1;
+    a.mt = nullptr;
+    a.mt_snap = nullptr;
+    a.paths = (hist_cell*)buf + path_off[k];
+    a.capacity = path_off[k + 1] - path_off[k];
+    a.offs = (long long*)(buf + b_paths) + 2 * k;
+    a.status = (int*)(buf + b_paths + b_offs) + k;
+    a.cand_cap = (int)cand;
+  }
+  TraceArgs* d_args = (TraceArgs*)(buf + b_paths + b_offs + b_stat);
+  int rc = check_cuda(ctx, cudaMemcpyAsync(d_args, args.data(), (size_t)n * sizeof(TraceArgs), cudaMemcpyHostToDevice, ctx->stream), "H2D trace args");
+  if (!rc) {
+    trace_kernel<<<n, 32, smem, ctx->stream>>>(d_args);
+    ctx->launches += 1;
+    rc = check_cuda(ctx, cudaGetLastError(), "trace_kernel");
+  }
+  std::vector<long long> offs((size_t)2 * n);
+  std::vector<int> status(n);
+  if (!rc) rc = check_cuda(ctx, cudaMemcpyAsync(offs.data(), buf + b_paths, offs.size() * sizeof(long long), cudaMemcpyDeviceToHost, ctx->stream), "D2H trace lengths");
+  if (!rc) rc = check_cuda(ctx, cudaMemcpyAsync(status.data(), buf + b_paths + b_offs, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream), "D2H trace status");
+  if (!rc) rc = check_cuda(ctx, cudaStreamSynchronize(ctx->stream), "sync after traces");
+  len.assign(n, 0);
+  for (int k = 0; k < n && !rc; ++k) {
+    if (status[k] == 1) rc = set_err(ctx, HIST_ERR_CAPACITY, "%s: path buffer too small (pair %d)", what, k);
+    else if (status[k] == 2) rc = set_err(ctx, HIST_ERR_NUMERIC, "%s: no finite predecessor (pair %d)", what, k);
+    else if (status[k] == 3) rc = set_err(ctx, HIST_ERR_CAPACITY, "%s: candidate buffer too small (pair %d)", what, k);
+    len[k] = offs[(size_t)2 * k + 1];
+  }
+  if (rc) {
+    cudaFreeAsync(buf, ctx->stream);
+    return rc;
+  }
+  *d_paths = (hist_cell*)buf;
+  return HIST_OK;
+}
+
+int trace_sample_snap(hist_pair* pair, const uint32_t* mt_state, int n_traces, std::vector<hist_cell>& paths,
+                      std::vector<long long>& path_off, std::vector<uint32_t>& mt_snap) {
+  const char* what = "trace_sample_snap";
+  hist_ctx* ctx = pair->ctx;
+  if (!pair->fwd_done) return set_err(ctx, HIST_ERR_STATE, "%s: the matrix has not been filled", what);
+  if (!pair->x->sorted_in || !pair->y->sorted_in)
+    return set_err(ctx, HIST_ERR_ARG, "%s: profile transitions must be sorted by (source, destination) without repeats", what);
+  cudaSetDevice(ctx->device);
+  const long long cand = cand_bound(pair);
+  if (cand * 24 > 200 * 1024) return set_err(ctx, HIST_ERR_CAPACITY, "%s: %lld candidate cells per step exceed the device buffer", what, cand);
+  const size_t smem = (size_t)cand * (sizeof(double) + sizeof(DCell));
+  if (smem > 48 * 1024) HB_CUDA(ctx, cudaFuncSetAttribute(trace_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const long long per = pair->info.x_size + pair->info.y_size + 4, cap = per * n_traces;
+  const size_t b_paths = ((size_t)cap * sizeof(hist_cell) + 255) & ~(size_t)255, b_offs = ((size_t)(n_traces + 1) * 8 + 255) & ~(size_t)255;
+  const size_t b_mt = (625 * 4 + 255) & ~(size_t)255, b_snap = ((size_t)n_traces * 625 * 4 + 255) & ~(size_t)255;
+  char* buf = nullptr;
+  HB_CUDA(ctx, cudaMallocAsync((void**)&buf, b_paths + b_offs + b_mt + b_snap + 256 + sizeof(TraceArgs), ctx->stream));
+  TraceArgs a;
+  a.P = pair->d_dev;
+  a.mode = 1;
+  a.origin = {0, 0, 0};
+  a.n_traces = n_traces;
+  a.paths = (hist_cell*)buf;
+  a.capacity = cap;
+  a.offs = (long long*)(buf + b_paths);
+  a.mt = (uint32_t*)(buf + b_paths + b_offs);
+  a.mt_snap = (uint32_t*)(buf + b_paths + b_offs + b_mt);
+  a.status = (int*)(buf + b_paths + b_offs + b_mt + b_snap);
+  a.cand_cap = (int)cand;
+  TraceArgs* d_args = (TraceArgs*)(buf + b_paths + b_offs + b_mt + b_snap + 256);
+  int rc = check_cuda(ctx, cudaMemcpyAsync(a.mt, mt_state, 625 * 4, cudaMemcpyHostToDevice, ctx->stream), "H2D generator");
+  if (!rc) rc = check_cuda(ctx, cudaMemcpyAsync(d_args, &a, sizeof(TraceArgs), cudaMemcpyHostToDevice, ctx->stream), "H2D trace args");
+  if (!rc) {
+    trace_kernel<<<1, 32, smem, ctx->stream>>>(d_args);
+    ctx->launches += 1;
+    rc = check_cuda(ctx, cudaGetLastError(), "trace_kernel");
+  }
+  path_off.assign(n_traces + 1, 0);
+  mt_snap.assign((size_t)n_traces * 625, 0);
+  int status = 0;
+  if (!rc) rc = check_cuda(ctx, cudaMemcpyAsync(path_off.data(), a.offs, (size_t)(n_traces + 1) * 8, cudaMemcpyDeviceToHost, ctx->stream), "D2H offsets");
+  if (!rc) rc = check_cuda(ctx, cudaMemcpyAsync(mt_snap.data(), a.mt_snap, mt_snap.size() * 4, cudaMemcpyDeviceToHost, ctx->stream), "D2H generator snapshots");
+  if (!rc) rc = check_cuda(ctx, cudaMemcpyAsync(&status, a.status, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream), "D2H status");
+  if (!rc) rc = check_cuda(ctx, cudaStreamSynchronize(ctx->stream), "sync after sampled traces");
+  if (!rc && status == 1) rc = set_err(ctx, HIST_ERR_CAPACITY, "%s: path buffer too small", what);
+  if (!rc && status == 2) rc = set_err(ctx, HIST_ERR_NUMERIC, "%s: no finite predecessor (zero forward likelihood)", what);
+  if (!rc && status == 3) rc = set_err(ctx, HIST_ERR_CAPACITY, "%s: candidate buffer too small", what);
+  if (!rc) {
+    paths.resize((size_t)path_off[n_traces]);
+    if (!paths.empty()) rc = check_cuda(ctx, cudaMemcpyAsync(paths.data(), a.paths, paths.size() * sizeof(hist_cell), cudaMemcpyDeviceToHost, ctx->stream), "D2H paths");
+    if (!rc) rc = check_cuda(ctx, cudaStreamSynchronize(ctx->stream), "sync after paths");
+  }
+  cudaFreeAsync(buf, ctx->stream);
+  return rc;
+}
+
+}  // namespace hb
 
 extern "C" int hist_trace_best(hist_pair* pair, hist_cell end, hist_cell* path, int64_t capacity, int64_t* n) {
   if (!pair || !n) return HIST_ERR_ARG;

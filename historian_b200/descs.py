@@ -70,6 +70,20 @@ class ElimResult(C.Structure):
     ]
 
 
+class MergeDesc(C.Structure):
+    _fields_ = [("node", C.c_int32), ("left", C.c_int32), ("right", C.c_int32),
+                ("closest_left", C.c_int32), ("closest_right", C.c_int32), ("closest", C.c_int32),
+                ("hmm", C.POINTER(PairHmmDesc))]
+
+
+class ReconParams(C.Structure):
+    _fields_ = [("band", C.c_int32), ("strategy", C.c_int32), ("profile_samples", C.c_int32), ("max_profile_states", C.c_int32),
+                ("min_post_prob", C.c_double), ("root_node", C.c_int32), ("mt_state", c_uint32_p)]
+
+
+RECON_STAGES = ["env", "prepare", "fill", "retry", "trace", "select", "elim", "assemble", "gather", "cleanup"]
+
+
 class ModelDesc(C.Structure):
     _fields_ = [
         ("alph_size", C.c_int32), ("components", C.c_int32), ("alphabet", C.c_char_p),

@@ -413,6 +413,87 @@ class Reconstructor:
         return path, lp_final, prof
 
 
+class NativeReconstructor:
+    """Reconstructor::reconstruct on the native, level-batched driver (hist_recon_*, csrc/hist_recon.cu): the same
+    parameters and results as Reconstructor above, but every guide-tree level is ONE library call, the parent
+    profiles stay on the device and the makeProfile bookkeeping runs on the library's host threads.
+
+    Deterministic profiles (best trace only: profile_samples == 0 or max_profile_states == 1) are batched by level;
+    sampled profiles share one mt19937 stream in node order (recon.cpp:38, forward.cpp:257-276), so their merges
+    go through the library one node at a time, in node order."""
+
+    def __init__(self, ctx, model, band=20, profile_samples=10, max_profile_states=0, seed=5489, include_best_trace=True,
+                 keep_gaps_open=False):
+        self.ctx, self.model = ctx, model
+        self.band, self.profile_samples, self.max_profile_states, self.seed = band, profile_samples, max_profile_states, seed
+        self.strategy = (D.COLLAPSE_CHAINS | (D.INCLUDE_BEST_TRACE if include_best_trace else 0)
+                         | (D.KEEP_GAPS_OPEN if keep_gaps_open else 0))
+        self.lp_end = {}
+        self.stage_ms = {}
+        self._hmm_cache = {}
+
+    def draws(self):
+        return self.profile_samples > 0 and not (self.strategy & D.INCLUDE_BEST_TRACE and self.max_profile_states == 1)
+
+    def _hmm(self, tl, tr):
+        from . import model as M
+        key = (float(tl), float(tr))
+        h = self._hmm_cache.get(key)
+        if h is None:
+            hm = M.pair_hmm(self.model, key[0], key[1])
+            h = self._hmm_cache[key] = (hm, hm.desc())
+        return h[1]
+
+    def schedule(self, tree):
+        """Lists of internal nodes that go through the library together."""
+        if self.draws():
+            return [[v] for v in range(tree.n_nodes) if not tree.is_leaf(v)]   # one generator stream, node order
+        return merge_levels(tree)
+
+    def reconstruct(self, tree, seqs, guide=None, rec=None, groups=None, on_group=None):
+        """Same arguments as Reconstructor.reconstruct.  Returns (alignment bool [n_nodes][cols], final Forward
+        log-likelihood, capi.Recon).  `rec`/`groups`: continue on an existing hist_recon with a given schedule;
+        on_group(nodes, rec) is called after every library call (the new parents are still live then)."""
+        from . import capi
+        cl, _ = closest_leaves(tree)
+        if rec is None:
+            rec = capi.Recon(self.ctx, tree.n_nodes, self.model.alphabet, self.model.components)
+            leaves = tree.leaves()
+            if guide is not None:
+                rec.set_guide(leaves, np.array([guide[v] for v in leaves], np.uint8))
+            rec.add_leaves(leaves, [seqs[v] for v in leaves])
+        mt_state = mt19937_seed(self.seed)
+        band = self.band if guide is not None else -1
+        lp_final = -np.inf
+        for nodes in (groups if groups is not None else self.schedule(tree)):
+            merges, hd = [], []
+            for v in nodes:
+                l, r = tree.children[v]
+                merges.append((v, l, r, cl[l], cl[r], cl[v]))
+                hd.append(self._hmm(tree.branch_length[l], tree.branch_length[r]))
+            lp = rec.level(merges, hd, band, self.strategy, self.profile_samples, self.max_profile_states,
+                           tree.root if tree.root in nodes else -1, mt_state)
+            for v, x in zip(nodes, lp):
+                self.lp_end[v] = float(x)
+            if tree.root in nodes:
+                lp_final = self.lp_end[tree.root]
+            if on_group is not None:
+                on_group(nodes, rec)
+        self.stage_ms = rec.stage_ms()
+        return rec.alignment(), lp_final, rec
+
+
+def gapped_rows_dense(bits, tree, seqs, wildcard="*"):
+    """gapped_rows for the dense alignment matrix NativeReconstructor returns."""
+    out = {}
+    for row in range(bits.shape[0]):
+        rp = bits[row]
+        s = seqs[row] if tree.is_leaf(row) else wildcard * int(rp.sum())
+        it = iter(s)
+        out[row] = "".join(next(it) if b else "-" for b in rp)
+    return out
+
+
 def merge_levels(tree):
     """Internal nodes grouped by height above the leaves (level 0 = cherries).  The merges of one level
     depend only on lower levels (recon.cpp:938-1033 is a postorder loop whose only dependencies are

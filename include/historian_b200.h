@@ -15,7 +15,9 @@
  *     caller widens the band (recon.cpp:954-975).
  *   - descriptors (hist_*_desc) are borrowed for the duration of the call only.
  *   - handles (hist_profile, hist_pair, hist_sumprod) are library-owned device
- *     objects, released by the matching _destroy.
+ *     objects, released by the matching _destroy.  A hist_pair keeps its two
+ *     profiles alive: hist_profile_destroy on a profile that pairs still use is
+ *     deferred until the last of those pairs is destroyed.
  *   - a hist_ctx is bound to one device and one stream and is not thread-safe;
  *     multi-GPU = one ctx (one process) per device.
  *   - there is no CPU fallback: hist_ctx_create fails if no CUDA device is usable.
@@ -312,6 +314,60 @@ typedef struct {
 } hist_elim_result;
 int hist_profile_eliminate(hist_pair* pair, const hist_cell* cells, int64_t n_cells, int32_t strategy,
                            hist_elim_result* result);
+
+/* ------------------------------------------------------------------ reconstruction
+ * The node loop of Reconstructor::reconstruct (recon.cpp:917-1052) one guide-tree LEVEL at a time: all sibling
+ * merges whose children are complete are independent iterations of that loop (its only dependencies are
+ * child -> parent).  One hist_recon_level call runs, for every merge of the level: the DPMatrix constructor and
+ * Forward fill with the band-widening retry (recon.cpp:954-975), ForwardMatrix::sampleProfile / bestProfile
+ * (forward.cpp:845-895) -> traces on device, ForwardMatrix::makeProfile (forward.cpp:686-843) -> elimination on
+ * device + state/transition/alignPath/seqCoords bookkeeping on the library's host threads, and
+ * Profile::addReadyStates (profile.cpp:268-319).  The parent profiles stay on the device (their lpAbsorb tables
+ * are gathered from the pairs' leftMultiply results, never copied to the host) and are the inputs of the next
+ * level.  The children of a merge are released once their parent is built.
+ * Sampled profiles draw from ONE std::mt19937 stream in node order in the reference (recon.cpp:38, 1010):
+ * pass the merges of such a run in node order (the draws of merge k+1 start where those of merge k end). */
+typedef struct hist_recon hist_recon;
+
+typedef struct {
+  int32_t node;                      /* row index of the parent (the tree node being built) */
+  int32_t left, right;               /* its children: tree.getChild(node,0/1) */
+  int32_t closest_left, closest_right, closest;  /* Dataset::closestLeaf of left, right and node (recon.cpp:890-911) */
+  const hist_pairhmm_desc* hmm;      /* PairHMM(ProbModel(model,t_left), ProbModel(model,t_right), insProb) (recon.cpp:946-948) */
+} hist_merge_desc;
+
+typedef struct {
+  int32_t band;                      /* maxDistanceFromGuide (-band); < 0 or no guide set: no envelope */
+  int32_t strategy;                  /* ProfilingStrategy bits of the non-root nodes (recon.cpp:925-930); Count* not supported */
+  int32_t profile_samples;           /* -profsamples */
+  int32_t max_profile_states;        /* maxProfileStates() (0 = unlimited) */
+  double min_post_prob;              /* must be <= 0 here: posterior profiles use hist_posterior_cells */
+  int32_t root_node;                 /* the tree's root, or -1: that merge uses bestAlignPath + bestProfile (recon.cpp:1008-1011) */
+  uint32_t* mt_state;                /* [625] std::mt19937 image, advanced by the sampled traces; may be NULL when nothing is sampled */
+} hist_recon_params;
+
+/* wall-clock split of hist_recon_level, accumulated over calls (milliseconds) */
+enum { HIST_RECON_ENV = 0, HIST_RECON_PREPARE, HIST_RECON_FILL, HIST_RECON_RETRY, HIST_RECON_TRACE, HIST_RECON_SELECT,
+       HIST_RECON_ELIM, HIST_RECON_ASSEMBLE, HIST_RECON_GATHER, HIST_RECON_CLEANUP, HIST_RECON_NSTAGES };
+
+int hist_recon_create(hist_ctx* ctx, int32_t n_nodes, const char* alphabet, int32_t components, hist_recon** out);
+void hist_recon_destroy(hist_recon* rec);
+/* Dataset::guide restricted to the leaves: bits[n_rows][n_cols] (non-zero = residue), row_node[r] = tree node of row r. */
+int hist_recon_set_guide(hist_recon* rec, int32_t n_rows, int32_t n_cols, const int32_t* row_node, const uint8_t* bits);
+/* prof[node] = Profile(components, alphabet, seq, node) for the leaves (recon.cpp:940-941), built on device. */
+int hist_recon_add_leaves(hist_recon* rec, int32_t n, const int32_t* nodes, const char* const* residues, const int32_t* lengths);
+int hist_recon_level(hist_recon* rec, int32_t n, const hist_merge_desc* merges, const hist_recon_params* params, double* lp_end);
+/* makeAlignment(path) as a dense 0/1 matrix bits[n_nodes][*n_cols] (forward->bestAlignPath() of the root, recon.cpp:1009,
+ * 1040); HIST_ERR_CAPACITY with *n_cols set when `capacity` (bytes) is too small. */
+int hist_recon_alignment(hist_recon* rec, int32_t* n_cols, uint8_t* bits, int64_t capacity);
+int hist_recon_stage_ms(hist_recon* rec, double* ms /* [HIST_RECON_NSTAGES] */, int reset);
+/* The device profile of a built node that has not been consumed by its parent yet (borrowed; NULL otherwise). */
+hist_profile* hist_recon_profile(hist_recon* rec, int32_t node);
+
+/* Read a device profile back in the hist_profile_desc layout (any pointer may be NULL). */
+int hist_profile_get_sizes(const hist_profile* p, int32_t* n_states, int32_t* n_trans, int32_t* alph_size, int32_t* components);
+int hist_profile_fetch(hist_profile* p, uint8_t* is_emit, int32_t* trans_src, int32_t* trans_dest, double* trans_lp,
+                       double* lp_absorb, int32_t* closest_leaf_pos);
 
 /* ------------------------------------------------------------------ P3
  * Profile::calcSumPathAbsorbProbs (profile.cpp:112-131): 1-D Forward over the profile with the insertion
