@@ -152,14 +152,17 @@ struct FwdPeek : ForwardMatrix {
     putD(pfx + "insy", vector<double>(insy.begin(), insy.end()));
     putD(pfx + "rootsubx", vector<double>(rootsubx.begin(), rootsubx.end()));
     putD(pfx + "rootsuby", vector<double>(rootsuby.begin(), rootsuby.end()));
-    vector<uint8_t> ns(xSize), ne(ySize), env((xSize - 1) * (ySize - 1));
+    vector<uint8_t> ns(xSize), ne(ySize);
     for (size_t i = 0; i < xSize; ++i) ns[i] = xNearStart[i];
     for (size_t j = 0; j < ySize; ++j) ne[j] = yNearEnd[j];
-    for (size_t i = 0; i + 1 < xSize; ++i)
-      for (size_t j = 0; j + 1 < ySize; ++j) env[i * (ySize - 1) + j] = inEnvelope(i, j);
     putB(pfx + "x_near_start", ns);
     putB(pfx + "y_near_end", ne);
-    putB(pfx + "in_envelope", env, {(uint64_t)xSize - 1, (uint64_t)ySize - 1});
+    if (!getenv("REF_DUMP_SPARSE")) {
+      vector<uint8_t> env((xSize - 1) * (ySize - 1));
+      for (size_t i = 0; i + 1 < xSize; ++i)
+        for (size_t j = 0; j + 1 < ySize; ++j) env[i * (ySize - 1) + j] = inEnvelope(i, j);
+      putB(pfx + "in_envelope", env, {(uint64_t)xSize - 1, (uint64_t)ySize - 1});
+    }
   }
 };
 
@@ -171,6 +174,28 @@ static void dumpCells(const string& name, const M& m) {
       for (int s = 0; s < 5; ++s)
         c[(i * (m.ySize - 1) + j) * 5 + s] = m.cell(i, j, (PairHMM::State)s);
   putD(name, c, {(uint64_t)m.xSize - 1, (uint64_t)m.ySize - 1, 5});
+}
+
+// REF_DUMP_SPARSE=<stride>: large matrices.  Instead of the dense cell array, every stride-th in-envelope cell in
+// row-major order (coordinates + five values), plus the per-row in-envelope counts.
+template <class M>
+static void dumpCellsSparse(const string& name, const M& m, int stride) {
+  vector<int32_t> xy, rowCount(m.xSize - 1, 0);
+  vector<double> v;
+  size_t k = 0;
+  for (size_t i = 0; i + 1 < m.xSize; ++i)
+    for (size_t j = 0; j + 1 < m.ySize; ++j)
+      if (m.inEnvelope(i, j)) {
+        ++rowCount[i];
+        if (k++ % stride == 0) {
+          xy.push_back((int32_t)i);
+          xy.push_back((int32_t)j);
+          for (int s = 0; s < 5; ++s) v.push_back(m.cell(i, j, (PairHMM::State)s));
+        }
+      }
+  putI(name + "_xy", xy, {(uint64_t)xy.size() / 2, 2});
+  putD(name + "_vals", v, {(uint64_t)xy.size() / 2, 5});
+  putI(name + "_row_count", rowCount);
 }
 
 static void dumpPath(const string& name, const ForwardMatrix::Path& p) {
@@ -294,9 +319,10 @@ int main(int argc, char** argv) {
       dumpHmm(pfx + "hmm.", hmm);
       dumpEnv(pfx + "env.", env);
       forward->dumpTables(pfx);
-      dumpCells(pfx + "fwd", *forward);
+      const int sparse = getenv("REF_DUMP_SPARSE") ? max(1, atoi(getenv("REF_DUMP_SPARSE"))) : 0;
+      if (sparse) dumpCellsSparse(pfx + "fwd", *forward, sparse); else dumpCells(pfx + "fwd", *forward);
       putD(pfx + "lp_end", {forward->lpEnd});
-      dumpCells(pfx + "bwd", *backward);
+      if (sparse) dumpCellsSparse(pfx + "bwd", *backward, sparse); else dumpCells(pfx + "bwd", *backward);
       putD(pfx + "lp_start", {backward->lpStart()});
       dumpPath(pfx + "best_trace", forward->bestTrace());
       // posterior cells in pop order
