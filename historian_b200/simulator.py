@@ -74,6 +74,56 @@ class Tree:
         blen[-1] = 0.0
         return Tree(parent, blen, names)
 
+    @staticmethod
+    def from_newick(text):
+        """Newick / NHX string -> Tree with the reference's node numbering (knhx.cpp:62-84: leaves are numbered as they
+        are read, internal nodes as their ')' closes, i.e. postorder; NHX comments [...] are skipped)."""
+        parent, blen, names = [], [], []
+        stack, pos, n = [], 0, len(text)
+        last = -1
+
+        def label(p):
+            q = p
+            while q < n and text[q] not in ",():;[":
+                q += 1
+            return text[p:q].strip(), q
+
+        while pos < n:
+            ch = text[pos]
+            if ch == "(":
+                stack.append([])
+                pos += 1
+            elif ch == ",":
+                pos += 1
+            elif ch == ")" or ch not in " \t\r\n;[":
+                if ch == ")":
+                    kids = stack.pop()
+                    name, pos = label(pos + 1)
+                    parent.append(-1); blen.append(0.0); names.append(name)
+                    v = len(parent) - 1
+                    for c in kids:
+                        parent[c] = v
+                else:
+                    name, pos = label(pos)
+                    parent.append(-1); blen.append(0.0); names.append(name)
+                    v = len(parent) - 1
+                if pos < n and text[pos] == ":":
+                    num, pos = label(pos + 1)
+                    blen[v] = float(num)
+                if pos < n and text[pos] == "[":
+                    pos = text.index("]", pos) + 1
+                if stack:
+                    stack[-1].append(v)
+                last = v
+            elif ch == "[":
+                pos = text.index("]", pos) + 1
+            elif ch == ";":
+                break
+            else:
+                pos += 1
+        assert last == len(parent) - 1 and not stack, "malformed Newick string"
+        return Tree(parent, blen, names)
+
     def newick(self):
         def rec(v):
             if self.is_leaf(v):

@@ -255,6 +255,7 @@ int main(int argc, char** argv) {
   putI("profile_samples", {(int32_t)recon.profileSamples});
   putI("max_profile_states", {(int32_t)recon.maxProfileStates()});
   putD("min_post_prob", {recon.minPostProb});
+  putI("root_node", {(int32_t)dataset.tree.root()});
 
   // REF_DUMP_COUNTS=1: also run BackwardMatrix::getCounts (forward.cpp:1183-1214) at the dumped nodes, with the
   // SumProduct attached as recon.cpp:932-934 does.  The profiling strategy above carries no Count* flags, so
@@ -302,7 +303,10 @@ int main(int argc, char** argv) {
     }
     const bool isRoot = node == dataset.tree.root();
     bool want = which == "all";
-    if (!want) {  // comma-separated node list
+    if (which == "auto3") {  // the root and those of its children that are internal nodes
+      const TreeNodeIndex rt = dataset.tree.root();
+      want = isRoot || ((node == dataset.tree.getChild(rt, 0) || node == dataset.tree.getChild(rt, 1)) && !dataset.tree.isLeaf(node));
+    } else if (!want) {  // comma-separated node list
       stringstream ws(which);
       string tok;
       while (getline(ws, tok, ',')) want = want || atoi(tok.c_str()) == node;

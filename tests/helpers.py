@@ -9,8 +9,13 @@ from historian_b200 import descs as D
 GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
 
-def golden_files():
-    return sorted(f for f in glob.glob(os.path.join(GOLDEN_DIR, "*.npz")) if not os.path.basename(f).startswith(("sumprod_", "fbcounts_")))
+# fixtures of large matrices, dumped sparsely (REF_DUMP_SPARSE, oracle/ref_dump.cpp): every stride-th in-envelope cell
+SPARSE = ("gp120_nodes.npz", "lg16x300_n14.npz")
+
+
+def golden_files(sparse=False):
+    return sorted(f for f in glob.glob(os.path.join(GOLDEN_DIR, "*.npz"))
+                  if not os.path.basename(f).startswith(("sumprod_", "fbcounts_")) and (os.path.basename(f) in SPARSE) == sparse)
 
 
 def load_golden(path):
@@ -18,10 +23,10 @@ def load_golden(path):
     return {k: z[k] for k in z.files}
 
 
-def golden_cases():
+def golden_cases(sparse=False):
     """[(id, path, node)] for every dumped node of every fixture."""
     cases = []
-    for f in golden_files():
+    for f in golden_files(sparse):
         z = np.load(f)
         for n in z["dumped_nodes"]:
             cases.append(("%s-n%d" % (os.path.basename(f)[:-4], int(n)), f, int(n)))

@@ -20,7 +20,8 @@ import helpers as H
 from historian_b200 import descs as D, recon as R
 
 pytestmark = pytest.mark.gpu
-CASES = H.golden_cases()
+CASES = H.golden_cases() + H.golden_cases(sparse=True)
+DIVERGED = {}   # fixture -> nodes whose device traces differ from the reference's (table log-sum-exp margin)
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 REF_BIN = os.path.join(ROOT, "oracle", "_ref", "bin", "historian")
 
@@ -45,7 +46,10 @@ def test_parent_profile_matches_reference(ctx, cid, path, node):
     view = R.PairView(hx, hy, node)
     strategy, max_states = int(d["strategy"][0]), int(d["max_profile_states"][0])
     min_post = float(d["min_post_prob"][0])
-    is_root = node == int(max(d["dumped_nodes"])) and ("pf16593" in cid or node == int(d["dumped_nodes"][-1]))
+    if "root_node" in d:
+        is_root = node == int(d["root_node"][0])
+    else:   # round-1 fixtures: the root is the last dumped node
+        is_root = node == int(max(d["dumped_nodes"])) and ("pf16593" in cid or node == int(d["dumped_nodes"][-1]))
     best = pair.trace_best()
     same_traces = H.same(best, d[pfx + "best_trace"])
     if is_root:
@@ -72,7 +76,10 @@ def test_parent_profile_matches_reference(ctx, cid, path, node):
         strat = strategy
     prof, e = R.make_profile(pair, view, cells, strat)
     if not same_traces:
-        pytest.xfail("a trace differs from the reference's (table log-sum-exp margin); profile not comparable")
+        # the reference walks its table-log-sum-exp matrix: a step can differ when two candidates lie within ~1e-4.
+        # The profile is then not comparable; the node is counted and test_trace_divergences_are_rare bounds the count.
+        DIVERGED.setdefault(os.path.basename(path), []).append(node)
+        return
     p = prof.flat
     assert H.same(p.is_emit, d[pfx + "parent.is_emit"]), cid
     assert H.same(p.trans_src, d[pfx + "parent.trans_src"]) and H.same(p.trans_dest, d[pfx + "parent.trans_dest"]), cid
@@ -84,6 +91,12 @@ def test_parent_profile_matches_reference(ctx, cid, path, node):
     ref_leaf = d[pfx + "parent.closest_leaf_pos"]
     if env.max_distance >= 0:  # fixtures dumped with -noband carry no child coordinates
         assert any(H.same(a[1:], ref_leaf[1:]) for a in prof.leaf_rows.values()), cid + ": closest-leaf coordinates"
+
+
+def test_trace_divergences_are_rare():
+    """At most one node per fixture may have been skipped above because a trace left the reference's."""
+    assert all(len(v) <= 1 for v in DIVERGED.values()), DIVERGED
+    assert sum(len(v) for v in DIVERGED.values()) <= 2, DIVERGED
 
 
 def _simulate(tmp, n_leaves, root_len, seed, bl=0.3):
