@@ -81,6 +81,11 @@ def load():
     lib.hist_recon_stage_ms.argtypes = [vp, D.c_double_p, C.c_int]
     lib.hist_recon_profile.argtypes = [vp, C.c_int32]
     lib.hist_recon_profile.restype = vp
+    lib.hist_recon_export_node.argtypes = [vp, C.c_int32, vp, C.c_int64, D.c_int64_p, vp, D.c_int64_p]
+    lib.hist_recon_import_node.argtypes = [vp, C.c_int32, vp, C.c_int64, vp]
+    lib.hist_recon_release_node.argtypes = [vp, C.c_int32]
+    lib.hist_recon_export_stores.argtypes = [vp, vp, C.c_int64, D.c_int64_p]
+    lib.hist_recon_import_stores.argtypes = [vp, vp, C.c_int64]
     lib.hist_profile_get_sizes.argtypes = [vp, D.c_int32_p, D.c_int32_p, D.c_int32_p, D.c_int32_p]
     lib.hist_profile_fetch.argtypes = [vp, D.c_uint8_p, D.c_int32_p, D.c_int32_p, D.c_double_p, D.c_double_p, D.c_int32_p]
     lib.hist_sumprod_create.argtypes = [vp, C.POINTER(D.ModelDesc), C.POINTER(D.TreeDesc), C.POINTER(vp)]
@@ -553,6 +558,43 @@ class Recon:
         if bits.size:
             self.ctx.check(self.ctx.lib.hist_recon_alignment(self.h, C.byref(nc), _p(bits, C.c_uint8), bits.size))
         return bits.astype(bool)
+
+    # ---- exchange between ranks (one hist_recon per GPU)
+    def export_sizes(self, node):
+        """(bytes of the host blob, bytes of the device table) of a live node."""
+        nb, db = C.c_int64(), C.c_int64()
+        rc = self.ctx.lib.hist_recon_export_node(self.h, node, None, 0, C.byref(nb), None, C.byref(db))
+        if rc not in (0, -5):
+            self.ctx.check(rc)
+        return nb.value, db.value
+
+    def export_node(self, node, dev_out_ptr):
+        """Host blob (uint8 array) of `node`; its lpAbsorb table is copied into the device buffer at dev_out_ptr."""
+        nb, db = self.export_sizes(node)
+        blob = np.empty(nb, np.uint8)
+        n2, d2 = C.c_int64(), C.c_int64()
+        self.ctx.check(self.ctx.lib.hist_recon_export_node(self.h, node, blob.ctypes.data, nb, C.byref(n2), C.c_void_p(dev_out_ptr), C.byref(d2)))
+        return blob
+
+    def import_node(self, node, blob, dev_table_ptr):
+        blob = np.ascontiguousarray(blob, np.uint8)
+        self.ctx.check(self.ctx.lib.hist_recon_import_node(self.h, node, blob.ctypes.data, blob.size, C.c_void_p(dev_table_ptr)))
+
+    def release_node(self, node):
+        self.ctx.check(self.ctx.lib.hist_recon_release_node(self.h, node))
+
+    def export_stores(self):
+        nb = C.c_int64()
+        rc = self.ctx.lib.hist_recon_export_stores(self.h, None, 0, C.byref(nb))
+        if rc not in (0, -5):
+            self.ctx.check(rc)
+        blob = np.empty(nb.value, np.uint8)
+        self.ctx.check(self.ctx.lib.hist_recon_export_stores(self.h, blob.ctypes.data, blob.size, C.byref(nb)))
+        return blob
+
+    def import_stores(self, blob):
+        blob = np.ascontiguousarray(blob, np.uint8)
+        self.ctx.check(self.ctx.lib.hist_recon_import_stores(self.h, blob.ctypes.data, blob.size))
 
     def stage_ms(self, reset=False):
         ms = np.zeros(len(D.RECON_STAGES))

@@ -1199,7 +1199,7 @@ int launch_fill_uniform(hist_ctx* ctx, hist_pair* const* pairs, int n, int n_dir
   while (rows > 0 && rows * row > limit) rows >>= 1;
   if (rows < 4) rows = 0;
   const size_t smem = rows * row;
-  if (smem > 48 * 1024 && smem > ctx->fill_smem_configured) {
+  if (smem + 4096 > 48 * 1024 && smem > ctx->fill_smem_configured) {
     HB_CUDA(ctx, cudaFuncSetAttribute(fill_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)limit));
     ctx->fill_smem_configured = limit;
   }
@@ -1218,7 +1218,7 @@ int launch_fill_uniform(hist_ctx* ctx, hist_pair* const* pairs, int n, int n_dir
     int tile_rows = 96;
     while (tile_rows > 8 && (size_t)2 * tile_rows * maxKp * sizeof(float) > 96 * 1024) tile_rows >>= 1;
     const size_t abs_smem = (size_t)2 * tile_rows * maxKp * sizeof(float);
-    if (abs_smem > 48 * 1024 && abs_smem > ctx->absorb_smem_configured) {
+    if (abs_smem + 2048 > 48 * 1024 && abs_smem > ctx->absorb_smem_configured) {   // + the kernel's static shared memory
       HB_CUDA(ctx, cudaFuncSetAttribute(absorb_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
       ctx->absorb_smem_configured = 96 * 1024;
     }
@@ -1248,7 +1248,7 @@ int launch_fill_uniform(hist_ctx* ctx, hist_pair* const* pairs, int n, int n_dir
     const size_t qbytes = (size_t)HB_SDEPTH * hb_sslot(ring_cap) * 16;
     while (srows > 4 && (size_t)per_sm * (srows * row + qbytes + 2048) > 200 * 1024) srows >>= 1;
     const size_t ssmem = srows * row + qbytes;
-    if (ssmem > 48 * 1024) HB_CUDA(ctx, cudaFuncSetAttribute(fill_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+    if (ssmem + 4096 > 48 * 1024) HB_CUDA(ctx, cudaFuncSetAttribute(fill_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
     const int chunk = HB_BUILD_WARPS * HB_BUILD_DIAGS;
     build_records_kernel<<<dim3((maxDiag + chunk - 1) / chunk, n_cta), 32 * HB_BUILD_WARPS, 0, ctx->stream>>>(dptrs, (int4* const*)rec_buf, n_dir,
                                                                                                             only_dir, ring_cap, srows);

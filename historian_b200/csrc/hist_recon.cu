@@ -46,6 +46,7 @@ enum { IT_COL = 0, IT_SEQ0 = 1, IT_SEQ1 = 2 };
 
 struct PathStore {
   int child_node[2] = {-1, -1};
+  bool full = true;             // false: imported with a profile from another rank (state_col / trans_seq only)
   std::vector<ColNode> cols;
   std::vector<SeqNode> seqs;
   std::vector<int> items;
@@ -724,7 +725,195 @@ extern "C" int hist_recon_stage_ms(hist_recon* R, double* ms, int reset) {
   return HIST_OK;
 }
 
-// ------------------------------------------------------------------ profile read-back (tests, exchange between ranks)
+
+// ------------------------------------------------------------------ exchange between ranks (one process per GPU)
+// A profile moves as (host blob, device table): the blob holds the integer structure, the transition weights, the
+// closest-leaf coordinates and the state/transition path ids its parent's assembly needs; the [n][C][A] lpAbsorb table
+// stays in device memory (the caller moves it with ncclSend/Recv or a peer copy and hands the received copy to
+// hist_recon_import_node).  The full path stores (needed only to expand the final alignment) travel separately, once.
+namespace {
+template <class T>
+void put(std::vector<char>& b, const T* v, size_t n) {
+  const char* p = (const char*)v;
+  b.insert(b.end(), p, p + n * sizeof(T));
+}
+template <class T>
+bool get(const char*& p, const char* end, T* v, size_t n) {
+  if ((size_t)(end - p) < n * sizeof(T)) return false;
+  memcpy(v, p, n * sizeof(T));
+  p += n * sizeof(T);
+  return true;
+}
+template <class T>
+void put_vec(std::vector<char>& b, const std::vector<T>& v) {
+  const long long n = (long long)v.size();
+  put(b, &n, 1);
+  put(b, v.data(), v.size());
+}
+template <class T>
+bool get_vec(const char*& p, const char* end, std::vector<T>& v) {
+  long long n = 0;
+  if (!get(p, end, &n, 1) || n < 0 || (size_t)(end - p) < (size_t)n * sizeof(T)) return false;
+  v.resize((size_t)n);
+  return get(p, end, v.data(), (size_t)n);
+}
+int copy_out(hist_ctx* ctx, const std::vector<char>& b, void* buf, int64_t capacity, int64_t* bytes, const char* what) {
+  *bytes = (int64_t)b.size();
+  if (!buf || capacity < *bytes) return set_err(ctx, HIST_ERR_CAPACITY, "%s: need %lld bytes", what, (long long)b.size());
+  memcpy(buf, b.data(), b.size());
+  return HIST_OK;
+}
+}  // namespace
+
+extern "C" int hist_recon_export_node(hist_recon* R, int32_t node, void* host_buf, int64_t capacity, int64_t* bytes, void* dev_out,
+                                      int64_t* dev_bytes) {
+  if (!R || !bytes || node < 0 || node >= R->n_nodes) return HIST_ERR_ARG;
+  const NodeRec& nr = R->node[node];
+  if (!nr.prof || !nr.store) return set_err(R->ctx, HIST_ERR_STATE, "hist_recon_export_node: node %d has no live profile", node);
+  const hist_profile* p = nr.prof;
+  std::vector<char> b;
+  const int hdr[6] = {p->n, p->nt, p->A, p->C, p->leaf_pos.empty() ? 0 : 1, p->chain ? 1 : 0};
+  put(b, hdr, 6);
+  put(b, p->is_emit.data(), p->is_emit.size());
+  put(b, p->t_src.data(), p->t_src.size());
+  put(b, p->t_dst.data(), p->t_dst.size());
+  put(b, p->t_lp.data(), p->t_lp.size());
+  put(b, p->leaf_pos.data(), p->leaf_pos.size());
+  put(b, nr.store->child_node, 2);
+  put(b, nr.store->state_col.data(), nr.store->state_col.size());
+  put(b, nr.store->trans_seq.data(), nr.store->trans_seq.size());
+  const int64_t tb = (int64_t)p->n * p->A * p->C * (int64_t)sizeof(double);
+  if (dev_bytes) *dev_bytes = tb;
+  const int rc = copy_out(R->ctx, b, host_buf, capacity, bytes, "hist_recon_export_node");
+  if (rc || !dev_out) return rc;
+  cudaSetDevice(R->ctx->device);
+  HB_CUDA(R->ctx, cudaMemcpyAsync(dev_out, p->d_lp_absorb, (size_t)tb, cudaMemcpyDeviceToDevice, R->ctx->stream));
+  HB_CUDA(R->ctx, cudaStreamSynchronize(R->ctx->stream));   // the caller sends dev_out on a stream of its own
+  return HIST_OK;
+}
+
+extern "C" int hist_recon_import_node(hist_recon* R, int32_t node, const void* host_buf, int64_t bytes, const void* dev_table) {
+  if (!R || !host_buf || !dev_table || node < 0 || node >= R->n_nodes) return HIST_ERR_ARG;
+  hist_ctx* ctx = R->ctx;
+  NodeRec& nr = R->node[node];
+  if (nr.prof) return set_err(ctx, HIST_ERR_STATE, "hist_recon_import_node: node %d already has a profile", node);
+  const char* q = (const char*)host_buf;
+  const char* end = q + bytes;
+  int hdr[6];
+  if (!get(q, end, hdr, 6) || hdr[0] < 2 || hdr[1] < 0) return set_err(ctx, HIST_ERR_ARG, "hist_recon_import_node: malformed blob");
+  hist_profile* p = new hist_profile();
+  PathStore* st = new PathStore();
+  st->full = false;
+  p->ctx = ctx;
+  p->n = hdr[0]; p->nt = hdr[1]; p->A = hdr[2]; p->C = hdr[3];
+  p->chain = hdr[5] != 0;
+  p->is_emit.resize(p->n);
+  p->t_src.resize(p->nt); p->t_dst.resize(p->nt); p->t_lp.resize(p->nt);
+  if (hdr[4]) p->leaf_pos.resize(p->n);
+  st->state_col.resize(p->n);
+  st->trans_seq.resize(p->nt);
+  bool ok = get(q, end, p->is_emit.data(), p->is_emit.size()) && get(q, end, p->t_src.data(), p->t_src.size()) &&
+            get(q, end, p->t_dst.data(), p->t_dst.size()) && get(q, end, p->t_lp.data(), p->t_lp.size()) &&
+            get(q, end, p->leaf_pos.data(), p->leaf_pos.size()) && get(q, end, st->child_node, 2) &&
+            get(q, end, st->state_col.data(), st->state_col.size()) && get(q, end, st->trans_seq.data(), st->trans_seq.size());
+  for (int t = 0; ok && t < p->nt; ++t) ok = p->t_src[t] >= 0 && p->t_src[t] < p->t_dst[t] && p->t_dst[t] < p->n;
+  if (!ok) {
+    delete p;
+    delete st;
+    return set_err(ctx, HIST_ERR_ARG, "hist_recon_import_node: malformed blob");
+  }
+  p->sorted_in = true;
+  {
+    std::vector<int> last(p->n, -1);
+    for (int t = 0; t < p->nt; ++t) {
+      if (p->t_src[t] <= last[p->t_dst[t]]) p->sorted_in = false;
+      last[p->t_dst[t]] = p->t_src[t];
+    }
+  }
+  p->empty = true;
+  for (int i = 0; i < p->n; ++i)
+    if (p->is_emit[i]) p->empty = false;
+  cudaSetDevice(ctx->device);
+  const size_t tb = (size_t)p->n * p->A * p->C * sizeof(double);
+  p->arena = nullptr;
+  int rc = check_cuda(ctx, cudaMallocAsync((void**)&p->d_lp_absorb, tb, ctx->stream), "cudaMallocAsync(imported profile)");
+  if (!rc) rc = check_cuda(ctx, cudaMemcpyAsync(p->d_lp_absorb, dev_table, tb, cudaMemcpyDeviceToDevice, ctx->stream), "D2D imported table");
+  if (!rc) rc = check_cuda(ctx, cudaStreamSynchronize(ctx->stream), "sync after import");   // the caller's buffer is only borrowed
+  if (rc) {
+    if (p->d_lp_absorb) cudaFreeAsync(p->d_lp_absorb, ctx->stream);
+    delete p;
+    delete st;
+    return rc;
+  }
+  nr.prof = p;
+  if (nr.store && nr.store->full) delete st;   // this rank built the node itself: its complete store stays
+  else {
+    delete nr.store;
+    nr.store = st;
+  }
+  build_in_lists(p, nr.in_off, nr.in_idx);
+  return HIST_OK;
+}
+
+// The profile of `node` has been handed to another rank: free its device table here (its path store stays).
+extern "C" int hist_recon_release_node(hist_recon* R, int32_t node) {
+  if (!R || node < 0 || node >= R->n_nodes) return HIST_ERR_ARG;
+  NodeRec& nr = R->node[node];
+  if (nr.prof) hist_profile_destroy(nr.prof);
+  nr.prof = nullptr;
+  std::vector<int>().swap(nr.in_off);
+  std::vector<int>().swap(nr.in_idx);
+  return HIST_OK;
+}
+
+extern "C" int hist_recon_export_stores(hist_recon* R, void* buf, int64_t capacity, int64_t* bytes) {
+  if (!R || !bytes) return HIST_ERR_ARG;
+  std::vector<char> b;
+  int count = 0;
+  for (auto& nr : R->node)
+    if (nr.store && nr.store->full) ++count;
+  put(b, &count, 1);
+  for (int v = 0; v < R->n_nodes; ++v) {
+    const PathStore* st = R->node[v].store;
+    if (!st || !st->full) continue;
+    put(b, &v, 1);
+    put(b, st->child_node, 2);
+    put_vec(b, st->cols);
+    put_vec(b, st->seqs);
+    put_vec(b, st->items);
+    put_vec(b, st->state_col);
+    put_vec(b, st->trans_seq);
+  }
+  return copy_out(R->ctx, b, buf, capacity, bytes, "hist_recon_export_stores");
+}
+
+extern "C" int hist_recon_import_stores(hist_recon* R, const void* buf, int64_t bytes) {
+  if (!R || !buf) return HIST_ERR_ARG;
+  const char* q = (const char*)buf;
+  const char* end = q + bytes;
+  int count = 0;
+  if (!get(q, end, &count, 1)) return set_err(R->ctx, HIST_ERR_ARG, "hist_recon_import_stores: malformed blob");
+  for (int k = 0; k < count; ++k) {
+    int v = -1;
+    PathStore* st = new PathStore();
+    const bool ok = get(q, end, &v, 1) && v >= 0 && v < R->n_nodes && get(q, end, st->child_node, 2) && get_vec(q, end, st->cols) &&
+                    get_vec(q, end, st->seqs) && get_vec(q, end, st->items) && get_vec(q, end, st->state_col) && get_vec(q, end, st->trans_seq);
+    if (!ok) {
+      delete st;
+      return set_err(R->ctx, HIST_ERR_ARG, "hist_recon_import_stores: malformed blob");
+    }
+    if (R->node[v].store && R->node[v].store->full) {   // this rank built it itself
+      delete st;
+      continue;
+    }
+    delete R->node[v].store;
+    R->node[v].store = st;
+  }
+  R->aln_cols = -1;
+  return HIST_OK;
+}
+
+// ------------------------------------------------------------------ profile read-back (tests)
 extern "C" int hist_profile_get_sizes(const hist_profile* p, int32_t* n_states, int32_t* n_trans, int32_t* alph_size, int32_t* components) {
   if (!p) return HIST_ERR_ARG;
   if (n_states) *n_states = p->n;

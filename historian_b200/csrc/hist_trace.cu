@@ -270,7 +270,7 @@ int run_trace(hist_pair* pair, int mode, hist_cell origin, uint32_t* mt_state, i
   long long cand = 5ll * dx * dy + 4ll * (dx + dy) + 8;
   if (cand * 24 > 200 * 1024) return set_err(ctx, HIST_ERR_CAPACITY, "%s: %lld candidate cells per step exceed the device buffer", what, cand);
   const size_t smem = (size_t)cand * (sizeof(double) + sizeof(DCell));
-  if (smem > 48 * 1024) HB_CUDA(ctx, cudaFuncSetAttribute(trace_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  if (smem + 4096 > 48 * 1024) HB_CUDA(ctx, cudaFuncSetAttribute(trace_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int64_t cap = std::max<int64_t>(capacity, 1);
   char* buf = nullptr;
   const size_t b_paths = (size_t)cap * sizeof(hist_cell), b_offs = (size_t)(n_traces + 1) * sizeof(long long);
@@ -347,7 +347,7 @@ int trace_best_batch(hist_ctx* ctx, hist_pair* const* pairs, int n, hist_cell** 
   }
   if (cand * 24 > 200 * 1024) return set_err(ctx, HIST_ERR_CAPACITY, "%s: %lld candidate cells per step exceed the device buffer", what, cand);
   const size_t smem = (size_t)cand * (sizeof(double) + sizeof(DCell));
-  if (smem > 48 * 1024) HB_CUDA(ctx, cudaFuncSetAttribute(trace_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  if (smem + 4096 > 48 * 1024) HB_CUDA(ctx, cudaFuncSetAttribute(trace_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const size_t b_paths = ((size_t)path_off[n] * sizeof(hist_cell) + 255) & ~(size_t)255;
   const size_t b_offs = ((size_t)n * 2 * sizeof(long long) + 255) & ~(size_t)255, b_stat = ((size_t)n * sizeof(int) + 255) & ~(size_t)255;
   char* buf = nullptr;
@@ -405,7 +405,7 @@ int trace_sample_snap(hist_pair* pair, const uint32_t* mt_state, int n_traces, s
   const long long cand = cand_bound(pair);
   if (cand * 24 > 200 * 1024) return set_err(ctx, HIST_ERR_CAPACITY, "%s: %lld candidate cells per step exceed the device buffer", what, cand);
   const size_t smem = (size_t)cand * (sizeof(double) + sizeof(DCell));
-  if (smem > 48 * 1024) HB_CUDA(ctx, cudaFuncSetAttribute(trace_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  if (smem + 4096 > 48 * 1024) HB_CUDA(ctx, cudaFuncSetAttribute(trace_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const long long per = pair->info.x_size + pair->info.y_size + 4, cap = per * n_traces;
   const size_t b_paths = ((size_t)cap * sizeof(hist_cell) + 255) & ~(size_t)255, b_offs = ((size_t)(n_traces + 1) * 8 + 255) & ~(size_t)255;
   const size_t b_mt = (625 * 4 + 255) & ~(size_t)255, b_snap = ((size_t)n_traces * 625 * 4 + 255) & ~(size_t)255;

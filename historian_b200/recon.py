@@ -483,6 +483,120 @@ class NativeReconstructor:
         return rec.alignment(), lp_final, rec
 
 
+# ------------------------------------------------------------------ sibling merges over several GPUs
+def plan_owners(tree, world):
+    """Placement of the progressive reconstruction on `world` ranks (one process per GPU): the leaves are dealt out in
+    contiguous blocks of the tree's leaf order, and an internal node is built where its larger child (by leaf count;
+    ties: the left one) lives, so whole subtrees stay on one rank and only the smaller child's flattened profile moves
+    (SURVEY.md 8(e)).  Returns owner[node]."""
+    n = tree.n_nodes
+    leaves = tree.leaves()
+    owner = np.zeros(n, np.int64)
+    size = np.zeros(n, np.int64)
+    for k, v in enumerate(leaves):
+        owner[v] = k * world // len(leaves)
+        size[v] = 1
+    for v in range(n):
+        kids = tree.children[v]
+        if kids:
+            size[v] = sum(size[c] for c in kids)
+            owner[v] = owner[max(kids, key=lambda c: (size[c], -kids.index(c)))]
+    return owner
+
+
+def level_moves(tree, nodes, owner):
+    """Profiles that must change rank before the merges `nodes` can run: [(child node, from rank, to rank)]."""
+    return [(c, int(owner[c]), int(owner[v])) for v in nodes for c in tree.children[v] if owner[c] != owner[v]]
+
+
+def exchange_profiles(rec, moves, rank, dist, device):
+    """Moves finished profiles between ranks with point-to-point transfers (torch.distributed send/recv: NCCL over NVLink
+    for CUDA tensors).  A profile travels as a header (two sizes), the host blob and the lpAbsorb table; the table goes
+    device to device.  Every rank walks the same list, so sends and receives pair up in order."""
+    import torch
+    for node, src, dst in moves:
+        if rank == src:
+            nb, db = rec.export_sizes(node)
+            table = torch.empty(db, dtype=torch.uint8, device=device)
+            blob = rec.export_node(node, table.data_ptr())
+            dist.send(torch.tensor([nb, db], dtype=torch.int64, device=device), dst)
+            dist.send(torch.from_numpy(blob).to(device), dst)
+            dist.send(table, dst)
+            rec.release_node(node)
+        elif rank == dst:
+            hdr = torch.zeros(2, dtype=torch.int64, device=device)
+            dist.recv(hdr, src)
+            nb, db = (int(v) for v in hdr.tolist())
+            blob = torch.empty(nb, dtype=torch.uint8, device=device)
+            table = torch.empty(db, dtype=torch.uint8, device=device)
+            dist.recv(blob, src)
+            dist.recv(table, src)
+            if table.is_cuda:
+                torch.cuda.synchronize()
+            rec.import_node(node, blob.cpu().numpy(), table.data_ptr())
+
+
+def gather_stores(rec, to_rank, rank, world, dist, device):
+    """The alignment-path stores of every rank, sent once to the rank that expands the final alignment."""
+    import torch
+    if rank != to_rank:
+        blob = rec.export_stores()
+        dist.send(torch.tensor([blob.size], dtype=torch.int64, device=device), to_rank)
+        dist.send(torch.from_numpy(blob).to(device), to_rank)
+        return
+    for src in range(world):
+        if src == to_rank:
+            continue
+        hdr = torch.zeros(1, dtype=torch.int64, device=device)
+        dist.recv(hdr, src)
+        blob = torch.empty(int(hdr.item()), dtype=torch.uint8, device=device)
+        dist.recv(blob, src)
+        rec.import_stores(blob.cpu().numpy())
+
+
+def reconstruct_partitioned(nat, tree, seqs, guide, rank, world, dist, device):
+    """NativeReconstructor.reconstruct with the sibling merges of every guide-tree level spread over `world` ranks
+    (plan_owners).  Only RNG-free profiles (deterministic mode) can be spread: sampled profiles share one mt19937 stream
+    in node order.  Returns (alignment or None, final log-likelihood or None, capi.Recon); the alignment and the
+    likelihood are returned on the rank that owns the root."""
+    from . import capi
+    if nat.draws() and world > 1:
+        raise ValueError("sampled profiles share one RNG stream in node order; use max_profile_states=1 or profile_samples=0 for multi-GPU runs")
+    owner = plan_owners(tree, world)
+    cl, _ = closest_leaves(tree)
+    rec = capi.Recon(nat.ctx, tree.n_nodes, nat.model.alphabet, nat.model.components)
+    leaves = tree.leaves()
+    if guide is not None:
+        rec.set_guide(leaves, np.array([guide[v] for v in leaves], np.uint8))
+    mine = [v for v in leaves if owner[v] == rank]
+    if mine:
+        rec.add_leaves(mine, [seqs[v] for v in mine])
+    band = nat.band if guide is not None else -1
+    mt_state = mt19937_seed(nat.seed)
+    lp_final = None
+    for nodes in merge_levels(tree):
+        exchange_profiles(rec, level_moves(tree, nodes, owner), rank, dist, device)
+        todo = [v for v in nodes if owner[v] == rank]
+        if not todo:
+            continue
+        merges, hd = [], []
+        for v in todo:
+            l, r = tree.children[v]
+            merges.append((v, l, r, cl[l], cl[r], cl[v]))
+            hd.append(nat._hmm(tree.branch_length[l], tree.branch_length[r]))
+        lp = rec.level(merges, hd, band, nat.strategy, nat.profile_samples, nat.max_profile_states,
+                       tree.root if tree.root in todo else -1, mt_state)
+        for v, x in zip(todo, lp):
+            nat.lp_end[v] = float(x)
+        if tree.root in todo:
+            lp_final = nat.lp_end[tree.root]
+    root_rank = int(owner[tree.root])
+    if world > 1:
+        gather_stores(rec, root_rank, rank, world, dist, device)
+    nat.stage_ms = rec.stage_ms()
+    return (rec.alignment() if rank == root_rank else None), lp_final, rec
+
+
 def gapped_rows_dense(bits, tree, seqs, wildcard="*"):
     """gapped_rows for the dense alignment matrix NativeReconstructor returns."""
     out = {}

@@ -364,6 +364,20 @@ int hist_recon_stage_ms(hist_recon* rec, double* ms /* [HIST_RECON_NSTAGES] */, 
 /* The device profile of a built node that has not been consumed by its parent yet (borrowed; NULL otherwise). */
 hist_profile* hist_recon_profile(hist_recon* rec, int32_t node);
 
+/* Sibling merges over several GPUs (one process and one hist_recon per GPU): a finished profile moves to the rank
+ * that builds its parent as a host blob (integer structure, transition weights, coordinates, path ids) plus its
+ * [n][C][A] lpAbsorb table, which stays in DEVICE memory on both sides: export copies it device-to-device into the
+ * caller's device buffer dev_out (*dev_bytes long; call with host_buf == NULL first to learn both sizes), the caller
+ * moves those bytes (ncclSend/Recv or a peer copy) and passes the received device buffer to import, which copies it
+ * device-to-device again.  release drops the sender's copy.  The alignment-path stores that hist_recon_alignment expands
+ * are gathered once, at the end, with export_stores / import_stores (host blobs). */
+int hist_recon_export_node(hist_recon* rec, int32_t node, void* host_buf, int64_t capacity, int64_t* bytes,
+                           void* dev_out, int64_t* dev_bytes);
+int hist_recon_import_node(hist_recon* rec, int32_t node, const void* host_buf, int64_t bytes, const void* dev_table);
+int hist_recon_release_node(hist_recon* rec, int32_t node);
+int hist_recon_export_stores(hist_recon* rec, void* buf, int64_t capacity, int64_t* bytes);
+int hist_recon_import_stores(hist_recon* rec, const void* buf, int64_t bytes);
+
 /* Read a device profile back in the hist_profile_desc layout (any pointer may be NULL). */
 int hist_profile_get_sizes(const hist_profile* p, int32_t* n_states, int32_t* n_trans, int32_t* alph_size, int32_t* components);
 int hist_profile_fetch(hist_profile* p, uint8_t* is_emit, int32_t* trans_src, int32_t* trans_dest, double* trans_lp,

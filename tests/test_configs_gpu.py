@@ -2,8 +2,8 @@
 run at test time on the same box) -- both drivers (per-merge Python driver and the native level-batched one):
 
   config 1  data/gp120.fa (10 HIV/SIV GP120 sequences, ~500 aa) with its guide alignment and tree
-  config 2  data/PF16593.fa (43 sequences x 32-36 aa) with data/PF16593.nhx and the guide the reference itself
-            computes (saved once with -saveguide by tools/make_golden_r2.py; the guide aligner is outside the hot path)
+  config 2  data/PF16593.fa (43 sequences x 32-36 aa) with data/PF16593.nhx and the reference's own guide alignment of
+            it (data/PF16593.guide.fa; the guide aligner is outside the hot path)
 
 in deterministic mode (-profmaxstates 1) and in the DEFAULT sampling mode (-profsamples 10, seed 5489, one mt19937
 stream in node order), with -profmaxstates fixed (the reference derives it from host RAM otherwise).  The reconstructed
@@ -25,7 +25,7 @@ pytestmark = pytest.mark.gpu
 G = H.GOLDEN_DIR
 CONFIGS = {
     "gp120": (os.path.join(G, "gp120", "gp120.guide.fa"), os.path.join(G, "gp120", "gp120.tree.nh")),
-    "pf16593": (os.path.join(G, "pf16593", "PF16593.refguide.fa"), os.path.join(G, "pf16593", "PF16593.nhx")),
+    "pf16593": (os.path.join(G, "pf16593", "PF16593.guide.fa"), os.path.join(G, "pf16593", "PF16593.nhx")),
 }
 
 
@@ -46,11 +46,46 @@ def _reference(gf, tf, extra):
     return _read_fasta(out)
 
 
-def _check(ref_rows, ours, tree, what):
+def _diff_rows(ref_rows, ours, tree):
     assert len(ref_rows) == tree.n_nodes
-    diff = [k for k, (name, row) in enumerate(ref_rows) if not (ours[k] == row or ours[k].lower() == row.lower())]
+    return [k for k, (name, row) in enumerate(ref_rows) if not (ours[k] == row or ours[k].lower() == row.lower())]
+
+
+def _check(ref_rows, ours, tree, what):
+    diff = _diff_rows(ref_rows, ours, tree)
     assert not diff, "%s: %d of %d rows differ from the reference's (first: node %d)\n%s\n%s" % (
         what, len(diff), tree.n_nodes, diff[0], ours[diff[0]], ref_rows[diff[0]][1])
+
+
+def _root_margin_explains(ctx, lg, tree, grows, kids, band):
+    """The root row alone differs: show that the reference's own table log-sum-exp is what separates the two best
+    traces.  With the two child profiles of the root (read back from the device), the CPU oracle -- bit-identical to
+    the reference with the table, exact otherwise -- must give the device's root trace under exact arithmetic and a
+    different one under the table (north_star: alignments identical wherever the best-path margin exceeds the
+    tolerance)."""
+    import oracle_lib as O
+    from historian_b200 import descs as D
+    l, r = tree.children[tree.root]
+    cl, _ = R.closest_leaves(tree)
+    x, y = kids[l], kids[r]
+    hmm = M.pair_hmm(lg, float(tree.branch_length[l]), float(tree.branch_length[r]))
+    env = D.Envelope.from_guide_rows(grows[int(cl[l])], grows[int(cl[r])], band)
+    dx, dy = ctx.upload(x), ctx.upload(y)
+    pair = ctx.prepare(dx, dy, hmm, env)
+    pair.forward()
+    ours = pair.trace_best()
+    end = (x.n_states - 1, y.n_states - 1, D.EEE)
+    tfwd, _ = O.forward(x, y, hmm, env)
+    t_table = O.trace_best(x, y, hmm, env, np.ascontiguousarray(tfwd), end)
+    O.set_exact_lse(True)
+    try:
+        efwd, _ = O.forward(x, y, hmm, env)
+        t_exact = O.trace_best(x, y, hmm, env, np.ascontiguousarray(efwd), end)
+    finally:
+        O.set_exact_lse(False)
+    same_exact = H.same(ours, t_exact)
+    n_diff = len(set(map(tuple, ours.tolist())) ^ set(map(tuple, t_table.tolist())))
+    return same_exact and not H.same(t_table, t_exact), n_diff
 
 
 @pytest.mark.parametrize("name,max_states,samples", [("gp120", 1, 10), ("gp120", 1500, 10), ("pf16593", 1, 10), ("pf16593", 300, 10), ("pf16593", 0, 3)])
@@ -61,11 +96,24 @@ def test_whole_tree_matches_reference_binary(ctx, name, max_states, samples):
     ref_rows = _reference(gf, tf, ["-profmaxstates", str(max_states), "-profsamples", str(samples)])
     lg = M.RateModel.preset("lg")   # the reference's default amino-acid model (recon.cpp:671-680)
     nat = R.NativeReconstructor(ctx, lg, band=20, profile_samples=samples, max_profile_states=max_states)
-    bits, lp_nat, rec = nat.reconstruct(tree, seqs, grows)
-    _check(ref_rows, R.gapped_rows_dense(bits, tree, seqs, wildcard="x"), tree, name + " native")
+    kids = {}
+
+    def on_group(nodes, rec):   # keep the root's children: they are consumed by the root merge
+        for v in nodes:
+            if v in tree.children[tree.root]:
+                kids[v] = rec.profile(v)
+
+    bits, lp_nat, rec = nat.reconstruct(tree, seqs, grows, on_group=on_group)
+    ours = R.gapped_rows_dense(bits, tree, seqs, wildcard="x")
+    diff = _diff_rows(ref_rows, ours, tree)
+    if diff == [tree.root] and len(kids) == 2:
+        ok, n_cells = _root_margin_explains(ctx, lg, tree, grows, kids, 20)
+        assert ok and n_cells <= 8, "%s: the root row differs and the table log-sum-exp margin does not explain it (%d cells)" % (name, n_cells)
+    else:
+        _check(ref_rows, ours, tree, name + " native")
     rec.close()
     if name == "pf16593" or max_states == 1:   # the per-merge driver too (slow on the large sampled profiles of gp120)
         py = R.Reconstructor(ctx, lg, band=20, profile_samples=samples, max_profile_states=max_states)
         path, lp_py, _ = py.reconstruct(tree, seqs, grows)
-        _check(ref_rows, R.gapped_rows(path, tree, seqs, wildcard="x"), tree, name + " python")
+        assert _diff_rows(ref_rows, R.gapped_rows(path, tree, seqs, wildcard="x"), tree) == diff, name + ": the two drivers disagree"
         assert lp_py == lp_nat
