@@ -165,47 +165,75 @@ __device__ int pool_entry(const ElimDev& E, int& pool_n, int s, int k) {
   return e;
 }
 
+__device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+
 // forward.cpp:751-807, then the transition list of forward.cpp:810-831.  `retained` holds state indices
 // (exclusive scan) with retained[n] = number of states; is_ret = retained[c+1] != retained[c].
-// One thread per job.
-__global__ void elim_reduce_kernel(const ElimDev* __restrict__ jobs) {
-  if (threadIdx.x != 0) return;
+// One warp per job: the elimination itself is a dependent chain over the cells (lane 0 walks it), and what it
+// costs is the latency of its loads; the other lanes run ahead of it and pull the next ELIM_CHUNK cells' records
+// (cells, edge lists, list heads) into L1, so that the chain sees L1 hits instead of L2 round trips.
+#define ELIM_CHUNK 128
+__global__ void __launch_bounds__(32) elim_reduce_kernel(const ElimDev* __restrict__ jobs) {
   const ElimDev E = jobs[blockIdx.x];
   const PairDev& P = *E.P;
+  const int lane = threadIdx.x;
   int pool_n = 0;
   bool overflow = false;
-  for (int c = E.n - 1; c >= 0 && !overflow; --c) {
-    const DCell d = E.cells[c];
-    // eliminatedLogProbInsert (forward.cpp:503-526)
-    double ins = 0;
-    if (d.s == HIST_IIW && (P.x.flags[d.x] & F_EMIT)) ins = P.x.insl[d.x];
-    else if (d.s == HIST_IMI && (P.y.flags[d.y] & F_EMIT)) ins = P.y.insl[d.y];
-    const bool is_ret = E.retained[c + 1] != E.retained[c];
-    for (int q = E.in_cnt[c]; q < E.in_cnt[c + 1] && !overflow; ++q) {
-      const int s = E.e_src[q];
-      const double lp = E.e_lp[q] + ins;
-      if (is_ret) {
-        const int e = pool_entry(E, pool_n, s, E.retained[c]);
-        if (e < 0) { overflow = true; break; }
-        E.p_path[e] = lp;
-        E.p_best[e] = lp;
-        E.p_via_cell[e] = -1;
-        E.p_via_next[e] = -1;
-      } else {
-        for (int ce = E.head[c]; ce >= 0; ce = E.p_next[ce]) {
-          const int e = pool_entry(E, pool_n, s, E.p_k[ce]);
-          if (e < 0) { overflow = true; break; }
-          E.p_path[e] = lse2(E.p_path[e], lp + E.p_path[ce]);
-          const double best = lp + E.p_best[ce];
-          if (best > E.p_best[e]) {
-            E.p_best[e] = best;
-            E.p_via_cell[e] = c;
-            E.p_via_next[e] = ce;
+  for (int hi = E.n - 1; hi >= 0; hi -= ELIM_CHUNK) {
+    const int lo = max(hi - ELIM_CHUNK + 1, 0);
+    {
+      // one 128-B line holds 10 cells / 32 ints / 16 doubles
+      const int nxt_hi = lo - 1, nxt_lo = max(lo - ELIM_CHUNK, 0);
+      const int first = hi == E.n - 1 ? lo : nxt_lo, last = hi == E.n - 1 ? hi : nxt_hi;   // the first round also covers its own chunk
+      if (last >= first) {
+        for (int c = first + lane * 8; c <= last; c += 32 * 8) prefetch_l1(E.cells + c);
+        for (int c = first + lane * 32; c <= last + 1; c += 32 * 32) {
+          prefetch_l1(E.in_cnt + c);
+          prefetch_l1(E.retained + c);
+          prefetch_l1(E.head + min(c, E.n - 1));
+        }
+        const int q0 = E.in_cnt[first], q1 = E.in_cnt[last + 1];
+        for (int q = q0 + lane * 16; q < q1; q += 32 * 16) prefetch_l1(E.e_lp + q);
+        for (int q = q0 + lane * 32; q < q1; q += 32 * 32) prefetch_l1(E.e_src + q);
+      }
+    }
+    __syncwarp();
+    if (lane == 0)
+      for (int c = hi; c >= lo && !overflow; --c) {
+        const DCell d = E.cells[c];
+        // eliminatedLogProbInsert (forward.cpp:503-526)
+        double ins = 0;
+        if (d.s == HIST_IIW) { if (P.x.flags[d.x] & F_EMIT) ins = P.x.insl[d.x]; }
+        else if (d.s == HIST_IMI) { if (P.y.flags[d.y] & F_EMIT) ins = P.y.insl[d.y]; }
+        const bool is_ret = E.retained[c + 1] != E.retained[c];
+        for (int q = E.in_cnt[c]; q < E.in_cnt[c + 1] && !overflow; ++q) {
+          const int s = E.e_src[q];
+          const double lp = E.e_lp[q] + ins;
+          if (is_ret) {
+            const int e = pool_entry(E, pool_n, s, E.retained[c]);
+            if (e < 0) { overflow = true; break; }
+            E.p_path[e] = lp;
+            E.p_best[e] = lp;
+            E.p_via_cell[e] = -1;
+            E.p_via_next[e] = -1;
+          } else {
+            for (int ce = E.head[c]; ce >= 0; ce = E.p_next[ce]) {
+              const int e = pool_entry(E, pool_n, s, E.p_k[ce]);
+              if (e < 0) { overflow = true; break; }
+              E.p_path[e] = lse2(E.p_path[e], lp + E.p_path[ce]);
+              const double best = lp + E.p_best[ce];
+              if (best > E.p_best[e]) {
+                E.p_best[e] = best;
+                E.p_via_cell[e] = c;
+                E.p_via_next[e] = ce;
+              }
+            }
           }
         }
       }
-    }
+    __syncwarp();
   }
+  if (lane != 0) return;
   // transitions of the retained cells, ascending destination state, and their via-path lengths
   int nt = 0;
   long long nv = 0;
@@ -301,23 +329,28 @@ int gather_absorb_rows(hist_ctx* ctx, const GatherRow* d_rows, long long n_rows,
 
 namespace {
 struct JobLayout {
-  size_t cells, in, out, ret, head, pk, pn, pvc, pvn, pp, pb, cnt, nv, ts, td, te, tl, tb, tv, end;
+  size_t cells, in, out, ret, head, small_end;                    // small per-cell arrays (zeroed by ONE memset for all jobs)
+  size_t pk, pn, pvc, pvn, pp, pb, ts, td, te, tl, tb, tv, end;   // effective-transition pool and transition lists
   long long pool_cap;
 };
 
-JobLayout layout_job(size_t base, int n, long long pool_cap, bool own_cells) {
-  JobLayout L;
+void layout_small(JobLayout& L, size_t base, int n, bool own_cells) {
+  size_t off = base;
+  auto take = [&](size_t bytes) { off = (off + 15) / 16 * 16; const size_t o = off; off += bytes; return o; };
+  L.cells = take(own_cells ? (size_t)n * sizeof(DCell) : 0);
+  L.in = take((size_t)(n + 1) * 4); L.out = take((size_t)n * 4); L.ret = take((size_t)(n + 1) * 4); L.head = take((size_t)n * 4);
+  L.small_end = (off + 255) & ~(size_t)255;
+}
+
+void layout_pool(JobLayout& L, size_t base, long long pool_cap) {
   size_t off = base;
   auto take = [&](size_t bytes) { off = (off + 15) / 16 * 16; const size_t o = off; off += bytes; return o; };
   L.pool_cap = pool_cap;
-  L.cells = take(own_cells ? (size_t)n * sizeof(DCell) : 0);
-  L.in = take((size_t)(n + 1) * 4); L.out = take((size_t)n * 4); L.ret = take((size_t)(n + 1) * 4); L.head = take((size_t)n * 4);
   L.pk = take((size_t)pool_cap * 4); L.pn = take((size_t)pool_cap * 4); L.pvc = take((size_t)pool_cap * 4); L.pvn = take((size_t)pool_cap * 4);
-  L.pp = take((size_t)pool_cap * 8); L.pb = take((size_t)pool_cap * 8); L.cnt = take(16); L.nv = take(8);
+  L.pp = take((size_t)pool_cap * 8); L.pb = take((size_t)pool_cap * 8);
   L.ts = take((size_t)pool_cap * 4); L.td = take((size_t)pool_cap * 4); L.te = take((size_t)pool_cap * 4);
   L.tl = take((size_t)pool_cap * 8); L.tb = take((size_t)pool_cap * 8); L.tv = take((size_t)(pool_cap + 1) * 8);
   L.end = (off + 255) & ~(size_t)255;
-  return L;
 }
 
 // One attempt over a set of jobs with the given pool capacities; overflowed[k] is set for jobs whose pool ran out.
@@ -329,12 +362,22 @@ int eliminate_attempt(hist_ctx* ctx, const std::vector<ElimJob>& jobs, const std
   size_t total = ((size_t)nj * sizeof(ElimDev) + 255) & ~(size_t)255;
   const size_t tot_off = total;
   total += ((size_t)nj * sizeof(int) + 255) & ~(size_t)255;
+  const size_t cnt_off = total;   // counts [nj][4] and via counts [nj] of all jobs, contiguous: one read-back
+  total += ((size_t)nj * 16 + 255) & ~(size_t)255;
+  const size_t nv_off = total;
+  total += ((size_t)nj * 8 + 255) & ~(size_t)255;
   int max_n = 1;
+  const size_t small_off = total;
   for (int q = 0; q < nj; ++q) {
     const ElimJob& J = jobs[which[q]];
-    L[q] = layout_job(total, J.n, pool_cap[q], J.d_cells == nullptr);
-    total = L[q].end;
+    layout_small(L[q], total, J.n, J.d_cells == nullptr);
+    total = L[q].small_end;
     max_n = std::max(max_n, J.n);
+  }
+  const size_t small_end = total;
+  for (int q = 0; q < nj; ++q) {
+    layout_pool(L[q], total, pool_cap[q]);
+    total = L[q].end;
   }
   char* buf = nullptr;
   HB_CUDA(ctx, cudaMallocAsync((void**)&buf, total, ctx->stream));
@@ -346,7 +389,7 @@ int eliminate_attempt(hist_ctx* ctx, const std::vector<ElimJob>& jobs, const std
     cudaFreeAsync(buf, ctx->stream);
   };
   std::vector<ElimDev> E(nj);
-  int rc = HIST_OK;
+  int rc = check_cuda(ctx, cudaMemsetAsync(buf + small_off, 0, small_end - small_off, ctx->stream), "memset counts");
   for (int q = 0; q < nj && !rc; ++q) {
     const ElimJob& J = jobs[which[q]];
     const JobLayout& l = L[q];
@@ -364,10 +407,9 @@ int eliminate_attempt(hist_ctx* ctx, const std::vector<ElimJob>& jobs, const std
     e.pool_cap = (int)l.pool_cap;
     e.p_k = (int*)(buf + l.pk); e.p_next = (int*)(buf + l.pn); e.p_via_cell = (int*)(buf + l.pvc); e.p_via_next = (int*)(buf + l.pvn);
     e.p_path = (double*)(buf + l.pp); e.p_best = (double*)(buf + l.pb);
-    e.counts = (int*)(buf + l.cnt); e.n_via = (long long*)(buf + l.nv);
+    e.counts = (int*)(buf + cnt_off) + 4 * q; e.n_via = (long long*)(buf + nv_off) + q;
     e.t_src = (int*)(buf + l.ts); e.t_dst = (int*)(buf + l.td); e.t_entry = (int*)(buf + l.te);
     e.t_lp = (double*)(buf + l.tl); e.t_best = (double*)(buf + l.tb); e.t_via_off = (long long*)(buf + l.tv);
-    if (!rc) rc = check_cuda(ctx, cudaMemsetAsync(buf + l.in, 0, l.head - l.in, ctx->stream), "memset counts");
   }
   if (rc) { cleanup(); return rc; }
   ElimDev* d_jobs = (ElimDev*)buf;
@@ -407,10 +449,8 @@ int eliminate_attempt(hist_ctx* ctx, const std::vector<ElimJob>& jobs, const std
   rc = check_cuda(ctx, cudaGetLastError(), "elimination kernels");
   std::vector<int> counts((size_t)nj * 4);
   std::vector<long long> nvia(nj);
-  for (int q = 0; q < nj && !rc; ++q) {
-    rc = check_cuda(ctx, cudaMemcpyAsync(&counts[(size_t)q * 4], E[q].counts, 16, cudaMemcpyDeviceToHost, ctx->stream), "D2H counts");
-    if (!rc) rc = check_cuda(ctx, cudaMemcpyAsync(&nvia[q], E[q].n_via, 8, cudaMemcpyDeviceToHost, ctx->stream), "D2H via count");
-  }
+  if (!rc) rc = check_cuda(ctx, cudaMemcpyAsync(counts.data(), buf + cnt_off, (size_t)nj * 16, cudaMemcpyDeviceToHost, ctx->stream), "D2H counts");
+  if (!rc) rc = check_cuda(ctx, cudaMemcpyAsync(nvia.data(), buf + nv_off, (size_t)nj * 8, cudaMemcpyDeviceToHost, ctx->stream), "D2H via counts");
   if (!rc) rc = check_cuda(ctx, cudaStreamSynchronize(ctx->stream), "sync");
   if (rc) { cleanup(); return rc; }
   // ---- packed results, one device->host copy

@@ -576,6 +576,22 @@ __device__ __forceinline__ int pred_index(const PairDev& P, const Ring& ring, co
   return (d2 & (ring.R - 1)) * ring.cap + s;
 }
 
+// Register wavefront: lane (= slot) of cell (i2,j2) in its diagonal if that diagonal lies exactly `want` steps back;
+// -1: not stored; -2: elsewhere (generic path through HBM).
+template <bool BWD>
+__device__ __forceinline__ int pred_lane(const PairDev& P, const Recent& rc, int dcur, bool en, int i2, int j2, int xs, int ys, int want) {
+  if (!en) return -1;
+  const int d2 = i2 + j2;
+  const int dist = BWD ? d2 - dcur : dcur - d2;
+  if (dist != want) return -2;
+  const int ilo = want == 1 ? rc.ilo1 : rc.ilo2, width = want == 1 ? rc.w1 : rc.w2;
+  const int r = i2 - ilo;
+  if ((unsigned)r < (unsigned)width) return P.nS + r;
+  if (xs >= 0) return xs;
+  if (ys >= 0) return P.nS + width + ys;
+  return -1;
+}
+
 __device__ __forceinline__ DiagInfo load_dinfo_early(const DiagInfo* p) {
   // volatile: keeps the load where it is written (ahead of its use in the NEXT iteration)
   DiagInfo d;
@@ -586,7 +602,9 @@ __device__ __forceinline__ DiagInfo load_dinfo_early(const DiagInfo* p) {
 // Everything about one cell that does not depend on earlier cells, as the 64-B record (r0..r3) the consumer
 // works from: ring addresses of its predecessors, flags, transition exponents / mantissas, emission factors,
 // absorb value.  `m`: the per-lane state records of diagonal d.
-template <bool BWD>
+// LANES: the predecessor fields of r0 are lanes of the previous (X, Y moves) / second previous (XY move) diagonal
+// (register wavefront) instead of ring addresses.
+template <bool BWD, bool LANES = false>
 __device__ __forceinline__ void make_record(const PairDev& P, const Ring& ring, int d, const Recent rc, const LaneMeta<BWD>& m, int4& r0,
                                             int4& r1, int4& r2, int4& r3) {
   // a near-start slot owns cells of near-end columns; then DPMatrix::inEnvelope (forward.h:92-98)
@@ -605,9 +623,9 @@ __device__ __forceinline__ void make_record(const PairDev& P, const Ring& ring, 
     const bool doX = ok && yReady && xc > 0;
     const bool doY = ok && (yEmit ? xReady : true) && yc > 0;
     const bool doD = ok && both && xc > 0 && yc > 0;
-    const int aX = pred_index<false>(P, ring, rc, d, doX, m.xb.x, j, m.xb.w, m.ya.w);
-    const int aY = pred_index<false>(P, ring, rc, d, doY, i, m.yb.x, m.xa.w, m.yb.w);
-    const int aD = pred_index<false>(P, ring, rc, d, doD, m.xb.x, m.yb.x, m.xb.w, m.yb.w);
+    const int aX = LANES ? pred_lane<false>(P, rc, d, doX, m.xb.x, j, m.xb.w, m.ya.w, 1) : pred_index<false>(P, ring, rc, d, doX, m.xb.x, j, m.xb.w, m.ya.w);
+    const int aY = LANES ? pred_lane<false>(P, rc, d, doY, i, m.yb.x, m.xa.w, m.yb.w, 1) : pred_index<false>(P, ring, rc, d, doY, i, m.yb.x, m.xa.w, m.yb.w);
+    const int aD = LANES ? pred_lane<false>(P, rc, d, doD, m.xb.x, m.yb.x, m.xb.w, m.yb.w, 2) : pred_index<false>(P, ring, rc, d, doD, m.xb.x, m.yb.x, m.xb.w, m.yb.w);
     if (xEmit) flags |= R_XEMIT;
     if (yEmit) flags |= R_YEMIT;
     if (!xEmit && !(!yEmit && xEmitOrStart)) flags |= R_IMM_BY_X;
@@ -626,9 +644,9 @@ __device__ __forceinline__ void make_record(const PairDev& P, const Ring& ring, 
     const bool doD = ok && xac > 0 && yac > 0;
     const bool doX = ok && yReady && xac > 0;
     const bool doY = ok && xReady && yac > 0;
-    const int aD = pred_index<true>(P, ring, rc, d, doD, m.x0.x, m.y0.x, m.x0.z, m.y0.z);
-    const int aX = pred_index<true>(P, ring, rc, d, doX, m.x0.x, j, m.x0.z, m.ya.w);
-    const int aY = pred_index<true>(P, ring, rc, d, doY, i, m.y0.x, m.xa.w, m.y0.z);
+    const int aD = LANES ? pred_lane<true>(P, rc, d, doD, m.x0.x, m.y0.x, m.x0.z, m.y0.z, 2) : pred_index<true>(P, ring, rc, d, doD, m.x0.x, m.y0.x, m.x0.z, m.y0.z);
+    const int aX = LANES ? pred_lane<true>(P, rc, d, doX, m.x0.x, j, m.x0.z, m.ya.w, 1) : pred_index<true>(P, ring, rc, d, doX, m.x0.x, j, m.x0.z, m.ya.w);
+    const int aY = LANES ? pred_lane<true>(P, rc, d, doY, i, m.y0.x, m.xa.w, m.y0.z, 1) : pred_index<true>(P, ring, rc, d, doY, i, m.y0.x, m.xa.w, m.y0.z);
     const bool toEnd = (fx & F_TO_END) && (fy & F_TO_END);
     if (toEnd) flags |= R_TO_END;
     const bool xNull = yReady && m.xb.y > ((fx & F_TO_END) ? 1 : 0);
@@ -709,13 +727,11 @@ __device__ __forceinline__ WReg load_weights(const PairDev& P) {
   return r;
 }
 
-__device__ __forceinline__ Cell forward_fast(const WReg& WR, const Ring& ring, const int4 r0, const int4 r1, const int4 r2, const int4 r3) {
+// Forward cell from its record and the three predecessor cells (A = IMM,IMD,IDM,IMI; B = IIW, exponent bits, aux)
+__device__ __forceinline__ Cell forward_math(const WReg& WR, const int flags, const int4 r1, const int4 r2, const int4 r3, const bool vX,
+                                             const float4 xA, const float4 xB, const bool vY, const float4 yA, const float4 yB, const bool vD,
+                                             const float4 dA, const float4 dB) {
   const float (*W)[6] = WR.w;
-  const int flags = r0.w;
-  float4 xA, xB, yA, yB, dA, dB;
-  const bool vX = ring_read(ring, r0.x, xA, xB);
-  const bool vY = ring_read(ring, r0.y, yA, yB);
-  const bool vD = ring_read(ring, r0.z, dA, dB);
   const bool origin = flags & R_ORIGIN;
   const int eX = vX ? __float_as_int(xB.y) + r1.x : HB_EXP_ZERO;
   const int eY = vY ? __float_as_int(yB.y) + r1.y : HB_EXP_ZERO;
@@ -757,13 +773,18 @@ __device__ __forceinline__ Cell forward_fast(const WReg& WR, const Ring& ring, c
   return a;
 }
 
-__device__ __forceinline__ Cell backward_fast(const WReg& WR, const Ring& ring, const int4 r0, const int4 r1, const int4 r2, const int4 r3) {
+__device__ __forceinline__ Cell forward_fast(const WReg& WR, const Ring& ring, const int4 r0, const int4 r1, const int4 r2, const int4 r3) {
+  float4 xA, xB, yA, yB, dA, dB;
+  const bool vX = ring_read(ring, r0.x, xA, xB);
+  const bool vY = ring_read(ring, r0.y, yA, yB);
+  const bool vD = ring_read(ring, r0.z, dA, dB);
+  return forward_math(WR, r0.w, r1, r2, r3, vX, xA, xB, vY, yA, yB, vD, dA, dB);
+}
+
+__device__ __forceinline__ Cell backward_math(const WReg& WR, const int flags, const int4 r1, const int4 r2, const int4 r3, const bool vD,
+                                              const float4 dA, const float4 dB, const bool vX, const float4 xA, const float4 xB, const bool vY,
+                                              const float4 yA, const float4 yB) {
   const float (*W)[6] = WR.w;
-  const int flags = r0.w;
-  float4 dA, dB, xA, xB, yA, yB;
-  const bool vD = ring_read(ring, r0.x, dA, dB);
-  const bool vX = ring_read(ring, r0.y, xA, xB);
-  const bool vY = ring_read(ring, r0.z, yA, yB);
   const bool toEnd = flags & R_TO_END;
   const int eD = vD ? __float_as_int(dB.y) + r1.x : HB_EXP_ZERO;
   const int eX = vX ? __float_as_int(xB.y) + r1.y : HB_EXP_ZERO;
@@ -784,6 +805,14 @@ __device__ __forceinline__ Cell backward_fast(const WReg& WR, const Ring& ring, 
   a.v[4] = W[4][0] * dest + W[4][4] * diw + W[4][2] * ddm + sE * W[4][5];
   cell_normalise(a);
   return a;
+}
+
+__device__ __forceinline__ Cell backward_fast(const WReg& WR, const Ring& ring, const int4 r0, const int4 r1, const int4 r2, const int4 r3) {
+  float4 dA, dB, xA, xB, yA, yB;
+  const bool vD = ring_read(ring, r0.x, dA, dB);
+  const bool vX = ring_read(ring, r0.y, xA, xB);
+  const bool vY = ring_read(ring, r0.z, yA, yB);
+  return backward_math(WR, r0.w, r1, r2, r3, vD, dA, dB, vX, xA, xB, vY, yA, yB);
 }
 
 template <bool BWD>
@@ -992,6 +1021,107 @@ __device__ __forceinline__ void consumer_stream(const PairDev& P, const Ring& ri
   }
 }
 
+
+// ------------------------------------------------------------------ narrow strips, register wavefront
+// One warp per strip and NOTHING between the lanes but shuffles: lane t owns slot t of every anti-diagonal and keeps
+// the cells it computed on the last two diagonals in registers; a cell's three predecessors (forward.cpp:95-200) sit
+// on exactly those two diagonals for chain-like profiles, so they are fetched with warp shuffles from the lanes that
+// own them.  There is no shared-memory ring, no record stream through HBM and no queue: everything that does not
+// depend on DP values (state records, layout records, absorb value) is requested one step ahead of its use, and the
+// dependent part of a step is shuffle -> FMAs -> normalise.  Predecessors that lie further back (long transitions of
+// DAG profiles), extra in-edges and null out-edges take the generic cell routine, which reads earlier cells from HBM
+// (every cell is stored as soon as it is computed).  Strips of up to 32 slots per anti-diagonal.
+struct RegCell {
+  float4 a;     // IMM, IMD, IDM, IMI
+  float iiw;
+  int e;        // exponent
+  float aux;    // Backward: IMM * absorb
+};
+
+__device__ __forceinline__ bool shfl_cell(const RegCell& c, int src, float4& A, float4& B) {
+  const int l = src & 31;
+  A.x = __shfl_sync(0xffffffffu, c.a.x, l);
+  A.y = __shfl_sync(0xffffffffu, c.a.y, l);
+  A.z = __shfl_sync(0xffffffffu, c.a.z, l);
+  A.w = __shfl_sync(0xffffffffu, c.a.w, l);
+  B.x = __shfl_sync(0xffffffffu, c.iiw, l);
+  const int e = __shfl_sync(0xffffffffu, c.e, l);
+  B.y = __int_as_float(e);
+  B.z = __shfl_sync(0xffffffffu, c.aux, l);
+  B.w = 0.f;
+  return src >= 0 && e > HB_EXP_ZERO / 2;
+}
+
+template <bool BWD>
+__device__ __forceinline__ void reg_step(const PairDev& P, const WReg& WR, const Ring& ring, const Recent& rc, const DiagInfo& di, int d, int t,
+                                         const LaneMeta<BWD>& m, RegCell& p1, RegCell& p2, float4* gA, float2* gB) {
+  int4 r0, r1, r2, r3;
+  make_record<BWD, true>(P, ring, d, rc, m, r0, r1, r2, r3);
+  float4 xA, xB, yA, yB, dA, dB;
+  // Forward: r0 = (X, Y, XY, flags); Backward: r0 = (XY, X, Y, flags).  X and Y moves come from the previous diagonal,
+  // the XY move from the one before.
+  const bool vX = shfl_cell(p1, BWD ? r0.y : r0.x, xA, xB);
+  const bool vY = shfl_cell(p1, BWD ? r0.z : r0.y, yA, yB);
+  const bool vD = shfl_cell(p2, BWD ? r0.x : r0.z, dA, dB);
+  Cell c = zero_cell();
+  float aux = 0.f;
+  if (r0.w & R_OK) {
+    const float ab = __int_as_float(r2.w);
+    if (r0.w & R_SLOW) c = generic_cell<BWD>(P, ring, rc, di, d, t, ab);
+    else c = BWD ? backward_math(WR, r0.w, r1, r2, r3, vD, dA, dB, vX, xA, xB, vY, yA, yB)
+                 : forward_math(WR, r0.w, r1, r2, r3, vX, xA, xB, vY, yA, yB, vD, dA, dB);
+    if (BWD) aux = c.v[0] * ab;  // absorb is 0 unless both states emit
+  }
+  const float4 va = make_float4(c.v[0], c.v[1], c.v[2], c.v[3]);
+  if (t < P.nS + di.width + P.nE) {
+    __stcs(gA + di.off + t, va);
+    __stcs(gB + di.off + t, make_float2(c.v[4], __int_as_float(c.E)));
+  }
+  p2 = p1;
+  p1.a = va; p1.iiw = c.v[4]; p1.e = c.E; p1.aux = aux;
+}
+
+template <bool BWD>
+__device__ __forceinline__ void consumer_reg(const PairDev& P, const Ring& ring) {
+  float4* gA = BWD ? P.bA : P.fA;
+  float2* gB = BWD ? P.bB : P.fB;
+  const int nD = P.n_diag;
+  const int t = threadIdx.x;
+  auto diag_of = [&](int q) { return min(max(BWD ? nD - 1 - q : q, 0), nD - 1); };
+  const WReg WR = load_weights(P);
+  RegCell p1, p2;
+  p1.a = make_float4(0.f, 0.f, 0.f, 0.f); p1.iiw = 0.f; p1.e = HB_EXP_ZERO; p1.aux = 0.f;
+  p2 = p1;
+  Recent rc = {0, 0, 0, 0};
+  // layout records two steps ahead, per-lane state records one step ahead; two named buffers (mA, mB) alternate so
+  // that no register copy has to wait for the loads
+  DiagInfo c0 = P.dinfo[diag_of(0)], n0 = P.dinfo[diag_of(1)], n1 = P.dinfo[diag_of(2)];
+  LaneMeta<BWD> mA = load_meta<BWD>(P, ring, c0, diag_of(0), t, true), mB;
+  for (int q = 0; q < nD; q += 2) {
+    {
+      const DiagInfo di = c0;
+      mB = load_meta<BWD>(P, ring, n0, diag_of(q + 1), t, true);
+      c0 = n0; n0 = n1;
+      n1 = load_dinfo_early(P.dinfo + diag_of(q + 3));
+      reg_step<BWD>(P, WR, ring, rc, di, diag_of(q), t, mA, p1, p2, gA, gB);
+      __syncwarp();
+      rc.ilo2 = rc.ilo1; rc.w2 = rc.w1;
+      rc.ilo1 = di.ilo; rc.w1 = di.width;
+    }
+    if (q + 1 >= nD) break;
+    {
+      const DiagInfo di = c0;
+      mA = load_meta<BWD>(P, ring, n0, diag_of(q + 2), t, true);
+      c0 = n0; n0 = n1;
+      n1 = load_dinfo_early(P.dinfo + diag_of(q + 4));
+      reg_step<BWD>(P, WR, ring, rc, di, diag_of(q + 1), t, mB, p1, p2, gA, gB);
+      __syncwarp();
+      rc.ilo2 = rc.ilo1; rc.w2 = rc.w1;
+      rc.ilo1 = di.ilo; rc.w1 = di.width;
+    }
+  }
+}
+
 // General strips: a CTA of several warps, each thread looping over the slots of the diagonal.
 template <bool BWD>
 __device__ __forceinline__ void sweep_wide(const PairDev& P, const Ring& ring) {
@@ -1015,7 +1145,8 @@ __device__ __forceinline__ void sweep_wide(const PairDev& P, const Ring& ring) {
 
 // grid.x = n_pairs * n_dir; block b handles pair b / n_dir, direction (b % n_dir) (0 = Forward, 1 = Backward;
 // with n_dir == 1 the direction is `only_dir`).
-// MODE 0: general strips (CTA-wide sweep); 1: narrow strips, producer/consumer warps; 2: narrow strips, streamed records
+// MODE 0: general strips (CTA-wide sweep); 1: narrow strips, producer/consumer warps; 2: narrow strips, streamed records;
+// 3: narrow strips, register wavefront
 template <int MODE>
 __device__ __forceinline__ void fill_body(PairDev* const* __restrict__ pairs, int n_dir, int only_dir, int ring_cap, int ring_rows,
                                           int4* const* __restrict__ recs = nullptr) {
@@ -1051,7 +1182,10 @@ __device__ __forceinline__ void fill_body(PairDev* const* __restrict__ pairs, in
     ring.ecols = edge_cols;
     __syncthreads();
   }
-  if (MODE == 2) {
+  if (MODE == 3) {
+    ring.R = 0;   // no shared-memory ring: earlier cells are in registers or in HBM
+    if (bwd) consumer_reg<true>(P, ring); else consumer_reg<false>(P, ring);
+  } else if (MODE == 2) {
     int4* queue = reinterpret_cast<int4*>(ring.B + (size_t)ring_rows * ring_cap);
     if (bwd) consumer_stream<true>(P, ring, recs[blockIdx.x], queue, mbar); else consumer_stream<false>(P, ring, recs[blockIdx.x], queue, mbar);
   } else if (MODE == 1) {
@@ -1103,6 +1237,10 @@ __global__ void __maxnreg__(HB_NARROW_REGS) fill_narrow_kernel(PairDev* const* _
 __global__ void __maxnreg__(200) fill_stream_kernel(PairDev* const* __restrict__ pairs, int4* const* __restrict__ recs, int n_dir, int only_dir,
                                                          int ring_cap, int ring_rows) {
   fill_body<2>(pairs, n_dir, only_dir, ring_cap, ring_rows, recs);
+}
+// one warp per strip, no dynamic shared memory
+__global__ void __launch_bounds__(32) fill_reg_kernel(PairDev* const* __restrict__ pairs, int n_dir, int only_dir) {
+  fill_body<3>(pairs, n_dir, only_dir, 32, 0);
 }
 __global__ void __launch_bounds__(512) fill_kernel(PairDev* const* __restrict__ pairs, int n_dir, int only_dir, int ring_cap, int ring_rows) {
   fill_body<0>(pairs, n_dir, only_dir, ring_cap, ring_rows);
@@ -1226,6 +1364,15 @@ int launch_fill_uniform(hist_ctx* ctx, hist_pair* const* pairs, int n, int n_dir
     ctx->launches += 1;
   }
   static const bool use_queue = getenv("HIST_B200_FILL") && !strcmp(getenv("HIST_B200_FILL"), "queue");
+  static const bool use_stream = getenv("HIST_B200_FILL") && !strcmp(getenv("HIST_B200_FILL"), "stream");
+  if (narrow && maxThreads <= 32 && !use_queue && !use_stream) {
+    // register wavefront: no record stream, no ring
+    fill_reg_kernel<<<n * n_dir, 32, 0, ctx->stream>>>(dptrs, n_dir, only_dir);
+    ctx->launches += 1;
+    HB_CUDA(ctx, cudaGetLastError());
+    HB_CUDA(ctx, cudaFreeAsync(dptrs, ctx->stream));
+    return HIST_OK;
+  }
   char* rec_buf = nullptr;
   const int n_cta = n * n_dir;
   std::vector<size_t> off(n_cta + 1, 0);

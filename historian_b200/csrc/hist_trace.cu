@@ -59,6 +59,31 @@ struct Mt {
   }
 };
 
+// lpCellEmitOrAbsorb (forward.cpp:404-440) of one cell by the whole warp: the lanes split the C*A terms of
+// computeLogProbAbsorb (forward.h:112-124) instead of every lane repeating the serial sum (FP64 exp is the
+// expensive part of a traceback step).  Every lane returns the same value (xor-shuffle reductions).
+__device__ __forceinline__ double dp_emit_warp(const PairDev& P, const DCell& c, int lane) {
+  const bool xe = c.x < P.x.n && (P.x.flags[c.x] & F_EMIT), ye = c.y < P.y.n && (P.y.flags[c.y] & F_EMIT);
+  if (c.s != HIST_IMM || !(xe && ye)) return dp_emit(P, c);
+  const double* sx = P.x.sub + (size_t)c.x * P.K;
+  const double* sy = P.y.sub + (size_t)c.y * P.K;
+  double t0 = -INFINITY, t1 = -INFINITY, t2 = -INFINITY;   // K <= 96 in registers, more through a loop
+  if (lane < P.K) t0 = P.log_root[lane] + sx[lane] + sy[lane];
+  if (lane + 32 < P.K) t1 = P.log_root[lane + 32] + sx[lane + 32] + sy[lane + 32];
+  if (lane + 64 < P.K) t2 = P.log_root[lane + 64] + sx[lane + 64] + sy[lane + 64];
+  double m = fmax(fmax(t0, t1), t2);
+  for (int k = lane + 96; k < P.K; k += 32) m = fmax(m, P.log_root[k] + sx[k] + sy[k]);
+  for (int o = 16; o; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if (m == -INFINITY) return -INFINITY;
+  double acc = 0;
+  if (t0 > -INFINITY) acc += exp(t0 - m);
+  if (t1 > -INFINITY) acc += exp(t1 - m);
+  if (t2 > -INFINITY) acc += exp(t2 - m);
+  for (int k = lane + 96; k < P.K; k += 32) acc += exp(P.log_root[k] + sx[k] + sy[k] - m);
+  for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  return m + log(acc);
+}
+
 // destination candidates of the Backward walk (destTransitions + destCells, forward.cpp:1216-1285);
 // lane 0 lists them (the lists are short), all lanes then evaluate them
 __device__ int list_dests(const PairDev& P, const DCell& sc, DCell* cand, double* clp, int cap) {
@@ -155,7 +180,7 @@ __global__ void __launch_bounds__(32) trace_kernel(const TraceArgs* __restrict__
         const SrcEnum e = source_enum(P, cur, nullptr);
         n = e.n;
         if (n > a.cand_cap) { if (lane == 0) s_flag = 3; break; }
-        const double emit = dp_emit(P, cur);
+        const double emit = dp_emit_warp(P, cur, lane);
         for (int c = lane; c < n; c += 32) {
           DCell s;
           double lp;

@@ -21,7 +21,8 @@ from historian_b200 import descs as D, recon as R
 
 pytestmark = pytest.mark.gpu
 CASES = H.golden_cases() + H.golden_cases(sparse=True)
-DIVERGED = {}   # fixture -> nodes whose device traces differ from the reference's (table log-sum-exp margin)
+DIVERGED = {}   # fixture -> nodes whose device traces differ from the reference's AND from the exact-arithmetic oracle's
+EXPLAINED = {}  # fixture -> nodes whose device traces differ from the reference's but equal the exact-arithmetic oracle's
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 REF_BIN = os.path.join(ROOT, "oracle", "_ref", "bin", "historian")
 
@@ -76,9 +77,27 @@ def test_parent_profile_matches_reference(ctx, cid, path, node):
         strat = strategy
     prof, e = R.make_profile(pair, view, cells, strat)
     if not same_traces:
-        # the reference walks its table-log-sum-exp matrix: a step can differ when two candidates lie within ~1e-4.
-        # The profile is then not comparable; the node is counted and test_trace_divergences_are_rare bounds the count.
-        DIVERGED.setdefault(os.path.basename(path), []).append(node)
+        # The reference walks its table-log-sum-exp matrix: a step can differ when two candidates (or a draw and a
+        # boundary) lie within ~1e-4 -- on 500-residue sequences with thousands of sampled steps per node that is not
+        # rare.  The arbiter is the CPU oracle, which is bit-identical to the reference with the table and exact
+        # without it: the device's traces must then be the exact-arithmetic ones.  The parent profile is not comparable
+        # with the reference's in that case; nodes the oracle does not explain are counted and bounded below.
+        import oracle_lib as O
+        O.set_exact_lse(True)
+        try:
+            efwd, _ = O.forward(x, y, hmm, env)
+            efwd = np.ascontiguousarray(efwd)
+            ok = H.same(best, O.trace_best(x, y, hmm, env, efwd, (x.n_states - 1, y.n_states - 1, D.EEE)))
+            if ok and not is_root and min_post <= 0:
+                n_probe = 0
+                while pfx + "sample_trace%d" % n_probe in d:
+                    n_probe += 1
+                etr, _ = O.trace_sample(x, y, hmm, env, efwd, d[pfx + "rng_before"], n_probe)
+                probe = d[pfx + "rng_before"].astype(np.uint32).copy()
+                ok = all(H.same(pair.trace_sample(probe, 1)[0], etr[k]) for k in range(n_probe))
+        finally:
+            O.set_exact_lse(False)
+        (EXPLAINED if ok else DIVERGED).setdefault(os.path.basename(path), []).append(node)
         return
     p = prof.flat
     assert H.same(p.is_emit, d[pfx + "parent.is_emit"]), cid
@@ -93,10 +112,11 @@ def test_parent_profile_matches_reference(ctx, cid, path, node):
         assert any(H.same(a[1:], ref_leaf[1:]) for a in prof.leaf_rows.values()), cid + ": closest-leaf coordinates"
 
 
-def test_trace_divergences_are_rare():
-    """At most one node per fixture may have been skipped above because a trace left the reference's."""
-    assert all(len(v) <= 1 for v in DIVERGED.values()), DIVERGED
-    assert sum(len(v) for v in DIVERGED.values()) <= 2, DIVERGED
+def test_trace_divergences_are_explained():
+    """Every node whose traces left the reference's must have been reproduced by the exact-arithmetic oracle (at most one
+    exception over all fixtures: FP32 cell mantissas against FP64 at a ~1e-7 margin), and most nodes must not diverge."""
+    assert sum(len(v) for v in DIVERGED.values()) <= 1, (DIVERGED, EXPLAINED)
+    assert sum(len(v) for v in EXPLAINED.values()) <= len(CASES) // 4, EXPLAINED
 
 
 def _simulate(tmp, n_leaves, root_len, seed, bl=0.3):
