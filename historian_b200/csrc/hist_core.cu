@@ -239,6 +239,10 @@ __global__ void pack_meta_kernel(PairDev* const* __restrict__ pairs) {
   s.bm[s.n + i] = make_int4(nb, nc, end_e, __float_as_int((float)end_sum));
   s.bm[2 * s.n + i] = f0;
   s.bm[3 * s.n + i] = f1;
+  // records of the chain kernels (leaf x leaf merges): own emission factors, and those of the next state
+  s.cf[i] = make_int4(s.ex[i], __float_as_int(s.rs[i]), __float_as_int(s.ins[i]), s.key[i]);
+  const int nx = min(i + 1, s.n - 1);
+  s.cb[i] = make_int4(s.ex[nx], __float_as_int(s.rs[nx]), __float_as_int(s.ins[nx]), s.key[i]);
 }
 
 // Exact in-envelope cell count (the GCUPS unit, forward.cpp:78-86), one thread per stored slot.
@@ -524,6 +528,11 @@ extern "C" int hist_profile_upload(hist_ctx* ctx, const hist_profile_desc* d, hi
   p->empty = true;
   for (int i = 0; i < p->n; ++i)
     if (p->is_emit[i]) p->empty = false;
+  // a leaf chain (Profile(components, alphabet, FastSeq, row), profile.cpp:23-76) uploaded by hand gets the same fast paths
+  // as one built by hist_profile_from_sequences
+  p->chain = p->nt == p->n - 1;
+  for (int t = 0; t < p->nt && p->chain; ++t) p->chain = p->t_src[t] == t && p->t_dst[t] == t + 1 && p->t_lp[t] == 0.0;
+  for (int i = 1; i + 1 < p->n && p->chain; ++i) p->chain = p->is_emit[i] != 0;
   const size_t bytes = (size_t)p->n * p->C * p->A * sizeof(double);
   p->d_lp_absorb = nullptr;
   p->arena = nullptr;
@@ -736,7 +745,7 @@ struct SideHost {
 
 struct SideOff {  // h_*: offsets in the host-initialised part, d_*: in the device-only part
   size_t h_flags, h_t_src, h_t_dst, h_t_lp, h_in_off, h_in_idx, h_ao_off, h_ao_idx, h_no_off, h_no_idx, h_key, h_near, h_slot;
-  size_t d_t_m, d_t_e, d_ex, d_rs, d_ins, d_H, d_sub, d_rootsub, d_insl, d_fm_a, d_fm_b, d_emis, d_in_edges, d_bm, d_ao_edges, d_no_edges;
+  size_t d_t_m, d_t_e, d_ex, d_rs, d_ins, d_H, d_sub, d_rootsub, d_insl, d_fm_a, d_fm_b, d_emis, d_in_edges, d_bm, d_ao_edges, d_no_edges, d_cf, d_cb;
 };
 
 struct PairBuild {
@@ -961,6 +970,8 @@ int build_pair_host(hist_ctx* ctx, const hist_profile* x, const hist_profile* y,
     o.d_emis = Dv.reserve((size_t)p->n * sizeof(float2));
     o.d_in_edges = Dv.reserve(nt1 * sizeof(int4));
     o.d_bm = Dv.reserve((size_t)p->n * 4 * sizeof(int4));
+    o.d_cf = Dv.reserve((size_t)p->n * sizeof(int4));
+    o.d_cb = Dv.reserve((size_t)p->n * sizeof(int4));
     o.d_ao_edges = Dv.reserve(nt1 * 2 * sizeof(int4));
     o.d_no_edges = Dv.reserve(nt1 * 2 * sizeof(int4));
     return o;
@@ -1020,6 +1031,7 @@ int build_pair_host(hist_ctx* ctx, const hist_profile* x, const hist_profile* y,
   D.n_diag = nDiag;
   D.nS = nS; D.nE = nE;
   D.max_threads = maxThreads;
+  D.chain = x->chain && y->chain && nx >= 3 && ny >= 3 && nS == 1 && nE == 1 ? 1 : 0;
   D.n_stored = nStored;
   pr->x_key = sx.key; pr->y_key = sy.key;
   pr->x_near = sx.near_; pr->y_near = sy.near_;
@@ -1054,6 +1066,7 @@ void place_pair(PairBuild& b, char* arena, size_t scal_off, bool want_bwd) {
     s.sub = (double*)(db + o.d_sub); s.rootsub = (double*)(db + o.d_rootsub); s.insl = (double*)(db + o.d_insl);
     s.fm_a = (int4*)(db + o.d_fm_a); s.fm_b = (int4*)(db + o.d_fm_b); s.emis = (float2*)(db + o.d_emis);
     s.in_edges = (int4*)(db + o.d_in_edges); s.bm = (int4*)(db + o.d_bm);
+    s.cf = (int4*)(db + o.d_cf); s.cb = (int4*)(db + o.d_cb);
     s.ao_edges = (int4*)(db + o.d_ao_edges); s.no_edges = (int4*)(db + o.d_no_edges);
   };
   PairDev& D = pr->dev;

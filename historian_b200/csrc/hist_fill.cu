@@ -1122,6 +1122,229 @@ __device__ __forceinline__ void consumer_reg(const PairDev& P, const Ring& ring)
   }
 }
 
+
+// ------------------------------------------------------------------ leaf x leaf strips: chain kernel
+// Both profiles are leaf chains (state t -> t+1 with log-weight 0, states 1..n-2 emit): every state has in-degree and
+// out-degree 1 and the only null states are START and END, so everything make_record derives from packed state
+// records follows from (i, j) by arithmetic: predecessor cells are (i-1,j), (i,j-1), (i-1,j-1), flags are comparisons
+// against 0 and n-2, transition mantissas are 1.  What is left to load per step is ONE 16-B record per profile
+// ({ex, rootsub, ins, band key} of the lane's state) and, because the lane keeps the emission rows of its two states
+// in registers and only one of them changes from one anti-diagonal to the next, ONE row of K floats: the absorb term
+// exp(computeLogProbAbsorb(i,j)) (forward.h:112-124) is a K-term dot product of two register-resident rows, computed
+// in the wavefront warp itself instead of a separate pass through HBM.  No absorb plane, no record stream, no
+// shared-memory ring: HBM sees the cell stores and nothing else.
+struct ChainPos {
+  int i, j;
+  bool ok;     // the slot owns an in-range cell (envelope test not included)
+};
+
+__device__ __forceinline__ ChainPos chain_pos(const DiagInfo& di, int d, int t, int nx, int ny) {
+  // slot layout with one near-start row (x START) and one near-end column (y state ny-2): [row 0 | main interval | column ny-2]
+  ChainPos p;
+  const bool head = t == 0, mid = t >= 1 && t <= di.width;
+  const int i = head ? 0 : mid ? di.ilo + t - 1 : d - (ny - 2);
+  const int j = d - i;
+  const bool in_main = (unsigned)(i - di.ilo) < (unsigned)di.width;
+  // row 0 / column ny-2 cells inside the main interval belong to it; (0, ny-2) belongs to the near-start slot
+  bool ok = t < di.width + 2 && (mid || !in_main) && (head || mid || i != 0);
+  ok = ok && i >= 0 && j >= 0 && i <= nx - 2 && j <= ny - 2;
+  p.i = ok ? i : 0; p.j = ok ? j : 0; p.ok = ok;
+  return p;
+}
+
+// slot of cell (i2,j2) on a diagonal with layout (ilo, width); -1 if it is not stored there
+__device__ __forceinline__ int chain_slot(int ilo, int width, int i2, int j2, int ny) {
+  const int r = i2 - ilo;
+  const int edge = i2 == 0 ? 0 : (j2 == ny - 2 ? 1 + width : -1);
+  return (unsigned)r < (unsigned)width ? 1 + r : edge;
+}
+
+// Predicated in-place load of one emission row: lanes whose predicate is false keep their registers (a plain
+// `if (pred) h = load` makes the compiler load into temporaries and copy, 4*K4 moves per row and step).
+template <int K4>
+__device__ __forceinline__ void load_row(float4 (&h)[K4], const float* __restrict__ H, int row, int Kp, bool pred) {
+  const float4* g = reinterpret_cast<const float4*>(H + (size_t)row * Kp);
+#pragma unroll
+  for (int k = 0; k < K4; ++k)
+    asm volatile("{\n .reg .pred p;\n setp.ne.s32 p, %5, 0;\n @p ld.global.nc.v4.f32 {%0,%1,%2,%3}, [%4];\n}"
+                 : "+f"(h[k].x), "+f"(h[k].y), "+f"(h[k].z), "+f"(h[k].w)
+                 : "l"(g + k), "r"((int)pred));
+}
+
+// Forward cell of a chain x chain strip, branch-free (forward_math with the flag tests resolved: an x-move implies
+// that x emits, a y-move that y emits, and IMM is fed by the xy-move alone; forward.cpp:95-200).
+__device__ __forceinline__ Cell chain_forward_math(const WReg& WR, bool origin, int ex, int ey, float rsx, float insx, float rsy, float insy,
+                                                   float ab, bool vX, const float4 xA, const float4 xB, bool vY, const float4 yA,
+                                                   const float4 yB, bool vD, const float4 dA, const float4 dB) {
+  const float (*W)[6] = WR.w;
+  const int eX = vX ? __float_as_int(xB.y) + ex : HB_EXP_ZERO;
+  const int eY = vY ? __float_as_int(yB.y) + ey : HB_EXP_ZERO;
+  const int eD = vD ? __float_as_int(dB.y) + ex + ey : HB_EXP_ZERO;
+  Cell a;
+  a.E = max(max(eX, eY), max(eD, origin ? 0 : HB_EXP_ZERO));
+  const float sX = vX ? pow2_neg(eX - a.E) : 0.f;
+  const float sY = vY ? pow2_neg(eY - a.E) : 0.f;
+  const float sD = vD ? pow2_neg(eD - a.E) : 0.f;
+  a.v[1] = sX * rsx * (xA.x * W[0][1] + xA.y * W[1][1] + xA.z * W[2][1] + xA.w * W[3][1]);
+  a.v[4] = sX * insx * (xA.x * W[0][4] + xA.w * W[3][4] + xB.x * W[4][4]);
+  a.v[2] = sY * rsy * (yA.x * W[0][2] + yA.y * W[1][2] + yA.z * W[2][2] + yB.x * W[4][2]);
+  a.v[3] = sY * insy * (yA.x * W[0][3] + yA.w * W[3][3]);
+  const float imm = sD * ab * (dA.x * W[0][0] + dA.y * W[1][0] + dA.z * W[2][0] + dA.w * W[3][0] + dB.x * W[4][0]);
+  a.v[0] = origin ? 1.f : imm;   // lpStart() = 0 at (0,0) (forward.cpp:73): no predecessor, exponent 0
+  cell_normalise(a);
+  return a;
+}
+
+template <bool BWD, int K4>
+__device__ __forceinline__ void consumer_chain(const PairDev& P) {
+  float4* gA = BWD ? P.bA : P.fA;
+  float2* gB = BWD ? P.bB : P.fB;
+  const int nD = P.n_diag, nx = P.x.n, ny = P.y.n, Kp = P.Kp;
+  const int t = threadIdx.x;
+  auto diag_of = [&](int q) { return min(max(BWD ? nD - 1 - q : q, 0), nD - 1); };
+  const WReg WR = load_weights(P);
+  const int4* __restrict__ recx = BWD ? P.x.cb : P.x.cf;
+  const int4* __restrict__ recy = BWD ? P.y.cb : P.y.cf;
+  const float* __restrict__ Hx = P.x.H;
+  const float* __restrict__ Hy = P.y.H;
+  const int max_dist = P.max_dist;
+  RegCell p1, p2;
+  p1.a = make_float4(0.f, 0.f, 0.f, 0.f); p1.iiw = 0.f; p1.e = HB_EXP_ZERO; p1.aux = 0.f;
+  p2 = p1;
+  int ilo1 = 0, w1 = 0, ilo2 = 0, w2 = 0;
+  DiagInfo c0 = P.dinfo[diag_of(0)], n0 = P.dinfo[diag_of(1)], n1 = P.dinfo[diag_of(2)];
+  ChainPos cur = chain_pos(c0, diag_of(0), t, nx, ny);
+  float4 hx[K4], hy[K4];
+#pragma unroll
+  for (int k = 0; k < K4; ++k) hx[k] = hy[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+  int hi = -1, hj = -1;   // states whose emission rows hx / hy hold
+  {
+    const bool px = cur.ok && cur.i >= 1, py = cur.ok && cur.j >= 1;
+    load_row<K4>(hx, Hx, cur.i, Kp, px);
+    load_row<K4>(hy, Hy, cur.j, Kp, py);
+    hi = px ? cur.i : hi;
+    hj = py ? cur.j : hj;
+  }
+  int4 rx = __ldg(recx + cur.i), ry = __ldg(recy + cur.j);
+  for (int q = 0; q < nD; ++q) {
+    const DiagInfo di = c0;
+    const int i = cur.i, j = cur.j;
+    const bool xEmit = i >= 1, yEmit = j >= 1;
+    // ---- the absorb term of this cell from the register-resident rows, then the rows are free for the next step
+    float ab = 0.f;
+    {
+      float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+      for (int k = 0; k < K4; ++k) {
+        a0 = fmaf(hx[k].x, hy[k].x, a0);
+        a1 = fmaf(hx[k].y, hy[k].y, a1);
+        a0 = fmaf(hx[k].z, hy[k].z, a0);
+        a1 = fmaf(hx[k].w, hy[k].w, a1);
+      }
+      // the rows are overwritten in place below: pin the dot product ahead of those loads (both are volatile asm)
+      asm volatile("" : "+f"(a0), "+f"(a1));
+      if (cur.ok && xEmit && yEmit && hi == i && hj == j) ab = a0 + a1;
+    }
+    // ---- requests for the next step (nothing here depends on DP values): at most one row changes for a main-interval lane
+    const ChainPos nxt = chain_pos(n0, diag_of(q + 1), t, nx, ny);
+    const int4 rxn = __ldg(recx + nxt.i), ryn = __ldg(recy + nxt.j);
+    {
+      const bool px = nxt.ok && nxt.i >= 1 && nxt.i != hi, py = nxt.ok && nxt.j >= 1 && nxt.j != hj;
+      load_row<K4>(hx, Hx, nxt.i, Kp, px);
+      load_row<K4>(hy, Hy, nxt.j, Kp, py);
+      hi = px ? nxt.i : hi;
+      hj = py ? nxt.j : hj;
+    }
+    c0 = n0; n0 = n1;
+    n1 = load_dinfo_early(P.dinfo + diag_of(q + 3));
+    // ---- this step
+    const bool xLast = i == nx - 2, yLast = j == ny - 2;      // the states with the null transition into END: not ready
+    const bool ok = cur.ok && (i == 0 || yLast || max_dist < 0 || hb_iabs(rx.w - ry.w) <= max_dist);   // DPMatrix::inEnvelope (forward.h:92-98)
+    int sX, sY, sD;
+    if (!BWD) {
+      const bool doX = ok && !yLast && xEmit;             // x-move from (i-1, j)    (forward.cpp:95-129)
+      const bool doY = ok && !xLast && yEmit;             // y-move from (i, j-1)    (forward.cpp:131-163)
+      const bool doD = ok && xEmit && yEmit;              // xy-move from (i-1, j-1) (forward.cpp:165-184)
+      sX = doX ? chain_slot(ilo1, w1, i - 1, j, ny) : -1;
+      sY = doY ? chain_slot(ilo1, w1, i, j - 1, ny) : -1;
+      sD = doD ? chain_slot(ilo2, w2, i - 1, j - 1, ny) : -1;
+    } else {
+      const bool xac = i + 1 <= nx - 2, yac = j + 1 <= ny - 2;   // the absorbing out-edge i -> i+1 exists iff i+1 emits
+      sD = ok && xac && yac ? chain_slot(ilo2, w2, i + 1, j + 1, ny) : -1;     // forward.cpp:1017-1030
+      sX = ok && !yLast && xac ? chain_slot(ilo1, w1, i + 1, j, ny) : -1;      // forward.cpp:1032-1048
+      sY = ok && !xLast && yac ? chain_slot(ilo1, w1, i, j + 1, ny) : -1;      // forward.cpp:1050-1065
+    }
+    float4 xA, xB, yA, yB, dA, dB;
+    const bool vX = shfl_cell(p1, sX, xA, xB);
+    const bool vY = shfl_cell(p1, sY, yA, yB);
+    const bool vD = shfl_cell(p2, sD, dA, dB);
+    Cell c;
+    if (!BWD) {
+      c = chain_forward_math(WR, i == 0 && j == 0, rx.x, ry.x, __int_as_float(rx.y), __int_as_float(rx.z), __int_as_float(ry.y),
+                             __int_as_float(ry.z), ab, vX, xA, xB, vY, yA, yB, vD, dA, dB);
+    } else {
+      const int4 r1 = make_int4(rx.x + ry.x, rx.x, ry.x, i);
+      const int4 r2 = make_int4(__float_as_int(1.f), rx.y, rx.z, 0);
+      const int4 r3 = make_int4(ry.y, ry.z, 0, __float_as_int(1.f));
+      c = backward_math(WR, xLast && yLast ? R_TO_END : 0, r1, r2, r3, vD, dA, dB, vX, xA, xB, vY, yA, yB);
+    }
+    if (!ok) c = zero_cell();
+    const float4 va = make_float4(c.v[0], c.v[1], c.v[2], c.v[3]);
+    if (t < di.width + 2) {
+      __stcs(gA + di.off + t, va);
+      __stcs(gB + di.off + t, make_float2(c.v[4], __int_as_float(c.E)));
+    }
+    p2 = p1;
+    p1.a = va; p1.iiw = c.v[4]; p1.e = c.E; p1.aux = BWD ? c.v[0] * ab : 0.f;
+    ilo2 = ilo1; w2 = w1;
+    ilo1 = di.ilo; w1 = di.width;
+    cur = nxt;
+    rx = rxn; ry = ryn;
+  }
+}
+
+template <int K4>
+__global__ void __launch_bounds__(32) fill_chain_kernel(PairDev* const* __restrict__ pairs, int n_dir, int only_dir) {
+  __shared__ PairDev P;
+  {
+    const int* s = reinterpret_cast<const int*>(pairs[blockIdx.x / n_dir]);
+    int* dptr = reinterpret_cast<int*>(&P);
+    for (int k = threadIdx.x; k < (int)(sizeof(PairDev) / sizeof(int)); k += blockDim.x) dptr[k] = s[k];
+  }
+  __syncthreads();
+  const bool bwd = n_dir == 2 ? (blockIdx.x % n_dir) == 1 : only_dir == 1;
+  if (bwd) consumer_chain<true, K4>(P); else consumer_chain<false, K4>(P);
+  __threadfence_block();
+  __syncwarp();
+  if (threadIdx.x == 0) {
+    if (!bwd) {
+      // transitions into EEE (forward.cpp:205-220): the one cell (nx-2, ny-2)
+      const int i = P.x.n - 2, j = P.y.n - 2, d = i + j;
+      const DiagInfo di = P.dinfo[d];
+      const int s = chain_slot(di.ilo, di.width, i, j, P.y.n);
+      double lp = -INFINITY;
+      if (s >= 0) {
+        const float4 a = P.fA[di.off + s];
+        const float2 b = P.fB[di.off + s];
+        const int E = __float_as_int(b.y);
+        const double v = (double)a.x * P.W[0][5] + (double)a.y * P.W[1][5] + (double)a.z * P.W[2][5] + (double)a.w * P.W[3][5] + (double)b.x * P.W[4][5];
+        if (E > HB_EXP_ZERO / 2 && v > 0) lp = log(v) + (double)E * HB_LN2;
+      }
+      *P.lp_end = lp;
+    } else {
+      const DiagInfo di = P.dinfo[0];
+      const int s = chain_slot(di.ilo, di.width, 0, 0, P.y.n);
+      double lp = -INFINITY;
+      if (s >= 0) {
+        const float4 a = P.bA[di.off + s];
+        const float2 b = P.bB[di.off + s];
+        if (__float_as_int(b.y) > HB_EXP_ZERO / 2) lp = cell_log(a.x, __float_as_int(b.y));
+      }
+      *P.lp_start = lp;  // BackwardMatrix::lpStart() = cell(0,0,IMM)
+    }
+  }
+}
+
 // General strips: a CTA of several warps, each thread looping over the slots of the diagonal.
 template <bool BWD>
 __device__ __forceinline__ void sweep_wide(const PairDev& P, const Ring& ring) {
@@ -1365,7 +1588,9 @@ int launch_fill_uniform(hist_ctx* ctx, hist_pair* const* pairs, int n, int n_dir
   }
   static const bool use_queue = getenv("HIST_B200_FILL") && !strcmp(getenv("HIST_B200_FILL"), "queue");
   static const bool use_stream = getenv("HIST_B200_FILL") && !strcmp(getenv("HIST_B200_FILL"), "stream");
-  if (narrow && maxThreads <= 32 && !use_queue && !use_stream) {
+  static const bool use_reg = getenv("HIST_B200_FILL") && !strcmp(getenv("HIST_B200_FILL"), "reg");
+  (void)use_stream;
+  if (narrow && maxThreads <= 32 && use_reg) {
     // register wavefront: no record stream, no ring
     fill_reg_kernel<<<n * n_dir, 32, 0, ctx->stream>>>(dptrs, n_dir, only_dir);
     ctx->launches += 1;
@@ -1413,9 +1638,42 @@ int launch_fill_uniform(hist_ctx* ctx, hist_pair* const* pairs, int n, int n_dir
   return HIST_OK;
 }
 
+// leaf x leaf merges whose strips fit one warp and whose emission rows fit the register budget
+bool chain_eligible(const hist_pair* pr) {
+  static const bool off = getenv("HIST_B200_FILL") != nullptr;   // any explicit kernel choice switches the chain kernel off (A/B runs)
+  const int K4 = pr->dev.Kp / 4;
+  return !off && pr->dev.chain && pr->dev.max_threads <= 32 && (K4 == 1 || K4 == 2 || K4 == 5);
+}
+
+int launch_fill_chain(hist_ctx* ctx, hist_pair* const* pairs, int n, int n_dir, int only_dir) {
+  // one launch per row length (a batch of leaf merges shares one alphabet: normally exactly one launch)
+  for (int K4 : {1, 2, 5}) {
+    std::vector<PairDev*> h;
+    for (int k = 0; k < n; ++k)
+      if (pairs[k]->dev.Kp / 4 == K4) h.push_back(pairs[k]->d_dev);
+    if (h.empty()) continue;
+    const int m = (int)h.size();
+    PairDev** dptrs = nullptr;
+    HB_CUDA(ctx, cudaMallocAsync((void**)&dptrs, m * sizeof(PairDev*), ctx->stream));
+    HB_CUDA(ctx, cudaMemcpyAsync(dptrs, h.data(), m * sizeof(PairDev*), cudaMemcpyHostToDevice, ctx->stream));
+    if (K4 == 1) fill_chain_kernel<1><<<m * n_dir, 32, 0, ctx->stream>>>(dptrs, n_dir, only_dir);
+    else if (K4 == 2) fill_chain_kernel<2><<<m * n_dir, 32, 0, ctx->stream>>>(dptrs, n_dir, only_dir);
+    else fill_chain_kernel<5><<<m * n_dir, 32, 0, ctx->stream>>>(dptrs, n_dir, only_dir);
+    ctx->launches += 1;
+    HB_CUDA(ctx, cudaGetLastError());
+    HB_CUDA(ctx, cudaFreeAsync(dptrs, ctx->stream));
+  }
+  return HIST_OK;
+}
+
 // Narrow strips (every anti-diagonal fits one warp) and general strips use different kernels; one wide merge
 // must not push a whole level of narrow ones onto the general kernel, so a mixed batch is launched in two parts.
-int launch_fill(hist_ctx* ctx, hist_pair* const* pairs, int n, int n_dir, int only_dir) {
+// Leaf x leaf merges go to the chain kernel first.
+int launch_fill(hist_ctx* ctx, hist_pair* const* pairs_in, int n_in, int n_dir, int only_dir) {
+  std::vector<hist_pair*> chain, rest;
+  for (int k = 0; k < n_in; ++k) (chain_eligible(pairs_in[k]) ? chain : rest).push_back(pairs_in[k]);
+  hist_pair* const* pairs = rest.data();
+  const int n = (int)rest.size();
   std::vector<hist_pair*> narrow, wide;
   for (int k = 0; k < n; ++k) (pairs[k]->dev.max_threads <= 32 ? narrow : wide).push_back(pairs[k]);   // wide: streamed up to HB_SMAX slots, else general
   cudaEvent_t e0 = nullptr, e1 = nullptr;   // one event pair per fill call (bench.py's roofline leg)
@@ -1425,7 +1683,10 @@ int launch_fill(hist_ctx* ctx, hist_pair* const* pairs, int n, int n_dir, int on
     HB_CUDA(ctx, cudaEventRecord(e0, ctx->stream));
   }
   int rc = HIST_OK;
-  if (narrow.empty() || wide.empty()) {
+  if (!chain.empty()) rc = launch_fill_chain(ctx, chain.data(), (int)chain.size(), n_dir, only_dir);
+  if (rc || n == 0) {
+    // nothing but leaf merges in this batch
+  } else if (narrow.empty() || wide.empty()) {
     rc = launch_fill_uniform(ctx, pairs, n, n_dir, only_dir);
   } else {
     // the few general strips are latency-bound on their own (one CTA each): run them beside the narrow part

@@ -63,6 +63,7 @@ struct SideDev {
   int4* fm_a; int4* fm_b; float2* emis;   // [n] forward meta, (rs, ins)
   int4* in_edges;                         // [max(1,nt)]
   int4* bm;                               // [4][n] backward meta (plane-major)
+  int4* cf; int4* cb;                     // [n] chain records: {ex[i], rs[i], ins[i], key[i]} and {ex[i+1], rs[i+1], ins[i+1], key[i]}
   int4* ao_edges; int4* no_edges;         // [max(1,n_ao)][2], [max(1,n_no)][2]
   // natural-log doubles kept for fetch / makeProfile
   const double* lp_absorb;  // [n][K] input
@@ -97,6 +98,7 @@ struct PairDev {
   const int* end_cols;    // [nE]
   const DiagInfo* dinfo;  // [n_diag]
   int max_threads;        // max over d of nS + width + nE
+  int chain;              // both profiles are leaf chains (START -> residue 1 -> ... -> residue L -> END, log-weight 0 transitions)
   unsigned n_stored;
   float4* fA; float2* fB; // forward cells: (IMM,IMD,IDM,IMI), (IIW, E)
   float4* bA; float2* bB; // backward cells
