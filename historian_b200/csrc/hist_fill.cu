@@ -781,6 +781,7 @@ __device__ __forceinline__ Cell forward_fast(const WReg& WR, const Ring& ring, c
   return forward_math(WR, r0.w, r1, r2, r3, vX, xA, xB, vY, yA, yB, vD, dA, dB);
 }
 
+template <bool NORMALISE = true>
 __device__ __forceinline__ Cell backward_math(const WReg& WR, const int flags, const int4 r1, const int4 r2, const int4 r3, const bool vD,
                                               const float4 dA, const float4 dB, const bool vX, const float4 xA, const float4 xB, const bool vY,
                                               const float4 yA, const float4 yB) {
@@ -803,7 +804,7 @@ __device__ __forceinline__ Cell backward_math(const WReg& WR, const int flags, c
   a.v[2] = W[2][0] * dest + W[2][1] * dmd + W[2][2] * ddm + sE * W[2][5];
   a.v[3] = W[3][0] * dest + W[3][1] * dmd + W[3][4] * diw + W[3][3] * dmi + sE * W[3][5];
   a.v[4] = W[4][0] * dest + W[4][4] * diw + W[4][2] * ddm + sE * W[4][5];
-  cell_normalise(a);
+  if (NORMALISE) cell_normalise(a);
   return a;
 }
 
@@ -1171,6 +1172,18 @@ __device__ __forceinline__ void load_row(float4 (&h)[K4], const float* __restric
                  : "l"(g + k), "r"((int)pred));
 }
 
+// cell_normalise without a branch and with one scale factor: 2^-k is representable for every k a normal maximum can
+// have here (k = 127 would need a cell value >= 2^127; predecessors are normalised to [1,2) and weights are <= 1).
+__device__ __forceinline__ void cell_normalise_nb(Cell& a, bool ok) {
+  const float m = fmaxf(fmaxf(fmaxf(a.v[0], a.v[1]), fmaxf(a.v[2], a.v[3])), a.v[4]);
+  const int k = ((__float_as_int(m) >> 23) & 0xff) - 127;  // floor(log2 m) for normal m; -127 for 0
+  const float s = __int_as_float((127 - k) << 23);
+  const bool live = ok && m > 0.f;
+#pragma unroll
+  for (int q = 0; q < 5; ++q) a.v[q] = live ? a.v[q] * s : 0.f;
+  a.E = live ? a.E + k : HB_EXP_ZERO;
+}
+
 // Forward cell of a chain x chain strip, branch-free (forward_math with the flag tests resolved: an x-move implies
 // that x emits, a y-move that y emits, and IMM is fed by the xy-move alone; forward.cpp:95-200).
 __device__ __forceinline__ Cell chain_forward_math(const WReg& WR, bool origin, int ex, int ey, float rsx, float insx, float rsy, float insy,
@@ -1191,7 +1204,6 @@ __device__ __forceinline__ Cell chain_forward_math(const WReg& WR, bool origin, 
   a.v[3] = sY * insy * (yA.x * W[0][3] + yA.w * W[3][3]);
   const float imm = sD * ab * (dA.x * W[0][0] + dA.y * W[1][0] + dA.z * W[2][0] + dA.w * W[3][0] + dB.x * W[4][0]);
   a.v[0] = origin ? 1.f : imm;   // lpStart() = 0 at (0,0) (forward.cpp:73): no predecessor, exponent 0
-  cell_normalise(a);
   return a;
 }
 
@@ -1286,11 +1298,13 @@ __device__ __forceinline__ void consumer_chain(const PairDev& P) {
       const int4 r1 = make_int4(rx.x + ry.x, rx.x, ry.x, i);
       const int4 r2 = make_int4(__float_as_int(1.f), rx.y, rx.z, 0);
       const int4 r3 = make_int4(ry.y, ry.z, 0, __float_as_int(1.f));
-      c = backward_math(WR, xLast && yLast ? R_TO_END : 0, r1, r2, r3, vD, dA, dB, vX, xA, xB, vY, yA, yB);
+      c = backward_math<false>(WR, xLast && yLast ? R_TO_END : 0, r1, r2, r3, vD, dA, dB, vX, xA, xB, vY, yA, yB);
     }
-    if (!ok) c = zero_cell();
+    cell_normalise_nb(c, ok);
     const float4 va = make_float4(c.v[0], c.v[1], c.v[2], c.v[3]);
-    if (t < di.width + 2) {
+    // (di.pad is 0: using it keeps the fourth register of the early layout load alive until here; dead, the compiler
+    // reuses it as a scratch register and every write to it waits for the load issued three steps ahead)
+    if (t < di.width + 2 + di.pad) {
       __stcs(gA + di.off + t, va);
       __stcs(gB + di.off + t, make_float2(c.v[4], __int_as_float(c.E)));
     }
