@@ -37,20 +37,25 @@ BAND = 20
 BRANCH = 0.05
 N_LEAVES = 1024
 ROOT_LEN = 1000
-# dram__bytes_read.sum + dram__bytes_write.sum of the three fill kernels per launch, from the ncu --set full capture under profiles/ (None = not captured)
+# dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel per launch, from the ncu --set full capture under profiles/ (None = not captured)
 EM_TRAFFIC_BYTES = 5.78e9     # profiles/r01_sumprod_ncu_details_final.txt: sumprod_columns_kernel 3.68 GB read + 2.10 GB written per launch (default EM family)
-FILL_TRAFFIC_BYTES = 7.44e9   # profiles/r01_fill_ncu_details_final.txt: absorb 0.17 + build_records 3.21 + fill_stream 4.06 GB
+FILL_TRAFFIC_BYTES = 1.36e9   # profiles/r02_fill_chain_ncu_details.txt: fill_chain_kernel<5> 0.33 GB read + 1.04 GB written per launch (default family)
+# FP32 work of one cell update in the chain kernel: K-term absorb dot product (K FMA) + 24 FMA/FMUL of the five state sums
+# + 9 scale/emission multiplies + 5 normalisation multiplies, FMA counted as 2 flop
+FILL_FLOP_PER_CELL = 2 * 20 + 2 * 24 + 9 + 5
 ALG_BYTES_PER_CELL = 80.0   # 40 B written once + 40 B read once per DP cell (reference layout)
 METRIC = "profile Forward/Backward cells/s (GCUPS)"
 UNIT = "Gcells/s"
 
 
-def make_family(seed):
+def make_family(seed, n_leaves=N_LEAVES, with_tree=False):
     from historian_b200 import model as M, simulator as S
-    tree = S.Tree.balanced(N_LEAVES, BRANCH)
+    tree = S.Tree.balanced(n_leaves, BRANCH)
     lg = M.RateModel.preset("lg")
     gapped, _ = S.simulate_family(lg, tree, ROOT_LEN, seed)
-    _, guide = S.leaf_guide(tree, gapped)
+    leaves, guide = S.leaf_guide(tree, gapped)
+    if with_tree:
+        return lg, guide, tree, leaves
     return lg, guide
 
 
@@ -141,7 +146,10 @@ def run_ref_time(fasta, first, count, procs):
     for j in jobs:
         if j.returncode != 0:
             raise RuntimeError("ref_time failed")
-    return 2 * sum(o["cells"] for o in outs), wall, outs
+    # the time inside the reference's ForwardMatrix + BackwardMatrix constructors (the processes run side by side: the
+    # slowest one bounds the set); process start, FASTA parsing and the cell-counting loop of ref_time are left out
+    busy = max(o["fwd_s"] + o["bwd_s"] for o in outs)
+    return 2 * sum(o["cells"] for o in outs), busy, outs, wall
 
 
 def cpu_baseline(guide, sample_pairs, procs):
@@ -151,10 +159,11 @@ def cpu_baseline(guide, sample_pairs, procs):
     with tempfile.TemporaryDirectory() as tmp:
         fa = os.path.join(tmp, "leaves.fa")
         write_fasta(fa, guide[:2 * sample_pairs])
-        cells, wall, _ = run_ref_time(fa, 0, sample_pairs, procs)
-    return {"value": cells / wall / 1e9, "unit": UNIT, "cores": procs, "kind": "reference",
+        cells, busy, _, wall = run_ref_time(fa, 0, sample_pairs, procs)
+    return {"value": cells / busy / 1e9, "unit": UNIT, "cores": procs, "kind": "reference",
             "sample": "%d of the 512 leaf x leaf merges (Forward+Backward, band %d), unmodified reference ForwardMatrix/BackwardMatrix "
-                      "via oracle/_ref/bin/ref_time, %d single-threaded process(es), %.1f s wall" % (sample_pairs, BAND, procs, wall)}
+                      "via oracle/_ref/bin/ref_time, %d single-threaded process(es), %.1f s inside the two constructors (%.1f s wall)"
+                      % (sample_pairs, BAND, procs, busy, wall)}
 
 
 def reference_arm(args):
@@ -175,21 +184,38 @@ def reference_arm(args):
             run_ref_time(fa, (w * per_step) % (512 - per_step + 1), per_step, cores)
         cells, wall = 0, 0.0
         for s in range(args.steps):
-            c, t, _ = run_ref_time(fa, (s * per_step) % (512 - per_step + 1), per_step, cores)
+            c, t, _, _ = run_ref_time(fa, (s * per_step) % (512 - per_step + 1), per_step, cores)
             cells += c
             wall += t
     v = cells / wall / 1e9
-    sample = "%d leaf x leaf merges per step (Forward+Backward, band %d) on %d single-threaded processes" % (per_step, BAND, cores)
+    sample = ("%d leaf x leaf merges per step (Forward+Backward, band %d) on %d single-threaded processes; time = the slowest process's "
+              "seconds inside the ForwardMatrix + BackwardMatrix constructors" % (per_step, BAND, cores))
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * wall / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-        "data": "synthetic", "config": workload_config(512),
+        "data": "synthetic", "config": workload_config(per_step),
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}))
 
 
+def fp32_roofline(cells_per_launch, per_launch_s):
+    """The fill against the FP32 issue peak measured on this box (tools/microbench/peaks.cu, profiles/r02_peaks_microbench.json):
+    SURVEY.md 8(d) names FP32/SFU issue, not HBM, as the binding roofline of the fills.  The cells hold linear-space
+    mantissas, so there is no transcendental in the inner loop (MUFU is idle by design)."""
+    peak = 69.8
+    try:
+        peak = float(json.load(open(os.path.join(ROOT, "profiles", "r02_peaks_microbench.json")))["fp32_fma_tflops"])
+    except Exception:
+        pass
+    ach = cells_per_launch * FILL_FLOP_PER_CELL / per_launch_s / 1e12
+    return {"achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak, "flop_per_cell": FILL_FLOP_PER_CELL,
+            "note": "one warp per strip walks 2000 dependent anti-diagonals: the kernel is bound by dependent-issue latency "
+                    "(ncu: IPC 1.3 of 4, 0.36 eligible warps per scheduler), not by FP32 throughput"}
+
+
 def workload_config(pairs):
-    return {"workload": "lg_1024x1000_seed1 level-0 sibling merges (leaf x leaf), Forward+Backward fill, guide band %d" % BAND,
+    return {"workload": "lg_1024x1000_seed1, LEAF LEVEL ONLY: the level-0 sibling merges (leaf x leaf), Forward+Backward fill, guide band %d "
+                        "(the whole tree, all levels, is the `recon` record)" % BAND,
             "family": "LG, %d leaves x %d root residues, balanced tree, branch %.2f, insrate=delrate=0.01" % (N_LEAVES, ROOT_LEN, BRANCH),
             "merges_per_step_per_gpu": pairs, "band": BAND, "alphabet": 20, "components": 1,
             "l2_policy": "cell planes written per step (>1 GB) exceed the 126 MB L2; no reuse between steps"}
@@ -321,6 +347,115 @@ def em_leg(ctx, args, rank, world, local, barrier):
     return out
 
 
+
+# ------------------------------------------------------------------ reconstruction leg (BASELINE.json metric 2, configs[2])
+REF_BIN = os.path.join(ROOT, "oracle", "_ref", "bin", "historian")
+RECON_REF_LEAVES = 64
+
+
+def _family_inputs(tree, leaves, guide):
+    seqs = {v: bytes(row[row != ord("-")]).decode() for v, row in zip(leaves, guide)}
+    grows = {v: row != ord("-") for v, row in zip(leaves, guide)}
+    return seqs, grows
+
+
+def _reference_recon(tree, leaves, guide, extra):
+    """Wall seconds and FASTA rows of the unmodified reference binary (one core: it has no threads) on a family."""
+    with tempfile.TemporaryDirectory() as tmp:
+        tf, gf = os.path.join(tmp, "tree.nh"), os.path.join(tmp, "guide.fa")
+        open(tf, "w").write(tree.newick())
+        with open(gf, "w") as f:
+            for v, row in zip(leaves, guide):
+                f.write(">%s\n%s\n" % (tree.names[v], bytes(row).decode()))
+        t0 = time.perf_counter()
+        out = subprocess.run([REF_BIN, "recon", "-guide", gf, "-tree", tf, "-preset", "lg", "-output", "fasta", "-norefine", "-band", str(BAND)] + extra,
+                             stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, check=True, cwd=tmp).stdout.decode()
+        wall = time.perf_counter() - t0
+    rows = []
+    for line in out.splitlines():
+        if line.startswith(">"):
+            rows.append("")
+        elif rows:
+            rows[-1] += line.strip()
+    return wall, rows
+
+
+def recon_leg(ctx, args, rank, world, local, barrier):
+    """recon wall-time: the whole progressive reconstruction (every level: DPMatrix constructors, Forward fills, traces,
+    makeProfile, parent profiles kept on the device; recon.cpp:917-1052) of the 1024 x 1000 LG family, band 20,
+    deterministic profiles (-profmaxstates 1).  N GPUs: ONE family, its sibling merges spread over the ranks
+    (historian_b200.recon.plan_owners), profiles moved between ranks with NCCL send/recv: strong scaling.  At N = 1 also
+    the sampled-profile mode (-profsamples 10 -profmaxstates 5000) and the reference binary, both on a 64-leaf family."""
+    import torch
+    import torch.distributed as dist
+    from historian_b200 import recon as R
+    dev = torch.device("cuda", local)
+    lg, guide, tree, leaves = make_family(args.family_seed, with_tree=True)
+    seqs, grows = _family_inputs(tree, leaves, guide)
+    owner = R.plan_owners(tree, world)
+    root_rank = int(owner[tree.root])
+    walls, bits, lp, stage = [], None, None, None
+    for rep in range(1 + args.recon_reps):      # the first run is the warm-up
+        nat = R.NativeReconstructor(ctx, lg, band=BAND, max_profile_states=1)
+        barrier()
+        t0 = time.perf_counter()
+        b, l, rec = R.reconstruct_partitioned(nat, tree, seqs, grows, rank, world, dist, dev)
+        barrier()
+        wall = time.perf_counter() - t0
+        if rep:
+            walls.append(wall)
+        if rank == root_rank:
+            bits, lp, stage = b, l, nat.stage_ms
+        rec.close()
+    t = torch.tensor([min(walls)], dtype=torch.float64, device=dev)
+    flag = torch.tensor([1.0 if rank == root_rank else 0.0, float(bits.shape[1]) if bits is not None else 0.0, lp if lp is not None else 0.0],
+                        dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(flag)      # only the root's rank contributes columns and likelihood
+    out = None
+    if rank == 0:
+        levels = R.merge_levels(tree)
+        moves = sum(len(R.level_moves(tree, lv, owner)) for lv in levels)
+        out = {"metric": "recon wall-time", "value": t.item(), "unit": "s", "higher_is_better": False, "scaling": "strong", "n_gpus": world,
+               "config": {"workload": "lg_1024x1000_seed%d whole-tree progressive reconstruction: %d merges on %d levels, band %d, -profmaxstates 1"
+                                      % (args.family_seed, tree.n_nodes - len(leaves), len(levels), BAND),
+                          "parallelism": "sibling merges of a level spread over %d GPU(s); %d profile(s) cross ranks (NCCL send/recv); "
+                                         "levels with fewer merges than GPUs leave ranks idle (the last %d levels)" % (
+                                             world, moves, sum(1 for lv in levels if len(lv) < world))},
+               "reps": args.recon_reps, "alignment_columns": int(flag[1].item()), "lp_final": flag[2].item()}
+        if world == 1:
+            out["stage_ms"] = {k: round(v, 2) for k, v in stage.items()}
+    if world == 1 and rank == 0:
+        # ---- a 64-leaf family: sampled profiles, and the reference binary on the same inputs
+        lg2, guide2, tree2, leaves2 = make_family(args.family_seed, n_leaves=RECON_REF_LEAVES, with_tree=True)
+        seqs2, grows2 = _family_inputs(tree2, leaves2, guide2)
+        small = {}
+        for name, kw, extra in (("deterministic", dict(max_profile_states=1), ["-profmaxstates", "1"]),
+                                ("sampled", dict(profile_samples=10, max_profile_states=5000, seed=1), ["-profsamples", "10", "-profmaxstates", "5000", "-seed", "1"])):
+            nat = R.NativeReconstructor(ctx, lg2, band=BAND, **kw)
+            nat.reconstruct(tree2, seqs2, grows2)[2].close()
+            nat = R.NativeReconstructor(ctx, lg2, band=BAND, **kw)
+            t0 = time.perf_counter()
+            b2, l2, rec2 = nat.reconstruct(tree2, seqs2, grows2)
+            w2 = time.perf_counter() - t0
+            rec2.close()
+            entry = {"ours_s": w2, "alignment_columns": int(b2.shape[1])}
+            if os.path.exists(REF_BIN) and (name == "deterministic" or args.recon_ref_sampled):
+                rw, rows = _reference_recon(tree2, leaves2, guide2, extra)
+                ours = R.gapped_rows_dense(b2, tree2, seqs2, wildcard="x")
+                same = len(rows) == tree2.n_nodes and all(ours[k] == r.lower() or ours[k] == r for k, r in enumerate(rows))
+                entry.update({"reference_s": rw, "identical_alignment": bool(same)})
+            small[name] = entry
+        out["family_%d_leaves" % RECON_REF_LEAVES] = small
+        det = small["deterministic"]
+        if "reference_s" in det:
+            out["cpu_baseline"] = {"value": det["reference_s"], "unit": "s", "cores": 1, "kind": "reference",
+                                   "sample": "oracle/_ref/bin/historian recon on the %d-leaf x %d family of the same model and tree shape (deterministic "
+                                             "profiles, band %d): %.2f s against %.3f s here, identical alignment: %s"
+                                             % (RECON_REF_LEAVES, ROOT_LEN, BAND, det["reference_s"], det["ours_s"], det["identical_alignment"])}
+    return out
+
 # ------------------------------------------------------------------ GPU arm
 def gpu_arm(args):
     import torch
@@ -445,7 +580,10 @@ def gpu_arm(args):
                     "host_memory": "residue strings and band descriptors in pageable host memory, staged through the context's pinned buffer"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": FILL_TRAFFIC_BYTES, "kernel": "hb::absorb_kernel + hb::build_records_kernel + hb::fill_stream_kernel (one batched Forward+Backward fill call; events bracket all three)", "launches_timed": int(kernel_launches),
+                         "traffic": FILL_TRAFFIC_BYTES if n_pairs == 512 and args.family_seed == 1 else None,
+                         "kernel": "hb::fill_chain_kernel<5> (one launch = the Forward and Backward fills of all merges of the step; absorb dot products inside)",
+                         "launches_timed": int(kernel_launches),
+                         "fp32": fp32_roofline(cells_per_step, per_launch_s),
                          "avg_launch_ms": 1e3 * per_launch_s, "algorithmic_bytes_per_cell": ALG_BYTES_PER_CELL,
                          "cells_per_launch": int(cells_per_step),
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"},
@@ -454,9 +592,14 @@ def gpu_arm(args):
     em_line = None
     if not args.no_em:
         em_line = em_leg(ctx, args, rank, world, local, barrier)
+    recon_line = None
+    if not args.no_recon:
+        recon_line = recon_leg(ctx, args, rank, world, local, barrier)
     if rank == 0:
         if em_line is not None:
             line["em_counts"] = em_line
+        if recon_line is not None:
+            line["recon"] = recon_line
         print(json.dumps(line))
     ctx.close()
     if world > 1:
@@ -479,6 +622,9 @@ def main():
     ap.add_argument("--cpu-cols", type=int, default=64, help="columns in the EM leg's cpu_baseline sample")
     ap.add_argument("--family-seed", type=int, default=1, help="simulation seed of rank 0's family (rank r uses seed + r)")
     ap.add_argument("--no-em", action="store_true", help="skip the EM count leg (profiling runs)")
+    ap.add_argument("--no-recon", action="store_true", help="skip the whole-tree reconstruction leg")
+    ap.add_argument("--recon-reps", type=int, default=3, help="timed repetitions of the whole-tree reconstruction (best is reported)")
+    ap.add_argument("--recon-ref-sampled", action="store_true", help="also time the reference binary in sampled mode on the 64-leaf family (minutes)")
     args = ap.parse_args()
     if args.impl == "reference":
         reference_arm(args)

@@ -1257,6 +1257,17 @@ __device__ __forceinline__ void consumer_chain(const PairDev& P) {
       asm volatile("" : "+f"(a0), "+f"(a1));
       if (cur.ok && xEmit && yEmit && hi == i && hj == j) ab = a0 + a1;
     }
+    // ---- far ahead: pull the layout records, state records and emission rows the sweep will reach in ~24 steps into L1
+    // (they come from HBM the first time; the loads below are then L1 hits instead of waiting out a DRAM round trip)
+    if ((q & 3) == 0) {
+      const int far = BWD ? -1 : 1;
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(P.dinfo + diag_of(q + 32 + (t & 3) * 8)));
+      const int fi = min(max(i + far * 14, 0), nx - 1), fj = min(max(j + far * 14, 0), ny - 1);
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(recx + fi));
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(recy + fj));
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(Hx + (size_t)fi * Kp));
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(Hy + (size_t)fj * Kp));
+    }
     // ---- requests for the next step (nothing here depends on DP values): at most one row changes for a main-interval lane
     const ChainPos nxt = chain_pos(n0, diag_of(q + 1), t, nx, ny);
     const int4 rxn = __ldg(recx + nxt.i), ryn = __ldg(recy + nxt.j);
