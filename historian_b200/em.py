@@ -123,3 +123,134 @@ class ColumnCounter:
         buf = count_sharded(compute, len(columns), rank, world, all_reduce)
         self.ctx.synchronize()
         return buf.cpu().numpy()
+
+
+# ------------------------------------------------------------------ M-step and the EM loop (historian fit)
+class EventCounts:
+    """EventCounts (model.h): indel counts (ins, del, insExt, delExt, insTime, delTime, lp), rootCount [C][A] and
+    subCount [C][A][A] (diagonal = wait time), as EigenCounts::transform returns them (model.cpp:924-931)."""
+
+    def __init__(self, indel, root, sub):
+        self.indel = np.array(indel, float)
+        self.root = np.array(root, float)
+        self.sub = np.array(sub, float)
+
+    @property
+    def lp(self):
+        return float(self.indel[6])
+
+    def __add__(self, other):
+        return EventCounts(self.indel + other.indel, self.root + other.root, self.sub + other.sub)
+
+    def optimize(self, model, fit_indel_rates=True, fit_subst_rates=True):
+        """EventCounts::optimize (model.cpp:1022-1059): the closed-form M-step, in place on a model.RateModel."""
+        C, A = self.root.shape
+        if fit_subst_rates:
+            cpt_count = []
+            for c in range(C):
+                ins_norm = self.root[c].sum()
+                model.insProb[c] = self.root[c] / ins_norm
+                r = np.zeros((A, A))
+                for i in range(A):
+                    for j in range(A):
+                        if j != i:
+                            r[i, j] = self.sub[c][i][j] / self.sub[c][i][i]
+                    r[i, i] = -(r[i].sum() - r[i, i])
+                model.subRate[c] = r
+                cpt_count.append(ins_norm)
+            tot = float(sum(cpt_count))
+            model.cptWeight = [float(x) / tot for x in cpt_count]
+        if fit_indel_rates:
+            ins, dele, ins_ext, del_ext, ins_time, del_time = self.indel[:6]
+            model.insRate = ins / ins_time
+            model.delRate = dele / del_time
+            model.insExtProb = ins_ext / (ins_ext + ins)
+            model.delExtProb = del_ext / (del_ext + dele)
+        return model
+
+    def expected_log_likelihood(self, model):
+        """EventCounts::expectedLogLikelihood (model.cpp:1083-1104)."""
+        def xlogy(x, y):
+            return 0.0 if x == 0 else x * math.log(y)
+        ins, dele, ins_ext, del_ext, ins_time, del_time = self.indel[:6]
+        lp = (-model.insRate * ins_time + xlogy(ins, model.insRate) - model.delRate * del_time + xlogy(dele, model.delRate)
+              + xlogy(ins_ext, model.insExtProb) + xlogy(ins, 1 - model.insExtProb)
+              + xlogy(del_ext, model.delExtProb) + xlogy(dele, 1 - model.delExtProb))
+        C, A = self.root.shape
+        for c in range(C):
+            sr = np.asarray(model.subRate[c])
+            for i in range(A):
+                lp += xlogy(self.root[c][i], model.insProb[c][i]) - (-sr[i, i]) * self.sub[c][i][i]
+                for j in range(A):
+                    if i != j:
+                        lp += xlogy(self.sub[c][i][j], sr[i, j])
+        return lp
+
+
+def laplace_prior(components, alph_size):
+    """The default prior of `historian fit` (recon.cpp:1277-1280): one pseudocount on every event count and wait time."""
+    return EventCounts([1, 1, 1, 1, 1, 1, 0], np.ones((components, alph_size)), np.ones((components, alph_size, alph_size)))
+
+
+def log_prior(prior, model, fit_indel_rates=True, fit_subst_rates=True):
+    """EventCounts::logPrior (model.cpp:1060-1078) with logGammaPdf / logBetaPdf / logDirichletPdf (logsumexp.cpp:101-115)."""
+    from scipy import stats
+    lp = 0.0
+    ins, dele, ins_ext, del_ext, ins_time, del_time = prior.indel[:6]
+    if fit_indel_rates:
+        lp += stats.gamma.logpdf(model.insRate, ins + 1, scale=1.0 / ins_time) + stats.gamma.logpdf(model.delRate, dele + 1, scale=1.0 / del_time)
+        lp += stats.beta.logpdf(model.insExtProb, ins_ext + 1, ins + 1) + stats.beta.logpdf(model.delExtProb, del_ext + 1, dele + 1)
+    if fit_subst_rates:
+        C, A = prior.root.shape
+        for c in range(C):
+            p = np.asarray(model.insProb[c], float)
+            lp += stats.dirichlet.logpdf(p / p.sum(), prior.root[c] + 1)
+            sr = np.asarray(model.subRate[c])
+            for i in range(A):
+                for j in range(A):
+                    if i != j:
+                        lp += stats.gamma.logpdf(sr[i, j], prior.sub[c][i][j] + 1, scale=1.0 / prior.sub[c][i][i])
+    return float(lp)
+
+
+def count_alignment(ctx, model, tree, columns, rank=0, world=1, fit_indel_rates=True, fit_subst_rates=True):
+    """Reconstructor::count (recon.cpp:1284-1291) for one reconstructed alignment: EigenCounts::accumulateCounts
+    (model.cpp:917-922) -- substitution counts on the device, columns sharded over the ranks with one all-reduce;
+    indel counts by branch on the host -- then EigenCounts::transform.  tree: descs.TreeTopology."""
+    from . import descs as D
+    spm = D.SumProdModel.from_rate_model(model)
+    cc = ColumnCounter(ctx, spm, tree)
+    try:
+        if fit_subst_rates:
+            counts = cc.count(columns, rank, world)
+        else:
+            counts = np.zeros(cc.sp.counts_size)
+        if fit_indel_rates:
+            counts[:7] += indel_counts(columns, tree.parent, tree.branch_length, model.insRate, model.delRate, model.insExtProb, model.delExtProb)
+        root, sub = cc.sp.transform_counts(counts)
+    finally:
+        cc.close()
+    return EventCounts(counts[:7], root, sub)
+
+
+def fit(ctx, model, tree, columns, max_iter=100, min_improvement=1e-3, rank=0, world=1, fit_indel_rates=True, fit_subst_rates=True,
+        prior="laplace", counter=None, log=None):
+    """Reconstructor::fit (recon.cpp:1385-1408) on one reconstructed alignment: E-step (count), stop when log-likelihood +
+    log-prior improves by less than min_improvement (relative), else the closed-form M-step on data + prior counts.
+    prior: "laplace" (the reference's default pseudocounts), None (-nolaplace) or an EventCounts.
+    `counter(model) -> EventCounts` replaces the device E-step (tests run the loop against the CPU oracle).
+    Returns (model, [(log-likelihood, log-prior) per iteration])."""
+    if isinstance(prior, str):
+        prior = laplace_prior(model.components, model.alphabetSize)
+    lp_last, lps = -math.inf, []
+    for it in range(max_iter):
+        ev = counter(model) if counter is not None else count_alignment(ctx, model, tree, columns, rank, world, fit_indel_rates, fit_subst_rates)
+        lp_prior = log_prior(prior, model, fit_indel_rates, fit_subst_rates) if prior is not None else 0.0
+        lps.append((ev.lp, lp_prior))
+        if log is not None:
+            log("EM iteration #%d: log-likelihood (%.6f) + log-prior (%.6f) = %g" % (it + 1, ev.lp, lp_prior, ev.lp + lp_prior))
+        if ev.lp + lp_prior <= lp_last + abs(lp_last) * min_improvement:
+            break
+        (ev + prior if prior is not None else ev).optimize(model, fit_indel_rates, fit_subst_rates)
+        lp_last = ev.lp + lp_prior
+    return model, lps
