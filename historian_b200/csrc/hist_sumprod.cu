@@ -551,6 +551,299 @@ __global__ void __launch_bounds__(SP_THREADS) sumprod_columns_kernel(SpDev S, Sp
   }
 }
 
+
+// ------------------------------------------------------------------ dense columns: node-major, level-synchronous
+// A column in which most of the tree is ungapped (an alignment column that descends from the root sequence) costs
+// a whole-tree pruning pass, and the one-block-per-column kernel above walks its levels with 256 threads whose every
+// message is a dependent L2 access: ~3.7 ms per 8191-node column however many SMs are idle.  The dense columns of a
+// batch are therefore taken out and processed TOGETHER, node-major: messages are laid out [node][component][residue]
+// [column] so that the threads of a warp work on 32 columns of the same node and every load and store is coalesced;
+// one launch per tree level (deepest first for fillUp, root first for fillDown) over all dense columns, then one
+// count launch whose threads keep the A x A eigen-count accumulators of one (component, column) in registers over a
+// chunk of nodes and reduce over columns per block.  Same arithmetic, same operation order inside a message as above.
+// Alphabets up to 8 residues (the accumulators live in registers); larger alphabets keep the kernel above.
+#define DN_COLS 128     // columns per block (thread = column)
+#define DN_NODES 64     // nodes per block of the count kernel
+#define DN_MAXA 8
+
+struct DnArgs {
+  const char* columns;     // [n_cols][N]
+  const int* order;        // dense column b is columns[order[b]]
+  const double* weights;   // indexed by original column, or NULL
+  int nb;                  // dense columns in this batch (= stride of the column axis)
+  signed char* tok;        // [N][nb]
+  double* E; double* F; double* G;        // [N][C][A][nb]
+  double* logE; double* logF; double* logG; double* rootterm;   // [N][C][nb]
+  double* colll;           // [nb]
+  double* col_loglike;     // user output indexed by original column, or NULL
+  double* partials;        // [n_partials][counts_size]
+  int counts_size;
+  int* err;
+};
+
+__global__ void dn_init_kernel(SpDev S, DnArgs a) {
+  const int col = blockIdx.x * blockDim.x + threadIdx.x, node = blockIdx.y;
+  if (col >= a.nb) return;
+  const unsigned char ch = (unsigned char)a.columns[(size_t)a.order[col] * S.N + S.orig[node]];
+  signed char tk;
+  if (ch == '-' || ch == '.') tk = SP_TOK_GAP;
+  else tk = ch == '*' ? SP_TOK_WILD : S.tokmap[ch];
+  a.tok[(size_t)node * a.nb + col] = tk;
+}
+
+// fillUp of one level (sumprod.cpp:99-161): thread = (column, node of the level, component)
+__global__ void __launch_bounds__(DN_COLS) dn_up_kernel(SpDev S, DnArgs a, int lev) {
+  const int col = blockIdx.x * blockDim.x + threadIdx.x;
+  if (col >= a.nb) return;
+  const int A = S.A, C = S.C, nb = a.nb;
+  const int node = S.lvl_off[lev] + blockIdx.y, c = blockIdx.z;
+  const size_t nc = (size_t)node * C + c;
+  const int tk = a.tok[(size_t)node * nb + col];
+  if (tk == SP_TOK_GAP) {
+    a.rootterm[nc * nb + col] = 0;
+    return;
+  }
+  const int k0 = S.kid_off[node], k1 = S.kid_off[node + 1];
+  double lF = 0;
+  for (int k = k0; k < k1; ++k) {
+    const int kid = S.kid_idx[k];
+    if (a.tok[(size_t)kid * nb + col] != SP_TOK_GAP) lF += a.logE[((size_t)kid * C + c) * nb + col];
+  }
+  double* Fn = a.F + nc * A * nb + col;   // Fn[i * nb]
+  if (tk == SP_TOK_WILD) {
+    double Fmax = 0;
+    for (int i = 0; i < A; ++i) {
+      double Fi = 1;
+      for (int k = k0; k < k1; ++k) {
+        const int kid = S.kid_idx[k];
+        if (a.tok[(size_t)kid * nb + col] != SP_TOK_GAP) Fi *= a.E[(((size_t)kid * C + c) * A + i) * nb + col];
+      }
+      Fn[(size_t)i * nb] = Fi;
+      if (Fi > Fmax) Fmax = Fi;
+    }
+    if (Fmax < SP_RESCALE) {
+      for (int i = 0; i < A; ++i) Fn[(size_t)i * nb] /= Fmax;
+      lF += log(Fmax);
+    }
+  } else {
+    double Ftok = 1;
+    for (int k = k0; k < k1; ++k) {
+      const int kid = S.kid_idx[k];
+      if (a.tok[(size_t)kid * nb + col] != SP_TOK_GAP) Ftok *= a.E[(((size_t)kid * C + c) * A + tk) * nb + col];
+    }
+    if (Ftok < SP_RESCALE) {
+      lF += log(Ftok);
+      Ftok = 1;
+    }
+    for (int i = 0; i < A; ++i) Fn[(size_t)i * nb] = i == tk ? Ftok : 0;
+  }
+  const int p = S.parent[node];
+  const bool is_root = p < 0 || a.tok[(size_t)p * nb + col] == SP_TOK_GAP;
+  double rterm = 0;
+  if (is_root) {
+    double ip = 0;
+    for (int i = 0; i < A; ++i) ip += Fn[(size_t)i * nb] * S.ins[c * A + i];
+    rterm = lF + log(ip);
+    a.logE[nc * nb + col] = 0;
+  } else {
+    a.logE[nc * nb + col] = lF;
+    // E = P F
+    const double* Pt = S.PT + nc * A * A;  // Pt[j * A + i] = P(i -> j)
+    double* En = a.E + nc * A * nb + col;
+    for (int i = 0; i < A; ++i) {
+      double Ei;
+      if (tk >= 0) Ei = Pt[tk * A + i] * Fn[(size_t)tk * nb];
+      else {
+        Ei = 0;
+        for (int j = 0; j < A; ++j) Ei += Pt[j * A + i] * Fn[(size_t)j * nb];
+      }
+      En[(size_t)i * nb] = Ei;
+    }
+  }
+  a.rootterm[nc * nb + col] = rterm;
+  a.logF[nc * nb + col] = lF;
+}
+
+// column log-likelihoods, the root's counts and the likelihood term of the count buffer: thread = column
+__global__ void __launch_bounds__(DN_COLS) dn_root_kernel(SpDev S, DnArgs a, int want_counts, int first_partial) {
+  const int col = blockIdx.x * blockDim.x + threadIdx.x;
+  if (col >= a.nb) return;
+  const int A = S.A, C = S.C, N = S.N, CA = C * A, nb = a.nb;
+  double cpt[4];
+  int n_roots = 0, root = -1;
+  for (int c = 0; c < C; ++c) cpt[c] = 0;
+  for (int node = 0; node < N; ++node) {
+    if (a.tok[(size_t)node * nb + col] == SP_TOK_GAP) continue;
+    const int p = S.parent[node];
+    if (p < 0 || a.tok[(size_t)p * nb + col] == SP_TOK_GAP) { ++n_roots; root = node; }
+    for (int c = 0; c < C; ++c) cpt[c] += a.rootterm[((size_t)node * C + c) * nb + col];
+  }
+  double ll = -INFINITY;
+  for (int c = 0; c < C; ++c) ll = lse2_exact(ll, S.logcw[c] + cpt[c]);
+  a.colll[col] = ll;
+  const int ocol = a.order[col];
+  if (a.col_loglike) a.col_loglike[ocol] = ll;
+  if (!want_counts) return;
+  double* out = a.partials + (size_t)(first_partial + col) * a.counts_size;
+  for (int q = 0; q < a.counts_size; ++q) out[q] = 0;
+  if (n_roots != 1) {  // assertSingleRoot
+    if (root >= 0) atomicExch(a.err, 1);
+    return;
+  }
+  const double weight = a.weights ? a.weights[ocol] : 1.0;
+  out[6] = ll;
+  for (int q = 0; q < CA; ++q) {
+    const int c = q / A;
+    const double norm = exp(S.logcw[c] + a.logF[((size_t)root * C + c) * nb + col] - ll);
+    out[7 + q] = weight * S.ins[q] * a.F[((size_t)root * CA + q) * nb + col] * norm;
+  }
+}
+
+// fillDown of one level (sumprod.cpp:163-198): thread = (column, node of the level, component)
+__global__ void __launch_bounds__(DN_COLS) dn_down_kernel(SpDev S, DnArgs a, int lev) {
+  const int col = blockIdx.x * blockDim.x + threadIdx.x;
+  if (col >= a.nb) return;
+  const int A = S.A, C = S.C, nb = a.nb;
+  const int node = S.lvl_off[lev] + blockIdx.y, c = blockIdx.z;
+  if (a.tok[(size_t)node * nb + col] == SP_TOK_GAP) return;
+  const size_t nc = (size_t)node * C + c;
+  const int p = S.parent[node];
+  double* Gn = a.G + nc * A * nb + col;
+  if (p < 0 || a.tok[(size_t)p * nb + col] == SP_TOK_GAP) {
+    for (int j = 0; j < A; ++j) Gn[(size_t)j * nb] = S.ins[c * A + j];
+    a.logG[nc * nb + col] = 0;
+    return;
+  }
+  const int k0 = S.kid_off[p], k1 = S.kid_off[p + 1];
+  double lG = a.logG[((size_t)p * C + c) * nb + col];
+  for (int k = k0; k < k1; ++k) {
+    const int s = S.kid_idx[k];
+    if (s != node && a.tok[(size_t)s * nb + col] != SP_TOK_GAP) lG += a.logE[((size_t)s * C + c) * nb + col];
+  }
+  a.logG[nc * nb + col] = lG;
+  const double* Gp = a.G + ((size_t)p * C + c) * A * nb + col;
+  const double* Pn = S.P + nc * A * A;
+  for (int j = 0; j < A; ++j) {
+    double Gj = 0;
+    for (int i = 0; i < A; ++i) {
+      double pr = Gp[(size_t)i * nb] * Pn[i * A + j];   // the reference's order: G_p[i] * P, then the siblings
+      for (int k = k0; k < k1; ++k) {
+        const int s = S.kid_idx[k];
+        if (s != node && a.tok[(size_t)s * nb + col] != SP_TOK_GAP) pr *= a.E[(((size_t)s * C + c) * A + i) * nb + col];
+      }
+      Gj += pr;
+    }
+    Gn[(size_t)j * nb] = Gj;
+  }
+}
+
+// accumulateEigenCounts (sumprod.cpp:294-372): block = DN_COLS columns x DN_NODES nodes x one component; every thread
+// accumulates its column's A x A complex contributions over the block's nodes, then the block reduces over columns.
+template <int A>
+__global__ void __launch_bounds__(DN_COLS) dn_counts_kernel(SpDev S, DnArgs a, int first_partial) {
+  const int C = S.C, nb = a.nb, CA = C * A, CAA = CA * A;
+  const int col = blockIdx.x * blockDim.x + threadIdx.x, c = blockIdx.z;
+  const int n0 = blockIdx.y * DN_NODES, n1 = min(n0 + DN_NODES, S.N);
+  double2 acc[A * A];
+#pragma unroll
+  for (int q = 0; q < A * A; ++q) acc[q] = make_double2(0, 0);
+  if (col < nb) {
+    const double colLL = a.colll[col];
+    const double weight = a.weights ? a.weights[a.order[col]] : 1.0;
+    for (int node = n0; node < n1; ++node) {
+      if (a.tok[(size_t)node * nb + col] == SP_TOK_GAP) continue;
+      const int p = S.parent[node];
+      if (p < 0 || a.tok[(size_t)p * nb + col] == SP_TOK_GAP) continue;   // the column root
+      const size_t nc = (size_t)node * C + c;
+      const int k0 = S.kid_off[p], k1 = S.kid_off[p + 1];
+      double U[A], D[A];
+      double maxU = -INFINITY, maxD = -INFINITY, lsib = 0;
+      for (int k = k0; k < k1; ++k) {
+        const int s = S.kid_idx[k];
+        if (s != node && a.tok[(size_t)s * nb + col] != SP_TOK_GAP) lsib += a.logE[((size_t)s * C + c) * nb + col];
+      }
+#pragma unroll
+      for (int i = 0; i < A; ++i) {
+        double d = a.G[(((size_t)p * C + c) * A + i) * nb + col];
+        for (int k = k0; k < k1; ++k) {
+          const int s = S.kid_idx[k];
+          if (s != node && a.tok[(size_t)s * nb + col] != SP_TOK_GAP) d *= a.E[(((size_t)s * C + c) * A + i) * nb + col];
+        }
+        D[i] = d;
+        U[i] = a.F[(nc * A + i) * nb + col];
+        maxD = fmax(maxD, d);
+        maxU = fmax(maxU, U[i]);
+      }
+      const double norm = exp(colLL - S.logcw[c] - a.logF[nc * nb + col] - a.logG[((size_t)p * C + c) * nb + col] - lsib) / (maxU * maxD);
+      const double scale = weight / norm;
+#pragma unroll
+      for (int i = 0; i < A; ++i) {
+        U[i] = U[i] / maxU;
+        D[i] = D[i] / maxD;
+      }
+      double2 ub[A], db[A];
+#pragma unroll
+      for (int k = 0; k < A; ++k) {
+        double2 u = make_double2(0, 0), d = make_double2(0, 0);
+        if (S.is_real) {
+#pragma unroll
+          for (int b = 0; b < A; ++b) {
+            u.x += S.Vinv[((size_t)c * A + k) * A + b].x * U[b];
+            d.x += S.V[((size_t)c * A + b) * A + k].x * D[b];
+          }
+        } else {
+#pragma unroll
+          for (int b = 0; b < A; ++b) {
+            u = cadd(u, cscale(S.Vinv[((size_t)c * A + k) * A + b], U[b]));
+            d = cadd(d, cscale(S.V[((size_t)c * A + b) * A + k], D[b]));
+          }
+        }
+        ub[k] = u;
+        db[k] = d;
+      }
+#pragma unroll
+      for (int k = 0; k < A; ++k)
+#pragma unroll
+        for (int l = 0; l < A; ++l) {
+          const double2 esc = eigen_sub_count(S, node, c, k, l);
+          acc[k * A + l] = cadd(acc[k * A + l], cscale(cmul(db[k], cmul(esc, ub[l])), scale));
+        }
+    }
+  }
+  // ---- block reduction over the columns, fixed order: lanes by xor-shuffle, warps in order
+  __shared__ double2 s_part[DN_COLS / 32][A * A];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int q = 0; q < A * A; ++q) {
+    double2 v = acc[q];
+    for (int o = 16; o; o >>= 1) {
+      v.x += __shfl_xor_sync(0xffffffffu, v.x, o);
+      v.y += __shfl_xor_sync(0xffffffffu, v.y, o);
+    }
+    if (lane == 0) s_part[warp][q] = v;
+  }
+  __syncthreads();
+  const int part = first_partial + (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+  double* out = a.partials + (size_t)part * a.counts_size;
+  for (int q = threadIdx.x; q < a.counts_size; q += blockDim.x) out[q] = 0;
+  __syncthreads();
+  if (threadIdx.x < A * A) {
+    double2 v = make_double2(0, 0);
+    for (int w = 0; w < DN_COLS / 32; ++w) v = cadd(v, s_part[w][threadIdx.x]);
+    out[7 + CA + 2 * (c * A * A + threadIdx.x)] = v.x;
+    out[7 + CA + 2 * (c * A * A + threadIdx.x) + 1] = v.y;
+  }
+  (void)CAA;
+}
+
+// number of columns whose occupancy reaches `threshold` (they are the first entries of the occupancy order)
+__global__ void count_dense_kernel(const int* __restrict__ occ, int n_cols, int threshold, int* __restrict__ out) {
+  int n = 0;
+  for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < n_cols; c += gridDim.x * blockDim.x) n += occ[c] >= threshold;
+  for (int o = 16; o; o >>= 1) n += __shfl_down_sync(0xffffffffu, n, o);
+  if ((threadIdx.x & 31) == 0 && n) atomicAdd(out, n);
+}
+
 // counts[q] += sum over blocks, in block order
 __global__ void reduce_partials_kernel(const double* partials, int n_blocks, int counts_size, double* counts) {
   const int q = blockIdx.x * blockDim.x + threadIdx.x;
@@ -602,6 +895,11 @@ struct hist_sumprod {
   int chunk, n_slices;
   size_t smem;
   int max_blocks;
+  // dense (node-major) path
+  std::vector<int> lvl_off_h;   // host copy of the level ranges
+  char* dn_work = nullptr;      // workspace of a batch of dense columns
+  size_t dn_work_bytes = 0;
+  int* d_ndense = nullptr;
 };
 
 namespace {
@@ -805,6 +1103,7 @@ extern "C" int hist_sumprod_create(hist_ctx* ctx, const hist_model_desc* m, cons
   sp->chunk = chunk;
   sp->n_slices = n_slices;
   sp->smem = sp_smem_bytes(A, C, N, chunk, n_slices, n_levels);
+  sp->lvl_off_h = lvl_off;
   e = cudaFuncSetAttribute(sumprod_columns_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sp->smem);
   int per_sm = 1;
   if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sumprod_columns_kernel, SP_THREADS, sp->smem);
@@ -837,6 +1136,8 @@ extern "C" void hist_sumprod_destroy(hist_sumprod* sp) {
   cudaFree(sp->d_counts);
   cudaFree(sp->d_err);
   cudaFree(sp->d_order);
+  cudaFree(sp->dn_work);
+  cudaFree(sp->d_ndense);
   delete sp;
 }
 
@@ -889,7 +1190,15 @@ int run_columns(hist_sumprod* sp, const char* d_cols, const double* d_w, int64_t
     cudaEventRecord(e0, ctx->stream);
   }
   a.order = nullptr;
-  if (n_cols > blocks && n_cols < (1ll << 30)) {
+  // ---- dense columns first, node-major over the whole batch (see dn_* kernels); the rest goes to the column kernel
+  const int csz = a.counts_size;
+  int widest = 1;
+  for (size_t l = 0; l + 1 < sp->lvl_off_h.size(); ++l) widest = std::max(widest, sp->lvl_off_h[l + 1] - sp->lvl_off_h[l]);
+  static const int dense_min = getenv("HIST_B200_SP_DENSE_MIN") ? atoi(getenv("HIST_B200_SP_DENSE_MIN")) : 64;
+  const bool dense_ok = force_blocks == 0 && sp->A == 4 && sp->C <= 4 && !d_map && !d_post && widest <= 65535 && n_cols >= dense_min &&
+                        n_cols < (1ll << 30) && dense_min >= 0;
+  int64_t n_dense = 0;
+  if ((n_cols > blocks || dense_ok) && n_cols < (1ll << 30)) {
     if (sp->order_cap < n_cols) {
       cudaStreamSynchronize(ctx->stream);
       cudaFree(sp->d_order);
@@ -902,16 +1211,76 @@ int run_columns(hist_sumprod* sp, const char* d_cols, const double* d_w, int64_t
     column_order_kernel<<<1, 1024, 0, ctx->stream>>>(occ, (int)n_cols, sp->d_order);
     ctx->launches += 2;
     a.order = sp->d_order;
+    if (dense_ok) {
+      // the densest occupancy class (at least 2^floor(log2 N) ungapped rows) is a prefix of the order
+      int threshold = 1;
+      while (threshold * 2 <= sp->N) threshold *= 2;
+      if (!sp->d_ndense) HB_CUDA(ctx, cudaMalloc(&sp->d_ndense, sizeof(int)));
+      HB_CUDA(ctx, cudaMemsetAsync(sp->d_ndense, 0, sizeof(int), ctx->stream));
+      count_dense_kernel<<<64, 256, 0, ctx->stream>>>(occ, (int)n_cols, threshold, sp->d_ndense);
+      ctx->launches += 1;
+      int nd = 0;
+      HB_CUDA(ctx, cudaMemcpyAsync(&nd, sp->d_ndense, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+      HB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+      n_dense = nd >= dense_min ? nd : 0;
+    }
   }
-  sumprod_columns_kernel<<<blocks, SP_THREADS, sp->smem, ctx->stream>>>(sp->dev, a);
+  const bool want_partials = (flags & HIST_SP_COUNTS) && counts_dev;
+  for (int64_t b0 = 0; b0 < n_dense;) {
+    const int A = sp->A, C = sp->C, N = sp->N, CA = C * A;
+    const int nb = (int)std::min<int64_t>(n_dense - b0, 1024);
+    const size_t nbs = (size_t)nb;
+    const int col_blocks = (nb + DN_COLS - 1) / DN_COLS, node_blocks = (N + DN_NODES - 1) / DN_NODES;
+    const int n_part = want_partials ? col_blocks * node_blocks * C + nb : 0;
+    ArenaPlan plan;
+    const size_t o_tok = plan.add((size_t)N * nbs), o_E = plan.add(8 * (size_t)N * CA * nbs), o_F = plan.add(8 * (size_t)N * CA * nbs),
+                 o_G = plan.add(8 * (size_t)N * CA * nbs), o_lE = plan.add(8 * (size_t)N * C * nbs), o_lF = plan.add(8 * (size_t)N * C * nbs),
+                 o_lG = plan.add(8 * (size_t)N * C * nbs), o_rt = plan.add(8 * (size_t)N * C * nbs), o_ll = plan.add(8 * nbs),
+                 o_part = plan.add(8 * (size_t)std::max(1, n_part) * csz);
+    if (sp->dn_work_bytes < plan.bytes) {
+      cudaStreamSynchronize(ctx->stream);
+      cudaFree(sp->dn_work);
+      sp->dn_work = nullptr; sp->dn_work_bytes = 0;
+      HB_CUDA(ctx, cudaMalloc(&sp->dn_work, plan.bytes));
+      sp->dn_work_bytes = plan.bytes;
+    }
+    char* w = sp->dn_work;
+    DnArgs d;
+    d.columns = d_cols; d.order = sp->d_order + b0; d.weights = d_w; d.nb = nb;
+    d.tok = (signed char*)(w + o_tok);
+    d.E = (double*)(w + o_E); d.F = (double*)(w + o_F); d.G = (double*)(w + o_G);
+    d.logE = (double*)(w + o_lE); d.logF = (double*)(w + o_lF); d.logG = (double*)(w + o_lG); d.rootterm = (double*)(w + o_rt);
+    d.colll = (double*)(w + o_ll); d.col_loglike = d_ll; d.partials = (double*)(w + o_part); d.counts_size = csz; d.err = sp->d_err;
+    const int n_levels = (int)sp->lvl_off_h.size() - 1;
+    dn_init_kernel<<<dim3(col_blocks, N), DN_COLS, 0, ctx->stream>>>(sp->dev, d);
+    for (int lev = n_levels - 1; lev >= 0; --lev)
+      dn_up_kernel<<<dim3(col_blocks, sp->lvl_off_h[lev + 1] - sp->lvl_off_h[lev], C), DN_COLS, 0, ctx->stream>>>(sp->dev, d, lev);
+    dn_root_kernel<<<col_blocks, DN_COLS, 0, ctx->stream>>>(sp->dev, d, want_partials ? 1 : 0, col_blocks * node_blocks * C);
+    ctx->launches += 2 + n_levels;
+    if (want_partials) {
+      for (int lev = 0; lev < n_levels; ++lev)
+        dn_down_kernel<<<dim3(col_blocks, sp->lvl_off_h[lev + 1] - sp->lvl_off_h[lev], C), DN_COLS, 0, ctx->stream>>>(sp->dev, d, lev);
+      dn_counts_kernel<4><<<dim3(col_blocks, node_blocks, C), DN_COLS, 0, ctx->stream>>>(sp->dev, d, 0);
+      reduce_partials_kernel<<<(csz + 127) / 128, 128, 0, ctx->stream>>>(d.partials, n_part, csz, counts_dev);
+      ctx->launches += 2 + n_levels;
+    }
+    b0 += nb;
+  }
+  const int64_t n_rest = n_cols - n_dense;
+  if (n_rest > 0) {
+    if (a.order) a.order += n_dense;
+    a.n_cols = n_rest;
+    const int rblocks = (int)std::min<int64_t>(n_rest, blocks);
+    sumprod_columns_kernel<<<rblocks, SP_THREADS, sp->smem, ctx->stream>>>(sp->dev, a);
+    ctx->launches += 1;
+    if (a.partials) {
+      reduce_partials_kernel<<<(a.counts_size + 127) / 128, 128, 0, ctx->stream>>>(sp->partials, rblocks, a.counts_size, counts_dev);
+      ctx->launches += 1;
+    }
+  }
   if (ctx->timing) {
     cudaEventRecord(e1, ctx->stream);
     ctx->fill_events.push_back(std::make_pair(e0, e1));
-  }
-  ctx->launches += 1;
-  if (a.partials) {
-    reduce_partials_kernel<<<(a.counts_size + 127) / 128, 128, 0, ctx->stream>>>(sp->partials, blocks, a.counts_size, counts_dev);
-    ctx->launches += 1;
   }
   HB_CUDA(ctx, cudaGetLastError());
   return HIST_OK;

@@ -177,3 +177,44 @@ def test_multiple_roots_is_an_error_for_counts_but_not_for_likelihood(ctx):
     r = sp.columns(empty)
     assert np.all(r["counts"] == 0)
     sp.close()
+
+
+@pytest.mark.parametrize("path", [f for f in FIX if "dna12" in f], ids=[i for f, i in zip(FIX, IDS) if "dna12" in f])
+def test_dense_columns_node_major_path(ctx, path):
+    """A batch large enough for the node-major kernels (dn_*: the dense columns of the batch processed together, level
+    by level): counts and column likelihoods equal the oracle's, weights included, and equal the one-block-per-column
+    kernel's (the same columns in a batch too small to be routed there)."""
+    d, model, tree = load(path)
+    rng = np.random.default_rng(1)
+    cols = np.ascontiguousarray(np.tile(d["columns"], (12, 1)))
+    rng.shuffle(cols)
+    assert len(cols) >= 128
+    w = rng.uniform(0.5, 2.0, len(cols))
+    sp = ctx.sumprod(model, tree)
+    launches0 = ctx.launch_count
+    r = sp.columns(cols, weights=w, flags=capi.SP_COUNTS)
+    n_launches = ctx.launch_count - launches0
+    o = O.sumprod_columns(model, tree, cols, weights=w, flags=O.SP_COUNTS)
+    assert close(r["col_loglike"], o["col_loglike"], 0, 1e-10)
+    scale = np.abs(o["counts"][7:]).max()
+    assert np.all(np.abs(r["counts"] - o["counts"])[7:] <= 1e-9 * scale)
+    assert abs(r["counts"][6] - o["counts"][6]) <= 1e-9 * len(cols)
+    # one launch per tree level and pass: the batch really went through the level-synchronous kernels
+    depth = 0
+    p = np.asarray(d["parent"])
+    for v in range(len(p)):
+        k, q = 0, v
+        while p[q] >= 0:
+            q, k = p[q], k + 1
+        depth = max(depth, k + 1)
+    assert n_launches >= 2 * depth, (n_launches, depth)
+    # the same columns, a few at a time (column kernel only)
+    acc = np.zeros_like(r["counts"])
+    ll = []
+    for k0 in range(0, len(cols), 40):
+        part = sp.columns(cols[k0:k0 + 40], weights=w[k0:k0 + 40], flags=capi.SP_COUNTS)
+        acc += part["counts"]
+        ll.append(part["col_loglike"])
+    assert close(r["col_loglike"], np.concatenate(ll), 0, 1e-10)
+    assert np.all(np.abs(r["counts"] - acc)[7:] <= 1e-9 * scale)
+    sp.close()
