@@ -573,8 +573,11 @@ struct DnArgs {
   int nb;                  // dense columns in this batch (= stride of the column axis)
   signed char* tok;        // [N][nb]
   double* E; double* F; double* G;        // [N][C][A][nb]
-  double* logE; double* logF; double* logG; double* rootterm;   // [N][C][nb]
+  double* logE; double* logF; double* logG;   // [N][C][nb]
   double* colll;           // [nb]
+  double* cpt;             // [C][nb] sum of the root terms of each component (zeroed per batch)
+  int* n_roots;            // [nb] (zeroed per batch)
+  int* root_node;          // [nb] internal index of the (last) root (zeroed per batch)
   double* col_loglike;     // user output indexed by original column, or NULL
   double* partials;        // [n_partials][counts_size]
   int counts_size;
@@ -599,10 +602,7 @@ __global__ void __launch_bounds__(DN_COLS) dn_up_kernel(SpDev S, DnArgs a, int l
   const int node = S.lvl_off[lev] + blockIdx.y, c = blockIdx.z;
   const size_t nc = (size_t)node * C + c;
   const int tk = a.tok[(size_t)node * nb + col];
-  if (tk == SP_TOK_GAP) {
-    a.rootterm[nc * nb + col] = 0;
-    return;
-  }
+  if (tk == SP_TOK_GAP) return;
   const int k0 = S.kid_off[node], k1 = S.kid_off[node + 1];
   double lF = 0;
   for (int k = k0; k < k1; ++k) {
@@ -639,11 +639,15 @@ __global__ void __launch_bounds__(DN_COLS) dn_up_kernel(SpDev S, DnArgs a, int l
   }
   const int p = S.parent[node];
   const bool is_root = p < 0 || a.tok[(size_t)p * nb + col] == SP_TOK_GAP;
-  double rterm = 0;
   if (is_root) {
+    // a column has one root (several only where no counts are asked for: their terms are then summed in arrival order)
     double ip = 0;
     for (int i = 0; i < A; ++i) ip += Fn[(size_t)i * nb] * S.ins[c * A + i];
-    rterm = lF + log(ip);
+    atomicAdd(a.cpt + (size_t)c * nb + col, lF + log(ip));
+    if (c == 0) {
+      atomicAdd(a.n_roots + col, 1);
+      atomicMax(a.root_node + col, node);
+    }
     a.logE[nc * nb + col] = 0;
   } else {
     a.logE[nc * nb + col] = lF;
@@ -660,7 +664,6 @@ __global__ void __launch_bounds__(DN_COLS) dn_up_kernel(SpDev S, DnArgs a, int l
       En[(size_t)i * nb] = Ei;
     }
   }
-  a.rootterm[nc * nb + col] = rterm;
   a.logF[nc * nb + col] = lF;
 }
 
@@ -668,18 +671,10 @@ __global__ void __launch_bounds__(DN_COLS) dn_up_kernel(SpDev S, DnArgs a, int l
 __global__ void __launch_bounds__(DN_COLS) dn_root_kernel(SpDev S, DnArgs a, int want_counts, int first_partial) {
   const int col = blockIdx.x * blockDim.x + threadIdx.x;
   if (col >= a.nb) return;
-  const int A = S.A, C = S.C, N = S.N, CA = C * A, nb = a.nb;
-  double cpt[4];
-  int n_roots = 0, root = -1;
-  for (int c = 0; c < C; ++c) cpt[c] = 0;
-  for (int node = 0; node < N; ++node) {
-    if (a.tok[(size_t)node * nb + col] == SP_TOK_GAP) continue;
-    const int p = S.parent[node];
-    if (p < 0 || a.tok[(size_t)p * nb + col] == SP_TOK_GAP) { ++n_roots; root = node; }
-    for (int c = 0; c < C; ++c) cpt[c] += a.rootterm[((size_t)node * C + c) * nb + col];
-  }
+  const int A = S.A, C = S.C, CA = C * A, nb = a.nb;
+  const int n_roots = a.n_roots[col], root = n_roots ? a.root_node[col] : -1;
   double ll = -INFINITY;
-  for (int c = 0; c < C; ++c) ll = lse2_exact(ll, S.logcw[c] + cpt[c]);
+  for (int c = 0; c < C; ++c) ll = lse2_exact(ll, S.logcw[c] + a.cpt[(size_t)c * nb + col]);
   a.colll[col] = ll;
   const int ocol = a.order[col];
   if (a.col_loglike) a.col_loglike[ocol] = ll;
@@ -723,23 +718,34 @@ __global__ void __launch_bounds__(DN_COLS) dn_down_kernel(SpDev S, DnArgs a, int
   a.logG[nc * nb + col] = lG;
   const double* Gp = a.G + ((size_t)p * C + c) * A * nb + col;
   const double* Pn = S.P + nc * A * A;
+  // G_p[i] and the product of the siblings' E[i], loaded once per residue.  With one ungapped sibling (binary trees)
+  // (G_p[i] * P) * E_s is the reference's own operation order; with more, the siblings are multiplied together first.
+  double gp[DN_MAXA], sib[DN_MAXA];
+  for (int i = 0; i < A; ++i) {
+    gp[i] = Gp[(size_t)i * nb];
+    double v = 1;
+    bool any = false;
+    for (int k = k0; k < k1; ++k) {
+      const int s = S.kid_idx[k];
+      if (s != node && a.tok[(size_t)s * nb + col] != SP_TOK_GAP) {
+        const double e = a.E[(((size_t)s * C + c) * A + i) * nb + col];
+        v = any ? v * e : e;
+        any = true;
+      }
+    }
+    sib[i] = any ? v : 1.0;
+  }
   for (int j = 0; j < A; ++j) {
     double Gj = 0;
-    for (int i = 0; i < A; ++i) {
-      double pr = Gp[(size_t)i * nb] * Pn[i * A + j];   // the reference's order: G_p[i] * P, then the siblings
-      for (int k = k0; k < k1; ++k) {
-        const int s = S.kid_idx[k];
-        if (s != node && a.tok[(size_t)s * nb + col] != SP_TOK_GAP) pr *= a.E[(((size_t)s * C + c) * A + i) * nb + col];
-      }
-      Gj += pr;
-    }
+    for (int i = 0; i < A; ++i) Gj += (gp[i] * Pn[i * A + j]) * sib[i];
     Gn[(size_t)j * nb] = Gj;
   }
 }
 
 // accumulateEigenCounts (sumprod.cpp:294-372): block = DN_COLS columns x DN_NODES nodes x one component; every thread
 // accumulates its column's A x A complex contributions over the block's nodes, then the block reduces over columns.
-template <int A>
+// REAL: the eigen-system is real (every reversible model): the imaginary halves are exact zeros and are not computed.
+template <int A, bool REAL>
 __global__ void __launch_bounds__(DN_COLS) dn_counts_kernel(SpDev S, DnArgs a, int first_partial) {
   const int C = S.C, nb = a.nb, CA = C * A, CAA = CA * A;
   const int col = blockIdx.x * blockDim.x + threadIdx.x, c = blockIdx.z;
@@ -747,6 +753,13 @@ __global__ void __launch_bounds__(DN_COLS) dn_counts_kernel(SpDev S, DnArgs a, i
   double2 acc[A * A];
 #pragma unroll
   for (int q = 0; q < A * A; ++q) acc[q] = make_double2(0, 0);
+  // eigenSubCount of the block's branches (model.cpp:1329-1350), shared by every column
+  __shared__ double2 s_esc[DN_NODES][A * A];
+  for (int q = threadIdx.x; q < (n1 - n0) * A * A; q += blockDim.x) {
+    const int n = q / (A * A), kl = q % (A * A);
+    s_esc[n][kl] = eigen_sub_count(S, n0 + n, c, kl / A, kl % A);
+  }
+  __syncthreads();
   if (col < nb) {
     const double colLL = a.colll[col];
     const double weight = a.weights ? a.weights[a.order[col]] : 1.0;
@@ -785,7 +798,7 @@ __global__ void __launch_bounds__(DN_COLS) dn_counts_kernel(SpDev S, DnArgs a, i
 #pragma unroll
       for (int k = 0; k < A; ++k) {
         double2 u = make_double2(0, 0), d = make_double2(0, 0);
-        if (S.is_real) {
+        if (REAL) {
 #pragma unroll
           for (int b = 0; b < A; ++b) {
             u.x += S.Vinv[((size_t)c * A + k) * A + b].x * U[b];
@@ -805,8 +818,9 @@ __global__ void __launch_bounds__(DN_COLS) dn_counts_kernel(SpDev S, DnArgs a, i
       for (int k = 0; k < A; ++k)
 #pragma unroll
         for (int l = 0; l < A; ++l) {
-          const double2 esc = eigen_sub_count(S, node, c, k, l);
-          acc[k * A + l] = cadd(acc[k * A + l], cscale(cmul(db[k], cmul(esc, ub[l])), scale));
+          const double2 esc = s_esc[node - n0][k * A + l];
+          if (REAL) acc[k * A + l].x += (db[k].x * (esc.x * ub[l].x)) * scale;   // the same products, imaginary parts all zero
+          else acc[k * A + l] = cadd(acc[k * A + l], cscale(cmul(db[k], cmul(esc, ub[l])), scale));
         }
     }
   }
@@ -851,6 +865,23 @@ __global__ void reduce_partials_kernel(const double* partials, int n_blocks, int
   double v = 0;
   for (int b = 0; b < n_blocks; ++b) v += partials[(size_t)b * counts_size + q];
   counts[q] += v;
+}
+
+// the same for thousands of partials: one block per count, fixed summation order (thread t takes partials t, t+256, ...;
+// then lanes by shuffle, warps in order)
+__global__ void __launch_bounds__(256) reduce_partials_wide_kernel(const double* partials, int n_blocks, int counts_size, double* counts) {
+  const int q = blockIdx.x;
+  double v = 0;
+  for (int b = threadIdx.x; b < n_blocks; b += 256) v += partials[(size_t)b * counts_size + q];
+  for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  __shared__ double s[8];
+  if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = v;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0;
+    for (int w = 0; w < 8; ++w) t += s[w];
+    counts[q] += t;
+  }
 }
 
 // EigenModel::getSubCounts (model.cpp:1352-1377): one thread per (c, i, j)
@@ -1212,9 +1243,11 @@ int run_columns(hist_sumprod* sp, const char* d_cols, const double* d_w, int64_t
     ctx->launches += 2;
     a.order = sp->d_order;
     if (dense_ok) {
-      // the densest occupancy class (at least 2^floor(log2 N) ungapped rows) is a prefix of the order
+      // the four densest occupancy classes (at least 2^floor(log2 N) / 8 ungapped rows) are a prefix of the order: the
+      // full-tree columns, and the few large-subtree insertions whose level walks would otherwise be the column kernel's tail
       int threshold = 1;
       while (threshold * 2 <= sp->N) threshold *= 2;
+      threshold = std::max(1, threshold / 8);
       if (!sp->d_ndense) HB_CUDA(ctx, cudaMalloc(&sp->d_ndense, sizeof(int)));
       HB_CUDA(ctx, cudaMemsetAsync(sp->d_ndense, 0, sizeof(int), ctx->stream));
       count_dense_kernel<<<64, 256, 0, ctx->stream>>>(occ, (int)n_cols, threshold, sp->d_ndense);
@@ -1235,7 +1268,7 @@ int run_columns(hist_sumprod* sp, const char* d_cols, const double* d_w, int64_t
     ArenaPlan plan;
     const size_t o_tok = plan.add((size_t)N * nbs), o_E = plan.add(8 * (size_t)N * CA * nbs), o_F = plan.add(8 * (size_t)N * CA * nbs),
                  o_G = plan.add(8 * (size_t)N * CA * nbs), o_lE = plan.add(8 * (size_t)N * C * nbs), o_lF = plan.add(8 * (size_t)N * C * nbs),
-                 o_lG = plan.add(8 * (size_t)N * C * nbs), o_rt = plan.add(8 * (size_t)N * C * nbs), o_ll = plan.add(8 * nbs),
+                 o_lG = plan.add(8 * (size_t)N * C * nbs), o_ll = plan.add(8 * nbs), o_cpt = plan.add(8 * (size_t)C * nbs + 8 * nbs),
                  o_part = plan.add(8 * (size_t)std::max(1, n_part) * csz);
     if (sp->dn_work_bytes < plan.bytes) {
       cudaStreamSynchronize(ctx->stream);
@@ -1249,7 +1282,9 @@ int run_columns(hist_sumprod* sp, const char* d_cols, const double* d_w, int64_t
     d.columns = d_cols; d.order = sp->d_order + b0; d.weights = d_w; d.nb = nb;
     d.tok = (signed char*)(w + o_tok);
     d.E = (double*)(w + o_E); d.F = (double*)(w + o_F); d.G = (double*)(w + o_G);
-    d.logE = (double*)(w + o_lE); d.logF = (double*)(w + o_lF); d.logG = (double*)(w + o_lG); d.rootterm = (double*)(w + o_rt);
+    d.logE = (double*)(w + o_lE); d.logF = (double*)(w + o_lF); d.logG = (double*)(w + o_lG);
+    d.cpt = (double*)(w + o_cpt); d.n_roots = (int*)(w + o_cpt + 8 * (size_t)C * nbs); d.root_node = d.n_roots + nbs;
+    HB_CUDA(ctx, cudaMemsetAsync(w + o_cpt, 0, 8 * (size_t)C * nbs + 8 * nbs, ctx->stream));
     d.colll = (double*)(w + o_ll); d.col_loglike = d_ll; d.partials = (double*)(w + o_part); d.counts_size = csz; d.err = sp->d_err;
     const int n_levels = (int)sp->lvl_off_h.size() - 1;
     dn_init_kernel<<<dim3(col_blocks, N), DN_COLS, 0, ctx->stream>>>(sp->dev, d);
@@ -1260,8 +1295,9 @@ int run_columns(hist_sumprod* sp, const char* d_cols, const double* d_w, int64_t
     if (want_partials) {
       for (int lev = 0; lev < n_levels; ++lev)
         dn_down_kernel<<<dim3(col_blocks, sp->lvl_off_h[lev + 1] - sp->lvl_off_h[lev], C), DN_COLS, 0, ctx->stream>>>(sp->dev, d, lev);
-      dn_counts_kernel<4><<<dim3(col_blocks, node_blocks, C), DN_COLS, 0, ctx->stream>>>(sp->dev, d, 0);
-      reduce_partials_kernel<<<(csz + 127) / 128, 128, 0, ctx->stream>>>(d.partials, n_part, csz, counts_dev);
+      if (sp->dev.is_real) dn_counts_kernel<4, true><<<dim3(col_blocks, node_blocks, C), DN_COLS, 0, ctx->stream>>>(sp->dev, d, 0);
+      else dn_counts_kernel<4, false><<<dim3(col_blocks, node_blocks, C), DN_COLS, 0, ctx->stream>>>(sp->dev, d, 0);
+      reduce_partials_wide_kernel<<<csz, 256, 0, ctx->stream>>>(d.partials, n_part, csz, counts_dev);
       ctx->launches += 2 + n_levels;
     }
     b0 += nb;

@@ -1,25 +1,22 @@
-"""Kernel time of the sum-product column kernel on dense vs sparse column subsets of the EM bench alignment."""
-import sys, os, time
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-import numpy as np, torch
+"""One E-step of the EM leg (bench.py's em_family) for kernel-level timing under ncu:
+    ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file out.csv python tools/em_probe.py"""
+import os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import numpy as np
+import torch
 import bench
 from historian_b200 import capi
 model, tree, cols = bench.em_family()
 ctx = capi.Context(0)
 sp = ctx.sumprod(model, tree)
-occ = (cols != ord("-")).sum(1)
-print("columns", cols.shape, "dense(>N/2):", int((occ > cols.shape[1] / 2).sum()), "median occ", int(np.median(occ)), "mean", float(occ.mean()))
-def run(sub, label):
-    d = torch.from_numpy(np.ascontiguousarray(sub)).cuda()
-    c = torch.zeros(sp.counts_size, dtype=torch.float64, device="cuda")
-    ll = torch.zeros(len(sub), dtype=torch.float64, device="cuda")
-    for _ in range(2): sp.columns_device(d, len(sub), c, ll)
-    ctx.set_timing(True); ctx.fill_time_ms()
-    for _ in range(3): sp.columns_device(d, len(sub), c, ll)
-    ms, n = ctx.fill_time_ms(); ctx.set_timing(False)
-    print("%-28s %6d cols  %.3f ms  (%.1f us/col)" % (label, len(sub), ms / n, 1e3 * ms / n / len(sub)))
-run(cols, "all")
-run(cols[occ > cols.shape[1] / 2], "dense")
-run(cols[occ <= cols.shape[1] / 2], "sparse")
-run(cols[occ <= 8], "very sparse (<=8 rows)")
-run(cols[:888], "first 888")
+dev = torch.device("cuda", 0)
+d_cols = torch.from_numpy(np.ascontiguousarray(cols)).to(dev)
+d_counts = torch.zeros(sp.counts_size, dtype=torch.float64, device=dev)
+d_ll = torch.zeros(len(cols), dtype=torch.float64, device=dev)
+for _ in range(int(sys.argv[1]) if len(sys.argv) > 1 else 2):
+    d_counts.zero_()
+    torch.cuda.synchronize()
+    sp.columns_device(d_cols, len(cols), d_counts, d_ll)
+    ctx.synchronize()
+print("lp", float(d_counts[6]))
