@@ -156,7 +156,10 @@ Profile with_absorb(const Profile& p, const std::vector<double>& sub) {   // wha
   return q;
 }
 
-Profile prepare_x(const Profile& x, const Profile& y, const PairHMM& hmm, const GuideAlignmentEnvelope& env) {
+// Runs the DPMatrix constructor on the device.  Called from the initialiser of cellStorage, the FIRST member of DPMatrix
+// in declaration order (members are initialised in that order, whatever the order of the initialiser list): every other
+// member below then reads the finished tables.  Returns the size cellStorage is constructed with.
+size_t prepare(const Profile& x, const Profile& y, const PairHMM& hmm, const GuideAlignmentEnvelope& env) {
   hist_ctx* ctx = b200_ctx();
   Build& b = g_build;
   b.release();
@@ -173,7 +176,7 @@ Profile prepare_x(const Profile& x, const Profile& y, const PairHMM& hmm, const 
         "hist_pair_fetch_tables");
   b.near_start.resize(nx); b.near_end.resize(ny);
   check(hist_pair_fetch_envelope(b.pair, nullptr, nullptr, b.near_start.data(), b.near_end.data(), nullptr), "hist_pair_fetch_envelope");
-  return with_absorb(x, b.subx);
+  return x.size();
 }
 
 }  // namespace
@@ -188,9 +191,9 @@ DPMatrix::DPMatrix (const Profile& x, const Profile& y, const PairHMM& hmm, cons
     yEmpty (y.isEmpty()),
     xSize (x.size()),
     ySize (y.size()),
-    subx (prepare_x (x, y, hmm, env)),           // leftMultiply of both profiles + the four tables, on the device
+    subx (with_absorb (x, g_build.subx)),       // Profile::leftMultiply of both profiles, computed on the device
     suby (with_absorb (y, g_build.suby)),
-    cellStorage (x.size()),
+    cellStorage (prepare (x, y, hmm, env)),      // initialised first (declaration order): runs the constructor kernels
     absorbScratch (hmm.components(), vguard<LogProb> (hmm.alphabetSize())),
     insx (g_build.insx.begin(), g_build.insx.end()),
     insy (g_build.insy.begin(), g_build.insy.end()),
