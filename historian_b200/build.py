@@ -14,7 +14,7 @@ NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 
 FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-    "-Xcompiler", "-fPIC", "-shared", "--use_fast_math=false", "-I" + os.path.join(ROOT, "include"),
+    "-Xcompiler", "-fPIC", "-shared", "-I" + os.path.join(ROOT, "include"),
 ]
 
 
@@ -33,8 +33,7 @@ def needs_build():
 def build(force=False, verbose=False):
     if not force and not needs_build():
         return LIB
-    flags = [f for f in FLAGS if f != "--use_fast_math=false"]
-    cmd = [NVCC] + flags + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB] + sources()
+    cmd = [NVCC] + FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB] + sources()
     # the image's /opt/gcc wrapper links libstdc++ statically; use the system host compiler
     if os.path.exists("/usr/bin/g++"):
         cmd[1:1] = ["-ccbin", "/usr/bin/g++"]

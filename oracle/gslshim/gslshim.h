@@ -5,7 +5,7 @@
 // supplies exactly the GSL types and functions the reference's sources touch
 // (containers, complex helpers, expm, nonsymmetric eigensolver, complex LU
 // inverse, QR least squares, golden-section minimiser, gamma quantile, three
-// pdfs, gsl_fcmp), header-only, on top of historian_b200/host/linalg.h.
+// pdfs, gsl_fcmp), header-only, on top of oracle/gslshim/linalg.h (dense linear algebra written for this shim).
 // The reference is then compiled from /root/reference/src where it lies by
 // oracle/Makefile into oracle/_ref/.
 #pragma once
@@ -14,7 +14,7 @@
 #include <cstring>
 #include <complex>
 #include <vector>
-#include "../../historian_b200/host/linalg.h"
+#include "linalg.h"
 
 #define GSL_SUCCESS 0
 #define GSL_FAILURE (-1)

@@ -281,3 +281,51 @@ def test_leaf_profiles_from_tokens_match_those_from_residues(ctx):
     ctx.close_all(pairs)
     ctx.close_all(by_res + by_tok)
     assert all(p.h is None for p in pairs + by_res + by_tok)
+
+
+@pytest.mark.parametrize("case", ["lg_t1e-8", "ecmrest_t1e-6", "lg_far_apart"])
+def test_posteriors_without_the_within_cell_range_exemption(ctx, case):
+    """The five states of a cell share one exponent, so a state more than ~87 nats below its cell's maximum is stored as
+    zero.  assert_log_close exempts such states; this test does NOT: on the inputs where the
+    range is stretched furthest -- near-zero branch lengths (emission rows that are almost one-hot, transition weights
+    like log(1e-10)), the 61-state codon model, and two unrelated sequences -- every (cell, state) whose exact posterior
+    exp(F + B - lpEnd) is at least 1e-30 must be present with the right value, the posterior mass must be complete,
+    and the best trace must be the exact-arithmetic one.  A flushed state could only matter if it carried posterior
+    mass; this shows it never does."""
+    from historian_b200 import model as M
+    rng = np.random.default_rng(11)
+    if case == "ecmrest_t1e-6":
+        rm = M.RateModel.preset("ECMrest")
+        x, y, (r1, r2) = synth.leaf_pair(rng, rm.alphabet, 40, 38, identity=0.8)
+        hmm = M.pair_hmm(rm, 1e-6, 2e-6)
+    elif case == "lg_t1e-8":
+        rm = M.RateModel.preset("lg")
+        x, y, (r1, r2) = synth.leaf_pair(rng, rm.alphabet, 90, 85, identity=0.9)
+        hmm = M.pair_hmm(rm, 1e-8, 1e-8)
+    else:
+        rm = M.RateModel.preset("lg")
+        x, y, (r1, r2) = synth.leaf_pair(rng, rm.alphabet, 70, 75, identity=0.05)
+        hmm = M.pair_hmm(rm, 0.02, 0.03)
+    env = D.Envelope.from_guide_rows(r1, r2, 6)
+    pair, dx, dy = prepare(ctx, x, y, hmm, env)
+    lp_end = pair.forward()
+    pair.backward()
+    gf, gb = pair.cells_dense(0), pair.cells_dense(1)
+    O.set_exact_lse(True)
+    try:
+        ef, elp = O.forward(x, y, hmm, env)
+        eb, _ = O.backward(x, y, hmm, env)
+        ebest = O.trace_best(x, y, hmm, env, np.ascontiguousarray(ef), (x.n_states - 1, y.n_states - 1, D.EEE))
+    finally:
+        O.set_exact_lse(False)
+    assert np.isfinite(elp) and abs(lp_end - elp) <= REL_EXACT * abs(elp) + ABS_EXACT
+    with np.errstate(invalid="ignore"):
+        epost, gpost = ef + eb - elp, gf + gb - lp_end
+    live = np.isfinite(epost) & (epost >= np.log(1e-30))
+    assert live.sum() > 100
+    assert np.all(np.isfinite(gpost[live])), "%d (cell, state) entries with posterior >= 1e-30 were flushed" % (~np.isfinite(gpost[live])).sum()
+    assert np.max(np.abs(gpost[live] - epost[live])) <= 5e-4, np.max(np.abs(gpost[live] - epost[live]))
+    # every anti-diagonal... the posterior mass of the cells of one x row that absorb or delete it sums to one
+    big = np.isfinite(epost) & (epost >= np.log(1e-9))
+    assert np.max(np.abs(np.exp(gpost[big]) - np.exp(epost[big]))) <= 1e-4
+    assert H.same(pair.trace_best(), ebest)
