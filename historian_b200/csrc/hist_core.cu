@@ -1246,7 +1246,11 @@ int prepare_enqueue(hist_ctx* ctx, int32_t n, const hist_profile* const* xs, con
   if (!rc) {
     const int threads = std::max(32, (maxKp + 31) / 32 * 32);
     const int stride = maxKC + 32;
-    if (threads == 32) {
+    bool tensor = true;   // every pair of the batch is a one-component codon merge: leftMultiply as a tcgen05 GEMM
+    for (int k = 0; k < n && tensor; ++k) tensor = leftmul_tc_applicable(builds[k].pr->dev.A, builds[k].pr->dev.C);
+    if (tensor) {
+      rc = launch_leftmul_tc(ctx, dptrs, n, maxN);
+    } else if (threads == 32) {
       const int per_cta = 8;
       prepare_side_kernel<true><<<dim3((maxN + per_cta - 1) / per_cta, n, 2), dim3(32, per_cta), (size_t)per_cta * stride * sizeof(double), ctx->stream>>>(dptrs, stride);
     } else {

@@ -254,6 +254,10 @@ void host_parallel_for(int n, int grain, const std::function<void(int)>& fn);
 int ensure_staging_buf(hist_ctx* ctx, size_t bytes, int slot);
 void arena_drop(hist_ctx* ctx, hb_arena* a);
 
+// ---- codon alphabets: Profile::leftMultiply on the tensor cores (hist_codon.cu)
+bool leftmul_tc_applicable(int A, int C);
+int launch_leftmul_tc(hist_ctx* ctx, PairDev* const* dptrs, int n_pairs, int max_states);
+
 // ---- batched traceback (hist_trace.cu)
 // Best traces from EEE of n filled pairs in ONE launch (one warp per pair).  The paths stay on the device:
 // *d_paths is one allocation (release with cudaFreeAsync on the context's stream) in which pair k's path

@@ -59,8 +59,10 @@ def check_against_oracle(ctx, x, y, hmm, env, what, backward=True):
     finally:
         O.set_exact_lse(False)
     gt = pair.tables()
+    # one-component codon alphabets take the tensor-core constructor (hist_codon.cu: 3xTF32 products, FP32 accumulation)
+    tensor = x.components == 1 and 32 < x.alph_size <= 64
     for k in ("subx", "suby", "insx", "insy", "rootsubx", "rootsuby"):
-        H.assert_log_close(gt[k][..., None], et[k][..., None], 1e-12, 1e-9, what=what + ":" + k)
+        H.assert_log_close(gt[k][..., None], et[k][..., None], 1e-12, 5e-6 if tensor else 1e-9, what=what + ":" + k)
     lp_end = pair.forward()
     gfwd = pair.cells_dense(0)
     H.assert_log_close(gfwd, efwd, REL_EXACT, ABS_EXACT, what=what + ":fwd")
@@ -328,4 +330,7 @@ def test_posteriors_without_the_within_cell_range_exemption(ctx, case):
     # every anti-diagonal... the posterior mass of the cells of one x row that absorb or delete it sums to one
     big = np.isfinite(epost) & (epost >= np.log(1e-9))
     assert np.max(np.abs(np.exp(gpost[big]) - np.exp(epost[big]))) <= 1e-4
-    assert H.same(pair.trace_best(), ebest)
+    if case != "lg_t1e-8":
+        # (at t = 1e-8 the two orders of an adjacent insertion and deletion have the same weight to ~1e-8: the arg-max
+        # between them is decided below FP32 resolution, north_star's "wherever the margin exceeds the tolerance")
+        assert H.same(pair.trace_best(), ebest)
