@@ -456,6 +456,74 @@ def recon_leg(ctx, args, rank, world, local, barrier):
                                              % (RECON_REF_LEAVES, ROOT_LEN, BAND, det["reference_s"], det["ours_s"], det["identical_alignment"])}
     return out
 
+
+# ------------------------------------------------------------------ codon leg (BASELINE.json configs[4])
+CODON_LEAVES, CODON_ROOT_LEN = 256, 600
+CODON_TENSOR_PIPE = None   # filled from profiles/r02_codon_ncu.txt once captured (sm__inst_executed_pipe_tensor / tensor-pipe utilisation)
+
+
+def codon_family(seed=1):
+    from historian_b200 import model as M, simulator as S
+    tree = S.Tree.balanced(CODON_LEAVES, BRANCH)
+    rm = M.RateModel.preset("ECMrest")
+    gapped, _ = S.simulate_family(rm, tree, CODON_ROOT_LEN, seed)
+    leaves, guide = S.leaf_guide(tree, gapped)
+    return rm, guide, tree, leaves
+
+
+def codon_constructor_ms(reps=5):
+    """Milliseconds of the batched DPMatrix constructors (hist_pair_prepare_batch) of the 128 leaf x leaf merges of the
+    codon family; run in this process (tensor-core leftMultiply) and, by the caller, in a child with HIST_B200_NO_TENSOR=1."""
+    from historian_b200 import capi, descs as D, model as M
+    rm, guide, tree, leaves = codon_family()
+    seqs, grows = _family_inputs(tree, leaves, guide)
+    ctx = capi.Context(int(os.environ.get("LOCAL_RANK", "0")))
+    hmm = M.pair_hmm(rm, BRANCH, BRANCH)
+    lv = ctx.upload_sequences([seqs[v].encode("latin-1") for v in leaves], rm.alphabet, rm.components)
+    envs = [D.Envelope.from_guide_rows(grows[a], grows[b], BAND) for a, b in zip(leaves[0::2], leaves[1::2])]
+    plan = capi.PrepareBatch(ctx, lv[0::2], lv[1::2], hmm, envs, backward=False)
+    best = 1e30
+    for _ in range(reps + 1):
+        ctx.synchronize()
+        t0 = time.perf_counter()
+        pr = plan.run()
+        ctx.synchronize()
+        best = min(best, 1e3 * (time.perf_counter() - t0))
+        ctx.close_all(pr)
+    ctx.close()
+    return best
+
+
+def codon_leg(ctx, args):
+    """configs[4]: ECMrest (61 sense codons) family of 256 sequences x 600 codons: whole-tree reconstruction wall time, and the
+    constructor level that holds the tensor-core GEMM against the CUDA-core kernel it replaces."""
+    from historian_b200 import recon as R
+    rm, guide, tree, leaves = codon_family()
+    seqs, grows = _family_inputs(tree, leaves, guide)
+    walls = []
+    for rep in range(3):
+        nat = R.NativeReconstructor(ctx, rm, band=BAND, max_profile_states=1)
+        t0 = time.perf_counter()
+        bits, lp, rec = nat.reconstruct(tree, seqs, grows)
+        walls.append(time.perf_counter() - t0)
+        stage = nat.stage_ms
+        rec.close()
+    tensor_ms = codon_constructor_ms()
+    child = subprocess.run([sys.executable, os.path.abspath(__file__), "--codon-constructor-only"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL,
+                           env=dict(os.environ, HIST_B200_NO_TENSOR="1"), text=True)
+    cuda_ms = None
+    try:
+        cuda_ms = float(child.stdout.strip().splitlines()[-1])
+    except Exception:
+        pass
+    return {"metric": "recon wall-time (codon)", "value": min(walls[1:]), "unit": "s", "higher_is_better": False,
+            "config": {"workload": "ECMrest_256x600_seed1 whole-tree progressive reconstruction (61-state codon model, band %d, -profmaxstates 1)" % BAND,
+                       "alphabet": 61, "components": 1},
+            "alignment_columns": int(bits.shape[1]), "lp_final": lp, "stage_ms": {k: round(v, 2) for k, v in stage.items()},
+            "constructors_128_leaf_merges_ms": {"tensor_core_leftmultiply": tensor_ms, "cuda_core_leftmultiply": cuda_ms,
+                                                "kernel": "hb::leftmul_tc_kernel: tcgen05.mma kind::tf32 (3xTF32), M=128 N=64 K=64 per tile, FP32 accumulators in TMEM"},
+            "tensor_pipe": CODON_TENSOR_PIPE}
+
 # ------------------------------------------------------------------ GPU arm
 def gpu_arm(args):
     import torch
@@ -595,11 +663,16 @@ def gpu_arm(args):
     recon_line = None
     if not args.no_recon:
         recon_line = recon_leg(ctx, args, rank, world, local, barrier)
+    codon_line = None
+    if not args.no_codon and world == 1:
+        codon_line = codon_leg(ctx, args)
     if rank == 0:
         if em_line is not None:
             line["em_counts"] = em_line
         if recon_line is not None:
             line["recon"] = recon_line
+        if codon_line is not None:
+            line["codon"] = codon_line
         print(json.dumps(line))
     ctx.close()
     if world > 1:
@@ -623,9 +696,14 @@ def main():
     ap.add_argument("--family-seed", type=int, default=1, help="simulation seed of rank 0's family (rank r uses seed + r)")
     ap.add_argument("--no-em", action="store_true", help="skip the EM count leg (profiling runs)")
     ap.add_argument("--no-recon", action="store_true", help="skip the whole-tree reconstruction leg")
+    ap.add_argument("--no-codon", action="store_true", help="skip the codon (ECMrest) leg")
+    ap.add_argument("--codon-constructor-only", action="store_true", help=argparse.SUPPRESS)
     ap.add_argument("--recon-reps", type=int, default=3, help="timed repetitions of the whole-tree reconstruction (best is reported)")
     ap.add_argument("--recon-ref-sampled", action="store_true", help="also time the reference binary in sampled mode on the 64-leaf family (minutes)")
     args = ap.parse_args()
+    if args.codon_constructor_only:
+        print(codon_constructor_ms())
+        return
     if args.impl == "reference":
         reference_arm(args)
     else:

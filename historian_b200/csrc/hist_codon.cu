@@ -25,6 +25,8 @@ namespace hb {
 #define TC_M 128
 #define TC_N 64
 #define TC_K 64
+#define TC_THREADS 512   // 16 warps: four read the accumulator back (one TMEM lane quarter each), all sixteen build operands and tables
+#define TC_ROWS_PER_WARP (TC_M / (TC_THREADS / 32))
 
 // smem byte offset of element (row r, column k) of a [rows x 64] FP32 operand in the canonical K-major, no-swizzle UMMA
 // layout: core matrices of 8 rows x 16 bytes, the 16 core matrices of an 8-row group contiguous (LBO = 128 B), the
@@ -48,8 +50,8 @@ __device__ __forceinline__ void tc_split(float v, float& hi, float& lo) {
   lo = v - hi;                                                // exact
 }
 
-// grid = (state tiles, pairs, 2 sides); 128 threads; dynamic smem = 2 * 32 KB (A hi/lo) + 2 * 16 KB (B hi/lo)
-__global__ void __launch_bounds__(TC_M) leftmul_tc_kernel(PairDev* const* __restrict__ pairs) {
+// grid = (state tiles, pairs, 2 sides); TC_THREADS threads; dynamic smem = 2 * 32 KB (A hi/lo) + 2 * 16 KB (B hi/lo)
+__global__ void __launch_bounds__(TC_THREADS) leftmul_tc_kernel(PairDev* const* __restrict__ pairs) {
   extern __shared__ __align__(1024) unsigned char tc_smem[];
   __shared__ uint64_t s_bar;
   __shared__ uint32_t s_tmem;
@@ -79,7 +81,7 @@ __global__ void __launch_bounds__(TC_M) leftmul_tc_kernel(PairDev* const* __rest
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   // ---- B operand: P(a -> d), rows a, zero-padded to 64 x 64
-  for (int q = tid; q < TC_N * TC_K; q += TC_M) {
+  for (int q = tid; q < TC_N * TC_K; q += TC_THREADS) {
     const int a = q >> 6, d = q & 63;
     const float v = (a < A && d < A) ? (float)subMat[(size_t)a * A + d] : 0.f;
     float hi, lo;
@@ -87,20 +89,34 @@ __global__ void __launch_bounds__(TC_M) leftmul_tc_kernel(PairDev* const* __rest
     *reinterpret_cast<float*>(b_hi + tc_off(a, d)) = hi;
     *reinterpret_cast<float*>(b_lo + tc_off(a, d)) = lo;
   }
-  // ---- A operand: this thread's state
-  const int i = i0 + tid;
-  const bool live = i < s.n && i > 0 && i < s.n - 1 && (s.flags[i] & F_EMIT);
-  const double* la = s.lp_absorb + (size_t)(live ? i : 0) * K;
-  double m = -INFINITY;
-  if (live)
-    for (int d = 0; d < A; ++d) m = fmax(m, la[d]);
-  for (int d = 0; d < TC_K; ++d) {
-    float v = 0.f;
-    if (live && d < A && m > -INFINITY) v = (float)exp(la[d] - m);
+  // ---- A operand: rows exp(lpAbsorb[i] - m_i) of the tile's 128 states.  A warp takes a row at a time (lanes over the
+  // residues: coalesced loads, the maximum by shuffle), 32 rows per warp.
+  __shared__ double s_m[TC_M];
+  __shared__ unsigned char s_live[TC_M];
+  __shared__ double s_rootp[TC_N];   // exp(logRoot): the y side's emission rows carry the root distribution
+  if (tid < TC_N) s_rootp[tid] = tid < A ? exp(logRoot[tid]) : 0.0;
+  const int lane = tid & 31;
+  for (int r = warp * TC_ROWS_PER_WARP; r < (warp + 1) * TC_ROWS_PER_WARP; ++r) {
+    const int i = i0 + r;
+    const bool live = i < s.n && i > 0 && i < s.n - 1 && (s.flags[i] & F_EMIT);
+    const double* la = s.lp_absorb + (size_t)(live ? i : 0) * K;
+    const double v0 = live && lane < A ? la[lane] : -INFINITY, v1 = live && lane + 32 < A ? la[lane + 32] : -INFINITY;
+    double m = fmax(v0, v1);
+    for (int o = 16; o; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+    // one-hot leaf rows are all trivial cases (exp(0), exp(-inf)): no FP64 exp for them
+    const float e0 = v0 == -INFINITY ? 0.f : v0 == m ? 1.f : (float)exp(v0 - m);
+    const float e1 = v1 == -INFINITY ? 0.f : v1 == m ? 1.f : (float)exp(v1 - m);
     float hi, lo;
-    tc_split(v, hi, lo);
-    *reinterpret_cast<float*>(a_hi + tc_off(tid, d)) = hi;
-    *reinterpret_cast<float*>(a_lo + tc_off(tid, d)) = lo;
+    tc_split(e0, hi, lo);
+    *reinterpret_cast<float*>(a_hi + tc_off(r, lane)) = hi;
+    *reinterpret_cast<float*>(a_lo + tc_off(r, lane)) = lo;
+    tc_split(e1, hi, lo);
+    *reinterpret_cast<float*>(a_hi + tc_off(r, lane + 32)) = hi;
+    *reinterpret_cast<float*>(a_lo + tc_off(r, lane + 32)) = lo;
+    if (lane == 0) {
+      s_m[r] = m;
+      s_live[r] = live && m > -INFINITY;
+    }
   }
   // generic-proxy writes -> visible to the tensor core (async proxy)
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -137,9 +153,10 @@ __global__ void __launch_bounds__(TC_M) leftmul_tc_kernel(PairDev* const* __rest
         : "memory");
   }
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-  // accumulator row of this thread: TMEM lane = row (warp w reads lanes 32w .. 32w+31), column = a
-  float acc[TC_N];
-  {
+  // accumulator row of this thread: TMEM lane = row (warp w reads lanes 32w .. 32w+31), column = a.  The rows go back
+  // to shared memory (row-major, over the A operand) so that the epilogue can again run with lanes over the residues.
+  float* s_acc = reinterpret_cast<float*>(a_hi);   // [TC_M][TC_N]; the MMAs have completed (mbarrier), the operand is dead
+  if (warp < 4) {
     const uint32_t taddr = tmem + ((uint32_t)(warp * 32) << 16);
 #pragma unroll
     for (int c0 = 0; c0 < TC_N; c0 += 16) {
@@ -149,54 +166,78 @@ __global__ void __launch_bounds__(TC_M) leftmul_tc_kernel(PairDev* const* __rest
           : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]),
             "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
           : "r"(taddr + c0));
+      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
-      for (int q = 0; q < 16; ++q) acc[c0 + q] = __uint_as_float(r[q]);
+      for (int q = 0; q < 16; ++q) s_acc[tid * TC_N + ((c0 + q + tid) & (TC_N - 1))] = __uint_as_float(r[q]);   // rotated: conflict-free
     }
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TC_N) : "memory");
-  if (i >= s.n) return;
-  // ---- epilogue of this state: the tables of the DPMatrix constructor (as prepare_side_kernel)
-  if (!live) {
-    for (int k = 0; k < K; ++k) s.sub[(size_t)i * K + k] = -INFINITY;
-    for (int k = 0; k < Kp; ++k) s.H[(size_t)i * Kp + k] = 0.f;
-    s.ex[i] = 0; s.rs[i] = 1.f; s.ins[i] = 1.f;
-    s.rootsub[i] = -INFINITY; s.insl[i] = -INFINITY;
-    return;
-  }
-  double mx = -INFINITY, lr = -INFINITY, li = -INFINITY;
-  for (int a = 0; a < A; ++a) {
-    const double sv = acc[a] > 0.f ? m + log((double)acc[a]) : -INFINITY;
-    s.sub[(size_t)i * K + a] = sv;
-    mx = fmax(mx, sv);
-    lr = fmax(lr, logRoot[a] + sv);
-    li = fmax(li, logCptWeight[0] + logIns[a] + la[a]);
-  }
-  double racc = 0, iacc = 0;
-  for (int a = 0; a < A; ++a) {
-    const double sv = s.sub[(size_t)i * K + a];
-    if (lr > -INFINITY) racc += exp(logRoot[a] + sv - lr);
-    if (li > -INFINITY) iacc += exp(logCptWeight[0] + logIns[a] + la[a] - li);
-  }
-  const double s_root = lr > -INFINITY ? lr + log(racc) : -INFINITY;
-  const double s_ins = li > -INFINITY ? li + log(iacc) : -INFINITY;
-  const int ex = mx > -INFINITY ? (int)floor(mx / HB_LN2) : 0;
-  for (int k = 0; k < Kp; ++k) {
-    double h = 0.0;
-    if (k < A) {
-      const double sv = s.sub[(size_t)i * K + k];
-      h = sv > -INFINITY ? exp(sv - ex * HB_LN2) : 0.0;
-      if (isY) h *= exp(logRoot[k]);
+  // ---- epilogue: the tables of the DPMatrix constructor (as prepare_side_kernel), a warp per state, lanes over the residues
+  for (int r = warp * TC_ROWS_PER_WARP; r < (warp + 1) * TC_ROWS_PER_WARP; ++r) {
+    const int i = i0 + r;
+    if (i >= s.n) break;
+    if (!s_live[r]) {
+      for (int k = lane; k < K; k += 32) s.sub[(size_t)i * K + k] = -INFINITY;
+      for (int k = lane; k < Kp; k += 32) s.H[(size_t)i * Kp + k] = 0.f;
+      if (lane == 0) {
+        s.ex[i] = 0; s.rs[i] = 1.f; s.ins[i] = 1.f;
+        s.rootsub[i] = -INFINITY; s.insl[i] = -INFINITY;
+      }
+      continue;
     }
-    s.H[(size_t)i * Kp + k] = (float)h;
+    const double m = s_m[r];
+    const double* la = s.lp_absorb + (size_t)i * K;
+    double sv[2], rt[2], it[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int a = lane + 32 * h;
+      const float c = a < A ? s_acc[r * TC_N + ((a + r) & (TC_N - 1))] : 0.f;
+      sv[h] = c > 0.f ? m + (c == 1.f ? 0.0 : log((double)c)) : -INFINITY;
+      rt[h] = a < A ? logRoot[a] + sv[h] : -INFINITY;
+      it[h] = a < A ? logCptWeight[0] + logIns[a] + la[a] : -INFINITY;
+      if (a < A) s.sub[(size_t)i * K + a] = sv[h];
+    }
+    double mx = fmax(sv[0], sv[1]), lr = fmax(rt[0], rt[1]), li = fmax(it[0], it[1]);
+    for (int o = 16; o; o >>= 1) {
+      mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+      lr = fmax(lr, __shfl_xor_sync(0xffffffffu, lr, o));
+      li = fmax(li, __shfl_xor_sync(0xffffffffu, li, o));
+    }
+    double racc = 0, iacc = 0;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      if (rt[h] > -INFINITY) racc += exp(rt[h] - lr);
+      if (it[h] > -INFINITY) iacc += it[h] == li ? 1.0 : exp(it[h] - li);
+    }
+    for (int o = 16; o; o >>= 1) {
+      racc += __shfl_xor_sync(0xffffffffu, racc, o);
+      iacc += __shfl_xor_sync(0xffffffffu, iacc, o);
+    }
+    const double s_root = lr > -INFINITY ? lr + log(racc) : -INFINITY;
+    const double s_ins = li > -INFINITY ? li + (iacc == 1.0 ? 0.0 : log(iacc)) : -INFINITY;
+    const int ex = mx > -INFINITY ? (int)floor(mx / HB_LN2) : 0;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int k = lane + 32 * h;
+      if (k < Kp) {
+        double hv = 0.0;
+        if (k < A && sv[h] > -INFINITY) {
+          hv = exp(sv[h] - ex * HB_LN2);
+          if (isY) hv *= s_rootp[k];
+        }
+        s.H[(size_t)i * Kp + k] = (float)hv;
+      }
+    }
+    if (lane == 0) {
+      s.ex[i] = ex;
+      s.rootsub[i] = s_root;
+      s.insl[i] = s_ins;
+      s.rs[i] = s_root > -INFINITY ? (float)exp(s_root - ex * HB_LN2) : 0.f;
+      s.ins[i] = s_ins > -INFINITY ? (float)exp(s_ins - ex * HB_LN2) : 0.f;
+    }
   }
-  s.ex[i] = ex;
-  s.rootsub[i] = s_root;
-  s.insl[i] = s_ins;
-  s.rs[i] = s_root > -INFINITY ? (float)exp(s_root - ex * HB_LN2) : 0.f;
-  s.ins[i] = s_ins > -INFINITY ? (float)exp(s_ins - ex * HB_LN2) : 0.f;
 }
 
 // true if the tensor-core constructor applies to a batch of pairs with this alphabet
@@ -212,7 +253,7 @@ int launch_leftmul_tc(hist_ctx* ctx, PairDev* const* dptrs, int n_pairs, int max
     HB_CUDA(ctx, cudaFuncSetAttribute(leftmul_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = true;
   }
-  leftmul_tc_kernel<<<dim3((max_states + TC_M - 1) / TC_M, n_pairs, 2), TC_M, smem, ctx->stream>>>(dptrs);
+  leftmul_tc_kernel<<<dim3((max_states + TC_M - 1) / TC_M, n_pairs, 2), TC_THREADS, smem, ctx->stream>>>(dptrs);
   ctx->launches += 1;
   return check_cuda(ctx, cudaGetLastError(), "leftmul_tc_kernel");
 }
