@@ -26,14 +26,14 @@ def cell_set(*paths):
     return np.array(sorted(s), np.int32).reshape(-1, 3)
 
 
-def compare(g, o, what):
+def compare(g, o, what, tol=TOL):
     for k in ("state_cell", "trans_src", "trans_dest", "via_off", "via"):
         assert H.same(g[k], o[k]), "%s: %s differs (%s vs %s)" % (what, k, g[k].shape, o[k].shape)
     for k in ("state_lp_absorb", "state_fwd_lp", "trans_lp", "trans_best_lp"):
         a, b = np.asarray(g[k]), np.asarray(o[k])
         assert H.same(np.isneginf(a), np.isneginf(b)), (what, k)
         fin = np.isfinite(b)
-        assert np.all(np.abs(a[fin] - b[fin]) <= TOL * (1 + np.abs(b[fin]))), (what, k, np.abs(a[fin] - b[fin]).max())
+        assert np.all(np.abs(a[fin] - b[fin]) <= tol * (1 + np.abs(b[fin]))), (what, k, np.abs(a[fin] - b[fin]).max())
 
 
 def check_elim(ctx, x, y, hmm, env, what, seed=5489):
@@ -52,7 +52,9 @@ def check_elim(ctx, x, y, hmm, env, what, seed=5489):
             for strategy in (D.COLLAPSE_CHAINS, 0, D.COLLAPSE_CHAINS | D.KEEP_GAPS_OPEN):
                 o = O.profile_eliminate(x, y, hmm, env, fwd, lp_end, cells, strategy)
                 g = pair.eliminate(cells, strategy)
-                compare(g, o, "%s/%s/strategy%d" % (what, name, strategy))
+                # one-component codon alphabets: the leftMultiply tables come from FP32 tensor arithmetic (hist_codon.cu)
+                tensor = x.components == 1 and 32 < x.alph_size <= 64
+                compare(g, o, "%s/%s/strategy%d" % (what, name, strategy), 2e-6 if tensor else TOL)
     finally:
         O.set_exact_lse(False)
     return pair
