@@ -201,6 +201,14 @@ class Context:
         plan = PrepareBatch(self, xs, ys, hmms, envs, backward)
         return plan.run()
 
+    def fill_batch_async(self, pairs, backward=False, arr=None):
+        """hist_fill_batch with lp_end == NULL: enqueue the fills, no read-back, no synchronisation."""
+        n = len(pairs)
+        if arr is None:
+            arr = (C.c_void_p * n)(*[p.h for p in pairs])
+        self.check(self.lib.hist_fill_batch(self.h, arr, n, int(backward), None, None))
+        return arr
+
     def fill_batch(self, pairs, backward=False):
         n = len(pairs)
         arr = (C.c_void_p * n)(*[p.h for p in pairs])

@@ -1740,7 +1740,7 @@ int launch_fill(hist_ctx* ctx, hist_pair* const* pairs_in, int n_in, int n_dir, 
 }  // namespace
 
 extern "C" int hist_fill_batch(hist_ctx* ctx, hist_pair* const* pairs, int32_t n, int do_backward, double* lp_end, double* lp_start) {
-  if (!ctx || !pairs || n <= 0 || !lp_end) return set_err(ctx, HIST_ERR_ARG, "hist_fill_batch: bad arguments");
+  if (!ctx || !pairs || n <= 0) return set_err(ctx, HIST_ERR_ARG, "hist_fill_batch: bad arguments");
   cudaSetDevice(ctx->device);
   for (int k = 0; k < n; ++k) {
     if (!pairs[k] || pairs[k]->ctx != ctx) return set_err(ctx, HIST_ERR_ARG, "hist_fill_batch: pair %d belongs to another context", k);
@@ -1751,6 +1751,13 @@ extern "C" int hist_fill_batch(hist_ctx* ctx, hist_pair* const* pairs, int32_t n
   }
   int rc = launch_fill(ctx, pairs, n, do_backward ? 2 : 1, 0);
   if (rc) return rc;
+  if (!lp_end) {   // enqueue only: the likelihoods stay on the device until a later call (or hist_ctx_synchronize) asks for them
+    for (int k = 0; k < n; ++k) {
+      pairs[k]->fwd_done = true;
+      if (do_backward) pairs[k]->bwd_done = true;
+    }
+    return HIST_OK;
+  }
   // likelihoods: the scalar blocks (4 doubles) of pairs prepared in one batch are contiguous, so
   // consecutive pairs come back in one transfer
   std::vector<double> tmp(4 * (size_t)n);

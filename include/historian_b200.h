@@ -219,7 +219,8 @@ int hist_bwd_fill(hist_pair* pair, double* lp_start);
 /* Batched form used for all sibling merges of one guide-tree depth
  * (recon.cpp:938-1033 loop, independent iterations): one launch fills every
  * pair.  do_backward != 0 also runs the Backward fills (concurrently).
- * lp_end / lp_start: [n] outputs (lp_start may be NULL when !do_backward). */
+ * lp_end / lp_start: [n] outputs (lp_start may be NULL when !do_backward).  lp_end == NULL: the fills are only enqueued on
+ * the context's stream (no read-back, no synchronisation); the matrices are usable by later calls on the same context. */
 int hist_fill_batch(hist_ctx* ctx, hist_pair* const* pairs, int32_t n, int do_backward,
                     double* lp_end, double* lp_start);
 
