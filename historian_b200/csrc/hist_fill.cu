@@ -1370,6 +1370,249 @@ __global__ void __launch_bounds__(32) fill_chain_kernel(PairDev* const* __restri
   }
 }
 
+
+// ------------------------------------------------------------------ leaf x leaf strips, two warps per strip
+// The step of consumer_chain has two halves: everything that does NOT depend on DP values (position of the lane's cell,
+// its state records, the absorb dot product from the register-resident emission rows, the envelope test, the lanes its
+// three predecessors sit on) and the part that does (shuffles, sums, normalisation, stores).  Here a HELPER warp runs the
+// first half a few steps ahead and hands every lane a 32-byte record through shared memory; the MAIN warp carries the
+// dependency chain with half the instructions.  The hand-over is lane-private (lane t of the main warp reads what lane t
+// of the helper wrote), so it needs no barrier and no fence (a release would make the helper wait for its own prefetch
+// loads at every step): every 16-byte chunk of a record carries the step number it belongs to -- a 16-byte shared
+// store of one lane is a single transaction -- and the main lane re-reads until all three chunks show its step; a
+// per-lane `consumed` counter, stored with a data dependency on the chunks just read, keeps the helper from lapping it.
+#define CH_DEPTH 8
+#define CH_SPIN_LIMIT (1 << 22)   // a hand-over that never arrives is a bug: give up (results invalid, flagged) instead of hanging the GPU
+
+struct ChainShared {
+  int4 rec[CH_DEPTH][3][32];   // per step, per lane: {ab, rs_x, ins_x, step} {rs_y, ins_y, ex | ey << 16, step} {store offset, control, step, 0}
+  int consumed[32];
+  int failed;
+};
+
+__device__ __forceinline__ int4 ld_volatile_shared4(const int4* p) {
+  int4 v;
+  asm volatile("ld.volatile.shared.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"((unsigned)__cvta_generic_to_shared(p)) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_volatile_shared4(int4* p, int4 v) {
+  asm volatile("st.volatile.shared.v4.s32 [%0], {%1,%2,%3,%4};" ::"r"((unsigned)__cvta_generic_to_shared(p)), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ int ld_volatile_shared(const int* p) {
+  int v;
+  asm volatile("ld.volatile.shared.s32 %0, [%1];" : "=r"(v) : "r"((unsigned)__cvta_generic_to_shared(p)) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_volatile_shared(int* p, int v) {
+  asm volatile("st.volatile.shared.s32 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(p)), "r"(v) : "memory");
+}
+
+// control word: predecessor lanes (0xff = none) in bytes 0-2, flags in byte 3
+enum { CH_OK = 1, CH_ORIGIN = 2, CH_TO_END = 4, CH_STORE = 8 };
+
+template <bool BWD, int K4>
+__device__ __forceinline__ void chain_helper(const PairDev& P, ChainShared& S) {
+  const int nD = P.n_diag, nx = P.x.n, ny = P.y.n, Kp = P.Kp;
+  const int t = threadIdx.x & 31;
+  auto diag_of = [&](int q) { return min(max(BWD ? nD - 1 - q : q, 0), nD - 1); };
+  const int4* __restrict__ recx = BWD ? P.x.cb : P.x.cf;
+  const int4* __restrict__ recy = BWD ? P.y.cb : P.y.cf;
+  const float* __restrict__ Hx = P.x.H;
+  const float* __restrict__ Hy = P.y.H;
+  const int max_dist = P.max_dist;
+  int ilo1 = 0, w1 = 0, ilo2 = 0, w2 = 0;
+  DiagInfo c0 = P.dinfo[diag_of(0)], n0 = P.dinfo[diag_of(1)], n1 = P.dinfo[diag_of(2)];
+  ChainPos cur = chain_pos(c0, diag_of(0), t, nx, ny);
+  float4 hx[K4], hy[K4];
+#pragma unroll
+  for (int k = 0; k < K4; ++k) hx[k] = hy[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+  int hi = -1, hj = -1;
+  {
+    const bool px = cur.ok && cur.i >= 1, py = cur.ok && cur.j >= 1;
+    load_row<K4>(hx, Hx, cur.i, Kp, px);
+    load_row<K4>(hy, Hy, cur.j, Kp, py);
+    hi = px ? cur.i : hi;
+    hj = py ? cur.j : hj;
+  }
+  int4 rx = __ldg(recx + cur.i), ry = __ldg(recy + cur.j);
+  for (int q = 0; q < nD; ++q) {
+    const DiagInfo di = c0;
+    const int i = cur.i, j = cur.j;
+    const bool xEmit = i >= 1, yEmit = j >= 1;
+    float ab = 0.f;
+    {
+      float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+      for (int k = 0; k < K4; ++k) {
+        a0 = fmaf(hx[k].x, hy[k].x, a0);
+        a1 = fmaf(hx[k].y, hy[k].y, a1);
+        a0 = fmaf(hx[k].z, hy[k].z, a0);
+        a1 = fmaf(hx[k].w, hy[k].w, a1);
+      }
+      asm volatile("" : "+f"(a0), "+f"(a1));   // the rows are overwritten in place below
+      if (cur.ok && xEmit && yEmit && hi == i && hj == j) ab = a0 + a1;
+    }
+    if ((q & 3) == 0) {
+      const int far = BWD ? -1 : 1;
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(P.dinfo + diag_of(q + 32 + (t & 3) * 8)));
+      const int fi = min(max(i + far * 14, 0), nx - 1), fj = min(max(j + far * 14, 0), ny - 1);
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(recx + fi));
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(recy + fj));
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(Hx + (size_t)fi * Kp));
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(Hy + (size_t)fj * Kp));
+    }
+    const ChainPos nxt = chain_pos(n0, diag_of(q + 1), t, nx, ny);
+    const int4 rxn = __ldg(recx + nxt.i), ryn = __ldg(recy + nxt.j);
+    {
+      const bool px = nxt.ok && nxt.i >= 1 && nxt.i != hi, py = nxt.ok && nxt.j >= 1 && nxt.j != hj;
+      load_row<K4>(hx, Hx, nxt.i, Kp, px);
+      load_row<K4>(hy, Hy, nxt.j, Kp, py);
+      hi = px ? nxt.i : hi;
+      hj = py ? nxt.j : hj;
+    }
+    c0 = n0; n0 = n1;
+    n1 = load_dinfo_early(P.dinfo + diag_of(q + 3));
+    const bool xLast = i == nx - 2, yLast = j == ny - 2;
+    const bool ok = cur.ok && (i == 0 || yLast || max_dist < 0 || hb_iabs(rx.w - ry.w) <= max_dist);
+    int sX, sY, sD;
+    if (!BWD) {
+      sX = ok && !yLast && xEmit ? chain_slot(ilo1, w1, i - 1, j, ny) : -1;
+      sY = ok && !xLast && yEmit ? chain_slot(ilo1, w1, i, j - 1, ny) : -1;
+      sD = ok && xEmit && yEmit ? chain_slot(ilo2, w2, i - 1, j - 1, ny) : -1;
+    } else {
+      const bool xac = i + 1 <= nx - 2, yac = j + 1 <= ny - 2;
+      sD = ok && xac && yac ? chain_slot(ilo2, w2, i + 1, j + 1, ny) : -1;
+      sX = ok && !yLast && xac ? chain_slot(ilo1, w1, i + 1, j, ny) : -1;
+      sY = ok && !xLast && yac ? chain_slot(ilo1, w1, i, j + 1, ny) : -1;
+    }
+    const bool store = t < di.width + 2 + di.pad;
+    int flags = (ok ? CH_OK : 0) | (store ? CH_STORE : 0);
+    if (!BWD && i == 0 && j == 0) flags |= CH_ORIGIN;
+    if (BWD && xLast && yLast) flags |= CH_TO_END;
+    const int ctrl = (sX & 0xff) | ((sY & 0xff) << 8) | ((sD & 0xff) << 16) | (flags << 24);
+    // ---- hand the record over: wait until the main warp has freed this ring slot
+    const int slot = q & (CH_DEPTH - 1);
+    if (q >= CH_DEPTH) {
+      int spins = 0;
+      while (ld_volatile_shared(&S.consumed[t]) < q - CH_DEPTH + 1)
+        if (++spins > CH_SPIN_LIMIT) { S.failed = 1; break; }
+    }
+    st_volatile_shared4(&S.rec[slot][0][t], make_int4(__float_as_int(ab), rx.y, rx.z, q + 1));
+    st_volatile_shared4(&S.rec[slot][1][t], make_int4(ry.y, ry.z, (rx.x & 0xffff) | (ry.x << 16), q + 1));
+    st_volatile_shared4(&S.rec[slot][2][t], make_int4((int)(di.off + t), ctrl, q + 1, 0));
+    ilo2 = ilo1; w2 = w1;
+    ilo1 = di.ilo; w1 = di.width;
+    cur = nxt;
+    rx = rxn; ry = ryn;
+  }
+}
+
+template <bool BWD>
+__device__ __forceinline__ void chain_main(const PairDev& P, ChainShared& S) {
+  float4* gA = BWD ? P.bA : P.fA;
+  float2* gB = BWD ? P.bB : P.fB;
+  const int nD = P.n_diag;
+  const int t = threadIdx.x & 31;
+  const WReg WR = load_weights(P);
+  RegCell p1, p2;
+  p1.a = make_float4(0.f, 0.f, 0.f, 0.f); p1.iiw = 0.f; p1.e = HB_EXP_ZERO; p1.aux = 0.f;
+  p2 = p1;
+  for (int q = 0; q < nD; ++q) {
+    const int slot = q & (CH_DEPTH - 1);
+    int4 ra, rb, rc;
+    {
+      int spins = 0;
+      for (;;) {
+        ra = ld_volatile_shared4(&S.rec[slot][0][t]);
+        rb = ld_volatile_shared4(&S.rec[slot][1][t]);
+        rc = ld_volatile_shared4(&S.rec[slot][2][t]);
+        if (ra.w == q + 1 && rb.w == q + 1 && rc.z == q + 1) break;
+        if (++spins > CH_SPIN_LIMIT) { S.failed = 1; break; }
+      }
+    }
+    st_volatile_shared(&S.consumed[t], min(min(ra.w, rb.w), rc.z));   // = q + 1, and cannot be issued before the chunks have arrived
+    const float ab = __int_as_float(ra.x);
+    const int ctrl = rc.y, flags = (unsigned)ctrl >> 24;
+    const int ex = (int)(short)(rb.z & 0xffff), ey = rb.z >> 16;
+    const int bX = ctrl & 0xff, bY = (ctrl >> 8) & 0xff, bD = (ctrl >> 16) & 0xff;
+    const int sX = bX == 0xff ? -1 : bX, sY = bY == 0xff ? -1 : bY, sD = bD == 0xff ? -1 : bD;
+    const bool ok = flags & CH_OK;
+    float4 xA, xB, yA, yB, dA, dB;
+    const bool vX = shfl_cell(p1, sX, xA, xB);
+    const bool vY = shfl_cell(p1, sY, yA, yB);
+    const bool vD = shfl_cell(p2, sD, dA, dB);
+    Cell c;
+    if (!BWD) {
+      c = chain_forward_math(WR, (flags & CH_ORIGIN) != 0, ex, ey, __int_as_float(ra.y), __int_as_float(ra.z), __int_as_float(rb.x),
+                             __int_as_float(rb.y), ab, vX, xA, xB, vY, yA, yB, vD, dA, dB);
+    } else {
+      const int4 r1 = make_int4(ex + ey, ex, ey, 0);
+      const int4 r2 = make_int4(__float_as_int(1.f), ra.y, ra.z, 0);
+      const int4 r3 = make_int4(rb.x, rb.y, 0, __float_as_int(1.f));
+      c = backward_math<false>(WR, (flags & CH_TO_END) ? R_TO_END : 0, r1, r2, r3, vD, dA, dB, vX, xA, xB, vY, yA, yB);
+    }
+    cell_normalise_nb(c, ok);
+    const float4 va = make_float4(c.v[0], c.v[1], c.v[2], c.v[3]);
+    if (flags & CH_STORE) {
+      __stcs(gA + (unsigned)rc.x, va);
+      __stcs(gB + (unsigned)rc.x, make_float2(c.v[4], __int_as_float(c.E)));
+    }
+    p2 = p1;
+    p1.a = va; p1.iiw = c.v[4]; p1.e = c.E; p1.aux = BWD ? c.v[0] * ab : 0.f;
+  }
+}
+
+template <int K4>
+__global__ void __launch_bounds__(64) fill_chain2_kernel(PairDev* const* __restrict__ pairs, int n_dir, int only_dir, int* __restrict__ err) {
+  __shared__ PairDev P;
+  __shared__ ChainShared S;
+  {
+    const int* s = reinterpret_cast<const int*>(pairs[blockIdx.x / n_dir]);
+    int* dptr = reinterpret_cast<int*>(&P);
+    for (int k = threadIdx.x; k < (int)(sizeof(PairDev) / sizeof(int)); k += blockDim.x) dptr[k] = s[k];
+  }
+  if (threadIdx.x < 32) S.consumed[threadIdx.x] = 0;
+  for (int k = threadIdx.x; k < CH_DEPTH * 3 * 32; k += blockDim.x) (&S.rec[0][0][0])[k] = make_int4(0, 0, 0, 0);   // step numbers start at 1
+  if (threadIdx.x == 0) S.failed = 0;
+  __syncthreads();
+  const bool bwd = n_dir == 2 ? (blockIdx.x % n_dir) == 1 : only_dir == 1;
+  if (threadIdx.x >= 32) {
+    if (bwd) chain_helper<true, K4>(P, S); else chain_helper<false, K4>(P, S);
+  } else {
+    if (bwd) chain_main<true>(P, S); else chain_main<false>(P, S);
+  }
+  __threadfence_block();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    if (S.failed && err) atomicExch(err, 1);
+    if (!bwd) {
+      // transitions into EEE (forward.cpp:205-220): the one cell (nx-2, ny-2)
+      const int i = P.x.n - 2, j = P.y.n - 2, d = i + j;
+      const DiagInfo di = P.dinfo[d];
+      const int s = chain_slot(di.ilo, di.width, i, j, P.y.n);
+      double lp = -INFINITY;
+      if (s >= 0) {
+        const float4 a = P.fA[di.off + s];
+        const float2 b = P.fB[di.off + s];
+        const int E = __float_as_int(b.y);
+        const double v = (double)a.x * P.W[0][5] + (double)a.y * P.W[1][5] + (double)a.z * P.W[2][5] + (double)a.w * P.W[3][5] + (double)b.x * P.W[4][5];
+        if (E > HB_EXP_ZERO / 2 && v > 0) lp = log(v) + (double)E * HB_LN2;
+      }
+      *P.lp_end = S.failed ? NAN : lp;
+    } else {
+      const DiagInfo di = P.dinfo[0];
+      const int s = chain_slot(di.ilo, di.width, 0, 0, P.y.n);
+      double lp = -INFINITY;
+      if (s >= 0) {
+        const float4 a = P.bA[di.off + s];
+        const float2 b = P.bB[di.off + s];
+        if (__float_as_int(b.y) > HB_EXP_ZERO / 2) lp = cell_log(a.x, __float_as_int(b.y));
+      }
+      *P.lp_start = S.failed ? NAN : lp;
+    }
+  }
+}
+
 // General strips: a CTA of several warps, each thread looping over the slots of the diagonal.
 template <bool BWD>
 __device__ __forceinline__ void sweep_wide(const PairDev& P, const Ring& ring) {
@@ -1681,9 +1924,16 @@ int launch_fill_chain(hist_ctx* ctx, hist_pair* const* pairs, int n, int n_dir, 
     PairDev** dptrs = nullptr;
     HB_CUDA(ctx, cudaMallocAsync((void**)&dptrs, m * sizeof(PairDev*), ctx->stream));
     HB_CUDA(ctx, cudaMemcpyAsync(dptrs, h.data(), m * sizeof(PairDev*), cudaMemcpyHostToDevice, ctx->stream));
-    if (K4 == 1) fill_chain_kernel<1><<<m * n_dir, 32, 0, ctx->stream>>>(dptrs, n_dir, only_dir);
-    else if (K4 == 2) fill_chain_kernel<2><<<m * n_dir, 32, 0, ctx->stream>>>(dptrs, n_dir, only_dir);
-    else fill_chain_kernel<5><<<m * n_dir, 32, 0, ctx->stream>>>(dptrs, n_dir, only_dir);
+    static const bool one_warp = getenv("HIST_B200_CHAIN") && !strcmp(getenv("HIST_B200_CHAIN"), "1warp");   // A/B runs
+    if (one_warp) {
+      if (K4 == 1) fill_chain_kernel<1><<<m * n_dir, 32, 0, ctx->stream>>>(dptrs, n_dir, only_dir);
+      else if (K4 == 2) fill_chain_kernel<2><<<m * n_dir, 32, 0, ctx->stream>>>(dptrs, n_dir, only_dir);
+      else fill_chain_kernel<5><<<m * n_dir, 32, 0, ctx->stream>>>(dptrs, n_dir, only_dir);
+    } else {
+      if (K4 == 1) fill_chain2_kernel<1><<<m * n_dir, 64, 0, ctx->stream>>>(dptrs, n_dir, only_dir, nullptr);
+      else if (K4 == 2) fill_chain2_kernel<2><<<m * n_dir, 64, 0, ctx->stream>>>(dptrs, n_dir, only_dir, nullptr);
+      else fill_chain2_kernel<5><<<m * n_dir, 64, 0, ctx->stream>>>(dptrs, n_dir, only_dir, nullptr);
+    }
     ctx->launches += 1;
     HB_CUDA(ctx, cudaGetLastError());
     HB_CUDA(ctx, cudaFreeAsync(dptrs, ctx->stream));
