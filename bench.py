@@ -39,7 +39,7 @@ N_LEAVES = 1024
 ROOT_LEN = 1000
 # dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel per launch, from the ncu --set full capture under profiles/ (None = not captured)
 EM_TRAFFIC_BYTES = 5.78e9     # profiles/r01_sumprod_ncu_details_final.txt: sumprod_columns_kernel 3.68 GB read + 2.10 GB written per launch (default EM family)
-FILL_TRAFFIC_BYTES = 1.36e9   # profiles/r02_fill_chain_ncu_details.txt: fill_chain_kernel<5> 0.33 GB read + 1.04 GB written per launch (default family)
+FILL_TRAFFIC_BYTES = 1.387e9   # profiles/r02_fill_chain2_ncu_details.txt: fill_chain2_kernel<5> 0.348 GB read + 1.039 GB written per launch (default family)
 # FP32 work of one cell update in the chain kernel: K-term absorb dot product (K FMA) + 24 FMA/FMUL of the five state sums
 # + 9 scale/emission multiplies + 5 normalisation multiplies, FMA counted as 2 flop
 FILL_FLOP_PER_CELL = 2 * 20 + 2 * 24 + 9 + 5
@@ -459,7 +459,7 @@ def recon_leg(ctx, args, rank, world, local, barrier):
 
 # ------------------------------------------------------------------ codon leg (BASELINE.json configs[4])
 CODON_LEAVES, CODON_ROOT_LEN = 256, 600
-CODON_TENSOR_PIPE = None   # filled from profiles/r02_codon_ncu.txt once captured (sm__inst_executed_pipe_tensor / tensor-pipe utilisation)
+CODON_TENSOR_PIPE = 0.013   # profiles/r02_codon_sass_and_ncu.txt: tensor pipe active 1.3 % of leftmul_tc_kernel (24 UTCHMMA per CTA; the rest is the FP64 epilogue)
 
 
 def codon_family(seed=1):
@@ -657,7 +657,7 @@ def gpu_arm(args):
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": FILL_TRAFFIC_BYTES if n_pairs == 512 and args.family_seed == 1 else None,
-                         "kernel": "hb::fill_chain_kernel<5> (one launch = the Forward and Backward fills of all merges of the step; absorb dot products inside)",
+                         "kernel": "hb::fill_chain2_kernel<5> (one launch = the Forward and Backward fills of all merges of the step; absorb dot products inside)",
                          "launches_timed": int(kernel_launches),
                          "fp32": fp32_roofline(cells_per_step, per_launch_s),
                          "avg_launch_ms": 1e3 * per_launch_s, "algorithmic_bytes_per_cell": ALG_BYTES_PER_CELL,
