@@ -50,6 +50,9 @@ def load():
     lib.hist_profile_from_residues.argtypes = [vp, C.c_int32, C.POINTER(C.c_char_p), D.c_int32_p, C.c_char_p, C.c_int32, C.POINTER(vp)]
     lib.hist_profile_from_sequences.argtypes = [vp, C.c_int32, C.POINTER(vp), D.c_int32_p, C.c_int32, C.c_int32, C.POINTER(vp)]
     lib.hist_profile_sum_path_absorb.argtypes = [vp, D.c_double_p, D.c_double_p, D.c_double_p, D.c_double_p]
+    lib.hist_profile_sum_path_absorb_noalloc.argtypes = [vp, D.c_double_p, D.c_double_p, D.c_double_p, D.c_double_p]
+    lib.hist_noalloc_scratch_bytes.argtypes = []
+    lib.hist_noalloc_scratch_bytes.restype = C.c_int64
     lib.hist_profile_destroy.argtypes = [vp]
     lib.hist_profile_destroy.restype = None
     lib.hist_pair_prepare.argtypes = [vp, vp, vp, C.POINTER(D.PairHmmDesc), C.POINTER(D.EnvDesc), C.POINTER(vp)]
@@ -250,15 +253,16 @@ class DeviceProfile:
             self._host = D.Profile.from_sequence(seq, alphabet, components, wildcard)
         return self._host
 
-    def sum_path_absorb(self, log_cpt_weight, log_ins_prob):
-        """Profile::calcSumPathAbsorbProbs (profile.cpp:112-131): (lpCumAbs of END, per-state lpCumAbs)."""
+    def sum_path_absorb(self, log_cpt_weight, log_ins_prob, no_alloc=False):
+        """Profile::calcSumPathAbsorbProbs (profile.cpp:112-131): (lpCumAbs of END, per-state lpCumAbs).
+        no_alloc: through hist_profile_sum_path_absorb_noalloc (built-in device scratch, no cudaMalloc)."""
         n = self.host.n_states if self._host is not None else len(self._leaf[0]) + 2
         cum = np.empty(n)
         w = np.ascontiguousarray(log_cpt_weight, np.float64)
         ins = np.ascontiguousarray(log_ins_prob, np.float64)
         res = C.c_double()
-        self.ctx.check(self.ctx.lib.hist_profile_sum_path_absorb(self.h, _p(w, C.c_double), _p(ins, C.c_double), _p(cum, C.c_double),
-                                                                 C.byref(res)))
+        fn = self.ctx.lib.hist_profile_sum_path_absorb_noalloc if no_alloc else self.ctx.lib.hist_profile_sum_path_absorb
+        self.ctx.check(fn(self.h, _p(w, C.c_double), _p(ins, C.c_double), _p(cum, C.c_double), C.byref(res)))
         return res.value, cum
 
     def close(self):

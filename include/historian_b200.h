@@ -392,6 +392,22 @@ int hist_profile_fetch(hist_profile* p, uint8_t* is_emit, int32_t* trans_src, in
 int hist_profile_sum_path_absorb(hist_profile* profile, const double* log_cpt_weight, const double* log_ins_prob,
                                  double* cum, double* result);
 
+/* The same computation for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  This entry point has no counterpart in the reference.
+ * It calls no cudaMalloc / cudaFree / cudaMallocAsync and no allocating library
+ * routine: inputs are staged in, and the in-lists, lpAbs and lpCum are built in, ONE built-in device array of
+ * HIST_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until exit.  A profile whose scratch
+ * layout (about 20 B per transition + 25 B per state + 8 B per (component, residue)) exceeds that size is
+ * rejected with HIST_ERR_CAPACITY and a message naming the sizes -- use hist_profile_sum_path_absorb for it.
+ * All calls on a GPU share the array, which keeps the last call's contents (the kernel clears what must start
+ * at zero): calls that overlap on one GPU -- two contexts, two host threads -- race; serialise them.
+ * Arguments and results as hist_profile_sum_path_absorb. */
+#define HIST_NOALLOC_SCRATCH_BYTES (4u << 20)
+int hist_profile_sum_path_absorb_noalloc(hist_profile* profile, const double* log_cpt_weight, const double* log_ins_prob,
+                                         double* cum, double* result);
+/* Size of the built-in scratch array (HIST_NOALLOC_SCRATCH_BYTES of the loaded library). */
+int64_t hist_noalloc_scratch_bytes(void);
+
 /* ------------------------------------------------------------------ sum-product
  * SumProduct / AlignColSumProduct (sumprod.h:32-104, sumprod.cpp).
  * The model is passed in eigen-decomposed form (EigenModel, model.cpp:1135-1199):
