@@ -254,3 +254,46 @@ def fit(ctx, model, tree, columns, max_iter=100, min_improvement=1e-3, rank=0, w
         (ev + prior if prior is not None else ev).optimize(model, fit_indel_rates, fit_subst_rates)
         lp_last = ev.lp + lp_prior
     return model, lps
+
+
+# ------------------------------------------------------------------ #=GF LP: TreeAlignFuncs::logLikelihood
+def root_log_likelihood(model, root_row):
+    """TreeAlignFuncs::rootLogLikelihood (sampler.cpp:372-380): geometric length of the root sequence with
+    rootExtProb = insExtProb (sampler.h:52).  root_row: the root's characters over the alignment columns."""
+    root_len = int(np.count_nonzero(~np.isin(np.asarray(root_row), [ord("-"), ord(".")])))
+    ext = model.insExtProb
+    return math.log(1.0 - ext) + math.log(ext) * root_len
+
+
+def tree_align_log_likelihood(model, tree, columns, column_log_likelihoods):
+    """TreeAlignFuncs::logLikelihood(model, tree, gapped) (sampler.cpp:404-411), the `#=GF LP` line of the Stockholm
+    output (recon.cpp:1138): root + indels + substitutions.
+      indels: logBranchPathLikelihood summed over the branches (sampler.cpp:382-392, 439-449) -- slot 6 of indel_counts;
+      substitutions: the sum of the Felsenstein column likelihoods (fillUp, sampler.cpp:394-402), which the caller
+      computes -- on the device with SumProd.columns(columns, flags=0)["col_loglike"] (hist_sumprod_columns).
+    columns: uint8 [n_cols, N] characters in tree node order (root last).  Returns (lp, lp_root, lp_indels, lp_subst)."""
+    columns = np.asarray(columns)
+    lp_root = root_log_likelihood(model, columns[:, len(tree.parent) - 1])
+    lp_gaps = float(indel_counts(columns, tree.parent, tree.branch_length, model.insRate, model.delRate, model.insExtProb,
+                                 model.delExtProb)[6])
+    lp_sub = float(np.sum(column_log_likelihoods))
+    return lp_root + lp_gaps + lp_sub, lp_root, lp_gaps, lp_sub
+
+
+def read_stockholm_recon(path):
+    """A reconstruction as `historian recon -output stockholm` writes it: (names, rows, gf) with gf the #=GF tags
+    (NH = tree, LP = log-likelihood).  Rows of blocks are concatenated."""
+    rows, order, gf = {}, [], {}
+    with open(path) as f:
+        for line in f:
+            line = line.rstrip("\n")
+            if line.startswith("#=GF"):
+                _, tag, val = (line.split(None, 2) + [""])[:3]
+                gf[tag] = gf.get(tag, "") + val
+            elif line and not line.startswith("#") and not line.startswith("//"):
+                name, seq = line.split()
+                if name not in rows:
+                    order.append(name)
+                    rows[name] = ""
+                rows[name] += seq
+    return order, [rows[n] for n in order], gf

@@ -68,6 +68,14 @@ def main():
     for f in ("PF16593.fa", "PF16593.nhx", "PF16593.guide.fa"):
         shutil.copy(os.path.join(REF, "data", f), os.path.join(pf, f))
         os.chmod(os.path.join(pf, f), 0o644)
+    # the reference's own Stockholm output of that run (its #=GF LP line is what tests/test_loglike.py reproduces)
+    import subprocess
+    hist = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "bin", "historian")
+    for name, extra in (("PF16593.recon.stk", []), ("PF16593.recon.ancseq.stk", ["-ancseq"])):
+        txt = subprocess.run([hist, "recon", "-seqs", os.path.join(pf, "PF16593.fa"), "-tree", os.path.join(pf, "PF16593.nhx"), "-output",
+                              "stockholm"] + extra, stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, check=True).stdout
+        txt = "\n".join("#=GF ID             PF16593.fa" if l.startswith("#=GF ID") else l for l in txt.split("\n"))
+        open(os.path.join(pf, name), "w").write(txt)
     print("pf16593:", os.listdir(pf))
 
 
