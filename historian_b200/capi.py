@@ -40,6 +40,8 @@ def load():
     lib.hist_ctx_synchronize.argtypes = [vp]
     lib.hist_ctx_launch_count.argtypes = [vp]
     lib.hist_ctx_launch_count.restype = C.c_int64
+    lib.hist_ctx_h2d_bytes.argtypes = [vp]
+    lib.hist_ctx_h2d_bytes.restype = C.c_int64
     lib.hist_ctx_set_timing.argtypes = [vp, C.c_int]
     lib.hist_ctx_fill_time_ms.argtypes = [vp, D.c_double_p, D.c_int64_p]
     lib.hist_profile_upload.argtypes = [vp, C.POINTER(D.ProfileDesc), C.POINTER(vp)]
@@ -143,6 +145,11 @@ class Context:
     @property
     def launch_count(self):
         return int(self.lib.hist_ctx_launch_count(self.h))
+
+    @property
+    def h2d_bytes(self):
+        """Bytes copied host -> device so far for profiles and DPMatrix constructors (hist_ctx_h2d_bytes)."""
+        return int(self.lib.hist_ctx_h2d_bytes(self.h))
 
     def set_timing(self, enabled=True):
         self.check(self.lib.hist_ctx_set_timing(self.h, int(enabled)))

@@ -16,6 +16,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <limits>
+#include <climits>
 
 #include <atomic>
 #include <condition_variable>
@@ -284,6 +285,282 @@ __global__ void count_cells_kernel(PairDev* const* __restrict__ pairs) {
   if (threadIdx.x == 0 && s_cnt) atomicAdd(P.n_cells, s_cnt);
 }
 
+
+// ------------------------------------------------------------------ profile structure images
+// Offsets of the arrays of a ProfImage inside its allocation: the same function places them on the host (images built
+// from host lists) and in chain_image_kernel (leaf chains, generated on the device).
+struct ImgOff {
+  size_t flags, t_src, t_dst, t_lp, in_off, in_idx, ao_off, ao_idx, no_off, no_idx, leaf_pos, near_start, near_end, slot_start,
+      slot_end, start_rows, end_cols, bytes;
+};
+__host__ __device__ inline size_t img_take(size_t& b, size_t bytes) {
+  const size_t off = b;
+  b = (b + bytes + 15) & ~(size_t)15;
+  return off;
+}
+__host__ __device__ inline ImgOff image_offsets(int n, int nt) {
+  ImgOff o;
+  size_t b = 0;
+  const size_t nt1 = nt > 0 ? nt : 1, ns = (size_t)n;
+  o.t_lp = img_take(b, nt1 * sizeof(double));
+  o.t_src = img_take(b, nt1 * sizeof(int));
+  o.t_dst = img_take(b, nt1 * sizeof(int));
+  o.in_off = img_take(b, (ns + 1) * sizeof(int));
+  o.in_idx = img_take(b, nt1 * sizeof(int));
+  o.ao_off = img_take(b, (ns + 1) * sizeof(int));
+  o.ao_idx = img_take(b, nt1 * sizeof(int));
+  o.no_off = img_take(b, (ns + 1) * sizeof(int));
+  o.no_idx = img_take(b, nt1 * sizeof(int));
+  o.leaf_pos = img_take(b, ns * sizeof(int));
+  o.slot_start = img_take(b, ns * sizeof(int));
+  o.slot_end = img_take(b, ns * sizeof(int));
+  o.start_rows = img_take(b, ns * sizeof(int));
+  o.end_cols = img_take(b, ns * sizeof(int));
+  o.flags = img_take(b, ns);
+  o.near_start = img_take(b, ns);
+  o.near_end = img_take(b, ns);
+  o.bytes = (b + 255) & ~(size_t)255;
+  return o;
+}
+__host__ __device__ inline ProfImage image_at(char* base, const ImgOff& o) {
+  ProfImage im;
+  im.flags = (uint8_t*)(base + o.flags);
+  im.t_src = (int*)(base + o.t_src); im.t_dst = (int*)(base + o.t_dst); im.t_lp = (double*)(base + o.t_lp);
+  im.in_off = (int*)(base + o.in_off); im.in_idx = (int*)(base + o.in_idx);
+  im.ao_off = (int*)(base + o.ao_off); im.ao_idx = (int*)(base + o.ao_idx);
+  im.no_off = (int*)(base + o.no_off); im.no_idx = (int*)(base + o.no_idx);
+  im.leaf_pos = (int*)(base + o.leaf_pos);
+  im.near_start = (uint8_t*)(base + o.near_start); im.near_end = (uint8_t*)(base + o.near_end);
+  im.slot_start = (int*)(base + o.slot_start); im.slot_end = (int*)(base + o.slot_end);
+  im.start_rows = (int*)(base + o.start_rows); im.end_cols = (int*)(base + o.end_cols);
+  return im;
+}
+
+// A leaf (Profile(components, alphabet, FastSeq, row), profile.cpp:23-76) is the chain
+// START -> residue 1 -> ... -> residue L -> END with log-weight 0 transitions: transition t enters state t+1; it is an
+// absorbing out-edge of state t unless it enters END (t == n-2), which makes it the one null out-edge.  Every list of
+// the image is arithmetic on the index.  grid = (chunks, profiles); requires n >= 3.
+struct ChainImgJob {
+  long long off;
+  int n, pad;
+};
+__global__ void chain_image_kernel(char* arena, const ChainImgJob* __restrict__ jobs) {
+  const ChainImgJob J = jobs[blockIdx.y];
+  const int n = J.n, nt = n - 1;
+  const ProfImage im = image_at(arena + J.off, image_offsets(n, nt));
+  for (int k = blockIdx.x * blockDim.x + threadIdx.x; k <= n; k += gridDim.x * blockDim.x) {
+    im.in_off[k] = max(0, k - 1);
+    im.ao_off[k] = min(k, n - 2);
+    im.no_off[k] = k > n - 2 ? 1 : 0;
+    if (k < n) {
+      const bool emit = k >= 1 && k <= n - 2;
+      int f = 0;
+      if (emit) f |= F_EMIT;
+      if (k != n - 2) f |= F_READY;               // state n-2 has the null transition into END
+      if (emit || k == 0) f |= F_EMIT_OR_START;
+      im.flags[k] = (uint8_t)f;
+      im.leaf_pos[k] = min(k, n - 2);             // seqCoords of the leaf row (profile.cpp:33-36, 49)
+      im.near_start[k] = k == 0;
+      im.near_end[k] = k == n - 2;
+      im.slot_start[k] = k == 0 ? 0 : -1;
+      im.slot_end[k] = k == n - 2 ? 0 : -1;
+    }
+    if (k < nt) {
+      im.t_src[k] = k;
+      im.t_dst[k] = k + 1;
+      im.t_lp[k] = 0.0;
+      im.in_idx[k] = k;
+    }
+    if (k < n - 2) im.ao_idx[k] = k;
+    if (k == 0) {
+      im.no_idx[0] = n - 2;
+      im.start_rows[0] = 0;
+      im.end_cols[0] = n - 2;
+    }
+  }
+}
+
+// ------------------------------------------------------------------ band keys and the anti-diagonal layout
+// Inclusive scan of v[0..n) in place by the whole CTA (forward, or from the end when REVERSE): every thread folds a
+// contiguous chunk, the chunk totals are combined through shared memory, the chunk is folded again from its prefix.
+struct OpMax { __device__ int operator()(int a, int b) const { return max(a, b); } };
+struct OpMin { __device__ int operator()(int a, int b) const { return min(a, b); } };
+struct OpAdd { __device__ int operator()(int a, int b) const { return a + b; } };
+template <bool REVERSE, class Op>
+__device__ void block_scan(int* v, int n, int identity, Op op, int* sm) {
+  const int T = blockDim.x, t = threadIdx.x;
+  const int chunk = (n + T - 1) / T, b = min(n, t * chunk), e = min(n, b + chunk);
+  __syncthreads();   // v was written by other threads; sm may still be read by the previous scan
+  int acc = identity;
+  for (int q = b; q < e; ++q) acc = op(acc, v[REVERSE ? n - 1 - q : q]);
+  sm[t] = acc;
+  __syncthreads();
+  acc = identity;
+  for (int q = 0; q < t; ++q) acc = op(acc, sm[q]);
+  for (int q = b; q < e; ++q) {
+    const int idx = REVERSE ? n - 1 - q : q;
+    acc = op(acc, v[idx]);
+    v[idx] = acc;
+  }
+  __syncthreads();
+}
+
+// One CTA per pair.  Band keys (forward.cpp:36-42, alignpath.h:56-61), the bounding column interval of every row, its
+// monotone hull (so that every anti-diagonal meets the band in ONE interval of i), and the per-diagonal layout records
+// with their plane offsets; integer work, bit-exact with the reference's inEnvelope predicate.  The totals go to
+// P.layout_out: the host sizes the cell planes from them.
+__global__ void __launch_bounds__(256) pair_layout_kernel(PairDev* const* __restrict__ pairs) {
+  PairDev& P = *pairs[blockIdx.x];
+  __shared__ int sm[256];
+  __shared__ unsigned long long smu[256];
+  __shared__ int s_err;
+  const int T = blockDim.x, t = threadIdx.x;
+  const int nx = P.x.n, ny = P.y.n, NI = nx - 1, NJ = ny - 1, md = P.max_dist;
+  int* xkey = P.x.key;
+  int* ykey = P.y.key;
+  int* jlo = P.scratch;
+  int* jhi = jlo + NI;
+  int* rows = jhi + NI;
+  int* cnt = rows + NI;
+  int* pmax = cnt + NI;
+  int* smin = pmax + NJ;
+  LayoutOut* out = P.layout_out;
+  if (t == 0) s_err = 0;
+  __syncthreads();
+  for (int i = t; i < nx; i += T) {
+    int key = 0;
+    if (md >= 0) {
+      const int pos = i == 0 ? 0 : P.x_leaf_pos[i];
+      if (pos < 0 || pos > P.env_len1) {
+        if (atomicCAS(&s_err, 0, 1) == 0) { out->err_state = i; out->err_pos = pos; }
+      } else {
+        key = P.env_k1[pos];
+      }
+    }
+    xkey[i] = key;
+  }
+  for (int j = t; j < ny; j += T) {
+    int key = 0;
+    if (md >= 0) {
+      const int pos = j == 0 ? 0 : P.y_leaf_pos[j];
+      if (pos < 0 || pos > P.env_len2) {
+        if (atomicCAS(&s_err, 0, 2) == 0) { out->err_state = j; out->err_pos = pos; }
+      } else {
+        key = P.env_k2[pos];
+      }
+    }
+    ykey[j] = key;
+  }
+  __syncthreads();
+  if (s_err) {
+    if (t == 0) { out->err = s_err; out->n_stored = 0; out->max_threads = 1; out->max_width = 0; }
+    return;
+  }
+  if (md < 0) {
+    for (int i = t; i < NI; i += T) { jlo[i] = 0; jhi[i] = NJ - 1; }
+  } else {
+    // prefix max / suffix min of the y keys make "first j with key >= a" / "last j with key <= b" binary-searchable
+    for (int j = t; j < NJ; j += T) { pmax[j] = ykey[j]; smin[j] = ykey[j]; }
+    block_scan<false>(pmax, NJ, INT_MIN, OpMax(), sm);
+    block_scan<true>(smin, NJ, INT_MAX, OpMin(), sm);
+    for (int i = t; i < NI; i += T) {
+      const int a = xkey[i] - md, b = xkey[i] + md;
+      int lo = 0, hi = NJ;   // first j: pmax[j] >= a
+      while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (pmax[mid] < a) lo = mid + 1; else hi = mid;
+      }
+      jlo[i] = lo;
+      lo = 0; hi = NJ;       // first j: smin[j] > b
+      while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (smin[mid] <= b) lo = mid + 1; else hi = mid;
+      }
+      jhi[i] = lo - 1;
+    }
+  }
+  __syncthreads();
+  // monotone hull over the non-empty rows: jhi becomes its running maximum, jlo its running minimum from the end
+  for (int i = t; i < NI; i += T) rows[i] = jlo[i] <= jhi[i] ? jhi[i] : -1;
+  block_scan<false>(rows, NI, -1, OpMax(), sm);
+  for (int i = t; i < NI; i += T)
+    if (jlo[i] <= jhi[i]) jhi[i] = rows[i];
+  __syncthreads();
+  for (int i = t; i < NI; i += T) rows[i] = jlo[i] <= jhi[i] ? jlo[i] : NJ;
+  block_scan<true>(rows, NI, NJ, OpMin(), sm);
+  for (int i = t; i < NI; i += T)
+    if (jlo[i] <= jhi[i]) jlo[i] = rows[i];
+  __syncthreads();
+  // the non-empty rows, ascending
+  for (int i = t; i < NI; i += T) cnt[i] = jlo[i] <= jhi[i] ? 1 : 0;
+  block_scan<false>(cnt, NI, 0, OpAdd(), sm);
+  const int nrows = cnt[NI - 1];
+  for (int i = t; i < NI; i += T)
+    if (jlo[i] <= jhi[i]) rows[cnt[i] - 1] = i;
+  __syncthreads();
+  // Over the non-empty rows i + jlo[i] and i + jhi[i] are strictly increasing, so the rows meeting diagonal d form a
+  // contiguous run of `rows`, found by two binary searches.
+  const int nDiag = NI + NJ - 1, nS = P.nS, nE = P.nE;
+  DiagInfo* dinfo = P.dinfo;
+  int maxW = 0;
+  for (int d = t; d < nDiag; d += T) {
+    int lo = 0, hi = nrows;   // first r: rows[r] + jhi[rows[r]] >= d
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1, r = rows[mid];
+      if (r + jhi[r] < d) lo = mid + 1; else hi = mid;
+    }
+    const int first = lo;
+    lo = 0; hi = nrows;       // first r: rows[r] + jlo[rows[r]] > d
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1, r = rows[mid];
+      if (r + jlo[r] <= d) lo = mid + 1; else hi = mid;
+    }
+    DiagInfo di;
+    di.ilo = 0; di.width = 0; di.off = 0; di.pad = 0;
+    if (first < lo) { di.ilo = rows[first]; di.width = rows[lo - 1] - rows[first] + 1; }
+    dinfo[d] = di;
+    maxW = max(maxW, di.width);
+  }
+  __syncthreads();
+  // plane offsets: exclusive sum of nS + width + nE over the diagonals
+  {
+    const int chunk = (nDiag + T - 1) / T, b = min(nDiag, t * chunk), e = min(nDiag, b + chunk);
+    unsigned long long acc = 0;
+    for (int d = b; d < e; ++d) acc += (unsigned long long)(nS + dinfo[d].width + nE);
+    smu[t] = acc;
+    sm[t] = maxW;
+    __syncthreads();
+    acc = 0;
+    for (int q = 0; q < t; ++q) acc += smu[q];
+    for (int d = b; d < e; ++d) {
+      dinfo[d].off = (unsigned)acc;
+      acc += (unsigned long long)(nS + dinfo[d].width + nE);
+    }
+    if (t == 0) {
+      unsigned long long total = 0;
+      int w = 0;
+      for (int q = 0; q < T; ++q) { total += smu[q]; w = max(w, sm[q]); }
+      out->n_stored = total;
+      out->max_width = w;
+      out->max_threads = max(1, nS + w + nE);
+      out->err = 0;
+      P.n_stored = (unsigned)total;
+      P.max_threads = max(1, nS + w + nE);
+    }
+  }
+}
+
+// The cell planes are allocated once the layout totals are back on the host: patch their addresses into the descriptors.
+struct PlanePlace {
+  float4* fA; float2* fB; float* absorb; float4* bA; float2* bB;
+};
+__global__ void place_planes_kernel(PairDev* const* __restrict__ pairs, const PlanePlace* __restrict__ pl, int n) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  PairDev& P = *pairs[k];
+  P.fA = pl[k].fA; P.fB = pl[k].fB; P.absorb = pl[k].absorb; P.bA = pl[k].bA; P.bB = pl[k].bB;
+}
+
 }  // namespace hb
 
 using namespace hb;
@@ -420,6 +697,10 @@ extern "C" int hist_ctx_create(int device, hist_ctx** out) {
   ctx->staging2_bytes = 0;
   cudaEventCreateWithFlags(&ctx->ev_stage[0], cudaEventDisableTiming);
   cudaEventCreateWithFlags(&ctx->ev_stage[1], cudaEventDisableTiming);
+  ctx->staging_img = nullptr;
+  ctx->staging_img_bytes = 0;
+  cudaEventCreateWithFlags(&ctx->ev_img, cudaEventDisableTiming);
+  ctx->h2d_bytes = 0;
   ctx->stream2 = nullptr;
   ctx->ev_fork = ctx->ev_join = nullptr;
   e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
@@ -452,6 +733,8 @@ extern "C" void hist_ctx_destroy(hist_ctx* ctx) {
   for (auto& e : ctx->fill_events) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
   if (ctx->staging) cudaFreeHost(ctx->staging);
   if (ctx->staging2) cudaFreeHost(ctx->staging2);
+  if (ctx->staging_img) cudaFreeHost(ctx->staging_img);
+  cudaEventDestroy(ctx->ev_img);
   cudaEventDestroy(ctx->ev_stage[0]);
   cudaEventDestroy(ctx->ev_stage[1]);
   if (ctx->stream2) { cudaStreamSynchronize(ctx->stream2); cudaStreamDestroy(ctx->stream2); }
@@ -491,6 +774,7 @@ extern "C" int hist_ctx_fill_time_ms(hist_ctx* ctx, double* total_ms, int64_t* n
   return HIST_OK;
 }
 extern "C" int64_t hist_ctx_launch_count(const hist_ctx* ctx) { return ctx ? ctx->launches : 0; }
+extern "C" int64_t hist_ctx_h2d_bytes(const hist_ctx* ctx) { return ctx ? ctx->h2d_bytes : 0; }
 
 // ------------------------------------------------------------------ profiles
 extern "C" int hist_profile_upload(hist_ctx* ctx, const hist_profile_desc* d, hist_profile** out) {
@@ -538,6 +822,7 @@ extern "C" int hist_profile_upload(hist_ctx* ctx, const hist_profile_desc* d, hi
   p->arena = nullptr;
   int rc = check_cuda(ctx, cudaMallocAsync((void**)&p->d_lp_absorb, bytes, ctx->stream), "cudaMallocAsync(lp_absorb)");
   if (!rc) rc = check_cuda(ctx, cudaMemcpyAsync(p->d_lp_absorb, d->lp_absorb, bytes, cudaMemcpyHostToDevice, ctx->stream), "H2D lp_absorb");
+  ctx->h2d_bytes += (long long)bytes;
   // the descriptor is only borrowed for the duration of the call
   if (!rc) rc = check_cuda(ctx, cudaStreamSynchronize(ctx->stream), "sync after profile upload");
   if (rc) {
@@ -619,6 +904,7 @@ static int leaf_profiles(hist_ctx* ctx, int32_t n, const int8_t* const* tokens, 
     memcpy(ctx->staging + so_st, state_off.data(), off_bytes);
     rc = check_cuda(ctx, cudaMemcpyAsync(arena->dev + tok_off, ctx->staging, n_tok, cudaMemcpyHostToDevice, ctx->stream), "H2D tokens");
     if (!rc) rc = check_cuda(ctx, cudaMemcpyAsync(arena->dev + so_off, ctx->staging + so_st, off_bytes, cudaMemcpyHostToDevice, ctx->stream), "H2D offsets");
+    ctx->h2d_bytes += (long long)(n_tok + off_bytes);
   }
   if (!rc) {
     const long long work = state_off[n] * (long long)K;
@@ -695,6 +981,7 @@ extern "C" void hist_profile_destroy(hist_profile* p) {
   cudaSetDevice(p->ctx->device);
   if (p->arena) arena_release(p->ctx, p->arena);
   else if (p->d_lp_absorb) cudaFreeAsync(p->d_lp_absorb, p->ctx->stream);
+  if (p->img_arena) arena_release(p->ctx, p->img_arena);
   delete p;
 }
 
@@ -712,6 +999,7 @@ extern "C" void hist_profiles_destroy(hist_profile* const* profiles, int32_t n) 
     cudaSetDevice(p->ctx->device);
     if (p->arena) arena_release(p->ctx, p->arena);
     else if (p->d_lp_absorb) cudaFreeAsync(p->d_lp_absorb, p->ctx->stream);
+    if (p->img_arena) arena_release(p->ctx, p->img_arena);
     gone.push_back(p);
   }
   parallel_for((int)gone.size(), 64, [&](int k) { delete gone[k]; });
@@ -739,53 +1027,30 @@ struct Layout {
 };
 
 struct SideHost {
-  std::vector<uint8_t> flags, near_;
-  std::vector<int> in_off, in_idx, ao_off, ao_idx, no_off, no_idx, key, slot;
+  std::vector<uint8_t> flags;
+  std::vector<int> in_off, in_idx, ao_off, ao_idx, no_off, no_idx;
 };
 
-struct SideOff {  // h_*: offsets in the host-initialised part, d_*: in the device-only part
-  size_t h_flags, h_t_src, h_t_dst, h_t_lp, h_in_off, h_in_idx, h_ao_off, h_ao_idx, h_no_off, h_no_idx, h_key, h_near, h_slot;
-  size_t d_t_m, d_t_e, d_ex, d_rs, d_ins, d_H, d_sub, d_rootsub, d_insl, d_fm_a, d_fm_b, d_emis, d_in_edges, d_bm, d_ao_edges, d_no_edges, d_cf, d_cb;
+struct SideOff {  // offsets in the device-only part of the pair arena
+  size_t d_key, d_t_m, d_t_e, d_ex, d_rs, d_ins, d_H, d_sub, d_rootsub, d_insl, d_fm_a, d_fm_b, d_emis, d_in_edges, d_bm, d_ao_edges, d_no_edges, d_cf, d_cb;
 };
 
 struct PairBuild {
   hist_pair* pr = nullptr;
-  SideHost sx, sy;
   Layout host, dev;
   SideOff ox, oy;
-  size_t h_start, h_end, h_dinfo, h_lsub, h_rsub, h_root, h_lins, h_rins, h_lcw, h_rcw, h_pairdev;
-  size_t d_scal, d_fA, d_fB, d_bA, d_bB, d_absorb;
+  size_t h_k1 = 0, h_k2 = 0, h_lsub = 0, h_rsub = 0, h_root = 0, h_lins = 0, h_rins = 0, h_lcw = 0, h_rcw = 0, h_pairdev = 0;
+  size_t d_dinfo = 0, d_scratch = 0;
   size_t host_base = 0, dev_base = 0;  // position of this pair's two parts in the arena
-  std::vector<int> one0 = std::vector<int>(1, 0);
+  std::vector<int> k1, k2;             // cumulativeMatches[rowPosToCol[pos]] of the two guide rows
+  size_t plane_base = 0;               // position of this pair's cell planes in the plane arena
+  size_t p_fA = 0, p_fB = 0, p_absorb = 0, p_bA = 0, p_bB = 0;
 };
 
+// The transition lists of a profile (the reference's ProfileState::in / absorbOut / nullOut, profile.h:13-40)
+// and its state flags, from the host transition arrays.
 void build_side_lists(const hist_profile* p, SideHost& s) {
   const int n = p->n, nt = p->nt;
-  if (p->chain) {
-    // a leaf: START -> residue 1 -> ... -> residue L -> END.  Transition t enters state t+1; it is an absorbing
-    // out-edge of state t unless it enters END (t == n-2), which makes it the one null out-edge.
-    s.in_off.resize(n + 1); s.ao_off.resize(n + 1); s.no_off.resize(n + 1);
-    for (int k = 0; k <= n; ++k) {
-      s.in_off[k] = std::max(0, k - 1);
-      s.ao_off[k] = std::min(k, n - 2);
-      s.no_off[k] = k > n - 2 ? 1 : 0;
-    }
-    s.in_idx.resize(std::max(1, nt));
-    for (int q = 0; q < nt; ++q) s.in_idx[q] = q;
-    s.ao_idx.resize(std::max(1, n - 2));
-    for (int q = 0; q < n - 2; ++q) s.ao_idx[q] = q;
-    if (n == 2) s.ao_idx[0] = 0;
-    s.no_idx.assign(1, n - 2);
-    s.flags.resize(n);
-    for (int i = 0; i < n; ++i) {
-      uint8_t f = 0;
-      if (p->is_emit[i]) f |= F_EMIT;
-      if (i != n - 2 || p->empty) f |= F_READY;
-      if (p->is_emit[i] || i == 0) f |= F_EMIT_OR_START;
-      s.flags[i] = f;
-    }
-    return;
-  }
   std::vector<int> in_cnt(n + 1, 0), ao_cnt(n + 1, 0), no_cnt(n + 1, 0);
   for (int t = 0; t < nt; ++t) {
     ++in_cnt[p->t_dst[t] + 1];
@@ -815,10 +1080,140 @@ void build_side_lists(const hist_profile* p, SideHost& s) {
   }
 }
 
-// Host part of the DPMatrix constructor for one pair: transition lists, band keys, edge flags and
-// the anti-diagonal layout, all O(states + diagonals).  Fills b.host / b.dev layouts.
-int build_pair_host(hist_ctx* ctx, const hist_profile* x, const hist_profile* y, const hist_pairhmm_desc* hmm,
-                    const hist_env_desc* env, bool want_bwd, PairBuild& b) {
+// Writes the structure image of a profile (host lists) into `base`, an image-sized block of host memory laid out by
+// image_offsets; returns the edge counts.  The edge flags are the reference's xNearStart / yNearEnd (forward.cpp:58-65).
+int build_image_host(hist_ctx* ctx, const hist_profile* p, char* base, int* nS_out, int* nE_out) {
+  const int n = p->n, nt = p->nt;
+  SideHost s;
+  build_side_lists(p, s);
+  for (int i = 0; i < n; ++i)
+    if (s.in_off[i + 1] - s.in_off[i] > HB_MAX_DEGREE || s.ao_off[i + 1] - s.ao_off[i] > HB_MAX_DEGREE)
+      return set_err(ctx, HIST_ERR_ARG, "hist_pair_prepare: state %d has more than %d transitions", i, HB_MAX_DEGREE);
+  const ImgOff off = image_offsets(n, nt);
+  memset(base, 0, off.bytes);
+  const ProfImage im = image_at(base, off);
+  memcpy(im.flags, s.flags.data(), n);
+  if (nt) {
+    memcpy(im.t_src, p->t_src.data(), (size_t)nt * sizeof(int));
+    memcpy(im.t_dst, p->t_dst.data(), (size_t)nt * sizeof(int));
+    memcpy(im.t_lp, p->t_lp.data(), (size_t)nt * sizeof(double));
+  }
+  memcpy(im.in_off, s.in_off.data(), (size_t)(n + 1) * sizeof(int));
+  memcpy(im.ao_off, s.ao_off.data(), (size_t)(n + 1) * sizeof(int));
+  memcpy(im.no_off, s.no_off.data(), (size_t)(n + 1) * sizeof(int));
+  memcpy(im.in_idx, s.in_idx.data(), (size_t)s.in_off[n] * sizeof(int));
+  memcpy(im.ao_idx, s.ao_idx.data(), (size_t)s.ao_off[n] * sizeof(int));
+  memcpy(im.no_idx, s.no_idx.data(), (size_t)s.no_off[n] * sizeof(int));
+  if (!p->leaf_pos.empty()) memcpy(im.leaf_pos, p->leaf_pos.data(), (size_t)n * sizeof(int));
+  im.near_start[0] = 1;
+  for (int i = 0; i < n; ++i)
+    if (im.near_start[i])
+      for (int q = s.no_off[i]; q < s.no_off[i + 1]; ++q) im.near_start[p->t_dst[s.no_idx[q]]] = 1;
+  for (int q = s.in_off[n - 1]; q < s.in_off[n]; ++q) im.near_end[p->t_src[s.in_idx[q]]] = 1;
+  int nS = 0, nE = 0;
+  for (int i = 0; i < n; ++i) {   // rows / columns 0 .. n-2 hold cells
+    im.slot_start[i] = -1;
+    im.slot_end[i] = -1;
+    if (i < n - 1 && im.near_start[i]) { im.slot_start[i] = nS; im.start_rows[nS++] = i; }
+    if (i < n - 1 && im.near_end[i]) { im.slot_end[i] = nE; im.end_cols[nE++] = i; }
+  }
+  *nS_out = nS;
+  *nE_out = nE;
+  return HIST_OK;
+}
+
+int ensure_pinned(hist_ctx* ctx, char*& buf, size_t& have, size_t bytes) {
+  if (have >= bytes) return HIST_OK;
+  if (buf) {
+    HB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    cudaFreeHost(buf);
+    buf = nullptr;
+    have = 0;
+  }
+  const size_t want = std::max(bytes + bytes / 4, (size_t)1 << 20);
+  HB_CUDA(ctx, cudaMallocHost((void**)&buf, want));
+  have = want;
+  return HIST_OK;
+}
+
+void arena_release(hist_ctx* ctx, hb_arena* a);
+
+// Structure images for every profile of the list that has none yet: one allocation, one transfer (the images built from
+// host lists, and the job records of the leaf chains, whose images chain_image_kernel then generates on the device).
+int ensure_images(hist_ctx* ctx, const hist_profile* const* xs, const hist_profile* const* ys, int n) {
+  std::vector<hist_profile*> need;
+  for (int k = 0; k < 2 * n; ++k) {
+    hist_profile* p = const_cast<hist_profile*>(k < n ? xs[k] : ys[k - n]);
+    if (p && p->ctx == ctx && !p->img_arena) need.push_back(p);
+  }
+  if (need.empty()) return HIST_OK;
+  std::sort(need.begin(), need.end());
+  need.erase(std::unique(need.begin(), need.end()), need.end());
+  // a leaf chain whose closest-leaf positions are the leaf's own (or absent) gets its image from chain_image_kernel
+  auto on_device = [](const hist_profile* p) {
+    if (!p->chain || p->n < 3) return false;
+    for (size_t i = 0; i < p->leaf_pos.size(); ++i)
+      if (p->leaf_pos[i] != std::min((int)i, p->n - 2)) return false;
+    return true;
+  };
+  // host-built images first (they are the transferred part), then the device-generated ones
+  const int m = (int)need.size();
+  std::vector<size_t> base(m + 1, 0);
+  const int n_host = (int)(std::stable_partition(need.begin(), need.end(), [&](hist_profile* p) { return !on_device(p); }) - need.begin());
+  int max_chain_n = 0;
+  for (int k = 0; k < m; ++k) {
+    const hist_profile* p = need[k];
+    base[k + 1] = base[k] + image_offsets(p->n, p->nt).bytes;
+    if (k >= n_host) max_chain_n = std::max(max_chain_n, p->n);
+  }
+  const int n_chain = m - n_host;
+  const size_t host_bytes = base[n_host], jobs_off = base[m], jobs_bytes = (size_t)n_chain * sizeof(ChainImgJob);
+  const size_t total = jobs_off + (jobs_bytes + 255) / 256 * 256 + 256;
+  hb_arena* arena = new hb_arena{nullptr, total, 0};
+  int rc = check_cuda(ctx, cudaMallocAsync((void**)&arena->dev, total, ctx->stream), "cudaMallocAsync(profile images)");
+  if (!rc) rc = ensure_pinned(ctx, ctx->staging_img, ctx->staging_img_bytes, host_bytes + jobs_bytes + 256);
+  if (!rc) rc = check_cuda(ctx, cudaEventSynchronize(ctx->ev_img), "wait for the image staging buffer");
+  std::vector<int> nS(m, 1), nE(m, 1);
+  if (!rc) {
+    std::vector<int> rcs(std::max(1, n_host), 0);
+    char* st = ctx->staging_img;
+    parallel_for(n_host, 8, [&](int k) { rcs[k] = build_image_host(ctx, need[k], st + base[k], &nS[k], &nE[k]); });
+    for (int k = 0; k < n_host && !rc; ++k) rc = rcs[k];
+    ChainImgJob* jobs = (ChainImgJob*)(st + host_bytes);
+    for (int k = 0; k < n_chain; ++k) jobs[k] = ChainImgJob{(long long)base[n_host + k], need[n_host + k]->n, 0};
+  }
+  if (!rc && host_bytes) rc = check_cuda(ctx, cudaMemcpyAsync(arena->dev, ctx->staging_img, host_bytes, cudaMemcpyHostToDevice, ctx->stream), "H2D profile images");
+  if (!rc && n_chain) {
+    rc = check_cuda(ctx, cudaMemcpyAsync(arena->dev + jobs_off, ctx->staging_img + host_bytes, jobs_bytes, cudaMemcpyHostToDevice, ctx->stream), "H2D chain jobs");
+    if (!rc) {
+      chain_image_kernel<<<dim3((max_chain_n + 1 + 255) / 256, n_chain), 256, 0, ctx->stream>>>(arena->dev, (const ChainImgJob*)(arena->dev + jobs_off));
+      ctx->launches += 1;
+      rc = check_cuda(ctx, cudaGetLastError(), "chain_image_kernel");
+    }
+  }
+  if (!rc) rc = check_cuda(ctx, cudaEventRecord(ctx->ev_img, ctx->stream), "record image staging event");
+  if (rc) {
+    if (arena->dev) cudaFreeAsync(arena->dev, ctx->stream);
+    delete arena;
+    return rc;
+  }
+  ctx->h2d_bytes += (long long)(host_bytes + jobs_bytes);
+  for (int k = 0; k < m; ++k) {
+    hist_profile* p = need[k];
+    p->img = image_at(arena->dev + base[k], image_offsets(p->n, p->nt));
+    p->img_arena = arena;
+    p->nS = nS[k];
+    p->nE = nE[k];
+    ++arena->refs;
+  }
+  return HIST_OK;
+}
+
+// Host part of the DPMatrix constructor for one pair: argument checks, the composed key tables of the two guide rows and
+// the byte layout of the pair's arrays.  Band keys, edge slots and the anti-diagonal layout are computed on the device
+// (pair_layout_kernel) from the profiles' structure images.
+int plan_pair(hist_ctx* ctx, const hist_profile* x, const hist_profile* y, const hist_pairhmm_desc* hmm,
+              const hist_env_desc* env, PairBuild& b) {
   if (!x || !y || !hmm) return set_err(ctx, HIST_ERR_ARG, "hist_pair_prepare: NULL argument");
   if (x->ctx != ctx || y->ctx != ctx) return set_err(ctx, HIST_ERR_ARG, "hist_pair_prepare: profile belongs to another context");
   if (x->A != hmm->alph_size || y->A != hmm->alph_size || x->C != hmm->components || y->C != hmm->components)
@@ -831,80 +1226,24 @@ int build_pair_host(hist_ctx* ctx, const hist_profile* x, const hist_profile* y,
       return set_err(ctx, HIST_ERR_ARG, "hist_pair_prepare: envelope given but profiles carry no closest_leaf_pos");
     if (!env->cumulative_matches || !env->row1_pos_to_col || !env->row2_pos_to_col)
       return set_err(ctx, HIST_ERR_ARG, "hist_pair_prepare: envelope arrays are NULL");
-  }
-  SideHost& sx = b.sx;
-  SideHost& sy = b.sy;
-  build_side_lists(x, sx);
-  build_side_lists(y, sy);
-  for (int i = 0; i < nx; ++i)
-    if (sx.in_off[i + 1] - sx.in_off[i] > HB_MAX_DEGREE || sx.ao_off[i + 1] - sx.ao_off[i] > HB_MAX_DEGREE)
-      return set_err(ctx, HIST_ERR_ARG, "hist_pair_prepare: x state %d has more than %d transitions", i, HB_MAX_DEGREE);
-  for (int j = 0; j < ny; ++j)
-    if (sy.in_off[j + 1] - sy.in_off[j] > HB_MAX_DEGREE || sy.ao_off[j + 1] - sy.ao_off[j] > HB_MAX_DEGREE)
-      return set_err(ctx, HIST_ERR_ARG, "hist_pair_prepare: y state %d has more than %d transitions", j, HB_MAX_DEGREE);
-
-  // ---- envelope keys (forward.cpp:36-42, alignpath.h:56-61) and edge flags (forward.cpp:58-65)
-  sx.key.assign(nx, 0);
-  sy.key.assign(ny, 0);
-  if (maxDist >= 0) {
-    for (int i = 0; i < nx; ++i) {
-      const int pos = i == 0 ? 0 : x->leaf_pos[i];
-      if (pos < 0 || pos > env->row1_len) return set_err(ctx, HIST_ERR_ARG, "x state %d: closest-leaf position %d outside guide row (len %d)", i, pos, env->row1_len);
-      sx.key[i] = env->cumulative_matches[env->row1_pos_to_col[pos]];
+    if (env->row1_len < 0 || env->row2_len < 0 || env->n_cols < 0) return set_err(ctx, HIST_ERR_ARG, "hist_pair_prepare: negative envelope sizes");
+    b.k1.resize((size_t)env->row1_len + 1);
+    b.k2.resize((size_t)env->row2_len + 1);
+    for (int q = 0; q <= env->row1_len; ++q) {
+      const int col = env->row1_pos_to_col[q];
+      if (col < 0 || col > env->n_cols) return set_err(ctx, HIST_ERR_ARG, "hist_pair_prepare: row1_pos_to_col[%d] = %d outside the guide alignment", q, col);
+      b.k1[q] = env->cumulative_matches[col];
     }
-    for (int j = 0; j < ny; ++j) {
-      const int pos = j == 0 ? 0 : y->leaf_pos[j];
-      if (pos < 0 || pos > env->row2_len) return set_err(ctx, HIST_ERR_ARG, "y state %d: closest-leaf position %d outside guide row (len %d)", j, pos, env->row2_len);
-      sy.key[j] = env->cumulative_matches[env->row2_pos_to_col[pos]];
+    for (int q = 0; q <= env->row2_len; ++q) {
+      const int col = env->row2_pos_to_col[q];
+      if (col < 0 || col > env->n_cols) return set_err(ctx, HIST_ERR_ARG, "hist_pair_prepare: row2_pos_to_col[%d] = %d outside the guide alignment", q, col);
+      b.k2[q] = env->cumulative_matches[col];
     }
-  }
-  sx.near_.assign(nx, 0);
-  sy.near_.assign(ny, 0);
-  sx.near_[0] = 1;
-  for (int i = 0; i < nx; ++i)
-    if (sx.near_[i])
-      for (int q = sx.no_off[i]; q < sx.no_off[i + 1]; ++q) sx.near_[x->t_dst[sx.no_idx[q]]] = 1;
-  for (int q = sy.in_off[ny - 1]; q < sy.in_off[ny]; ++q) sy.near_[y->t_src[sy.in_idx[q]]] = 1;
-
-  // ---- anti-diagonal layout.  Cells exist for 0<=i<=nx-2, 0<=j<=ny-2.
-  const int NI = nx - 1, NJ = ny - 1;  // number of rows / columns
-  std::vector<int> jlo(NI), jhi(NI);   // bounding column interval of the in-range cells of each row (jlo>jhi: empty)
-  if (maxDist < 0) {
-    for (int i = 0; i < NI; ++i) { jlo[i] = 0; jhi[i] = NJ - 1; }
   } else {
-    // prefix max / suffix min of the y keys make "first j with key >= a" / "last j with key <= b" binary-searchable
-    std::vector<int> pmax(NJ), smin(NJ);
-    for (int j = 0; j < NJ; ++j) pmax[j] = j ? std::max(pmax[j - 1], sy.key[j]) : sy.key[0];
-    for (int j = NJ - 1; j >= 0; --j) smin[j] = j < NJ - 1 ? std::min(smin[j + 1], sy.key[j]) : sy.key[NJ - 1];
-    for (int i = 0; i < NI; ++i) {
-      const int a = sx.key[i] - maxDist, bb = sx.key[i] + maxDist;
-      jlo[i] = (int)(std::lower_bound(pmax.begin(), pmax.end(), a) - pmax.begin());        // first j: key[j] >= a
-      jhi[i] = (int)(std::upper_bound(smin.begin(), smin.end(), bb) - smin.begin()) - 1;   // last j: key[j] <= b
-    }
+    b.k1.assign(1, 0);
+    b.k2.assign(1, 0);
   }
-  // monotone hull so that every anti-diagonal meets the band in ONE interval of i
-  std::vector<int> rows;  // non-empty rows, ascending
-  rows.reserve(NI);
-  {
-    int run = -1;
-    for (int i = 0; i < NI; ++i)  // jhi non-decreasing
-      if (jlo[i] <= jhi[i]) { run = std::max(run, jhi[i]); jhi[i] = run; rows.push_back(i); }
-    run = NJ;
-    for (int i = NI - 1; i >= 0; --i)  // jlo non-decreasing
-      if (jlo[i] <= jhi[i]) { run = std::min(run, jlo[i]); jlo[i] = run; }
-  }
-  // Over the non-empty rows i + jlo[i] and i + jhi[i] are strictly increasing, so the rows meeting
-  // diagonal d form a contiguous run of `rows`: two pointers, O(rows + diagonals).
-  const int nDiag = NI + NJ - 1;
-  std::vector<int> dlo(nDiag, 0), dhi(nDiag, -1);
-  {
-    size_t lo = 0, hi = 0;  // lo: first row with i + jhi[i] >= d;  hi: one past the last row with i + jlo[i] <= d
-    for (int d = 0; d < nDiag; ++d) {
-      while (lo < rows.size() && rows[lo] + jhi[rows[lo]] < d) ++lo;
-      while (hi < rows.size() && rows[hi] + jlo[rows[hi]] <= d) ++hi;
-      if (lo < hi) { dlo[d] = rows[lo]; dhi[d] = rows[hi - 1]; }
-    }
-  }
+  const int NI = nx - 1, NJ = ny - 1, nDiag = NI + NJ - 1;
 
   hist_pair* pr = new hist_pair();
   b.pr = pr;
@@ -912,50 +1251,19 @@ int build_pair_host(hist_ctx* ctx, const hist_profile* x, const hist_profile* y,
   pr->x = x;
   pr->y = y;
   pr->arena = nullptr;
+  pr->planes = nullptr;
   pr->bwd_planes = nullptr;
   pr->d_dev = nullptr;
   pr->fwd_done = pr->bwd_done = false;
   pr->lp_end = pr->lp_start = -INFINITY;
-  // edge slots
-  sx.slot.assign(nx, -1);
-  sy.slot.assign(ny, -1);
-  for (int i = 0; i < NI; ++i)
-    if (sx.near_[i]) { sx.slot[i] = (int)pr->start_rows.size(); pr->start_rows.push_back(i); }
-  for (int j = 0; j < NJ; ++j)
-    if (sy.near_[j]) { sy.slot[j] = (int)pr->end_cols.size(); pr->end_cols.push_back(j); }
-  const int nS = (int)pr->start_rows.size(), nE = (int)pr->end_cols.size();
-  pr->dinfo.resize(nDiag);
-  unsigned long long off = 0;
-  int maxThreads = 1, maxWidth = 0;
-  for (int d = 0; d < nDiag; ++d) {
-    DiagInfo di;
-    if (dhi[d] >= 0) { di.ilo = dlo[d]; di.width = dhi[d] - dlo[d] + 1; } else { di.ilo = 0; di.width = 0; }
-    di.off = (unsigned)off;
-    di.pad = 0;
-    pr->dinfo[d] = di;
-    off += (unsigned long long)(nS + di.width + nE);
-    maxThreads = std::max(maxThreads, nS + di.width + nE);
-    maxWidth = std::max(maxWidth, di.width);
-  }
-  if (off >= (1ull << 31))
-    return set_err(ctx, HIST_ERR_ARG, "hist_pair_prepare: %llu stored cells exceed the 2^31 limit of one pair", off);
-  const unsigned nStored = (unsigned)off;
 
   // ---- layouts
   Layout& H = b.host;
   Layout& Dv = b.dev;
-  auto putv = [&](const auto& v) { return H.put(v.data(), v.size() * sizeof(v[0])); };
-  auto layout_side = [&](const hist_profile* p, const SideHost& s) {
+  auto layout_side = [&](const hist_profile* p) {
     SideOff o;
     const size_t nt1 = std::max<size_t>(1, p->nt);
-    o.h_flags = putv(s.flags);
-    o.h_t_src = H.put(p->t_src.data(), p->nt * sizeof(int)); H.reserve(p->nt ? 0 : sizeof(int));
-    o.h_t_dst = H.put(p->t_dst.data(), p->nt * sizeof(int)); H.reserve(p->nt ? 0 : sizeof(int));
-    o.h_t_lp = H.put(p->t_lp.data(), p->nt * sizeof(double)); H.reserve(p->nt ? 0 : sizeof(double));
-    o.h_in_off = putv(s.in_off); o.h_in_idx = putv(s.in_idx);
-    o.h_ao_off = putv(s.ao_off); o.h_ao_idx = putv(s.ao_idx);
-    o.h_no_off = putv(s.no_off); o.h_no_idx = putv(s.no_idx);
-    o.h_key = putv(s.key); o.h_near = putv(s.near_); o.h_slot = putv(s.slot);
+    o.d_key = Dv.reserve((size_t)p->n * sizeof(int));
     o.d_t_m = Dv.reserve(nt1 * sizeof(float));
     o.d_t_e = Dv.reserve(nt1 * sizeof(int));
     o.d_ex = Dv.reserve((size_t)p->n * sizeof(int));
@@ -976,11 +1284,13 @@ int build_pair_host(hist_ctx* ctx, const hist_profile* x, const hist_profile* y,
     o.d_no_edges = Dv.reserve(nt1 * 2 * sizeof(int4));
     return o;
   };
-  b.ox = layout_side(x, sx);
-  b.oy = layout_side(y, sy);
-  b.h_start = H.put(nS ? (const void*)pr->start_rows.data() : (const void*)b.one0.data(), std::max(1, nS) * sizeof(int));
-  b.h_end = H.put(nE ? (const void*)pr->end_cols.data() : (const void*)b.one0.data(), std::max(1, nE) * sizeof(int));
-  b.h_dinfo = H.put(pr->dinfo.data(), pr->dinfo.size() * sizeof(DiagInfo));
+  b.ox = layout_side(x);
+  b.oy = layout_side(y);
+  b.d_dinfo = Dv.reserve(((size_t)nDiag + 64) * sizeof(DiagInfo));   // the fill kernels prefetch layout records a few dozen steps ahead
+  b.d_scratch = Dv.reserve(((size_t)4 * NI + 2 * NJ + 8) * sizeof(int));
+  Dv.reserve(0, 256);
+  b.h_k1 = H.put(b.k1.data(), b.k1.size() * sizeof(int));
+  b.h_k2 = H.put(b.k2.data(), b.k2.size() * sizeof(int));
   b.h_lsub = H.put(hmm->l_sub, (size_t)K * A * sizeof(double));
   b.h_rsub = H.put(hmm->r_sub, (size_t)K * A * sizeof(double));
   b.h_root = H.put(hmm->log_root, (size_t)K * sizeof(double));
@@ -990,20 +1300,13 @@ int build_pair_host(hist_ctx* ctx, const hist_profile* x, const hist_profile* y,
   b.h_rcw = H.put(hmm->r_log_cpt_weight, (size_t)C * sizeof(double));
   b.h_pairdev = H.reserve(sizeof(PairDev), 64);
   H.reserve(0, 256);
-  b.d_scal = 0;  // assigned by the batch (scalars of all pairs are contiguous)
-  b.d_fA = Dv.reserve((size_t)nStored * sizeof(float4), 256);
-  b.d_fB = Dv.reserve((size_t)nStored * sizeof(float2), 256);
-  b.d_absorb = Dv.reserve((size_t)nStored * sizeof(float), 256);
-  if (want_bwd) {
-    b.d_bA = Dv.reserve((size_t)nStored * sizeof(float4), 256);
-    b.d_bB = Dv.reserve((size_t)nStored * sizeof(float2), 256);
-  }
-  Dv.reserve(0, 256);
 
   PairDev& D = pr->dev;
   memset(&D, 0, sizeof(D));
   D.K = K; D.Kp = Kp; D.C = C; D.A = A;
   D.max_dist = maxDist;
+  D.env_len1 = maxDist >= 0 ? env->row1_len : 0;
+  D.env_len2 = maxDist >= 0 ? env->row2_len : 0;
   D.x.n = nx; D.x.nt = x->nt;
   D.y.n = ny; D.y.nt = y->nt;
   // HMM weights, w[src][dest] (pairhmm.cpp:46-115); absent pairs are -inf / 0
@@ -1029,36 +1332,35 @@ int build_pair_host(hist_ctx* ctx, const hist_profile* x, const hist_profile* y,
   pr->hmm_scalars.l_log_ins = pr->hmm_scalars.r_log_ins = nullptr;
   pr->hmm_scalars.l_log_cpt_weight = pr->hmm_scalars.r_log_cpt_weight = nullptr;
   D.n_diag = nDiag;
-  D.nS = nS; D.nE = nE;
-  D.max_threads = maxThreads;
-  D.chain = x->chain && y->chain && nx >= 3 && ny >= 3 && nS == 1 && nE == 1 ? 1 : 0;
-  D.n_stored = nStored;
-  pr->x_key = sx.key; pr->y_key = sy.key;
-  pr->x_near = sx.near_; pr->y_near = sy.near_;
-  pr->x_slot = sx.slot; pr->y_slot = sy.slot;
+  D.nS = x->nS; D.nE = y->nE;
+  D.max_threads = 1;
+  D.chain = x->chain && y->chain && nx >= 3 && ny >= 3 && D.nS == 1 && D.nE == 1 ? 1 : 0;
+  D.n_stored = 0;
   pr->info.x_size = nx;
   pr->info.y_size = ny;
   pr->info.n_cells = 0;
-  pr->info.n_stored = nStored;
+  pr->info.n_stored = 0;
   pr->info.n_diagonals = nDiag;
-  pr->info.max_diag_width = maxWidth;
+  pr->info.max_diag_width = 0;
   pr->info.h2d_bytes = (int64_t)H.bytes;
   return HIST_OK;
 }
 
-// Resolve the device pointers of one pair once its two arena parts are placed.
-void place_pair(PairBuild& b, char* arena, size_t scal_off, bool want_bwd) {
+// Resolve the device pointers of one pair once its two arena parts are placed (the cell planes follow later).
+void place_pair(PairBuild& b, char* arena, size_t scal_off, size_t lay_off) {
   hist_pair* pr = b.pr;
   char* hb_ = arena + b.host_base;
   char* db = arena + b.dev_base;
-  auto side = [&](SideDev& s, const hist_profile* p, const SideOff& o) {
-    s.flags = (const uint8_t*)(hb_ + o.h_flags);
-    s.t_src = (const int*)(hb_ + o.h_t_src); s.t_dst = (const int*)(hb_ + o.h_t_dst);
-    s.t_lp = (const double*)(hb_ + o.h_t_lp);
-    s.in_off = (const int*)(hb_ + o.h_in_off); s.in_idx = (const int*)(hb_ + o.h_in_idx);
-    s.ao_off = (const int*)(hb_ + o.h_ao_off); s.ao_idx = (const int*)(hb_ + o.h_ao_idx);
-    s.no_off = (const int*)(hb_ + o.h_no_off); s.no_idx = (const int*)(hb_ + o.h_no_idx);
-    s.key = (const int*)(hb_ + o.h_key); s.near_ = (const uint8_t*)(hb_ + o.h_near); s.slot = (const int*)(hb_ + o.h_slot);
+  auto side = [&](SideDev& s, const hist_profile* p, const SideOff& o, bool isY) {
+    const ProfImage& im = p->img;
+    s.flags = im.flags;
+    s.t_src = im.t_src; s.t_dst = im.t_dst; s.t_lp = im.t_lp;
+    s.in_off = im.in_off; s.in_idx = im.in_idx;
+    s.ao_off = im.ao_off; s.ao_idx = im.ao_idx;
+    s.no_off = im.no_off; s.no_idx = im.no_idx;
+    s.near_ = isY ? im.near_end : im.near_start;
+    s.slot = isY ? im.slot_end : im.slot_start;
+    s.key = (int*)(db + o.d_key);
     s.t_m = (float*)(db + o.d_t_m); s.t_e = (int*)(db + o.d_t_e);
     s.ex = (int*)(db + o.d_ex); s.rs = (float*)(db + o.d_rs); s.ins = (float*)(db + o.d_ins);
     s.H = (float*)(db + o.d_H);
@@ -1070,45 +1372,39 @@ void place_pair(PairBuild& b, char* arena, size_t scal_off, bool want_bwd) {
     s.ao_edges = (int4*)(db + o.d_ao_edges); s.no_edges = (int4*)(db + o.d_no_edges);
   };
   PairDev& D = pr->dev;
-  side(D.x, pr->x, b.ox);
-  side(D.y, pr->y, b.oy);
-  D.start_rows = (const int*)(hb_ + b.h_start);
-  D.end_cols = (const int*)(hb_ + b.h_end);
-  D.dinfo = (const DiagInfo*)(hb_ + b.h_dinfo);
+  side(D.x, pr->x, b.ox, false);
+  side(D.y, pr->y, b.oy, true);
+  D.start_rows = pr->x->img.start_rows;
+  D.end_cols = pr->y->img.end_cols;
+  D.dinfo = (DiagInfo*)(db + b.d_dinfo);
+  D.scratch = (int*)(db + b.d_scratch);
+  D.env_k1 = (const int*)(hb_ + b.h_k1);
+  D.env_k2 = (const int*)(hb_ + b.h_k2);
+  D.x_leaf_pos = pr->x->img.leaf_pos;
+  D.y_leaf_pos = pr->y->img.leaf_pos;
   D.l_sub = (const double*)(hb_ + b.h_lsub); D.r_sub = (const double*)(hb_ + b.h_rsub);
   D.log_root = (const double*)(hb_ + b.h_root);
   D.l_ins = (const double*)(hb_ + b.h_lins); D.r_ins = (const double*)(hb_ + b.h_rins);
   D.l_cw = (const double*)(hb_ + b.h_lcw); D.r_cw = (const double*)(hb_ + b.h_rcw);
-  D.fA = (float4*)(db + b.d_fA); D.fB = (float2*)(db + b.d_fB);
-  D.absorb = (float*)(db + b.d_absorb);
-  if (want_bwd) { D.bA = (float4*)(db + b.d_bA); D.bB = (float2*)(db + b.d_bB); } else { D.bA = nullptr; D.bB = nullptr; }
   double* scal = (double*)(arena + scal_off);
   D.lp_end = scal;
   D.lp_start = scal + 1;
   D.n_cells = (unsigned long long*)(scal + 2);
+  D.layout_out = (LayoutOut*)(arena + lay_off);
   pr->d_dev = (PairDev*)(hb_ + b.h_pairdev);
 }
 
 int ensure_staging(hist_ctx* ctx, size_t bytes, int slot) {
   char*& buf = slot ? ctx->staging2 : ctx->staging;
   size_t& have = slot ? ctx->staging2_bytes : ctx->staging_bytes;
-  if (have >= bytes) return HIST_OK;
-  if (buf) {
-    HB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    cudaFreeHost(buf);
-    buf = nullptr;
-    have = 0;
-  }
-  const size_t want = std::max(bytes + bytes / 4, (size_t)1 << 20);
-  HB_CUDA(ctx, cudaMallocHost((void**)&buf, want));
-  have = want;
-  return HIST_OK;
+  return ensure_pinned(ctx, buf, have, bytes);
 }
 
 // A sub-batch whose transfer and table kernels are enqueued but not yet waited for.
 struct PrepPending {
   std::vector<PairBuild> builds;
   hb_arena* arena = nullptr;
+  hb_arena* planes = nullptr;
   size_t scal_off = 0;
   hist_pair** out = nullptr;
 };
@@ -1116,11 +1412,12 @@ struct PrepPending {
 void drop_pending(hist_ctx* ctx, PrepPending& pd) {
   for (auto& b : pd.builds) delete b.pr;
   pd.builds.clear();
-  if (pd.arena) {
-    if (pd.arena->dev) cudaFreeAsync(pd.arena->dev, ctx->stream);
-    delete pd.arena;
-    pd.arena = nullptr;
-  }
+  for (hb_arena** a : {&pd.arena, &pd.planes})
+    if (*a) {
+      if ((*a)->dev) cudaFreeAsync((*a)->dev, ctx->stream);
+      delete *a;
+      *a = nullptr;
+    }
 }
 
 // After the stream has been waited for: cell counts back, pairs handed to the caller.
@@ -1135,18 +1432,16 @@ int finish_pending(hist_ctx* ctx, PrepPending& pd) {
     memcpy(&nc, &scal[(size_t)k * 4 + 2], sizeof(nc));
     pr->info.n_cells = (int64_t)nc;
     pr->arena = pd.arena;
+    pr->planes = pd.planes;
     ++pd.arena->refs;
+    ++pd.planes->refs;
     ++const_cast<hist_profile*>(pr->x)->refs;
     ++const_cast<hist_profile*>(pr->y)->refs;
     pd.out[k] = pr;
   }
-  // every build record owns a few dozen host vectors: free them on the worker threads
-  parallel_for(n, 32, [&](int k) {
-    PairBuild done;
-    std::swap(pd.builds[k], done);
-  });
   pd.builds.clear();
   pd.arena = nullptr;
+  pd.planes = nullptr;
   return HIST_OK;
 }
 
@@ -1167,48 +1462,153 @@ void arena_drop(hist_ctx* ctx, hb_arena* a) { arena_release(ctx, a); }
 }  // namespace hb
 
 namespace {
-// Host build, one H2D transfer and the table kernels of a sub-batch, enqueued on the context's stream through staging
-// buffer `slot`; does not wait for the device.
+// HIST_B200_VERIFY_PREP=1: the band keys, edge flags and layout records the device produced are read back and compared
+// with a plain host computation of the same integers (forward.cpp:36-42, 58-65); mismatches go to stderr.
+int verify_pair_layout(hist_ctx* ctx, const hist_pair* pr, const hist_env_desc* env, int k) {
+  const hist_profile* x = pr->x;
+  const hist_profile* y = pr->y;
+  const PairDev& D = pr->dev;
+  const int nx = x->n, ny = y->n, NI = nx - 1, NJ = ny - 1, nDiag = NI + NJ - 1, maxDist = D.max_dist;
+  SideHost sx, sy;
+  build_side_lists(x, sx);
+  build_side_lists(y, sy);
+  std::vector<int> xk(nx, 0), yk(ny, 0);
+  if (maxDist >= 0) {
+    for (int i = 0; i < nx; ++i) xk[i] = env->cumulative_matches[env->row1_pos_to_col[i == 0 ? 0 : x->leaf_pos[i]]];
+    for (int j = 0; j < ny; ++j) yk[j] = env->cumulative_matches[env->row2_pos_to_col[j == 0 ? 0 : y->leaf_pos[j]]];
+  }
+  std::vector<uint8_t> xn(nx, 0), yn(ny, 0);
+  xn[0] = 1;
+  for (int i = 0; i < nx; ++i)
+    if (xn[i])
+      for (int q = sx.no_off[i]; q < sx.no_off[i + 1]; ++q) xn[x->t_dst[sx.no_idx[q]]] = 1;
+  for (int q = sy.in_off[ny - 1]; q < sy.in_off[ny]; ++q) yn[y->t_src[sy.in_idx[q]]] = 1;
+  std::vector<int> jlo(NI), jhi(NI);
+  if (maxDist < 0) {
+    for (int i = 0; i < NI; ++i) { jlo[i] = 0; jhi[i] = NJ - 1; }
+  } else {
+    std::vector<int> pmax(NJ), smin(NJ);
+    for (int j = 0; j < NJ; ++j) pmax[j] = j ? std::max(pmax[j - 1], yk[j]) : yk[0];
+    for (int j = NJ - 1; j >= 0; --j) smin[j] = j < NJ - 1 ? std::min(smin[j + 1], yk[j]) : yk[NJ - 1];
+    for (int i = 0; i < NI; ++i) {
+      jlo[i] = (int)(std::lower_bound(pmax.begin(), pmax.end(), xk[i] - maxDist) - pmax.begin());
+      jhi[i] = (int)(std::upper_bound(smin.begin(), smin.end(), xk[i] + maxDist) - smin.begin()) - 1;
+    }
+  }
+  std::vector<int> rows;
+  {
+    int run = -1;
+    for (int i = 0; i < NI; ++i)
+      if (jlo[i] <= jhi[i]) { run = std::max(run, jhi[i]); jhi[i] = run; rows.push_back(i); }
+    run = NJ;
+    for (int i = NI - 1; i >= 0; --i)
+      if (jlo[i] <= jhi[i]) { run = std::min(run, jlo[i]); jlo[i] = run; }
+  }
+  int nS = 0, nE = 0;
+  for (int i = 0; i < NI; ++i) nS += xn[i];
+  for (int j = 0; j < NJ; ++j) nE += yn[j];
+  std::vector<DiagInfo> want(nDiag);
+  unsigned long long off = 0;
+  {
+    size_t lo = 0, hi = 0;
+    for (int d = 0; d < nDiag; ++d) {
+      while (lo < rows.size() && rows[lo] + jhi[rows[lo]] < d) ++lo;
+      while (hi < rows.size() && rows[hi] + jlo[rows[hi]] <= d) ++hi;
+      DiagInfo di = {0, 0, (unsigned)off, 0};
+      if (lo < hi) { di.ilo = rows[lo]; di.width = rows[hi - 1] - rows[lo] + 1; }
+      want[d] = di;
+      off += (unsigned long long)(nS + di.width + nE);
+    }
+  }
+  std::vector<DiagInfo> got(nDiag);
+  std::vector<int> gxk(nx), gyk(ny);
+  std::vector<uint8_t> gxn(nx), gyn(ny), gxf(nx), gyf(ny);
+  HB_CUDA(ctx, cudaMemcpy(got.data(), D.dinfo, nDiag * sizeof(DiagInfo), cudaMemcpyDeviceToHost));
+  HB_CUDA(ctx, cudaMemcpy(gxk.data(), D.x.key, nx * sizeof(int), cudaMemcpyDeviceToHost));
+  HB_CUDA(ctx, cudaMemcpy(gyk.data(), D.y.key, ny * sizeof(int), cudaMemcpyDeviceToHost));
+  HB_CUDA(ctx, cudaMemcpy(gxn.data(), D.x.near_, nx, cudaMemcpyDeviceToHost));
+  HB_CUDA(ctx, cudaMemcpy(gyn.data(), D.y.near_, ny, cudaMemcpyDeviceToHost));
+  HB_CUDA(ctx, cudaMemcpy(gxf.data(), D.x.flags, nx, cudaMemcpyDeviceToHost));
+  HB_CUDA(ctx, cudaMemcpy(gyf.data(), D.y.flags, ny, cudaMemcpyDeviceToHost));
+  int bad = 0;
+  auto report = [&](const char* what, int idx, long long g, long long w) {
+    if (bad++ < 8) fprintf(stderr, "[verify_prep] pair %d %s[%d]: device %lld, host %lld\n", k, what, idx, g, w);
+  };
+  for (int i = 0; i < nx; ++i) {
+    if (gxk[i] != xk[i]) report("x.key", i, gxk[i], xk[i]);
+    if (gxn[i] != xn[i]) report("x.near", i, gxn[i], xn[i]);
+    if (gxf[i] != sx.flags[i]) report("x.flags", i, gxf[i], sx.flags[i]);
+  }
+  for (int j = 0; j < ny; ++j) {
+    if (gyk[j] != yk[j]) report("y.key", j, gyk[j], yk[j]);
+    if (gyn[j] != yn[j]) report("y.near", j, gyn[j], yn[j]);
+    if (gyf[j] != sy.flags[j]) report("y.flags", j, gyf[j], sy.flags[j]);
+  }
+  for (int d = 0; d < nDiag; ++d) {
+    if (got[d].ilo != want[d].ilo) report("dinfo.ilo", d, got[d].ilo, want[d].ilo);
+    if (got[d].width != want[d].width) report("dinfo.width", d, got[d].width, want[d].width);
+    if (got[d].off != want[d].off) report("dinfo.off", d, got[d].off, want[d].off);
+    if (got[d].pad != 0) report("dinfo.pad", d, got[d].pad, 0);
+  }
+  if (D.nS != nS) report("nS", 0, D.nS, nS);
+  if (D.nE != nE) report("nE", 0, D.nE, nE);
+  if ((unsigned long long)D.n_stored != off) report("n_stored", 0, D.n_stored, (long long)off);
+  fprintf(stderr, "[verify_prep] pair %d: %d x %d states, %d diagonals, %llu stored: %s\n", k, nx, ny, nDiag, off, bad ? "MISMATCH" : "ok");
+  return bad ? set_err(ctx, HIST_ERR_STATE, "verify_prep: device layout of pair %d differs from the host computation", k) : HIST_OK;
+}
+}  // namespace
+
+namespace {
+// The DPMatrix constructors of a sub-batch.  Host: argument checks and byte layouts; ONE transfer of the guide-row key
+// tables, the PairHMM tables and the descriptors; the device builds band keys and the anti-diagonal layout
+// (pair_layout_kernel); its totals come back (the one host synchronisation), the cell planes are allocated, and the
+// table kernels are enqueued.  Does not wait for those.
 int prepare_enqueue(hist_ctx* ctx, int32_t n, const hist_profile* const* xs, const hist_profile* const* ys,
                     const hist_pairhmm_desc* const* hmms, const hist_env_desc* const* envs, int32_t flags, int slot,
                     PrepPending& pd) {
   const bool want_bwd = (flags & HIST_PREP_BACKWARD) != 0;
+  static const bool verify = getenv("HIST_B200_VERIFY_PREP") != nullptr;
   HostTimer tm("prepare_batch");
-  pd.builds.assign(n, PairBuild());
+  for (int k = 0; k < n; ++k)
+    if (!xs[k] || !ys[k] || !hmms[k]) return set_err(ctx, HIST_ERR_ARG, "hist_pair_prepare: NULL argument");
+  int rc = ensure_images(ctx, xs, ys, n);
+  if (rc) return rc;
+  tm.lap("profile images");
+  pd.builds.clear();
+  pd.builds.resize(n);
   std::vector<PairBuild>& builds = pd.builds;
-  auto fail = [&](int rc) {
+  auto fail = [&](int rc_) {
     for (auto& b : builds) {
       delete b.pr;
       b.pr = nullptr;
     }
-    return rc;
+    return rc_;
   };
-  size_t host_total = 0, dev_total = 0;
   {
-    // the host part of the DPMatrix constructors is independent per pair: spread it over host threads
     std::vector<int> rcs(n, 0);
-    parallel_for(n, 8, [&](int k) { rcs[k] = build_pair_host(ctx, xs[k], ys[k], hmms[k], envs ? envs[k] : nullptr, want_bwd, builds[k]); });
+    parallel_for(n, 32, [&](int k) { rcs[k] = plan_pair(ctx, xs[k], ys[k], hmms[k], envs ? envs[k] : nullptr, builds[k]); });
     for (int k = 0; k < n; ++k)
       if (rcs[k]) return fail(rcs[k]);
   }
-  tm.lap("host build");
+  tm.lap("host plan");
+  size_t host_total = 0;
   for (int k = 0; k < n; ++k) {
     builds[k].host_base = host_total;
     host_total += builds[k].host.bytes;
   }
-  // arena = [host-initialised parts][pointer table][scalars of all pairs][device-only parts]
+  // arena = [host-initialised parts][pointer table][plane placements][scalars of all pairs][layout totals][device-only parts]
+  auto up256 = [](size_t v) { return (v + 255) / 256 * 256; };
   const size_t ptr_off = host_total;
-  host_total += ((size_t)n * sizeof(PairDev*) + 255) / 256 * 256;
-  const size_t scal_off = host_total;
-  size_t total = scal_off + ((size_t)n * 4 * sizeof(double) + 255) / 256 * 256;
+  const size_t place_off = ptr_off + up256((size_t)n * sizeof(PairDev*));
+  const size_t scal_off = place_off + up256((size_t)n * sizeof(PlanePlace));
+  const size_t lay_off = scal_off + up256((size_t)n * 4 * sizeof(double));
+  size_t total = lay_off + up256((size_t)n * sizeof(LayoutOut));
   for (int k = 0; k < n; ++k) {
     builds[k].dev_base = total;
     total += builds[k].dev.bytes;
-    dev_total += builds[k].dev.bytes;
   }
-  (void)dev_total;
   hb_arena* arena = new hb_arena{nullptr, total, 0};
-  int rc = check_cuda(ctx, cudaMallocAsync((void**)&arena->dev, total, ctx->stream), "cudaMallocAsync(pair arena)");
+  rc = check_cuda(ctx, cudaMallocAsync((void**)&arena->dev, total, ctx->stream), "cudaMallocAsync(pair arena)");
   if (!rc) rc = ensure_staging(ctx, scal_off, slot);
   if (!rc) rc = check_cuda(ctx, cudaEventSynchronize(ctx->ev_stage[slot]), "wait for the staging buffer");  // its previous transfer
   if (rc) {
@@ -1216,21 +1616,28 @@ int prepare_enqueue(hist_ctx* ctx, int32_t n, const hist_profile* const* xs, con
     delete arena;
     return fail(rc);
   }
+  pd.arena = arena;
+  auto fail_all = [&](int rc_) {
+    cudaStreamSynchronize(ctx->stream);
+    fail(rc_);
+    builds.clear();
+    drop_pending(ctx, pd);
+    return rc_;
+  };
   tm.lap("alloc");
   // fill the pinned staging image and ship it in one transfer
   char* st = slot ? ctx->staging2 : ctx->staging;
   int maxN = 1, maxNt = 1, maxDiag = 1, maxKp = 4, maxKC = 1;
-  parallel_for(n, 8, [&](int k) {
+  parallel_for(n, 32, [&](int k) {
     PairBuild& b = builds[k];
-    place_pair(b, arena->dev, scal_off + (size_t)k * 4 * sizeof(double), want_bwd);
+    place_pair(b, arena->dev, scal_off + (size_t)k * 4 * sizeof(double), lay_off + (size_t)k * sizeof(LayoutOut));
     char* base = st + b.host_base;
     for (auto& c : b.host.copies) memcpy(base + c.first, c.second.first, c.second.second);
     memcpy(base + b.h_pairdev, &b.pr->dev, sizeof(PairDev));
     ((PairDev**)(st + ptr_off))[k] = b.pr->d_dev;
   });
   for (int k = 0; k < n; ++k) {
-    PairBuild& b = builds[k];
-    const PairDev& D = b.pr->dev;
+    const PairDev& D = builds[k].pr->dev;
     maxN = std::max(maxN, std::max(D.x.n, D.y.n));
     maxNt = std::max(maxNt, std::max(D.x.nt, D.y.nt));
     maxDiag = std::max(maxDiag, D.n_diag);
@@ -1238,12 +1645,73 @@ int prepare_enqueue(hist_ctx* ctx, int32_t n, const hist_profile* const* xs, con
     maxKC = std::max(maxKC, D.K + D.C);
   }
   tm.lap("staging fill");
-  rc = check_cuda(ctx, cudaMemcpyAsync(arena->dev, st, scal_off, cudaMemcpyHostToDevice, ctx->stream), "H2D pair arena");
-  if (!rc) rc = check_cuda(ctx, cudaEventRecord(ctx->ev_stage[slot], ctx->stream), "record staging event");
-  if (!rc) rc = check_cuda(ctx, cudaMemsetAsync(arena->dev + scal_off, 0, (size_t)n * 4 * sizeof(double), ctx->stream), "memset scalars");
-  // ---- F0/F1 and the packed records on device, one launch each for the whole batch
   PairDev* const* dptrs = (PairDev* const*)(arena->dev + ptr_off);
+  std::vector<LayoutOut> lay(n);
+  rc = check_cuda(ctx, cudaMemcpyAsync(arena->dev, st, place_off, cudaMemcpyHostToDevice, ctx->stream), "H2D pair arena");
+  ctx->h2d_bytes += (long long)place_off;
+  if (!rc) rc = check_cuda(ctx, cudaMemsetAsync(arena->dev + scal_off, 0, (size_t)n * 4 * sizeof(double), ctx->stream), "memset scalars");
   if (!rc) {
+    pair_layout_kernel<<<n, 256, 0, ctx->stream>>>(dptrs);
+    ctx->launches += 1;
+    rc = check_cuda(ctx, cudaGetLastError(), "pair_layout_kernel");
+  }
+  if (!rc) rc = check_cuda(ctx, cudaMemcpyAsync(lay.data(), arena->dev + lay_off, (size_t)n * sizeof(LayoutOut), cudaMemcpyDeviceToHost, ctx->stream), "D2H layout totals");
+  if (!rc) rc = check_cuda(ctx, cudaStreamSynchronize(ctx->stream), "sync after pair layout");
+  if (rc) return fail_all(rc);
+  tm.lap("layout on device");
+  // ---- cell planes, sized by the layout
+  size_t plane_total = 0;
+  for (int k = 0; k < n; ++k) {
+    PairBuild& b = builds[k];
+    const LayoutOut& L = lay[k];
+    if (L.err)
+      return fail_all(set_err(ctx, HIST_ERR_ARG, "%s state %d: closest-leaf position %d outside guide row (len %d)", L.err == 1 ? "x" : "y",
+                              L.err_state, L.err_pos, L.err == 1 ? b.pr->dev.env_len1 : b.pr->dev.env_len2));
+    if (L.n_stored >= (1ull << 31))
+      return fail_all(set_err(ctx, HIST_ERR_ARG, "hist_pair_prepare: %llu stored cells exceed the 2^31 limit of one pair", L.n_stored));
+    const size_t ns = (size_t)L.n_stored;
+    Layout P;
+    b.p_fA = P.reserve(ns * sizeof(float4), 256);
+    b.p_fB = P.reserve(ns * sizeof(float2), 256);
+    b.p_absorb = P.reserve(ns * sizeof(float), 256);
+    if (want_bwd) {
+      b.p_bA = P.reserve(ns * sizeof(float4), 256);
+      b.p_bB = P.reserve(ns * sizeof(float2), 256);
+    }
+    P.reserve(0, 256);
+    b.plane_base = plane_total;
+    plane_total += P.bytes;
+    PairDev& D = b.pr->dev;
+    D.n_stored = (unsigned)L.n_stored;
+    D.max_threads = L.max_threads;
+    b.pr->info.n_stored = (int64_t)L.n_stored;
+    b.pr->info.max_diag_width = L.max_width;
+  }
+  hb_arena* planes = new hb_arena{nullptr, std::max<size_t>(plane_total, 256), 0};
+  rc = check_cuda(ctx, cudaMallocAsync((void**)&planes->dev, planes->bytes, ctx->stream), "cudaMallocAsync(cell planes)");
+  if (rc) {
+    delete planes;
+    return fail_all(rc);
+  }
+  pd.planes = planes;
+  {
+    PlanePlace* pl = (PlanePlace*)(st + place_off);   // the staging buffer's first transfer has completed (stream waited for above)
+    for (int k = 0; k < n; ++k) {
+      PairBuild& b = builds[k];
+      char* pb = planes->dev + b.plane_base;
+      PairDev& D = b.pr->dev;
+      D.fA = (float4*)(pb + b.p_fA); D.fB = (float2*)(pb + b.p_fB); D.absorb = (float*)(pb + b.p_absorb);
+      D.bA = want_bwd ? (float4*)(pb + b.p_bA) : nullptr;
+      D.bB = want_bwd ? (float2*)(pb + b.p_bB) : nullptr;
+      pl[k] = PlanePlace{D.fA, D.fB, D.absorb, D.bA, D.bB};
+    }
+    rc = check_cuda(ctx, cudaMemcpyAsync(arena->dev + place_off, pl, (size_t)n * sizeof(PlanePlace), cudaMemcpyHostToDevice, ctx->stream), "H2D plane placements");
+    ctx->h2d_bytes += (long long)((size_t)n * sizeof(PlanePlace));
+    if (!rc) rc = check_cuda(ctx, cudaEventRecord(ctx->ev_stage[slot], ctx->stream), "record staging event");
+  }
+  // ---- F0/F1 and the packed records on device, one launch each for the whole batch
+  if (!rc) {
+    place_planes_kernel<<<(n + 127) / 128, 128, 0, ctx->stream>>>(dptrs, (const PlanePlace*)(arena->dev + place_off), n);
     const int threads = std::max(32, (maxKp + 31) / 32 * 32);
     const int stride = maxKC + 32;
     bool tensor = true;   // every pair of the batch is a one-component codon merge: leftMultiply as a tcgen05 GEMM
@@ -1260,17 +1728,15 @@ int prepare_enqueue(hist_ctx* ctx, int32_t n, const hist_profile* const* xs, con
     pack_meta_kernel<<<dim3((maxN + 127) / 128, n, 2), 128, 0, ctx->stream>>>(dptrs);
     const int chunks = std::max(1, std::min(maxDiag / 16 + 1, std::max(32, (4 * ctx->sm_count + n - 1) / n)));  // 4 diagonals in flight per CTA
     count_cells_kernel<<<dim3(chunks, n), 128, 0, ctx->stream>>>(dptrs);
-    ctx->launches += 4;
-    rc = check_cuda(ctx, cudaGetLastError(), "prepare kernels");
+    ctx->launches += 5;
+    if (!rc) rc = check_cuda(ctx, cudaGetLastError(), "prepare kernels");
   }
   tm.lap("enqueue");
-  if (rc) {
-    cudaStreamSynchronize(ctx->stream);
-    cudaFreeAsync(arena->dev, ctx->stream);
-    delete arena;
-    return fail(rc);
+  if (!rc && verify) {
+    rc = check_cuda(ctx, cudaStreamSynchronize(ctx->stream), "sync before verify");
+    for (int k = 0; k < n && !rc; ++k) rc = verify_pair_layout(ctx, builds[k].pr, envs ? envs[k] : nullptr, k);
   }
-  pd.arena = arena;
+  if (rc) return fail_all(rc);
   pd.scal_off = scal_off;
   return HIST_OK;
 }
@@ -1283,7 +1749,8 @@ extern "C" int hist_pair_prepare_batch(hist_ctx* ctx, int32_t n, const hist_prof
   for (int k = 0; k < n; ++k) out[k] = nullptr;
   cudaSetDevice(ctx->device);
   // a level is shipped in sub-batches: while the device receives and tabulates one, the host threads build the next
-  int parts = n >= 128 ? 4 : 1;   // measured on the 512-merge level: 1 -> 12.3 ms, 2 -> 10.9, 4 -> 10.0 (host-build bound)
+  // (every sub-batch costs one host synchronisation -- the layout totals -- so a level goes in two pieces at most)
+  int parts = n >= 256 ? 2 : 1;
   if (const char* e = getenv("HIST_B200_PREP_PARTS")) parts = std::max(1, std::min(n, atoi(e)));
   const int per = (n + parts - 1) / parts;
   std::vector<PrepPending> pend((n + per - 1) / per);
@@ -1327,6 +1794,7 @@ extern "C" void hist_pair_destroy(hist_pair* pr) {
   cudaSetDevice(pr->ctx->device);
   if (pr->bwd_planes) cudaFreeAsync(pr->bwd_planes, pr->ctx->stream);
   arena_release(pr->ctx, pr->arena);
+  arena_release(pr->ctx, pr->planes);
   profile_unref(pr->x);
   profile_unref(pr->y);
   delete pr;
@@ -1340,10 +1808,11 @@ extern "C" void hist_pairs_destroy(hist_pair* const* pairs, int32_t n) {
     cudaSetDevice(pr->ctx->device);
     if (pr->bwd_planes) cudaFreeAsync(pr->bwd_planes, pr->ctx->stream);
     arena_release(pr->ctx, pr->arena);
+    arena_release(pr->ctx, pr->planes);
     profile_unref(pr->x);
     profile_unref(pr->y);
   }
-  parallel_for(n, 32, [&](int k) { delete pairs[k]; });   // the host-side vectors of a level: spread the frees
+  for (int k = 0; k < n; ++k) delete pairs[k];
 }
 
 extern "C" int hist_pair_get_info(const hist_pair* pr, hist_pair_info* info) {
@@ -1372,17 +1841,26 @@ extern "C" int hist_pair_fetch_tables(hist_pair* pr, double* subx, double* suby,
 extern "C" int hist_pair_fetch_envelope(hist_pair* pr, int32_t* x_key, int32_t* y_key, uint8_t* x_near_start, uint8_t* y_near_end,
                                         uint8_t* in_envelope) {
   if (!pr) return HIST_ERR_ARG;
+  hist_ctx* ctx = pr->ctx;
+  cudaSetDevice(ctx->device);
   const int nx = pr->info.x_size, ny = pr->info.y_size;
-  if (x_key) memcpy(x_key, pr->x_key.data(), nx * sizeof(int));
-  if (y_key) memcpy(y_key, pr->y_key.data(), ny * sizeof(int));
-  if (x_near_start) memcpy(x_near_start, pr->x_near.data(), nx);
-  if (y_near_end) memcpy(y_near_end, pr->y_near.data(), ny);
+  // keys and edge flags live on the device (pair_layout_kernel, the profiles' structure images)
+  std::vector<int> xk(nx), yk(ny);
+  std::vector<uint8_t> xn(nx), yn(ny);
+  HB_CUDA(ctx, cudaMemcpyAsync(xk.data(), pr->dev.x.key, nx * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  HB_CUDA(ctx, cudaMemcpyAsync(yk.data(), pr->dev.y.key, ny * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  HB_CUDA(ctx, cudaMemcpyAsync(xn.data(), pr->dev.x.near_, nx, cudaMemcpyDeviceToHost, ctx->stream));
+  HB_CUDA(ctx, cudaMemcpyAsync(yn.data(), pr->dev.y.near_, ny, cudaMemcpyDeviceToHost, ctx->stream));
+  HB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if (x_key) memcpy(x_key, xk.data(), nx * sizeof(int));
+  if (y_key) memcpy(y_key, yk.data(), ny * sizeof(int));
+  if (x_near_start) memcpy(x_near_start, xn.data(), nx);
+  if (y_near_end) memcpy(y_near_end, yn.data(), ny);
   if (in_envelope) {
     const int md = pr->dev.max_dist;
     for (int i = 0; i < nx - 1; ++i)
       for (int j = 0; j < ny - 1; ++j)
-        in_envelope[(size_t)i * (ny - 1) + j] =
-            pr->x_near[i] || pr->y_near[j] || md < 0 || hb_iabs(pr->x_key[i] - pr->y_key[j]) <= md;
+        in_envelope[(size_t)i * (ny - 1) + j] = xn[i] || yn[j] || md < 0 || hb_iabs(xk[i] - yk[j]) <= md;
   }
   return HIST_OK;
 }

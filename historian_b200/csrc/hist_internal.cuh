@@ -71,9 +71,21 @@ struct SideDev {
   double* rootsub;       // [n]
   double* insl;          // [n]
   // envelope
-  const int* key;        // [n] cum[rowPosToCol[closestLeafPos]]
+  int* key;              // [n] cum[rowPosToCol[closestLeafPos]] (written by pair_layout_kernel)
   const uint8_t* near_;  // [n] xNearStart / yNearEnd
   const int* slot;       // [n] edge slot of this row/column, -1 if none
+};
+
+// Device image of a profile's integer structure: what the DPMatrix constructor derives from the profile alone,
+// whichever side of a merge it ends up on.
+struct ProfImage {
+  uint8_t* flags;                     // [n] F_EMIT | F_READY | F_EMIT_OR_START
+  int* t_src; int* t_dst; double* t_lp;
+  int* in_off; int* in_idx; int* ao_off; int* ao_idx; int* no_off; int* no_idx;
+  int* leaf_pos;                      // [n] closest-leaf sequence position (zeros if the profile carries none)
+  uint8_t* near_start; uint8_t* near_end;   // [n] xNearStart when used as x / yNearEnd when used as y
+  int* slot_start; int* slot_end;     // [n] rank among the near rows / columns, -1 elsewhere
+  int* start_rows; int* end_cols;     // [nS], [nE]
 };
 
 // per anti-diagonal d = i + j
@@ -82,6 +94,14 @@ struct DiagInfo {
   int width;   // cells in the main interval (may be 0)
   unsigned off;  // first stored cell of this diagonal
   int pad;
+};
+
+// What pair_layout_kernel reports back to the host for one pair (the plane allocation is sized from it).
+struct LayoutOut {
+  unsigned long long n_stored;   // stored cells over all diagonals
+  int max_threads, max_width;
+  int err;                       // 0 ok; 1/2: an x/y closest-leaf position lies outside its guide row
+  int err_state, err_pos, pad;
 };
 
 struct PairDev {
@@ -96,7 +116,7 @@ struct PairDev {
   int nS, nE;             // edge slots per diagonal: near-start rows, near-end columns
   const int* start_rows;  // [nS]
   const int* end_cols;    // [nE]
-  const DiagInfo* dinfo;  // [n_diag]
+  DiagInfo* dinfo;        // [n_diag] (written by pair_layout_kernel)
   int max_threads;        // max over d of nS + width + nE
   int chain;              // both profiles are leaf chains (START -> residue 1 -> ... -> residue L -> END, log-weight 0 transitions)
   unsigned n_stored;
@@ -106,6 +126,12 @@ struct PairDev {
   double* lp_end;         // [1]
   double* lp_start;       // [1]
   unsigned long long* n_cells;  // [1] in-envelope cell count
+  // inputs, scratch and result slot of pair_layout_kernel (band keys and the anti-diagonal layout are built on the device)
+  const int* env_k1; const int* env_k2;   // cumulativeMatches[rowPosToCol[pos]] of guide rows 1 and 2 (alignpath.cpp:282-310), [len+1]
+  int env_len1, env_len2;
+  const int* x_leaf_pos; const int* y_leaf_pos;
+  int* scratch;                 // [4 (nx-1) + 2 (ny-1)] jlo, jhi, rows, cnt | pmax, smin
+  LayoutOut* layout_out;
   // model tables of this merge (inputs of the DPMatrix-constructor kernels)
   const double* l_sub; const double* r_sub;      // [C][A][A]
   const double* log_root;                        // [C][A]
@@ -203,6 +229,11 @@ struct hist_ctx {
   char* staging2;
   size_t staging2_bytes;
   cudaEvent_t ev_stage[2];
+  // pinned staging buffer of the profile structure images (host-built ones and the chain job records)
+  char* staging_img;
+  size_t staging_img_bytes;
+  cudaEvent_t ev_img;
+  long long h2d_bytes;   // bytes the library has copied host -> device for profiles and DPMatrix constructors (bench.py)
 };
 
 struct hist_profile {
@@ -221,6 +252,11 @@ struct hist_profile {
   // device copy of lp_absorb
   double* d_lp_absorb;
   hb_arena* arena;            // owner of d_lp_absorb
+  // device image of the integer structure (flags, transitions, CSR lists, edge rows/columns), built once per profile --
+  // by a kernel for leaf chains, from the host lists otherwise -- the first time a DPMatrix constructor needs it
+  hb::ProfImage img = {};
+  hb_arena* img_arena = nullptr;
+  int nS = 0, nE = 0;         // states near START when this profile is x / near END when it is y (forward.cpp:58-65)
 };
 
 struct hist_pair {
@@ -229,17 +265,14 @@ struct hist_pair {
   const hist_profile* y;
   hb::PairDev dev;      // host copy of the device descriptor (pointers are device pointers)
   hb::PairDev* d_dev;   // device copy
-  hb_arena* arena;      // the batch allocation holding every per-pair array
+  hb_arena* arena;      // the batch allocation holding every per-pair array but the cell planes
+  hb_arena* planes;     // the batch allocation of the cell planes (sized by the layout the device computed)
   void* bwd_planes;     // separately allocated Backward planes (when not part of the arena)
   hist_pair_info info;
   bool fwd_done, bwd_done;
   double lp_end, lp_start;
   double w_log[6][6];   // natural-log HMM weights (host, for traceback etc.)
   hist_pairhmm_desc hmm_scalars;  // scalar fields only (pointers nulled)
-  std::vector<int> x_key, y_key;
-  std::vector<uint8_t> x_near, y_near;
-  std::vector<hb::DiagInfo> dinfo;
-  std::vector<int> start_rows, end_cols, x_slot, y_slot;
 };
 
 #include <functional>

@@ -147,6 +147,9 @@ void* hist_ctx_stream(hist_ctx* ctx);
 int hist_ctx_synchronize(hist_ctx* ctx);
 /* Number of kernels this context has launched so far (bench.py's gpu_launches). */
 int64_t hist_ctx_launch_count(const hist_ctx* ctx);
+/* Bytes this context has copied host -> device so far for leaf profiles, profile structure and the
+ * DPMatrix constructors (bench.py's e2e.h2d_bytes_per_step is a difference of two readings). */
+int64_t hist_ctx_h2d_bytes(const hist_ctx* ctx);
 /* Device-side timing of the Forward/Backward fill kernels: when enabled, every fill launch is
  * bracketed by CUDA events on the context's stream.  hist_ctx_fill_time_ms waits for them,
  * returns the summed kernel time and launch count since the last query, and resets. */
