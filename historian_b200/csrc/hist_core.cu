@@ -817,6 +817,8 @@ extern "C" int hist_profile_upload(hist_ctx* ctx, const hist_profile_desc* d, hi
   p->chain = p->nt == p->n - 1;
   for (int t = 0; t < p->nt && p->chain; ++t) p->chain = p->t_src[t] == t && p->t_dst[t] == t + 1 && p->t_lp[t] == 0.0;
   for (int i = 1; i + 1 < p->n && p->chain; ++i) p->chain = p->is_emit[i] != 0;
+  p->leaf_std = p->chain;
+  for (size_t i = 0; i < p->leaf_pos.size() && p->leaf_std; ++i) p->leaf_std = p->leaf_pos[i] == std::min((int)i, p->n - 2);
   const size_t bytes = (size_t)p->n * p->C * p->A * sizeof(double);
   p->d_lp_absorb = nullptr;
   p->arena = nullptr;
@@ -886,6 +888,7 @@ static int leaf_profiles(hist_ctx* ctx, int32_t n, const int8_t* const* tokens, 
   int rc = check_cuda(ctx, cudaMallocAsync((void**)&arena->dev, total, ctx->stream), "cudaMallocAsync(leaf profiles)");
   const size_t so_st = (n_tok + 255) & ~(size_t)255;
   if (!rc) rc = ensure_staging(ctx, so_st + off_bytes);
+  if (!rc) rc = check_cuda(ctx, cudaEventSynchronize(ctx->ev_stage[0]), "wait for the staging buffer");   // its previous transfer
   if (rc) {
     if (arena->dev) cudaFreeAsync(arena->dev, ctx->stream);
     delete arena;
@@ -905,6 +908,7 @@ static int leaf_profiles(hist_ctx* ctx, int32_t n, const int8_t* const* tokens, 
     rc = check_cuda(ctx, cudaMemcpyAsync(arena->dev + tok_off, ctx->staging, n_tok, cudaMemcpyHostToDevice, ctx->stream), "H2D tokens");
     if (!rc) rc = check_cuda(ctx, cudaMemcpyAsync(arena->dev + so_off, ctx->staging + so_st, off_bytes, cudaMemcpyHostToDevice, ctx->stream), "H2D offsets");
     ctx->h2d_bytes += (long long)(n_tok + off_bytes);
+    if (!rc) rc = check_cuda(ctx, cudaEventRecord(ctx->ev_stage[0], ctx->stream), "record staging event");
   }
   if (!rc) {
     const long long work = state_off[n] * (long long)K;
@@ -914,9 +918,10 @@ static int leaf_profiles(hist_ctx* ctx, int32_t n, const int8_t* const* tokens, 
     ctx->launches += 1;
     rc = check_cuda(ctx, cudaGetLastError(), "leaf_absorb_kernel");
   }
-  // the token strings are only borrowed, and the staging buffer is reused by the next call
-  if (!rc) rc = check_cuda(ctx, cudaStreamSynchronize(ctx->stream), "sync after leaf profiles");
+  // the borrowed token strings have been copied into the staging buffer (guarded by its event): nothing to wait for;
+  // the profiles' tables are complete for whatever is enqueued next on the context's stream
   if (rc) {
+    cudaStreamSynchronize(ctx->stream);
     cudaFreeAsync(arena->dev, ctx->stream);
     delete arena;
     return rc;
@@ -940,6 +945,7 @@ static int leaf_profiles(hist_ctx* ctx, int32_t n, const int8_t* const* tokens, 
     for (int i = 0; i < p->n; ++i) p->leaf_pos[i] = std::min(i, L);   // seqCoords of the leaf row (profile.cpp:33-36, 49)
     p->sorted_in = true;
     p->chain = true;
+    p->leaf_std = true;
     p->empty = L == 0;
     p->d_lp_absorb = (double*)arena->dev + (size_t)state_off[k] * K;
     p->arena = arena;
@@ -1150,13 +1156,7 @@ int ensure_images(hist_ctx* ctx, const hist_profile* const* xs, const hist_profi
   std::sort(need.begin(), need.end());
   need.erase(std::unique(need.begin(), need.end()), need.end());
   // a leaf chain whose closest-leaf positions are the leaf's own (or absent) gets its image from chain_image_kernel
-  auto on_device = [](const hist_profile* p) {
-    if (!p->chain || p->n < 3) return false;
-    for (size_t i = 0; i < p->leaf_pos.size(); ++i)
-      if (p->leaf_pos[i] != std::min((int)i, p->n - 2)) return false;
-    return true;
-  };
-  // host-built images first (they are the transferred part), then the device-generated ones
+  auto on_device = [](const hist_profile* p) { return p->chain && p->leaf_std && p->n >= 3; };
   const int m = (int)need.size();
   std::vector<size_t> base(m + 1, 0);
   const int n_host = (int)(std::stable_partition(need.begin(), need.end(), [&](hist_profile* p) { return !on_device(p); }) - need.begin());
@@ -1420,17 +1420,17 @@ void drop_pending(hist_ctx* ctx, PrepPending& pd) {
     }
 }
 
-// After the stream has been waited for: cell counts back, pairs handed to the caller.
+// Pairs handed to the caller.  Nothing is waited for: the table kernels are still running, and the exact cell counts
+// they produce are read back by pair_cells when somebody asks.
 int finish_pending(hist_ctx* ctx, PrepPending& pd) {
+  (void)ctx;
   const int n = (int)pd.builds.size();
-  std::vector<double> scal((size_t)n * 4);
-  HB_CUDA(ctx, cudaMemcpyAsync(scal.data(), pd.arena->dev + pd.scal_off, scal.size() * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
-  HB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  pd.arena->scal_off = pd.scal_off;
+  pd.arena->n_pairs = n;
   for (int k = 0; k < n; ++k) {
     hist_pair* pr = pd.builds[k].pr;
-    unsigned long long nc;
-    memcpy(&nc, &scal[(size_t)k * 4 + 2], sizeof(nc));
-    pr->info.n_cells = (int64_t)nc;
+    pr->batch_index = k;
+    pr->info.n_cells = -1;
     pr->arena = pd.arena;
     pr->planes = pd.planes;
     ++pd.arena->refs;
@@ -1459,6 +1459,26 @@ namespace hb {
 void host_parallel_for(int n, int grain, const std::function<void(int)>& fn) { parallel_for(n, grain, fn); }
 int ensure_staging_buf(hist_ctx* ctx, size_t bytes, int slot) { return ensure_staging(ctx, bytes, slot); }
 void arena_drop(hist_ctx* ctx, hb_arena* a) { arena_release(ctx, a); }
+int pair_cells(hist_pair* pr, long long* n_cells) {
+  hist_ctx* ctx = pr->ctx;
+  hb_arena* a = pr->arena;
+  if (!a->counted) {
+    cudaSetDevice(ctx->device);
+    std::vector<double> scal((size_t)a->n_pairs * 4);
+    HB_CUDA(ctx, cudaMemcpyAsync(scal.data(), a->dev + a->scal_off, scal.size() * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    HB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    a->n_cells.resize(a->n_pairs);
+    for (int k = 0; k < a->n_pairs; ++k) {
+      unsigned long long nc;
+      memcpy(&nc, &scal[(size_t)k * 4 + 2], sizeof(nc));
+      a->n_cells[k] = (long long)nc;
+    }
+    a->counted = true;
+  }
+  pr->info.n_cells = a->n_cells[pr->batch_index];
+  if (n_cells) *n_cells = pr->info.n_cells;
+  return HIST_OK;
+}
 }  // namespace hb
 
 namespace {
@@ -1760,8 +1780,9 @@ extern "C" int hist_pair_prepare_batch(hist_ctx* ctx, int32_t n, const hist_prof
     pend[c].out = out + first;
     rc = prepare_enqueue(ctx, cnt, xs + first, ys + first, hmms + first, envs ? envs + first : nullptr, flags, (int)(c & 1), pend[c]);
   }
-  // descriptors were only borrowed, and the staging buffers are reused by the next call
-  if (!rc) rc = check_cuda(ctx, cudaStreamSynchronize(ctx->stream), "sync after pair prepare");
+  // The borrowed descriptors have been copied into the pinned staging buffers, which are guarded by events: nothing to
+  // wait for.  The table kernels keep running behind this call; whatever is enqueued next on the context's stream
+  // (the fills) follows them.
   for (size_t c = 0; c < pend.size() && !rc; ++c) rc = finish_pending(ctx, pend[c]);
   if (rc) {
     cudaStreamSynchronize(ctx->stream);
@@ -1817,6 +1838,8 @@ extern "C" void hist_pairs_destroy(hist_pair* const* pairs, int32_t n) {
 
 extern "C" int hist_pair_get_info(const hist_pair* pr, hist_pair_info* info) {
   if (!pr || !info) return HIST_ERR_ARG;
+  int rc = pair_cells(const_cast<hist_pair*>(pr), nullptr);
+  if (rc) return rc;
   *info = pr->info;
   return HIST_OK;
 }

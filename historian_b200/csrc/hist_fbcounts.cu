@@ -173,6 +173,7 @@ extern "C" int hist_fb_counts(hist_pair* pair, const double* waits, double* inde
   if (!(pair->lp_end > -INFINITY)) return set_err(ctx, HIST_ERR_NUMERIC, "hist_fb_counts: zero forward likelihood");
   cudaSetDevice(ctx->device);
   const int xn = pair->dev.x.n, yn = pair->dev.y.n;
+  { int rc_ = hb::pair_cells(pair, nullptr); if (rc_) return rc_; }
   const unsigned long long cap = (unsigned long long)std::max<int64_t>(pair->info.n_cells, 1);
   const size_t n_d = (size_t)(xn - 1) * 6 + 2 * (size_t)xn + 2 * (size_t)yn;
   double* d_buf = nullptr;

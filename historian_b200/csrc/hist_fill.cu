@@ -2056,6 +2056,7 @@ extern "C" int hist_bwd_fill(hist_pair* pair, double* lp_start) {
 extern "C" int hist_cells_fetch(hist_pair* pair, int which, double* lp, int32_t* xpos, int32_t* ypos, int64_t capacity, int64_t* n_cells) {
   if (!pair || !n_cells) return HIST_ERR_ARG;
   hist_ctx* ctx = pair->ctx;
+  { int rc_ = hb::pair_cells(pair, nullptr); if (rc_) return rc_; }
   *n_cells = pair->info.n_cells;
   if (which ? !pair->bwd_done : !pair->fwd_done) return set_err(ctx, HIST_ERR_STATE, "hist_cells_fetch: matrix %d has not been filled", which);
   if (capacity < pair->info.n_cells || !lp) return set_err(ctx, HIST_ERR_CAPACITY, "hist_cells_fetch: need room for %lld cells", (long long)pair->info.n_cells);

@@ -204,6 +204,11 @@ struct hb_arena {
   char* dev;
   size_t bytes;
   int refs;
+  // pair arenas: the exact in-envelope cell counts (the GCUPS unit) stay on the device until somebody asks (hb::pair_cells)
+  size_t scal_off = 0;
+  int n_pairs = 0;
+  bool counted = false;
+  std::vector<long long> n_cells;
 };
 
 struct hist_ctx {
@@ -247,6 +252,7 @@ struct hist_profile {
   bool empty;                 // Profile::isEmpty
   bool sorted_in;             // every in-list ascending in source state, no repeated (src,dest)
   bool chain = false;         // leaf profile built by the library: transition t is t -> t+1, states 1..n-2 emit
+  bool leaf_std = false;      // chain whose closest-leaf positions are its own residues' (or absent): image generated on the device
   int refs = 0;               // pairs currently built on this profile (hist_profile_destroy defers while > 0)
   bool doomed = false;        // destroy requested while pairs still referred to it
   // device copy of lp_absorb
@@ -268,7 +274,8 @@ struct hist_pair {
   hb_arena* arena;      // the batch allocation holding every per-pair array but the cell planes
   hb_arena* planes;     // the batch allocation of the cell planes (sized by the layout the device computed)
   void* bwd_planes;     // separately allocated Backward planes (when not part of the arena)
-  hist_pair_info info;
+  hist_pair_info info;   // n_cells is valid once hb::pair_cells has run (hist_pair_get_info does that)
+  int batch_index = 0;   // position in its prepare batch (arena->n_cells)
   bool fwd_done, bwd_done;
   double lp_end, lp_start;
   double w_log[6][6];   // natural-log HMM weights (host, for traceback etc.)
@@ -286,6 +293,8 @@ void host_parallel_for(int n, int grain, const std::function<void(int)>& fn);
 // pinned staging buffer `slot` (0/1) of the context, grown on demand (hist_core.cu)
 int ensure_staging_buf(hist_ctx* ctx, size_t bytes, int slot);
 void arena_drop(hist_ctx* ctx, hb_arena* a);
+// exact in-envelope cell count of a pair (forward.cpp:78-86): read back from the device, for the whole batch, on first use
+int pair_cells(hist_pair* pair, long long* n_cells);
 
 // ---- codon alphabets: Profile::leftMultiply on the tensor cores (hist_codon.cu)
 bool leftmul_tc_applicable(int A, int C);

@@ -86,6 +86,7 @@ extern "C" int hist_posterior_cells(hist_pair* pair, double min_post_prob, hist_
   if (!(pair->lp_end > -INFINITY)) return set_err(ctx, HIST_ERR_NUMERIC, "hist_posterior_cells: zero forward likelihood");
   if (!(min_post_prob > 0)) return set_err(ctx, HIST_ERR_ARG, "hist_posterior_cells: min_post_prob must be positive");
   cudaSetDevice(ctx->device);
+  { int rc_ = hb::pair_cells(pair, nullptr); if (rc_) return rc_; }
   const unsigned long long cap = 5ull * (unsigned long long)std::max<int64_t>(pair->info.n_cells, 1);
   PostCell* buf = nullptr;
   unsigned long long* cnt = nullptr;
