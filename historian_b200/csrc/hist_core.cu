@@ -84,7 +84,8 @@ __device__ __forceinline__ double log_t(double x) { return x == 1.0 ? 0.0 : log(
 
 // WARP: C*A <= 32, one warp per state and blockDim.y states per CTA (a CTA per state would be a million
 // 32-thread CTAs for a level of merges); otherwise one CTA per state.  Same arithmetic either way.
-template <bool WARP>
+// TOK: the rows are the A+1 token classes of a leaf side (index = token, A = wildcard) instead of its states.
+template <bool WARP, bool TOK = false>
 __global__ void prepare_side_kernel(PairDev* const* __restrict__ pairs, int sm_stride) {
   extern __shared__ double sm_all[];
   double* sm = WARP ? sm_all + (size_t)threadIdx.y * sm_stride : sm_all;
@@ -92,7 +93,15 @@ __global__ void prepare_side_kernel(PairDev* const* __restrict__ pairs, int sm_s
   const bool isY = blockIdx.z == 1;
   const SideDev& s = isY ? P.y : P.x;
   const int i = WARP ? blockIdx.x * blockDim.y + threadIdx.y : blockIdx.x;
-  if (i >= s.n) return;
+  if ((s.tokens != nullptr) != TOK) return;   // leaf sides go through the token-class pass and leaf_scatter_kernel
+  if (i >= (TOK ? P.A + 1 : s.n)) return;
+  double* const o_sub = TOK ? s.tk_sub : s.sub;
+  float* const o_H = TOK ? s.tk_H : s.H;
+  int* const o_ex = TOK ? s.tk_ex : s.ex;
+  float* const o_rs = TOK ? s.tk_rs : s.rs;
+  float* const o_ins = TOK ? s.tk_ins : s.ins;
+  double* const o_rootsub = TOK ? s.tk_rootsub : s.rootsub;
+  double* const o_insl = TOK ? s.tk_insl : s.insl;
   auto sync = [&]() { if (WARP) __syncwarp(); else __syncthreads(); };
   auto red_max = [&](double v, double* r) { return WARP ? warp_max(v) : block_reduce<true>(v, r); };
   auto red_sum = [&](double v, double* r) { return WARP ? warp_sum(v) : block_reduce<false>(v, r); };
@@ -105,8 +114,8 @@ __global__ void prepare_side_kernel(PairDev* const* __restrict__ pairs, int sm_s
   double* mc = sm + K;         // [C] per-component max
   double* red = sm + K + C;    // [32] reduction scratch
   const int k = threadIdx.x;
-  const bool emit = (s.flags[i] & F_EMIT) != 0;
-  if (!emit || i == 0 || i == s.n - 1) {
+  const bool emit = TOK || (s.flags[i] & F_EMIT) != 0;
+  if (!TOK && (!emit || i == 0 || i == s.n - 1)) {
     if (k < K) s.sub[(size_t)i * K + k] = -INFINITY;
     if (k < Kp) s.H[(size_t)i * Kp + k] = 0.f;
     if (k == 0) {
@@ -118,7 +127,7 @@ __global__ void prepare_side_kernel(PairDev* const* __restrict__ pairs, int sm_s
     }
     return;
   }
-  const double* la = s.lp_absorb + (size_t)i * K;
+  const double* la = (TOK ? s.tk_onehot : s.lp_absorb) + (size_t)i * K;
   if (k < C) {
     double m = -INFINITY;
     for (int d = 0; d < A; ++d) m = fmax(m, la[k * A + d]);
@@ -135,7 +144,7 @@ __global__ void prepare_side_kernel(PairDev* const* __restrict__ pairs, int sm_s
     double acc = 0;
     for (int d = 0; d < A; ++d) acc = fma(Pm[d], e_abs[c * A + d], acc);
     subv = acc > 0 ? mc[c] + log(acc) : -INFINITY;
-    s.sub[(size_t)i * K + k] = subv;
+    o_sub[(size_t)i * K + k] = subv;
   }
   // block reductions: max of sub -> ex; rootsub; ins
   const double mx = red_max(subv, red);
@@ -151,14 +160,47 @@ __global__ void prepare_side_kernel(PairDev* const* __restrict__ pairs, int sm_s
   if (k < Kp) {
     double h = subv > -INFINITY ? exp(subv - ex * HB_LN2) : 0.0;
     if (isY && k < K) h *= exp(logRoot[k]);
-    s.H[(size_t)i * Kp + k] = (float)h;
+    o_H[(size_t)i * Kp + k] = (float)h;
   }
   if (k == 0) {
-    s.ex[i] = ex;
-    s.rootsub[i] = s_root;
-    s.insl[i] = s_ins;
-    s.rs[i] = s_root > -INFINITY ? (float)exp(s_root - ex * HB_LN2) : 0.f;
-    s.ins[i] = s_ins > -INFINITY ? (float)exp(s_ins - ex * HB_LN2) : 0.f;
+    o_ex[i] = ex;
+    o_rootsub[i] = s_root;
+    o_insl[i] = s_ins;
+    o_rs[i] = s_root > -INFINITY ? (float)exp(s_root - ex * HB_LN2) : 0.f;
+    o_ins[i] = s_ins > -INFINITY ? (float)exp(s_ins - ex * HB_LN2) : 0.f;
+  }
+}
+
+// Leaf sides: every state takes the rows of its residue's token class.  grid = (chunks, pairs, 2 sides), one warp per state.
+__global__ void leaf_scatter_kernel(PairDev* const* __restrict__ pairs) {
+  const PairDev& P = *pairs[blockIdx.y];
+  const SideDev& s = blockIdx.z == 1 ? P.y : P.x;
+  if (!s.tokens) return;
+  const int i = blockIdx.x * blockDim.y + threadIdx.y, lane = threadIdx.x;
+  if (i >= s.n) return;
+  const int K = P.K, Kp = P.Kp;
+  if (i == 0 || i == s.n - 1) {   // START / END: the null-state rows of prepare_side_kernel
+    for (int k = lane; k < K; k += 32) s.sub[(size_t)i * K + k] = -INFINITY;
+    for (int k = lane; k < Kp; k += 32) s.H[(size_t)i * Kp + k] = 0.f;
+    if (lane == 0) {
+      s.ex[i] = 0;
+      s.rs[i] = 1.f;
+      s.ins[i] = 1.f;
+      s.rootsub[i] = -INFINITY;
+      s.insl[i] = -INFINITY;
+    }
+    return;
+  }
+  int q = s.tokens[i - 1];
+  if (q < 0 || q >= P.A) q = P.A;
+  for (int k = lane; k < K; k += 32) s.sub[(size_t)i * K + k] = s.tk_sub[(size_t)q * K + k];
+  for (int k = lane; k < Kp; k += 32) s.H[(size_t)i * Kp + k] = s.tk_H[(size_t)q * Kp + k];
+  if (lane == 0) {
+    s.ex[i] = s.tk_ex[q];
+    s.rs[i] = s.tk_rs[q];
+    s.ins[i] = s.tk_ins[q];
+    s.rootsub[i] = s.tk_rootsub[q];
+    s.insl[i] = s.tk_insl[q];
   }
 }
 
@@ -734,6 +776,7 @@ extern "C" void hist_ctx_destroy(hist_ctx* ctx) {
   if (ctx->staging) cudaFreeHost(ctx->staging);
   if (ctx->staging2) cudaFreeHost(ctx->staging2);
   if (ctx->staging_img) cudaFreeHost(ctx->staging_img);
+  for (auto& e : ctx->onehot) cudaFree(e.second);
   cudaEventDestroy(ctx->ev_img);
   cudaEventDestroy(ctx->ev_stage[0]);
   cudaEventDestroy(ctx->ev_stage[1]);
@@ -948,6 +991,7 @@ static int leaf_profiles(hist_ctx* ctx, int32_t n, const int8_t* const* tokens, 
     p->leaf_std = true;
     p->empty = L == 0;
     p->d_lp_absorb = (double*)arena->dev + (size_t)state_off[k] * K;
+    p->d_tokens = (const int8_t*)(arena->dev + tok_off) + (state_off[k] - 2 * (long long)k);
     p->arena = arena;
     out[k] = p;
   });
@@ -1038,6 +1082,8 @@ struct SideHost {
 };
 
 struct SideOff {  // offsets in the device-only part of the pair arena
+  bool tok = false;   // leaf side: token-class rows
+  size_t k_sub = 0, k_H = 0, k_ex = 0, k_rs = 0, k_ins = 0, k_rootsub = 0, k_insl = 0;
   size_t d_key, d_t_m, d_t_e, d_ex, d_rs, d_ins, d_H, d_sub, d_rootsub, d_insl, d_fm_a, d_fm_b, d_emis, d_in_edges, d_bm, d_ao_edges, d_no_edges, d_cf, d_cb;
 };
 
@@ -1209,6 +1255,28 @@ int ensure_images(hist_ctx* ctx, const hist_profile* const* xs, const hist_profi
   return HIST_OK;
 }
 
+// lpAbsorb rows of the A+1 token classes of a leaf (profile.cpp:52-66): row q < A is 0 at residue q of every component
+// and -inf elsewhere, row A (wildcard) is all 0.  One device table per (A, C) and context, built on first use.
+int ensure_onehot(hist_ctx* ctx, int A, int C, const double** out) {
+  for (auto& e : ctx->onehot)
+    if (e.first.first == A && e.first.second == C) {
+      *out = e.second;
+      return HIST_OK;
+    }
+  const size_t K = (size_t)A * C;
+  std::vector<double> h((size_t)(A + 1) * K, -INFINITY);
+  for (int q = 0; q < A; ++q)
+    for (int c = 0; c < C; ++c) h[(size_t)q * K + (size_t)c * A + q] = 0.0;
+  for (size_t k = 0; k < K; ++k) h[(size_t)A * K + k] = 0.0;
+  double* d = nullptr;
+  HB_CUDA(ctx, cudaMalloc((void**)&d, h.size() * sizeof(double)));
+  HB_CUDA(ctx, cudaMemcpy(d, h.data(), h.size() * sizeof(double), cudaMemcpyHostToDevice));
+  ctx->h2d_bytes += (long long)(h.size() * sizeof(double));
+  ctx->onehot.push_back({{A, C}, d});
+  *out = d;
+  return HIST_OK;
+}
+
 // Host part of the DPMatrix constructor for one pair: argument checks, the composed key tables of the two guide rows and
 // the byte layout of the pair's arrays.  Band keys, edge slots and the anti-diagonal layout are computed on the device
 // (pair_layout_kernel) from the profiles' structure images.
@@ -1282,6 +1350,18 @@ int plan_pair(hist_ctx* ctx, const hist_profile* x, const hist_profile* y, const
     o.d_cb = Dv.reserve((size_t)p->n * sizeof(int4));
     o.d_ao_edges = Dv.reserve(nt1 * 2 * sizeof(int4));
     o.d_no_edges = Dv.reserve(nt1 * 2 * sizeof(int4));
+    // a leaf the library built from residues (and not a codon batch, whose leftMultiply runs on the tensor cores)
+    o.tok = p->d_tokens != nullptr && p->chain && p->n >= 3 && !leftmul_tc_applicable(A, C);
+    if (o.tok) {
+      const size_t rows = (size_t)A + 1;
+      o.k_sub = Dv.reserve(rows * K * sizeof(double));
+      o.k_H = Dv.reserve(rows * Kp * sizeof(float));
+      o.k_ex = Dv.reserve(rows * sizeof(int));
+      o.k_rs = Dv.reserve(rows * sizeof(float));
+      o.k_ins = Dv.reserve(rows * sizeof(float));
+      o.k_rootsub = Dv.reserve(rows * sizeof(double));
+      o.k_insl = Dv.reserve(rows * sizeof(double));
+    }
     return o;
   };
   b.ox = layout_side(x);
@@ -1347,7 +1427,7 @@ int plan_pair(hist_ctx* ctx, const hist_profile* x, const hist_profile* y, const
 }
 
 // Resolve the device pointers of one pair once its two arena parts are placed (the cell planes follow later).
-void place_pair(PairBuild& b, char* arena, size_t scal_off, size_t lay_off) {
+void place_pair(PairBuild& b, char* arena, size_t scal_off, size_t lay_off, const double* onehot) {
   hist_pair* pr = b.pr;
   char* hb_ = arena + b.host_base;
   char* db = arena + b.dev_base;
@@ -1370,6 +1450,13 @@ void place_pair(PairBuild& b, char* arena, size_t scal_off, size_t lay_off) {
     s.in_edges = (int4*)(db + o.d_in_edges); s.bm = (int4*)(db + o.d_bm);
     s.cf = (int4*)(db + o.d_cf); s.cb = (int4*)(db + o.d_cb);
     s.ao_edges = (int4*)(db + o.d_ao_edges); s.no_edges = (int4*)(db + o.d_no_edges);
+    if (o.tok) {
+      s.tokens = p->d_tokens;
+      s.tk_onehot = onehot;
+      s.tk_sub = (double*)(db + o.k_sub); s.tk_H = (float*)(db + o.k_H); s.tk_ex = (int*)(db + o.k_ex);
+      s.tk_rs = (float*)(db + o.k_rs); s.tk_ins = (float*)(db + o.k_ins);
+      s.tk_rootsub = (double*)(db + o.k_rootsub); s.tk_insl = (double*)(db + o.k_insl);
+    }
   };
   PairDev& D = pr->dev;
   side(D.x, pr->x, b.ox, false);
@@ -1463,7 +1550,13 @@ int pair_cells(hist_pair* pr, long long* n_cells) {
   hist_ctx* ctx = pr->ctx;
   hb_arena* a = pr->arena;
   if (!a->counted) {
+    // the count is the GCUPS unit, not something the reference's constructor computes: its kernel runs when asked for
     cudaSetDevice(ctx->device);
+    const int n = a->n_pairs;
+    const int chunks = std::max(1, std::min(a->max_diag / 16 + 1, std::max(32, (4 * ctx->sm_count + n - 1) / n)));  // 4 diagonals in flight per CTA
+    count_cells_kernel<<<dim3(chunks, n), 128, 0, ctx->stream>>>((PairDev* const*)(a->dev + a->ptr_off));
+    ctx->launches += 1;
+    HB_CUDA(ctx, cudaGetLastError());
     std::vector<double> scal((size_t)a->n_pairs * 4);
     HB_CUDA(ctx, cudaMemcpyAsync(scal.data(), a->dev + a->scal_off, scal.size() * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
     HB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
@@ -1593,6 +1686,13 @@ int prepare_enqueue(hist_ctx* ctx, int32_t n, const hist_profile* const* xs, con
     if (!xs[k] || !ys[k] || !hmms[k]) return set_err(ctx, HIST_ERR_ARG, "hist_pair_prepare: NULL argument");
   int rc = ensure_images(ctx, xs, ys, n);
   if (rc) return rc;
+  // lpAbsorb rows of the token classes of leaf sides, one table per (alphabet size, components) of the context
+  std::vector<const double*> onehots(n, nullptr);
+  for (int k = 0; k < n; ++k)
+    if ((xs[k]->d_tokens || ys[k]->d_tokens) && xs[k]->A == ys[k]->A && xs[k]->C == ys[k]->C) {
+      rc = ensure_onehot(ctx, xs[k]->A, xs[k]->C, &onehots[k]);
+      if (rc) return rc;
+    }
   tm.lap("profile images");
   pd.builds.clear();
   pd.builds.resize(n);
@@ -1650,7 +1750,8 @@ int prepare_enqueue(hist_ctx* ctx, int32_t n, const hist_profile* const* xs, con
   int maxN = 1, maxNt = 1, maxDiag = 1, maxKp = 4, maxKC = 1;
   parallel_for(n, 32, [&](int k) {
     PairBuild& b = builds[k];
-    place_pair(b, arena->dev, scal_off + (size_t)k * 4 * sizeof(double), lay_off + (size_t)k * sizeof(LayoutOut));
+    place_pair(b, arena->dev, scal_off + (size_t)k * 4 * sizeof(double), lay_off + (size_t)k * sizeof(LayoutOut),
+               (b.ox.tok || b.oy.tok) ? onehots[k] : nullptr);
     char* base = st + b.host_base;
     for (auto& c : b.host.copies) memcpy(base + c.first, c.second.first, c.second.second);
     memcpy(base + b.h_pairdev, &b.pr->dev, sizeof(PairDev));
@@ -1744,11 +1845,27 @@ int prepare_enqueue(hist_ctx* ctx, int32_t n, const hist_profile* const* xs, con
     } else {
       prepare_side_kernel<false><<<dim3(maxN, n, 2), threads, (size_t)stride * sizeof(double), ctx->stream>>>(dptrs, stride);
     }
+    bool any_tok = false;
+    int maxA = 1;
+    for (int k = 0; k < n; ++k) {
+      any_tok = any_tok || builds[k].ox.tok || builds[k].oy.tok;
+      maxA = std::max(maxA, builds[k].pr->dev.A);
+    }
+    if (any_tok) {   // (never in a tensor batch)
+      if (threads == 32) {
+        const int per_cta = 8;
+        prepare_side_kernel<true, true><<<dim3((maxA + 1 + per_cta - 1) / per_cta, n, 2), dim3(32, per_cta), (size_t)per_cta * stride * sizeof(double), ctx->stream>>>(dptrs, stride);
+      } else {
+        prepare_side_kernel<false, true><<<dim3(maxA + 1, n, 2), threads, (size_t)stride * sizeof(double), ctx->stream>>>(dptrs, stride);
+      }
+      leaf_scatter_kernel<<<dim3((maxN + 7) / 8, n, 2), dim3(32, 8), 0, ctx->stream>>>(dptrs);
+      ctx->launches += 2;
+    }
     prepare_trans_kernel<<<dim3((maxNt + 127) / 128, n, 2), 128, 0, ctx->stream>>>(dptrs);
     pack_meta_kernel<<<dim3((maxN + 127) / 128, n, 2), 128, 0, ctx->stream>>>(dptrs);
-    const int chunks = std::max(1, std::min(maxDiag / 16 + 1, std::max(32, (4 * ctx->sm_count + n - 1) / n)));  // 4 diagonals in flight per CTA
-    count_cells_kernel<<<dim3(chunks, n), 128, 0, ctx->stream>>>(dptrs);
-    ctx->launches += 5;
+    arena->ptr_off = ptr_off;
+    arena->max_diag = maxDiag;
+    ctx->launches += 4;
     if (!rc) rc = check_cuda(ctx, cudaGetLastError(), "prepare kernels");
   }
   tm.lap("enqueue");

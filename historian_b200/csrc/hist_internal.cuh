@@ -70,6 +70,11 @@ struct SideDev {
   double* sub;           // [n][K] leftMultiply result (profile.cpp:78-91), -inf rows for null states
   double* rootsub;       // [n]
   double* insl;          // [n]
+  // Leaf sides (profiles the library built from residues): the constructor tables take only A+1 distinct rows, one per
+  // residue and one for the wildcard.  They are computed once per (merge, side) and scattered by the residue of each state.
+  const int8_t* tokens;       // [n-2] token of state i+1 (< 0: wildcard); NULL: not a leaf side, every row is computed
+  const double* tk_onehot;    // [A+1][K] lpAbsorb rows of the token classes (profile.cpp:52-66)
+  double* tk_sub; float* tk_H; int* tk_ex; float* tk_rs; float* tk_ins; double* tk_rootsub; double* tk_insl;   // [A+1] rows
   // envelope
   int* key;              // [n] cum[rowPosToCol[closestLeafPos]] (written by pair_layout_kernel)
   const uint8_t* near_;  // [n] xNearStart / yNearEnd
@@ -205,8 +210,8 @@ struct hb_arena {
   size_t bytes;
   int refs;
   // pair arenas: the exact in-envelope cell counts (the GCUPS unit) stay on the device until somebody asks (hb::pair_cells)
-  size_t scal_off = 0;
-  int n_pairs = 0;
+  size_t scal_off = 0, ptr_off = 0;
+  int n_pairs = 0, max_diag = 1;
   bool counted = false;
   std::vector<long long> n_cells;
 };
@@ -238,6 +243,7 @@ struct hist_ctx {
   char* staging_img;
   size_t staging_img_bytes;
   cudaEvent_t ev_img;
+  std::vector<std::pair<std::pair<int, int>, double*>> onehot;   // (A, C) -> device table of token-class lpAbsorb rows
   long long h2d_bytes;   // bytes the library has copied host -> device for profiles and DPMatrix constructors (bench.py)
 };
 
@@ -252,6 +258,7 @@ struct hist_profile {
   bool empty;                 // Profile::isEmpty
   bool sorted_in;             // every in-list ascending in source state, no repeated (src,dest)
   bool chain = false;         // leaf profile built by the library: transition t is t -> t+1, states 1..n-2 emit
+  const int8_t* d_tokens = nullptr;   // leaf built by the library: its tokens on the device ([n-2], inside `arena`)
   bool leaf_std = false;      // chain whose closest-leaf positions are its own residues' (or absent): image generated on the device
   int refs = 0;               // pairs currently built on this profile (hist_profile_destroy defers while > 0)
   bool doomed = false;        // destroy requested while pairs still referred to it
