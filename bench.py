@@ -38,7 +38,6 @@ BRANCH = 0.05
 N_LEAVES = 1024
 ROOT_LEN = 1000
 # dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel per launch, from the ncu --set full capture under profiles/ (None = not captured)
-EM_TRAFFIC_BYTES = 5.78e9     # profiles/r01_sumprod_ncu_details_final.txt: sumprod_columns_kernel 3.68 GB read + 2.10 GB written per launch (default EM family)
 FILL_TRAFFIC_BYTES = 1.387e9   # profiles/r02_fill_chain2_ncu_details.txt: fill_chain2_kernel<5> 0.348 GB read + 1.039 GB written per launch (default family)
 # FP32 work of one cell update in the chain kernel: K-term absorb dot product (K FMA) + 24 FMA/FMUL of the five state sums
 # + 9 scale/emission multiplies + 5 normalisation multiplies, FMA counted as 2 flop
@@ -310,7 +309,10 @@ def em_leg(ctx, args, rank, world, local, barrier):
     out = None
     if rank == 0:
         A, Cc = model.alph_size, model.components
-        alg_bytes = 3.0 * Cc * N * A * 8 + N        # E/F/G messages of one column + its characters
+        # E/F/G messages of the UNGAPPED nodes of every column (the kernels visit nothing else) + its characters
+        ungapped = int(np.count_nonzero(~np.isin(mine, [ord("-"), ord(".")])))
+        alg_total = 3.0 * Cc * A * 8 * ungapped + float(N) * (hi - lo)
+        alg_bytes = alg_total / max(1, hi - lo)
         per_launch_s = kernel_ms / 1e3 / max(1, kernel_launches)
         peaks = {}
         try:
@@ -339,9 +341,13 @@ def em_leg(ctx, args, rank, world, local, barrier):
                           "parallelism": "columns sharded over %d GPU(s), one all-reduce of %d doubles per step" % (world, sp.counts_size)},
                "e2e": {"value": n_cols * steps / (e2e_ms / 1e3), "unit": "columns/s", "h2d_bytes_per_step": int((hi - lo) * N),
                        "d2h_bytes_per_step": int(8 * sp.counts_size)},
-               "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": EM_TRAFFIC_BYTES if (world == 1 and int(n_cols) == 12997 and int(N) == 8191) else None,
-                            "kernel": "hb::sumprod_columns_kernel", "avg_launch_ms": 1e3 * per_launch_s,
-                            "algorithmic_bytes_per_column": alg_bytes, "columns_per_launch": int(hi - lo)},
+               "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                            "kernel": "one hist_sumprod_columns call: hb::dn_up / dn_down / dn_counts / dn_root over the dense columns (node-major, one launch per tree level) "
+                                      "+ hb::sumprod_columns_kernel over the sparse ones",
+                            "avg_launch_ms": 1e3 * per_launch_s, "algorithmic_bytes_per_column": alg_bytes, "ungapped_nodes": ungapped,
+                            "columns_per_launch": int(hi - lo),
+                            "note": "algorithmic bytes = 3*C*A*8 per UNGAPPED node of each column + N characters per column (full-tree columns are "
+                                    "996 of 12 997); the call is latency-bound on the level-by-level walk of the dense columns, not on HBM"},
                "cpu_baseline": base, "gpu_launches": int(2 * steps)}
     sp.close()
     return out

@@ -1886,8 +1886,9 @@ extern "C" int hist_pair_prepare_batch(hist_ctx* ctx, int32_t n, const hist_prof
   for (int k = 0; k < n; ++k) out[k] = nullptr;
   cudaSetDevice(ctx->device);
   // a level is shipped in sub-batches: while the device receives and tabulates one, the host threads build the next
-  // (every sub-batch costs one host synchronisation -- the layout totals -- so a level goes in two pieces at most)
-  int parts = n >= 256 ? 2 : 1;
+  // (every sub-batch costs one host synchronisation, the layout totals; measured on the 512-merge leaf level, end to
+  // end: 1 piece 8.4 G cells/s, 2 pieces 8.1, 4 pieces 7.2 -- so one piece unless HIST_B200_PREP_PARTS says otherwise)
+  int parts = 1;
   if (const char* e = getenv("HIST_B200_PREP_PARTS")) parts = std::max(1, std::min(n, atoi(e)));
   const int per = (n + parts - 1) / parts;
   std::vector<PrepPending> pend((n + per - 1) / per);
