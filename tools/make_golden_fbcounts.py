@@ -37,14 +37,15 @@ TREE_CASES = [
 KEEP = ("x.", "y.", "hmm.", "env.", "fbc.")
 
 
-def tree_cases():
+def tree_cases(sfx=""):
     import make_golden as G
     for name, n, bl, spec, gen, rec in TREE_CASES:
+        name += sfx
         with tempfile.TemporaryDirectory() as tmp:
             tf, gf = G.simulate(tmp, G.balanced(n, bl), gen, n)
             binf = os.path.join(tmp, "d.bin")
             root = 2 * n - 2
-            subprocess.run([os.path.join(BIN, "ref_dump"), binf, str(root), "sample", "-guide", gf, "-tree", tf] + rec, check=True,
+            subprocess.run([os.path.join(BIN, "ref_dump" + sfx), binf, str(root), "sample", "-guide", gf, "-tree", tf] + rec, check=True,
                            cwd=G.REF, env=dict(os.environ, REF_DUMP_COUNTS="1"), stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
             d = D.read_dump(binf)
         pfx = "n%d." % root
@@ -58,9 +59,12 @@ def tree_cases():
               "%.1f kB" % (os.path.getsize(os.path.join(OUT, name + ".npz")) / 1e3))
 
 
-def main():
-    tree_cases()
+def main(sfx=""):
+    """sfx "": the reference as shipped (table log-sum-exp); "_exact": the same sources compiled with the reference's own
+    -DLOG_SUM_EXP_SLOW switch (oracle/Makefile ref_exact) -> tests/golden/fbcounts_*_exact.npz, exact arithmetic."""
+    tree_cases(sfx)
     for name, spec, gen, (tl, tr), band in CASES:
+        name += sfx
         with tempfile.TemporaryDirectory() as tmp:
             tf = os.path.join(tmp, "tree.nh")
             open(tf, "w").write("(x:%g,y:%g);\n" % (tl, tr))
@@ -80,7 +84,7 @@ def main():
                 for k, v in rows.items():
                     f.write(">%s\n%s\n" % (k, "".join(v[i] for i in keep)))
             binf = os.path.join(tmp, "d.bin")
-            subprocess.run([os.path.join(BIN, "ref_dump_fbcounts"), binf, "preset:" + spec, gf, tf, str(band)], check=True,
+            subprocess.run([os.path.join(BIN, "ref_dump_fbcounts" + sfx), binf, "preset:" + spec, gf, tf, str(band)], check=True,
                            stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
             d = D.read_dump(binf)
         d = {k: (np.frombuffer(v.encode(), np.uint8) if isinstance(v, str) else v) for k, v in d.items()}
@@ -90,3 +94,4 @@ def main():
 
 if __name__ == "__main__":
     main()
+    main("_exact")
