@@ -171,36 +171,37 @@ __global__ void prepare_side_kernel(PairDev* const* __restrict__ pairs, int sm_s
   }
 }
 
-// Leaf sides: every state takes the rows of its residue's token class.  grid = (chunks, pairs, 2 sides), one warp per state.
+// Leaf sides: every state takes the rows of its residue's token class.  grid = (chunks, pairs, 2 sides); thread e of a
+// side writes element e of its state-major `sub` array, and of `H` and of the per-state scalars where e is in range, so
+// that consecutive threads write consecutive addresses.
 __global__ void leaf_scatter_kernel(PairDev* const* __restrict__ pairs) {
   const PairDev& P = *pairs[blockIdx.y];
   const SideDev& s = blockIdx.z == 1 ? P.y : P.x;
   if (!s.tokens) return;
-  const int i = blockIdx.x * blockDim.y + threadIdx.y, lane = threadIdx.x;
-  if (i >= s.n) return;
-  const int K = P.K, Kp = P.Kp;
-  if (i == 0 || i == s.n - 1) {   // START / END: the null-state rows of prepare_side_kernel
-    for (int k = lane; k < K; k += 32) s.sub[(size_t)i * K + k] = -INFINITY;
-    for (int k = lane; k < Kp; k += 32) s.H[(size_t)i * Kp + k] = 0.f;
-    if (lane == 0) {
-      s.ex[i] = 0;
-      s.rs[i] = 1.f;
-      s.ins[i] = 1.f;
-      s.rootsub[i] = -INFINITY;
-      s.insl[i] = -INFINITY;
+  const int K = P.K, Kp = P.Kp, A = P.A, n = s.n;
+  const long long total = (long long)n * max(K, Kp);
+  for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total; e += (long long)gridDim.x * blockDim.x) {
+    auto token_class = [&](int i) {   // -1: START / END (the null-state rows of prepare_side_kernel)
+      if (i == 0 || i == n - 1) return -1;
+      const int q = s.tokens[i - 1];
+      return q < 0 || q >= A ? A : q;
+    };
+    if (e < (long long)n * K) {
+      const int i = (int)(e / K), k = (int)(e - (long long)i * K), q = token_class(i);
+      s.sub[e] = q < 0 ? -INFINITY : s.tk_sub[(size_t)q * K + k];
     }
-    return;
-  }
-  int q = s.tokens[i - 1];
-  if (q < 0 || q >= P.A) q = P.A;
-  for (int k = lane; k < K; k += 32) s.sub[(size_t)i * K + k] = s.tk_sub[(size_t)q * K + k];
-  for (int k = lane; k < Kp; k += 32) s.H[(size_t)i * Kp + k] = s.tk_H[(size_t)q * Kp + k];
-  if (lane == 0) {
-    s.ex[i] = s.tk_ex[q];
-    s.rs[i] = s.tk_rs[q];
-    s.ins[i] = s.tk_ins[q];
-    s.rootsub[i] = s.tk_rootsub[q];
-    s.insl[i] = s.tk_insl[q];
+    if (e < (long long)n * Kp) {
+      const int i = (int)(e / Kp), k = (int)(e - (long long)i * Kp), q = token_class(i);
+      s.H[e] = q < 0 ? 0.f : s.tk_H[(size_t)q * Kp + k];
+    }
+    if (e < n) {
+      const int i = (int)e, q = token_class(i);
+      s.ex[i] = q < 0 ? 0 : s.tk_ex[q];
+      s.rs[i] = q < 0 ? 1.f : s.tk_rs[q];
+      s.ins[i] = q < 0 ? 1.f : s.tk_ins[q];
+      s.rootsub[i] = q < 0 ? -INFINITY : s.tk_rootsub[q];
+      s.insl[i] = q < 0 ? -INFINITY : s.tk_insl[q];
+    }
   }
 }
 
@@ -1837,8 +1838,12 @@ int prepare_enqueue(hist_ctx* ctx, int32_t n, const hist_profile* const* xs, con
     const int stride = maxKC + 32;
     bool tensor = true;   // every pair of the batch is a one-component codon merge: leftMultiply as a tcgen05 GEMM
     for (int k = 0; k < n && tensor; ++k) tensor = leftmul_tc_applicable(builds[k].pr->dev.A, builds[k].pr->dev.C);
+    bool all_tok = true;   // every side of every pair is a leaf side: the per-state pass has nothing to do
+    for (int k = 0; k < n && all_tok; ++k) all_tok = builds[k].ox.tok && builds[k].oy.tok;
     if (tensor) {
       rc = launch_leftmul_tc(ctx, dptrs, n, maxN);
+    } else if (all_tok) {
+      ctx->launches -= 1;
     } else if (threads == 32) {
       const int per_cta = 8;
       prepare_side_kernel<true><<<dim3((maxN + per_cta - 1) / per_cta, n, 2), dim3(32, per_cta), (size_t)per_cta * stride * sizeof(double), ctx->stream>>>(dptrs, stride);
@@ -1858,7 +1863,7 @@ int prepare_enqueue(hist_ctx* ctx, int32_t n, const hist_profile* const* xs, con
       } else {
         prepare_side_kernel<false, true><<<dim3(maxA + 1, n, 2), threads, (size_t)stride * sizeof(double), ctx->stream>>>(dptrs, stride);
       }
-      leaf_scatter_kernel<<<dim3((maxN + 7) / 8, n, 2), dim3(32, 8), 0, ctx->stream>>>(dptrs);
+      leaf_scatter_kernel<<<dim3((unsigned)std::min<long long>(((long long)maxN * maxKp + 255) / 256, 64), n, 2), 256, 0, ctx->stream>>>(dptrs);
       ctx->launches += 2;
     }
     prepare_trans_kernel<<<dim3((maxNt + 127) / 128, n, 2), 128, 0, ctx->stream>>>(dptrs);
