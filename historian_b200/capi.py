@@ -40,6 +40,8 @@ def load():
     lib.hist_ctx_synchronize.argtypes = [vp]
     lib.hist_ctx_launch_count.argtypes = [vp]
     lib.hist_ctx_launch_count.restype = C.c_int64
+    lib.hist_quickalign_batch.argtypes = [vp, C.c_int32, C.POINTER(D.QuickAlignPair), C.POINTER(D.QuickAlignScores), D.c_double_p,
+                                          D.c_int32_p, D.c_int32_p, D.c_uint8_p, D.c_int64_p, D.c_int32_p]
     lib.hist_ctx_h2d_bytes.argtypes = [vp]
     lib.hist_ctx_h2d_bytes.restype = C.c_int64
     lib.hist_ctx_set_timing.argtypes = [vp, C.c_int]
@@ -145,6 +147,30 @@ class Context:
     @property
     def launch_count(self):
         return int(self.lib.hist_ctx_launch_count(self.h))
+
+    def quickalign(self, pairs, submat, scores, want_paths=True):
+        """QuickAlignMatrix (quickalign.cpp:7-214) for a batch of pairs: hist_quickalign_batch.
+        pairs: [(x_tok int8[], y_tok int8[], diagonals int32[])]; submat [A][A]; scores: the 11 scalars
+        (noGap, gapOpen, gapExtend, m2m, m2i, m2d, i2i, i2m, i2d, d2d, d2m).
+        Returns (result[n], ends[n][2], [path uint8[] per pair] or None)."""
+        n = len(pairs)
+        sub = np.ascontiguousarray(submat, np.float64)
+        sc = D.QuickAlignScores(int(sub.shape[0]), _p(sub, C.c_double), *[float(v) for v in scores])
+        keep, arr = [], (D.QuickAlignPair * n)()
+        off = np.zeros(n + 1, np.int64)
+        for k, (xt, yt, dg) in enumerate(pairs):
+            xt, yt, dg = np.ascontiguousarray(xt, np.int8), np.ascontiguousarray(yt, np.int8), np.ascontiguousarray(dg, np.int32)
+            keep.append((xt, yt, dg))
+            arr[k] = D.QuickAlignPair(len(xt), len(yt), _p(xt, C.c_int8), _p(yt, C.c_int8), len(dg), _p(dg, C.c_int32))
+            off[k + 1] = off[k] + len(xt) + len(yt)
+        result, xe, ye = np.zeros(n), np.zeros(n, np.int32), np.zeros(n, np.int32)
+        buf = np.zeros(max(1, int(off[n])), np.uint8) if want_paths else None
+        plen = np.zeros(n, np.int32)
+        self.check(self.lib.hist_quickalign_batch(self.h, n, arr, C.byref(sc), _p(result, C.c_double), _p(xe, C.c_int32), _p(ye, C.c_int32),
+                                                  _p(buf, C.c_uint8) if want_paths else None, _p(off, C.c_int64) if want_paths else None,
+                                                  _p(plen, C.c_int32) if want_paths else None))
+        paths = [buf[off[k]:off[k] + plen[k]].copy() for k in range(n)] if want_paths else None
+        return result, np.stack([xe, ye], 1), paths
 
     @property
     def h2d_bytes(self):

@@ -273,6 +273,18 @@ class Envelope:
         return Envelope(max_distance, cum, r1, r2)
 
 
+class QuickAlignScores(C.Structure):
+    """hist_quickalign_scores (quickalign.cpp:22-50)."""
+    _fields_ = [("alph_size", C.c_int32), ("submat", C.POINTER(C.c_double))] + [(k, C.c_double) for k in (
+        "no_gap", "gap_open", "gap_extend", "m2m", "m2i", "m2d", "i2i", "i2m", "i2d", "d2d", "d2m")]
+
+
+class QuickAlignPair(C.Structure):
+    """hist_quickalign_pair."""
+    _fields_ = [("x_len", C.c_int32), ("y_len", C.c_int32), ("x_tok", C.POINTER(C.c_int8)), ("y_tok", C.POINTER(C.c_int8)),
+                ("n_diagonals", C.c_int32), ("diagonals", C.POINTER(C.c_int32))]
+
+
 def read_dump(path):
     """Reads the binary container written by oracle/ref_dump.cpp into {name: ndarray|str}."""
     out = {}

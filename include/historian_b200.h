@@ -411,6 +411,36 @@ int hist_profile_sum_path_absorb_noalloc(hist_profile* profile, const double* lo
 /* Size of the built-in scratch array (HIST_NOALLOC_SCRATCH_BYTES of the loaded library). */
 int64_t hist_noalloc_scratch_bytes(void);
 
+/* ------------------------------------------------------------------ guide-alignment stage
+ * QuickAlignMatrix (quickalign.h:8-76, quickalign.cpp:7-214): three-state Viterbi alignment of two sequences inside
+ * the diagonals of a DiagonalEnvelope (diagenv.h:38-155) -- the pairwise step AlignGraph runs for every selected pair
+ * of sequences (span.cpp:57-158) before the progressive reconstruction.  The constructor does the fill; alignPath()
+ * the traceback.  Scores are bit-exact FP64 and paths identical to the reference's (ties included).
+ *
+ * hist_quickalign_scores: what the QuickAlignMatrix constructor derives from (model, time), quickalign.cpp:22-50:
+ *   submat [A][A] = logSubProb[i][j] - logInsProb[j]; the public members noGap, gapOpen, gapExtend, m2m .. d2m.
+ * hist_quickalign_pair: tokens as FastSeq::unvalidatedTokens gives them (< 0 or >= A: not in the alphabet) and
+ *   DiagonalEnvelope::diagonals (ascending values of i - j, within [1 - y_len, x_len - 1]; initFull or initSparse).
+ * Outputs per pair k: result[k] = mx.result (-inf: no alignment inside the envelope), x_end / y_end = mx.xEnd / yEnd,
+ *   and, if paths != NULL, the columns of alignPath() from paths[path_off[k]] on (capacity x_len + y_len, path_len[k]
+ *   columns): 3 = both rows, 1 = row 0 (x) only, 2 = row 1 (y) only; path_len[k] = 0 when result is -inf. */
+typedef struct {
+  int32_t alph_size;
+  const double* submat;
+  double no_gap, gap_open, gap_extend;
+  double m2m, m2i, m2d, i2i, i2m, i2d, d2d, d2m;
+} hist_quickalign_scores;
+typedef struct {
+  int32_t x_len, y_len;
+  const int8_t* x_tok;
+  const int8_t* y_tok;
+  int32_t n_diagonals;
+  const int32_t* diagonals;
+} hist_quickalign_pair;
+int hist_quickalign_batch(hist_ctx* ctx, int32_t n, const hist_quickalign_pair* pairs, const hist_quickalign_scores* scores,
+                          double* result, int32_t* x_end, int32_t* y_end, uint8_t* paths, const int64_t* path_off,
+                          int32_t* path_len);
+
 /* ------------------------------------------------------------------ sum-product
  * SumProduct / AlignColSumProduct (sumprod.h:32-104, sumprod.cpp).
  * The model is passed in eigen-decomposed form (EigenModel, model.cpp:1135-1199):

@@ -234,3 +234,18 @@ def split_counts(counts, Cc, A):
     root = counts[7:7 + Cc * A].reshape(Cc, A)
     ec = counts[7 + Cc * A:].reshape(Cc, A, A, 2)
     return counts[:7], root, ec[..., 0] + 1j * ec[..., 1]
+
+
+# ------------------------------------------------------------------ guide-alignment stage (oracle/oracle_quickalign.cpp)
+def quickalign(x_tok, y_tok, diagonals, submat, scores):
+    """QuickAlignMatrix over the envelope `diagonals`: (result, (xEnd, yEnd), path uint8[] or None)."""
+    xt, yt = np.ascontiguousarray(x_tok, np.int8), np.ascontiguousarray(y_tok, np.int8)
+    dg = np.ascontiguousarray(diagonals, np.int32)
+    sub = np.ascontiguousarray(submat, np.float64)
+    sc = D.QuickAlignScores(int(sub.shape[0]), _p(sub, C.c_double), *[float(v) for v in scores])
+    pr = D.QuickAlignPair(len(xt), len(yt), _p(xt, C.c_int8), _p(yt, C.c_int8), len(dg), _p(dg, C.c_int32))
+    res, xe, ye, n = C.c_double(), C.c_int32(), C.c_int32(), C.c_int32()
+    path = np.zeros(len(xt) + len(yt), np.uint8)
+    rc = lib().oracle_quickalign(C.byref(pr), C.byref(sc), C.byref(res), C.byref(xe), C.byref(ye), _p(path, C.c_uint8), C.byref(n))
+    assert rc == 0, "oracle traceback inconsistent"
+    return res.value, (xe.value, ye.value), (path[:n.value].copy() if np.isfinite(res.value) else None)
