@@ -530,6 +530,58 @@ def codon_leg(ctx, args):
                                                 "kernel": "hb::leftmul_tc_kernel: tcgen05.mma kind::tf32 (3xTF32), M=128 N=64 K=64 per tile, FP32 accumulators in TMEM"},
             "tensor_pipe": CODON_TENSOR_PIPE}
 
+# ------------------------------------------------------------------ guide-alignment leg
+def guide_leg(ctx, args, lg, guide_rows):
+    """The pairwise step of the guide-alignment stage on the bench family: QuickAlignMatrix (quickalign.cpp:7-214) for
+    --guide-pairs random pairs of its 1024 leaves (AlignGraph takes ceil(n log2 n) such pairs, span.cpp:57-118), k-mer seeded
+    envelopes (band 64, 6-mers, threshold 14), time 1.  End to end by construction: tokens and diagonals go up, scores, end
+    cells and paths come back inside the timed call."""
+    from historian_b200 import guide as G
+    A = len(lg.alphabet)
+    lut = {ch: k for k, ch in enumerate(lg.alphabet)}
+    toks = [np.array([lut.get(chr(c), -1) for c in row[row != ord("-")]], np.int8) for row in np.asarray(guide_rows)]
+    rng = np.random.default_rng(11)
+    n = len(toks)
+    picks = [(int(a), int(b)) for a, b in zip(rng.integers(0, n, args.guide_pairs), rng.integers(0, n, args.guide_pairs)) if a != b]
+    sub, sc = G.quickalign_scores(lg, 1.0)
+    # The reference's default envelope (kmerThreshold = -1, diagenv.cpp:109-116) is the FULL one whenever xLen * yLen * cellSize
+    # fits in memory, as it does for 1000-residue sequences; --guide-envelope sparse takes the k-mer seeded bands instead.
+    if args.guide_envelope == "sparse":
+        pairs = [(toks[a], toks[b], G.sparse_envelope(toks[a], toks[b], A)) for a, b in picks]
+    else:
+        pairs = [(toks[a], toks[b], np.arange(1 - len(toks[b]), len(toks[a]), dtype=np.int32)) for a, b in picks]
+    cells = sum(G.envelope_cells(dg, len(x), len(y)) for x, y, dg in pairs)
+    h2d0 = ctx.h2d_bytes
+    ctx.quickalign(pairs, sub, sc)
+    h2d = ctx.h2d_bytes - h2d0
+    launches0 = ctx.launch_count
+    walls = []
+    for _ in range(3):
+        t0 = time.perf_counter()
+        res, ends, paths = ctx.quickalign(pairs, sub, sc)
+        walls.append(time.perf_counter() - t0)
+    wall = min(walls)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as O
+    sample = list(range(0, len(pairs), max(1, len(pairs) // args.guide_cpu_pairs)))[: args.guide_cpu_pairs]
+    c0 = time.perf_counter()
+    for k in sample:
+        want, end, wpath = O.quickalign(*pairs[k], sub, sc)
+        assert want == res[k] and tuple(ends[k]) == end and np.array_equal(paths[k], wpath), "device alignment differs from the CPU oracle"
+    cpu_s = time.perf_counter() - c0
+    cpu_cells = sum(G.envelope_cells(pairs[k][2], len(pairs[k][0]), len(pairs[k][1])) for k in sample)
+    return {"metric": "guide-alignment Viterbi cells/s", "value": cells / wall / 1e9, "unit": "Gcells/s", "higher_is_better": True, "ms": 1e3 * wall,
+            "dtype": "f64 (bit-exact with the reference)", "pairs": len(pairs), "cells": int(cells),
+            "diagonals_per_pair": [int(min(len(p[2]) for p in pairs)), int(max(len(p[2]) for p in pairs))],
+            "config": {"workload": "lg_1024x1000_seed%d: %d random pairs of leaves, %s, time 1" % (
+                args.family_seed, len(pairs), "full envelopes (the reference's default at this size)" if args.guide_envelope == "full"
+                else "k-mer seeded envelopes (6-mers, >= 14 matches, band 64)")},
+            "e2e": {"value": cells / wall / 1e9, "unit": "Gcells/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(sum(len(p) for p in paths) + 16 * len(pairs))},
+            "gpu_launches": int((ctx.launch_count - launches0) // 3),
+            "cpu_baseline": {"value": cpu_cells / cpu_s / 1e9, "unit": "Gcells/s", "cores": 1, "kind": "port",
+                             "sample": "%d of the pairs through oracle/oracle_quickalign.cpp (dense cell array, 1 thread), %.1f s; scores, end cells and paths equal the device's" % (len(sample), cpu_s)}}
+
+
 # ------------------------------------------------------------------ GPU arm
 def gpu_arm(args):
     import torch
@@ -680,7 +732,12 @@ def gpu_arm(args):
     codon_line = None
     if not args.no_codon and world == 1:
         codon_line = codon_leg(ctx, args)
+    guide_line = None
+    if not args.no_guide and world == 1:
+        guide_line = guide_leg(ctx, args, lg, guide)
     if rank == 0:
+        if guide_line is not None:
+            line["guide_align"] = guide_line
         if em_line is not None:
             line["em_counts"] = em_line
         if recon_line is not None:
@@ -711,6 +768,10 @@ def main():
     ap.add_argument("--no-em", action="store_true", help="skip the EM count leg (profiling runs)")
     ap.add_argument("--no-recon", action="store_true", help="skip the whole-tree reconstruction leg")
     ap.add_argument("--no-codon", action="store_true", help="skip the codon (ECMrest) leg")
+    ap.add_argument("--no-guide", action="store_true", help="skip the guide-alignment (QuickAlign) leg")
+    ap.add_argument("--guide-pairs", type=int, default=1024, help="sequence pairs in the guide-alignment leg")
+    ap.add_argument("--guide-envelope", default="full", choices=["full", "sparse"])
+    ap.add_argument("--guide-cpu-pairs", type=int, default=24, help="pairs in that leg's cpu_baseline sample")
     ap.add_argument("--codon-constructor-only", action="store_true", help=argparse.SUPPRESS)
     ap.add_argument("--recon-reps", type=int, default=3, help="timed repetitions of the whole-tree reconstruction (best is reported)")
     ap.add_argument("--recon-ref-sampled", action="store_true", help="also time the reference binary in sampled mode on the 64-leaf family (minutes)")

@@ -84,7 +84,10 @@ __global__ void __launch_bounds__(1024) quickalign_kernel(const QaPair* __restri
   __syncthreads();
   const int A = S.A;
   for (int a = 2; a <= xLen + yLen; ++a) {
-    for (int k = tid; k < nd; k += T) {
+    // a thread owns PAIRS of consecutive slots: neighbouring diagonals have opposite parity, so in a contiguous band every
+    // thread has exactly one cell per step (slot-per-thread would leave every other lane idle)
+    for (int kk = 2 * tid; kk < nd + 1; kk += 2 * T)
+    for (int k = kk; k < min(kk + 2, nd); ++k) {
       const int delta = dg[k];
       if ((a ^ delta) & 1) continue;
       const int i = (a + delta) / 2, j = a - i;
@@ -219,7 +222,7 @@ extern "C" int hist_quickalign_batch(hist_ctx* ctx, int32_t n, const hist_quicka
     q.path = (long long)path_bytes; path_bytes += 2 * ((size_t)p.x_len + p.y_len);
     max_nd = std::max(max_nd, p.n_diagonals);
   }
-  const int threads = std::min(1024, (max_nd + 31) / 32 * 32);
+  const int threads = std::min(1024, ((max_nd + 1) / 2 + 31) / 32 * 32);   // one thread per pair of slots
   const size_t smem = (size_t)3 * max_nd * sizeof(double) + (size_t)threads * (sizeof(double) + 2 * sizeof(int));
   if (smem > ctx->smem_optin) return set_err(ctx, HIST_ERR_ARG, "hist_quickalign_batch: an envelope of %d diagonals needs %zu bytes of shared memory (limit %zu)", max_nd, smem, ctx->smem_optin);
   // one host blob: [pair records | tokens | diagonals | score table], one device allocation: [blob | results | traceback | paths]

@@ -1,0 +1,63 @@
+"""Host side of the guide-alignment stage's pairwise step: what the QuickAlignMatrix constructor
+derives from (model, time) before its fill (quickalign.cpp:22-50) and the k-mer seeded DiagonalEnvelope with a fixed
+threshold (diagenv.cpp:101-190, the kmerThreshold >= 0 branch).  The Viterbi fill and traceback run on the device
+(hist_quickalign_batch, csrc/hist_quickalign.cu)."""
+import math
+
+import numpy as np
+
+from .model import ProbModel
+
+
+def quickalign_scores(model, time):
+    """(submat [A][A], (noGap, gapOpen, gapExtend, m2m, m2i, m2d, i2i, i2m, i2d, d2d, d2m)), quickalign.cpp:22-50."""
+    pm = ProbModel(model, time)
+    with np.errstate(divide="ignore"):
+        sub = np.log(np.asarray(pm.subMat[0], float)) - np.log(np.asarray(pm.insVec[0], float))[None, :]
+    gap = pm.ins + (1 - pm.ins) * pm.del_
+    no_gap = 1 - gap
+    gap_ext = 1 / ((pm.ins / gap) / pm.insExt + (1 - pm.ins / gap) / pm.delExt)
+    no_gap_ext = 1 - gap_ext
+    lg = math.log
+    return sub, (lg(no_gap), lg(gap) + lg(no_gap_ext), lg(gap_ext), lg(no_gap * no_gap), lg(gap), lg(no_gap * gap),
+                 lg(gap_ext), lg(no_gap_ext * no_gap), lg(no_gap_ext * gap), lg(gap_ext), lg(no_gap_ext))
+
+
+def sparse_envelope(x_tok, y_tok, alph_size, kmer_len=6, band=64, threshold=14):
+    """DiagonalEnvelope::initSparse with kmerThreshold >= 0 (diagenv.cpp:101-190): diagonals i - j (0-based k-mer starts)
+    with at least `threshold` shared k-mers seed bands of +-band/2; diagonal 0 is always present; sequences shorter than
+    2 * (kmer_len + threshold) get the full envelope.  Returns the ascending diagonal list."""
+    x, y = np.asarray(x_tok, np.int64), np.asarray(y_tok, np.int64)
+    lx, ly = len(x), len(y)
+    lo, hi = 1 - ly, lx - 1
+    if lx < 2 * (kmer_len + threshold) or ly < 2 * (kmer_len + threshold):
+        return np.arange(lo, hi + 1, dtype=np.int32)
+
+    def kmers(t):
+        n = len(t) - kmer_len + 1
+        w = np.lib.stride_tricks.sliding_window_view(t, kmer_len)
+        valid = np.all(w >= 0, axis=1)
+        code = (np.where(w < 0, 0, w) * (alph_size ** np.arange(kmer_len - 1, -1, -1, dtype=np.int64))).sum(axis=1)   # makeKmer, fastseq.cpp
+        return np.arange(n)[valid], code[valid]
+
+    xi, xc = kmers(x)
+    yj, yc = kmers(y)
+    order = np.argsort(yc, kind="stable")
+    ys, yjs = yc[order], yj[order]
+    left, right = np.searchsorted(ys, xc, "left"), np.searchsorted(ys, xc, "right")
+    counts = {}
+    for i, a, b in zip(xi[right > left], left[right > left], right[right > left]):
+        for j in yjs[a:b]:
+            counts[i - j] = counts.get(i - j, 0) + 1
+    diags = {0}
+    half = band // 2
+    for d, c in counts.items():
+        if c >= threshold:
+            diags.update(range(max(lo, d - half), min(hi, d + half) + 1))
+    return np.array(sorted(diags), np.int32)
+
+
+def envelope_cells(diagonals, x_len, y_len):
+    """Cells the fill visits: for every diagonal the (i, j) with i - j = d, 1 <= i <= xLen, 1 <= j <= yLen."""
+    d = np.asarray(diagonals, np.int64)
+    return int(np.maximum(0, np.minimum(y_len, x_len - d) - np.maximum(1, 1 - d) + 1).sum())

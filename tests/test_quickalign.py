@@ -109,3 +109,20 @@ def test_argument_checks(ctx):
         ctx.quickalign([(x, y, np.array([3, 2], np.int32))], sub, scores)          # not ascending
     with pytest.raises(capi.HistError):
         ctx.quickalign([(x, y, np.array([len(x)], np.int32))], sub, scores)        # outside [1 - yLen, xLen - 1]
+
+
+def test_host_envelope_and_scores_match_the_reference():
+    """historian_b200/guide.py: the k-mer seeded envelope (diagenv.cpp:101-190, fixed threshold) reproduces the reference's
+    diagonal lists exactly, and the constructor's score table (quickalign.cpp:22-50) its values to rounding."""
+    from historian_b200 import guide
+    from historian_b200.model import RateModel
+    d = H.load_golden(os.path.join(H.GOLDEN_DIR, "quickalign_pf16593_pair_full.npz"))
+    sub, sc = guide.quickalign_scores(RateModel.preset("lg"), 1.0)
+    assert np.allclose(sub.ravel(), d["submat"], rtol=0, atol=1e-12) and np.allclose(sc, d["scores"], rtol=0, atol=1e-12)
+    for name, A, args in (("quickalign_lg8x300_sparse", 20, (5, 16, 2)), ("quickalign_jc5x200_sparse", 4, (6, 8, 1))):
+        d = H.load_golden(os.path.join(H.GOLDEN_DIR, name + ".npz"))
+        for k in range(int(d["n_pairs"][0])):
+            p = "p%d." % k
+            dg = guide.sparse_envelope(d[p + "x_tok"], d[p + "y_tok"], A, *args)
+            assert np.array_equal(dg, d[p + "diagonals"]), (name, k)
+            assert guide.envelope_cells(dg, len(d[p + "x_tok"]), len(d[p + "y_tok"])) > 0
