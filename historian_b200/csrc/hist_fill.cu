@@ -1958,18 +1958,39 @@ int launch_fill(hist_ctx* ctx, hist_pair* const* pairs_in, int n_in, int n_dir, 
     HB_CUDA(ctx, cudaEventRecord(e0, ctx->stream));
   }
   int rc = HIST_OK;
-  if (!chain.empty()) rc = launch_fill_chain(ctx, chain.data(), (int)chain.size(), n_dir, only_dir);
+  auto ensure_stream2 = [&]() -> int {
+    if (ctx->stream2) return HIST_OK;
+    HB_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking));
+    HB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
+    HB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
+    return HIST_OK;
+  };
+  bool forked = false;
+  if (!chain.empty()) {
+    if (n == 0) {
+      rc = launch_fill_chain(ctx, chain.data(), (int)chain.size(), n_dir, only_dir);
+    } else {
+      // a level of leaf merges with a few strips too wide for the chain kernel: those go through the three latency-bound
+      // launches of the DAG path (~1 ms whatever their number); run them beside the chain kernel, not after it
+      rc = ensure_stream2();
+      if (!rc) {
+        HB_CUDA(ctx, cudaEventRecord(ctx->ev_fork, ctx->stream));
+        HB_CUDA(ctx, cudaStreamWaitEvent(ctx->stream2, ctx->ev_fork, 0));
+        cudaStream_t main_stream = ctx->stream;
+        ctx->stream = ctx->stream2;
+        rc = launch_fill_chain(ctx, chain.data(), (int)chain.size(), n_dir, only_dir);
+        ctx->stream = main_stream;
+        forked = true;
+      }
+    }
+  }
   if (rc || n == 0) {
     // nothing but leaf merges in this batch
   } else if (narrow.empty() || wide.empty()) {
     rc = launch_fill_uniform(ctx, pairs, n, n_dir, only_dir);
   } else {
     // the few general strips are latency-bound on their own (one CTA each): run them beside the narrow part
-    if (!ctx->stream2) {
-      HB_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking));
-      HB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
-      HB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
-    }
+    { const int rc2 = ensure_stream2(); if (rc2) return rc2; }
     HB_CUDA(ctx, cudaEventRecord(ctx->ev_fork, ctx->stream));
     HB_CUDA(ctx, cudaStreamWaitEvent(ctx->stream2, ctx->ev_fork, 0));
     cudaStream_t main_stream = ctx->stream;
@@ -1977,6 +1998,10 @@ int launch_fill(hist_ctx* ctx, hist_pair* const* pairs_in, int n_in, int n_dir, 
     rc = launch_fill_uniform(ctx, wide.data(), (int)wide.size(), n_dir, only_dir);
     ctx->stream = main_stream;
     if (!rc) rc = launch_fill_uniform(ctx, narrow.data(), (int)narrow.size(), n_dir, only_dir);
+    HB_CUDA(ctx, cudaEventRecord(ctx->ev_join, ctx->stream2));
+    HB_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_join, 0));
+  }
+  if (forked) {
     HB_CUDA(ctx, cudaEventRecord(ctx->ev_join, ctx->stream2));
     HB_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_join, 0));
   }
