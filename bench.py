@@ -583,6 +583,42 @@ def guide_leg(ctx, args, lg, guide_rows):
                              "sample": "%d of the pairs through oracle/oracle_quickalign.cpp (dense cell array, 1 thread), %.1f s; scores, end cells and paths equal the device's" % (len(sample), cpu_s)}}
 
 
+# ------------------------------------------------------------------ distance-matrix leg
+def distmat_leg(ctx, args, lg, guide_rows):
+    """RateModel::distanceMatrix (model.cpp:506-655) of the bench family's guide alignment: n (n - 1) / 2 maximum-likelihood
+    distances, each a golden-section search over matrix exponentials.  End to end: the alignment goes up, the matrix comes back."""
+    from historian_b200 import descs as D, guide as G
+    rows = np.ascontiguousarray(np.asarray(guide_rows)[: args.distmat_rows], np.uint8)
+    n = len(rows)
+    spm, rate = D.SumProdModel.from_rate_model(lg), G.expected_substitution_rate(lg)
+    ctx.distance_matrix(spm, rate, rows[:8])
+    walls = []
+    for _ in range(2):
+        t0 = time.perf_counter()
+        dist = ctx.distance_matrix(spm, rate, rows)
+        walls.append(time.perf_counter() - t0)
+    wall = min(walls)
+    pairs = n * (n - 1) // 2
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as O
+    pick = np.linspace(0, n - 1, args.distmat_cpu_rows).astype(int)
+    c0 = time.perf_counter()
+    want = O.distance_matrix(spm, rate, rows[pick])
+    cpu_s = time.perf_counter() - c0
+    got = dist[np.ix_(pick, pick)]
+    iu = np.triu_indices(len(pick), 1)
+    rel = np.abs(got[iu] - want[iu]) / np.abs(want[iu])
+    assert np.all(rel <= 0.0101) and np.mean(rel <= 1e-6) >= 0.9, "device distances differ from the CPU oracle"
+    return {"metric": "distance-matrix pairs/s", "value": pairs / wall, "unit": "pairs/s", "higher_is_better": True, "s": wall, "dtype": "f64",
+            "config": {"workload": "lg_1024x1000_seed%d guide alignment: %d rows x %d columns, %d ML distances (100 golden-section iterations at most)" % (
+                args.family_seed, n, rows.shape[1], pairs)},
+            "e2e": {"value": pairs / wall, "unit": "pairs/s", "h2d_bytes_per_step": int(rows.size), "d2h_bytes_per_step": int(8 * n * n)},
+            "gpu_launches": 1,
+            "cpu_baseline": {"value": len(iu[0]) / cpu_s, "unit": "pairs/s", "cores": 1, "kind": "port",
+                             "sample": "the %d pairs among %d evenly spaced rows through oracle/oracle_distmat.cpp (eigen-decomposed exponentials, 1 thread), %.1f s; "
+                                       "device distances equal to 1e-6 on >= 90 %% of them, within the search's 1 %% on all" % (len(iu[0]), len(pick), cpu_s)}}
+
+
 # ------------------------------------------------------------------ GPU arm
 def gpu_arm(args):
     import torch
@@ -740,9 +776,14 @@ def gpu_arm(args):
     guide_line = None
     if not args.no_guide and world == 1:
         guide_line = guide_leg(ctx, args, lg, guide)
+    distmat_line = None
+    if not args.no_guide and world == 1:
+        distmat_line = distmat_leg(ctx, args, lg, guide)
     if rank == 0:
         if guide_line is not None:
             line["guide_align"] = guide_line
+        if distmat_line is not None:
+            line["distance_matrix"] = distmat_line
         if em_line is not None:
             line["em_counts"] = em_line
         if recon_line is not None:
@@ -774,9 +815,11 @@ def main():
     ap.add_argument("--no-em", action="store_true", help="skip the EM count leg (profiling runs)")
     ap.add_argument("--no-recon", action="store_true", help="skip the whole-tree reconstruction leg")
     ap.add_argument("--no-codon", action="store_true", help="skip the codon (ECMrest) leg")
-    ap.add_argument("--no-guide", action="store_true", help="skip the guide-alignment (QuickAlign) leg")
+    ap.add_argument("--no-guide", action="store_true", help="skip the guide-alignment (QuickAlign) and distance-matrix legs")
     ap.add_argument("--guide-pairs", type=int, default=1024, help="sequence pairs in the guide-alignment leg")
     ap.add_argument("--guide-envelope", default="full", choices=["full", "sparse"])
+    ap.add_argument("--distmat-rows", type=int, default=1024, help="rows of the guide alignment in the distance-matrix leg")
+    ap.add_argument("--distmat-cpu-rows", type=int, default=16, help="rows in that leg's cpu_baseline sample")
     ap.add_argument("--guide-cpu-pairs", type=int, default=24, help="pairs in that leg's cpu_baseline sample")
     ap.add_argument("--codon-constructor-only", action="store_true", help=argparse.SUPPRESS)
     ap.add_argument("--recon-reps", type=int, default=3, help="timed repetitions of the whole-tree reconstruction (best is reported)")

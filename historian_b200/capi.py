@@ -42,6 +42,7 @@ def load():
     lib.hist_ctx_launch_count.restype = C.c_int64
     lib.hist_quickalign_batch.argtypes = [vp, C.c_int32, C.POINTER(D.QuickAlignPair), C.POINTER(D.QuickAlignScores), D.c_double_p,
                                           D.c_int32_p, D.c_int32_p, D.c_uint8_p, D.c_int64_p, D.c_int32_p]
+    lib.hist_distance_matrix.argtypes = [vp, C.POINTER(D.ModelDesc), C.c_double, C.c_int32, C.c_int32, C.c_char_p, C.c_int32, D.c_double_p]
     lib.hist_ctx_h2d_bytes.argtypes = [vp]
     lib.hist_ctx_h2d_bytes.restype = C.c_int64
     lib.hist_ctx_set_timing.argtypes = [vp, C.c_int]
@@ -171,6 +172,17 @@ class Context:
                                                   _p(plen, C.c_int32) if want_paths else None))
         paths = [buf[off[k]:off[k] + plen[k]].copy() for k in range(n)] if want_paths else None
         return result, np.stack([xe, ye], 1), paths
+
+    def distance_matrix(self, sp_model, expected_sub_rate, rows, max_iterations=100):
+        """RateModel::distanceMatrix (model.cpp:533-553): hist_distance_matrix.  sp_model: descs.SumProdModel (alphabet, component
+        weights, eigen-decomposition); rows: uint8 [n][cols] gapped characters.  Returns dist [n][n]."""
+        rows = np.ascontiguousarray(rows, np.uint8)
+        n, cols = rows.shape
+        dist = np.zeros((n, n))
+        md = sp_model.desc()
+        self.check(self.lib.hist_distance_matrix(self.h, C.byref(md), float(expected_sub_rate), n, cols, rows.ctypes.data_as(C.c_char_p),
+                                                 int(max_iterations), _p(dist, C.c_double)))
+        return dist
 
     @property
     def h2d_bytes(self):

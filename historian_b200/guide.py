@@ -61,3 +61,19 @@ def envelope_cells(diagonals, x_len, y_len):
     """Cells the fill visits: for every diagonal the (i, j) with i - j = d, 1 <= i <= xLen, 1 <= j <= yLen."""
     d = np.asarray(diagonals, np.int64)
     return int(np.maximum(0, np.minimum(y_len, x_len - d) - np.maximum(1, 1 - d) + 1).sum())
+
+
+def expected_substitution_rate(model):
+    """RateModel::expectedSubstitutionRate (model.cpp:336-347): sum_c w_c sum_{i != j} eqm_c[i] R_c[i][j]."""
+    rate = 0.0
+    for c in range(model.components):
+        r = np.asarray(model.subRate[c], float)
+        eqm = np.asarray(model.getEqmProbVector(r), float)
+        rate += float(model.cptWeight[c]) * float((eqm[:, None] * r).sum() - (eqm * np.diag(r)).sum())
+    return rate
+
+
+def distance_matrix(ctx, model, rows, max_iterations=100):
+    """RateModel::distanceMatrix (model.cpp:533-553) of a gapped alignment (uint8 [n][cols]) on the device."""
+    from . import descs as D
+    return ctx.distance_matrix(D.SumProdModel.from_rate_model(model), expected_substitution_rate(model), rows, max_iterations)

@@ -514,6 +514,18 @@ int hist_sumprod_transform_counts(hist_sumprod* sp, const double* counts, double
  * be NULL.  For parity tests. */
 int hist_sumprod_branch_tables(hist_sumprod* sp, double* branch_sub, double* branch_esc);
 
+/* ------------------------------------------------------------------ distance-matrix stage
+ * RateModel::distanceMatrix (model.cpp:533-553): dist[i][j] = mlDistance of rows i and j of a gapped alignment --
+ * aligned residue-pair counts (model.cpp:506-531), then DistanceMatrixParams::tML (model.cpp:583-655): Jukes-Cantor
+ * first guess, bracket scan, golden-section steps to 1 % (max_iterations <= 0: the Jukes-Cantor estimate itself).
+ * model: alphabet, cpt_weight and the eigen-decomposition are used (P_t from eigenvalues, where the reference calls
+ * GSL's matrix exponential: agreement ~1e-13 in P, so results equal the reference's unless two trial likelihoods tie
+ * to that precision, and then differ by less than the search's 1 %).  expected_sub_rate =
+ * RateModel::expectedSubstitutionRate (model.cpp:336-347).  rows: [n_rows][n_cols] characters, gaps '-' '.', wildcard '*'.
+ * dist: [n_rows][n_rows], symmetric, zero diagonal. */
+int hist_distance_matrix(hist_ctx* ctx, const hist_model_desc* model, double expected_sub_rate, int32_t n_rows, int32_t n_cols,
+                         const char* rows, int32_t max_iterations, double* dist);
+
 #ifdef __cplusplus
 }
 #endif

@@ -249,3 +249,15 @@ def quickalign(x_tok, y_tok, diagonals, submat, scores):
     rc = lib().oracle_quickalign(C.byref(pr), C.byref(sc), C.byref(res), C.byref(xe), C.byref(ye), _p(path, C.c_uint8), C.byref(n))
     assert rc == 0, "oracle traceback inconsistent"
     return res.value, (xe.value, ye.value), (path[:n.value].copy() if np.isfinite(res.value) else None)
+
+
+# ------------------------------------------------------------------ distance-matrix stage (oracle/oracle_distmat.cpp)
+def distance_matrix(sp_model, expected_sub_rate, rows, max_iterations=100):
+    rows = np.ascontiguousarray(rows, np.uint8)
+    n, cols = rows.shape
+    dist = np.zeros((n, n))
+    md = sp_model.desc()
+    rc = lib().oracle_distance_matrix(C.byref(md), C.c_double(float(expected_sub_rate)), n, cols, rows.ctypes.data_as(C.c_char_p),
+                                      int(max_iterations), _p(dist, C.c_double))
+    assert rc == 0
+    return dist
