@@ -43,6 +43,7 @@ def load():
     lib.hist_quickalign_batch.argtypes = [vp, C.c_int32, C.POINTER(D.QuickAlignPair), C.POINTER(D.QuickAlignScores), D.c_double_p,
                                           D.c_int32_p, D.c_int32_p, D.c_uint8_p, D.c_int64_p, D.c_int32_p]
     lib.hist_distance_matrix.argtypes = [vp, C.POINTER(D.ModelDesc), C.c_double, C.c_int32, C.c_int32, C.c_char_p, C.c_int32, D.c_double_p]
+    lib.hist_build_tree.argtypes = [vp, C.c_int32, D.c_double_p, C.c_int32, C.c_double, D.c_int32_p, D.c_double_p]
     lib.hist_ctx_h2d_bytes.argtypes = [vp]
     lib.hist_ctx_h2d_bytes.restype = C.c_int64
     lib.hist_ctx_set_timing.argtypes = [vp, C.c_int]
@@ -183,6 +184,14 @@ class Context:
         self.check(self.lib.hist_distance_matrix(self.h, C.byref(md), float(expected_sub_rate), n, cols, rows.ctypes.data_as(C.c_char_p),
                                                  int(max_iterations), _p(dist, C.c_double)))
         return dist
+
+    def build_tree(self, dist, method=0, min_branch_length=1e-9):
+        """Tree::buildByUPGMA (method 0) / buildByNeighborJoining (method 1): hist_build_tree.  Returns (child [2n-1][2], branch_length [2n-1])."""
+        dist = np.ascontiguousarray(dist, np.float64)
+        n = len(dist)
+        child, blen = np.zeros((2 * n - 1, 2), np.int32), np.zeros(2 * n - 1)
+        self.check(self.lib.hist_build_tree(self.h, n, _p(dist, C.c_double), int(method), float(min_branch_length), _p(child, C.c_int32), _p(blen, C.c_double)))
+        return child, blen
 
     @property
     def h2d_bytes(self):

@@ -77,3 +77,24 @@ def distance_matrix(ctx, model, rows, max_iterations=100):
     """RateModel::distanceMatrix (model.cpp:533-553) of a gapped alignment (uint8 [n][cols]) on the device."""
     from . import descs as D
     return ctx.distance_matrix(D.SumProdModel.from_rate_model(model), expected_substitution_rate(model), rows, max_iterations)
+
+
+def newick(names, child, branch_length):
+    """Tree::toString (tree.cpp:56-102) of the tree hist_build_tree returns: internal nodes unnamed, branch lengths with the
+    stream's default 6 significant digits -- the text the reference parses back (tree.cpp:347-350), so its trees carry these
+    rounded lengths."""
+    import sys
+    n = len(names)
+    sys.setrecursionlimit(max(sys.getrecursionlimit(), 4 * n + 100))
+
+    def rec(k):
+        if child[k][0] < 0:
+            return names[k]
+        return "(" + ",".join("%s:%s" % (rec(int(c)), "%g" % branch_length[int(c)]) for c in child[k]) + ")"
+    return rec(2 * n - 2) + ";"
+
+
+def build_tree(ctx, names, dist, method="upgma"):
+    """Tree::buildByUPGMA / buildByNeighborJoining on the device -> Newick text equal to the reference's."""
+    child, blen = ctx.build_tree(dist, 0 if method == "upgma" else 1)
+    return newick(list(names), child, blen)

@@ -526,6 +526,15 @@ int hist_sumprod_branch_tables(hist_sumprod* sp, double* branch_sub, double* bra
 int hist_distance_matrix(hist_ctx* ctx, const hist_model_desc* model, double expected_sub_rate, int32_t n_rows, int32_t n_cols,
                          const char* rows, int32_t max_iterations, double* dist);
 
+/* Guide tree from a distance matrix: Tree::buildByUPGMA (tree.cpp:362-454; method 0, the default of `historian recon`) or
+ * Tree::buildByNeighborJoining (tree.cpp:240-352; method 1).  dist: [n][n] symmetric; min_branch_length:
+ * Tree::minBranchLength (TREE_MIN_BRANCH_LEN = 1e-9, tree.h:24).  Nodes 0 .. n-1 are the rows of the matrix, node n + r is
+ * created by the r-th join, the root is node 2n - 2.  child: [2n-1][2] (-1, -1 for leaves), branch_length: [2n-1] length
+ * of the branch above each node (0 for the root).  Joins and lengths are bit-identical to the reference's before it
+ * serialises the tree with 6 significant digits and parses it back (tree.cpp:347-350). */
+int hist_build_tree(hist_ctx* ctx, int32_t n, const double* dist, int32_t method, double min_branch_length, int32_t* child,
+                    double* branch_length);
+
 #ifdef __cplusplus
 }
 #endif

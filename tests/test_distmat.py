@@ -75,3 +75,15 @@ def test_edge_cases(ctx):
     assert got[0, 1] == 10.0 and got[0, 1] == want[0, 1]   # no counts: the scan finds no bracket, tUpper comes back
     assert got[2, 3] < 1e-3                      # identical up to case and a wildcard
     assert np.array_equal(ctx.distance_matrix(spm, rate, rows[:1]), np.zeros((1, 1)))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("path", FIX, ids=IDS)
+@pytest.mark.parametrize("method", ["upgma", "nj"])
+def test_trees_equal_the_reference(ctx, path, method):
+    """Tree::buildByUPGMA / buildByNeighborJoining (tree.cpp:240-461) from the reference's own distance matrix: the Newick text
+    (joins, child order, 6-digit branch lengths) must be the reference's, character for character."""
+    d, m, iters = load(path)
+    names = bytes(d["names"]).decode().split("\n")[:-1]
+    got = G.build_tree(ctx, names, d["dist"], method)
+    assert got == bytes(d[method]).decode()
