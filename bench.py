@@ -609,7 +609,25 @@ def distmat_leg(ctx, args, lg, guide_rows):
     iu = np.triu_indices(len(pick), 1)
     rel = np.abs(got[iu] - want[iu]) / np.abs(want[iu])
     assert np.all(rel <= 0.0101) and np.mean(rel <= 1e-6) >= 0.9, "device distances differ from the CPU oracle"
-    return {"metric": "distance-matrix pairs/s", "value": pairs / wall, "unit": "pairs/s", "higher_is_better": True, "s": wall, "dtype": "f64",
+    # the guide tree from that matrix (Tree::buildByUPGMA, the default of `historian recon`; tree.cpp:362-454)
+    ctx.build_tree(dist[:16, :16])
+    t0 = time.perf_counter()
+    child, blen = ctx.build_tree(dist, 0)
+    tree_s = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    child_nj, blen_nj = ctx.build_tree(dist, 1)
+    tree_nj_s = time.perf_counter() - t0
+    sub = min(n, args.tree_cpu_rows)
+    c0 = time.perf_counter()
+    wc, wb = O.build_tree(dist[:sub, :sub], 0)
+    tree_cpu_s = time.perf_counter() - c0
+    gc, gb = ctx.build_tree(dist[:sub, :sub], 0)
+    assert np.array_equal(gc, wc) and np.array_equal(gb, wb), "device UPGMA tree differs from the CPU oracle"
+    tree = {"upgma_s": tree_s, "nj_s": tree_nj_s, "leaves": n,
+            "cpu_baseline": {"value": tree_cpu_s, "unit": "s", "cores": 1, "kind": "port",
+                             "sample": "UPGMA on the first %d rows through oracle/oracle_tree.cpp (O(n^3): the full matrix costs (%d/%d)^3 times that), %.2f s; "
+                                       "children and branch lengths bit-identical to the device's" % (sub, n, sub, tree_cpu_s)}}
+    return {"metric": "distance-matrix pairs/s", "value": pairs / wall, "guide_tree": tree, "unit": "pairs/s", "higher_is_better": True, "s": wall, "dtype": "f64",
             "config": {"workload": "lg_1024x1000_seed%d guide alignment: %d rows x %d columns, %d ML distances (100 golden-section iterations at most)" % (
                 args.family_seed, n, rows.shape[1], pairs)},
             "e2e": {"value": pairs / wall, "unit": "pairs/s", "h2d_bytes_per_step": int(rows.size), "d2h_bytes_per_step": int(8 * n * n)},
@@ -819,6 +837,7 @@ def main():
     ap.add_argument("--guide-pairs", type=int, default=1024, help="sequence pairs in the guide-alignment leg")
     ap.add_argument("--guide-envelope", default="full", choices=["full", "sparse"])
     ap.add_argument("--distmat-rows", type=int, default=1024, help="rows of the guide alignment in the distance-matrix leg")
+    ap.add_argument("--tree-cpu-rows", type=int, default=384, help="rows of the UPGMA cpu_baseline sample")
     ap.add_argument("--distmat-cpu-rows", type=int, default=16, help="rows in that leg's cpu_baseline sample")
     ap.add_argument("--guide-cpu-pairs", type=int, default=24, help="pairs in that leg's cpu_baseline sample")
     ap.add_argument("--codon-constructor-only", action="store_true", help=argparse.SUPPRESS)

@@ -261,3 +261,13 @@ def distance_matrix(sp_model, expected_sub_rate, rows, max_iterations=100):
                                       int(max_iterations), _p(dist, C.c_double))
     assert rc == 0
     return dist
+
+
+def build_tree(dist, method=0, min_branch_length=1e-9):
+    """oracle/oracle_tree.cpp: (child [2n-1][2], branch_length [2n-1])."""
+    dist = np.ascontiguousarray(dist, np.float64)
+    n = len(dist)
+    child, blen = np.zeros((2 * n - 1, 2), np.int32), np.zeros(2 * n - 1)
+    rc = lib().oracle_build_tree(n, _p(dist, C.c_double), int(method), C.c_double(float(min_branch_length)), _p(child, C.c_int32), _p(blen, C.c_double))
+    assert rc == 0
+    return child, blen

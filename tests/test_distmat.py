@@ -87,3 +87,27 @@ def test_trees_equal_the_reference(ctx, path, method):
     names = bytes(d["names"]).decode().split("\n")[:-1]
     got = G.build_tree(ctx, names, d["dist"], method)
     assert got == bytes(d[method]).decode()
+
+
+@pytest.mark.parametrize("path", FIX, ids=IDS)
+@pytest.mark.parametrize("method", ["upgma", "nj"])
+def test_oracle_trees_equal_the_reference(path, method):
+    d, m, iters = load(path)
+    names = bytes(d["names"]).decode().split("\n")[:-1]
+    child, blen = O.build_tree(d["dist"], 0 if method == "upgma" else 1)
+    assert G.newick(names, child, blen) == bytes(d[method]).decode()
+
+
+@pytest.mark.gpu
+def test_device_tree_is_bit_identical_to_the_oracle_on_a_large_matrix(ctx):
+    """300 rows (more than any fixture), distances with many exact ties (multiples of 1/8) so that the first-minimum rule decides
+    joins: children and branch lengths must be equal bit for bit, for both methods."""
+    rng = np.random.default_rng(3)
+    n = 300
+    a = rng.integers(1, 40, (n, n)) / 8.0
+    dist = np.triu(a, 1) + np.triu(a, 1).T
+    for method in (0, 1):
+        child, blen = ctx.build_tree(dist, method)
+        wc, wb = O.build_tree(dist, method)
+        assert np.array_equal(child, wc), method
+        assert np.array_equal(blen, wb), method
