@@ -708,6 +708,9 @@ def gpu_arm(args):
     # ---- end to end from host buffers through the public C-ABI calls
     seqs = cherry_sequences(guide, n_pairs)
     envs = [e for _, _, e in inputs]
+    # the host buffer of the step: the residue strings back to back (as a FASTA reader holds them) + their offsets
+    packed = np.frombuffer(b"".join(seqs), np.uint8).copy()
+    packed_off = np.concatenate([[0], np.cumsum([len(q) for q in seqs])]).astype(np.int64)
 
     # the ctypes argument arrays of hist_pair_prepare_batch (pointers to the host descriptors) are built once;
     # every step passes them, with that step's fresh profile handles, to the C ABI
@@ -717,12 +720,12 @@ def gpu_arm(args):
         # the calls a reference user makes per level: leaf Profile constructors (profile.cpp:23-76) from the residue
         # strings, DPMatrix constructors (forward.cpp:11-66), Forward + Backward fills, likelihoods read back
         h2d0 = ctx.h2d_bytes   # counted inside the library at every host -> device copy it issues
-        leaves = ctx.upload_sequences(seqs, lg.alphabet, lg.components)
-        pr = plan.run(leaves[0::2], leaves[1::2])
-        r = ctx.fill_batch(pr, backward=True)
+        leaves = ctx.upload_packed(packed, packed_off, lg.alphabet, lg.components)   # hist_profile_from_residues
+        pr = plan.run_batch(leaves)                                                  # hist_pair_prepare_batch
+        r = ctx.fill_batch(pr, backward=True)                                        # hist_fill_batch, likelihoods read back
         h2d = ctx.h2d_bytes - h2d0
-        ctx.close_all(pr)
-        ctx.close_all(leaves)
+        pr.close()                                                                   # hist_pairs_destroy
+        leaves.close()                                                               # hist_profiles_destroy
         return r, h2d
 
     for _ in range(min(args.warmup, 2)):
@@ -770,7 +773,7 @@ def gpu_arm(args):
             "config": workload_config(n_pairs),
             "e2e": {"value": total_cells_per_step * e2e_steps / (e2e_ms / 1e3) / 1e9, "unit": UNIT,
                     "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": int(n_pairs * 24), "steps": e2e_steps,
-                    "host_memory": "residue strings and guide-row descriptors in pageable host memory, staged through the context's pinned buffers; profile structure, band keys and the anti-diagonal layout are built on the device"},
+                    "host_memory": "one buffer of residue strings and the guide-row descriptors in pageable host memory, staged through the context's pinned buffers; profile structure, band keys and the anti-diagonal layout are built on the device"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": FILL_TRAFFIC_BYTES if n_pairs == 512 and args.family_seed == 1 else None,

@@ -226,6 +226,20 @@ class Context:
         A = len(alphabet)
         return [leaf(self, h, s, alphabet, components, wildcard, A) for h, s in zip(out, seqs)]
 
+    def upload_packed(self, residues, offsets, alphabet, components=1):
+        """hist_profile_from_residues for a level of leaves whose residue strings sit back to back in ONE host buffer
+        (residues: uint8 array; sequence k = residues[offsets[k]:offsets[k+1]]).  No per-sequence Python object is made:
+        returns a HandleBatch.  What a compiled caller does with its own FASTA buffer."""
+        residues = np.ascontiguousarray(residues, np.uint8)
+        offsets = np.ascontiguousarray(offsets, np.int64)
+        n = len(offsets) - 1
+        ptrs = (residues.ctypes.data + offsets[:-1]).astype(np.uint64)
+        lens = np.diff(offsets).astype(np.int32)
+        out = (C.c_void_p * n)()
+        self.check(self.lib.hist_profile_from_residues(self.h, n, ptrs.ctypes.data_as(C.POINTER(C.c_char_p)), _p(lens, C.c_int32),
+                                                       alphabet.encode(), components, out))
+        return HandleBatch(self, out, n, "profile", keep=(residues, offsets))
+
     def upload_tokens(self, tokens, alph_size, components=1):
         """Same from token strings (int8 arrays, negative = wildcard): hist_profile_from_sequences."""
         toks = [np.ascontiguousarray(t, np.int8) for t in tokens]
@@ -241,6 +255,9 @@ class Context:
 
     def close_all(self, objs):
         """Destroy a level's pairs or profiles with one call (hist_pairs_destroy / hist_profiles_destroy)."""
+        if isinstance(objs, HandleBatch):
+            objs.close()
+            return
         objs = [o for o in objs if o.h]
         if not objs or not self.h:
             return
@@ -268,11 +285,36 @@ class Context:
 
     def fill_batch(self, pairs, backward=False):
         n = len(pairs)
-        arr = (C.c_void_p * n)(*[p.h for p in pairs])
+        arr = pairs.arr if isinstance(pairs, HandleBatch) else (C.c_void_p * n)(*[p.h for p in pairs])
         lp_end = np.empty(n)
         lp_start = np.empty(n) if backward else None
         self.check(self.lib.hist_fill_batch(self.h, arr, n, int(backward), _p(lp_end, C.c_double), _p(lp_start, C.c_double)))
         return lp_end, lp_start
+
+
+class HandleBatch:
+    """A level's profiles or pairs as ONE array of library handles (no Python object per item): what hist_profile_from_residues
+    / hist_pair_prepare_batch hand back, passed on as it is to hist_pair_prepare_batch / hist_fill_batch / hist_*_destroy."""
+
+    def __init__(self, ctx, arr, n, kind, keep=None):
+        self.ctx, self.arr, self.n, self.kind, self.keep = ctx, arr, n, kind, keep
+
+    def __len__(self):
+        return self.n
+
+    def handles(self):
+        return np.frombuffer(self.arr, np.uint64, self.n)
+
+    def close(self):
+        if self.arr is not None and self.ctx.h:
+            (self.ctx.lib.hist_pairs_destroy if self.kind == "pair" else self.ctx.lib.hist_profiles_destroy)(self.arr, self.n)
+        self.arr = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 class DeviceProfile:
@@ -359,6 +401,17 @@ class PrepareBatch:
         ctx.check(ctx.lib.hist_pair_prepare_batch(ctx.h, n, xp, yp, self.hp, self.ep, self.flags, out))
         made = Pair.made
         return [made(ctx, x, y, h) for x, y, h in zip(self.xs, self.ys, out)]
+
+    def run_batch(self, leaves):
+        """The same call for a HandleBatch of 2 n profiles, merge k joining profiles 2k and 2k + 1; returns a HandleBatch of pairs.
+        The profiles must outlive the pairs (the library also holds a reference)."""
+        n, ctx = self.n, self.ctx
+        h = leaves.handles()
+        xh, yh = np.ascontiguousarray(h[0::2]), np.ascontiguousarray(h[1::2])
+        out = (C.c_void_p * n)()
+        ctx.check(ctx.lib.hist_pair_prepare_batch(ctx.h, n, xh.ctypes.data_as(C.POINTER(C.c_void_p)), yh.ctypes.data_as(C.POINTER(C.c_void_p)),
+                                                  self.hp, self.ep, self.flags, out))
+        return HandleBatch(ctx, out, n, "pair", keep=leaves)
 
 
 class Pair:

@@ -334,3 +334,28 @@ def test_posteriors_without_the_within_cell_range_exemption(ctx, case):
         # (at t = 1e-8 the two orders of an adjacent insertion and deletion have the same weight to ~1e-8: the arg-max
         # between them is decided below FP32 resolution, north_star's "wherever the margin exceeds the tolerance")
         assert H.same(pair.trace_best(), ebest)
+
+
+def test_handle_batches_equal_the_object_api(ctx):
+    """upload_packed / PrepareBatch.run_batch / fill_batch on HandleBatch (no Python object per profile or pair) give the same
+    likelihoods as the per-object calls: the same C-ABI entry points underneath."""
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    from historian_b200 import capi
+    lg, guide = bench.make_family(3, n_leaves=16)
+    hmm, inputs = bench.cherry_inputs(lg, guide, 8)
+    seqs = bench.cherry_sequences(guide, 8)
+    leaves = ctx.upload_sequences(seqs, lg.alphabet, lg.components)
+    plan = capi.PrepareBatch(ctx, leaves[0::2], leaves[1::2], hmm, [e for _, _, e in inputs], backward=True)
+    want = ctx.fill_batch(plan.run(), backward=True)
+    packed = np.frombuffer(b"".join(seqs), np.uint8).copy()
+    off = np.concatenate([[0], np.cumsum([len(q) for q in seqs])]).astype(np.int64)
+    for _ in range(2):
+        lb = ctx.upload_packed(packed, off, lg.alphabet, lg.components)
+        pb = plan.run_batch(lb)
+        got = ctx.fill_batch(pb, backward=True)
+        assert len(lb) == 16 and len(pb) == 8
+        assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
+        pb.close()
+        lb.close()
