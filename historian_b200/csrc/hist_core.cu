@@ -753,13 +753,23 @@ extern "C" int hist_ctx_create(int device, hist_ctx** out) {
     return HIST_ERR_CUDA;
   }
   {
-    // keep freed arenas in the stream-ordered pool: every level of a reconstruction allocates a multi-GB
-    // arena, and the default threshold (0) would hand it back to the OS at each synchronisation
-    cudaMemPool_t pool;
-    if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
-      unsigned long long keep = ~0ull;
-      cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    // A private stream-ordered pool (the device's default pool, which a host application may share with torch or its own
+    // cudaMallocAsync calls, is left alone).  Freed arenas stay in it: every level of a reconstruction allocates a multi-GB
+    // arena, and the default release threshold (0) would hand it back to the driver at each synchronisation.
+    cudaMemPoolProps props = {};
+    props.allocType = cudaMemAllocationTypePinned;
+    props.handleTypes = cudaMemHandleTypeNone;
+    props.location.type = cudaMemLocationTypeDevice;
+    props.location.id = device;
+    e = cudaMemPoolCreate(&ctx->pool, &props);
+    if (e != cudaSuccess) {
+      set_err(nullptr, HIST_ERR_CUDA, "cudaMemPoolCreate: %s", cudaGetErrorString(e));
+      cudaStreamDestroy(ctx->stream);
+      delete ctx;
+      return HIST_ERR_CUDA;
     }
+    unsigned long long keep = ~0ull;
+    cudaMemPoolSetAttribute(ctx->pool, cudaMemPoolAttrReleaseThreshold, &keep);
   }
   cudaDeviceProp prop;
   cudaGetDeviceProperties(&prop, device);
@@ -785,6 +795,7 @@ extern "C" void hist_ctx_destroy(hist_ctx* ctx) {
   if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
   if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
   cudaStreamDestroy(ctx->stream);
+  cudaMemPoolDestroy(ctx->pool);
   delete ctx;
 }
 
@@ -866,7 +877,7 @@ extern "C" int hist_profile_upload(hist_ctx* ctx, const hist_profile_desc* d, hi
   const size_t bytes = (size_t)p->n * p->C * p->A * sizeof(double);
   p->d_lp_absorb = nullptr;
   p->arena = nullptr;
-  int rc = check_cuda(ctx, cudaMallocAsync((void**)&p->d_lp_absorb, bytes, ctx->stream), "cudaMallocAsync(lp_absorb)");
+  int rc = check_cuda(ctx, cudaMallocFromPoolAsync((void**)&p->d_lp_absorb, bytes, ctx->pool, ctx->stream), "cudaMallocAsync(lp_absorb)");
   if (!rc) rc = check_cuda(ctx, cudaMemcpyAsync(p->d_lp_absorb, d->lp_absorb, bytes, cudaMemcpyHostToDevice, ctx->stream), "H2D lp_absorb");
   ctx->h2d_bytes += (long long)bytes;
   // the descriptor is only borrowed for the duration of the call
@@ -929,7 +940,7 @@ static int leaf_profiles(hist_ctx* ctx, int32_t n, const int8_t* const* tokens, 
   const size_t lp_bytes = (size_t)state_off[n] * K * sizeof(double), off_bytes = (n + 1) * sizeof(long long);
   const size_t tok_off = (lp_bytes + 255) & ~(size_t)255, so_off = (tok_off + n_tok + 255) & ~(size_t)255, total = so_off + off_bytes;
   hb_arena* arena = new hb_arena{nullptr, total, 0};
-  int rc = check_cuda(ctx, cudaMallocAsync((void**)&arena->dev, total, ctx->stream), "cudaMallocAsync(leaf profiles)");
+  int rc = check_cuda(ctx, cudaMallocFromPoolAsync((void**)&arena->dev, total, ctx->pool, ctx->stream), "cudaMallocAsync(leaf profiles)");
   const size_t so_st = (n_tok + 255) & ~(size_t)255;
   if (!rc) rc = ensure_staging(ctx, so_st + off_bytes);
   if (!rc) rc = check_cuda(ctx, cudaEventSynchronize(ctx->ev_stage[0]), "wait for the staging buffer");   // its previous transfer
@@ -1217,7 +1228,7 @@ int ensure_images(hist_ctx* ctx, const hist_profile* const* xs, const hist_profi
   const size_t host_bytes = base[n_host], jobs_off = base[m], jobs_bytes = (size_t)n_chain * sizeof(ChainImgJob);
   const size_t total = jobs_off + (jobs_bytes + 255) / 256 * 256 + 256;
   hb_arena* arena = new hb_arena{nullptr, total, 0};
-  int rc = check_cuda(ctx, cudaMallocAsync((void**)&arena->dev, total, ctx->stream), "cudaMallocAsync(profile images)");
+  int rc = check_cuda(ctx, cudaMallocFromPoolAsync((void**)&arena->dev, total, ctx->pool, ctx->stream), "cudaMallocAsync(profile images)");
   if (!rc) rc = ensure_pinned(ctx, ctx->staging_img, ctx->staging_img_bytes, host_bytes + jobs_bytes + 256);
   if (!rc) rc = check_cuda(ctx, cudaEventSynchronize(ctx->ev_img), "wait for the image staging buffer");
   std::vector<int> nS(m, 1), nE(m, 1);
@@ -1729,7 +1740,7 @@ int prepare_enqueue(hist_ctx* ctx, int32_t n, const hist_profile* const* xs, con
     total += builds[k].dev.bytes;
   }
   hb_arena* arena = new hb_arena{nullptr, total, 0};
-  rc = check_cuda(ctx, cudaMallocAsync((void**)&arena->dev, total, ctx->stream), "cudaMallocAsync(pair arena)");
+  rc = check_cuda(ctx, cudaMallocFromPoolAsync((void**)&arena->dev, total, ctx->pool, ctx->stream), "cudaMallocAsync(pair arena)");
   if (!rc) rc = ensure_staging(ctx, scal_off, slot);
   if (!rc) rc = check_cuda(ctx, cudaEventSynchronize(ctx->ev_stage[slot]), "wait for the staging buffer");  // its previous transfer
   if (rc) {
@@ -1810,7 +1821,7 @@ int prepare_enqueue(hist_ctx* ctx, int32_t n, const hist_profile* const* xs, con
     b.pr->info.max_diag_width = L.max_width;
   }
   hb_arena* planes = new hb_arena{nullptr, std::max<size_t>(plane_total, 256), 0};
-  rc = check_cuda(ctx, cudaMallocAsync((void**)&planes->dev, planes->bytes, ctx->stream), "cudaMallocAsync(cell planes)");
+  rc = check_cuda(ctx, cudaMallocFromPoolAsync((void**)&planes->dev, planes->bytes, ctx->pool, ctx->stream), "cudaMallocAsync(cell planes)");
   if (rc) {
     delete planes;
     return fail_all(rc);

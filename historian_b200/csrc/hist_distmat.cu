@@ -237,7 +237,7 @@ extern "C" int hist_distance_matrix(hist_ctx* ctx, const hist_model_desc* model,
   memcpy(blob.data() + o_vi, model->evec_inv_re, AA * 8);
   memcpy(blob.data() + o_vi + AA * 8, model->evec_inv_im, AA * 8);
   char* d = nullptr;
-  HB_CUDA(ctx, cudaMallocAsync((void**)&d, total, ctx->stream));
+  HB_CUDA(ctx, cudaMallocFromPoolAsync((void**)&d, total, ctx->pool, ctx->stream));
   int rc = check_cuda(ctx, cudaMemcpyAsync(d, blob.data(), blob_bytes, cudaMemcpyHostToDevice, ctx->stream), "H2D distance-matrix inputs");
   ctx->h2d_bytes += (long long)blob_bytes;
   if (!rc) rc = check_cuda(ctx, cudaMemsetAsync(d + o_dist, 0, (size_t)n_rows * n_rows * 8, ctx->stream), "memset distances");

@@ -380,7 +380,7 @@ int eliminate_attempt(hist_ctx* ctx, const std::vector<ElimJob>& jobs, const std
     total = L[q].end;
   }
   char* buf = nullptr;
-  HB_CUDA(ctx, cudaMallocAsync((void**)&buf, total, ctx->stream));
+  HB_CUDA(ctx, cudaMallocFromPoolAsync((void**)&buf, total, ctx->pool, ctx->stream));
   char* ebuf = nullptr;
   char* obuf = nullptr;
   auto cleanup = [&]() {
@@ -433,7 +433,7 @@ int eliminate_attempt(hist_ctx* ctx, const std::vector<ElimJob>& jobs, const std
     eoff[q] = etot;
     etot += ((size_t)std::max(n_edges[q], 1) * 12 + 255) & ~(size_t)255;
   }
-  rc = check_cuda(ctx, cudaMallocAsync((void**)&ebuf, etot, ctx->stream), "cudaMallocAsync(edges)");
+  rc = check_cuda(ctx, cudaMallocFromPoolAsync((void**)&ebuf, etot, ctx->pool, ctx->stream), "cudaMallocAsync(edges)");
   if (rc) { ebuf = nullptr; cleanup(); return rc; }
   for (int q = 0; q < nj; ++q) {
     E[q].e_lp = (double*)(ebuf + eoff[q]);
@@ -473,7 +473,7 @@ int eliminate_attempt(hist_ctx* ctx, const std::vector<ElimJob>& jobs, const std
     max_work = std::max(max_work, std::max(jobs[which[q]].n, (int)nt + 1));
   }
   if (otot) {
-    rc = check_cuda(ctx, cudaMallocAsync((void**)&obuf, otot, ctx->stream), "cudaMallocAsync(results)");
+    rc = check_cuda(ctx, cudaMallocFromPoolAsync((void**)&obuf, otot, ctx->pool, ctx->stream), "cudaMallocAsync(results)");
     if (rc) { obuf = nullptr; cleanup(); return rc; }
     for (int q = 0; q < nj; ++q) {
       if (overflowed[q]) continue;
@@ -594,7 +594,7 @@ extern "C" int hist_profile_eliminate(hist_pair* pair, const hist_cell* cells, i
   const size_t b_rows = ((size_t)ns * sizeof(GatherRow) + 255) & ~(size_t)255, b_abs = ((size_t)ns * K * 8 + 255) & ~(size_t)255,
                b_cell = ((size_t)ns * sizeof(hist_cell) + 255) & ~(size_t)255;
   char* obuf = nullptr;
-  HB_CUDA(ctx, cudaMallocAsync((void**)&obuf, b_rows + b_abs + b_cell + (size_t)ns * 8, ctx->stream));
+  HB_CUDA(ctx, cudaMallocFromPoolAsync((void**)&obuf, b_rows + b_abs + b_cell + (size_t)ns * 8, ctx->pool, ctx->stream));
   std::vector<GatherRow> rows(ns);
   for (int k = 0; k < ns; ++k) rows[k] = {pair->d_dev, o.state_cell[k].xpos, o.state_cell[k].ypos, o.state_cell[k].state == HIST_EEE ? -1 : o.state_cell[k].state};
   double* d_abs = (double*)(obuf + b_rows);

@@ -177,7 +177,7 @@ extern "C" int hist_fb_counts(hist_pair* pair, const double* waits, double* inde
   const unsigned long long cap = (unsigned long long)std::max<int64_t>(pair->info.n_cells, 1);
   const size_t n_d = (size_t)(xn - 1) * 6 + 2 * (size_t)xn + 2 * (size_t)yn;
   double* d_buf = nullptr;
-  HB_CUDA(ctx, cudaMallocAsync((void**)&d_buf, n_d * sizeof(double) + cap * sizeof(FbCell) + 16, ctx->stream));
+  HB_CUDA(ctx, cudaMallocFromPoolAsync((void**)&d_buf, n_d * sizeof(double) + cap * sizeof(FbCell) + 16, ctx->pool, ctx->stream));
   double* d_part = d_buf;
   double* d_wx = d_part + (size_t)(xn - 1) * 6;
   double* d_wy = d_wx + 2 * (size_t)xn;

@@ -1803,7 +1803,7 @@ int ensure_backward_planes(hist_pair* pr) {
   const size_t n = pr->dev.n_stored;
   const size_t bytesA = (n * sizeof(float4) + 255) / 256 * 256;
   char* p = nullptr;
-  HB_CUDA(ctx, cudaMallocAsync((void**)&p, bytesA + n * sizeof(float2), ctx->stream));
+  HB_CUDA(ctx, cudaMallocFromPoolAsync((void**)&p, bytesA + n * sizeof(float2), ctx->pool, ctx->stream));
   pr->bwd_planes = p;
   pr->dev.bA = (float4*)p;
   pr->dev.bB = (float2*)(p + bytesA);
@@ -1835,7 +1835,7 @@ int launch_fill_uniform(hist_ctx* ctx, hist_pair* const* pairs, int n, int n_dir
   std::vector<PairDev*> h(n);
   for (int k = 0; k < n; ++k) h[k] = pairs[k]->d_dev;
   PairDev** dptrs = nullptr;
-  HB_CUDA(ctx, cudaMallocAsync((void**)&dptrs, n * sizeof(PairDev*), ctx->stream));
+  HB_CUDA(ctx, cudaMallocFromPoolAsync((void**)&dptrs, n * sizeof(PairDev*), ctx->pool, ctx->stream));
   HB_CUDA(ctx, cudaMemcpyAsync(dptrs, h.data(), n * sizeof(PairDev*), cudaMemcpyHostToDevice, ctx->stream));
   bool narrow = maxThreads <= HB_SMAX && rows >= 4;
   for (int k = 0; k < n && narrow; ++k) narrow = pairs[k]->dev.nS <= 32 && pairs[k]->dev.nE <= 32;   // edge-slot lists are staged in 32-entry arrays
@@ -1873,7 +1873,7 @@ int launch_fill_uniform(hist_ctx* ctx, hist_pair* const* pairs, int n, int n_dir
   if (narrow && !use_queue) {
     // streamed records: 64 B per stored cell and direction (+ 32 B per diagonal), built by one parallel pass
     for (int b = 0; b < n_cta; ++b) off[b + 1] = off[b] + (((size_t)pairs[b / n_dir]->dev.n_stored * 64 + (size_t)pairs[b / n_dir]->dev.n_diag * 32 + 255) & ~(size_t)255);
-    if (cudaMallocAsync((void**)&rec_buf, tab + off[n_cta] + 256, ctx->stream) != cudaSuccess) {
+    if (cudaMallocFromPoolAsync((void**)&rec_buf, tab + off[n_cta] + 256, ctx->pool, ctx->stream) != cudaSuccess) {
       cudaGetLastError();   // no room for the record buffer: the in-CTA producer/consumer kernel needs none
       rec_buf = nullptr;
     }
@@ -1922,7 +1922,7 @@ int launch_fill_chain(hist_ctx* ctx, hist_pair* const* pairs, int n, int n_dir, 
     if (h.empty()) continue;
     const int m = (int)h.size();
     PairDev** dptrs = nullptr;
-    HB_CUDA(ctx, cudaMallocAsync((void**)&dptrs, m * sizeof(PairDev*), ctx->stream));
+    HB_CUDA(ctx, cudaMallocFromPoolAsync((void**)&dptrs, m * sizeof(PairDev*), ctx->pool, ctx->stream));
     HB_CUDA(ctx, cudaMemcpyAsync(dptrs, h.data(), m * sizeof(PairDev*), cudaMemcpyHostToDevice, ctx->stream));
     static const bool one_warp = getenv("HIST_B200_CHAIN") && !strcmp(getenv("HIST_B200_CHAIN"), "1warp");   // A/B runs
     if (one_warp) {
@@ -2092,10 +2092,10 @@ extern "C" int hist_cells_fetch(hist_pair* pair, int which, double* lp, int32_t*
   unsigned long long* d_start = nullptr;
   double* d_lp = nullptr;
   int* d_pos = nullptr;
-  HB_CUDA(ctx, cudaMallocAsync((void**)&d_cnt, NI * sizeof(unsigned), ctx->stream));
-  HB_CUDA(ctx, cudaMallocAsync((void**)&d_start, NI * sizeof(unsigned long long), ctx->stream));
-  HB_CUDA(ctx, cudaMallocAsync((void**)&d_lp, std::max<size_t>(1, nc) * 5 * sizeof(double), ctx->stream));
-  HB_CUDA(ctx, cudaMallocAsync((void**)&d_pos, std::max<size_t>(1, nc) * 2 * sizeof(int), ctx->stream));
+  HB_CUDA(ctx, cudaMallocFromPoolAsync((void**)&d_cnt, NI * sizeof(unsigned), ctx->pool, ctx->stream));
+  HB_CUDA(ctx, cudaMallocFromPoolAsync((void**)&d_start, NI * sizeof(unsigned long long), ctx->pool, ctx->stream));
+  HB_CUDA(ctx, cudaMallocFromPoolAsync((void**)&d_lp, std::max<size_t>(1, nc) * 5 * sizeof(double), ctx->pool, ctx->stream));
+  HB_CUDA(ctx, cudaMallocFromPoolAsync((void**)&d_pos, std::max<size_t>(1, nc) * 2 * sizeof(int), ctx->pool, ctx->stream));
   cells_rank_kernel<<<NI, 128, 0, ctx->stream>>>(pair->d_dev, d_cnt);
   std::vector<unsigned> cnt(NI);
   HB_CUDA(ctx, cudaMemcpyAsync(cnt.data(), d_cnt, NI * sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));

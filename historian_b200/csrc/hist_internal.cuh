@@ -219,6 +219,7 @@ struct hb_arena {
 struct hist_ctx {
   int device;
   cudaStream_t stream;
+  cudaMemPool_t pool;   // the context's own stream-ordered pool: every device allocation of the library comes from it
   std::string err;
   long long launches;
   int sm_count;

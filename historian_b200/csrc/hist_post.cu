@@ -90,7 +90,7 @@ extern "C" int hist_posterior_cells(hist_pair* pair, double min_post_prob, hist_
   const unsigned long long cap = 5ull * (unsigned long long)std::max<int64_t>(pair->info.n_cells, 1);
   PostCell* buf = nullptr;
   unsigned long long* cnt = nullptr;
-  HB_CUDA(ctx, cudaMallocAsync((void**)&buf, cap * sizeof(PostCell) + 16, ctx->stream));
+  HB_CUDA(ctx, cudaMallocFromPoolAsync((void**)&buf, cap * sizeof(PostCell) + 16, ctx->pool, ctx->stream));
   cnt = (unsigned long long*)(buf + cap);
   HB_CUDA(ctx, cudaMemsetAsync(cnt, 0, sizeof(unsigned long long), ctx->stream));
   const double thr = std::log(min_post_prob);
@@ -194,7 +194,7 @@ extern "C" int hist_profile_sum_path_absorb(hist_profile* p, const double* log_c
                o_ins = o_cw + ((8 * (size_t)C + 255) & ~(size_t)255), o_abs = o_ins + ((8 * (size_t)C * A + 255) & ~(size_t)255),
                o_cum = o_abs + ((8 * (size_t)n + 255) & ~(size_t)255), total = o_cum + 8 * (size_t)n;
   char* d = nullptr;
-  HB_CUDA(ctx, cudaMallocAsync((void**)&d, total, ctx->stream));
+  HB_CUDA(ctx, cudaMallocFromPoolAsync((void**)&d, total, ctx->pool, ctx->stream));
   int rc = 0;
   auto up = [&](size_t off, const void* src, size_t bytes) {
     if (!rc) rc = hb::check_cuda(ctx, cudaMemcpyAsync(d + off, src, bytes, cudaMemcpyHostToDevice, ctx->stream), "H2D sum_path_absorb");

@@ -244,7 +244,7 @@ extern "C" int hist_quickalign_batch(hist_ctx* ctx, int32_t n, const hist_quicka
   }
   memcpy(blob.data() + o_sub, scores->submat, (size_t)A * A * sizeof(double));
   char* d = nullptr;
-  HB_CUDA(ctx, cudaMallocAsync((void**)&d, total, ctx->stream));
+  HB_CUDA(ctx, cudaMallocFromPoolAsync((void**)&d, total, ctx->pool, ctx->stream));
   int rc = check_cuda(ctx, cudaMemcpyAsync(d, blob.data(), blob_bytes, cudaMemcpyHostToDevice, ctx->stream), "H2D quickalign inputs");
   ctx->h2d_bytes += (long long)blob_bytes;
   if (!rc && smem > 48 * 1024) rc = check_cuda(ctx, cudaFuncSetAttribute(quickalign_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "quickalign shared memory");

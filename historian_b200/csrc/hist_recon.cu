@@ -649,8 +649,8 @@ extern "C" int hist_recon_level(hist_recon* R, int32_t n, const hist_merge_desc*
   const size_t rows_bytes = (size_t)total_rows * sizeof(GatherRow);
   hb_arena* arena = new hb_arena{nullptr, tab_bytes, 0};
   char* d_rows = nullptr;
-  rc = check_cuda(ctx, cudaMallocAsync((void**)&arena->dev, tab_bytes, ctx->stream), "cudaMallocAsync(parent profiles)");
-  if (!rc) rc = check_cuda(ctx, cudaMallocAsync((void**)&d_rows, rows_bytes, ctx->stream), "cudaMallocAsync(gather rows)");
+  rc = check_cuda(ctx, cudaMallocFromPoolAsync((void**)&arena->dev, tab_bytes, ctx->pool, ctx->stream), "cudaMallocAsync(parent profiles)");
+  if (!rc) rc = check_cuda(ctx, cudaMallocFromPoolAsync((void**)&d_rows, rows_bytes, ctx->pool, ctx->stream), "cudaMallocAsync(gather rows)");
   if (!rc) rc = ensure_staging_buf(ctx, rows_bytes, 0);
   if (!rc) {
     GatherRow* hr = (GatherRow*)ctx->staging;
@@ -836,7 +836,7 @@ extern "C" int hist_recon_import_node(hist_recon* R, int32_t node, const void* h
   cudaSetDevice(ctx->device);
   const size_t tb = (size_t)p->n * p->A * p->C * sizeof(double);
   p->arena = nullptr;
-  int rc = check_cuda(ctx, cudaMallocAsync((void**)&p->d_lp_absorb, tb, ctx->stream), "cudaMallocAsync(imported profile)");
+  int rc = check_cuda(ctx, cudaMallocFromPoolAsync((void**)&p->d_lp_absorb, tb, ctx->pool, ctx->stream), "cudaMallocAsync(imported profile)");
   if (!rc) rc = check_cuda(ctx, cudaMemcpyAsync(p->d_lp_absorb, dev_table, tb, cudaMemcpyDeviceToDevice, ctx->stream), "D2D imported table");
   if (!rc) rc = check_cuda(ctx, cudaStreamSynchronize(ctx->stream), "sync after import");   // the caller's buffer is only borrowed
   if (rc) {

@@ -301,7 +301,7 @@ int run_trace(hist_pair* pair, int mode, hist_cell origin, uint32_t* mt_state, i
   const size_t b_paths = (size_t)cap * sizeof(hist_cell), b_offs = (size_t)(n_traces + 1) * sizeof(long long);
   const size_t o_offs = (b_paths + 15) / 16 * 16, o_mt = o_offs + (b_offs + 15) / 16 * 16, o_status = o_mt + 625 * 4 + 12;
   const size_t o_args = o_status + 16;
-  HB_CUDA(ctx, cudaMallocAsync((void**)&buf, o_args + sizeof(TraceArgs), ctx->stream));
+  HB_CUDA(ctx, cudaMallocFromPoolAsync((void**)&buf, o_args + sizeof(TraceArgs), ctx->pool, ctx->stream));
   TraceArgs a;
   a.P = pair->d_dev;
   a.mode = mode;
@@ -376,7 +376,7 @@ int trace_best_batch(hist_ctx* ctx, hist_pair* const* pairs, int n, hist_cell** 
   const size_t b_paths = ((size_t)path_off[n] * sizeof(hist_cell) + 255) & ~(size_t)255;
   const size_t b_offs = ((size_t)n * 2 * sizeof(long long) + 255) & ~(size_t)255, b_stat = ((size_t)n * sizeof(int) + 255) & ~(size_t)255;
   char* buf = nullptr;
-  HB_CUDA(ctx, cudaMallocAsync((void**)&buf, b_paths + b_offs + b_stat + (size_t)n * sizeof(TraceArgs), ctx->stream));
+  HB_CUDA(ctx, cudaMallocFromPoolAsync((void**)&buf, b_paths + b_offs + b_stat + (size_t)n * sizeof(TraceArgs), ctx->pool, ctx->stream));
   std::vector<TraceArgs> args(n);
   for (int k = 0; k < n; ++k) {
     TraceArgs& a = args[k];
@@ -435,7 +435,7 @@ int trace_sample_snap(hist_pair* pair, const uint32_t* mt_state, int n_traces, s
   const size_t b_paths = ((size_t)cap * sizeof(hist_cell) + 255) & ~(size_t)255, b_offs = ((size_t)(n_traces + 1) * 8 + 255) & ~(size_t)255;
   const size_t b_mt = (625 * 4 + 255) & ~(size_t)255, b_snap = ((size_t)n_traces * 625 * 4 + 255) & ~(size_t)255;
   char* buf = nullptr;
-  HB_CUDA(ctx, cudaMallocAsync((void**)&buf, b_paths + b_offs + b_mt + b_snap + 256 + sizeof(TraceArgs), ctx->stream));
+  HB_CUDA(ctx, cudaMallocFromPoolAsync((void**)&buf, b_paths + b_offs + b_mt + b_snap + 256 + sizeof(TraceArgs), ctx->pool, ctx->stream));
   TraceArgs a;
   a.P = pair->d_dev;
   a.mode = 1;

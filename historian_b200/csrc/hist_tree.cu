@@ -202,7 +202,7 @@ extern "C" int hist_build_tree(hist_ctx* ctx, int32_t n, const double* dist, int
   HB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, TR_THREADS, smem));
   if (per_sm < 1) return set_err(ctx, HIST_ERR_CUDA, "hist_build_tree: the kernel does not fit one CTA per SM");
   char* d = nullptr;
-  HB_CUDA(ctx, cudaMallocAsync((void**)&d, total, ctx->stream));
+  HB_CUDA(ctx, cudaMallocFromPoolAsync((void**)&d, total, ctx->pool, ctx->stream));
   int rc = check_cuda(ctx, cudaMemsetAsync(d, 0, o_aux, ctx->stream), "memset tree distances");
   if (!rc) rc = check_cuda(ctx, cudaMemcpy2DAsync(d + o_dist, (size_t)M * 8, dist, (size_t)n * 8, (size_t)n * 8, n, cudaMemcpyHostToDevice, ctx->stream), "H2D distance matrix");
   ctx->h2d_bytes += (long long)n * n * 8;
