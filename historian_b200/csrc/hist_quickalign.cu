@@ -59,7 +59,7 @@ __device__ __forceinline__ double qa_end_gap(const QaScores& S, unsigned i, unsi
 }
 
 // grid = pairs; dynamic shared memory: 3 * max_nd doubles + blockDim (double + 2 int) for the end-cell reduction
-__global__ void __launch_bounds__(1024) quickalign_kernel(const QaPair* __restrict__ pairs, const char* __restrict__ blob, const int* __restrict__ diags,
+__global__ void __launch_bounds__(1024, 2) quickalign_kernel(const QaPair* __restrict__ pairs, const char* __restrict__ blob, const int* __restrict__ diags,
                                                           const double* __restrict__ submat, QaScores S, unsigned char* __restrict__ tb_all,
                                                           unsigned char* __restrict__ path_all, double* __restrict__ result,
                                                           int* __restrict__ ends, int* __restrict__ path_len, int max_nd) {
