@@ -571,6 +571,24 @@ def guide_leg(ctx, args, lg, guide_rows):
         assert want == res[k] and tuple(ends[k]) == end and np.array_equal(paths[k], wpath), "device alignment differs from the CPU oracle"
     cpu_s = time.perf_counter() - c0
     cpu_cells = sum(G.envelope_cells(pairs[k][2], len(pairs[k][0]), len(pairs[k][1])) for k in sample)
+    ref_base = None
+    ref_bin = os.path.join(ROOT, "oracle", "_ref", "bin", "ref_dump_quickalign")
+    if os.path.exists(ref_bin) and args.guide_envelope == "full":
+        # the unmodified reference's QuickAlignMatrix constructor + alignPath() on all pairs of a few of the same sequences
+        with tempfile.TemporaryDirectory() as tmp:
+            fa = os.path.join(tmp, "s.fa")
+            with open(fa, "w") as f:
+                for k in range(args.guide_ref_seqs):
+                    f.write(">s%d\n%s\n" % (k, "".join(lg.alphabet[t] if t >= 0 else "*" for t in toks[k])))
+            out = subprocess.run([ref_bin, os.path.join(tmp, "d.bin"), "lg", fa, "1", "full"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True).stdout
+        try:
+            f_ = out.split()
+            rc_, rf_, rt_ = float(f_[f_.index("cells") + 1]), float(f_[f_.index("fill_s") + 1]), float(f_[f_.index("trace_s") + 1])
+            ref_base = {"value": rc_ / (rf_ + rt_) / 1e9, "unit": "Gcells/s", "cores": 1, "kind": "reference",
+                        "sample": "the %d pairs among %d of the family's sequences, unmodified reference QuickAlignMatrix constructor + alignPath() via "
+                                  "oracle/_ref/bin/ref_dump_quickalign, %.1f s inside them" % (int(f_[f_.index("pairs") + 1]), args.guide_ref_seqs, rf_ + rt_)}
+        except Exception:
+            ref_base = None
     return {"metric": "guide-alignment Viterbi cells/s", "value": cells / wall / 1e9, "unit": "Gcells/s", "higher_is_better": True, "ms": 1e3 * wall,
             "dtype": "f64 (bit-exact with the reference)", "pairs": len(pairs), "cells": int(cells),
             "diagonals_per_pair": [int(min(len(p[2]) for p in pairs)), int(max(len(p[2]) for p in pairs))],
@@ -579,8 +597,11 @@ def guide_leg(ctx, args, lg, guide_rows):
                 else "k-mer seeded envelopes (6-mers, >= 14 matches, band 64)")},
             "e2e": {"value": cells / wall / 1e9, "unit": "Gcells/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(sum(len(p) for p in paths) + 16 * len(pairs))},
             "gpu_launches": int((ctx.launch_count - launches0) // 3),
-            "cpu_baseline": {"value": cpu_cells / cpu_s / 1e9, "unit": "Gcells/s", "cores": 1, "kind": "port",
-                             "sample": "%d of the pairs through oracle/oracle_quickalign.cpp (dense cell array, 1 thread), %.1f s; scores, end cells and paths equal the device's" % (len(sample), cpu_s)}}
+            "cpu_baseline": ref_base if ref_base is not None else
+            {"value": cpu_cells / cpu_s / 1e9, "unit": "Gcells/s", "cores": 1, "kind": "port",
+             "sample": "%d of the pairs through oracle/oracle_quickalign.cpp (dense cell array, 1 thread), %.1f s" % (len(sample), cpu_s)},
+            "checked": "scores, end cells and paths of %d pairs equal the CPU port's (oracle/oracle_quickalign.cpp, %.3f Gcells/s on one core)" % (
+                len(sample), cpu_cells / cpu_s / 1e9)}
 
 
 # ------------------------------------------------------------------ distance-matrix leg
@@ -627,14 +648,35 @@ def distmat_leg(ctx, args, lg, guide_rows):
             "cpu_baseline": {"value": tree_cpu_s, "unit": "s", "cores": 1, "kind": "port",
                              "sample": "UPGMA on the first %d rows through oracle/oracle_tree.cpp (O(n^3): the full matrix costs (%d/%d)^3 times that), %.2f s; "
                                        "children and branch lengths bit-identical to the device's" % (sub, n, sub, tree_cpu_s)}}
+    ref_base = None
+    ref_bin = os.path.join(ROOT, "oracle", "_ref", "bin", "ref_dump_distmat")
+    if os.path.exists(ref_bin):
+        # the unmodified reference's RateModel::distanceMatrix and tree builders on the first rows of the same alignment
+        nref = min(n, args.distmat_ref_rows)
+        with tempfile.TemporaryDirectory() as tmp:
+            fa = os.path.join(tmp, "g.fa")
+            with open(fa, "w") as f:
+                for k in range(nref):
+                    f.write(">s%d\n%s\n" % (k, bytes(rows[k]).decode()))
+            out = subprocess.run([ref_bin, os.path.join(tmp, "d.bin"), "lg", fa, "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True).stdout
+        try:
+            f_ = out.split()
+            ds_, us_ = float(f_[f_.index("dist_s") + 1]), float(f_[f_.index("upgma_s") + 1])
+            ref_base = {"value": nref * (nref - 1) / 2 / ds_, "unit": "pairs/s", "cores": 1, "kind": "reference",
+                        "sample": "the %d pairs among the first %d rows, unmodified reference RateModel::distanceMatrix via oracle/_ref/bin/ref_dump_distmat, "
+                                  "%.1f s inside it (its UPGMA of those %d rows: %.4f s)" % (nref * (nref - 1) // 2, nref, ds_, nref, us_)}
+        except Exception:
+            ref_base = None
     return {"metric": "distance-matrix pairs/s", "value": pairs / wall, "guide_tree": tree, "unit": "pairs/s", "higher_is_better": True, "s": wall, "dtype": "f64",
             "config": {"workload": "lg_1024x1000_seed%d guide alignment: %d rows x %d columns, %d ML distances (100 golden-section iterations at most)" % (
                 args.family_seed, n, rows.shape[1], pairs)},
             "e2e": {"value": pairs / wall, "unit": "pairs/s", "h2d_bytes_per_step": int(rows.size), "d2h_bytes_per_step": int(8 * n * n)},
             "gpu_launches": 1,
-            "cpu_baseline": {"value": len(iu[0]) / cpu_s, "unit": "pairs/s", "cores": 1, "kind": "port",
-                             "sample": "the %d pairs among %d evenly spaced rows through oracle/oracle_distmat.cpp (eigen-decomposed exponentials, 1 thread), %.1f s; "
-                                       "device distances equal to 1e-6 on >= 90 %% of them, within the search's 1 %% on all" % (len(iu[0]), len(pick), cpu_s)}}
+            "cpu_baseline": ref_base if ref_base is not None else
+            {"value": len(iu[0]) / cpu_s, "unit": "pairs/s", "cores": 1, "kind": "port",
+             "sample": "the %d pairs among %d evenly spaced rows through oracle/oracle_distmat.cpp (eigen-decomposed exponentials, 1 thread), %.1f s" % (len(iu[0]), len(pick), cpu_s)},
+            "checked": "device distances of %d pairs equal the CPU port's (oracle/oracle_distmat.cpp, %.0f pairs/s on one core) to 1e-6 on >= 90 %% of them, "
+                       "within the search's 1 %% on all" % (len(iu[0]), len(iu[0]) / cpu_s)}
 
 
 # ------------------------------------------------------------------ GPU arm
@@ -842,6 +884,8 @@ def main():
     ap.add_argument("--distmat-rows", type=int, default=1024, help="rows of the guide alignment in the distance-matrix leg")
     ap.add_argument("--tree-cpu-rows", type=int, default=384, help="rows of the UPGMA cpu_baseline sample")
     ap.add_argument("--distmat-cpu-rows", type=int, default=16, help="rows in that leg's cpu_baseline sample")
+    ap.add_argument("--guide-ref-seqs", type=int, default=24, help="sequences whose all-pairs alignments time the reference in the guide-alignment leg")
+    ap.add_argument("--distmat-ref-rows", type=int, default=96, help="rows of the reference's distance-matrix timing sample")
     ap.add_argument("--guide-cpu-pairs", type=int, default=24, help="pairs in that leg's cpu_baseline sample")
     ap.add_argument("--codon-constructor-only", action="store_true", help=argparse.SUPPRESS)
     ap.add_argument("--recon-reps", type=int, default=3, help="timed repetitions of the whole-tree reconstruction (best is reported)")

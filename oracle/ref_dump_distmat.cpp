@@ -4,6 +4,7 @@
 // Compiled against the UNMODIFIED reference (oracle/Makefile).
 //
 //   ref_dump_distmat <out.bin> <preset[:bins:shape]> <gapped.fa> <maxIterations>
+#include <chrono>
 #include <cstdint>
 #include <cstdio>
 #include <iostream>
@@ -53,7 +54,9 @@ int main(int argc, char** argv) {
   const vguard<FastSeq> gapped = readFastSeqs(argv[3]);
   const int maxIter = atoi(argv[4]);
   const size_t n = gapped.size();
+  const auto t0 = chrono::steady_clock::now();
   const auto dist = model.distanceMatrix(gapped, maxIter);
+  const double distSeconds = chrono::duration<double>(chrono::steady_clock::now() - t0).count();
   vector<double> flat;
   for (const auto& row : dist) flat.insert(flat.end(), row.begin(), row.end());
   putRaw("dist", 'd', {(uint64_t)n, (uint64_t)n}, flat.data(), flat.size() * 8);
@@ -68,8 +71,14 @@ int main(int argc, char** argv) {
   putS("alphabet", model.alphabet);
   {
     Tree nj, up;
+    const auto t1 = chrono::steady_clock::now();
     nj.buildByNeighborJoining(gapped, dist);
+    const auto t2 = chrono::steady_clock::now();
     up.buildByUPGMA(gapped, dist);
+    const auto t3 = chrono::steady_clock::now();
+    const double timing[3] = {distSeconds, chrono::duration<double>(t2 - t1).count(), chrono::duration<double>(t3 - t2).count()};
+    putRaw("timing", 'd', {3}, timing, 24);
+    printf("rows %zu dist_s %.6f nj_s %.6f upgma_s %.6f\n", n, timing[0], timing[1], timing[2]);
     putS("nj", nj.toString());
     putS("upgma", up.toString());
   }

@@ -6,6 +6,7 @@
 // tools/make_golden_quickalign.py turns the dump into tests/golden/quickalign_*.npz.
 //
 //   ref_dump_quickalign <out.bin> <preset> <seqs.fa> <time> full | sparse:<band>:<kmerLen>:<kmerThreshold>
+#include <chrono>
 #include <cstdint>
 #include <cstdio>
 #include <iostream>
@@ -58,6 +59,7 @@ int main(int argc, char** argv) {
   const int A = model.alphabetSize();
   bool scoresDone = false;
   int k = 0;
+  double fillSeconds = 0, traceSeconds = 0, cells = 0;   // time inside the reference's own constructor / alignPath()
   for (size_t a = 0; a < seqs.size(); ++a)
     for (size_t b = a + 1; b < seqs.size(); ++b, ++k) {
       DiagonalEnvelope env(seqs[a], seqs[b]);
@@ -66,7 +68,13 @@ int main(int argc, char** argv) {
         env.initSparse(yKmerIndex, band, kmerThreshold, 3 * sizeof(double), 0);
       } else
         env.initFull();
+      const auto t0 = chrono::steady_clock::now();
       QuickAlignMatrix mx(env, model, time);
+      fillSeconds += chrono::duration<double>(chrono::steady_clock::now() - t0).count();
+      for (auto d : env.diagonals) {
+        const long lo = max(1L, 1L - d), hi = min((long)env.yLen, (long)env.xLen - d);
+        if (hi >= lo) cells += (double)(hi - lo + 1);
+      }
       if (!scoresDone) {
         vector<double> sub;
         for (int i = 0; i < A; ++i)
@@ -83,7 +91,9 @@ int main(int argc, char** argv) {
       putD(p + "result", {mx.result});
       putI(p + "end", {(int32_t)mx.xEnd, (int32_t)mx.yEnd});
       if (mx.resultIsFinite()) {
+        const auto t1 = chrono::steady_clock::now();
         const AlignPath path = mx.alignPath();
+        traceSeconds += chrono::duration<double>(chrono::steady_clock::now() - t1).count();
         const vector<bool>& r0 = path.at(0);
         const vector<bool>& r1 = path.at(1);
         vector<uint8_t> ops(r0.size());
@@ -92,6 +102,8 @@ int main(int argc, char** argv) {
       }
     }
   putI("n_pairs", {k});
+  putD("timing", {fillSeconds, traceSeconds, cells});
+  printf("pairs %d cells %.0f fill_s %.6f trace_s %.6f\n", k, cells, fillSeconds, traceSeconds);
   fclose(gOut);
   return 0;
 }

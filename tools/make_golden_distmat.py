@@ -40,6 +40,7 @@ def main():
             binf = os.path.join(tmp, "d.bin")
             subprocess.run([os.path.join(BIN, "ref_dump_distmat"), binf, spec, fa, str(iters)], check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
             d = D.read_dump(binf)
+            d.pop("timing", None)   # wall-clock of this run: not part of the fixture
         d["preset"] = spec
         d["max_iterations"] = np.array([iters], np.int32)
         d = {k: (np.frombuffer(v.encode(), np.uint8) if isinstance(v, str) else v) for k, v in d.items()}
