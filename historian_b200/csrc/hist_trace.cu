@@ -180,13 +180,15 @@ __global__ void __launch_bounds__(32) trace_kernel(const TraceArgs* __restrict__
         const SrcEnum e = source_enum(P, cur, nullptr);
         n = e.n;
         if (n > a.cand_cap) { if (lane == 0) s_flag = 3; break; }
-        const double emit = dp_emit_warp(P, cur, lane);
+        // The reference adds lpCellEmitOrAbsorb(cur) to every candidate (forward.cpp:225-255).  It is the same term for all of
+        // them: it cannot move the maximum and it cancels in exp(lp - max), so neither the best nor the sampled source depends
+        // on it -- and it was a quarter of the step (an A-term log-sum-exp in FP64 behind two emission-row loads).  Left out.
         for (int c = lane; c < n; c += 32) {
           DCell s;
           double lp;
           source_get(P, w, cur, e, c, s, lp);
           cand[c] = s;
-          clp[c] = lp + emit + dp_cell(P, false, s.x, s.y, s.s);
+          clp[c] = lp + dp_cell(P, false, s.x, s.y, s.s);
         }
       }
       __syncwarp();
