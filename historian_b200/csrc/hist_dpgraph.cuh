@@ -42,6 +42,8 @@ __device__ __forceinline__ int dp_cell_slot(const PairDev& P, const DiagInfo& di
 }
 
 // DPMatrix::cell (forward.h:75-81): natural log of state s of cell (i,j); -inf for absent cells.
+// FAST: ln of the stored float by cell_log_fast (2e-10): for the traceback, which only compares and samples these values.
+template <bool FAST = false>
 __device__ __forceinline__ double dp_cell(const PairDev& P, bool backward, int i, int j, int s) {
   if (i < 0 || j < 0 || i > P.x.n - 2 || j > P.y.n - 2 || s < 0 || s > 4) return -INFINITY;
   const DiagInfo di = P.dinfo[i + j];
@@ -52,7 +54,7 @@ __device__ __forceinline__ double dp_cell(const PairDev& P, bool backward, int i
   const int E = __float_as_int(b.y);
   if (E <= HB_EXP_ZERO / 2) return -INFINITY;
   const float v = s == 0 ? a.x : s == 1 ? a.y : s == 2 ? a.z : s == 3 ? a.w : b.x;
-  return cell_log(v, E);
+  return FAST ? cell_log_fast(v, E) : cell_log(v, E);
 }
 
 __device__ __forceinline__ bool dp_in_envelope(const PairDev& P, int i, int j) {

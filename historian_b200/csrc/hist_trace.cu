@@ -173,7 +173,7 @@ __global__ void __launch_bounds__(32) trace_kernel(const TraceArgs* __restrict__
         for (int c = lane; c < n; c += 32) {
           const DCell d = cand[c];
           double lp = clp[c] + dp_emit(P, d);
-          if (d.s != HIST_EEE) lp += dp_cell(P, true, d.x, d.y, d.s);
+          if (d.s != HIST_EEE) lp += dp_cell<true>(P, true, d.x, d.y, d.s);
           clp[c] = lp;
         }
       } else {
@@ -188,7 +188,7 @@ __global__ void __launch_bounds__(32) trace_kernel(const TraceArgs* __restrict__
           double lp;
           source_get(P, w, cur, e, c, s, lp);
           cand[c] = s;
-          clp[c] = lp + dp_cell(P, false, s.x, s.y, s.s);
+          clp[c] = lp + dp_cell<true>(P, false, s.x, s.y, s.s);
         }
       }
       __syncwarp();
