@@ -652,11 +652,13 @@ class Recon:
         """merges: list of (node, left, right, closest_left, closest_right, closest); hmm_descs: one PairHmmDesc per merge
         (kept alive by the caller).  Returns lp_end per merge."""
         n = len(merges)
-        arr = (D.MergeDesc * n)()
-        for k, (m, hd) in enumerate(zip(merges, hmm_descs)):
-            a = arr[k]
-            a.node, a.left, a.right, a.closest_left, a.closest_right, a.closest = (int(v) for v in m)
-            a.hmm = C.pointer(hd)
+        # hist_merge_desc[n] filled column-wise (a level holds hundreds of merges): six int32 and the PairHMM pointer
+        rec = np.zeros(n, np.dtype([("i", np.int32, 6), ("hmm", np.uint64)], align=True))
+        assert rec.dtype.itemsize == C.sizeof(D.MergeDesc)
+        rec["i"] = np.asarray(merges, np.int32).reshape(n, 6)
+        addr = {}
+        rec["hmm"] = [addr.setdefault(id(hd), C.addressof(hd)) for hd in hmm_descs]
+        arr = rec.ctypes.data_as(C.POINTER(D.MergeDesc))
         prm = D.ReconParams()
         prm.band, prm.strategy, prm.profile_samples, prm.max_profile_states = int(band), int(strategy), int(profile_samples), int(max_profile_states)
         prm.min_post_prob = 0.0
@@ -673,10 +675,10 @@ class Recon:
         rc = self.ctx.lib.hist_recon_alignment(self.h, C.byref(nc), None, 0)
         if rc not in (0, -5):
             self.ctx.check(rc)
-        bits = np.zeros((self.n_nodes, max(nc.value, 0)), np.uint8)
+        bits = np.empty((self.n_nodes, max(nc.value, 0)), np.uint8)
         if bits.size:
             self.ctx.check(self.ctx.lib.hist_recon_alignment(self.h, C.byref(nc), _p(bits, C.c_uint8), bits.size))
-        return bits.astype(bool)
+        return bits.view(np.bool_)   # the library writes 0 / 1
 
     # ---- exchange between ranks (one hist_recon per GPU)
     def export_sizes(self, node):
