@@ -100,7 +100,7 @@ struct hist_recon {
   int root = -1;
   std::vector<int> root_items;      // items of the root's best alignment path (tags as seen from the root's store)
   int aln_cols = -1;
-  std::vector<uint8_t> aln;         // [n_nodes][aln_cols]
+  std::vector<std::pair<const PathStore*, int>> aln_roots;   // [aln_cols] the column trees of the root's alignment path
   double stage_ms[HIST_RECON_NSTAGES] = {0};
 };
 
@@ -302,36 +302,23 @@ int trace_items(const hist_pair* pair, const NodeRec* xr, const NodeRec* yr, int
   return HIST_OK;
 }
 
-// Expands the root's alignment path into a dense [n_nodes][cols] 0/1 matrix.
-void expand_alignment(hist_recon* R) {
+// The columns of the root's alignment path, in order: (store, column node) roots of the trees whose rows a column holds.
+// Sequential (the item lists nest), but short: one entry per column.
+void collect_columns(hist_recon* R) {
   struct Frame { const PathStore* st; int first, count, pos; };   // walking items [first, first+count) of store st
-  std::vector<std::vector<int>> columns;   // rows of each column
   const PathStore* root = R->node[R->root].store;
   std::vector<Frame> stack;
-  std::vector<std::pair<const PathStore*, int>> cstack;
+  std::vector<std::pair<const PathStore*, int>>& cols = R->aln_roots;
+  cols.clear();
   // the root's items live outside its store: treat them as a virtual sequence
   const std::vector<int>& top = R->root_items;
   auto child_store = [&](const PathStore* st, int which) -> const PathStore* {
     const int cn = st->child_node[which];
     return cn >= 0 ? R->node[cn].store : nullptr;
   };
-  auto emit_col = [&](const PathStore* st, int id) {
-    std::vector<int> rows;
-    cstack.clear();
-    cstack.push_back({st, id});
-    while (!cstack.empty()) {
-      const auto cur = cstack.back();
-      cstack.pop_back();
-      const ColNode& c = cur.first->cols[cur.second];
-      if (c.row >= 0) rows.push_back(c.row);
-      if (c.a >= 0) cstack.push_back({child_store(cur.first, 0), c.a});
-      if (c.b >= 0) cstack.push_back({child_store(cur.first, 1), c.b});
-    }
-    columns.push_back(std::move(rows));
-  };
   for (size_t q = 0; q < top.size(); ++q) {
     const int it = top[q], id = it >> 2, tag = it & 3;
-    if (tag == IT_COL) { emit_col(root, id); continue; }
+    if (tag == IT_COL) { cols.push_back({root, id}); continue; }
     const PathStore* cs = child_store(root, tag == IT_SEQ0 ? 0 : 1);
     stack.clear();
     stack.push_back({cs, cs->seqs[id].first, cs->seqs[id].count, 0});
@@ -340,18 +327,47 @@ void expand_alignment(hist_recon* R) {
       if (f.pos == f.count) { stack.pop_back(); continue; }
       const int it2 = f.st->items[f.first + f.pos++];
       const int id2 = it2 >> 2, tag2 = it2 & 3;
-      if (tag2 == IT_COL) emit_col(f.st, id2);
+      if (tag2 == IT_COL) cols.push_back({f.st, id2});
       else {
         const PathStore* c2 = child_store(f.st, tag2 == IT_SEQ0 ? 0 : 1);
         stack.push_back({c2, c2->seqs[id2].first, c2->seqs[id2].count, 0});
       }
     }
   }
-  R->aln_cols = (int)columns.size();
-  R->aln.assign((size_t)R->n_nodes * std::max(1, R->aln_cols), 0);
-  for (size_t c = 0; c < columns.size(); ++c)
-    for (int row : columns[c])
-      if (row >= 0 && row < R->n_nodes) R->aln[(size_t)row * R->aln_cols + c] = 1;
+  R->aln_cols = (int)cols.size();
+}
+
+// Expands the columns into the caller's dense [n_nodes][cols] 0/1 matrix: rows are cleared, then blocks of 64 columns (a
+// cache line of every row) walk their column trees, both over the host threads.
+void expand_alignment(const hist_recon* R, uint8_t* bits) {
+  const int n_cols = R->aln_cols, n_nodes = R->n_nodes;
+  if (n_cols <= 0) return;
+  const int row_grain = std::max(1, (int)((1 << 20) / n_cols));
+  host_parallel_for((n_nodes + row_grain - 1) / row_grain, 1, [&](int b) {
+    const int r0 = b * row_grain, r1 = std::min(n_nodes, r0 + row_grain);
+    memset(bits + (size_t)r0 * n_cols, 0, (size_t)(r1 - r0) * n_cols);
+  });
+  const int blk = 64;
+  host_parallel_for((n_cols + blk - 1) / blk, 1, [&](int b) {
+    std::vector<std::pair<const PathStore*, int>> cstack;
+    const int c1 = std::min(n_cols, (b + 1) * blk);
+    for (int c = b * blk; c < c1; ++c) {
+      cstack.clear();
+      cstack.push_back(R->aln_roots[c]);
+      while (!cstack.empty()) {
+        const auto cur = cstack.back();
+        cstack.pop_back();
+        const ColNode& cn = cur.first->cols[cur.second];
+        if (cn.row >= 0 && cn.row < n_nodes) bits[(size_t)cn.row * n_cols + c] = 1;
+        for (int w = 0; w < 2; ++w) {
+          const int id = w ? cn.b : cn.a;
+          if (id < 0) continue;
+          const int ch = cur.first->child_node[w];
+          cstack.push_back({R->node[ch].store, id});
+        }
+      }
+    }
+  });
 }
 
 struct EnvHost {
@@ -708,11 +724,11 @@ extern "C" int hist_recon_level(hist_recon* R, int32_t n, const hist_merge_desc*
 extern "C" int hist_recon_alignment(hist_recon* R, int32_t* n_cols, uint8_t* bits, int64_t capacity) {
   if (!R || !n_cols) return HIST_ERR_ARG;
   if (R->root < 0) return set_err(R->ctx, HIST_ERR_STATE, "hist_recon_alignment: the root has not been reconstructed");
-  if (R->aln_cols < 0) expand_alignment(R);
+  if (R->aln_cols < 0) collect_columns(R);
   *n_cols = R->aln_cols;
   const int64_t need = (int64_t)R->n_nodes * R->aln_cols;
   if (!bits || capacity < need) return set_err(R->ctx, HIST_ERR_CAPACITY, "hist_recon_alignment: need room for %d x %d bytes", R->n_nodes, R->aln_cols);
-  if (need) memcpy(bits, R->aln.data(), (size_t)need);
+  if (need) expand_alignment(R, bits);
   return HIST_OK;
 }
 
