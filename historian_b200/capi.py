@@ -44,6 +44,10 @@ def load():
                                           D.c_int32_p, D.c_int32_p, D.c_uint8_p, D.c_int64_p, D.c_int32_p]
     lib.hist_distance_matrix.argtypes = [vp, C.POINTER(D.ModelDesc), C.c_double, C.c_int32, C.c_int32, C.c_char_p, C.c_int32, D.c_double_p]
     lib.hist_build_tree.argtypes = [vp, C.c_int32, D.c_double_p, C.c_int32, C.c_double, D.c_int32_p, D.c_double_p]
+    lib.hist_guide_align.argtypes = [vp, C.c_int32, C.POINTER(C.c_int8), D.c_int64_p, C.POINTER(D.QuickAlignScores), C.POINTER(D.GuideParams),
+                                     D.c_int32_p, D.c_int32_p, D.c_int32_p, D.c_int32_p, D.c_double_p, C.c_int64, D.c_int32_p]
+    lib.hist_align_path_merge.argtypes = [vp, C.c_int32, D.c_int32_p, D.c_int32_p, D.c_int32_p, C.POINTER(C.c_uint8), C.c_int32, D.c_int64_p,
+                                          D.c_int32_p, D.c_int32_p]
     lib.hist_ctx_h2d_bytes.argtypes = [vp]
     lib.hist_ctx_h2d_bytes.restype = C.c_int64
     lib.hist_ctx_set_timing.argtypes = [vp, C.c_int]
@@ -174,6 +178,33 @@ class Context:
         paths = [buf[off[k]:off[k] + plen[k]].copy() for k in range(n)] if want_paths else None
         return result, np.stack([xe, ye], 1), paths
 
+    def guide_align(self, seq_tokens, submat, scores, all_pairs=False, seed=5489, sparse=True, kmer_len=6, kmer_threshold=-1, band_size=64,
+                    cell_size=40, max_size=None):
+        """AlignGraph::mstAlign (span.cpp:35-158) of unaligned sequences: hist_guide_align.  seq_tokens: int8 token arrays
+        (< 0: not in the alphabet); submat / scores as for quickalign; the rest is hist_guide_params (defaults: the reference's
+        random spanning graph, generator seed and DiagEnvParams; max_size None = this machine's memory, DiagEnvParams::effectiveMaxSize,
+        diagenv.cpp:79-89).  Returns (bits uint8 [n][cols], info) with info = {"edges": [E][2], "edge_lp": [E], "mst": [n-1]}."""
+        toks = [np.ascontiguousarray(t, np.int8) for t in seq_tokens]
+        n = len(toks)
+        off = np.zeros(n + 1, np.int64)
+        off[1:] = np.cumsum([len(t) for t in toks])
+        flat = np.ascontiguousarray(np.concatenate(toks), np.int8)
+        sub = np.ascontiguousarray(submat, np.float64)
+        sc = D.QuickAlignScores(int(sub.shape[0]), _p(sub, C.c_double), *[float(v) for v in scores])
+        if max_size is None:
+            max_size = os.sysconf("SC_PAGE_SIZE") * os.sysconf("SC_PHYS_PAGES")
+        gp = D.GuideParams(int(bool(all_pairs)), int(seed), int(bool(sparse)), int(kmer_len), int(kmer_threshold), int(band_size), int(cell_size), 0, int(max_size))
+        cap = n * (n - 1) // 2
+        rcol, ncols, nedges = np.zeros(int(off[n]), np.int32), np.zeros(1, np.int32), np.zeros(1, np.int32)
+        erows, elp, mst = np.zeros((max(1, cap), 2), np.int32), np.zeros(max(1, cap)), np.zeros(max(1, n - 1), np.int32)
+        self.check(self.lib.hist_guide_align(self.h, n, _p(flat, C.c_int8), _p(off, C.c_int64), C.byref(sc), C.byref(gp), _p(rcol, C.c_int32),
+                                             _p(ncols, C.c_int32), _p(nedges, C.c_int32), _p(erows, C.c_int32), _p(elp, C.c_double), cap, _p(mst, C.c_int32)))
+        bits = np.zeros((n, int(ncols[0])), np.uint8)
+        for s in range(n):
+            bits[s, rcol[off[s]:off[s + 1]]] = 1
+        e = int(nedges[0])
+        return bits, {"edges": erows[:e].copy(), "edge_lp": elp[:e].copy(), "mst": mst[:max(0, n - 1)].copy()}
+
     def distance_matrix(self, sp_model, expected_sub_rate, rows, max_iterations=100):
         """RateModel::distanceMatrix (model.cpp:533-553): hist_distance_matrix.  sp_model: descs.SumProdModel (alphabet, component
         weights, eigen-decomposition); rows: uint8 [n][cols] gapped characters.  Returns dist [n][n]."""
@@ -290,6 +321,28 @@ class Context:
         lp_start = np.empty(n) if backward else None
         self.check(self.lib.hist_fill_batch(self.h, arr, n, int(backward), _p(lp_end, C.c_double), _p(lp_start, C.c_double)))
         return lp_end, lp_start
+
+
+def align_path_merge(alignments, row_lengths, lib=None):
+    """alignPathMerge (alignpath.cpp:153-207) on the host: hist_align_path_merge.  alignments: [(rows int[], bits uint8 [len(rows)][cols])];
+    row_lengths: residues of every row.  Returns bits uint8 [n_rows][cols]; rows no alignment mentions stay empty."""
+    lib = lib or load()
+    nrows = np.array([len(r) for r, _ in alignments], np.int32)
+    ncols = np.array([np.asarray(b).shape[1] if len(r) else 0 for r, b in alignments], np.int32)
+    rows = np.ascontiguousarray(np.concatenate([np.asarray(r, np.int32) for r, _ in alignments] + [np.zeros(0, np.int32)]), np.int32)
+    bits = np.ascontiguousarray(np.concatenate([np.asarray(b, np.uint8).ravel() for _, b in alignments] + [np.zeros(0, np.uint8)]), np.uint8)
+    off = np.zeros(len(row_lengths) + 1, np.int64)
+    off[1:] = np.cumsum(row_lengths)
+    rcol, nout = np.zeros(max(1, int(off[-1])), np.int32), np.zeros(1, np.int32)
+    rc = lib.hist_align_path_merge(None, len(alignments), _p(nrows, C.c_int32), _p(ncols, C.c_int32), _p(rows, C.c_int32), _p(bits, C.c_uint8),
+                                   len(row_lengths), _p(off, C.c_int64), _p(rcol, C.c_int32), _p(nout, C.c_int32))
+    if rc:
+        raise HistError(rc, (lib.hist_last_error(None) or b"").decode())
+    out = np.zeros((len(row_lengths), int(nout[0])), np.uint8)
+    for r in range(len(row_lengths)):
+        c = rcol[off[r]:off[r + 1]]
+        out[r, c[c >= 0]] = 1
+    return out
 
 
 class HandleBatch:

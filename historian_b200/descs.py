@@ -285,6 +285,12 @@ class QuickAlignPair(C.Structure):
                 ("n_diagonals", C.c_int32), ("diagonals", C.POINTER(C.c_int32))]
 
 
+class GuideParams(C.Structure):
+    """hist_guide_params (DiagEnvParams, diagenv.h:24-35, plus AlignGraph's choice of edges and the generator's seed)."""
+    _fields_ = [("all_pairs", C.c_int32), ("seed", C.c_uint32), ("sparse", C.c_int32), ("kmer_len", C.c_int32), ("kmer_threshold", C.c_int32),
+                ("band_size", C.c_int32), ("cell_size", C.c_int32), ("reserved", C.c_int32), ("max_size", C.c_int64)]
+
+
 def read_dump(path):
     """Reads the binary container written by oracle/ref_dump.cpp into {name: ndarray|str}."""
     out = {}

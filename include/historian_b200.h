@@ -441,6 +441,45 @@ int hist_quickalign_batch(hist_ctx* ctx, int32_t n, const hist_quickalign_pair* 
                           double* result, int32_t* x_end, int32_t* y_end, uint8_t* paths, const int64_t* path_off,
                           int32_t* path_len);
 
+/* AlignGraph (span.h:9-52, span.cpp:35-158) as `historian recon -seqs` runs it (recon.cpp:806-821): trial edges, one
+ * DiagonalEnvelope (diagenv.cpp:93-190) and one QuickAlignMatrix per edge (on the device, batched), the spanning tree of
+ * the best-scoring edges grown from sequence 0, and alignPathMerge of its n - 1 pairwise alignments.
+ *
+ * hist_guide_params: all_pairs = AlignGraph's all-vs-all constructor (`-allspan`, guideAlignTryAllPairs, recon.cpp:41,
+ *   811-812), else the sparse random graph of ceil(n log2 n) edges, continued until connected (span.cpp:66-91), drawn from
+ *   std::mt19937 seeded with `seed` (Reconstructor::rndSeed, recon.cpp:38, 745-748; 5489 by default).  The rest is
+ *   DiagEnvParams (diagenv.h:24-35): sparse = 0 is -kmatchoff; kmer_threshold >= 0 is -kmatchn; kmer_threshold < 0 takes the
+ *   full envelope when xLen * yLen * cell_size < max_size (the reference's default, with max_size = the machine's memory
+ *   and cell_size = ForwardMatrix::cellSize() = 40) and otherwise the largest set of seeded diagonals that fits max_size.
+ * tokens: FastSeq::unvalidatedTokens of every sequence, concatenated; tok_off [n_seqs + 1].
+ * Outputs: residue_col [tok_off[n_seqs]] = the guide alignment's column of every residue (row s of Alignment::path has its
+ *   k-th `true` at column residue_col[tok_off[s] + k]), *n_cols its number of columns; optionally the trial edges in the
+ *   order they were drawn (*n_edges of them; the first edge_capacity written to edge_rows [2 * e], edge_lp [e] = mx.end) and
+ *   the indices of the spanning tree's edges in joining order (mst_edges [n_seqs - 1]). */
+typedef struct {
+  int32_t all_pairs;
+  uint32_t seed;
+  int32_t sparse;
+  int32_t kmer_len;
+  int32_t kmer_threshold;
+  int32_t band_size;
+  int32_t cell_size;
+  int32_t reserved;
+  int64_t max_size;
+} hist_guide_params;
+int hist_guide_align(hist_ctx* ctx, int32_t n_seqs, const int8_t* tokens, const int64_t* tok_off, const hist_quickalign_scores* scores,
+                     const hist_guide_params* params, int32_t* residue_col, int32_t* n_cols, int32_t* n_edges, int32_t* edge_rows,
+                     double* edge_lp, int64_t edge_capacity, int32_t* mst_edges);
+
+/* alignPathMerge (alignpath.cpp:153-207) on the host: merges alignments that share rows into one.  Alignment k has
+ * n_rows[k] rows (their global indices consecutive in `rows`) and n_cols[k] columns, its 0/1 matrix row-major and
+ * consecutive in `bits`; row r of the result has row_off[r + 1] - row_off[r] residues (every alignment mentioning the row
+ * must agree, alignpath.cpp:113).  residue_col [row_off[n_total_rows]]: output column of every residue (-1 for rows no
+ * alignment mentions); *n_out_cols: number of columns.  HIST_ERR_STATE for inconsistent alignments (the reference aborts).
+ * ctx may be NULL (no device work; used for the error text only). */
+int hist_align_path_merge(hist_ctx* ctx, int32_t n_alignments, const int32_t* n_rows, const int32_t* n_cols, const int32_t* rows,
+                          const uint8_t* bits, int32_t n_total_rows, const int64_t* row_off, int32_t* residue_col, int32_t* n_out_cols);
+
 /* ------------------------------------------------------------------ sum-product
  * SumProduct / AlignColSumProduct (sumprod.h:32-104, sumprod.cpp).
  * The model is passed in eigen-decomposed form (EigenModel, model.cpp:1135-1199):
