@@ -589,6 +589,7 @@ def guide_leg(ctx, args, lg, guide_rows):
                                   "oracle/_ref/bin/ref_dump_quickalign, %.1f s inside them" % (int(f_[f_.index("pairs") + 1]), args.guide_ref_seqs, rf_ + rt_)}
         except Exception:
             ref_base = None
+    stage = guide_stage(ctx, args, lg, toks)
     return {"metric": "guide-alignment Viterbi cells/s", "value": cells / wall / 1e9, "unit": "Gcells/s", "higher_is_better": True, "ms": 1e3 * wall,
             "dtype": "f64 (bit-exact with the reference)", "pairs": len(pairs), "cells": int(cells),
             "diagonals_per_pair": [int(min(len(p[2]) for p in pairs)), int(max(len(p[2]) for p in pairs))],
@@ -601,7 +602,50 @@ def guide_leg(ctx, args, lg, guide_rows):
             {"value": cpu_cells / cpu_s / 1e9, "unit": "Gcells/s", "cores": 1, "kind": "port",
              "sample": "%d of the pairs through oracle/oracle_quickalign.cpp (dense cell array, 1 thread), %.1f s" % (len(sample), cpu_s)},
             "checked": "scores, end cells and paths of %d pairs equal the CPU port's (oracle/oracle_quickalign.cpp, %.3f Gcells/s on one core)" % (
-                len(sample), cpu_cells / cpu_s / 1e9)}
+                len(sample), cpu_cells / cpu_s / 1e9),
+            "stage": stage}
+
+
+def guide_stage(ctx, args, lg, toks):
+    """The whole guide-alignment stage (AlignGraph, span.cpp:35-158) on the first --guide-stage-seqs leaves: random graph of
+    ceil(n log2 n) pairs, full envelopes, Viterbi on the device, spanning tree and merge on the host (hist_guide_align); the
+    unmodified reference's AlignGraph on the first --guide-stage-ref-seqs of them through oracle/_ref/bin/ref_dump_guide, its
+    guide alignment compared with the device's for equality."""
+    from historian_b200 import guide as G
+    sub, sc = G.quickalign_scores(lg, 1.0)
+    n = min(args.guide_stage_seqs, len(toks))
+    ctx.guide_align(toks[:8], sub, sc, sparse=False)
+    wall = float("inf")
+    for _ in range(2):
+        t0 = time.perf_counter()
+        bits, info = ctx.guide_align(toks[:n], sub, sc, sparse=False)
+        wall = min(wall, time.perf_counter() - t0)
+    out = {"seqs": n, "pairs": int(len(info["edges"])), "columns": int(bits.shape[1]), "seconds": wall,
+           "cells": int(sum(len(toks[a]) * len(toks[b]) for a, b in info["edges"]))}
+    ref_bin = os.path.join(ROOT, "oracle", "_ref", "bin", "ref_dump_guide")
+    m = min(args.guide_stage_ref_seqs, n)
+    if os.path.exists(ref_bin) and m >= 2:
+        with tempfile.TemporaryDirectory() as tmp:
+            fa = os.path.join(tmp, "s.fa")
+            with open(fa, "w") as f:
+                for k in range(m):
+                    f.write(">s%d\n%s\n" % (k, "".join(lg.alphabet[t] if t >= 0 else "*" for t in toks[k])))
+            r = subprocess.run([ref_bin, "lg", fa, "1", "rnd", "5489", "full"], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+        try:
+            tl = [ln.split() for ln in r.stderr.splitlines() if ln.startswith("timing")][0]
+            rows = []
+            for ln in r.stdout.splitlines():   # FASTA rows may be wrapped
+                if ln.startswith(">"):
+                    rows.append("")
+                elif rows:
+                    rows[-1] += ln.strip()
+            mine, minfo = ctx.guide_align(toks[:m], sub, sc, sparse=False)
+            same = mine.shape == (m, len(rows[0])) and all(np.array_equal(mine[k], np.frombuffer(rows[k].encode(), np.uint8) != ord("-")) for k in range(m))
+            out["reference"] = {"seqs": m, "pairs": int(len(minfo["edges"])), "graph_seconds": float(tl[2]), "merge_seconds": float(tl[4]), "cores": 1,
+                                "kind": "reference", "guide_alignment_equal": bool(same)}
+        except Exception as e:   # noqa: BLE001
+            out["reference"] = {"unavailable": repr(e)}
+    return out
 
 
 # ------------------------------------------------------------------ distance-matrix leg (SURVEY 8(f) row 2)
@@ -879,6 +923,8 @@ def main():
     ap.add_argument("--no-recon", action="store_true", help="skip the whole-tree reconstruction leg")
     ap.add_argument("--no-codon", action="store_true", help="skip the codon (ECMrest) leg")
     ap.add_argument("--no-guide", action="store_true", help="skip the guide-alignment (QuickAlign) and distance-matrix legs")
+    ap.add_argument("--guide-stage-seqs", type=int, default=1024, help="sequences of the whole-stage guide alignment (hist_guide_align)")
+    ap.add_argument("--guide-stage-ref-seqs", type=int, default=16, help="sequences the reference's AlignGraph is timed on")
     ap.add_argument("--guide-pairs", type=int, default=1024, help="sequence pairs in the guide-alignment leg")
     ap.add_argument("--guide-envelope", default="full", choices=["full", "sparse"])
     ap.add_argument("--distmat-rows", type=int, default=1024, help="rows of the guide alignment in the distance-matrix leg")

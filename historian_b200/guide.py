@@ -98,3 +98,38 @@ def build_tree(ctx, names, dist, method="upgma"):
     """Tree::buildByUPGMA / buildByNeighborJoining on the device -> Newick text equal to the reference's."""
     child, blen = ctx.build_tree(dist, 0 if method == "upgma" else 1)
     return newick(list(names), child, blen)
+
+
+def tokenize(seqs, alphabet):
+    """FastSeq::unvalidatedTokens (fastseq.cpp): token of every character, case-insensitive, -1 outside the alphabet."""
+    lut = np.full(256, -1, np.int8)
+    for k, c in enumerate(alphabet):
+        lut[ord(c.lower())] = lut[ord(c.upper())] = k
+    return [lut[np.frombuffer(s.encode(), np.uint8)] for s in seqs]
+
+
+def guide_alignment(ctx, model, seqs, time=1.0, **params):
+    """AlignGraph::mstAlign as `historian recon -seqs` runs it (recon.cpp:806-821, time 1): hist_guide_align on the device.
+    params: all_pairs, seed, sparse, kmer_len, kmer_threshold, band_size, max_size (Context.guide_align).
+    Returns (bits uint8 [n][cols], info)."""
+    sub, sc = quickalign_scores(model, time)
+    return ctx.guide_align(tokenize(seqs, model.alphabet), sub, sc, **params)
+
+
+def gapped(bits, seqs, gap="-"):
+    """Alignment::gapped (alignpath.cpp:245-276)."""
+    rows = []
+    for b, s in zip(bits, seqs):
+        r = np.full(len(b), ord(gap), np.uint8)
+        r[np.flatnonzero(b)] = np.frombuffer(s.encode(), np.uint8)
+        rows.append(r.tobytes().decode())
+    return rows
+
+
+def tree_from_sequences(ctx, model, names, seqs, method="upgma", max_iterations=100, **guide_params):
+    """The front end of `historian recon -seqs` (recon.cpp:806-821, 731-743): guide alignment, distance matrix of its gapped
+    rows, UPGMA (the default) or neighbour-joining tree -- every stage on the device.  Returns (guide bits [n][cols], Newick)."""
+    bits, _ = guide_alignment(ctx, model, seqs, **guide_params)
+    rows = np.array([np.frombuffer(r.encode(), np.uint8) for r in gapped(bits, seqs)])
+    dist = distance_matrix(ctx, model, rows, max_iterations)
+    return bits, build_tree(ctx, names, dist, method)
