@@ -48,6 +48,9 @@ def load():
                                      D.c_int32_p, D.c_int32_p, D.c_int32_p, D.c_int32_p, D.c_double_p, C.c_int64, D.c_int32_p]
     lib.hist_align_path_merge.argtypes = [vp, C.c_int32, D.c_int32_p, D.c_int32_p, D.c_int32_p, C.POINTER(C.c_uint8), C.c_int32, D.c_int64_p,
                                           D.c_int32_p, D.c_int32_p]
+    lib.hist_sumprod_excluded_posteriors.argtypes = [vp, C.c_char_p, C.c_int64, C.c_int32, D.c_int32_p, D.c_int32_p, C.c_int32, D.c_double_p]
+    lib.hist_branch_align.argtypes = [vp, C.POINTER(D.BranchModel), C.c_int32, D.c_double_p, C.c_int32, D.c_double_p, C.c_int32, D.c_int32_p,
+                                      D.c_int32_p, D.c_double_p, C.POINTER(C.c_uint8), D.c_int32_p]
     lib.hist_ctx_h2d_bytes.argtypes = [vp]
     lib.hist_ctx_h2d_bytes.restype = C.c_int64
     lib.hist_ctx_set_timing.argtypes = [vp, C.c_int]
@@ -204,6 +207,25 @@ class Context:
             bits[s, rcol[off[s]:off[s + 1]]] = 1
         e = int(nedges[0])
         return bits, {"edges": erows[:e].copy(), "edge_lp": elp[:e].copy(), "mst": mst[:max(0, n - 1)].copy()}
+
+    def branch_align(self, log_sub, log_ins, log_cpt_weight, lp_trans, x_pwm, y_pwm, max_distance=-1, x_key=None, y_key=None):
+        """Refiner::BranchMatrix + best() (refiner.cpp:10-106): hist_branch_align.  log_sub [C][A][A], log_ins [C][A], log_cpt_weight [C],
+        lp_trans [3][4]; x_pwm [x_len][C][A], y_pwm [y_len][C][A].  Returns (lp_end, path uint8[]: 3 both, 1 parent only, 2 child only)."""
+        log_sub, log_ins, lcw = (np.ascontiguousarray(v, np.float64) for v in (log_sub, log_ins, log_cpt_weight))
+        Cc, A = log_ins.shape
+        bm = D.BranchModel(A, Cc, _p(log_sub, C.c_double), _p(log_ins, C.c_double), _p(lcw, C.c_double))
+        for a in range(3):
+            for b in range(4):
+                bm.lp_trans[a][b] = float(lp_trans[a][b])
+        x_pwm, y_pwm = np.ascontiguousarray(x_pwm, np.float64).reshape(-1, Cc, A), np.ascontiguousarray(y_pwm, np.float64).reshape(-1, Cc, A)
+        xl, yl = len(x_pwm), len(y_pwm)
+        kx = None if x_key is None else np.ascontiguousarray(x_key, np.int32)
+        ky = None if y_key is None else np.ascontiguousarray(y_key, np.int32)
+        assert max_distance < 0 or (len(kx) == xl + 1 and len(ky) == yl + 1)
+        lp, path, plen = np.zeros(1), np.zeros(max(1, xl + yl), np.uint8), np.zeros(1, np.int32)
+        self.check(self.lib.hist_branch_align(self.h, C.byref(bm), xl, _p(x_pwm, C.c_double), yl, _p(y_pwm, C.c_double), int(max_distance),
+                                              _p(kx, C.c_int32), _p(ky, C.c_int32), _p(lp, C.c_double), _p(path, C.c_uint8), _p(plen, C.c_int32)))
+        return float(lp[0]), path[:int(plen[0])].copy()
 
     def distance_matrix(self, sp_model, expected_sub_rate, rows, max_iterations=100):
         """RateModel::distanceMatrix (model.cpp:533-553): hist_distance_matrix.  sp_model: descs.SumProdModel (alphabet, component
@@ -837,6 +859,20 @@ class SumProd:
         self.ctx.check(self.ctx.lib.hist_sumprod_columns(self.h, _addr(columns), _addr(w), L, int(flags), _addr(r.get("col_loglike")),
                                                          _addr(r.get("counts")), _addr(r.get("map_state")), _addr(r.get("node_post"))))
         return r
+
+    def excluded_posteriors(self, columns, queries, normalize=True):
+        """SumProduct::logNodeExcludedPostProb (sumprod.cpp:219-250) for every column and every query
+        (node, excluded neighbour or -1): hist_sumprod_excluded_posteriors.  Returns [n_queries][n_cols][C][A]."""
+        columns = np.ascontiguousarray(columns, np.uint8)
+        L, N = columns.shape
+        assert N == self.N, "columns must be [n_cols, %d]" % self.N
+        nodes = np.array([q[0] for q in queries], np.int32)
+        excl = np.array([q[1] for q in queries], np.int32)
+        out = np.zeros((len(queries), L, self.C, self.A))
+        if L:
+            self.ctx.check(self.ctx.lib.hist_sumprod_excluded_posteriors(self.h, columns.ctypes.data_as(C.c_char_p), L, len(queries),
+                                                                         _p(nodes, C.c_int32), _p(excl, C.c_int32), int(bool(normalize)), _p(out, C.c_double)))
+        return out
 
     def columns_device(self, d_columns, n_cols, d_counts, d_col_loglike=None, d_weights=None, flags=SP_COUNTS):
         """Same call with every buffer already resident on the device (torch CUDA tensors)."""

@@ -189,6 +189,10 @@ struct SpArgs {
   const int* order;        // [n_cols] processing order (densest columns first: static load balance) or NULL
   int full;                // process every node of every level (debug fetch of all messages); else only the
                            // per-level index ranges that hold ungapped nodes
+  int n_excl;              // logNodeExcludedPostProb queries per column
+  const int* excl_q;       // [n_excl][2] internal indices (node, excluded neighbour or -1)
+  double* excl_out;        // [n_excl][n_cols][C][A] or NULL
+  int excl_norm;           // normalise every [C][A] block
 };
 
 // (forcing more resident blocks through a register cap was measured: 48 / 40 / 32 registers all spill and lose)
@@ -372,7 +376,11 @@ __global__ void __launch_bounds__(SP_THREADS) sumprod_columns_kernel(SpDev S, Sp
       __syncthreads();
     }
     const double colLL = s_misc[0];
-    if (n_ungapped == 0) continue;  // uniform over the block
+    if (n_ungapped == 0) {  // uniform over the block
+      if (a.excl_out)
+        for (int q = tid; q < a.n_excl * CA; q += nt) a.excl_out[((size_t)(q / CA) * a.n_cols + col) * CA + q % CA] = -INFINITY;
+      continue;
+    }
 
     // ---- fillDown (sumprod.cpp:163-198), root first
     for (int lev = 0; lev < S.n_levels; ++lev) {
@@ -408,6 +416,36 @@ __global__ void __launch_bounds__(SP_THREADS) sumprod_columns_kernel(SpDev S, Sp
         }
       }
       __syncthreads();
+    }
+
+    // ---- logNodeExcludedPostProb without normalisation (sumprod.cpp:219-250): the messages a node receives from all its
+    // neighbours but one, restricted to its own residue; rows of -inf where the node is gapped
+    if (a.excl_out)
+      for (int q = tid; q < a.n_excl * CA; q += nt) {
+        const int e = q / CA, c = (q / A) % C, i = q % A;
+        const int node = a.excl_q[2 * e], ex = a.excl_q[2 * e + 1];
+        const int tk = s_tok[node];
+        double v = -INFINITY;
+        if (tk != SP_TOK_GAP) {
+          v = (tk == SP_TOK_WILD || tk == i) ? 0. : -INFINITY;
+          v += S.logcw[c];
+          for (int k = S.kid_off[node]; k < S.kid_off[node + 1]; ++k) {
+            const int ch = S.kid_idx[k];
+            if (ch != ex && s_tok[ch] != SP_TOK_GAP) v += log(E[((size_t)ch * C + c) * A + i]) + logE[(size_t)ch * C + c];   // gapped children: E = 1, logE = 0
+          }
+          if (S.parent[node] != ex || ex < 0) v += log(G[((size_t)node * C + c) * A + i]) + logG[(size_t)node * C + c];
+        }
+        a.excl_out[((size_t)e * a.n_cols + col) * CA + c * A + i] = v;
+      }
+    if (a.excl_out && a.excl_norm) {   // lp -= norm, norm = log-sum-exp over components and residues (sumprod.cpp:242, 245-248)
+      __syncthreads();
+      for (int e = tid; e < a.n_excl; e += nt) {
+        double* o = a.excl_out + ((size_t)e * a.n_cols + col) * CA;
+        double norm = -INFINITY;
+        for (int q = 0; q < CA; ++q) norm = lse2_exact(norm, o[q]);
+        if (norm > -INFINITY)
+          for (int q = 0; q < CA; ++q) o[q] -= norm;
+      }
     }
 
     const bool need_root = (a.flags & (HIST_SP_COUNTS | HIST_SP_MAP_STATES | HIST_SP_NODE_POST)) != 0;
@@ -1203,7 +1241,7 @@ int ensure_work(hist_sumprod* sp, int blocks) {
 
 // Runs the column kernel on device-resident columns; counts_dev (device, accumulated into) may be NULL.
 int run_columns(hist_sumprod* sp, const char* d_cols, const double* d_w, int64_t n_cols, int flags, double* d_ll, double* counts_dev,
-                char* d_map, double* d_post, int force_blocks) {
+                char* d_map, double* d_post, int force_blocks, int n_excl = 0, const int* d_excl_q = nullptr, double* d_excl_out = nullptr, int excl_norm = 0) {
   hist_ctx* ctx = sp->ctx;
   const int blocks = force_blocks > 0 ? force_blocks : (int)std::min<int64_t>(n_cols, sp->max_blocks);
   if (int rc = ensure_work(sp, blocks)) return rc;
@@ -1215,6 +1253,7 @@ int run_columns(hist_sumprod* sp, const char* d_cols, const double* d_w, int64_t
   a.counts_size = (int)hist_sumprod_counts_size(sp);
   a.chunk = sp->chunk; a.n_slices = sp->n_slices; a.err = sp->d_err;
   a.full = force_blocks > 0;  // the debug fetch reads every node's messages
+  a.n_excl = n_excl; a.excl_q = d_excl_q; a.excl_out = d_excl_out; a.excl_norm = excl_norm;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (ctx->timing) {
     cudaEventCreate(&e0); cudaEventCreate(&e1);
@@ -1226,7 +1265,7 @@ int run_columns(hist_sumprod* sp, const char* d_cols, const double* d_w, int64_t
   int widest = 1;
   for (size_t l = 0; l + 1 < sp->lvl_off_h.size(); ++l) widest = std::max(widest, sp->lvl_off_h[l + 1] - sp->lvl_off_h[l]);
   static const int dense_min = getenv("HIST_B200_SP_DENSE_MIN") ? atoi(getenv("HIST_B200_SP_DENSE_MIN")) : 64;
-  const bool dense_ok = force_blocks == 0 && sp->A == 4 && sp->C <= 4 && !d_map && !d_post && widest <= 65535 && n_cols >= dense_min &&
+  const bool dense_ok = force_blocks == 0 && sp->A == 4 && sp->C <= 4 && !d_map && !d_post && !d_excl_out && widest <= 65535 && n_cols >= dense_min &&
                         n_cols < (1ll << 30) && dense_min >= 0;
   int64_t n_dense = 0;
   if ((n_cols > blocks || dense_ok) && n_cols < (1ll << 30)) {
@@ -1392,6 +1431,35 @@ extern "C" int hist_sumprod_columns(hist_sumprod* sp, const char* columns, const
   if (err) return set_err(ctx, HIST_ERR_ARG, "hist_sumprod_columns: a column has more than one root (assertSingleRoot, sumprod.cpp:273)");
   for (size_t q = 0; q < host_counts.size(); ++q) counts[q] += host_counts[q];
   return HIST_OK;
+}
+
+extern "C" int hist_sumprod_excluded_posteriors(hist_sumprod* sp, const char* columns, int64_t n_cols, int32_t n_queries, const int32_t* nodes,
+                                                const int32_t* excludes, int32_t normalize, double* out) {
+  if (!sp) return HIST_ERR_ARG;
+  hist_ctx* ctx = sp->ctx;
+  if (n_cols < 0 || (n_cols > 0 && !columns) || n_queries < 1 || !nodes || !excludes || !out)
+    return set_err(ctx, HIST_ERR_ARG, "hist_sumprod_excluded_posteriors: bad arguments");
+  if (n_cols == 0) return HIST_OK;
+  cudaSetDevice(ctx->device);
+  const size_t N = sp->N, CA = (size_t)sp->C * sp->A;
+  std::vector<int> q(2 * (size_t)n_queries);
+  for (int k = 0; k < n_queries; ++k) {
+    if (nodes[k] < 0 || nodes[k] >= (int)N || excludes[k] >= (int)N)
+      return set_err(ctx, HIST_ERR_ARG, "hist_sumprod_excluded_posteriors: query %d: node %d / %d out of range", k, nodes[k], excludes[k]);
+    q[2 * k] = sp->internal[nodes[k]];
+    q[2 * k + 1] = excludes[k] < 0 ? -1 : sp->internal[excludes[k]];
+  }
+  ArenaPlan plan;
+  const size_t o_cols = plan.add(n_cols * N), o_q = plan.add(q.size() * sizeof(int)), o_out = plan.add(8 * (size_t)n_queries * n_cols * CA);
+  char* scratch = nullptr;
+  HB_CUDA(ctx, cudaMalloc(&scratch, plan.bytes));
+  int rc = hb::check_cuda(ctx, cudaMemcpyAsync(scratch + o_cols, columns, n_cols * N, cudaMemcpyHostToDevice, ctx->stream), "H2D columns");
+  if (!rc) rc = hb::check_cuda(ctx, cudaMemcpyAsync(scratch + o_q, q.data(), q.size() * sizeof(int), cudaMemcpyHostToDevice, ctx->stream), "H2D queries");
+  if (!rc) rc = run_columns(sp, scratch + o_cols, nullptr, n_cols, 0, nullptr, nullptr, nullptr, nullptr, 0, n_queries, (const int*)(scratch + o_q), (double*)(scratch + o_out), normalize ? 1 : 0);
+  if (!rc) rc = hb::check_cuda(ctx, cudaMemcpyAsync(out, scratch + o_out, 8 * (size_t)n_queries * n_cols * CA, cudaMemcpyDeviceToHost, ctx->stream), "D2H excluded posteriors");
+  const int rs = hb::check_cuda(ctx, cudaStreamSynchronize(ctx->stream), "sync after excluded posteriors");
+  cudaFree(scratch);
+  return rc ? rc : rs;
 }
 
 extern "C" int hist_sumprod_debug_column(hist_sumprod* sp, const char* column, double* E, double* F, double* G, double* logE, double* logF,

@@ -285,6 +285,12 @@ class QuickAlignPair(C.Structure):
                 ("n_diagonals", C.c_int32), ("diagonals", C.POINTER(C.c_int32))]
 
 
+class BranchModel(C.Structure):
+    """hist_branch_model."""
+    _fields_ = [("alph_size", C.c_int32), ("components", C.c_int32), ("log_sub", C.POINTER(C.c_double)), ("log_ins", C.POINTER(C.c_double)),
+                ("log_cpt_weight", C.POINTER(C.c_double)), ("lp_trans", (C.c_double * 4) * 3)]
+
+
 class GuideParams(C.Structure):
     """hist_guide_params (DiagEnvParams, diagenv.h:24-35, plus AlignGraph's choice of edges and the generator's seed)."""
     _fields_ = [("all_pairs", C.c_int32), ("seed", C.c_uint32), ("sparse", C.c_int32), ("kmer_len", C.c_int32), ("kmer_threshold", C.c_int32),

@@ -537,6 +537,39 @@ int hist_sumprod_columns(hist_sumprod* sp, const char* columns, const double* we
                          int32_t flags, double* col_loglike, double* counts, char* map_state,
                          double* node_post);
 
+/* SumProduct::logNodeExcludedPostProb (sumprod.cpp:219-250), for every column and every query
+ * (nodes[q], excludes[q]): log of cptWeight[c] x the messages node receives from all its tree neighbours except `exclude`
+ * (a child, the parent, or -1 for none), restricted to the node's own residue -- the conditional position weight
+ * matrices of TreeAlignFuncs::getConditionalPWMs (sampler.cpp:356-372), whose restricted fillUp / fillDown orders yield
+ * the same messages as the full passes.  normalize != 0 (getConditionalPWMs' default): every [C][A] block minus its
+ * log-sum-exp.  out [n_queries][n_cols][C][A]; rows of -inf in columns where the node is gapped. */
+int hist_sumprod_excluded_posteriors(hist_sumprod* sp, const char* columns, int64_t n_cols, int32_t n_queries, const int32_t* nodes,
+                                     const int32_t* excludes, int32_t normalize, double* out);
+
+/* ------------------------------------------------------------------ refinement stage
+ * Refiner::BranchMatrix (refiner.cpp:10-106) over TreeAlignFuncs::BranchMatrixBase (sampler.h:183-210, sampler.cpp:1005-1031):
+ * Viterbi alignment of a parent's and a child's conditional position weight matrices (hist_sumprod_excluded_posteriors:
+ * parent excluding the child, child excluding the parent) under the branch's ProbModel, and its traceback best().
+ *   model: logProbModel.logSubProb [C][A][A] (parent residue i -> child residue j), logInsProb [C][A], logCptWeight [C] of
+ *          ProbModel (model, max (Tree::minBranchLength, dist)), and lp_trans[src][dest] = log transProb (src, dest) for
+ *          src in Match, Insert, Delete and dest in Match, Insert, Delete, End (model.cpp:400-447).
+ *   x_pwm [x_len][C][A], y_pwm [y_len][C][A]: log weights of the parent's / child's residues.
+ *   max_distance, x_key [x_len + 1], y_key [y_len + 1]: the envelope, cell (x, y) is inside iff it lies on the border of
+ *          the matrix or |x_key[x] - y_key[y]| <= max_distance (sampler.h:146-149 with GuideAlignmentEnvelope::inRange:
+ *          x_key[x] = cumulativeMatches[row1PosToCol[xEnvPos[x]]]); max_distance < 0: no envelope, keys may be NULL.
+ * Outputs: *lp_end (the Viterbi log-likelihood), path [capacity x_len + y_len] / *path_len: the columns of best(),
+ *          3 = both rows, 1 = parent only, 2 = child only. */
+typedef struct {
+  int32_t alph_size;
+  int32_t components;
+  const double* log_sub;
+  const double* log_ins;
+  const double* log_cpt_weight;
+  double lp_trans[3][4];
+} hist_branch_model;
+int hist_branch_align(hist_ctx* ctx, const hist_branch_model* model, int32_t x_len, const double* x_pwm, int32_t y_len, const double* y_pwm,
+                      int32_t max_distance, const int32_t* x_key, const int32_t* y_key, double* lp_end, uint8_t* path, int32_t* path_len);
+
 /* Fetch E/F/G messages and their log scale factors of ONE column for parity tests
  * (SumProductStorage, sumprod.h:14-30): each [C][N][A] resp. [C][N]. */
 int hist_sumprod_debug_column(hist_sumprod* sp, const char* column, double* E, double* F, double* G,
