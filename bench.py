@@ -648,6 +648,57 @@ def guide_stage(ctx, args, lg, toks):
     return out
 
 
+# ------------------------------------------------------------------ refinement leg
+def refine_leg(ctx, args, lg):
+    """Refiner::refine (refiner.cpp:108-194) on BASELINE config 2 (PF16593, 43 leaves, committed under tests/golden/pf16593):
+    the deterministic reconstruction, then branch refinement moves until n - 1 in a row fail to improve the log-likelihood.
+    Every move = conditional position weight matrices (hist_sumprod_excluded_posteriors), branch Viterbi (hist_branch_align),
+    merge, log-likelihood (hist_sumprod_columns).  Reference: the binary's `recon -refine` minus `recon -norefine` wall time."""
+    from historian_b200 import recon as R, refine as RF, simulator as S
+    gdir = os.path.join(ROOT, "tests", "golden", "pf16593")
+    gf, tf = os.path.join(gdir, "PF16593.guide.fa"), os.path.join(gdir, "PF16593.nhx")
+    if not (os.path.exists(gf) and os.path.exists(tf)):
+        return None
+    tree = S.Tree.from_newick(open(tf).read())
+    names, rows = [], []
+    for ln in open(gf).read().splitlines():
+        if ln.startswith(">"):
+            names.append(ln[1:].split()[0]); rows.append("")
+        elif names:
+            rows[-1] += ln.strip()
+    node_of = {nm: v for v, nm in enumerate(tree.names) if tree.is_leaf(v)}
+    seqs = {node_of[nm]: r.replace("-", "").replace(".", "") for nm, r in zip(names, rows)}
+    grows = {node_of[nm]: np.array([c not in "-." for c in r]) for nm, r in zip(names, rows)}
+    nat = R.NativeReconstructor(ctx, lg, band=20, profile_samples=10, max_profile_states=1)
+    bits, _, rec = nat.reconstruct(tree, seqs, grows)
+    gapped = R.gapped_rows_dense(bits, tree, seqs, wildcard="x")
+    start = np.array([np.frombuffer(gapped[v].encode(), np.uint8) for v in range(tree.n_nodes)])
+    best = None
+    launches0 = ctx.launch_count
+    for _ in range(2):
+        r = RF.Refiner(ctx, lg, tree)
+        t0 = time.perf_counter()
+        lp0 = r.log_likelihood(start)
+        got, lp = r.refine(start)
+        wall = time.perf_counter() - t0
+        r.close()
+        if best is None or wall < best[0]:
+            best = (wall, r.moves, r.accepted, lp0, lp)
+    out = {"metric": "branch refinement wall time", "value": best[0], "unit": "s", "higher_is_better": False, "moves": best[1], "accepted": best[2],
+           "log_likelihood": [best[3], best[4]], "ms_per_move": 1e3 * best[0] / max(1, best[1]), "gpu_launches": int((ctx.launch_count - launches0) // 2),
+           "config": {"workload": "PF16593 (43 leaves x 32-36 residues, 85 nodes), deterministic reconstruction, band 20"}}
+    ref_bin = os.path.join(ROOT, "oracle", "_ref", "bin", "historian")
+    if os.path.exists(ref_bin):
+        t = {}
+        for flag in ("-norefine", "-refine"):
+            t0 = time.perf_counter()
+            subprocess.run([ref_bin, "recon", "-guide", gf, "-tree", tf, "-output", "fasta", "-profmaxstates", "1", flag], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+            t[flag] = time.perf_counter() - t0
+        out["cpu_baseline"] = {"value": t["-refine"] - t["-norefine"], "unit": "s", "cores": 1, "kind": "reference",
+                               "sample": "oracle/_ref/bin/historian recon -refine minus -norefine on the same input, wall clock"}
+    return out
+
+
 # ------------------------------------------------------------------ distance-matrix leg (SURVEY 8(f) row 2)
 def distmat_leg(ctx, args, lg, guide_rows):
     """RateModel::distanceMatrix (model.cpp:506-655) of the bench family's guide alignment: n (n - 1) / 2 maximum-likelihood
@@ -886,7 +937,12 @@ def gpu_arm(args):
     distmat_line = None
     if not args.no_guide and world == 1:
         distmat_line = distmat_leg(ctx, args, lg, guide)
+    refine_line = None
+    if not args.no_guide and world == 1:
+        refine_line = refine_leg(ctx, args, lg)
     if rank == 0:
+        if refine_line is not None:
+            line["refine"] = refine_line
         if guide_line is not None:
             line["guide_align"] = guide_line
         if distmat_line is not None:
