@@ -450,10 +450,11 @@ class NativeReconstructor:
             return [[v] for v in range(tree.n_nodes) if not tree.is_leaf(v)]   # one generator stream, node order
         return merge_levels(tree)
 
-    def reconstruct(self, tree, seqs, guide=None, rec=None, groups=None, on_group=None):
+    def reconstruct(self, tree, seqs, guide=None, rec=None, groups=None, on_group=None, mt_state=None):
         """Same arguments as Reconstructor.reconstruct.  Returns (alignment bool [n_nodes][cols], final Forward
         log-likelihood, capi.Recon).  `rec`/`groups`: continue on an existing hist_recon with a given schedule;
-        on_group(nodes, rec) is called after every library call (the new parents are still live then)."""
+        on_group(nodes, rec) is called after every library call (the new parents are still live then); mt_state: the
+        generator image to continue from (a resumed sampled run), updated in place; kept in self.mt_state."""
         from . import capi
         cl, _ = closest_leaves(tree)
         if rec is None:
@@ -462,7 +463,8 @@ class NativeReconstructor:
             if guide is not None:
                 rec.set_guide(leaves, np.array([guide[v] for v in leaves], np.uint8))
             rec.add_leaves(leaves, [seqs[v] for v in leaves])
-        mt_state = mt19937_seed(self.seed)
+        mt_state = mt19937_seed(self.seed) if mt_state is None else mt_state
+        self.mt_state = mt_state
         band = self.band if guide is not None else -1
         lp_final = -np.inf
         for nodes in (groups if groups is not None else self.schedule(tree)):
@@ -480,6 +482,8 @@ class NativeReconstructor:
             if on_group is not None:
                 on_group(nodes, rec)
         self.stage_ms = rec.stage_ms()
+        if tree.root not in self.lp_end and groups is not None:
+            return None, lp_final, rec   # a partial schedule: no root yet
         return rec.alignment(), lp_final, rec
 
 
@@ -691,3 +695,37 @@ def gapped_rows(path, tree, seqs, wildcard="*"):
         it = iter(s)
         out[row] = "".join(next(it) if b else "-" for b in rp)
     return out
+
+
+# ------------------------------------------------------------------ checkpoint / resume of a partial progressive run
+def save_checkpoint(path, rec, live_nodes, done_groups, mt_state=None):
+    """Writes a partial progressive reconstruction to `path` (the flattened-profile format of
+    hist_recon_export_node / hist_recon_export_stores, one .npz): the profiles that still wait for their parent -- host blob
+    (structure, transition weights, coordinates, path ids) and lpAbsorb table, read back from the device -- and the
+    alignment-path stores of every node built so far.  `done_groups`: how many groups of the schedule are finished."""
+    import torch
+    out = {"stores": rec.export_stores(), "live": np.array(sorted(live_nodes), np.int32), "done_groups": np.array([done_groups], np.int64)}
+    if mt_state is not None:
+        out["mt_state"] = np.asarray(mt_state, np.uint32)
+    dev = torch.device("cuda", rec.ctx.device) if hasattr(rec.ctx, "device") else torch.device("cuda")
+    for v in out["live"]:
+        nb, db = rec.export_sizes(int(v))
+        table = torch.empty(db, dtype=torch.uint8, device=dev)
+        out["blob%d" % v] = rec.export_node(int(v), table.data_ptr())
+        torch.cuda.synchronize()
+        out["table%d" % v] = table.cpu().numpy()
+    np.savez(path, **out)
+
+
+def load_checkpoint(path, rec):
+    """Restores what save_checkpoint wrote into a fresh hist_recon (guide set, no leaves added).  Returns (live nodes,
+    done_groups, mt_state or None)."""
+    import torch
+    d = np.load(path)
+    dev = torch.device("cuda", rec.ctx.device) if hasattr(rec.ctx, "device") else torch.device("cuda")
+    for v in d["live"]:
+        table = torch.from_numpy(d["table%d" % v]).to(dev)
+        torch.cuda.synchronize()
+        rec.import_node(int(v), np.ascontiguousarray(d["blob%d" % v]), table.data_ptr())
+    rec.import_stores(np.ascontiguousarray(d["stores"]))
+    return [int(v) for v in d["live"]], int(d["done_groups"][0]), (d["mt_state"] if "mt_state" in d.files else None)
