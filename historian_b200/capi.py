@@ -167,10 +167,11 @@ class Context:
         sc = D.QuickAlignScores(int(sub.shape[0]), _p(sub, C.c_double), *[float(v) for v in scores])
         keep, arr = [], (D.QuickAlignPair * n)()
         off = np.zeros(n + 1, np.int64)
-        for k, (xt, yt, dg) in enumerate(pairs):
-            xt, yt, dg = np.ascontiguousarray(xt, np.int8), np.ascontiguousarray(yt, np.int8), np.ascontiguousarray(dg, np.int32)
+        for k, (xt, yt, dg) in enumerate(pairs):   # dg None: the full envelope
+            xt, yt = np.ascontiguousarray(xt, np.int8), np.ascontiguousarray(yt, np.int8)
+            dg = None if dg is None else np.ascontiguousarray(dg, np.int32)
             keep.append((xt, yt, dg))
-            arr[k] = D.QuickAlignPair(len(xt), len(yt), _p(xt, C.c_int8), _p(yt, C.c_int8), len(dg), _p(dg, C.c_int32))
+            arr[k] = D.QuickAlignPair(len(xt), len(yt), _p(xt, C.c_int8), _p(yt, C.c_int8), len(xt) + len(yt) - 1 if dg is None else len(dg), _p(dg, C.c_int32))
             off[k + 1] = off[k] + len(xt) + len(yt)
         result, xe, ye = np.zeros(n), np.zeros(n, np.int32), np.zeros(n, np.int32)
         buf = np.zeros(max(1, int(off[n])), np.uint8) if want_paths else None

@@ -36,24 +36,63 @@ struct DmModel {
   const double* ev_re; const double* ev_im;          // [C][A]
   const double* v_re; const double* v_im;            // [C][A][A]  V[a][k]
   const double* vi_re; const double* vi_im;          // [C][A][A]  V^-1[k][b]
+  int is_real;            // every eigenvalue and eigenvector entry has a zero imaginary part (reversible models)
+  int staged;             // is_real and the real parts fit the shared-memory budget: V and V^-1 transposed are staged per CTA
 };
 
 __device__ __forceinline__ double dm_max(double a, double b) { return a < b ? b : a; }   // std::max
 __device__ __forceinline__ double dm_min(double a, double b) { return b < a ? b : a; }   // std::min
 
-// dynamic shared memory, carved by dm_shared(): [term A*A doubles | e_re, e_im C*A doubles | counts, ent_idx, ent_cnt A*A ints]
+// dynamic shared memory: [term A*A doubles | e_re, e_im C*A doubles | staged V, V^-1 transposed (optional) | counts, ent_idx, ent_cnt A*A ints]
 struct DmShared {
   double* term; double* e_re; double* e_im;
+  double* sv; double* svit;   // staged V[c][i][k] and V^-1 transposed [c][j][k], row stride A | 1 (bank-conflict padding)
   int* counts; int* ent_idx; int* ent_cnt;
   int n_ent;
   double f;
 };
-__host__ __device__ inline size_t dm_shared_bytes(int A, int C) { return ((size_t)A * A + 2 * (size_t)C * A) * sizeof(double) + 3 * (size_t)A * A * sizeof(int); }
+__host__ __device__ inline size_t dm_staged_doubles(int A, int C) { return 2 * (size_t)C * A * (A | 1); }
+__host__ __device__ inline size_t dm_shared_bytes(int A, int C, int staged) {
+  return ((size_t)A * A + 2 * (size_t)C * A + (staged ? dm_staged_doubles(A, C) : 0)) * sizeof(double) + 3 * (size_t)A * A * sizeof(int);
+}
 
 // distanceMatrixNegLogLike (model.cpp:555-569) for the CTA's pair; every thread returns the value
 __device__ double dm_neg_loglike(const DmModel& M, DmShared& S, double t) {
   const int A = M.A, C = M.C, tid = threadIdx.x;
   __syncthreads();
+  if (M.is_real) {
+    // Real spectrum: the complex expressions below reduce to these, bit for bit (cos 0 = 1, every imaginary term is a
+    // signed zero), with the roundings written out so that no contraction can change them.
+    for (int k = tid; k < A * C; k += DM_THREADS) S.e_re[k] = exp(M.ev_re[k] * t);
+    __syncthreads();
+    const int ld = A | 1;
+    for (int q = tid; q < S.n_ent; q += DM_THREADS) {
+      const int i = S.ent_idx[q] / A, j = S.ent_idx[q] % A;
+      double p = 0;
+      for (int c = 0; c < C; ++c) {
+        double acc = 0;
+        if (M.staged) {
+          const double* vr = S.sv + ((size_t)c * A + i) * ld;
+          const double* ir = S.svit + ((size_t)c * A + j) * ld;
+          for (int k = 0; k < A; ++k) acc = __dadd_rn(acc, __dmul_rn(__dmul_rn(vr[k], S.e_re[c * A + k]), ir[k]));
+        } else {
+          const double* vr = M.v_re + ((size_t)c * A + i) * A;
+          const double* ir = M.vi_re + (size_t)c * A * A + j;
+          for (int k = 0; k < A; ++k) acc = __dadd_rn(acc, __dmul_rn(__dmul_rn(vr[k], S.e_re[c * A + k]), ir[(size_t)k * A]));
+        }
+        p = __fma_rn(M.w[c], acc, p);   // as the compiler contracts `p += w * acc` below
+      }
+      S.term[q] = log(p) * (double)S.ent_cnt[q];
+    }
+    __syncthreads();
+    if (tid == 0) {
+      double ll = 0;
+      for (int q = 0; q < S.n_ent; ++q) ll += S.term[q];
+      S.f = -ll;
+    }
+    __syncthreads();
+    return S.f;
+  }
   for (int k = tid; k < A * C; k += DM_THREADS) {
     const double m = exp(M.ev_re[k] * t), ph = M.ev_im[k] * t;
     S.e_re[k] = m * cos(ph);
@@ -99,11 +138,21 @@ __global__ void __launch_bounds__(DM_THREADS) distmat_kernel(DmModel M, const si
     S.term = dm_smem;
     S.e_re = S.term + A * A;
     S.e_im = S.e_re + M.C * A;
-    S.counts = reinterpret_cast<int*>(S.e_im + M.C * A);
+    S.sv = S.e_im + M.C * A;
+    S.svit = S.sv + (M.staged ? (size_t)M.C * A * (A | 1) : 0);
+    S.counts = reinterpret_cast<int*>(S.svit + (M.staged ? (size_t)M.C * A * (A | 1) : 0));
     S.ent_idx = S.counts + A * A;
     S.ent_cnt = S.ent_idx + A * A;
   }
   __syncthreads();
+  if (M.staged) {
+    const int ld = A | 1;
+    for (int q = tid; q < M.C * A * A; q += DM_THREADS) {
+      const int c = q / (A * A), r = (q / A) % A, k = q % A;
+      S.sv[((size_t)c * A + r) * ld + k] = M.v_re[q];                                   // V[c][r][k]
+      S.svit[((size_t)c * A + r) * ld + k] = M.vi_re[((size_t)c * A + k) * A + r];      // V^-1[c][k][r]
+    }
+  }
   // pair index -> (i, j)
   long long p = blockIdx.x;
   int i = 0;
@@ -249,7 +298,14 @@ extern "C" int hist_distance_matrix(hist_ctx* ctx, const hist_model_desc* model,
     M.v_re = (const double*)(d + o_v); M.v_im = M.v_re + AA;
     M.vi_re = (const double*)(d + o_vi); M.vi_im = M.vi_re + AA;
     const long long n_pairs = (long long)n_rows * (n_rows - 1) / 2;
-    const size_t smem = dm_shared_bytes(A, C);
+    auto all_zero = [](const double* v, size_t n) {
+      for (size_t k = 0; k < n; ++k)
+        if (v[k] != 0.0) return false;
+      return true;
+    };
+    M.is_real = all_zero(model->eval_im, CA) && all_zero(model->evec_im, AA) && all_zero(model->evec_inv_im, AA);
+    M.staged = M.is_real && dm_staged_doubles(A, C) * sizeof(double) <= 16 * 1024;
+    const size_t smem = dm_shared_bytes(A, C, M.staged);
     if (smem > 48 * 1024) rc = check_cuda(ctx, cudaFuncSetAttribute(distmat_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "distmat shared memory");
     if (!rc) distmat_kernel<<<(unsigned)n_pairs, DM_THREADS, smem, ctx->stream>>>(M, (const signed char*)(d + o_tok), n_rows, n_cols, expected_sub_rate, max_iterations,
                                                                        (double*)(d + o_dist));

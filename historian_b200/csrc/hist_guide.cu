@@ -126,12 +126,10 @@ long long merge_alignments(const std::vector<MergeAlign>& al, long long n_res, s
 
 // DiagonalEnvelope::initFull / initSparse (diagenv.cpp:93-190): the ascending list of diagonals i - j of a pair.
 // tokens < 0: not in the alphabet.  P: hist_guide_params.
+// An empty list stands for the full envelope (all xLen + yLen - 1 diagonals).
 void envelope_diagonals(const int8_t* x, int xLen, const int8_t* y, int yLen, int A, const hist_guide_params& P, std::vector<int>& diags) {
   const int lo = 1 - yLen, hi = xLen - 1;
-  auto full = [&]() {
-    diags.resize((size_t)xLen + yLen - 1);
-    std::iota(diags.begin(), diags.end(), lo);
-  };
+  auto full = [&]() { diags.clear(); };
   const int K = P.kmer_len;
   if (!P.sparse) return full();
   if (P.kmer_threshold >= 0) {
@@ -336,7 +334,7 @@ extern "C" int hist_guide_align(hist_ctx* ctx, int32_t n_seqs, const int8_t* tok
       const int xl = (int)(tok_off[a + 1] - tok_off[a]), yl = (int)(tok_off[b + 1] - tok_off[b]);
       std::vector<int> d;
       envelope_diagonals(tokens + tok_off[a], xl, tokens + tok_off[b], yl, scores->alph_size, P, d);
-      const size_t need = d.size() * ((size_t)yl + 1);
+      const size_t need = (d.empty() ? (size_t)xl + yl - 1 : d.size()) * ((size_t)yl + 1);
       if (end > at && (tb + need > tb_budget || end - at >= 8192)) break;
       tb += need;
       diags.push_back(std::move(d));
@@ -352,8 +350,8 @@ extern "C" int hist_guide_align(hist_ctx* ctx, int32_t n_seqs, const int8_t* tok
       qp[k].y_len = (int32_t)(tok_off[b + 1] - tok_off[b]);
       qp[k].x_tok = tokens + tok_off[a];
       qp[k].y_tok = tokens + tok_off[b];
-      qp[k].n_diagonals = (int32_t)diags[k].size();
-      qp[k].diagonals = diags[k].data();
+      qp[k].n_diagonals = diags[k].empty() ? qp[k].x_len + qp[k].y_len - 1 : (int32_t)diags[k].size();
+      qp[k].diagonals = diags[k].empty() ? nullptr : diags[k].data();
       poff[k] = ptot;
       ptot += (int64_t)qp[k].x_len + qp[k].y_len;
     }

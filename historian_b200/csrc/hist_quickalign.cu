@@ -75,7 +75,9 @@ __global__ void __launch_bounds__(1024, 2) quickalign_kernel(const QaPair* __res
   int* rI = rJ + T;
   const signed char* xt = reinterpret_cast<const signed char*>(blob + P.x_tok);
   const signed char* yt = reinterpret_cast<const signed char*>(blob + P.y_tok);
-  const int* dg = diags + P.diag;
+  const int* dgp = P.diag >= 0 ? diags + P.diag : nullptr;   // NULL: the full envelope, slot k holds diagonal 1 - yLen + k
+  const int dlo = 1 - P.y_len;
+#define dg(k) (dgp ? dgp[(k)] : dlo + (k))
   unsigned char* tb = tb_all + P.tb;
   const double NEG = -INFINITY;
   for (int k = tid; k < nd; k += T) { sM[k] = NEG; sI[k] = NEG; sD[k] = NEG; }
@@ -88,14 +90,14 @@ __global__ void __launch_bounds__(1024, 2) quickalign_kernel(const QaPair* __res
     // thread has exactly one cell per step (slot-per-thread would leave every other lane idle)
     for (int kk = 2 * tid; kk < nd + 1; kk += 2 * T)
     for (int k = kk; k < min(kk + 2, nd); ++k) {
-      const int delta = dg[k];
+      const int delta = dg(k);
       if ((a ^ delta) & 1) continue;
       const int i = (a + delta) / 2, j = a - i;
       if (i < 1 || i > xLen || j < 1 || j > yLen) continue;
       // (i-1, j-1): this diagonal's previous cell
       const double M0 = sM[k], I0 = sI[k], D0 = sD[k];
       // (i, j-1): diagonal delta + 1;  (i-1, j): diagonal delta - 1
-      const bool up = k + 1 < nd && dg[k + 1] == delta + 1, lf = k > 0 && dg[k - 1] == delta - 1;
+      const bool up = k + 1 < nd && dg(k + 1) == delta + 1, lf = k > 0 && dg(k - 1) == delta - 1;
       const double Mu = up ? sM[k + 1] : NEG, Iu = up ? sI[k + 1] : NEG;
       const double Ml = lf ? sM[k - 1] : NEG, Il = lf ? sI[k - 1] : NEG, Dl = lf ? sD[k - 1] : NEG;
       const int tx = xt[i - 1], ty = yt[j - 1];
@@ -166,7 +168,7 @@ __global__ void __launch_bounds__(1024, 2) quickalign_kernel(const QaPair* __res
     const int delta = i - j;
     while (lo < hi) {
       const int mid = (lo + hi) >> 1;
-      if (dg[mid] < delta) lo = mid + 1; else hi = mid;
+      if (dg(mid) < delta) lo = mid + 1; else hi = mid;
     }
     k = lo;
   }
@@ -189,6 +191,7 @@ __global__ void __launch_bounds__(1024, 2) quickalign_kernel(const QaPair* __res
   for (int q = 0; q < xLen - bestI; ++q) out[c++] = 1;
   for (int q = 0; q < yLen - bestJ; ++q) out[c++] = 2;
   path_len[blockIdx.x] = c;
+#undef dg
 }
 
 }  // namespace hb
@@ -208,16 +211,21 @@ extern "C" int hist_quickalign_batch(hist_ctx* ctx, int32_t n, const hist_quicka
   int max_nd = 1;
   for (int k = 0; k < n; ++k) {
     const hist_quickalign_pair& p = pairs[k];
-    if (p.x_len < 1 || p.y_len < 1 || !p.x_tok || !p.y_tok || p.n_diagonals < 1 || !p.diagonals)
+    if (p.x_len < 1 || p.y_len < 1 || !p.x_tok || !p.y_tok || p.n_diagonals < 1)
       return set_err(ctx, HIST_ERR_ARG, "hist_quickalign_batch: pair %d: empty sequence or envelope", k);
-    for (int q = 0; q < p.n_diagonals; ++q)
+    const bool full = !p.diagonals;   // initFull without the list
+    if (full && p.n_diagonals != p.x_len + p.y_len - 1)
+      return set_err(ctx, HIST_ERR_ARG, "hist_quickalign_batch: pair %d: a full envelope (diagonals == NULL) has xLen + yLen - 1 = %d diagonals, not %d", k,
+                     p.x_len + p.y_len - 1, p.n_diagonals);
+    for (int q = 0; !full && q < p.n_diagonals; ++q)
       if (p.diagonals[q] < 1 - p.y_len || p.diagonals[q] > p.x_len - 1 || (q && p.diagonals[q] <= p.diagonals[q - 1]))
         return set_err(ctx, HIST_ERR_ARG, "hist_quickalign_batch: pair %d: diagonals must be ascending and inside [1 - yLen, xLen - 1]", k);
     QaPair& q = qp[k];
     q.x_len = p.x_len; q.y_len = p.y_len; q.nd = p.n_diagonals; q.pad = 0;
     q.x_tok = (long long)tok_bytes; tok_bytes += (size_t)p.x_len;
     q.y_tok = (long long)tok_bytes; tok_bytes += (size_t)p.y_len;
-    q.diag = (long long)n_diag; n_diag += (size_t)p.n_diagonals;
+    q.diag = full ? -1 : (long long)n_diag;
+    if (!full) n_diag += (size_t)p.n_diagonals;
     q.tb = (long long)tb_bytes; tb_bytes += (size_t)p.n_diagonals * ((size_t)p.y_len + 1);
     q.path = (long long)path_bytes; path_bytes += 2 * ((size_t)p.x_len + p.y_len);
     max_nd = std::max(max_nd, p.n_diagonals);
@@ -236,7 +244,7 @@ extern "C" int hist_quickalign_batch(hist_ctx* ctx, int32_t n, const hist_quicka
   for (int k = 0; k < n; ++k) {
     memcpy(blob.data() + o_tok + qp[k].x_tok, pairs[k].x_tok, (size_t)pairs[k].x_len);
     memcpy(blob.data() + o_tok + qp[k].y_tok, pairs[k].y_tok, (size_t)pairs[k].y_len);
-    memcpy(blob.data() + o_diag + (size_t)qp[k].diag * sizeof(int), pairs[k].diagonals, (size_t)pairs[k].n_diagonals * sizeof(int));
+    if (qp[k].diag >= 0) memcpy(blob.data() + o_diag + (size_t)qp[k].diag * sizeof(int), pairs[k].diagonals, (size_t)pairs[k].n_diagonals * sizeof(int));
   }
   for (size_t q = 0; q < tok_bytes; ++q) {   // tokens outside the alphabet count as "not in the alphabet"
     signed char& t = reinterpret_cast<signed char&>(blob[o_tok + q]);

@@ -420,7 +420,8 @@ int64_t hist_noalloc_scratch_bytes(void);
  * hist_quickalign_scores: what the QuickAlignMatrix constructor derives from (model, time), quickalign.cpp:22-50:
  *   submat [A][A] = logSubProb[i][j] - logInsProb[j]; the public members noGap, gapOpen, gapExtend, m2m .. d2m.
  * hist_quickalign_pair: tokens as FastSeq::unvalidatedTokens gives them (< 0 or >= A: not in the alphabet) and
- *   DiagonalEnvelope::diagonals (ascending values of i - j, within [1 - y_len, x_len - 1]; initFull or initSparse).
+ *   DiagonalEnvelope::diagonals (ascending values of i - j, within [1 - y_len, x_len - 1]; initFull or initSparse);
+ *   diagonals == NULL with n_diagonals = x_len + y_len - 1 is the full envelope without the list.
  * Outputs per pair k: result[k] = mx.result (-inf: no alignment inside the envelope), x_end / y_end = mx.xEnd / yEnd,
  *   and, if paths != NULL, the columns of alignPath() from paths[path_off[k]] on (capacity x_len + y_len, path_len[k]
  *   columns): 3 = both rows, 1 = row 0 (x) only, 2 = row 1 (y) only; path_len[k] = 0 when result is -inf. */

@@ -126,3 +126,22 @@ def test_host_envelope_and_scores_match_the_reference():
             dg = guide.sparse_envelope(d[p + "x_tok"], d[p + "y_tok"], A, *args)
             assert np.array_equal(dg, d[p + "diagonals"]), (name, k)
             assert guide.envelope_cells(dg, len(d[p + "x_tok"]), len(d[p + "y_tok"])) > 0
+
+
+@pytest.mark.gpu
+def test_full_envelope_without_the_diagonal_list(ctx):
+    """diagonals == NULL stands for initFull: same scores, end cells and paths as the explicit list."""
+    d = H.load_golden(os.path.join(H.GOLDEN_DIR, "quickalign_lg6x120_full.npz"))
+    cs = list(cases(d))
+    res, ends, paths = ctx.quickalign([(c[1][0], c[1][1], None) for c in cs], cs[0][2], cs[0][3])
+    for (k, _, _, _, want, end, wpath), got, gend, gpath in zip(cs, res, ends, paths):
+        assert got == want and tuple(gend) == end and np.array_equal(gpath, wpath), k
+    with pytest.raises(Exception):   # a NULL list with another count is rejected
+        from historian_b200 import descs as D
+        import ctypes as C
+        x, y = cs[0][1][0].astype(np.int8), cs[0][1][1].astype(np.int8)
+        sub = np.ascontiguousarray(cs[0][2], np.float64)
+        sc = D.QuickAlignScores(int(sub.shape[0]), sub.ctypes.data_as(C.POINTER(C.c_double)), *[float(v) for v in cs[0][3]])
+        pr = (D.QuickAlignPair * 1)(D.QuickAlignPair(len(x), len(y), x.ctypes.data_as(C.POINTER(C.c_int8)), y.ctypes.data_as(C.POINTER(C.c_int8)), 5, None))
+        r = np.zeros(1)
+        ctx.check(ctx.lib.hist_quickalign_batch(ctx.h, 1, pr, C.byref(sc), r.ctypes.data_as(C.POINTER(C.c_double)), None, None, None, None, None))
