@@ -79,6 +79,7 @@ def load():
     lib.hist_fwd_fill.argtypes = [vp, D.c_double_p]
     lib.hist_bwd_fill.argtypes = [vp, D.c_double_p]
     lib.hist_fill_batch.argtypes = [vp, C.POINTER(vp), C.c_int32, C.c_int, D.c_double_p, D.c_double_p]
+    lib.hist_fill_batch_results.argtypes = [vp, C.POINTER(vp), C.c_int32, C.c_int, D.c_double_p, D.c_double_p]
     lib.hist_cells_fetch.argtypes = [vp, C.c_int, D.c_double_p, D.c_int32_p, D.c_int32_p, C.c_int64, D.c_int64_p]
     lib.hist_trace_best.argtypes = [vp, D.Cell, C.POINTER(D.Cell), C.c_int64, D.c_int64_p]
     lib.hist_trace_best_forward.argtypes = [vp, D.Cell, C.POINTER(D.Cell), C.c_int64, D.c_int64_p]
@@ -333,9 +334,18 @@ class Context:
         """hist_fill_batch with lp_end == NULL: enqueue the fills, no read-back, no synchronisation."""
         n = len(pairs)
         if arr is None:
-            arr = (C.c_void_p * n)(*[p.h for p in pairs])
+            arr = pairs.arr if isinstance(pairs, HandleBatch) else (C.c_void_p * n)(*[p.h for p in pairs])
         self.check(self.lib.hist_fill_batch(self.h, arr, n, int(backward), None, None))
         return arr
+
+    def fill_results(self, pairs, backward=False):
+        """hist_fill_batch_results: the likelihoods of fills enqueued with fill_batch_async (waits for the stream)."""
+        n = len(pairs)
+        arr = pairs.arr if isinstance(pairs, HandleBatch) else (C.c_void_p * n)(*[p.h for p in pairs])
+        lp_end = np.empty(n)
+        lp_start = np.empty(n) if backward else None
+        self.check(self.lib.hist_fill_batch_results(self.h, arr, n, int(backward), _p(lp_end, C.c_double), _p(lp_start, C.c_double)))
+        return lp_end, lp_start
 
     def fill_batch(self, pairs, backward=False):
         n = len(pairs)

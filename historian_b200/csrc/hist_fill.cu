@@ -2014,6 +2014,29 @@ int launch_fill(hist_ctx* ctx, hist_pair* const* pairs_in, int n_in, int n_dir, 
 
 }  // namespace
 
+// likelihoods of filled pairs: the scalar blocks (4 doubles) of pairs prepared in one batch are contiguous, so consecutive
+// pairs come back in one transfer; waits for the context's stream
+static int read_likelihoods(hist_ctx* ctx, hist_pair* const* pairs, int32_t n, int do_backward, double* lp_end, double* lp_start) {
+  std::vector<double> tmp(4 * (size_t)n);
+  for (int k = 0; k < n;) {
+    int e = k + 1;
+    while (e < n && pairs[e]->dev.lp_end == pairs[e - 1]->dev.lp_end + 4) ++e;
+    HB_CUDA(ctx, cudaMemcpyAsync(&tmp[4 * (size_t)k], pairs[k]->dev.lp_end, (size_t)(e - k) * 4 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    k = e;
+  }
+  HB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  for (int k = 0; k < n; ++k) {
+    pairs[k]->fwd_done = true;
+    pairs[k]->lp_end = lp_end[k] = tmp[4 * (size_t)k];
+    if (do_backward) {
+      pairs[k]->bwd_done = true;
+      pairs[k]->lp_start = tmp[4 * (size_t)k + 1];
+      if (lp_start) lp_start[k] = tmp[4 * (size_t)k + 1];
+    }
+  }
+  return HIST_OK;
+}
+
 extern "C" int hist_fill_batch(hist_ctx* ctx, hist_pair* const* pairs, int32_t n, int do_backward, double* lp_end, double* lp_start) {
   if (!ctx || !pairs || n <= 0) return set_err(ctx, HIST_ERR_ARG, "hist_fill_batch: bad arguments");
   cudaSetDevice(ctx->device);
@@ -2033,26 +2056,16 @@ extern "C" int hist_fill_batch(hist_ctx* ctx, hist_pair* const* pairs, int32_t n
     }
     return HIST_OK;
   }
-  // likelihoods: the scalar blocks (4 doubles) of pairs prepared in one batch are contiguous, so
-  // consecutive pairs come back in one transfer
-  std::vector<double> tmp(4 * (size_t)n);
-  for (int k = 0; k < n;) {
-    int e = k + 1;
-    while (e < n && pairs[e]->dev.lp_end == pairs[e - 1]->dev.lp_end + 4) ++e;
-    HB_CUDA(ctx, cudaMemcpyAsync(&tmp[4 * (size_t)k], pairs[k]->dev.lp_end, (size_t)(e - k) * 4 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
-    k = e;
-  }
-  HB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  for (int k = 0; k < n; ++k) {
-    pairs[k]->fwd_done = true;
-    pairs[k]->lp_end = lp_end[k] = tmp[4 * (size_t)k];
-    if (do_backward) {
-      pairs[k]->bwd_done = true;
-      pairs[k]->lp_start = tmp[4 * (size_t)k + 1];
-      if (lp_start) lp_start[k] = tmp[4 * (size_t)k + 1];
-    }
-  }
-  return HIST_OK;
+  return read_likelihoods(ctx, pairs, n, do_backward, lp_end, lp_start);
+}
+
+extern "C" int hist_fill_batch_results(hist_ctx* ctx, hist_pair* const* pairs, int32_t n, int do_backward, double* lp_end, double* lp_start) {
+  if (!ctx || !pairs || n <= 0 || !lp_end) return set_err(ctx, HIST_ERR_ARG, "hist_fill_batch_results: bad arguments");
+  cudaSetDevice(ctx->device);
+  for (int k = 0; k < n; ++k)
+    if (!pairs[k] || pairs[k]->ctx != ctx || !pairs[k]->fwd_done || (do_backward && !pairs[k]->bwd_done))
+      return set_err(ctx, HIST_ERR_STATE, "hist_fill_batch_results: pair %d has not been filled on this context", k);
+  return read_likelihoods(ctx, pairs, n, do_backward, lp_end, lp_start);
 }
 
 extern "C" int hist_fwd_fill(hist_pair* pair, double* lp_end) {

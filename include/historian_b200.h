@@ -226,6 +226,11 @@ int hist_bwd_fill(hist_pair* pair, double* lp_start);
  * the context's stream (no read-back, no synchronisation); the matrices are usable by later calls on the same context. */
 int hist_fill_batch(hist_ctx* ctx, hist_pair* const* pairs, int32_t n, int do_backward,
                     double* lp_end, double* lp_start);
+/* The likelihoods of pairs whose fills were enqueued with lp_end == NULL: waits for the context's stream and reads them
+ * back (ForwardMatrix::lpEnd / BackwardMatrix::lpStart()).  With two contexts on one device a caller can prepare the next
+ * batch on one while the other's fills run. */
+int hist_fill_batch_results(hist_ctx* ctx, hist_pair* const* pairs, int32_t n, int do_backward,
+                            double* lp_end, double* lp_start);
 
 /* DPMatrix::cell for every in-envelope cell, in the row-major order of
  * DPMatrix::write (forward.cpp:448-464): lp[k*5+s] = natural-log value of state s

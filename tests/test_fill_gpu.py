@@ -359,3 +359,53 @@ def test_handle_batches_equal_the_object_api(ctx):
         assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
         pb.close()
         lb.close()
+
+
+def test_two_contexts_with_fills_in_flight(ctx):
+    """hist_fill_batch with lp_end == NULL + hist_fill_batch_results, alternating between two contexts on the device (the
+    pipelined end-to-end step of bench.py): same likelihoods as the synchronous call; results of unfilled pairs are refused."""
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    from historian_b200 import capi
+    lg, guide = bench.make_family(3, n_leaves=16)
+    hmm, inputs = bench.cherry_inputs(lg, guide, 8)
+    seqs = bench.cherry_sequences(guide, 8)
+    packed = np.frombuffer(b"".join(seqs), np.uint8).copy()
+    off = np.concatenate([[0], np.cumsum([len(q) for q in seqs])]).astype(np.int64)
+    envs = [e for _, _, e in inputs]
+    other = capi.Context(0)
+    try:
+        lanes = []
+        for c in (ctx, other):
+            leaves = c.upload_sequences(seqs, lg.alphabet, lg.components)
+            lanes.append((c, capi.PrepareBatch(c, leaves[0::2], leaves[1::2], hmm, envs, backward=True), leaves))
+        want = ctx.fill_batch(lanes[0][1].run(), backward=True)
+        jobs = []
+        for k in range(4):
+            c, plan, _ = lanes[k % 2]
+            lb = c.upload_packed(packed, off, lg.alphabet, lg.components)
+            pb = plan.run_batch(lb)
+            if k == 0:
+                with pytest.raises(capi.HistError) as e:
+                    c.fill_results(pb, backward=True)
+                assert e.value.code == -4
+            c.fill_batch_async(pb, backward=True)
+            jobs.append((c, lb, pb))
+            if len(jobs) == 2:
+                c0, lb0, pb0 = jobs.pop(0)
+                got = c0.fill_results(pb0, backward=True)
+                assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
+                pb0.close()
+                lb0.close()
+        c0, lb0, pb0 = jobs.pop(0)
+        got = c0.fill_results(pb0, backward=True)
+        assert np.array_equal(got[0], want[0]) and np.array_equal(got[1], want[1])
+        pb0.close()
+        lb0.close()
+        for _, plan, leaves in lanes:
+            del plan
+            for p in leaves:
+                p.close()
+    finally:
+        other.close()
