@@ -8,7 +8,8 @@
 //
 // Design.  Refinement is a serial chain of such alignments (every move starts from the alignment the previous one
 // produced), so one alignment is one small problem: a preparation kernel premultiplies the child's matrix by the branch's
-// substitution matrix (preMultiply) and sums its insertion scores (calcInsProbs), one CTA then sweeps the anti-diagonals
+// substitution matrix (preMultiply) and sums its insertion scores (calcInsProbs), a second one computes the match scores of
+// every cell of the envelope in parallel (they do not depend on the recurrence), one CTA then sweeps the anti-diagonals
 // x + y of the (xLen + 1) x (yLen + 1) matrix -- Delete comes from (x-1, y) and Insert from (x, y-1) on the previous
 // anti-diagonal, Match from (x-1, y-1) two back -- one thread per cell, one barrier per step, cells outside the envelope
 // written as -inf, and thread 0 walks the traceback with the reference's own candidate order (Match, Insert, Delete; the
@@ -29,6 +30,7 @@ struct BrDev {
   const double* y_emit;    // [yS-1]
   const int* kx;           // [xS] envelope key of every parent position
   const int* ky;           // [yS]
+  const double* lm;        // [xS][yS] logMatch of the cells inside the envelope (x, y > 0), filled by branch_match_kernel
   double lpt[3][4];        // log transProb(src, dest), dest 3 = End
 };
 
@@ -64,23 +66,36 @@ __global__ void branch_prep_kernel(int yLen, int C, int A, const double* __restr
   }
 }
 
-// logMatch (sampler.h:203-205): logInnerProduct over components of the inner products over residues
+// logMatch (sampler.h:203-205): logInnerProduct over components of the inner products over residues, as one
+// max-shifted sum (independent exponentials instead of a dependent chain of two-term log-sum-exps)
 __device__ double br_log_match(const BrDev& B, int x, int y) {
   const double* xv = B.x_pwm + (size_t)(x - 1) * B.C * B.A;
   const double* yv = B.y_sub + (size_t)(y - 1) * B.C * B.A;
-  double lip = -INFINITY;
-  for (int c = 0; c < B.C; ++c) {
-    double v = -INFINITY;
-    for (int i = 0; i < B.A; ++i) v = br_lse(v, xv[c * B.A + i] + yv[c * B.A + i]);
-    lip = br_lse(lip, v);
+  const int n = B.C * B.A;
+  double m = -INFINITY;
+  for (int q = 0; q < n; ++q) {
+    const double v = xv[q] + yv[q];
+    m = m < v ? v : m;
   }
-  return lip;
+  if (m == -INFINITY) return m;
+  double s = 0;
+  for (int q = 0; q < n; ++q) s += exp(xv[q] + yv[q] - m);
+  return m + log(s);
 }
 
 __device__ __forceinline__ bool br_in_env(const BrDev& B, int x, int y) {   // SparseDPMatrix::inEnvelope, sampler.h:146-149
   if (x == 0 || y == 0 || x == B.xS - 1 || y == B.yS - 1 || B.maxd < 0) return true;
   const int d = B.kx[x] - B.ky[y];
   return (d < 0 ? -d : d) <= B.maxd;
+}
+
+// every cell of the envelope at once: the emission scores do not depend on the recurrence
+__global__ void branch_match_kernel(BrDev B, double* __restrict__ lm) {
+  const long long n = (long long)B.xS * B.yS;
+  for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < n; q += (long long)gridDim.x * blockDim.x) {
+    const int x = (int)(q / B.yS), y = (int)(q % B.yS);
+    if (x > 0 && y > 0 && br_in_env(B, x, y)) lm[q] = br_log_match(B, x, y);
+  }
 }
 
 // one CTA; cells [xS][yS][3]; out: lp_end, path (reversed into place by thread 0), path_len (-1: no traceback state found)
@@ -108,7 +123,7 @@ __global__ void __launch_bounds__(1024) branch_viterbi_kernel(BrDev B, double* c
         }
         if (x > 0 && y > 0) {
           const double* s = cells + ((size_t)(x - 1) * yS + y - 1) * 3;
-          M = br_log_match(B, x, y) + br_max3(s[0] + mm, s[1] + im, s[2] + dm);
+          M = B.lm[(size_t)x * yS + y] + br_max3(s[0] + mm, s[1] + im, s[2] + dm);
         }
       }
       double* d = cells + ((size_t)x * yS + y) * 3;
@@ -130,7 +145,7 @@ __global__ void __launch_bounds__(1024) branch_viterbi_kernel(BrDev B, double* c
     const int sx = x - (bx ? 1 : 0), sy = y - (by ? 1 : 0);
     if (sx < 0 || sy < 0) { *path_len = -1; return; }
     double em = 0;
-    if (state == 0) em = (x > 0 && y > 0) ? br_log_match(B, x, y) : -INFINITY;
+    if (state == 0) em = (x > 0 && y > 0) ? B.lm[(size_t)x * yS + y] : -INFINITY;
     else if (state == 1) em = y > 0 ? B.y_emit[y - 1] : -INFINITY;
     const double* s = cells + ((size_t)sx * yS + sy) * 3;
     double best = -INFINITY;
@@ -168,7 +183,7 @@ extern "C" int hist_branch_align(hist_ctx* ctx, const hist_branch_model* model, 
   // host blob: [x_pwm | y_pwm | log_sub | log_ins | log_cw | kx | ky]; device: blob + [y_sub | y_emit | cells | lp_end | path_len | path]
   const size_t o_x = 0, o_y = o_x + up(8 * x_len * CA), o_sub = o_y + up(8 * y_len * CA), o_ins = o_sub + up(8 * CA * A), o_cw = o_ins + up(8 * CA),
                o_kx = o_cw + up(8 * (size_t)C), o_ky = o_kx + up(4 * xS), blob_bytes = o_ky + up(4 * yS);
-  const size_t o_ysub = blob_bytes, o_yemit = o_ysub + up(8 * y_len * CA), o_cells = o_yemit + up(8 * (size_t)y_len + 8), o_lp = o_cells + up(24 * xS * yS),
+  const size_t o_ysub = blob_bytes, o_yemit = o_ysub + up(8 * y_len * CA), o_cells = o_yemit + up(8 * (size_t)y_len + 8), o_lm = o_cells + up(24 * xS * yS), o_lp = o_lm + up(8 * xS * yS),
                o_len = o_lp + 256, o_path = o_len + 256, total = o_path + up(xS + yS);
   std::vector<char> blob(blob_bytes, 0);
   if (x_len) memcpy(blob.data() + o_x, x_pwm, 8 * x_len * CA);
@@ -196,6 +211,13 @@ extern "C" int hist_branch_align(hist_ctx* ctx, const hist_branch_model* model, 
     B.kx = (const int*)(d + o_kx); B.ky = (const int*)(d + o_ky);
     for (int s = 0; s < 3; ++s)
       for (int t = 0; t < 4; ++t) B.lpt[s][t] = model->lp_trans[s][t];
+    B.lm = (const double*)(d + o_lm);
+    {
+      const long long cells = (long long)xS * yS;
+      const int blocks = (int)std::min<long long>((cells + 127) / 128, 148 * 16);
+      branch_match_kernel<<<blocks, 128, 0, ctx->stream>>>(B, (double*)(d + o_lm));
+      ctx->launches += 1;
+    }
     const int threads = (int)std::min<size_t>(1024, (std::min(xS, yS) + 31) / 32 * 32);
     branch_viterbi_kernel<<<1, threads, 0, ctx->stream>>>(B, (double*)(d + o_cells), (double*)(d + o_lp), (unsigned char*)(d + o_path), (int*)(d + o_len));
     ctx->launches += 1;
