@@ -248,8 +248,13 @@ int main(int argc, char** argv) {
   recon.generator.seed(recon.rndSeed);
 
   vguard<gsl_vector*> rootProb = model.insProb;
+  // REF_DUMP_COUNTS=2: the profiling strategy of `historian fit` on unaligned sequences (recon.cpp:925-930 with
+  // accumulateSubstCounts and accumulateIndelCounts): every profile transition carries the EigenCounts of the paths it sums
+  // over (forward.cpp:753-790), and getCounts at the root reads them (forward.cpp:1183-1214).
+  const bool propagate = getenv("REF_DUMP_COUNTS") != NULL && string(getenv("REF_DUMP_COUNTS")) == "2";
   const int strategy = ForwardMatrix::CollapseChains | (recon.keepGapsOpen ? ForwardMatrix::KeepGapsOpen : 0) |
-                       (recon.includeBestTraceInProfile ? ForwardMatrix::IncludeBestTrace : 0);
+                       (recon.includeBestTraceInProfile ? ForwardMatrix::IncludeBestTrace : 0) |
+                       (propagate ? (ForwardMatrix::CountSubstEvents | ForwardMatrix::CountIndelEvents) : 0);
   putI("strategy", {strategy});
   putS("alphabet", model.alphabet);
   putI("profile_samples", {(int32_t)recon.profileSamples});
@@ -352,6 +357,25 @@ int main(int argc, char** argv) {
           for (size_t s = 0; s < p.size(); ++s)
             for (const auto& rc : p.alignColumn(s)) cols[s * N + rc.first] = (uint8_t)rc.second;
           putB(pfx + (side ? "y." : "x.") + "align_col", cols, {(uint64_t)p.size(), (uint64_t)N});
+          if (propagate) {   // the counts every transition of the child profile carries: indel slots, then the transformed event counts
+            const int C = model.components(), A = model.alphabetSize();
+            vector<double> tIndel, tRoot, tSub;
+            for (const auto& t : p.trans) {
+              EigenCounts ec = t.counts;
+              if (ec.rootCount.empty()) ec = EigenCounts(C, A) + ec;   // a transition without substitution counts
+              const IndelCounts& ic = ec.indelCounts;
+              for (double v : {ic.ins, ic.del, ic.insExt, ic.delExt, ic.insTime, ic.delTime, ic.lp}) tIndel.push_back(v);
+              const EventCounts ev = ec.transform(model);
+              for (int c = 0; c < C; ++c)
+                for (int i = 0; i < A; ++i) {
+                  tRoot.push_back(ev.rootCount[c][i]);
+                  for (int j = 0; j < A; ++j) tSub.push_back(ev.subCount[c][i][j]);
+                }
+            }
+            putD(pfx + (side ? "y." : "x.") + "trans_indel", tIndel, {(uint64_t)p.trans.size(), 7});
+            putD(pfx + (side ? "y." : "x.") + "trans_root_count", tRoot, {(uint64_t)p.trans.size(), (uint64_t)C, (uint64_t)A});
+            putD(pfx + (side ? "y." : "x.") + "trans_sub_count", tSub, {(uint64_t)p.trans.size(), (uint64_t)C, (uint64_t)A, (uint64_t)A});
+          }
         }
         const EigenCounts ec = backward->getCounts();
         const EventCounts ev = ec.transform(model);

@@ -24,7 +24,7 @@ import helpers as H
 from historian_b200 import capi, descs as D, fbcounts, model as M
 
 pytestmark = pytest.mark.gpu
-ALL = sorted(glob.glob(os.path.join(H.GOLDEN_DIR, "fbcounts_*.npz")))
+ALL = sorted(f for f in glob.glob(os.path.join(H.GOLDEN_DIR, "fbcounts_*.npz")) if "_prop_" not in os.path.basename(f))   # fbcounts_prop_*: tests/test_fbcounts_host.py
 FIX = [f for f in ALL if "_tree" not in os.path.basename(f)]         # two leaf profiles
 IDS = [os.path.basename(f)[9:-4] for f in FIX]
 TREES = [f for f in ALL if "_tree" in os.path.basename(f)]           # root merge of a progressive reconstruction

@@ -44,3 +44,34 @@ def test_prob_model_waits_order():
         def __init__(self, t, i, d):
             self.t, self.insWait, self.delWait = t, i, d
     assert list(F.prob_model_waits(P(1, 2, 3), P(4, 5, 6))) == [1, 4, 2, 3, 5, 6]
+
+
+def test_count_propagation_fixtures_state_the_open_target():
+    """tests/golden/fbcounts_prop_*.npz (tools/make_golden_fbcounts.py, REF_DUMP_COUNTS=2): the reference's getCounts at the
+    root of a reconstruction made WITH CountSubstEvents | CountIndelEvents, i.e. with counts carried by the transitions of
+    the internal profiles (forward.cpp:753-790) -- the part of row B3 the library does not build yet (DESIGN.md section 7,
+    item 1).  Nothing on the device is compared here; the test pins what the fixtures hold so that the target cannot rot:
+    the children's transitions carry counts, and the root's totals contain the whole subtree's events, not only the root
+    merge's (the count-free fixtures of the same runs)."""
+    import glob
+    import os
+    import helpers as H
+    props = sorted(glob.glob(os.path.join(H.GOLDEN_DIR, "fbcounts_prop_*.npz")))
+    assert len(props) == 4
+    for path in props:
+        d = H.load_golden(path)
+        base = H.load_golden(path.replace("fbcounts_prop_", "fbcounts_"))
+        root = int(d["root"][0])
+        pfx = "n%d." % root
+        assert np.array_equal(d[pfx + "x.trans_src"], base[pfx + "x.trans_src"])          # same reconstruction
+        assert d[pfx + "lp_end"][0] == base[pfx + "lp_end"][0]
+        for side in ("x.", "y."):
+            nt = int(d[pfx + side + "dims"][1])
+            ti, ts = d[pfx + side + "trans_indel"], d[pfx + side + "trans_sub_count"]
+            assert ti.shape == (nt, 7) and ts.shape[0] == nt
+            assert np.all(ti[:, :6] >= 0) and ti[:, :6].sum() > 0                            # transitions carry indel counts
+            assert np.all(np.isfinite(ts))     # substitution counts only where a path eliminated an inserted column
+        pi, bi = d[pfx + "fbc.indel"], base[pfx + "fbc.indel"]
+        assert pi[6] == bi[6]                                                                # lp = the root's Forward likelihood
+        assert np.all(pi[:6] >= bi[:6] - 1e-9) and pi[4] > bi[4] and pi[5] > bi[5]           # wait times of every branch, not two
+        assert d[pfx + "fbc.sub_count"].sum() >= base[pfx + "fbc.sub_count"].sum() - 1e-9

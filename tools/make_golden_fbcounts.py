@@ -37,16 +37,20 @@ TREE_CASES = [
 KEEP = ("x.", "y.", "hmm.", "env.", "fbc.")
 
 
-def tree_cases(sfx=""):
+def tree_cases(sfx="", propagate=False):
+    """propagate: REF_DUMP_COUNTS=2, the strategy of `historian fit` on unaligned sequences (CountSubstEvents | CountIndelEvents):
+    every transition of the internal profiles carries counts (forward.cpp:753-790) and getCounts reads them -- the fixtures
+    fbcounts_prop_* of the part of row B3 that is not built yet."""
     import make_golden as G
     for name, n, bl, spec, gen, rec in TREE_CASES:
+        name = name.replace("fbcounts_", "fbcounts_prop_") if propagate else name
         name += sfx
         with tempfile.TemporaryDirectory() as tmp:
             tf, gf = G.simulate(tmp, G.balanced(n, bl), gen, n)
             binf = os.path.join(tmp, "d.bin")
             root = 2 * n - 2
             subprocess.run([os.path.join(BIN, "ref_dump" + sfx), binf, str(root), "sample", "-guide", gf, "-tree", tf] + rec, check=True,
-                           cwd=G.REF, env=dict(os.environ, REF_DUMP_COUNTS="1"), stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+                           cwd=G.REF, env=dict(os.environ, REF_DUMP_COUNTS="2" if propagate else "1"), stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
             d = D.read_dump(binf)
         pfx = "n%d." % root
         out = {"preset": spec, "root": np.array([root], np.int32)}
@@ -63,6 +67,7 @@ def main(sfx=""):
     """sfx "": the reference as shipped (table log-sum-exp); "_exact": the same sources compiled with the reference's own
     -DLOG_SUM_EXP_SLOW switch (oracle/Makefile ref_exact) -> tests/golden/fbcounts_*_exact.npz, exact arithmetic."""
     tree_cases(sfx)
+    tree_cases(sfx, propagate=True)
     for name, spec, gen, (tl, tr), band in CASES:
         name += sfx
         with tempfile.TemporaryDirectory() as tmp:
