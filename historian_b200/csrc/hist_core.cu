@@ -179,22 +179,25 @@ __global__ void leaf_scatter_kernel(PairDev* const* __restrict__ pairs) {
   const SideDev& s = blockIdx.z == 1 ? P.y : P.x;
   if (!s.tokens) return;
   const int K = P.K, Kp = P.Kp, A = P.A, n = s.n;
-  const long long total = (long long)n * max(K, Kp);
-  for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total; e += (long long)gridDim.x * blockDim.x) {
+  const unsigned total = (unsigned)n * (unsigned)max(K, Kp);   // the host keeps n * max(K, Kp) below 2^31 for token sides
+  const unsigned nK = (unsigned)n * (unsigned)K, nKp = (unsigned)n * (unsigned)Kp;
+  for (unsigned e = blockIdx.x * blockDim.x + threadIdx.x; e < total; e += gridDim.x * blockDim.x) {
     auto token_class = [&](int i) {   // -1: START / END (the null-state rows of prepare_side_kernel)
       if (i == 0 || i == n - 1) return -1;
       const int q = s.tokens[i - 1];
       return q < 0 || q >= A ? A : q;
     };
-    if (e < (long long)n * K) {
-      const int i = (int)(e / K), k = (int)(e - (long long)i * K), q = token_class(i);
+    if (e < nK) {
+      const unsigned i = e / (unsigned)K, k = e - i * (unsigned)K;
+      const int q = token_class((int)i);
       s.sub[e] = q < 0 ? -INFINITY : s.tk_sub[(size_t)q * K + k];
     }
-    if (e < (long long)n * Kp) {
-      const int i = (int)(e / Kp), k = (int)(e - (long long)i * Kp), q = token_class(i);
+    if (e < nKp) {
+      const unsigned i = e / (unsigned)Kp, k = e - i * (unsigned)Kp;
+      const int q = token_class((int)i);
       s.H[e] = q < 0 ? 0.f : s.tk_H[(size_t)q * Kp + k];
     }
-    if (e < n) {
+    if (e < (unsigned)n) {
       const int i = (int)e, q = token_class(i);
       s.ex[i] = q < 0 ? 0 : s.tk_ex[q];
       s.rs[i] = q < 0 ? 1.f : s.tk_rs[q];
@@ -899,25 +902,38 @@ void arena_release(hist_ctx* ctx, hb_arena* a);
 namespace hb {
 // lpAbsorb of leaf profiles (profile.cpp:52-66): state 0 and END are null (rows unused, kept -inf), state pos+1
 // is 0 at the residue's token and -inf elsewhere, or all 0 for a wildcard / invalid character.
-// One thread per (state, component, residue) of the concatenated batch.
+// grid = (chunks, sequences): a block row walks the [states][C][A] elements of ITS sequence in order (coalesced stores,
+// 32-bit index arithmetic, no search for the owning sequence).
 __global__ void leaf_absorb_kernel(const int8_t* tokens, const long long* state_off, int n_seq, int C, int A, double* lp) {
-  const long long total = state_off[n_seq] * C * A;
-  for (long long q = blockIdx.x * (long long)blockDim.x + threadIdx.x; q < total; q += (long long)gridDim.x * blockDim.x) {
-    const int a = q % A;
-    const long long st = q / ((long long)C * A);  // global state index
-    // sequence of this state: binary search in state_off
-    int lo = 0, hi = n_seq;
-    while (hi - lo > 1) {
-      const int mid = (lo + hi) >> 1;
-      if (state_off[mid] <= st) lo = mid; else hi = mid;
+  const int K = C * A;
+  for (int s = blockIdx.y; s < n_seq; s += gridDim.y) {
+    const long long s0 = state_off[s];
+    const long long n_states = state_off[s + 1] - s0, total = n_states * K;
+    const int8_t* tk = tokens + (s0 - 2LL * s);   // token of local state i (1 .. n_states - 2) is tk[i - 1]: minus the START/END rows before it
+    double* out = lp + s0 * K;
+    if (total < (1LL << 31)) {
+      const unsigned tot = (unsigned)total, uK = (unsigned)K, uA = (unsigned)A, last = (unsigned)n_states - 1;
+      for (unsigned q = blockIdx.x * blockDim.x + threadIdx.x; q < tot; q += gridDim.x * blockDim.x) {
+        const unsigned i = q / uK, a = (q - i * uK) % uA;
+        double v = -INFINITY;
+        if (i > 0 && i < last) {
+          const int tok = tk[i - 1];
+          v = (tok < 0 || tok == (int)a) ? 0.0 : -INFINITY;
+        }
+        out[q] = v;
+      }
+    } else {
+      for (long long q = blockIdx.x * (long long)blockDim.x + threadIdx.x; q < total; q += (long long)gridDim.x * blockDim.x) {
+        const long long i = q / K;
+        const int a = (int)((q - i * K) % A);
+        double v = -INFINITY;
+        if (i > 0 && i < n_states - 1) {
+          const int tok = tk[i - 1];
+          v = (tok < 0 || tok == a) ? 0.0 : -INFINITY;
+        }
+        out[q] = v;
+      }
     }
-    const long long local = st - state_off[lo], n_states = state_off[lo + 1] - state_off[lo];
-    double v = -INFINITY;
-    if (local > 0 && local < n_states - 1) {
-      const int tok = tokens[st - 2 * lo - 1];  // token index = global state index minus the START/END rows before it
-      v = (tok < 0 || tok == a) ? 0.0 : -INFINITY;
-    }
-    lp[q] = v;
   }
 }
 }  // namespace hb
@@ -966,9 +982,10 @@ static int leaf_profiles(hist_ctx* ctx, int32_t n, const int8_t* const* tokens, 
     if (!rc) rc = check_cuda(ctx, cudaEventRecord(ctx->ev_stage[0], ctx->stream), "record staging event");
   }
   if (!rc) {
-    const long long work = state_off[n] * (long long)K;
-    const int blocks = (int)std::max<long long>(1, std::min<long long>((work + 255) / 256, (long long)ctx->sm_count * 16));
-    hb::leaf_absorb_kernel<<<blocks, 256, 0, ctx->stream>>>((const int8_t*)(arena->dev + tok_off), (const long long*)(arena->dev + so_off), n,
+    long long longest = 1;
+    for (int k = 0; k < n; ++k) longest = std::max(longest, state_off[k + 1] - state_off[k]);
+    const int chunks = (int)std::max<long long>(1, std::min<long long>((longest * K + 1023) / 1024, 64));   // ~4 elements per thread
+    hb::leaf_absorb_kernel<<<dim3(chunks, std::min(n, 65535)), 256, 0, ctx->stream>>>((const int8_t*)(arena->dev + tok_off), (const long long*)(arena->dev + so_off), n,
                                                            components, alph_size, (double*)arena->dev);
     ctx->launches += 1;
     rc = check_cuda(ctx, cudaGetLastError(), "leaf_absorb_kernel");
@@ -1363,7 +1380,8 @@ int plan_pair(hist_ctx* ctx, const hist_profile* x, const hist_profile* y, const
     o.d_ao_edges = Dv.reserve(nt1 * 2 * sizeof(int4));
     o.d_no_edges = Dv.reserve(nt1 * 2 * sizeof(int4));
     // a leaf the library built from residues (and not a codon batch, whose leftMultiply runs on the tensor cores)
-    o.tok = p->d_tokens != nullptr && p->chain && p->n >= 3 && !leftmul_tc_applicable(A, C);
+    o.tok = p->d_tokens != nullptr && p->chain && p->n >= 3 && !leftmul_tc_applicable(A, C) &&
+            (long long)p->n * (C * A + 8) < (1LL << 31);   // leaf_scatter_kernel indexes a side's arrays with 32 bits
     if (o.tok) {
       const size_t rows = (size_t)A + 1;
       o.k_sub = Dv.reserve(rows * K * sizeof(double));
