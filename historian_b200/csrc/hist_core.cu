@@ -1892,7 +1892,8 @@ int prepare_enqueue(hist_ctx* ctx, int32_t n, const hist_profile* const* xs, con
       } else {
         prepare_side_kernel<false, true><<<dim3(maxA + 1, n, 2), threads, (size_t)stride * sizeof(double), ctx->stream>>>(dptrs, stride);
       }
-      leaf_scatter_kernel<<<dim3((unsigned)std::min<long long>(((long long)maxN * maxKp + 255) / 256, 64), n, 2), 256, 0, ctx->stream>>>(dptrs);
+      // ~8 elements per thread: the per-block cost (the PairDev record, the side's pointers) is paid 10 times per side, not 64
+      leaf_scatter_kernel<<<dim3((unsigned)std::max<long long>(1, std::min<long long>(((long long)maxN * maxKp + 2047) / 2048, 64)), n, 2), 256, 0, ctx->stream>>>(dptrs);
       ctx->launches += 2;
     }
     prepare_trans_kernel<<<dim3((maxNt + 127) / 128, n, 2), 128, 0, ctx->stream>>>(dptrs);
