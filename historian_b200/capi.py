@@ -51,6 +51,8 @@ def load():
     lib.hist_sumprod_excluded_posteriors.argtypes = [vp, C.c_char_p, C.c_int64, C.c_int32, D.c_int32_p, D.c_int32_p, C.c_int32, D.c_double_p]
     lib.hist_branch_align.argtypes = [vp, C.POINTER(D.BranchModel), C.c_int32, D.c_double_p, C.c_int32, D.c_double_p, C.c_int32, D.c_int32_p,
                                       D.c_int32_p, D.c_double_p, C.POINTER(C.c_uint8), D.c_int32_p]
+    lib.hist_diagonal_envelope.argtypes = [vp, C.POINTER(C.c_int8), C.c_int32, C.POINTER(C.c_int8), C.c_int32, C.c_int32, C.POINTER(D.GuideParams),
+                                           D.c_int32_p, C.c_int32, D.c_int32_p]
     lib.hist_ctx_h2d_bytes.argtypes = [vp]
     lib.hist_ctx_h2d_bytes.restype = C.c_int64
     lib.hist_ctx_set_timing.argtypes = [vp, C.c_int]
@@ -354,6 +356,18 @@ class Context:
         lp_start = np.empty(n) if backward else None
         self.check(self.lib.hist_fill_batch(self.h, arr, n, int(backward), _p(lp_end, C.c_double), _p(lp_start, C.c_double)))
         return lp_end, lp_start
+
+
+def diagonal_envelope(x_tok, y_tok, alph_size, sparse=True, kmer_len=6, kmer_threshold=-1, band_size=64, cell_size=40, max_size=0, lib=None):
+    """DiagonalEnvelope::initFull / initSparse (diagenv.cpp:93-190) on the host: hist_diagonal_envelope.  Returns the ascending diagonals."""
+    lib = lib or load()
+    x, y = np.ascontiguousarray(x_tok, np.int8), np.ascontiguousarray(y_tok, np.int8)
+    gp = D.GuideParams(0, 0, int(bool(sparse)), int(kmer_len), int(kmer_threshold), int(band_size), int(cell_size), 0, int(max_size))
+    out, n = np.zeros(len(x) + len(y) - 1, np.int32), np.zeros(1, np.int32)
+    rc = lib.hist_diagonal_envelope(None, _p(x, C.c_int8), len(x), _p(y, C.c_int8), len(y), int(alph_size), C.byref(gp), _p(out, C.c_int32), len(out), _p(n, C.c_int32))
+    if rc:
+        raise HistError(rc, (lib.hist_last_error(None) or b"").decode())
+    return out[:int(n[0])].copy()
 
 
 def align_path_merge(alignments, row_lengths, lib=None):

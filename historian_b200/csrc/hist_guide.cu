@@ -416,3 +416,20 @@ extern "C" int hist_guide_align(hist_ctx* ctx, int32_t n_seqs, const int8_t* tok
   *n_cols = (int32_t)cols;
   return HIST_OK;
 }
+
+extern "C" int hist_diagonal_envelope(hist_ctx* ctx, const int8_t* x_tok, int32_t x_len, const int8_t* y_tok, int32_t y_len, int32_t alph_size,
+                                      const hist_guide_params* params, int32_t* diagonals, int32_t capacity, int32_t* n_diagonals) {
+  if (!x_tok || !y_tok || x_len < 1 || y_len < 1 || alph_size < 1 || !params || !n_diagonals)
+    return set_err(ctx, HIST_ERR_ARG, "hist_diagonal_envelope: bad arguments");
+  if (params->sparse && (params->kmer_len < 1 || params->kmer_len > 32)) return set_err(ctx, HIST_ERR_ARG, "hist_diagonal_envelope: kmer_len %d out of range", params->kmer_len);
+  std::vector<int> d;
+  envelope_diagonals(x_tok, x_len, y_tok, y_len, alph_size, *params, d);
+  if (d.empty()) {   // the full envelope
+    d.resize((size_t)x_len + y_len - 1);
+    std::iota(d.begin(), d.end(), 1 - y_len);
+  }
+  *n_diagonals = (int32_t)d.size();
+  if (!diagonals || capacity < *n_diagonals) return set_err(ctx, HIST_ERR_CAPACITY, "hist_diagonal_envelope: need room for %d diagonals", *n_diagonals);
+  for (size_t k = 0; k < d.size(); ++k) diagonals[k] = d[k];
+  return HIST_OK;
+}

@@ -477,6 +477,12 @@ int hist_guide_align(hist_ctx* ctx, int32_t n_seqs, const int8_t* tokens, const 
                      const hist_guide_params* params, int32_t* residue_col, int32_t* n_cols, int32_t* n_edges, int32_t* edge_rows,
                      double* edge_lp, int64_t edge_capacity, int32_t* mst_edges);
 
+/* DiagonalEnvelope::initFull / initSparse (diagenv.cpp:93-190) of one pair, host only: the ascending diagonals i - j that
+ * hist_guide_align hands to the pairwise alignment (params: the DiagEnvParams part of hist_guide_params).  capacity
+ * x_len + y_len - 1 always suffices.  ctx may be NULL. */
+int hist_diagonal_envelope(hist_ctx* ctx, const int8_t* x_tok, int32_t x_len, const int8_t* y_tok, int32_t y_len, int32_t alph_size,
+                           const hist_guide_params* params, int32_t* diagonals, int32_t capacity, int32_t* n_diagonals);
+
 /* alignPathMerge (alignpath.cpp:153-207) on the host: merges alignments that share rows into one.  Alignment k has
  * n_rows[k] rows (their global indices consecutive in `rows`) and n_cols[k] columns, its 0/1 matrix row-major and
  * consecutive in `bits`; row r of the result has row_off[r + 1] - row_off[r] residues (every alignment mentioning the row

@@ -145,3 +145,25 @@ def test_full_envelope_without_the_diagonal_list(ctx):
         pr = (D.QuickAlignPair * 1)(D.QuickAlignPair(len(x), len(y), x.ctypes.data_as(C.POINTER(C.c_int8)), y.ctypes.data_as(C.POINTER(C.c_int8)), 5, None))
         r = np.zeros(1)
         ctx.check(ctx.lib.hist_quickalign_batch(ctx.h, 1, pr, C.byref(sc), r.ctypes.data_as(C.POINTER(C.c_double)), None, None, None, None, None))
+
+
+@pytest.mark.parametrize("name,band,klen,thr", [("quickalign_lg8x300_sparse", 16, 5, 2), ("quickalign_jc5x200_sparse", 8, 6, 1), ("quickalign_lg6x120_full", 64, 6, -1)])
+def test_library_envelopes_equal_the_reference(name, band, klen, thr):
+    """DiagonalEnvelope::initSparse / initFull in the library's host code (hist_diagonal_envelope, what hist_guide_align builds per
+    pair) against the diagonals the reference built for the fixtures' pairs; and against the Python host restatement
+    (guide.sparse_envelope).  No device work."""
+    from historian_b200 import capi, guide
+    d = H.load_golden(os.path.join(H.GOLDEN_DIR, name + ".npz"))
+    A = int(round(np.sqrt(len(d["submat"]))))
+    for k, (x, y, want), *_ in cases(d):
+        # threshold -1 with a memory limit above xLen * yLen * cellSize: the full envelope, the reference's default
+        got = capi.diagonal_envelope(x, y, A, sparse=True, kmer_len=klen, kmer_threshold=thr, band_size=band, cell_size=40, max_size=1 << 40)
+        assert np.array_equal(got, want), k
+        if thr >= 0:
+            assert np.array_equal(guide.sparse_envelope(x, y, A, kmer_len=klen, band=band, threshold=thr), want), k
+    # memory-bounded threshold (-kmatchmb): shrinking the limit can only drop seeded diagonals, diagonal 0 always stays
+    _, (x, y, _), *_ = next(iter(cases(d)))
+    sizes = [len(capi.diagonal_envelope(x, y, A, sparse=True, kmer_len=5, kmer_threshold=-1, band_size=8, cell_size=40, max_size=m))
+             for m in (0, 20000, 200000, 2000000, 1 << 40)]
+    assert sizes[0] == 1 and sizes == sorted(sizes) and sizes[-1] == len(x) + len(y) - 1
+    assert 0 in capi.diagonal_envelope(x, y, A, sparse=True, kmer_len=5, kmer_threshold=-1, band_size=8, cell_size=40, max_size=20000)
