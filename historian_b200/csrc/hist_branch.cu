@@ -179,6 +179,10 @@ extern "C" int hist_branch_align(hist_ctx* ctx, const hist_branch_model* model, 
   if (A < 1 || C < 1 || !model->log_sub || !model->log_ins || !model->log_cpt_weight) return set_err(ctx, HIST_ERR_ARG, "hist_branch_align: bad model");
   cudaSetDevice(ctx->device);
   const size_t CA = (size_t)C * A, xS = (size_t)x_len + 1, yS = (size_t)y_len + 1;
+  // the matrix is stored whole (3 scores + 1 match score per cell): 32 bytes x (xLen + 1) x (yLen + 1)
+  if ((double)xS * (double)yS * 32.0 > 64.0 * 1024 * 1024 * 1024)
+    return set_err(ctx, HIST_ERR_CAPACITY, "hist_branch_align: a %d x %d matrix needs %.1f GB of device memory (limit 64 GB)", x_len, y_len,
+                   (double)xS * (double)yS * 32.0 / (1024.0 * 1024 * 1024));
   auto up = [](size_t v) { return (v + 255) / 256 * 256; };
   // host blob: [x_pwm | y_pwm | log_sub | log_ins | log_cw | kx | ky]; device: blob + [y_sub | y_emit | cells | lp_end | path_len | path]
   const size_t o_x = 0, o_y = o_x + up(8 * x_len * CA), o_sub = o_y + up(8 * y_len * CA), o_ins = o_sub + up(8 * CA * A), o_cw = o_ins + up(8 * CA),
