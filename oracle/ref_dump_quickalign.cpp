@@ -5,7 +5,7 @@
 // envelope diagonals, the score table the constructor derives) and the results (score, end cell, alignment path).
 // tools/make_golden_quickalign.py turns the dump into tests/golden/quickalign_*.npz.
 //
-//   ref_dump_quickalign <out.bin> <preset> <seqs.fa> <time> full | sparse:<band>:<kmerLen>:<kmerThreshold>
+//   ref_dump_quickalign <out.bin> <preset> <seqs.fa> <time> full | sparse:<band>:<kmerLen>:<kmerThreshold>[:<maxSize>]
 #include <chrono>
 #include <cstdint>
 #include <cstdio>
@@ -51,8 +51,9 @@ int main(int argc, char** argv) {
   const double time = atof(argv[4]);
   const string mode = argv[5];
   int band = 0, kmerLen = 0, kmerThreshold = 0;
+  long long maxSize = 0;   // optional fourth field: the memory limit of the kmerThreshold < 0 branch (-kmatchmb), cell size 40
   const bool sparse = mode != "full";
-  if (sparse && sscanf(mode.c_str(), "sparse:%d:%d:%d", &band, &kmerLen, &kmerThreshold) != 3) {
+  if (sparse && sscanf(mode.c_str(), "sparse:%d:%d:%d:%lld", &band, &kmerLen, &kmerThreshold, &maxSize) < 3) {
     cerr << "bad mode " << mode << endl;
     return 1;
   }
@@ -65,7 +66,7 @@ int main(int argc, char** argv) {
       DiagonalEnvelope env(seqs[a], seqs[b]);
       if (sparse) {
         KmerIndex yKmerIndex(seqs[b], model.alphabet, kmerLen);
-        env.initSparse(yKmerIndex, band, kmerThreshold, 3 * sizeof(double), 0);
+        env.initSparse(yKmerIndex, band, kmerThreshold, maxSize > 0 ? 40 : 3 * sizeof(double), (size_t)maxSize);
       } else
         env.initFull();
       const auto t0 = chrono::steady_clock::now();

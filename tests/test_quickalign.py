@@ -147,8 +147,9 @@ def test_full_envelope_without_the_diagonal_list(ctx):
         ctx.check(ctx.lib.hist_quickalign_batch(ctx.h, 1, pr, C.byref(sc), r.ctypes.data_as(C.POINTER(C.c_double)), None, None, None, None, None))
 
 
-@pytest.mark.parametrize("name,band,klen,thr", [("quickalign_lg8x300_sparse", 16, 5, 2), ("quickalign_jc5x200_sparse", 8, 6, 1), ("quickalign_lg6x120_full", 64, 6, -1)])
-def test_library_envelopes_equal_the_reference(name, band, klen, thr):
+@pytest.mark.parametrize("name,band,klen,thr,limit", [("quickalign_lg8x300_sparse", 16, 5, 2, 1 << 40), ("quickalign_jc5x200_sparse", 8, 6, 1, 1 << 40),
+                                                      ("quickalign_lg6x120_full", 64, 6, -1, 1 << 40), ("quickalign_lg6x250_kmatchmb", 12, 5, -1, 400000)])
+def test_library_envelopes_equal_the_reference(name, band, klen, thr, limit):
     """DiagonalEnvelope::initSparse / initFull in the library's host code (hist_diagonal_envelope, what hist_guide_align builds per
     pair) against the diagonals the reference built for the fixtures' pairs; and against the Python host restatement
     (guide.sparse_envelope).  No device work."""
@@ -157,7 +158,8 @@ def test_library_envelopes_equal_the_reference(name, band, klen, thr):
     A = int(round(np.sqrt(len(d["submat"]))))
     for k, (x, y, want), *_ in cases(d):
         # threshold -1 with a memory limit above xLen * yLen * cellSize: the full envelope, the reference's default
-        got = capi.diagonal_envelope(x, y, A, sparse=True, kmer_len=klen, kmer_threshold=thr, band_size=band, cell_size=40, max_size=1 << 40)
+        # (kmatchmb: -1 with a limit BELOW it: the largest set of seeded bands whose storage diagonals fit, diagenv.cpp:158-186)
+        got = capi.diagonal_envelope(x, y, A, sparse=True, kmer_len=klen, kmer_threshold=thr, band_size=band, cell_size=40, max_size=limit)
         assert np.array_equal(got, want), k
         if thr >= 0:
             assert np.array_equal(guide.sparse_envelope(x, y, A, kmer_len=klen, band=band, threshold=thr), want), k

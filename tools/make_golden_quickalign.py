@@ -49,6 +49,8 @@ CASES = [
     ("quickalign_lg6x120_full", "lg", None, 1.0, "full", dict(n=6, bl=0.15, rootlen=120, seed=3, extra=["-insrate", "0.05", "-delrate", "0.05"])),
     ("quickalign_lg8x300_sparse", "lg", None, 1.0, "sparse:16:5:2", dict(n=8, bl=0.05, rootlen=300, seed=5, extra=["-insrate", "0.03", "-delrate", "0.03"])),
     ("quickalign_jc5x200_sparse", "jc", None, 0.5, "sparse:8:6:1", dict(n=5, bl=0.1, rootlen=200, seed=7, extra=["-insrate", "0.04", "-delrate", "0.04"])),
+    # the memory-bounded threshold (-kmatchmb): kmerThreshold -1, the largest set of seeded bands that fits 400 kB at 40 B per cell
+    ("quickalign_lg6x250_kmatchmb", "lg", None, 1.0, "sparse:12:5:-1:400000", dict(n=6, bl=0.05, rootlen=250, seed=21, extra=["-insrate", "0.03", "-delrate", "0.03"])),
 ]
 
 
