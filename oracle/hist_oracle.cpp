@@ -758,6 +758,165 @@ int oracle_posterior_cells(const hist_profile_desc* x, const hist_profile_desc* 
   return 0;
 }
 
+// Indel part of ForwardMatrix::transitionEigenCounts (forward.cpp:579-652): c[6] = ins, del, insExt, delExt, insTime, delTime.
+// x_tc / y_tc: [n_trans][6] counts of the children's transitions or NULL; waits = l.t, r.t, l.insWait, l.delWait, r.insWait, r.delWait.
+static void indel_transition_counts(const DP& dp, const CellCoords& src, const CellCoords& dest, const double* x_tc, const double* y_tc,
+                                    const double* waits, double* c) {
+  enum { INS, DEL, INSEXT, DELEXT, INSTIME, DELTIME };
+  const double lt = waits[0], rt = waits[1], lInsWait = waits[2], lDelWait = waits[3], rInsWait = waits[4], rDelWait = waits[5];
+  for (int q = 0; q < 6; ++q) c[q] = 0;
+  auto getTrans = [](const Prof& p, int s, int d) {
+    for (int t : p.in[d])
+      if (p.src[t] == s) return t;
+    return -1;
+  };
+  if (src.xpos != dest.xpos && x_tc) {
+    const int t = getTrans(dp.x, src.xpos, dest.xpos);
+    if (t >= 0) for (int q = 0; q < 6; ++q) c[q] += x_tc[(size_t)t * 6 + q];
+  }
+  if (src.ypos != dest.ypos && y_tc) {
+    const int t = getTrans(dp.y, src.ypos, dest.ypos);
+    if (t >= 0) for (int q = 0; q < 6; ++q) c[q] += y_tc[(size_t)t * 6 + q];
+  }
+  if (dest.state == HIST_EEE) return;   // x.state[dest.xpos] is END: no case of the switch applies
+  const bool xNull = dp.x.isNull(dest.xpos), yNull = dp.y.isNull(dest.ypos);
+  const int s = dest.state;
+  switch (s) {   // forward.cpp:586-650
+    case HIST_IMM:
+      if (!xNull && !yNull) {
+        if (src.state == HIST_IMM || src.state == HIST_IMD) { c[INSTIME] += lt; c[DELTIME] += lt; }
+        if (src.state == HIST_IMM || src.state == HIST_IDM) { c[INSTIME] += rt; c[DELTIME] += rt; }
+      }
+      break;
+    case HIST_IMD:
+      if (!xNull) {
+        if (src.state == HIST_IMM || src.state == HIST_IMD) { c[INSTIME] += lt; c[DELTIME] += lt; }
+        if (src.state == s) c[DELEXT] += 1;
+        else { c[DEL] += 1; c[DELTIME] += rDelWait; }
+      }
+      break;
+    case HIST_IIW:
+      if (!xNull) {
+        if (src.state == s) c[INSEXT] += 1;
+        else { c[INS] += 1; c[INSTIME] += lInsWait; }
+      }
+      break;
+    case HIST_IDM:
+      if (!yNull) {
+        if (src.state == HIST_IMM || src.state == HIST_IDM) { c[INSTIME] += rt; c[DELTIME] += rt; }
+        if (src.state == s) c[DELEXT] += 1;
+        else { c[DEL] += 1; c[DELTIME] += lDelWait; }
+      }
+      break;
+    case HIST_IMI:
+      if (!yNull) {
+        if (src.state == s) c[INSEXT] += 1;
+        else { c[INS] += 1; c[INSTIME] += rInsWait; }
+      }
+      break;
+    default: break;
+  }
+}
+
+// The indel counts of the effective transitions of makeProfile (forward.cpp:753-790): the elimination of
+// oracle_profile_eliminate with an indel count vector per effective transition -- transitionEigenCounts for a direct
+// transition, and for every path through an eliminated cell the reference's running posterior mixture
+// (counts *= 1 - pp; counts += (src counts + cell->dest counts) * pp).  out [n_trans][6], transitions in the order
+// oracle_profile_eliminate returns them (the first n_trans transitions of the profile after addReadyStates).
+int oracle_eliminate_indel_counts(const hist_profile_desc* x, const hist_profile_desc* y, const hist_pairhmm_desc* hmm,
+                                  const hist_env_desc* env, const hist_cell* cells_in, int64_t n_cells, int32_t strategy,
+                                  const double* x_tc, const double* y_tc, const double* waits, double* out, int64_t capacity,
+                                  int64_t* n_trans) {
+  DP dp(x, y, hmm, env);
+  std::set<CellCoords> cells;
+  for (int64_t k = 0; k < n_cells; ++k) cells.insert({cells_in[k].xpos, cells_in[k].ypos, cells_in[k].state});
+  const CellCoords startCell{0, 0, HIST_IMM}, endCell{dp.xSize - 1, dp.ySize - 1, HIST_EEE};
+  if (!cells.count(startCell) || !cells.count(endCell)) return HIST_ERR_ARG;
+  std::map<CellCoords, int> profStateIndex, outgoing;
+  for (const auto& dest : cells)
+    for (const auto& kv : dp.sourceTransitions(dest)) ++outgoing[kv.first];
+  int n_states = 0;
+  for (const auto& c : cells)
+    if (dp.isAbsorbing(c) || c == startCell || c == endCell || outgoing[c] > 1 || (strategy & HIST_KEEP_GAPS_OPEN) != 0 ||
+        (strategy & HIST_COLLAPSE_CHAINS) == 0)
+      profStateIndex[c] = n_states++;
+  struct Eff { double lpPath = NEG_INF; double cnt[6] = {0, 0, 0, 0, 0, 0}; };
+  std::map<CellCoords, std::map<int, Eff>> effTrans;
+  for (auto it = cells.crbegin(); it != cells.crend(); ++it) {
+    const CellCoords& iterCell = *it;
+    const auto slp = dp.sourceTransNoEmit(iterCell);
+    const double ins = dp.eliminatedLogProbInsert(iterCell);
+    auto found = profStateIndex.find(iterCell);
+    if (found != profStateIndex.end()) {
+      for (const auto& kv : slp) {
+        Eff& eff = effTrans[kv.first][found->second];
+        eff.lpPath = kv.second + ins;
+        indel_transition_counts(dp, kv.first, iterCell, x_tc, y_tc, waits, eff.cnt);
+      }
+    } else {
+      const auto cellEff = effTrans[iterCell];
+      for (const auto& kv : slp) {
+        double srcCell[6];
+        indel_transition_counts(dp, kv.first, iterCell, x_tc, y_tc, waits, srcCell);
+        auto& srcEff = effTrans[kv.first];
+        for (const auto& ce : cellEff) {
+          Eff& sd = srcEff[ce.first];
+          const double lpPath = kv.second + ins + ce.second.lpPath;
+          lacc(sd.lpPath, lpPath);
+          const double pp = std::exp(lpPath - sd.lpPath);
+          for (int q = 0; q < 6; ++q) sd.cnt[q] = sd.cnt[q] * (1 - pp) + (srcCell[q] + ce.second.cnt[q]) * pp;
+        }
+      }
+    }
+  }
+  int64_t nt = 0;
+  for (const auto& ps : profStateIndex)
+    for (const auto& et : effTrans[ps.first]) {
+      if (nt < capacity)
+        for (int q = 0; q < 6; ++q) out[nt * 6 + q] = et.second.cnt[q];
+      ++nt;
+    }
+  *n_trans = nt;
+  return nt > capacity ? HIST_ERR_CAPACITY : 0;
+}
+
+// The indel half of BackwardMatrix::getCounts (forward.cpp:1183-1214) WITH counts carried by the children's transitions
+// (forward.cpp:579-583): for every cell and every source transition, posterior weight x transitionEigenCounts' indel part
+// (forward.cpp:579-652).  x_tc / y_tc: [n_trans][6] = ins, del, insExt, delExt, insTime, delTime of every transition of x / y
+// (NULL: none); waits = hmm.l.t, hmm.r.t, l.insWait, l.delWait, r.insWait, r.delWait.  out[7]: the six sums and lp = lpEnd.
+// The substitution half needs the reference's per-position cache of column counts (forward.cpp:903-917) and is not restated.
+int oracle_fb_indel_counts(const hist_profile_desc* x, const hist_profile_desc* y, const hist_pairhmm_desc* hmm,
+                           const hist_env_desc* env, const double* x_tc, const double* y_tc, const double* waits, double* out) {
+  DP dp(x, y, hmm, env);
+  const size_t n = (size_t)(dp.xSize - 1) * (dp.ySize - 1) * 5;
+  std::vector<double> fwd(n), bwd(n);
+  DP db(x, y, hmm, env);
+  db.fillBackward(bwd.data());
+  dp.fillForward(fwd.data());   // dp.cells = fwd: dp.cell() reads the Forward matrix
+  const double lpEnd = dp.lpEnd;
+  double tot[6] = {0, 0, 0, 0, 0, 0};
+  for (int i = 0; i < dp.xSize - 1; ++i)
+    for (int j = 0; j < dp.ySize - 1; ++j) {
+      if (!dp.inEnvelope(i, j)) continue;
+      for (int s = 0; s < 5; ++s) {
+        const CellCoords dest{i, j, s};
+        const double lpDest = bwd[dp.idx(i, j, s)];
+        if (!(lpDest > NEG_INF)) continue;
+        for (const auto& kv : dp.sourceTransitions(dest)) {
+          const CellCoords& src = kv.first;
+          const double w = std::exp(dp.cell(src) + kv.second + lpDest - lpEnd);
+          if (!(w > 0)) continue;
+          double c[6];
+          indel_transition_counts(dp, src, dest, x_tc, y_tc, waits, c);
+          for (int q = 0; q < 6; ++q) tot[q] += c[q] * w;
+        }
+      }
+    }
+  for (int q = 0; q < 6; ++q) out[q] = tot[q];
+  out[6] = lpEnd;
+  return 0;
+}
+
 // Numeric core of makeProfile, forward.cpp:686-843 (states, effective transitions).
 int oracle_profile_eliminate(const hist_profile_desc* x, const hist_profile_desc* y, const hist_pairhmm_desc* hmm,
                              const hist_env_desc* env, double* fwd_cells, double lp_end, const hist_cell* cells_in,

@@ -412,6 +412,14 @@ int main(int argc, char** argv) {
       for (size_t s = 0; s < nodeProf.size(); ++s)
         cum.push_back(s == 0 ? 0. : atof(nodeProf.state[s].meta.count("cumLogProb") ? nodeProf.state[s].meta.at("cumLogProb").c_str() : "0"));
       putD(pfx + "parent.cum_lp6", cum);
+      if (propagate) {   // the indel counts every transition of the new profile carries (forward.cpp:764-765, 779-790, 825-826)
+        vector<double> tIndel;
+        for (const auto& t : nodeProf.trans) {
+          const IndelCounts& ic = t.counts.indelCounts;
+          for (double v : {ic.ins, ic.del, ic.insExt, ic.delExt, ic.insTime, ic.delTime, ic.lp}) tIndel.push_back(v);
+        }
+        putD(pfx + "parent.trans_indel", tIndel, {(uint64_t)nodeProf.trans.size(), 7});
+      }
     }
     if (backward) delete backward;
     delete forward;

@@ -15,7 +15,7 @@ SPARSE = ("gp120_nodes.npz", "lg16x300_n14.npz")
 
 def golden_files(sparse=False):
     return sorted(f for f in glob.glob(os.path.join(GOLDEN_DIR, "*.npz"))
-                  if not os.path.basename(f).startswith(("sumprod_", "fbcounts_", "quickalign_", "distmat_", "guide_")) and (os.path.basename(f) in SPARSE) == sparse)
+                  if not os.path.basename(f).startswith(("sumprod_", "fbcounts_", "quickalign_", "distmat_", "guide_", "elimcounts_")) and (os.path.basename(f) in SPARSE) == sparse)
 
 
 def load_golden(path):

@@ -271,3 +271,33 @@ def build_tree(dist, method=0, min_branch_length=1e-9):
     rc = lib().oracle_build_tree(n, _p(dist, C.c_double), int(method), C.c_double(float(min_branch_length)), _p(child, C.c_int32), _p(blen, C.c_double))
     assert rc == 0
     return child, blen
+
+
+def fb_indel_counts(x, y, hmm, env, x_trans_indel, y_trans_indel, waits):
+    """The indel half of BackwardMatrix::getCounts (forward.cpp:1183-1214) with counts on the children's transitions
+    ([n_trans][6] or None).  Returns [ins, del, insExt, delExt, insTime, delTime, lp]."""
+    xd, yd, hd, ed = x.desc(), y.desc(), hmm.desc(), env.desc()
+    xt = None if x_trans_indel is None else np.ascontiguousarray(x_trans_indel, np.float64)
+    yt = None if y_trans_indel is None else np.ascontiguousarray(y_trans_indel, np.float64)
+    w = np.ascontiguousarray(waits, np.float64)
+    out = np.zeros(7)
+    rc = lib().oracle_fb_indel_counts(C.byref(xd), C.byref(yd), C.byref(hd), C.byref(ed), _p(xt, C.c_double), _p(yt, C.c_double),
+                                      _p(w, C.c_double), _p(out, C.c_double))
+    assert rc == 0
+    return out
+
+
+def eliminate_indel_counts(x, y, hmm, env, cells, strategy, x_trans_indel, y_trans_indel, waits):
+    """Indel counts of makeProfile's effective transitions (forward.cpp:753-790), [n_trans][6] in oracle_profile_eliminate's order."""
+    xd, yd, hd, ed = x.desc(), y.desc(), hmm.desc(), env.desc()
+    cells = np.ascontiguousarray(cells, np.int32).reshape(-1, 3)
+    xt = None if x_trans_indel is None else np.ascontiguousarray(x_trans_indel, np.float64)
+    yt = None if y_trans_indel is None else np.ascontiguousarray(y_trans_indel, np.float64)
+    w = np.ascontiguousarray(waits, np.float64)
+    cap = 4 * len(cells) + 16
+    out, n = np.zeros((cap, 6)), C.c_int64()
+    rc = lib().oracle_eliminate_indel_counts(C.byref(xd), C.byref(yd), C.byref(hd), C.byref(ed), cells.ctypes.data_as(C.c_void_p), C.c_int64(len(cells)),
+                                             C.c_int32(int(strategy)), _p(xt, C.c_double), _p(yt, C.c_double), _p(w, C.c_double), _p(out, C.c_double),
+                                             C.c_int64(cap), C.byref(n))
+    assert rc == 0, rc
+    return out[:n.value]

@@ -75,3 +75,65 @@ def test_count_propagation_fixtures_state_the_open_target():
         assert pi[6] == bi[6]                                                                # lp = the root's Forward likelihood
         assert np.all(pi[:6] >= bi[:6] - 1e-9) and pi[4] > bi[4] and pi[5] > bi[5]           # wait times of every branch, not two
         assert d[pfx + "fbc.sub_count"].sum() >= base[pfx + "fbc.sub_count"].sum() - 1e-9
+
+
+def test_oracle_indel_counts_with_transition_counts_equal_the_reference():
+    """oracle_fb_indel_counts -- the indel half of getCounts with the children's per-transition counts (forward.cpp:579-583,
+    1183-1214) -- against the reference on all eight tree fixtures: the count-free runs (transitions carry nothing) and the
+    runs made with the Count* strategy bits, whose per-transition counts the fixtures hold.  The exact-arithmetic builds
+    must agree to 1e-9; the table builds to the table's error.  This pins the oracle for the open part of B3's indel side."""
+    import glob
+    import os
+    import helpers as H
+    import oracle_lib as O
+    paths = sorted(glob.glob(os.path.join(H.GOLDEN_DIR, "fbcounts_*tree*.npz")))
+    assert len(paths) == 8
+    for path in paths:
+        d = H.load_golden(path)
+        root = int(d["root"][0])
+        pfx = "n%d." % root
+        x, y, hmm, env = H.node_inputs(d, root)
+        prop = "_prop_" in os.path.basename(path)
+        xt = d[pfx + "x.trans_indel"][:, :6] if prop else None
+        yt = d[pfx + "y.trans_indel"][:, :6] if prop else None
+        exact = path.endswith("_exact.npz")
+        O.set_exact_lse(exact)
+        try:
+            got = O.fb_indel_counts(x, y, hmm, env, xt, yt, d[pfx + "fbc.waits"])
+        finally:
+            O.set_exact_lse(False)
+        want = d[pfx + "fbc.indel"]
+        tol = 1e-9 if exact else 2e-3
+        assert abs(got[6] - want[6]) <= 1e-9 * abs(want[6]), path
+        assert np.allclose(got[:6], want[:6], rtol=tol, atol=tol), (os.path.basename(path), got, want)
+
+
+def test_oracle_counts_through_make_profile_equal_the_reference():
+    """oracle_eliminate_indel_counts -- makeProfile's count propagation (forward.cpp:753-790), indel part -- against the
+    reference on every non-root merge of the two tree families (tests/golden/elimcounts_*_best.npz: best-trace profiles
+    built with the Count* strategy bits): cherries (children without counts) and internal merges whose children's
+    transitions already carry counts.  The parent's first n transitions are the effective transitions in elimination order
+    (addReadyStates appends its own, count-free ones)."""
+    import glob
+    import os
+    import helpers as H
+    import oracle_lib as O
+    paths = sorted(glob.glob(os.path.join(H.GOLDEN_DIR, "elimcounts_*_best.npz")))
+    assert len(paths) == 2
+    checked = with_child_counts = 0
+    for path in paths:
+        d = H.load_golden(path)
+        nodes = [int(v) for v in d["dumped_nodes"]]
+        for node in nodes[:-1]:   # the root's profile is built without counts (recon.cpp:1009)
+            pfx = "n%d." % node
+            x, y, hmm, env = H.node_inputs(d, node)
+            xt, yt = d[pfx + "x.trans_indel"][:, :6], d[pfx + "y.trans_indel"][:, :6]
+            got = O.eliminate_indel_counts(x, y, hmm, env, d[pfx + "best_trace"], int(d["strategy"][0]), xt, yt, d[pfx + "fbc.waits"])
+            want = d[pfx + "parent.trans_indel"]
+            n = len(got)
+            assert n <= len(want) and np.all(want[n:, :6] == 0), (path, node)     # the ready transitions carry nothing
+            assert np.allclose(got, want[:n, :6], rtol=1e-9, atol=1e-12), (os.path.basename(path), node)
+            assert want[:n, :6].sum() > 0
+            checked += 1
+            with_child_counts += bool(xt.sum() + yt.sum() > 0)
+    assert checked == 6 and with_child_counts >= 2

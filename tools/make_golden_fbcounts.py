@@ -97,6 +97,36 @@ def main(sfx=""):
         print(name, "x", len(d["x_seq"]), "y", len(d["y_seq"]), "lp_end %.4f" % d["lp_end"][0], "indel", np.round(d["indel"], 4))
 
 
+
+
+def elim_count_cases():
+    """tests/golden/elimcounts_*_best.npz: every merge of the two tree families in `best` mode (one trace per profile) with the
+    Count* strategy bits: inputs of makeProfile (child profiles with the indel counts their transitions carry, PairHMM,
+    envelope, the best trace = the cell set) and its output (the parent's transitions and THEIR indel counts,
+    forward.cpp:753-790) -- the pin of oracle_eliminate_indel_counts."""
+    import make_golden as G
+    keep = ("x.", "y.", "hmm.", "env.", "best_trace", "parent.dims", "parent.trans_src", "parent.trans_dest", "parent.trans_lp", "parent.trans_indel",
+            "fbc.waits", "children", "lp_end")
+    for name, n, bl, spec, gen, rec in TREE_CASES:
+        with tempfile.TemporaryDirectory() as tmp:
+            tf, gf = G.simulate(tmp, G.balanced(n, bl), gen, n)
+            binf = os.path.join(tmp, "d.bin")
+            subprocess.run([os.path.join(BIN, "ref_dump"), binf, "all", "best", "-guide", gf, "-tree", tf] + rec, check=True, cwd=G.REF,
+                           env=dict(os.environ, REF_DUMP_COUNTS="2"), stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+            d = D.read_dump(binf)
+        out = {"preset": spec, "dumped_nodes": d["dumped_nodes"], "strategy": d["strategy"]}
+        for k, v in d.items():
+            if k.startswith("n") and "." in k and k.split(".", 1)[1].startswith(keep):
+                if k.endswith(("trans_root_count", "trans_sub_count", "align_col", "lp_absorb")) and not k.endswith("lp_absorb"):
+                    continue
+                out[k] = v
+        out = {k: (np.frombuffer(v.encode(), np.uint8) if isinstance(v, str) else v) for k, v in out.items()}
+        fn = os.path.join(OUT, name.replace("fbcounts_", "elimcounts_") + "_best.npz")
+        np.savez_compressed(fn, **out)
+        print(os.path.basename(fn), "nodes", list(d["dumped_nodes"]), "%.1f kB" % (os.path.getsize(fn) / 1e3))
+
+
 if __name__ == "__main__":
     main()
     main("_exact")
+    elim_count_cases()
